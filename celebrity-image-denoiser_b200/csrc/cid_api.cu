@@ -1,0 +1,576 @@
+// C-ABI entry points (include/cid_b200.h): context, weight packing, execution plans and the
+// layer-by-layer launch sequence of the denoise generator.
+//
+// Layer table (reference: backend/app.py:42-78, forward :80-103):
+//   L0  down1.0       conv3x3   3->64   +ReLU            first_conv_kernel      -> a0
+//   L1  down1.2       conv3x3  64->64   +ReLU +pool      <64 ,9,1,WRES,POOL>    -> cat1[:,64:128], p1
+//   L2  down2.0       conv3x3  64->128  +ReLU            <128,9,1,WRES,RELU>    -> a2
+//   L3  down2.2       conv3x3 128->128  +ReLU +pool      <128,9,2,ring,POOL>    -> cat2[:,128:256], p2
+//   L4  bottleneck.0  conv3x3 128->256  +ReLU            <256,9,1,ring,RELU>    -> b0
+//   L5  bottleneck.2  conv3x3 256->256  +ReLU            <256,9,1,ring,RELU>    -> b1
+//   L6  up2           convT2x2 256->128                  <256,1,1,ring,CONVT>   -> cat2[:,0:128]
+//   L7  upconv2.0     conv3x3 256->128  +ReLU            <128,9,2,ring,RELU>    -> u2a
+//   L8  upconv2.2     conv3x3 128->128  +ReLU            <128,9,2,ring,RELU>    -> u2b
+//   L9  up1           convT2x2 128->64                   <256,1,1,ring,CONVT>   -> cat1[:,0:64]
+//   L10 upconv1.0     conv3x3 128->64   +ReLU            <64 ,9,1,WRES,RELU>    -> u1a
+//   L11 upconv1.2     conv3x3  64->3    +tanh            <16 ,9,1,WRES,TANH_*>  -> y
+#include <cuda_bf16.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "cid_internal.h"
+#include "conv_umma.cuh"
+#include "edge_kernels.cuh"
+
+namespace cid {
+
+static thread_local char g_err[1024] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+// ---------------------------------------------------------------------------------------------
+// layer table
+// ---------------------------------------------------------------------------------------------
+enum LayerKind { L_FIRST, L_CONV, L_CONVT };
+struct LayerDesc {
+    const char* name;
+    LayerKind kind;
+    int cin, cout;
+};
+static const LayerDesc kLayers[12] = {
+    {"down1.0", L_FIRST, 3, 64},        {"down1.2", L_CONV, 64, 64},       {"down2.0", L_CONV, 64, 128},
+    {"down2.2", L_CONV, 128, 128},      {"bottleneck.0", L_CONV, 128, 256}, {"bottleneck.2", L_CONV, 256, 256},
+    {"up2", L_CONVT, 256, 128},         {"upconv2.0", L_CONV, 256, 128},   {"upconv2.2", L_CONV, 128, 128},
+    {"up1", L_CONVT, 128, 64},          {"upconv1.0", L_CONV, 128, 64},    {"upconv1.2", L_CONV, 64, 3},
+};
+
+// activation buffers inside the workspace
+enum Buf { B_A0, B_CAT1, B_P1, B_A2, B_CAT2, B_P2, B_B0, B_B1, B_U2A, B_U2B, B_U1A, B_COUNT };
+static const char* kBufNames[B_COUNT] = {"a0", "cat1", "p1", "a2", "cat2", "p2", "b0", "b1", "u2a", "u2b", "u1a"};
+static const int kBufC[B_COUNT] = {64, 128, 64, 128, 256, 128, 256, 256, 128, 128, 64};
+static const int kBufLevel[B_COUNT] = {0, 0, 1, 1, 1, 2, 2, 2, 1, 1, 0};  // spatial dims >> level
+
+static size_t buf_bytes(int buf, int B, int H, int W) {
+    const int lv = kBufLevel[buf];
+    size_t n = static_cast<size_t>(B) * (H >> lv) * (W >> lv) * kBufC[buf] * 2;
+    return (n + 1023) & ~static_cast<size_t>(1023);
+}
+
+static size_t layout_offsets(int B, int H, int W, size_t* off) {
+    size_t cur = 0;
+    for (int i = 0; i < B_COUNT; ++i) {
+        if (off) off[i] = cur;
+        cur += buf_bytes(i, B, H, W);
+    }
+    return cur;
+}
+
+// ---------------------------------------------------------------------------------------------
+// TMA descriptors
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// NHWC bf16 activation [B,H,W,C]: box = 64 channels x 8 pixels x box_rows rows x 1 image, 128B swizzle.
+static int make_act_map(CUtensorMap* tm, const void* base, int B, int H, int W, int C, int box_rows) {
+    EncodeTiledFn fn = get_encode_fn();
+    CID_REQUIRE(fn, "cuTensorMapEncodeTiled entry point not available");
+    cuuint64_t dims[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H),
+                          static_cast<cuuint64_t>(B)};
+    cuuint64_t strides[3] = {static_cast<cuuint64_t>(C) * 2, static_cast<cuuint64_t>(W) * C * 2,
+                             static_cast<cuuint64_t>(H) * W * C * 2};
+    cuuint32_t box[4] = {64, 8, static_cast<cuuint32_t>(box_rows), 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CID_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(activation %dx%dx%dx%d) failed: %d", B, H, W, C,
+                static_cast<int>(r));
+    return 0;
+}
+
+// packed weights [rows, Cin] bf16 (Cin contiguous): box = 64 x box_rows, 128B swizzle.
+static int make_weight_map(CUtensorMap* tm, const void* base, int rows, int cin, int box_rows) {
+    EncodeTiledFn fn = get_encode_fn();
+    CID_REQUIRE(fn, "cuTensorMapEncodeTiled entry point not available");
+    cuuint64_t dims[2] = {static_cast<cuuint64_t>(cin), static_cast<cuuint64_t>(rows)};
+    cuuint64_t strides[1] = {static_cast<cuuint64_t>(cin) * 2};
+    cuuint32_t box[2] = {64, static_cast<cuuint32_t>(box_rows)};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CID_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(weights %dx%d) failed: %d", rows, cin, static_cast<int>(r));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// host-side weight packing
+// ---------------------------------------------------------------------------------------------
+static uint16_t f32_to_bf16_rne(float f) {
+    uint32_t u;
+    memcpy(&u, &f, 4);
+    if ((u & 0x7fffffffu) > 0x7f800000u) return static_cast<uint16_t>((u >> 16) | 0x40);  // NaN
+    u += 0x7fffu + ((u >> 16) & 1u);
+    return static_cast<uint16_t>(u >> 16);
+}
+
+// per-layer tensor-core tile width N and padded row count per tap
+static int layer_n(int l) {
+    switch (l) {
+        case 1: case 10: return 64;
+        case 2: case 3: case 7: case 8: return 128;
+        case 4: case 5: case 6: case 9: return 256;
+        case 11: return 16;
+        default: return 0;
+    }
+}
+
+static int pack_layer(cid_ctx* c, int l) {
+    const LayerDesc& L = kLayers[l];
+    const std::string wkey = std::string(L.name) + ".weight";
+    const std::string bkey = std::string(L.name) + ".bias";
+    auto wi = c->params.find(wkey);
+    auto bi = c->params.find(bkey);
+    CID_REQUIRE(wi != c->params.end() && bi != c->params.end(), "missing parameter for layer %s", L.name);
+    const std::vector<float>& w = wi->second;
+    const std::vector<float>& b = bi->second;
+
+    if (L.kind == L_FIRST) {
+        if (!c->first_w_host) c->first_w_host = new FirstConvW();
+        FirstConvW* fw = static_cast<FirstConvW*>(c->first_w_host);
+        for (int co = 0; co < 64; ++co) {
+            for (int t = 0; t < 27; ++t) fw->w[t][co] = w[static_cast<size_t>(co) * 27 + t];  // [co][ci][ky][kx]
+            fw->b[co] = b[co];
+        }
+        return 0;
+    }
+
+    std::vector<uint16_t> packed;
+    int rows = 0;
+    if (L.kind == L_CONV) {
+        const int npad = std::max(L.cout, 16);
+        rows = 9 * npad;
+        packed.assign(static_cast<size_t>(rows) * L.cin, 0);
+        for (int co = 0; co < L.cout; ++co)
+            for (int ci = 0; ci < L.cin; ++ci)
+                for (int t = 0; t < 9; ++t)
+                    packed[(static_cast<size_t>(t) * npad + co) * L.cin + ci] =
+                        f32_to_bf16_rne(w[(static_cast<size_t>(co) * L.cin + ci) * 9 + t]);
+    } else {  // ConvTranspose2d weight [Cin, Cout, 2, 2] -> rows (dy*2+dx)*Cout + co
+        rows = 4 * L.cout;
+        packed.assign(static_cast<size_t>(rows) * L.cin, 0);
+        for (int ci = 0; ci < L.cin; ++ci)
+            for (int co = 0; co < L.cout; ++co)
+                for (int qd = 0; qd < 4; ++qd)
+                    packed[(static_cast<size_t>(qd) * L.cout + co) * L.cin + ci] =
+                        f32_to_bf16_rne(w[(static_cast<size_t>(ci) * L.cout + co) * 4 + qd]);
+    }
+    if (c->w_dev[l]) cudaFree(c->w_dev[l]);
+    if (c->bias_dev[l]) cudaFree(c->bias_dev[l]);
+    c->w_dev[l] = nullptr;
+    c->bias_dev[l] = nullptr;
+    CID_CHECK_CUDA(cudaMalloc(&c->w_dev[l], packed.size() * 2));
+    CID_CHECK_CUDA(cudaMemcpy(c->w_dev[l], packed.data(), packed.size() * 2, cudaMemcpyHostToDevice));
+    // bias padded to a multiple of 32 floats so float4 epilogue loads never run off the end
+    std::vector<float> bp((b.size() + 31) / 32 * 32, 0.f);
+    std::copy(b.begin(), b.end(), bp.begin());
+    CID_CHECK_CUDA(cudaMalloc(reinterpret_cast<void**>(&c->bias_dev[l]), bp.size() * 4));
+    CID_CHECK_CUDA(cudaMemcpy(c->bias_dev[l], bp.data(), bp.size() * 4, cudaMemcpyHostToDevice));
+    return make_weight_map(&c->tmW[l], c->w_dev[l], rows, L.cin, layer_n(l));
+}
+
+// ---------------------------------------------------------------------------------------------
+// plans
+// ---------------------------------------------------------------------------------------------
+static int layer_in_buf(int l) {
+    static const int in[12] = {-1, B_A0, B_P1, B_A2, B_P2, B_B0, B_B1, B_CAT2, B_U2A, B_U2B, B_CAT1, B_U1A};
+    return in[l];
+}
+
+static int get_plan(cid_ctx* c, int Bc, int H, int W, const void* ws, cid_plan** out) {
+    for (auto& pl : c->plans)
+        if (pl.Bc == Bc && pl.H == H && pl.W == W && pl.ws == ws) {
+            *out = &pl;
+            return 0;
+        }
+    if (c->plans.size() >= 64) c->plans.clear();
+    cid_plan pl;
+    pl.Bc = Bc;
+    pl.H = H;
+    pl.W = W;
+    pl.ws = ws;
+    layout_offsets(Bc, H, W, pl.off);
+    for (int l = 1; l < 12; ++l) {
+        const int buf = layer_in_buf(l);
+        const int lv = kBufLevel[buf];
+        const int rows = kLayers[l].kind == L_CONVT ? 16 : 18;
+        if (make_act_map(&pl.tmA[l], static_cast<const uint8_t*>(ws) + pl.off[buf], Bc, H >> lv, W >> lv, kBufC[buf],
+                         rows))
+            return 1;
+    }
+    c->plans.push_back(pl);
+    *out = &c->plans.back();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// launches
+// ---------------------------------------------------------------------------------------------
+template <int N, int TAPS, int S, bool WRES, int EPI>
+static int launch_conv(cid_ctx* c, int slot, const CUtensorMap& tmA, const CUtensorMap& tmW, ConvParams p,
+                       cudaStream_t st) {
+    using Cfg = ConvCfg<N, TAPS, S, WRES, EPI>;
+    const int budget = c->max_smem - 1024 - 512;
+    int w_stages = WRES ? 1 : 4;
+    const int w_bytes = (WRES ? p.kb_count * TAPS : w_stages) * Cfg::W_BYTES;
+    int a_stages = std::min(kMaxStages, (budget - w_bytes) / Cfg::A_BYTES);
+    CID_REQUIRE(a_stages >= S + 1, "conv<%d,%d,%d>: shared memory too small (%d stages)", N, TAPS, S, a_stages);
+    p.a_stages = a_stages;
+    p.w_stages = w_stages;
+    p.tiles_x = (p.W + 7) / 8;
+    p.tiles_y = (p.H + 15) / 16;
+    p.m_tiles = p.B * p.tiles_x * p.tiles_y;
+    p.num_work = ((p.m_tiles + S - 1) / S) * p.n_tiles;
+    const int smem = Cfg::smem_bytes(p.kb_count, a_stages, w_stages);
+    auto kern = conv_umma_kernel<N, TAPS, S, WRES, EPI>;
+    if (!(c->attr_done & (1u << slot))) {
+        CID_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c->max_smem));
+        c->attr_done |= (1u << slot);
+    }
+    const int grid = std::min(p.num_work, c->num_sms);
+    kern<<<grid, kConvThreads, smem, st>>>(tmA, tmW, p);
+    CID_CHECK_CUDA(cudaGetLastError());
+    c->launches++;
+    return 0;
+}
+
+struct IoSpec {
+    bool u8;
+    const void* x;
+    void* y;
+    int in_h, in_w, pad_l, pad_t;  // u8 mode
+};
+
+// one pass of nb (<= plan.Bc) images through the 12 layers
+static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaStream_t st) {
+    const int H = pl->H, W = pl->W;
+    uint8_t* ws = static_cast<uint8_t*>(const_cast<void*>(pl->ws));
+    auto buf = [&](int b) { return reinterpret_cast<__nv_bfloat16*>(ws + pl->off[b]); };
+
+    // L0
+    {
+        FirstConvParams fp;
+        fp.B = nb;
+        fp.H = H;
+        fp.W = W;
+        fp.in = io.x;
+        fp.in_h = io.in_h;
+        fp.in_w = io.in_w;
+        fp.pad_l = io.pad_l;
+        fp.pad_t = io.pad_t;
+        fp.out = buf(B_A0);
+        const size_t total = static_cast<size_t>(nb) * H * W;
+        const unsigned grid = static_cast<unsigned>((total + 127) / 128);
+        const FirstConvW& fw = *static_cast<const FirstConvW*>(c->first_w_host);
+        if (io.u8)
+            first_conv_kernel<true><<<grid, 128, 0, st>>>(fw, fp);
+        else
+            first_conv_kernel<false><<<grid, 128, 0, st>>>(fw, fp);
+        CID_CHECK_CUDA(cudaGetLastError());
+        c->launches++;
+    }
+
+    auto base = [&](int l, int lv) {
+        ConvParams p;
+        memset(&p, 0, sizeof(p));
+        p.B = nb;
+        p.H = H >> lv;
+        p.W = W >> lv;
+        p.kb_count = kLayers[l].cin / 64;
+        p.n_tiles = 1;
+        p.bias = c->bias_dev[l];
+        p.cout = kLayers[l].cout;
+        p.w_rows_per_tap = std::max(kLayers[l].cout, 16);
+        return p;
+    };
+
+    {  // L1 down1.2 -> cat1[:,64:128] + p1
+        ConvParams p = base(1, 0);
+        p.out = buf(B_CAT1); p.out_cs = 128; p.out_c0 = 64;
+        p.out2 = buf(B_P1); p.out2_cs = 64; p.out2_c0 = 0;
+        if (launch_conv<64, 9, 1, true, EPI_RELU_POOL>(c, 0, pl->tmA[1], c->tmW[1], p, st)) return 1;
+    }
+    {  // L2 down2.0 -> a2
+        ConvParams p = base(2, 1);
+        p.out = buf(B_A2); p.out_cs = 128; p.out_c0 = 0;
+        if (launch_conv<128, 9, 1, true, EPI_RELU>(c, 1, pl->tmA[2], c->tmW[2], p, st)) return 1;
+    }
+    {  // L3 down2.2 -> cat2[:,128:256] + p2
+        ConvParams p = base(3, 1);
+        p.out = buf(B_CAT2); p.out_cs = 256; p.out_c0 = 128;
+        p.out2 = buf(B_P2); p.out2_cs = 128; p.out2_c0 = 0;
+        if (launch_conv<128, 9, 2, false, EPI_RELU_POOL>(c, 2, pl->tmA[3], c->tmW[3], p, st)) return 1;
+    }
+    {  // L4 bottleneck.0 -> b0
+        ConvParams p = base(4, 2);
+        p.out = buf(B_B0); p.out_cs = 256; p.out_c0 = 0;
+        if (launch_conv<256, 9, 1, false, EPI_RELU>(c, 3, pl->tmA[4], c->tmW[4], p, st)) return 1;
+    }
+    {  // L5 bottleneck.2 -> b1
+        ConvParams p = base(5, 2);
+        p.out = buf(B_B1); p.out_cs = 256; p.out_c0 = 0;
+        if (launch_conv<256, 9, 1, false, EPI_RELU>(c, 3, pl->tmA[5], c->tmW[5], p, st)) return 1;
+    }
+    {  // L6 up2 (convT) -> cat2[:,0:128]
+        ConvParams p = base(6, 2);
+        p.n_tiles = 2;  // 4*128 columns in tiles of 256
+        p.out = buf(B_CAT2); p.out_cs = 256; p.out_c0 = 0;
+        if (launch_conv<256, 1, 1, false, EPI_CONVT>(c, 4, pl->tmA[6], c->tmW[6], p, st)) return 1;
+    }
+    {  // L7 upconv2.0 (reads cat2) -> u2a
+        ConvParams p = base(7, 1);
+        p.out = buf(B_U2A); p.out_cs = 128; p.out_c0 = 0;
+        if (launch_conv<128, 9, 2, false, EPI_RELU>(c, 5, pl->tmA[7], c->tmW[7], p, st)) return 1;
+    }
+    {  // L8 upconv2.2 -> u2b
+        ConvParams p = base(8, 1);
+        p.out = buf(B_U2B); p.out_cs = 128; p.out_c0 = 0;
+        if (launch_conv<128, 9, 2, false, EPI_RELU>(c, 5, pl->tmA[8], c->tmW[8], p, st)) return 1;
+    }
+    {  // L9 up1 (convT) -> cat1[:,0:64]
+        ConvParams p = base(9, 1);
+        p.n_tiles = 1;  // 4*64 columns in one tile of 256
+        p.out = buf(B_CAT1); p.out_cs = 128; p.out_c0 = 0;
+        if (launch_conv<256, 1, 1, false, EPI_CONVT>(c, 4, pl->tmA[9], c->tmW[9], p, st)) return 1;
+    }
+    {  // L10 upconv1.0 (reads cat1) -> u1a
+        ConvParams p = base(10, 0);
+        p.out = buf(B_U1A); p.out_cs = 64; p.out_c0 = 0;
+        if (launch_conv<64, 9, 1, true, EPI_RELU>(c, 6, pl->tmA[10], c->tmW[10], p, st)) return 1;
+    }
+    {  // L11 upconv1.2 + tanh -> y
+        ConvParams p = base(11, 0);
+        p.out = io.y;
+        if (io.u8) {
+            p.crop_l = io.pad_l; p.crop_t = io.pad_t; p.out_h = io.in_h; p.out_w = io.in_w;
+            if (launch_conv<16, 9, 1, true, EPI_TANH_U8>(c, 7, pl->tmA[11], c->tmW[11], p, st)) return 1;
+        } else {
+            if (launch_conv<16, 9, 1, true, EPI_TANH_F32>(c, 8, pl->tmA[11], c->tmW[11], p, st)) return 1;
+        }
+    }
+    return 0;
+}
+
+static int chunk_of(const cid_ctx* c, int B) {
+    return (c->chunk > 0 && c->chunk < B) ? static_cast<int>(c->chunk) : B;
+}
+
+static int forward_common(cid_ctx* c, int B, int H, int W, void* ws, size_t ws_bytes, cudaStream_t st,
+                          const uint8_t* x, size_t x_img_bytes, uint8_t* y, size_t y_img_bytes, IoSpec io) {
+    CID_REQUIRE(c && c->finalized, "generator not finalized (call cid_set_param for all 24 tensors, then cid_finalize)");
+    CID_REQUIRE(B >= 1 && H >= 4 && W >= 4, "bad shape B=%d H=%d W=%d", B, H, W);
+    CID_REQUIRE(H % 4 == 0 && W % 4 == 0, "network input %dx%d must be multiples of 4 (get_padding, app.py:276)", H,
+                W);
+    CID_REQUIRE(x && y && ws, "null pointer argument");
+    CID_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 1023) == 0, "workspace must be 1024-byte aligned");
+    DeviceGuard g(c->device);
+    CID_REQUIRE(g.ok, "cannot select CUDA device %d", c->device);
+    const int Bc = chunk_of(c, B);
+    const size_t need = layout_offsets(Bc, H, W, nullptr);
+    CID_REQUIRE(ws_bytes >= need, "workspace too small: %zu < %zu bytes", ws_bytes, need);
+    cid_plan* pl = nullptr;
+    if (get_plan(c, Bc, H, W, ws, &pl)) return 1;
+    for (int b0 = 0; b0 < B; b0 += Bc) {
+        const int nb = std::min(Bc, B - b0);
+        io.x = x + static_cast<size_t>(b0) * x_img_bytes;
+        io.y = y + static_cast<size_t>(b0) * y_img_bytes;
+        if (run_layers(c, pl, nb, io, st)) return 1;
+    }
+    return 0;
+}
+
+}  // namespace cid
+
+using namespace cid;
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+extern "C" {
+
+int cid_version(void) { return 1; }
+
+const char* cid_last_error(void) { return g_err; }
+
+int cid_create(int device, cid_handle* out) {
+    CID_REQUIRE(out, "cid_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    CID_REQUIRE(e == cudaSuccess && n > 0, "no CUDA device available (%s); this library has no CPU fallback",
+                e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    CID_REQUIRE(device >= 0 && device < n, "device %d out of range [0,%d)", device, n);
+    cudaDeviceProp prop;
+    CID_CHECK_CUDA(cudaGetDeviceProperties(&prop, device));
+    CID_REQUIRE(prop.major == 10, "device %d is sm_%d%d; this library is built for sm_100a (B200) only", device,
+                prop.major, prop.minor);
+    cid_ctx* c = new cid_ctx();
+    c->device = device;
+    c->num_sms = prop.multiProcessorCount;
+    c->max_smem = static_cast<int>(prop.sharedMemPerBlockOptin);
+    *out = c;
+    return 0;
+}
+
+int cid_destroy(cid_handle h) {
+    if (!h) return 0;
+    DeviceGuard g(h->device);
+    for (int l = 0; l < 12; ++l) {
+        if (h->w_dev[l]) cudaFree(h->w_dev[l]);
+        if (h->bias_dev[l]) cudaFree(h->bias_dev[l]);
+    }
+    delete static_cast<FirstConvW*>(h->first_w_host);
+    delete h;
+    return 0;
+}
+
+int cid_set_param(cid_handle h, const char* key, const float* data, const int64_t* shape, int ndim) {
+    CID_REQUIRE(h && key && data && shape, "cid_set_param: null argument");
+    const std::string k(key);
+    const size_t dot = k.rfind('.');
+    CID_REQUIRE(dot != std::string::npos, "unknown parameter key '%s'", key);
+    const std::string lname = k.substr(0, dot), what = k.substr(dot + 1);
+    int l = -1;
+    for (int i = 0; i < 12; ++i)
+        if (lname == kLayers[i].name) l = i;
+    CID_REQUIRE(l >= 0 && (what == "weight" || what == "bias"), "unknown parameter key '%s'", key);
+    const LayerDesc& L = kLayers[l];
+    int64_t expect[4];
+    int en;
+    if (what == "bias") {
+        expect[0] = L.cout;
+        en = 1;
+    } else if (L.kind == L_CONVT) {
+        expect[0] = L.cin; expect[1] = L.cout; expect[2] = 2; expect[3] = 2;
+        en = 4;
+    } else {
+        expect[0] = L.cout; expect[1] = L.cin; expect[2] = 3; expect[3] = 3;
+        en = 4;
+    }
+    CID_REQUIRE(ndim == en, "%s: expected %d dims, got %d", key, en, ndim);
+    size_t n = 1;
+    for (int i = 0; i < en; ++i) {
+        CID_REQUIRE(shape[i] == expect[i], "%s: dim %d is %lld, expected %lld", key, i,
+                    static_cast<long long>(shape[i]), static_cast<long long>(expect[i]));
+        n *= static_cast<size_t>(shape[i]);
+    }
+    DeviceGuard g(h->device);
+    CID_REQUIRE(g.ok, "cannot select CUDA device %d", h->device);
+    std::vector<float> v(n);
+    CID_CHECK_CUDA(cudaMemcpy(v.data(), data, n * 4, cudaMemcpyDefault));
+    h->params[k] = std::move(v);
+    h->finalized = false;
+    return 0;
+}
+
+int cid_finalize(cid_handle h) {
+    CID_REQUIRE(h, "cid_finalize: null handle");
+    DeviceGuard g(h->device);
+    CID_REQUIRE(g.ok, "cannot select CUDA device %d", h->device);
+    CID_CHECK_CUDA(cudaDeviceSynchronize());  // no forward may still be reading the old packed weights
+    for (int l = 0; l < 12; ++l)
+        if (pack_layer(h, l)) return 1;
+    h->finalized = true;
+    return 0;
+}
+
+int cid_set_option(cid_handle h, const char* name, int64_t value) {
+    CID_REQUIRE(h && name, "cid_set_option: null argument");
+    if (!strcmp(name, "chunk")) {
+        CID_REQUIRE(value >= 0, "chunk must be >= 0");
+        h->chunk = value;
+        return 0;
+    }
+    set_error("unknown option '%s'", name);
+    return 1;
+}
+
+int cid_workspace_bytes(cid_handle h, int B, int H, int W, size_t* bytes) {
+    CID_REQUIRE(h && bytes, "cid_workspace_bytes: null argument");
+    CID_REQUIRE(B >= 1 && H >= 4 && W >= 4 && H % 4 == 0 && W % 4 == 0, "bad shape B=%d H=%d W=%d", B, H, W);
+    *bytes = layout_offsets(chunk_of(h, B), H, W, nullptr);
+    return 0;
+}
+
+int cid_forward_f32_nchw(cid_handle h, const float* x, float* y, int B, int H, int W, void* ws, size_t ws_bytes,
+                         void* stream) {
+    IoSpec io;
+    memset(&io, 0, sizeof(io));
+    io.u8 = false;
+    const size_t img = static_cast<size_t>(3) * H * W * 4;
+    return forward_common(h, B, H, W, ws, ws_bytes, static_cast<cudaStream_t>(stream),
+                          reinterpret_cast<const uint8_t*>(x), img, reinterpret_cast<uint8_t*>(y), img, io);
+}
+
+int cid_forward_u8_nhwc(cid_handle h, const uint8_t* x, uint8_t* y, int B, int H, int W, int pad_l, int pad_t,
+                        int pad_r, int pad_b, void* ws, size_t ws_bytes, void* stream) {
+    CID_REQUIRE(pad_l >= 0 && pad_t >= 0 && pad_r >= 0 && pad_b >= 0, "negative padding");
+    CID_REQUIRE(H >= 1 && W >= 1, "bad image size %dx%d", H, W);
+    IoSpec io;
+    memset(&io, 0, sizeof(io));
+    io.u8 = true;
+    io.in_h = H;
+    io.in_w = W;
+    io.pad_l = pad_l;
+    io.pad_t = pad_t;
+    const size_t img = static_cast<size_t>(3) * H * W;
+    return forward_common(h, B, H + pad_t + pad_b, W + pad_l + pad_r, ws, ws_bytes, static_cast<cudaStream_t>(stream),
+                          x, img, y, img, io);
+}
+
+int64_t cid_kernel_launches(cid_handle h) { return h ? h->launches : -1; }
+
+int cid_debug_copy_activation(cid_handle h, const char* name, const void* ws, int B, int H, int W, void* dst_host,
+                              size_t dst_bytes, int* channels, int* height, int* width) {
+    CID_REQUIRE(h && name && ws && dst_host, "cid_debug_copy_activation: null argument");
+    int b = -1;
+    for (int i = 0; i < B_COUNT; ++i)
+        if (!strcmp(name, kBufNames[i])) b = i;
+    CID_REQUIRE(b >= 0, "unknown activation '%s'", name);
+    DeviceGuard g(h->device);
+    CID_REQUIRE(g.ok, "cannot select CUDA device %d", h->device);
+    const int Bc = chunk_of(h, B);
+    size_t off[B_COUNT];
+    layout_offsets(Bc, H, W, off);
+    const int lv = kBufLevel[b];
+    const size_t n = static_cast<size_t>(Bc) * (H >> lv) * (W >> lv) * kBufC[b] * 2;
+    CID_REQUIRE(dst_bytes >= n, "destination too small: %zu < %zu", dst_bytes, n);
+    CID_CHECK_CUDA(cudaDeviceSynchronize());
+    CID_CHECK_CUDA(cudaMemcpy(dst_host, static_cast<const uint8_t*>(ws) + off[b], n, cudaMemcpyDeviceToHost));
+    if (channels) *channels = kBufC[b];
+    if (height) *height = H >> lv;
+    if (width) *width = W >> lv;
+    return 0;
+}
+
+}  // extern "C"

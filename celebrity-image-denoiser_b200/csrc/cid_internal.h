@@ -1,0 +1,75 @@
+// Shared host-side declarations of the C-ABI library (context object, error plumbing).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/cid_b200.h"
+
+namespace cid {
+
+void set_error(const char* fmt, ...);
+
+#define CID_CHECK_CUDA(expr)                                                                       \
+    do {                                                                                           \
+        cudaError_t _e = (expr);                                                                   \
+        if (_e != cudaSuccess) {                                                                   \
+            cid::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return 1;                                                                              \
+        }                                                                                          \
+    } while (0)
+
+#define CID_REQUIRE(cond, ...)        \
+    do {                              \
+        if (!(cond)) {                \
+            cid::set_error(__VA_ARGS__); \
+            return 1;                 \
+        }                             \
+    } while (0)
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = false;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) return;
+        if (prev != dev && cudaSetDevice(dev) != cudaSuccess) return;
+        ok = true;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+}  // namespace cid
+
+// One (chunk, H, W, workspace) execution plan: buffer offsets and the TMA descriptors of every
+// tensor-core layer's activation operand.
+struct cid_plan {
+    int Bc = 0, H = 0, W = 0;
+    const void* ws = nullptr;
+    size_t off[11] = {0};   // byte offsets of a0,cat1,p1,a2,cat2,p2,b0,b1,u2a,u2b,u1a
+    CUtensorMap tmA[12];    // indexed by layer (0 unused)
+};
+
+struct cid_ctx {
+    int device = 0;
+    int num_sms = 0;
+    int max_smem = 0;
+    int64_t launches = 0;
+    int64_t chunk = 0;
+    bool finalized = false;
+    std::map<std::string, std::vector<float>> params;  // host fp32 copies, reference layout
+    void* w_dev[12] = {nullptr};      // packed bf16 weights per layer (0 unused)
+    float* bias_dev[12] = {nullptr};  // fp32 bias per layer
+    CUtensorMap tmW[12];
+    void* first_w_host = nullptr;     // cid::FirstConvW (kernel parameter block)
+    std::vector<cid_plan> plans;
+    uint32_t attr_done = 0;           // bit per kernel instantiation: max-dynamic-smem attribute set
+    std::map<uint64_t, void*> resize_coeffs;  // (in_size,out_size) -> device coefficient block
+};

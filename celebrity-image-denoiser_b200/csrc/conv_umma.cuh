@@ -1,0 +1,402 @@
+// K1/K2: implicit-GEMM 3x3 convolution (and 1x1 "GEMM" mode for the 2x2-stride-2 transposed
+// convolutions) on tcgen05 tensor cores, NHWC bf16 activations staged by TMA, fp32 accumulators
+// in TMEM, fused epilogues.
+//
+// Reference ops this replaces (file:line in /root/reference):
+//   nn.Conv2d(k3,p1)+nn.ReLU            backend/app.py:43-77
+//   nn.MaxPool2d(2,2)                   backend/app.py:48,56   (fused: EPI_RELU_POOL)
+//   nn.ConvTranspose2d(k2,s2)           backend/app.py:65,73   (TAPS=1 + EPI_CONVT)
+//   torch.cat([d,e],dim=1)              backend/app.py:93,100  (eliminated: producers write
+//                                                               channel slices of one buffer)
+//   torch.tanh + *0.5+0.5, clamp, u8    backend/app.py:103,435,472 (EPI_TANH_*)
+//
+// Geometry. One M-tile = 128 output pixels = 8 wide x 16 tall; GEMM row r <-> pixel
+// (y0 + r/8, x0 + r%8). The A operand for one 64-channel K block and one horizontal tap dx is ONE
+// TMA box {64 ch, 8 px, 18 rows} (rows y0-1 .. y0+16; out-of-image coordinates are zero-filled
+// by TMA = the conv's zero padding). In shared memory that box is 18 groups of 8 rows x 128 B
+// (128-byte swizzle), i.e. exactly the K-major SW128 UMMA layout with SBO = 1024 B, and the three
+// vertical taps dy are the same box read at start address + dy*1024 B. So 9 taps cost 3 box
+// loads (3.4x the minimum bytes instead of 9x).
+//
+// Warp roles (192 threads): warp 0 = TMA producer (one lane), warp 1 = TMEM owner + MMA issuer
+// (one lane), warps 2..5 = epilogue (TMEM lane quarter = warp & 3). TMEM holds two accumulator
+// buffers of S*N fp32 columns so the epilogue of work item i overlaps the MMAs of item i+1.
+// Weights are either resident in shared memory for the whole (persistent) CTA (WRES) or streamed
+// through a ring; with S > 1 one streamed weight tile feeds S pixel tiles.
+#pragma once
+#include "ptx.cuh"
+
+namespace cid {
+
+enum : int { EPI_RELU = 0, EPI_RELU_POOL = 1, EPI_CONVT = 2, EPI_TANH_F32 = 3, EPI_TANH_U8 = 4 };
+
+constexpr int kConvThreads = 192;
+constexpr int kMaxStages = 8;
+
+struct ConvParams {
+    int B, H, W;         // A-operand activation: batch, height, width (pixels)
+    int kb_count;        // Cin / 64
+    int n_tiles;         // tiles of width N across the GEMM N extent
+    int tiles_x, tiles_y;
+    int m_tiles;         // B * tiles_x * tiles_y
+    int num_work;        // ceil(m_tiles / S) * n_tiles
+    int a_stages, w_stages;
+    int w_rows_per_tap;  // rows of the packed weight matrix per tap (= padded Cout)
+    const float* bias;   // fp32 [cout]
+    int cout;            // real output channels (EPI_CONVT: channels per quadrant)
+    void* out;           // primary output
+    int out_cs, out_c0;  // channel count of the output buffer / first channel we write
+    void* out2;          // EPI_RELU_POOL: pooled output buffer
+    int out2_cs, out2_c0;
+    int crop_l, crop_t, out_h, out_w;  // EPI_TANH_U8: crop window into the u8 NHWC result
+};
+
+template <int N, int TAPS, int S, bool WRES, int EPI>
+struct ConvCfg {
+    static_assert(TAPS == 9 || TAPS == 1, "3x3 or 1x1");
+    static_assert(N % 16 == 0 && N >= 16 && N <= 256, "UMMA N for M=128");
+    static_assert(2 * S * N <= 512, "two accumulator buffers must fit TMEM");
+    static constexpr int DX = TAPS == 9 ? 3 : 1;
+    static constexpr int DY = DX;
+    static constexpr int A_ROWS = TAPS == 9 ? 18 : 16;
+    static constexpr int A_BYTES = A_ROWS * 1024;
+    static constexpr int W_BYTES = N * 128;
+    static constexpr int ACC_COLS = S * N;
+    static constexpr int TMEM_COLS = (2 * ACC_COLS <= 32)    ? 32
+                                     : (2 * ACC_COLS <= 64)  ? 64
+                                     : (2 * ACC_COLS <= 128) ? 128
+                                     : (2 * ACC_COLS <= 256) ? 256
+                                                             : 512;
+    // dynamic shared memory needed (bytes), including 1 KB of alignment slack
+    static int smem_bytes(int kb_count, int a_stages, int w_stages) {
+        int w_items = WRES ? kb_count * TAPS : w_stages;
+        return 1024 + w_items * W_BYTES + a_stages * A_BYTES + 512;
+    }
+};
+
+struct TileCoord {
+    int b, y0, x0;
+};
+
+__device__ __forceinline__ TileCoord decode_tile(const ConvParams& p, int mt) {
+    TileCoord t;
+    int tx = mt % p.tiles_x;
+    int r = mt / p.tiles_x;
+    int ty = r % p.tiles_y;
+    t.b = r / p.tiles_y;  // == B for padding tiles past m_tiles: TMA zero-fills, stores are masked
+    t.y0 = ty * 16;
+    t.x0 = tx * 8;
+    return t;
+}
+
+template <int N, int TAPS, int S, bool WRES, int EPI>
+__global__ void __launch_bounds__(kConvThreads, 1)
+conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                 const ConvParams p) {
+    using Cfg = ConvCfg<N, TAPS, S, WRES, EPI>;
+    constexpr int DX = Cfg::DX, DY = Cfg::DY;
+    constexpr int A_BYTES = Cfg::A_BYTES, W_BYTES = Cfg::W_BYTES;
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+
+    const int w_items = WRES ? p.kb_count * TAPS : p.w_stages;
+    uint8_t* w_smem = smem;
+    uint8_t* a_smem = smem + w_items * W_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(a_smem + p.a_stages * A_BYTES);
+    uint64_t* a_full = bars;
+    uint64_t* a_empty = bars + kMaxStages;
+    uint64_t* w_full = bars + 2 * kMaxStages;
+    uint64_t* w_empty = bars + 3 * kMaxStages;
+    uint64_t* acc_full = bars + 4 * kMaxStages;
+    uint64_t* acc_empty = acc_full + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int AST = p.a_stages;
+    const int WST = p.w_stages;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmW);
+        for (int i = 0; i < kMaxStages; ++i) {
+            mbar_init(&a_full[i], 1);
+            mbar_init(&a_empty[i], 1);
+            mbar_init(&w_full[i], 1);
+            mbar_init(&w_empty[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&acc_full[i], 1);
+            mbar_init(&acc_empty[i], 4);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ======================= TMA producer =======================
+        if (lane == 0) {
+            if (WRES) {
+                mbar_arrive_expect_tx(&w_full[0], static_cast<uint32_t>(w_items) * W_BYTES);
+                for (int kb = 0; kb < p.kb_count; ++kb)
+                    for (int tap = 0; tap < TAPS; ++tap)
+                        tma_load_2d(w_smem + (kb * TAPS + tap) * W_BYTES, &tmW, &w_full[0], kb * 64,
+                                    tap * p.w_rows_per_tap, kEvictLast);
+            }
+            uint32_t a_it = 0, w_it = 0;
+            for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
+                const int n_tile = work % p.n_tiles;
+                const int st = work / p.n_tiles;
+                TileCoord tc[S];
+#pragma unroll
+                for (int s = 0; s < S; ++s) tc[s] = decode_tile(p, st * S + s);
+                for (int kb = 0; kb < p.kb_count; ++kb) {
+                    for (int dx = 0; dx < DX; ++dx) {
+#pragma unroll
+                        for (int s = 0; s < S; ++s) {
+                            const uint32_t stage = a_it % AST;
+                            const uint32_t ph = (a_it / AST) & 1;
+                            mbar_wait(&a_empty[stage], ph ^ 1);
+                            mbar_arrive_expect_tx(&a_full[stage], A_BYTES);
+                            tma_load_4d(a_smem + stage * A_BYTES, &tmA, &a_full[stage], kb * 64,
+                                        tc[s].x0 + dx - (DX == 3 ? 1 : 0), tc[s].y0 - (DY == 3 ? 1 : 0), tc[s].b,
+                                        kEvictNormal);
+                            ++a_it;
+                        }
+                        if (!WRES) {
+                            for (int dy = 0; dy < DY; ++dy) {
+                                const uint32_t stage = w_it % WST;
+                                const uint32_t ph = (w_it / WST) & 1;
+                                mbar_wait(&w_empty[stage], ph ^ 1);
+                                mbar_arrive_expect_tx(&w_full[stage], W_BYTES);
+                                tma_load_2d(w_smem + stage * W_BYTES, &tmW, &w_full[stage], kb * 64,
+                                            (dy * DX + dx) * p.w_rows_per_tap + n_tile * N, kEvictLast);
+                                ++w_it;
+                            }
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ======================= MMA issuer =======================
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(128, N);
+            uint32_t a_it = 0, w_it = 0, acc_it = 0;
+            if (WRES) {
+                mbar_wait(&w_full[0], 0);
+                tc_fence_after();
+            }
+            for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
+                const uint32_t buf = acc_it & 1;
+                const uint32_t aph = (acc_it >> 1) & 1;
+                mbar_wait(&acc_empty[buf], aph ^ 1);
+                tc_fence_after();
+                const uint32_t d_base = tmem_base + buf * Cfg::ACC_COLS;
+                for (int kb = 0; kb < p.kb_count; ++kb) {
+                    for (int dx = 0; dx < DX; ++dx) {
+#pragma unroll
+                        for (int s = 0; s < S; ++s) {
+                            const uint32_t it = a_it + s;
+                            mbar_wait(&a_full[it % AST], (it / AST) & 1);
+                        }
+                        tc_fence_after();
+                        for (int dy = 0; dy < DY; ++dy) {
+                            uint32_t wb;
+                            uint32_t wstage = 0;
+                            if (WRES) {
+                                wb = smem_u32(w_smem + (kb * TAPS + dy * DX + dx) * W_BYTES);
+                            } else {
+                                wstage = w_it % WST;
+                                mbar_wait(&w_full[wstage], (w_it / WST) & 1);
+                                tc_fence_after();
+                                wb = smem_u32(w_smem + wstage * W_BYTES);
+                            }
+                            const uint32_t first = (kb == 0 && dx == 0 && dy == 0) ? 1u : 0u;
+#pragma unroll
+                            for (int s = 0; s < S; ++s) {
+                                const uint32_t ab =
+                                    smem_u32(a_smem + ((a_it + s) % AST) * A_BYTES) + dy * 1024;
+#pragma unroll
+                                for (int k = 0; k < 4; ++k) {
+                                    umma_bf16_ss(d_base + s * N, umma_desc_sw128(ab + k * 32, 1024),
+                                                 umma_desc_sw128(wb + k * 32, 1024), idesc,
+                                                 (first && k == 0) ? 0u : 1u);
+                                }
+                            }
+                            if (!WRES) {
+                                umma_commit(&w_empty[wstage]);
+                                ++w_it;
+                            }
+                        }
+#pragma unroll
+                        for (int s = 0; s < S; ++s) umma_commit(&a_empty[(a_it + s) % AST]);
+                        a_it += S;
+                    }
+                }
+                umma_commit(&acc_full[buf]);
+                ++acc_it;
+            }
+        }
+    } else {
+        // ======================= epilogue (4 warps) =======================
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        const int yl = row >> 3;
+        const int xl = row & 7;
+        uint32_t acc_it = 0;
+        for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
+            const int n_tile = work % p.n_tiles;
+            const int st = work / p.n_tiles;
+            const uint32_t buf = acc_it & 1;
+            const uint32_t aph = (acc_it >> 1) & 1;
+            mbar_wait(&acc_full[buf], aph);
+            tc_fence_after();
+#pragma unroll
+            for (int s = 0; s < S; ++s) {
+                const int mt = st * S + s;
+                const TileCoord tc = decode_tile(p, mt);
+                const int y = tc.y0 + yl;
+                const int x = tc.x0 + xl;
+                const bool valid = (mt < p.m_tiles) && (y < p.H) && (x < p.W);
+                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * Cfg::ACC_COLS + s * N;
+
+                if constexpr (EPI == EPI_RELU || EPI == EPI_RELU_POOL) {
+                    __nv_bfloat16* out = static_cast<__nv_bfloat16*>(p.out);
+                    const size_t pix = (static_cast<size_t>(tc.b) * p.H + y) * p.W + x;
+                    __nv_bfloat16* orow = out + pix * p.out_cs + p.out_c0 + n_tile * N;
+                    __nv_bfloat16* prow = nullptr;
+                    bool pvalid = false;
+                    int sub = 0;
+                    if constexpr (EPI == EPI_RELU_POOL) {
+                        const int PH = p.H >> 1, PW = p.W >> 1;
+                        pvalid = valid;  // H, W even: a valid pixel's 2x2 block is entirely valid
+                        const size_t ppix = (static_cast<size_t>(tc.b) * PH + (y >> 1)) * PW + (x >> 1);
+                        sub = (xl & 1) | ((yl & 1) << 1);
+                        prow = static_cast<__nv_bfloat16*>(p.out2) + ppix * p.out2_cs + p.out2_c0 + n_tile * N +
+                               sub * 8;
+                    }
+#pragma unroll 1
+                    for (int ch = 0; ch < N / 32; ++ch) {
+                        uint32_t v[32];
+                        tmem_ld_32x32(taddr + ch * 32, v);
+                        tmem_ld_wait();
+                        const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_tile * N + ch * 32);
+                        uint32_t pk[16];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 bb = __ldg(b4 + j);
+                            const float f0 = fmaxf(__uint_as_float(v[4 * j + 0]) + bb.x, 0.f);
+                            const float f1 = fmaxf(__uint_as_float(v[4 * j + 1]) + bb.y, 0.f);
+                            const float f2 = fmaxf(__uint_as_float(v[4 * j + 2]) + bb.z, 0.f);
+                            const float f3 = fmaxf(__uint_as_float(v[4 * j + 3]) + bb.w, 0.f);
+                            pk[2 * j + 0] = pack_bf16x2(f0, f1);
+                            pk[2 * j + 1] = pack_bf16x2(f2, f3);
+                        }
+                        if (valid) {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                st_global_v4(orow + ch * 32 + j * 8, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2],
+                                             pk[4 * j + 3]);
+                        }
+                        if constexpr (EPI == EPI_RELU_POOL) {
+                            // 2x2 max: x partner is lane^1, y partner is lane^8 (row = y*8 + x).
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) {
+                                uint32_t m = max_bf16x2(pk[j], __shfl_xor_sync(0xffffffffu, pk[j], 1));
+                                pk[j] = max_bf16x2(m, __shfl_xor_sync(0xffffffffu, m, 8));
+                            }
+                            // each of the 4 lanes of a 2x2 block stores a different 8-channel quarter
+                            const uint32_t o0 = sub == 0 ? pk[0] : sub == 1 ? pk[4] : sub == 2 ? pk[8] : pk[12];
+                            const uint32_t o1 = sub == 0 ? pk[1] : sub == 1 ? pk[5] : sub == 2 ? pk[9] : pk[13];
+                            const uint32_t o2 = sub == 0 ? pk[2] : sub == 1 ? pk[6] : sub == 2 ? pk[10] : pk[14];
+                            const uint32_t o3 = sub == 0 ? pk[3] : sub == 1 ? pk[7] : sub == 2 ? pk[11] : pk[15];
+                            if (pvalid) st_global_v4(prow + ch * 32, o0, o1, o2, o3);
+                        }
+                    }
+                } else if constexpr (EPI == EPI_CONVT) {
+                    // GEMM column n = quadrant*cout + c, quadrant = dy*2+dx; output pixel (2y+dy, 2x+dx).
+                    __nv_bfloat16* out = static_cast<__nv_bfloat16*>(p.out);
+                    const int OH = p.H * 2, OW = p.W * 2;
+#pragma unroll 1
+                    for (int ch = 0; ch < N / 32; ++ch) {
+                        uint32_t v[32];
+                        tmem_ld_32x32(taddr + ch * 32, v);
+                        tmem_ld_wait();
+                        const int n = n_tile * N + ch * 32;
+                        const int quad = n / p.cout;
+                        const int c = n - quad * p.cout;
+                        const float4* b4 = reinterpret_cast<const float4*>(p.bias + c);
+                        uint32_t pk[16];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 bb = __ldg(b4 + j);
+                            pk[2 * j + 0] =
+                                pack_bf16x2(__uint_as_float(v[4 * j + 0]) + bb.x, __uint_as_float(v[4 * j + 1]) + bb.y);
+                            pk[2 * j + 1] =
+                                pack_bf16x2(__uint_as_float(v[4 * j + 2]) + bb.z, __uint_as_float(v[4 * j + 3]) + bb.w);
+                        }
+                        if (valid) {
+                            const size_t pix =
+                                (static_cast<size_t>(tc.b) * OH + (2 * y + (quad >> 1))) * OW + (2 * x + (quad & 1));
+                            __nv_bfloat16* orow = out + pix * p.out_cs + p.out_c0 + c;
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                st_global_v4(orow + j * 8, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+                        }
+                    }
+                } else {
+                    // final 64->3 conv: columns 0..2 are real, tanh, then fp32 NCHW or u8 NHWC (cropped)
+                    uint32_t v[4];
+                    tmem_ld_32x4(taddr, v);
+                    tmem_ld_wait();
+                    float t[3];
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) t[c] = tanhf(__uint_as_float(v[c]) + __ldg(p.bias + c));
+                    if (valid) {
+                        if constexpr (EPI == EPI_TANH_F32) {
+                            float* out = static_cast<float*>(p.out);
+#pragma unroll
+                            for (int c = 0; c < 3; ++c)
+                                out[((static_cast<size_t>(tc.b) * 3 + c) * p.H + y) * p.W + x] = t[c];
+                        } else {
+                            // (y*0.5+0.5).clamp(0,1) then ToPILImage: mul(255) and a TRUNCATING byte cast
+                            // (backend/app.py:435,472)
+                            const int oy = y - p.crop_t, ox = x - p.crop_l;
+                            if (oy >= 0 && oy < p.out_h && ox >= 0 && ox < p.out_w) {
+                                uint8_t* out = static_cast<uint8_t*>(p.out) +
+                                               ((static_cast<size_t>(tc.b) * p.out_h + oy) * p.out_w + ox) * 3;
+#pragma unroll
+                                for (int c = 0; c < 3; ++c) {
+                                    float u = __fmaf_rn(t[c], 0.5f, 0.5f);
+                                    u = fminf(fmaxf(u, 0.f), 1.f);
+                                    out[c] = static_cast<uint8_t>(__fmul_rn(u, 255.f));
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[buf]);
+            ++acc_it;
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    }
+}
+
+}  // namespace cid

@@ -1,0 +1,217 @@
+"""Drop-in `DenoiseGenerator`: the reference's nn.Module surface over the CUDA C-ABI.
+
+Mirrors `DenoiseGenerator` of the reference (backend/app.py:39-103): same class name, no
+constructor arguments, the same 24 `state_dict` keys and shapes, `forward(x)` taking fp32 NCHW in
+[-1,1] and returning the tanh output as fp32 NCHW on the same device. So
+`PT_MODELS["denoise"] = DenoiseGenerator().to(DEVICE)` (backend/app.py:319-320),
+`load_state_safely(model, path)` (:257-274) and `net(x_pt)` (:433) work unchanged.
+
+The parameters are ordinary `nn.Parameter`s (so `.to()`, `load_state_dict(strict=False)`,
+`state_dict()` behave exactly as in the reference) but the module never computes with them in
+PyTorch: `forward` hands them to libcid_b200.so, which packs them to its bf16 tensor-core layout
+and runs the hand-written sm_100a kernels. No cuDNN, no CPU path: a CPU tensor or a missing
+library raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+from . import lib as _lib
+
+# (attribute, [(kind, cin, cout), ...]); conv entries are followed by a parameter-less ReLU slot
+# so the Sequential indices — and therefore the state_dict keys — are the reference's
+# (down1.0, down1.2, ...; the last conv of upconv1 has no ReLU after it: backend/app.py:74-78).
+_BLOCKS = (
+    ("down1", ((3, 64), (64, 64)), True),
+    ("down2", ((64, 128), (128, 128)), True),
+    ("bottleneck", ((128, 256), (256, 256)), True),
+    ("up2", (256, 128), None),
+    ("upconv2", ((256, 128), (128, 128)), True),
+    ("up1", (128, 64), None),
+    ("upconv1", ((128, 64), (64, 3)), False),
+)
+
+STATE_DICT_SHAPES: Dict[str, Tuple[int, ...]] = {}
+for _name, _spec, _last_relu in _BLOCKS:
+    if _last_relu is None:
+        STATE_DICT_SHAPES[f"{_name}.weight"] = (_spec[0], _spec[1], 2, 2)  # ConvTranspose2d: [Cin,Cout,kh,kw]
+        STATE_DICT_SHAPES[f"{_name}.bias"] = (_spec[1],)
+    else:
+        for _i, (_ci, _co) in enumerate(_spec):
+            STATE_DICT_SHAPES[f"{_name}.{2 * _i}.weight"] = (_co, _ci, 3, 3)
+            STATE_DICT_SHAPES[f"{_name}.{2 * _i}.bias"] = (_co,)
+
+
+class _Engine:
+    """One C-ABI handle (= one device) plus its cached workspace."""
+
+    def __init__(self, device_index: int):
+        self.lib = _lib.load()
+        self.device_index = device_index
+        h = C.c_void_p()
+        _lib.check(self.lib.cid_create(device_index, C.byref(h)), "cid_create")
+        self.handle = h
+        self.signature = None
+        self._ws: Optional[torch.Tensor] = None
+        self._ws_key = None
+
+    def close(self):
+        if self.handle:
+            self.lib.cid_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):  # best effort
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_option(self, name: str, value: int):
+        _lib.check(self.lib.cid_set_option(self.handle, name.encode(), int(value)), "cid_set_option")
+        self._ws = None
+        self._ws_key = None
+
+    def upload(self, state: Dict[str, torch.Tensor]):
+        for key, shape in STATE_DICT_SHAPES.items():
+            t = state[key].detach()
+            if t.dtype != torch.float32 or not t.is_contiguous():
+                t = t.float().contiguous()
+            if tuple(t.shape) != shape:
+                raise RuntimeError(f"{key}: shape {tuple(t.shape)} != {shape}")
+            dims = (C.c_int64 * len(shape))(*shape)
+            _lib.check(self.lib.cid_set_param(self.handle, key.encode(), C.c_void_p(t.data_ptr()), dims, len(shape)),
+                       f"cid_set_param({key})")
+        _lib.check(self.lib.cid_finalize(self.handle), "cid_finalize")
+
+    def workspace(self, B: int, H: int, W: int) -> torch.Tensor:
+        key = (B, H, W)
+        if self._ws_key != key:
+            n = C.c_size_t()
+            _lib.check(self.lib.cid_workspace_bytes(self.handle, B, H, W, C.byref(n)), "cid_workspace_bytes")
+            if self._ws is None or self._ws.numel() < n.value:
+                self._ws = None  # release before allocating the larger one
+                self._ws = torch.empty(n.value + 1024, dtype=torch.uint8, device=f"cuda:{self.device_index}")
+            self._ws_key = key
+        return self._ws
+
+    def ws_ptr(self, ws: torch.Tensor) -> Tuple[int, int]:
+        p = (ws.data_ptr() + 1023) & ~1023
+        return p, ws.numel() - (p - ws.data_ptr())
+
+    def launches(self) -> int:
+        return int(self.lib.cid_kernel_launches(self.handle))
+
+
+class DenoiseGenerator(nn.Module):
+    def __init__(self):
+        super().__init__()
+        for name, spec, last_relu in _BLOCKS:
+            if last_relu is None:
+                self.add_module(name, nn.ConvTranspose2d(spec[0], spec[1], kernel_size=2, stride=2))
+                continue
+            mods = []
+            for i, (ci, co) in enumerate(spec):
+                mods.append(nn.Conv2d(ci, co, kernel_size=3, padding=1))
+                if last_relu or i + 1 < len(spec):
+                    mods.append(nn.ReLU())
+            self.add_module(name, nn.Sequential(*mods))
+        self._engines: Dict[int, _Engine] = {}
+        self._options: Dict[str, int] = {}
+
+    # ---- engine plumbing -------------------------------------------------------------------
+    def _signature(self):
+        return tuple((k, v.data_ptr(), v._version) for k, v in self.state_dict(keep_vars=True).items())
+
+    def _engine(self, device: torch.device) -> _Engine:
+        if device.type != "cuda":
+            raise RuntimeError(
+                "DenoiseGenerator (B200-native) runs only on CUDA tensors; there is no CPU fallback")
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        eng = self._engines.get(idx)
+        if eng is None:
+            eng = _Engine(idx)
+            for k, v in self._options.items():
+                eng.set_option(k, v)
+            self._engines[idx] = eng
+        sig = self._signature()
+        if eng.signature != sig:  # parameters were loaded / moved / modified since the last pack
+            eng.upload(self.state_dict())
+            eng.signature = sig
+        return eng
+
+    def set_option(self, name: str, value: int) -> "DenoiseGenerator":
+        """Forwarded to cid_set_option (e.g. "chunk")."""
+        self._options[name] = int(value)
+        for eng in self._engines.values():
+            eng.set_option(name, value)
+        return self
+
+    def kernel_launches(self) -> int:
+        return sum(e.launches() for e in self._engines.values())
+
+    # ---- the reference's call: y = net(x) (backend/app.py:433) -----------------------------
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if x.dim() != 4 or x.size(1) != 3:
+            raise RuntimeError(f"expected input [B,3,H,W], got {tuple(x.shape)}")
+        eng = self._engine(x.device)
+        if x.dtype != torch.float32 or not x.is_contiguous():
+            x = x.float().contiguous()
+        B, _, H, W = x.shape
+        y = torch.empty_like(x)
+        if B == 0:
+            return y
+        ws = eng.workspace(B, H, W)
+        wp, wn = eng.ws_ptr(ws)
+        stream = torch.cuda.current_stream(x.device).cuda_stream
+        with torch.cuda.device(x.device):
+            _lib.check(eng.lib.cid_forward_f32_nchw(eng.handle, C.c_void_p(x.data_ptr()), C.c_void_p(y.data_ptr()),
+                                                    B, H, W, C.c_void_p(wp), wn, C.c_void_p(stream)),
+                       "cid_forward_f32_nchw")
+        return y
+
+    # ---- fused route path: u8 image(s) in -> u8 image(s) out -------------------------------
+    def forward_u8(self, x: torch.Tensor, padding: Tuple[int, int, int, int] = (0, 0, 0, 0),
+                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """x: CUDA uint8 NHWC [B,H,W,3] (un-padded). padding = get_padding()'s (l,t,r,b).
+        Returns uint8 NHWC [B,H,W,3]: pad -> normalise -> generator -> denorm -> clamp ->
+        truncating x255 -> crop, as backend/app.py:383-480 does for model=denoise."""
+        if x.dim() != 4 or x.size(3) != 3 or x.dtype != torch.uint8:
+            raise RuntimeError(f"expected uint8 input [B,H,W,3], got {x.dtype} {tuple(x.shape)}")
+        eng = self._engine(x.device)
+        x = x.contiguous()
+        B, H, W, _ = x.shape
+        l, t, r, b = (int(v) for v in padding)
+        y = out if out is not None else torch.empty_like(x)
+        if out is not None and (out.shape != x.shape or out.dtype != torch.uint8 or not out.is_contiguous()
+                                or out.device != x.device):
+            raise RuntimeError("out must be a contiguous uint8 tensor shaped like x on the same device")
+        if B == 0:
+            return y
+        ws = eng.workspace(B, H + t + b, W + l + r)
+        wp, wn = eng.ws_ptr(ws)
+        stream = torch.cuda.current_stream(x.device).cuda_stream
+        with torch.cuda.device(x.device):
+            _lib.check(eng.lib.cid_forward_u8_nhwc(eng.handle, C.c_void_p(x.data_ptr()), C.c_void_p(y.data_ptr()),
+                                                   B, H, W, l, t, r, b, C.c_void_p(wp), wn, C.c_void_p(stream)),
+                       "cid_forward_u8_nhwc")
+        return y
+
+    def debug_activation(self, name: str, x_shape: Tuple[int, int, int, int]) -> torch.Tensor:
+        """Test hook: intermediate activation `name` of the last forward with input [B,3,H,W], as a
+        float32 NHWC CPU tensor (values are bf16-exact)."""
+        B, _, H, W = x_shape
+        eng = next(iter(self._engines.values()))
+        ws = eng.workspace(B, H, W)
+        wp, _ = eng.ws_ptr(ws)
+        lvl_max = B * H * W * 256  # generous upper bound (elements)
+        buf = torch.empty(lvl_max, dtype=torch.bfloat16)
+        c, h, w = C.c_int(), C.c_int(), C.c_int()
+        _lib.check(eng.lib.cid_debug_copy_activation(eng.handle, name.encode(), C.c_void_p(wp), B, H, W,
+                                                     C.c_void_p(buf.data_ptr()), buf.numel() * 2, C.byref(c),
+                                                     C.byref(h), C.byref(w)), "cid_debug_copy_activation")
+        n = B * h.value * w.value * c.value
+        return buf[:n].view(B, h.value, w.value, c.value).float()

@@ -1,0 +1,123 @@
+/*
+ * cid_b200.h — C ABI of the B200-native generator forward for Celebrity-Image-Denoiser.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no torch types. Everything the
+ * reference's denoise path does between "decoded RGB image" and "denoised RGB image" is behind
+ * these entry points. The reference itself has no native interface (it is pure Python); each
+ * entry point cites the Python interface it replaces (file:line in flawyer/Celebrity-Image-Denoiser).
+ * INTEGRATION.md shows the ctypes stub a maintainer adds to backend/app.py.
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on failure; cid_last_error() gives the reason
+ *     (thread-local string). There is NO CPU fallback: without a CUDA device every compute call
+ *     fails loudly.
+ *   - the library never frees or retains caller memory; it owns only its packed weights.
+ *   - a handle is bound to one device and used from one thread at a time; handles on different
+ *     devices are independent (one per GPU for batch sharding).
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream). All work is
+ *     stream-ordered; nothing synchronises the host unless stated.
+ */
+#ifndef CID_B200_H
+#define CID_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct cid_ctx* cid_handle;
+
+/* ABI version of this header (bumped on any signature change). */
+int cid_version(void);
+
+/* Reason for the most recent failure on the calling thread ("" if none). */
+const char* cid_last_error(void);
+
+/* Replaces `DenoiseGenerator().to(DEVICE)` (backend/app.py:319-320): create an empty generator
+ * bound to CUDA device `device`. Weights are undefined until cid_set_param + cid_finalize. */
+int cid_create(int device, cid_handle* out);
+int cid_destroy(cid_handle h);
+
+/* Replaces `model.load_state_dict(new_state, strict=False)` (backend/app.py:272): hand over one
+ * state_dict tensor. `key` is one of the 24 reference keys (down1.0.weight ... upconv1.2.bias,
+ * backend/app.py:42-78); `data` is fp32, host or device memory, C-contiguous in the reference's
+ * own layout (Conv2d [Cout,Cin,3,3]; ConvTranspose2d [Cin,Cout,2,2]); shape is checked.
+ * Unknown keys fail (the Python mirror filters them, matching strict=False). */
+int cid_set_param(cid_handle h, const char* key, const float* data, const int64_t* shape, int ndim);
+
+/* Pack all 24 tensors into the device layouts the kernels read (bf16, per-tap K-major rows for
+ * the tensor-core layers; fp32 constant block for the first layer). Synchronous. Must be called
+ * after the last cid_set_param and before any forward; may be called again after new params. */
+int cid_finalize(cid_handle h);
+
+/* Tunables. "chunk": images processed per pass through the layers (0 = whole batch); bounds the
+ * activation working set (and the workspace). */
+int cid_set_option(cid_handle h, const char* name, int64_t value);
+
+/* Bytes of device scratch a forward of B images of H x W (network-input size, multiples of 4)
+ * needs. The caller allocates it (e.g. a torch uint8 tensor) and passes it to the forward. */
+int cid_workspace_bytes(cid_handle h, int B, int H, int W, size_t* bytes);
+
+/* Replaces `y = net(x_pt)` (backend/app.py:433; DenoiseGenerator.forward :80-103).
+ * x: device fp32 NCHW [B,3,H,W] in [-1,1]; y: device fp32 NCHW [B,3,H,W] = tanh output.
+ * H, W must be multiples of 4 (what get_padding guarantees, backend/app.py:276-281). */
+int cid_forward_f32_nchw(cid_handle h, const float* x, float* y, int B, int H, int W, void* ws, size_t ws_bytes,
+                         void* stream);
+
+/* Replaces the whole denoise branch of the route between PIL decode and PIL encode
+ * (backend/app.py:383-385 Pad, :401-406 ToTensor/Normalize, :433 net, :435 denorm+clamp,
+ * :472 ToPILImage's truncating x255 cast, :474-480 crop).
+ * x: device u8 NHWC [B,H,W,3] (the un-padded image); y: device u8 NHWC [B,H,W,3].
+ * (pad_l,pad_t,pad_r,pad_b) is get_padding()'s tuple; H+pad_t+pad_b and W+pad_l+pad_r must be
+ * multiples of 4. Workspace is sized for the PADDED dims. */
+int cid_forward_u8_nhwc(cid_handle h, const uint8_t* x, uint8_t* y, int B, int H, int W, int pad_l, int pad_t,
+                        int pad_r, int pad_b, void* ws, size_t ws_bytes, void* stream);
+
+/* Synthetic noiser (test-input builder).
+ * Gaussian: replaces add_gaussian_noise (trainingcode/denoise_gan_code/noise_generation.py:6-10):
+ *   out = u8(clip(in + noise, 0, 255)) in float64 with a truncating cast. If `noise` (device
+ *   float64, n values, exactly what np.random.normal(mean, sigma, shape) returned) is non-NULL it
+ *   is used verbatim (bit-exact parity mode); otherwise mean + sigma*z is drawn on the device
+ *   from Philox4x32-10 (seed, offset) by Box-Muller (statistical parity).
+ * n = number of u8 elements (H*W*C*B). */
+int cid_noise_gaussian_u8(cid_handle h, const uint8_t* in, uint8_t* out, size_t n, float mean, float sigma,
+                          const double* noise, uint64_t seed, uint64_t offset, void* stream);
+
+/* Salt & pepper: replaces add_salt_pepper_noise (noise_generation.py:12-22). Per image
+ * [H,W,C]: n_salt = int(H*W*C*salt_prob) pixel coordinates set to 255 on all channels, then
+ * n_pepper set to 0. If coords (device int32 [B][n_salt+n_pepper][2] = (row,col)) is non-NULL
+ * it is used verbatim (parity mode); otherwise coordinates are Philox draws in
+ * [0,H-1) x [0,W-1) — the reference's randint(0, dim-1) excludes the last row/col. */
+int cid_noise_salt_pepper_u8(cid_handle h, const uint8_t* in, uint8_t* out, int B, int H, int W, int C,
+                             float salt_prob, float pepper_prob, const int32_t* coords, uint64_t seed,
+                             uint64_t offset, void* stream);
+
+/* Resize + normalise data-prep: replaces Image.resize(size, BICUBIC) (noise_generation.py:61,
+ * denoisegan_eval.py:89) = Pillow's two-pass separable fixed-point bicubic (a = -0.5, support
+ * scaled by the down-sampling factor), u8 NHWC in -> u8 NHWC out. tmp: device scratch of
+ * B*in_h*out_w*C bytes. */
+int cid_resize_bicubic_u8(cid_handle h, const uint8_t* in, uint8_t* out, uint8_t* tmp, int B, int in_h, int in_w,
+                          int out_h, int out_w, int C, void* stream);
+
+/* Replaces ToTensor + Normalize(mean, std) (backend/app.py:401-406, denoisegan_eval.py:76-79):
+ * u8 NHWC [B,H,W,3] -> fp32 NCHW [B,3,H,W], (v/255 - mean)/std, each step rounded in fp32 as
+ * torch does. (The u8 forward above fuses this into its first layer; this entry point exists for
+ * callers that feed cid_forward_f32_nchw.) */
+int cid_normalize_u8_to_f32_nchw(cid_handle h, const uint8_t* in, float* out, int B, int H, int W, float mean,
+                                 float stdv, void* stream);
+
+/* Number of kernels this handle has launched so far (bench.py's gpu_launches evidence). */
+int64_t cid_kernel_launches(cid_handle h);
+
+/* Test hook: copy one intermediate activation of the most recent forward (same B,H,W,ws) to host
+ * as bf16 NHWC. name in {a0,cat1,p1,a2,cat2,p2,b0,b1,u2a,u2b,u1a}; *channels gets its C.
+ * Synchronises the device. */
+int cid_debug_copy_activation(cid_handle h, const char* name, const void* ws, int B, int H, int W, void* dst_host,
+                              size_t dst_bytes, int* channels, int* height, int* width);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CID_B200_H */
