@@ -1,0 +1,12 @@
+"""B200-native generator forward for Celebrity-Image-Denoiser (import as `cid_b200`).
+
+Public surface (mirrors the reference's names for the denoise path, backend/app.py):
+    DenoiseGenerator      nn.Module with the reference's state_dict keys; forward on CUDA only
+    load_state_safely     checkpoint loader with the reference's key-candidate / "module." rules
+    get_padding, MODEL_CFG
+    enhance_image / enhance_batch_u8 / enhance_batch_host   image-in -> image-out
+    patch_app(app)        swap the new generator into the reference's PT_MODELS registry
+"""
+from .generator import DenoiseGenerator, STATE_DICT_SHAPES  # noqa: F401
+from .loader import MODEL_CFG, get_padding, load_state_safely, patch_app  # noqa: F401
+from .pipeline import enhance_batch_host, enhance_batch_u8, enhance_image  # noqa: F401

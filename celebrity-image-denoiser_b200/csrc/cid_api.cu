@@ -271,12 +271,24 @@ struct IoSpec {
     int in_h, in_w, pad_l, pad_t;  // u8 mode
 };
 
+static int prof_mark(cid_ctx* c, cudaStream_t st) {
+    if (!c->profile) return 0;
+    if (c->prof_used == c->prof_events.size()) {
+        cudaEvent_t e;
+        CID_CHECK_CUDA(cudaEventCreate(&e));
+        c->prof_events.push_back(e);
+    }
+    CID_CHECK_CUDA(cudaEventRecord(c->prof_events[c->prof_used++], st));
+    return 0;
+}
+
 // one pass of nb (<= plan.Bc) images through the 12 layers
 static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaStream_t st) {
     const int H = pl->H, W = pl->W;
     uint8_t* ws = static_cast<uint8_t*>(const_cast<void*>(pl->ws));
     auto buf = [&](int b) { return reinterpret_cast<__nv_bfloat16*>(ws + pl->off[b]); };
 
+    if (prof_mark(c, st)) return 1;
     // L0
     {
         FirstConvParams fp;
@@ -299,6 +311,7 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         CID_CHECK_CUDA(cudaGetLastError());
         c->launches++;
     }
+    if (prof_mark(c, st)) return 1;
 
     auto base = [&](int l, int lv) {
         ConvParams p;
@@ -320,54 +333,64 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         p.out2 = buf(B_P1); p.out2_cs = 64; p.out2_c0 = 0;
         if (launch_conv<64, 9, 1, true, EPI_RELU_POOL>(c, 0, pl->tmA[1], c->tmW[1], p, st)) return 1;
     }
+    if (prof_mark(c, st)) return 1;
     {  // L2 down2.0 -> a2
         ConvParams p = base(2, 1);
         p.out = buf(B_A2); p.out_cs = 128; p.out_c0 = 0;
         if (launch_conv<128, 9, 1, true, EPI_RELU>(c, 1, pl->tmA[2], c->tmW[2], p, st)) return 1;
     }
+    if (prof_mark(c, st)) return 1;
     {  // L3 down2.2 -> cat2[:,128:256] + p2
         ConvParams p = base(3, 1);
         p.out = buf(B_CAT2); p.out_cs = 256; p.out_c0 = 128;
         p.out2 = buf(B_P2); p.out2_cs = 128; p.out2_c0 = 0;
         if (launch_conv<128, 9, 2, false, EPI_RELU_POOL>(c, 2, pl->tmA[3], c->tmW[3], p, st)) return 1;
     }
+    if (prof_mark(c, st)) return 1;
     {  // L4 bottleneck.0 -> b0
         ConvParams p = base(4, 2);
         p.out = buf(B_B0); p.out_cs = 256; p.out_c0 = 0;
         if (launch_conv<256, 9, 1, false, EPI_RELU>(c, 3, pl->tmA[4], c->tmW[4], p, st)) return 1;
     }
+    if (prof_mark(c, st)) return 1;
     {  // L5 bottleneck.2 -> b1
         ConvParams p = base(5, 2);
         p.out = buf(B_B1); p.out_cs = 256; p.out_c0 = 0;
         if (launch_conv<256, 9, 1, false, EPI_RELU>(c, 3, pl->tmA[5], c->tmW[5], p, st)) return 1;
     }
+    if (prof_mark(c, st)) return 1;
     {  // L6 up2 (convT) -> cat2[:,0:128]
         ConvParams p = base(6, 2);
         p.n_tiles = 2;  // 4*128 columns in tiles of 256
         p.out = buf(B_CAT2); p.out_cs = 256; p.out_c0 = 0;
         if (launch_conv<256, 1, 1, false, EPI_CONVT>(c, 4, pl->tmA[6], c->tmW[6], p, st)) return 1;
     }
+    if (prof_mark(c, st)) return 1;
     {  // L7 upconv2.0 (reads cat2) -> u2a
         ConvParams p = base(7, 1);
         p.out = buf(B_U2A); p.out_cs = 128; p.out_c0 = 0;
         if (launch_conv<128, 9, 2, false, EPI_RELU>(c, 5, pl->tmA[7], c->tmW[7], p, st)) return 1;
     }
+    if (prof_mark(c, st)) return 1;
     {  // L8 upconv2.2 -> u2b
         ConvParams p = base(8, 1);
         p.out = buf(B_U2B); p.out_cs = 128; p.out_c0 = 0;
         if (launch_conv<128, 9, 2, false, EPI_RELU>(c, 5, pl->tmA[8], c->tmW[8], p, st)) return 1;
     }
+    if (prof_mark(c, st)) return 1;
     {  // L9 up1 (convT) -> cat1[:,0:64]
         ConvParams p = base(9, 1);
         p.n_tiles = 1;  // 4*64 columns in one tile of 256
         p.out = buf(B_CAT1); p.out_cs = 128; p.out_c0 = 0;
         if (launch_conv<256, 1, 1, false, EPI_CONVT>(c, 4, pl->tmA[9], c->tmW[9], p, st)) return 1;
     }
+    if (prof_mark(c, st)) return 1;
     {  // L10 upconv1.0 (reads cat1) -> u1a
         ConvParams p = base(10, 0);
         p.out = buf(B_U1A); p.out_cs = 64; p.out_c0 = 0;
         if (launch_conv<64, 9, 1, true, EPI_RELU>(c, 6, pl->tmA[10], c->tmW[10], p, st)) return 1;
     }
+    if (prof_mark(c, st)) return 1;
     {  // L11 upconv1.2 + tanh -> y
         ConvParams p = base(11, 0);
         p.out = io.y;
@@ -378,6 +401,7 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
             if (launch_conv<16, 9, 1, true, EPI_TANH_F32>(c, 8, pl->tmA[11], c->tmW[11], p, st)) return 1;
         }
     }
+    if (prof_mark(c, st)) return 1;
     return 0;
 }
 
@@ -511,6 +535,11 @@ int cid_set_option(cid_handle h, const char* name, int64_t value) {
         h->chunk = value;
         return 0;
     }
+    if (!strcmp(name, "profile")) {
+        h->profile = value != 0;
+        h->prof_used = 0;
+        return 0;
+    }
     set_error("unknown option '%s'", name);
     return 1;
 }
@@ -549,6 +578,24 @@ int cid_forward_u8_nhwc(cid_handle h, const uint8_t* x, uint8_t* y, int B, int H
 }
 
 int64_t cid_kernel_launches(cid_handle h) { return h ? h->launches : -1; }
+
+int cid_profile_read(cid_handle h, double* layer_ms, int64_t* passes) {
+    CID_REQUIRE(h && layer_ms && passes, "cid_profile_read: null argument");
+    DeviceGuard g(h->device);
+    CID_REQUIRE(g.ok, "cannot select CUDA device %d", h->device);
+    CID_CHECK_CUDA(cudaDeviceSynchronize());
+    for (int l = 0; l < 12; ++l) layer_ms[l] = 0.0;
+    const size_t n = h->prof_used / 13;
+    for (size_t i = 0; i < n; ++i)
+        for (int l = 0; l < 12; ++l) {
+            float ms = 0.f;
+            CID_CHECK_CUDA(cudaEventElapsedTime(&ms, h->prof_events[i * 13 + l], h->prof_events[i * 13 + l + 1]));
+            layer_ms[l] += ms;
+        }
+    *passes = static_cast<int64_t>(n);
+    h->prof_used = 0;
+    return 0;
+}
 
 int cid_debug_copy_activation(cid_handle h, const char* name, const void* ws, int B, int H, int W, void* dst_host,
                               size_t dst_bytes, int* channels, int* height, int* width) {

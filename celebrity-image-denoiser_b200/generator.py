@@ -105,6 +105,12 @@ class _Engine:
     def launches(self) -> int:
         return int(self.lib.cid_kernel_launches(self.handle))
 
+    def profile_read(self):
+        ms = (C.c_double * 12)()
+        n = C.c_int64()
+        _lib.check(self.lib.cid_profile_read(self.handle, ms, C.byref(n)), "cid_profile_read")
+        return list(ms), int(n.value)
+
 
 class DenoiseGenerator(nn.Module):
     def __init__(self):
@@ -152,6 +158,15 @@ class DenoiseGenerator(nn.Module):
 
     def kernel_launches(self) -> int:
         return sum(e.launches() for e in self._engines.values())
+
+    LAYER_NAMES = ("down1.0", "down1.2", "down2.0", "down2.2", "bottleneck.0", "bottleneck.2", "up2", "upconv2.0",
+                   "upconv2.2", "up1", "upconv1.0", "upconv1.2")
+
+    def profile_read(self):
+        """(per-layer summed ms dict, passes) since the last read; needs set_option("profile", 1)."""
+        eng = next(iter(self._engines.values()))
+        ms, n = eng.profile_read()
+        return dict(zip(self.LAYER_NAMES, ms)), n
 
     # ---- the reference's call: y = net(x) (backend/app.py:433) -----------------------------
     def forward(self, x: torch.Tensor) -> torch.Tensor:

@@ -37,6 +37,7 @@ _SIGNATURES = {
     "cid_normalize_u8_to_f32_nchw": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                                C.c_float, C.c_float, C.c_void_p]),
     "cid_kernel_launches": (C.c_int64, [C.c_void_p]),
+    "cid_profile_read": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "cid_debug_copy_activation": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                             C.c_void_p, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int),
                                             C.POINTER(C.c_int)]),

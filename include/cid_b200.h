@@ -53,7 +53,7 @@ int cid_set_param(cid_handle h, const char* key, const float* data, const int64_
 int cid_finalize(cid_handle h);
 
 /* Tunables. "chunk": images processed per pass through the layers (0 = whole batch); bounds the
- * activation working set (and the workspace). */
+ * activation working set (and the workspace). "profile": 1 = record per-layer CUDA events. */
 int cid_set_option(cid_handle h, const char* name, int64_t value);
 
 /* Bytes of device scratch a forward of B images of H x W (network-input size, multiples of 4)
@@ -110,6 +110,13 @@ int cid_normalize_u8_to_f32_nchw(cid_handle h, const uint8_t* in, float* out, in
 
 /* Number of kernels this handle has launched so far (bench.py's gpu_launches evidence). */
 int64_t cid_kernel_launches(cid_handle h);
+
+/* Per-layer device timing. After cid_set_option(h, "profile", 1) every pass through the layers
+ * records 13 CUDA events on the caller's stream (one before each of the 12 layers and one after
+ * the last). cid_profile_read synchronises the device, returns the summed milliseconds per layer
+ * (layer_ms[12], order: down1.0 down1.2 down2.0 down2.2 bottleneck.0 bottleneck.2 up2 upconv2.0
+ * upconv2.2 up1 upconv1.0 upconv1.2) and the number of passes since the previous read. */
+int cid_profile_read(cid_handle h, double* layer_ms, int64_t* passes);
 
 /* Test hook: copy one intermediate activation of the most recent forward (same B,H,W,ws) to host
  * as bf16 NHWC. name in {a0,cat1,p1,a2,cat2,p2,b0,b1,u2a,u2b,u1a}; *channels gets its C.
