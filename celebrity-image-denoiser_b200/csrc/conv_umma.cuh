@@ -89,6 +89,25 @@ __device__ __forceinline__ TileCoord decode_tile(const ConvParams& p, int mt) {
     return t;
 }
 
+// Walk an accumulator row in 32-column chunks with the next chunk's tcgen05.ld already in
+// flight while the current one is processed (two register buffers, fully unrolled).
+template <int NCH, class F>
+__device__ __forceinline__ void for_each_chunk(uint32_t taddr, F&& f) {
+    uint32_t va[32], vb[32];
+    tmem_ld_32x32(taddr, va);
+#pragma unroll
+    for (int ch = 0; ch < NCH; ch += 2) {
+        tmem_ld_wait();
+        if (ch + 1 < NCH) tmem_ld_32x32(taddr + (ch + 1) * 32, vb);
+        f(ch, va);
+        if (ch + 1 < NCH) {
+            tmem_ld_wait();
+            if (ch + 2 < NCH) tmem_ld_32x32(taddr + (ch + 2) * 32, va);
+            f(ch + 1, vb);
+        }
+    }
+}
+
 template <int N, int TAPS, int S, bool WRES, int EPI>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
@@ -150,7 +169,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         tma_load_2d(w_smem + (kb * TAPS + tap) * W_BYTES, &tmW, &w_full[0], kb * 64,
                                     tap * p.w_rows_per_tap, kEvictLast);
             }
-            uint32_t a_it = 0, w_it = 0;
+            uint32_t a_stage = 0, a_phase = 0, w_stage = 0, w_phase = 0;
             for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
                 const int n_tile = work % p.n_tiles;
                 const int st = work / p.n_tiles;
@@ -161,24 +180,26 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     for (int dx = 0; dx < DX; ++dx) {
 #pragma unroll
                         for (int s = 0; s < S; ++s) {
-                            const uint32_t stage = a_it % AST;
-                            const uint32_t ph = (a_it / AST) & 1;
-                            mbar_wait(&a_empty[stage], ph ^ 1);
-                            mbar_arrive_expect_tx(&a_full[stage], A_BYTES);
-                            tma_load_4d(a_smem + stage * A_BYTES, &tmA, &a_full[stage], kb * 64,
+                            mbar_wait(&a_empty[a_stage], a_phase ^ 1);
+                            mbar_arrive_expect_tx(&a_full[a_stage], A_BYTES);
+                            tma_load_4d(a_smem + a_stage * A_BYTES, &tmA, &a_full[a_stage], kb * 64,
                                         tc[s].x0 + dx - (DX == 3 ? 1 : 0), tc[s].y0 - (DY == 3 ? 1 : 0), tc[s].b,
                                         kEvictNormal);
-                            ++a_it;
+                            if (++a_stage == static_cast<uint32_t>(AST)) {
+                                a_stage = 0;
+                                a_phase ^= 1;
+                            }
                         }
                         if (!WRES) {
                             for (int dy = 0; dy < DY; ++dy) {
-                                const uint32_t stage = w_it % WST;
-                                const uint32_t ph = (w_it / WST) & 1;
-                                mbar_wait(&w_empty[stage], ph ^ 1);
-                                mbar_arrive_expect_tx(&w_full[stage], W_BYTES);
-                                tma_load_2d(w_smem + stage * W_BYTES, &tmW, &w_full[stage], kb * 64,
+                                mbar_wait(&w_empty[w_stage], w_phase ^ 1);
+                                mbar_arrive_expect_tx(&w_full[w_stage], W_BYTES);
+                                tma_load_2d(w_smem + w_stage * W_BYTES, &tmW, &w_full[w_stage], kb * 64,
                                             (dy * DX + dx) * p.w_rows_per_tap + n_tile * N, kEvictLast);
-                                ++w_it;
+                                if (++w_stage == static_cast<uint32_t>(WST)) {
+                                    w_stage = 0;
+                                    w_phase ^= 1;
+                                }
                             }
                         }
                     }
@@ -187,63 +208,76 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
     } else if (warp == 1) {
         // ======================= MMA issuer =======================
-        if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(128, N);
-            uint32_t a_it = 0, w_it = 0, acc_it = 0;
-            if (WRES) {
-                mbar_wait(&w_full[0], 0);
-                tc_fence_after();
-            }
-            for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
-                const uint32_t buf = acc_it & 1;
-                const uint32_t aph = (acc_it >> 1) & 1;
-                mbar_wait(&acc_empty[buf], aph ^ 1);
-                tc_fence_after();
-                const uint32_t d_base = tmem_base + buf * Cfg::ACC_COLS;
-                for (int kb = 0; kb < p.kb_count; ++kb) {
-                    for (int dx = 0; dx < DX; ++dx) {
+        // The whole warp walks the loop (warp-uniform control flow keeps descriptors in uniform
+        // registers); one elected lane issues the MMAs and the commits.
+        constexpr uint32_t idesc = umma_idesc_bf16(128, N);
+        const uint32_t a_lo0 = umma_desc_lo(smem_u32(a_smem));
+        const uint32_t w_lo0 = umma_desc_lo(smem_u32(w_smem));
+        uint32_t a_stage = 0, a_phase = 0, w_stage = 0, w_phase = 0, acc_it = 0;
+        if (WRES) {
+            mbar_wait(&w_full[0], 0);
+            tc_fence_after();
+        }
+        for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
+            const uint32_t buf = acc_it & 1;
+            const uint32_t aph = (acc_it >> 1) & 1;
+            mbar_wait(&acc_empty[buf], aph ^ 1);
+            tc_fence_after();
+            const uint32_t d_base = tmem_base + buf * Cfg::ACC_COLS;
+            for (int kb = 0; kb < p.kb_count; ++kb) {
+                for (int dx = 0; dx < DX; ++dx) {
+                    uint32_t stg[S];
 #pragma unroll
-                        for (int s = 0; s < S; ++s) {
-                            const uint32_t it = a_it + s;
-                            mbar_wait(&a_full[it % AST], (it / AST) & 1);
+                    for (int s = 0; s < S; ++s) {
+                        mbar_wait(&a_full[a_stage], a_phase);
+                        stg[s] = a_stage;
+                        if (++a_stage == static_cast<uint32_t>(AST)) {
+                            a_stage = 0;
+                            a_phase ^= 1;
                         }
-                        tc_fence_after();
-                        for (int dy = 0; dy < DY; ++dy) {
-                            uint32_t wb;
-                            uint32_t wstage = 0;
-                            if (WRES) {
-                                wb = smem_u32(w_smem + (kb * TAPS + dy * DX + dx) * W_BYTES);
-                            } else {
-                                wstage = w_it % WST;
-                                mbar_wait(&w_full[wstage], (w_it / WST) & 1);
-                                tc_fence_after();
-                                wb = smem_u32(w_smem + wstage * W_BYTES);
-                            }
-                            const uint32_t first = (kb == 0 && dx == 0 && dy == 0) ? 1u : 0u;
+                    }
+                    tc_fence_after();
+#pragma unroll
+                    for (int dy = 0; dy < DY; ++dy) {
+                        uint32_t w_lo;
+                        if (WRES) {
+                            w_lo = w_lo0 + static_cast<uint32_t>(kb * TAPS + dy * DX + dx) * (W_BYTES >> 4);
+                        } else {
+                            mbar_wait(&w_full[w_stage], w_phase);
+                            tc_fence_after();
+                            w_lo = w_lo0 + w_stage * (W_BYTES >> 4);
+                        }
+                        const uint32_t first = (kb == 0 && dx == 0 && dy == 0) ? 1u : 0u;
+                        if (elect_one()) {
 #pragma unroll
                             for (int s = 0; s < S; ++s) {
-                                const uint32_t ab =
-                                    smem_u32(a_smem + ((a_it + s) % AST) * A_BYTES) + dy * 1024;
+                                const uint32_t a_lo = a_lo0 + stg[s] * (A_BYTES >> 4) + dy * (1024 >> 4);
 #pragma unroll
                                 for (int k = 0; k < 4; ++k) {
-                                    umma_bf16_ss(d_base + s * N, umma_desc_sw128(ab + k * 32, 1024),
-                                                 umma_desc_sw128(wb + k * 32, 1024), idesc,
-                                                 (first && k == 0) ? 0u : 1u);
+                                    umma_bf16_ss(d_base + s * N, umma_desc_join(a_lo + 2 * k),
+                                                 umma_desc_join(w_lo + 2 * k), idesc, (first && k == 0) ? 0u : 1u);
                                 }
                             }
-                            if (!WRES) {
-                                umma_commit(&w_empty[wstage]);
-                                ++w_it;
+                            if (!WRES) umma_commit(&w_empty[w_stage]);
+                        }
+                        __syncwarp();
+                        if (!WRES) {
+                            if (++w_stage == static_cast<uint32_t>(WST)) {
+                                w_stage = 0;
+                                w_phase ^= 1;
                             }
                         }
-#pragma unroll
-                        for (int s = 0; s < S; ++s) umma_commit(&a_empty[(a_it + s) % AST]);
-                        a_it += S;
                     }
+                    if (elect_one()) {
+#pragma unroll
+                        for (int s = 0; s < S; ++s) umma_commit(&a_empty[stg[s]]);
+                    }
+                    __syncwarp();
                 }
-                umma_commit(&acc_full[buf]);
-                ++acc_it;
             }
+            if (elect_one()) umma_commit(&acc_full[buf]);
+            __syncwarp();
+            ++acc_it;
         }
     } else {
         // ======================= epilogue (4 warps) =======================
@@ -283,11 +317,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         prow = static_cast<__nv_bfloat16*>(p.out2) + ppix * p.out2_cs + p.out2_c0 + n_tile * N +
                                sub * 8;
                     }
-#pragma unroll 1
-                    for (int ch = 0; ch < N / 32; ++ch) {
-                        uint32_t v[32];
-                        tmem_ld_32x32(taddr + ch * 32, v);
-                        tmem_ld_wait();
+                    for_each_chunk<N / 32>(taddr, [&](int ch, uint32_t (&v)[32]) {
                         const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_tile * N + ch * 32);
                         uint32_t pk[16];
 #pragma unroll
@@ -320,16 +350,12 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             const uint32_t o3 = sub == 0 ? pk[3] : sub == 1 ? pk[7] : sub == 2 ? pk[11] : pk[15];
                             if (pvalid) st_global_v4(prow + ch * 32, o0, o1, o2, o3);
                         }
-                    }
+                    });
                 } else if constexpr (EPI == EPI_CONVT) {
                     // GEMM column n = quadrant*cout + c, quadrant = dy*2+dx; output pixel (2y+dy, 2x+dx).
                     __nv_bfloat16* out = static_cast<__nv_bfloat16*>(p.out);
                     const int OH = p.H * 2, OW = p.W * 2;
-#pragma unroll 1
-                    for (int ch = 0; ch < N / 32; ++ch) {
-                        uint32_t v[32];
-                        tmem_ld_32x32(taddr + ch * 32, v);
-                        tmem_ld_wait();
+                    for_each_chunk<N / 32>(taddr, [&](int ch, uint32_t (&v)[32]) {
                         const int n = n_tile * N + ch * 32;
                         const int quad = n / p.cout;
                         const int c = n - quad * p.cout;
@@ -351,7 +377,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             for (int j = 0; j < 4; ++j)
                                 st_global_v4(orow + j * 8, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
                         }
-                    }
+                    });
                 } else {
                     // final 64->3 conv: columns 0..2 are real, tanh, then fp32 NCHW or u8 NHWC (cropped)
                     uint32_t v[4];

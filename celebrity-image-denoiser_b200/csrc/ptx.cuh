@@ -18,6 +18,20 @@ __device__ __forceinline__ uint32_t lane_id() {
     return l;
 }
 
+// One lane of a fully converged warp returns true (warp-uniform control flow is kept, so the
+// compiler can hold descriptors in uniform registers around the elected region).
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(pred));
+    return pred != 0;
+}
+
 // ----------------------------------------------------------------------------------------------
 // mbarrier
 // ----------------------------------------------------------------------------------------------
@@ -137,6 +151,16 @@ __device__ __forceinline__ void umma_bf16_ss(uint32_t tmem_d, uint64_t adesc, ui
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                  : "memory");
+}
+
+// Upper / lower 32-bit halves of the K-major SW128 descriptor below; the lower half is
+// (address >> 4) | LBO, so stepping 32 bytes along K inside the swizzle atom is "+2".
+constexpr uint32_t kDescHiSw128Sbo1024 = (1024u >> 4) | (1u << 14) | (2u << 29);
+__device__ __forceinline__ uint32_t umma_desc_lo(uint32_t smem_addr) {
+    return ((smem_addr & 0x3FFFF) >> 4) | (1u << 16);
+}
+__device__ __forceinline__ uint64_t umma_desc_join(uint32_t lo) {
+    return (static_cast<uint64_t>(kDescHiSw128Sbo1024) << 32) | lo;
 }
 
 // Shared-memory matrix descriptor, K-major operand, 128-byte swizzle, rows of 128 B
