@@ -22,6 +22,7 @@
 #include "cid_internal.h"
 #include "conv_umma.cuh"
 #include "edge_kernels.cuh"
+#include "first_conv_umma.cuh"
 
 namespace cid {
 
@@ -91,14 +92,14 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // NHWC bf16 activation [B,H,W,C]: box = 64 channels x 8 pixels x box_rows rows x 1 image, 128B swizzle.
-static int make_act_map(CUtensorMap* tm, const void* base, int B, int H, int W, int C, int box_rows) {
+static int make_act_map(CUtensorMap* tm, const void* base, int B, int H, int W, int C, int box_rows, int box_px) {
     EncodeTiledFn fn = get_encode_fn();
     CID_REQUIRE(fn, "cuTensorMapEncodeTiled entry point not available");
     cuuint64_t dims[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H),
                           static_cast<cuuint64_t>(B)};
     cuuint64_t strides[3] = {static_cast<cuuint64_t>(C) * 2, static_cast<cuuint64_t>(W) * C * 2,
                              static_cast<cuuint64_t>(H) * W * C * 2};
-    cuuint32_t box[4] = {64, 8, static_cast<cuuint32_t>(box_rows), 1};
+    cuuint32_t box[4] = {64, static_cast<cuuint32_t>(box_px), static_cast<cuuint32_t>(box_rows), 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -162,6 +163,25 @@ static int pack_layer(cid_ctx* c, int l) {
             for (int t = 0; t < 27; ++t) fw->w[t][co] = w[static_cast<size_t>(co) * 27 + t];  // [co][ci][ky][kx]
             fw->b[co] = b[co];
         }
+        // tensor-core variant: per tap a [cout 64][K 16] tile in the un-swizzled K-major layout
+        // [tap][k chunk][cout][8 bf16]; K chunk 0 = [w_r w_g w_b | w_r w_g w_b | 0 0] (the input is
+        // split hi+lo along K), K chunk 1 = 0.
+        std::vector<uint16_t> pk(kFirstWBytes / 2, 0);
+        for (int tap = 0; tap < 9; ++tap)
+            for (int co = 0; co < 64; ++co)
+                for (int ci = 0; ci < 3; ++ci) {
+                    const uint16_t v = f32_to_bf16_rne(w[(static_cast<size_t>(co) * 3 + ci) * 9 + tap]);
+                    pk[((tap * 2 + 0) * 64 + co) * 8 + ci] = v;
+                    pk[((tap * 2 + 0) * 64 + co) * 8 + 3 + ci] = v;
+                }
+        if (c->w_dev[0]) cudaFree(c->w_dev[0]);
+        if (c->bias_dev[0]) cudaFree(c->bias_dev[0]);
+        c->w_dev[0] = nullptr;
+        c->bias_dev[0] = nullptr;
+        CID_CHECK_CUDA(cudaMalloc(&c->w_dev[0], pk.size() * 2));
+        CID_CHECK_CUDA(cudaMemcpy(c->w_dev[0], pk.data(), pk.size() * 2, cudaMemcpyHostToDevice));
+        CID_CHECK_CUDA(cudaMalloc(reinterpret_cast<void**>(&c->bias_dev[0]), 64 * 4));
+        CID_CHECK_CUDA(cudaMemcpy(c->bias_dev[0], b.data(), 64 * 4, cudaMemcpyHostToDevice));
         return 0;
     }
 
@@ -224,8 +244,9 @@ static int get_plan(cid_ctx* c, int Bc, int H, int W, const void* ws, cid_plan**
         const int buf = layer_in_buf(l);
         const int lv = kBufLevel[buf];
         const int rows = kLayers[l].kind == L_CONVT ? 16 : 18;
+        const int px = (kLayers[l].kind == L_CONV && c->patch) ? 10 : 8;
         if (make_act_map(&pl.tmA[l], static_cast<const uint8_t*>(ws) + pl.off[buf], Bc, H >> lv, W >> lv, kBufC[buf],
-                         rows))
+                         rows, px))
             return 1;
     }
     c->plans.push_back(pl);
@@ -236,10 +257,10 @@ static int get_plan(cid_ctx* c, int Bc, int H, int W, const void* ws, cid_plan**
 // ---------------------------------------------------------------------------------------------
 // launches
 // ---------------------------------------------------------------------------------------------
-template <int N, int TAPS, int S, bool WRES, int EPI>
+template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0>
 static int launch_conv(cid_ctx* c, int slot, const CUtensorMap& tmA, const CUtensorMap& tmW, ConvParams p,
                        cudaStream_t st) {
-    using Cfg = ConvCfg<N, TAPS, S, WRES, EPI>;
+    using Cfg = ConvCfg<N, TAPS, S, WRES, EPI, PW>;
     const int budget = c->max_smem - 1024 - 512;
     int w_stages = WRES ? 1 : 4;
     const int w_bytes = (WRES ? p.kb_count * TAPS : w_stages) * Cfg::W_BYTES;
@@ -252,7 +273,7 @@ static int launch_conv(cid_ctx* c, int slot, const CUtensorMap& tmA, const CUten
     p.m_tiles = p.B * p.tiles_x * p.tiles_y;
     p.num_work = ((p.m_tiles + S - 1) / S) * p.n_tiles;
     const int smem = Cfg::smem_bytes(p.kb_count, a_stages, w_stages);
-    auto kern = conv_umma_kernel<N, TAPS, S, WRES, EPI>;
+    auto kern = conv_umma_kernel<N, TAPS, S, WRES, EPI, PW>;
     if (!(c->attr_done & (1u << slot))) {
         CID_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c->max_smem));
         c->attr_done |= (1u << slot);
@@ -290,7 +311,31 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
 
     if (prof_mark(c, st)) return 1;
     // L0
-    {
+    if (c->first_tc) {
+        FirstParams fp;
+        memset(&fp, 0, sizeof(fp));
+        fp.B = nb; fp.H = H; fp.W = W;
+        fp.in = io.x; fp.in_h = io.in_h; fp.in_w = io.in_w; fp.pad_l = io.pad_l; fp.pad_t = io.pad_t;
+        fp.bias = c->bias_dev[0];
+        fp.out = buf(B_A0);
+        fp.tiles_x = (W + 7) / 8;
+        fp.tiles_y = (H + 15) / 16;
+        fp.m_tiles = nb * fp.tiles_x * fp.tiles_y;
+        const int smem = kFirstSmem;
+        fp.w_packed = static_cast<const uint4*>(c->w_dev[0]);
+        if (!(c->attr_done & (1u << 30))) {
+            CID_CHECK_CUDA(cudaFuncSetAttribute(first_conv_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            CID_CHECK_CUDA(cudaFuncSetAttribute(first_conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            c->attr_done |= (1u << 30);
+        }
+        const int grid = std::min(fp.m_tiles, c->num_sms);
+        if (io.u8)
+            first_conv_umma_kernel<true><<<grid, kFirstThreads, smem, st>>>(fp);
+        else
+            first_conv_umma_kernel<false><<<grid, kFirstThreads, smem, st>>>(fp);
+        CID_CHECK_CUDA(cudaGetLastError());
+        c->launches++;
+    } else {
         FirstConvParams fp;
         fp.B = nb;
         fp.H = H;
@@ -324,6 +369,7 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         p.bias = c->bias_dev[l];
         p.cout = kLayers[l].cout;
         p.w_rows_per_tap = std::max(kLayers[l].cout, 16);
+        p.debug_flags = c->debug_flags;
         return p;
     };
 
@@ -331,32 +377,32 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         ConvParams p = base(1, 0);
         p.out = buf(B_CAT1); p.out_cs = 128; p.out_c0 = 64;
         p.out2 = buf(B_P1); p.out2_cs = 64; p.out2_c0 = 0;
-        if (launch_conv<64, 9, 1, true, EPI_RELU_POOL>(c, 0, pl->tmA[1], c->tmW[1], p, st)) return 1;
+        if ((c->patch ? launch_conv<64, 9, 1, true, EPI_RELU_POOL, 10>(c, 16, pl->tmA[1], c->tmW[1], p, st) : launch_conv<64, 9, 1, true, EPI_RELU_POOL, 0>(c, 0, pl->tmA[1], c->tmW[1], p, st))) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L2 down2.0 -> a2
         ConvParams p = base(2, 1);
         p.out = buf(B_A2); p.out_cs = 128; p.out_c0 = 0;
-        if (launch_conv<128, 9, 1, true, EPI_RELU>(c, 1, pl->tmA[2], c->tmW[2], p, st)) return 1;
+        if ((c->patch ? launch_conv<128, 9, 1, true, EPI_RELU, 10>(c, 17, pl->tmA[2], c->tmW[2], p, st) : launch_conv<128, 9, 1, true, EPI_RELU, 0>(c, 1, pl->tmA[2], c->tmW[2], p, st))) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L3 down2.2 -> cat2[:,128:256] + p2
         ConvParams p = base(3, 1);
         p.out = buf(B_CAT2); p.out_cs = 256; p.out_c0 = 128;
         p.out2 = buf(B_P2); p.out2_cs = 128; p.out2_c0 = 0;
-        if (launch_conv<128, 9, 2, false, EPI_RELU_POOL>(c, 2, pl->tmA[3], c->tmW[3], p, st)) return 1;
+        if ((c->patch ? launch_conv<128, 9, 2, false, EPI_RELU_POOL, 10>(c, 18, pl->tmA[3], c->tmW[3], p, st) : launch_conv<128, 9, 2, false, EPI_RELU_POOL, 0>(c, 2, pl->tmA[3], c->tmW[3], p, st))) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L4 bottleneck.0 -> b0
         ConvParams p = base(4, 2);
         p.out = buf(B_B0); p.out_cs = 256; p.out_c0 = 0;
-        if (launch_conv<256, 9, 1, false, EPI_RELU>(c, 3, pl->tmA[4], c->tmW[4], p, st)) return 1;
+        if ((c->patch ? launch_conv<256, 9, 1, false, EPI_RELU, 10>(c, 19, pl->tmA[4], c->tmW[4], p, st) : launch_conv<256, 9, 1, false, EPI_RELU, 0>(c, 3, pl->tmA[4], c->tmW[4], p, st))) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L5 bottleneck.2 -> b1
         ConvParams p = base(5, 2);
         p.out = buf(B_B1); p.out_cs = 256; p.out_c0 = 0;
-        if (launch_conv<256, 9, 1, false, EPI_RELU>(c, 3, pl->tmA[5], c->tmW[5], p, st)) return 1;
+        if ((c->patch ? launch_conv<256, 9, 1, false, EPI_RELU, 10>(c, 19, pl->tmA[5], c->tmW[5], p, st) : launch_conv<256, 9, 1, false, EPI_RELU, 0>(c, 3, pl->tmA[5], c->tmW[5], p, st))) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L6 up2 (convT) -> cat2[:,0:128]
@@ -369,13 +415,13 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
     {  // L7 upconv2.0 (reads cat2) -> u2a
         ConvParams p = base(7, 1);
         p.out = buf(B_U2A); p.out_cs = 128; p.out_c0 = 0;
-        if (launch_conv<128, 9, 2, false, EPI_RELU>(c, 5, pl->tmA[7], c->tmW[7], p, st)) return 1;
+        if ((c->patch ? launch_conv<128, 9, 2, false, EPI_RELU, 10>(c, 21, pl->tmA[7], c->tmW[7], p, st) : launch_conv<128, 9, 2, false, EPI_RELU, 0>(c, 5, pl->tmA[7], c->tmW[7], p, st))) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L8 upconv2.2 -> u2b
         ConvParams p = base(8, 1);
         p.out = buf(B_U2B); p.out_cs = 128; p.out_c0 = 0;
-        if (launch_conv<128, 9, 2, false, EPI_RELU>(c, 5, pl->tmA[8], c->tmW[8], p, st)) return 1;
+        if ((c->patch ? launch_conv<128, 9, 2, false, EPI_RELU, 10>(c, 21, pl->tmA[8], c->tmW[8], p, st) : launch_conv<128, 9, 2, false, EPI_RELU, 0>(c, 5, pl->tmA[8], c->tmW[8], p, st))) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L9 up1 (convT) -> cat1[:,0:64]
@@ -388,7 +434,7 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
     {  // L10 upconv1.0 (reads cat1) -> u1a
         ConvParams p = base(10, 0);
         p.out = buf(B_U1A); p.out_cs = 64; p.out_c0 = 0;
-        if (launch_conv<64, 9, 1, true, EPI_RELU>(c, 6, pl->tmA[10], c->tmW[10], p, st)) return 1;
+        if ((c->patch ? launch_conv<64, 9, 1, true, EPI_RELU, 10>(c, 22, pl->tmA[10], c->tmW[10], p, st) : launch_conv<64, 9, 1, true, EPI_RELU, 0>(c, 6, pl->tmA[10], c->tmW[10], p, st))) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L11 upconv1.2 + tanh -> y
@@ -396,9 +442,9 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         p.out = io.y;
         if (io.u8) {
             p.crop_l = io.pad_l; p.crop_t = io.pad_t; p.out_h = io.in_h; p.out_w = io.in_w;
-            if (launch_conv<16, 9, 1, true, EPI_TANH_U8>(c, 7, pl->tmA[11], c->tmW[11], p, st)) return 1;
+            if ((c->patch ? launch_conv<16, 9, 1, true, EPI_TANH_U8, 10>(c, 23, pl->tmA[11], c->tmW[11], p, st) : launch_conv<16, 9, 1, true, EPI_TANH_U8, 0>(c, 7, pl->tmA[11], c->tmW[11], p, st))) return 1;
         } else {
-            if (launch_conv<16, 9, 1, true, EPI_TANH_F32>(c, 8, pl->tmA[11], c->tmW[11], p, st)) return 1;
+            if ((c->patch ? launch_conv<16, 9, 1, true, EPI_TANH_F32, 10>(c, 24, pl->tmA[11], c->tmW[11], p, st) : launch_conv<16, 9, 1, true, EPI_TANH_F32, 0>(c, 8, pl->tmA[11], c->tmW[11], p, st))) return 1;
         }
     }
     if (prof_mark(c, st)) return 1;
@@ -533,6 +579,19 @@ int cid_set_option(cid_handle h, const char* name, int64_t value) {
     if (!strcmp(name, "chunk")) {
         CID_REQUIRE(value >= 0, "chunk must be >= 0");
         h->chunk = value;
+        return 0;
+    }
+    if (!strcmp(name, "first_tc")) {
+        h->first_tc = value != 0;
+        return 0;
+    }
+    if (!strcmp(name, "patch")) {
+        h->patch = value != 0;
+        h->plans.clear();
+        return 0;
+    }
+    if (!strcmp(name, "debug_flags")) {
+        h->debug_flags = static_cast<int>(value);
         return 0;
     }
     if (!strcmp(name, "profile")) {

@@ -73,6 +73,9 @@ struct cid_ctx {
     uint32_t attr_done = 0;           // bit per kernel instantiation: max-dynamic-smem attribute set
     std::map<uint64_t, void*> resize_coeffs;  // (in_size,out_size) -> device coefficient block
     // per-layer timing ("profile" option): 13 events bracket the 12 layers of every pass
+    int debug_flags = 0;
+    bool first_tc = true;             // layer 0 on tensor cores (false: CUDA-core direct conv)
+    bool patch = true;                // 3x3 layers load one halo patch per K block instead of 3 boxes
     bool profile = false;
     std::vector<cudaEvent_t> prof_events;  // 13 per recorded pass
     size_t prof_used = 0;                  // events recorded since the last cid_profile_read

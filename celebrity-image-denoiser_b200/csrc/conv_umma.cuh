@@ -49,17 +49,26 @@ struct ConvParams {
     void* out2;          // EPI_RELU_POOL: pooled output buffer
     int out2_cs, out2_c0;
     int crop_l, crop_t, out_h, out_w;  // EPI_TANH_U8: crop window into the u8 NHWC result
+    int debug_flags;     // bring-up experiments only: 1 = epilogue skips global stores, 2 = skips TMEM reads too
 };
 
-template <int N, int TAPS, int S, bool WRES, int EPI>
+// PW = 0: one TMA box per horizontal tap (8 px wide, 1024-B row groups).
+// PW = 10: one halo patch {64 ch, 10 px, 18 rows} per K block; tap (dy,dx) is the same patch read at
+//          start + (dy*PW + dx)*128 B with SBO = PW*128 B (relies on the 128-B swizzle being a
+//          function of the absolute shared-memory address, for TMA writes and UMMA reads alike).
+template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0>
 struct ConvCfg {
     static_assert(TAPS == 9 || TAPS == 1, "3x3 or 1x1");
     static_assert(N % 16 == 0 && N >= 16 && N <= 256, "UMMA N for M=128");
     static_assert(2 * S * N <= 512, "two accumulator buffers must fit TMEM");
     static constexpr int DX = TAPS == 9 ? 3 : 1;
     static constexpr int DY = DX;
+    static_assert(PW == 0 || TAPS == 9, "halo patches only for 3x3");
     static constexpr int A_ROWS = TAPS == 9 ? 18 : 16;
-    static constexpr int A_BYTES = A_ROWS * 1024;
+    static constexpr int A_LOADS = PW ? 1 : DX;                 // TMA boxes per K block per tile
+    static constexpr int A_TX = (PW ? PW : 8) * A_ROWS * 128;   // bytes one box delivers
+    static constexpr int A_BYTES = (A_TX + 1023) / 1024 * 1024; // stage pitch (1024-B aligned)
+    static constexpr int SBO = (PW ? PW : 8) * 128;
     static constexpr int W_BYTES = N * 128;
     static constexpr int ACC_COLS = S * N;
     static constexpr int TMEM_COLS = (2 * ACC_COLS <= 32)    ? 32
@@ -108,12 +117,13 @@ __device__ __forceinline__ void for_each_chunk(uint32_t taddr, F&& f) {
     }
 }
 
-template <int N, int TAPS, int S, bool WRES, int EPI>
+template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                  const ConvParams p) {
-    using Cfg = ConvCfg<N, TAPS, S, WRES, EPI>;
-    constexpr int DX = Cfg::DX, DY = Cfg::DY;
+    using Cfg = ConvCfg<N, TAPS, S, WRES, EPI, PW>;
+    constexpr int DX = Cfg::DX, DY = Cfg::DY, AL = Cfg::A_LOADS;
+    constexpr int DXI = PW ? DX : 1;  // horizontal taps served by one A box
     constexpr int A_BYTES = Cfg::A_BYTES, W_BYTES = Cfg::W_BYTES;
 
     extern __shared__ uint8_t smem_raw[];
@@ -177,28 +187,31 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
                 for (int s = 0; s < S; ++s) tc[s] = decode_tile(p, st * S + s);
                 for (int kb = 0; kb < p.kb_count; ++kb) {
-                    for (int dx = 0; dx < DX; ++dx) {
+                    for (int al = 0; al < AL; ++al) {
 #pragma unroll
                         for (int s = 0; s < S; ++s) {
                             mbar_wait(&a_empty[a_stage], a_phase ^ 1);
-                            mbar_arrive_expect_tx(&a_full[a_stage], A_BYTES);
+                            mbar_arrive_expect_tx(&a_full[a_stage], Cfg::A_TX);
                             tma_load_4d(a_smem + a_stage * A_BYTES, &tmA, &a_full[a_stage], kb * 64,
-                                        tc[s].x0 + dx - (DX == 3 ? 1 : 0), tc[s].y0 - (DY == 3 ? 1 : 0), tc[s].b,
-                                        kEvictNormal);
+                                        tc[s].x0 + (PW ? 0 : al) - (DX == 3 ? 1 : 0), tc[s].y0 - (DY == 3 ? 1 : 0),
+                                        tc[s].b, kEvictNormal);
                             if (++a_stage == static_cast<uint32_t>(AST)) {
                                 a_stage = 0;
                                 a_phase ^= 1;
                             }
                         }
                         if (!WRES) {
-                            for (int dy = 0; dy < DY; ++dy) {
-                                mbar_wait(&w_empty[w_stage], w_phase ^ 1);
-                                mbar_arrive_expect_tx(&w_full[w_stage], W_BYTES);
-                                tma_load_2d(w_smem + w_stage * W_BYTES, &tmW, &w_full[w_stage], kb * 64,
-                                            (dy * DX + dx) * p.w_rows_per_tap + n_tile * N, kEvictLast);
-                                if (++w_stage == static_cast<uint32_t>(WST)) {
-                                    w_stage = 0;
-                                    w_phase ^= 1;
+                            for (int dxi = 0; dxi < DXI; ++dxi) {
+                                const int dx = PW ? dxi : al;
+                                for (int dy = 0; dy < DY; ++dy) {
+                                    mbar_wait(&w_empty[w_stage], w_phase ^ 1);
+                                    mbar_arrive_expect_tx(&w_full[w_stage], W_BYTES);
+                                    tma_load_2d(w_smem + w_stage * W_BYTES, &tmW, &w_full[w_stage], kb * 64,
+                                                (dy * DX + dx) * p.w_rows_per_tap + n_tile * N, kEvictLast);
+                                    if (++w_stage == static_cast<uint32_t>(WST)) {
+                                        w_stage = 0;
+                                        w_phase ^= 1;
+                                    }
                                 }
                             }
                         }
@@ -225,7 +238,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             tc_fence_after();
             const uint32_t d_base = tmem_base + buf * Cfg::ACC_COLS;
             for (int kb = 0; kb < p.kb_count; ++kb) {
-                for (int dx = 0; dx < DX; ++dx) {
+                for (int al = 0; al < AL; ++al) {
                     uint32_t stg[S];
 #pragma unroll
                     for (int s = 0; s < S; ++s) {
@@ -238,33 +251,41 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     }
                     tc_fence_after();
 #pragma unroll
-                    for (int dy = 0; dy < DY; ++dy) {
-                        uint32_t w_lo;
-                        if (WRES) {
-                            w_lo = w_lo0 + static_cast<uint32_t>(kb * TAPS + dy * DX + dx) * (W_BYTES >> 4);
-                        } else {
-                            mbar_wait(&w_full[w_stage], w_phase);
-                            tc_fence_after();
-                            w_lo = w_lo0 + w_stage * (W_BYTES >> 4);
-                        }
-                        const uint32_t first = (kb == 0 && dx == 0 && dy == 0) ? 1u : 0u;
-                        if (elect_one()) {
+                    for (int dxi = 0; dxi < DXI; ++dxi) {
+                        const int dx = PW ? dxi : al;
 #pragma unroll
-                            for (int s = 0; s < S; ++s) {
-                                const uint32_t a_lo = a_lo0 + stg[s] * (A_BYTES >> 4) + dy * (1024 >> 4);
-#pragma unroll
-                                for (int k = 0; k < 4; ++k) {
-                                    umma_bf16_ss(d_base + s * N, umma_desc_join(a_lo + 2 * k),
-                                                 umma_desc_join(w_lo + 2 * k), idesc, (first && k == 0) ? 0u : 1u);
-                                }
+                        for (int dy = 0; dy < DY; ++dy) {
+                            uint32_t w_lo;
+                            if (WRES) {
+                                w_lo = w_lo0 + static_cast<uint32_t>(kb * TAPS + dy * DX + dx) * (W_BYTES >> 4);
+                            } else {
+                                mbar_wait(&w_full[w_stage], w_phase);
+                                tc_fence_after();
+                                w_lo = w_lo0 + w_stage * (W_BYTES >> 4);
                             }
-                            if (!WRES) umma_commit(&w_empty[w_stage]);
-                        }
-                        __syncwarp();
-                        if (!WRES) {
-                            if (++w_stage == static_cast<uint32_t>(WST)) {
-                                w_stage = 0;
-                                w_phase ^= 1;
+                            const uint32_t first = (kb == 0 && dx == 0 && dy == 0) ? 1u : 0u;
+                            if (elect_one()) {
+#pragma unroll
+                                for (int s = 0; s < S; ++s) {
+                                    // tap (dy,dx): PW=0 -> box dx, rows shifted by dy groups of 1024 B;
+                                    //              PW>0 -> patch pixel offset dy*PW+dx, 128 B each
+                                    const uint32_t a_lo = a_lo0 + stg[s] * (A_BYTES >> 4) +
+                                                          (PW ? (dy * PW + dxi) * (128 >> 4) : dy * (1024 >> 4));
+#pragma unroll
+                                    for (int k = 0; k < 4; ++k) {
+                                        umma_bf16_ss(d_base + s * N, umma_desc_join<Cfg::SBO>(a_lo + 2 * k),
+                                                     umma_desc_join<1024>(w_lo + 2 * k), idesc,
+                                                     (first && k == 0) ? 0u : 1u);
+                                    }
+                                }
+                                if (!WRES) umma_commit(&w_empty[w_stage]);
+                            }
+                            __syncwarp();
+                            if (!WRES) {
+                                if (++w_stage == static_cast<uint32_t>(WST)) {
+                                    w_stage = 0;
+                                    w_phase ^= 1;
+                                }
                             }
                         }
                     }
@@ -299,7 +320,8 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 const TileCoord tc = decode_tile(p, mt);
                 const int y = tc.y0 + yl;
                 const int x = tc.x0 + xl;
-                const bool valid = (mt < p.m_tiles) && (y < p.H) && (x < p.W);
+                const bool valid = (mt < p.m_tiles) && (y < p.H) && (x < p.W) && !(p.debug_flags & 1);
+                if (p.debug_flags & 2) continue;
                 const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * Cfg::ACC_COLS + s * N;
 
                 if constexpr (EPI == EPI_RELU || EPI == EPI_RELU_POOL) {

@@ -1,0 +1,238 @@
+// K0: the first generator layer (3 -> 64, 3x3, pad 1, +ReLU) on tcgen05 tensor cores, with the
+// reference's Pad / ToTensor / Normalize folded into the loader.
+//
+// Reference ops (file:line in /root/reference):
+//   get_padding + transforms.Pad(fill=0)          backend/app.py:276-281, 383-385
+//   ToTensor -> Normalize([.5]*3,[.5]*3)          backend/app.py:401-406
+//   down1[0] = Conv2d(3,64,k3,p1) + ReLU          backend/app.py:43-44
+//
+// GEMM view per tap: M = 128 pixels (8 x 16 tile), N = 64, K = 16 of which 6 are used: every input
+// value x is split x = hi + lo (two bf16) so the INPUT keeps ~16 mantissa bits on a bf16 tensor
+// core; K row of a pixel = [hi_r hi_g hi_b lo_r lo_g lo_b 0 0 | 0 x8]. The layer is HBM-bound
+// (3..12 B in, 128 B out per pixel), so the padded K is free.
+//
+// The A operand is the tile's 10 x 18 halo patch, one 16-byte K chunk per pixel, stored in the
+// un-swizzled K-major UMMA layout (8-row core matrices: rows 16 B apart, 8-row groups SBO = 160 B
+// apart = one patch row, the second K chunk LBO bytes away in an all-zero plane). Tap (dy,dx) is
+// the same patch read at start + (dy*10+dx)*16 B, so each input pixel is converted and written
+// to shared memory once per tile (180 writes) instead of 9 times.
+//
+// Warps (288 threads): 0..3 build patches (u8 mode: 3 byte loads + 3 LUT lookups + one 16-B
+// store per pixel); warp 4 owns TMEM and issues 9 MMAs per tile; warps 5..8 run the bias+ReLU
+// epilogue (TMEM lane quarter = warp & 3) and store bf16 NHWC.
+#pragma once
+#include <cuda_bf16.h>
+
+#include "conv_umma.cuh"
+
+namespace cid {
+
+constexpr int kFirstThreads = 288;
+constexpr int kFirstStages = 8;
+constexpr int kFirstPlane = 180 * 16;          // one K chunk of the 10x18 patch
+constexpr int kFirstStageBytes = 2 * kFirstPlane;
+constexpr int kFirstWBytes = 9 * 2 * 64 * 16;  // [tap][k chunk][cout][8 bf16]
+constexpr int kFirstSmem = 1024 + kFirstWBytes + kFirstStages * kFirstStageBytes + 1024 + 256;
+
+struct FirstParams {
+    int B, H, W;          // network-input dims (after padding to a multiple of 4)
+    const void* in;       // fp32 NCHW [B,3,H,W] in [-1,1]   or   u8 NHWC [B,in_h,in_w,3]
+    int in_h, in_w;       // u8 mode: un-padded image size
+    int pad_l, pad_t;     // u8 mode: where the image sits inside the padded frame
+    const uint4* w_packed;  // kFirstWBytes of bf16 in the shared-memory layout above
+    const float* bias;    // fp32 [64]
+    __nv_bfloat16* out;   // NHWC [B,H,W,64]
+    int tiles_x, tiles_y, m_tiles;
+};
+
+// un-swizzled K-major descriptor: start[0,14) LBO[16,30) SBO[32,46) version[46,48)=1 layout[61,64)=0
+__device__ __forceinline__ uint64_t umma_desc_nosw(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    const uint32_t lo = ((smem_addr & 0x3FFFF) >> 4) | ((lbo_bytes >> 4) << 16);
+    const uint32_t hi = (sbo_bytes >> 4) | (1u << 14);
+    return (static_cast<uint64_t>(hi) << 32) | lo;
+}
+
+__device__ __forceinline__ uint32_t split_hi_lo(float x) {
+    const __nv_bfloat16 h = __float2bfloat16_rn(x);
+    const __nv_bfloat16 l = __float2bfloat16_rn(x - __bfloat162float(h));
+    return static_cast<uint32_t>(__bfloat16_as_ushort(h)) | (static_cast<uint32_t>(__bfloat16_as_ushort(l)) << 16);
+}
+
+template <bool U8>
+__global__ void __launch_bounds__(kFirstThreads, 1) first_conv_umma_kernel(const FirstParams p) {
+    constexpr int N = 64;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* w_smem = smem;
+    uint8_t* a_smem = smem + kFirstWBytes;
+    uint32_t* lut = reinterpret_cast<uint32_t*>(a_smem + kFirstStages * kFirstStageBytes);  // 256 x {hi | lo<<16}
+    uint64_t* bars = reinterpret_cast<uint64_t*>(lut + 256);
+    uint64_t* a_full = bars;
+    uint64_t* a_empty = bars + kFirstStages;
+    uint64_t* acc_full = bars + 2 * kFirstStages;
+    uint64_t* acc_empty = acc_full + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    // one-time: weights -> smem, zero K-chunk-1 planes, u8 LUT, barriers, TMEM
+    for (int i = threadIdx.x; i < kFirstWBytes / 16; i += kFirstThreads)
+        reinterpret_cast<uint4*>(w_smem)[i] = __ldg(p.w_packed + i);
+    for (int i = threadIdx.x; i < kFirstStages * kFirstStageBytes / 16; i += kFirstThreads)
+        reinterpret_cast<uint4*>(a_smem)[i] = make_uint4(0u, 0u, 0u, 0u);
+    if (U8 && threadIdx.x < 256) {
+        // ToTensor: u8 -> f32 / 255 ; Normalize: (v - 0.5) / 0.5, each op rounded (backend/app.py:401-406)
+        const float v = __fdiv_rn(__fsub_rn(__fdiv_rn(static_cast<float>(threadIdx.x), 255.f), 0.5f), 0.5f);
+        lut[threadIdx.x] = split_hi_lo(v);
+    }
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kFirstStages; ++i) {
+            mbar_init(&a_full[i], 128);
+            mbar_init(&a_empty[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&acc_full[i], 1);
+            mbar_init(&acc_empty[i], 4);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 4) tmem_alloc(tmem_slot, 128);
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp < 4) {
+        // ======================= patch producers =======================
+        uint32_t stage = 0, phase = 0;
+        for (int mt = blockIdx.x; mt < p.m_tiles; mt += gridDim.x) {
+            const int tx = mt % p.tiles_x;
+            const int r2 = mt / p.tiles_x;
+            const int ty = r2 % p.tiles_y;
+            const int b = r2 / p.tiles_y;
+            uint4 px[2];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int t = threadIdx.x + h * 128;  // patch pixel 0..179
+                const int py = t / 10, pxx = t - py * 10;
+                const int yy = ty * 16 - 1 + py, xx = tx * 8 - 1 + pxx;
+                uint32_t l0 = 0u, l1 = 0u, l2 = 0u;  // conv zero padding / outside the frame
+                if (t < 180 && yy >= 0 && yy < p.H && xx >= 0 && xx < p.W) {
+                    if constexpr (U8) {
+                        const int oy = yy - p.pad_t, ox = xx - p.pad_l;
+                        if (oy >= 0 && oy < p.in_h && ox >= 0 && ox < p.in_w) {
+                            const uint8_t* s = static_cast<const uint8_t*>(p.in) +
+                                               ((static_cast<size_t>(b) * p.in_h + oy) * p.in_w + ox) * 3;
+                            l0 = lut[__ldg(s)];
+                            l1 = lut[__ldg(s + 1)];
+                            l2 = lut[__ldg(s + 2)];
+                        } else {
+                            l0 = l1 = l2 = 0x0000BF80u;  // Pad(fill=0) BEFORE Normalize: (0-0.5)/0.5 = -1 (exact in bf16)
+                        }
+                    } else {
+                        const float* s = static_cast<const float*>(p.in) +
+                                         (static_cast<size_t>(b) * 3 * p.H + yy) * p.W + xx;
+                        const size_t plane = static_cast<size_t>(p.H) * p.W;
+                        l0 = split_hi_lo(__ldg(s));
+                        l1 = split_hi_lo(__ldg(s + plane));
+                        l2 = split_hi_lo(__ldg(s + 2 * plane));
+                    }
+                }
+                // K chunk 0 = [hi0 hi1 hi2 lo0 lo1 lo2 0 0]
+                px[h] = make_uint4((l0 & 0xffffu) | (l1 << 16), (l2 & 0xffffu) | (l0 & 0xffff0000u),
+                                   (l1 >> 16) | (l2 & 0xffff0000u), 0u);
+            }
+            mbar_wait(&a_empty[stage], phase ^ 1);
+            uint4* plane0 = reinterpret_cast<uint4*>(a_smem + stage * kFirstStageBytes);
+            plane0[threadIdx.x] = px[0];
+            if (threadIdx.x + 128 < 180) plane0[threadIdx.x + 128] = px[1];
+            fence_proxy_async();  // generic-proxy smem writes -> visible to the tensor core's async proxy
+            mbar_arrive(&a_full[stage]);
+            if (++stage == kFirstStages) {
+                stage = 0;
+                phase ^= 1;
+            }
+        }
+    } else if (warp == 4) {
+        // ======================= MMA issuer =======================
+        constexpr uint32_t idesc = umma_idesc_bf16(128, N);
+        const uint32_t a0 = smem_u32(a_smem), w0 = smem_u32(w_smem);
+        uint32_t stage = 0, phase = 0, acc_it = 0;
+        for (int mt = blockIdx.x; mt < p.m_tiles; mt += gridDim.x) {
+            const uint32_t buf = acc_it & 1;
+            mbar_wait(&acc_empty[buf], ((acc_it >> 1) & 1) ^ 1);
+            mbar_wait(&a_full[stage], phase);
+            tc_fence_after();
+            if (elect_one()) {
+                const uint32_t ab = a0 + stage * kFirstStageBytes;
+#pragma unroll
+                for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+                    for (int dx = 0; dx < 3; ++dx) {
+                        const int tap = dy * 3 + dx;
+                        umma_bf16_ss(tmem_base + buf * N, umma_desc_nosw(ab + (dy * 10 + dx) * 16, kFirstPlane, 160),
+                                     umma_desc_nosw(w0 + tap * 2048, 1024, 128), idesc, tap == 0 ? 0u : 1u);
+                    }
+                umma_commit(&a_empty[stage]);
+                umma_commit(&acc_full[buf]);
+            }
+            __syncwarp();
+            if (++stage == kFirstStages) {
+                stage = 0;
+                phase ^= 1;
+            }
+            ++acc_it;
+        }
+    } else {
+        // ======================= epilogue: bias + ReLU -> bf16 NHWC =======================
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        const int yl = row >> 3, xl = row & 7;
+        uint32_t acc_it = 0;
+        for (int mt = blockIdx.x; mt < p.m_tiles; mt += gridDim.x) {
+            const int tx = mt % p.tiles_x;
+            const int r2 = mt / p.tiles_x;
+            const int ty = r2 % p.tiles_y;
+            const int b = r2 / p.tiles_y;
+            const int y = ty * 16 + yl, x = tx * 8 + xl;
+            const bool valid = y < p.H && x < p.W;
+            const uint32_t buf = acc_it & 1;
+            mbar_wait(&acc_full[buf], (acc_it >> 1) & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * N;
+            __nv_bfloat16* orow = p.out + ((static_cast<size_t>(b) * p.H + y) * p.W + x) * 64;
+            for_each_chunk<N / 32>(taddr, [&](int ch, uint32_t (&v)[32]) {
+                const float4* b4 = reinterpret_cast<const float4*>(p.bias + ch * 32);
+                uint32_t pk[16];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float4 bb = __ldg(b4 + j);
+                    pk[2 * j + 0] = pack_bf16x2(fmaxf(__uint_as_float(v[4 * j + 0]) + bb.x, 0.f),
+                                                fmaxf(__uint_as_float(v[4 * j + 1]) + bb.y, 0.f));
+                    pk[2 * j + 1] = pack_bf16x2(fmaxf(__uint_as_float(v[4 * j + 2]) + bb.z, 0.f),
+                                                fmaxf(__uint_as_float(v[4 * j + 3]) + bb.w, 0.f));
+                }
+                if (valid) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        st_global_v4(orow + ch * 32 + j * 8, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+                }
+            });
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[buf]);
+            ++acc_it;
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 128);
+    }
+}
+
+}  // namespace cid

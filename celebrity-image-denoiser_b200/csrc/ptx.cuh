@@ -155,12 +155,13 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
 
 // Upper / lower 32-bit halves of the K-major SW128 descriptor below; the lower half is
 // (address >> 4) | LBO, so stepping 32 bytes along K inside the swizzle atom is "+2".
-constexpr uint32_t kDescHiSw128Sbo1024 = (1024u >> 4) | (1u << 14) | (2u << 29);
 __device__ __forceinline__ uint32_t umma_desc_lo(uint32_t smem_addr) {
     return ((smem_addr & 0x3FFFF) >> 4) | (1u << 16);
 }
+template <uint32_t SBO_BYTES>
 __device__ __forceinline__ uint64_t umma_desc_join(uint32_t lo) {
-    return (static_cast<uint64_t>(kDescHiSw128Sbo1024) << 32) | lo;
+    constexpr uint32_t hi = (SBO_BYTES >> 4) | (1u << 14) | (2u << 29);
+    return (static_cast<uint64_t>(hi) << 32) | lo;
 }
 
 // Shared-memory matrix descriptor, K-major operand, 128-byte swizzle, rows of 128 B
