@@ -164,7 +164,6 @@ def main():
     ap.add_argument("--chunk", type=int, default=-1, help="images per pass through the layers (-1 = library default)")
     ap.add_argument("--sub-batch", type=int, default=64, help="e2e: images per H2D/compute/D2H pipeline slot")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--patch", type=int, default=-1, help="override the halo-patch A-load mode (0/1)")
     ap.add_argument("--debug-flags", type=int, default=0, help="bring-up experiments (invalidates results)")
     ap.add_argument("--layers", action="store_true", help="also print the per-layer table to stderr")
     args = ap.parse_args()
@@ -202,8 +201,6 @@ def main():
     if args.chunk >= 0:
         net.set_option("chunk", args.chunk)
     net.set_option("profile", 1)
-    if args.patch >= 0:
-        net.set_option("patch", args.patch)
     if args.debug_flags:
         net.set_option("debug_flags", args.debug_flags)
 

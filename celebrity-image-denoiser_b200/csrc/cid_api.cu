@@ -24,6 +24,14 @@
 #include "edge_kernels.cuh"
 #include "first_conv_umma.cuh"
 
+// TSV(1) layers stage their output in shared memory and write it with TMA stores; build with
+// -DCID_NO_TS to fall back to per-thread global stores (A/B experiments).
+#ifdef CID_NO_TS
+#define TSV(x) 0
+#else
+#define TSV(x) x
+#endif
+
 namespace cid {
 
 static thread_local char g_err[1024] = "";
@@ -105,6 +113,24 @@ static int make_act_map(CUtensorMap* tm, const void* base, int B, int H, int W, 
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     CID_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(activation %dx%dx%dx%d) failed: %d", B, H, W, C,
+                static_cast<int>(r));
+    return 0;
+}
+
+// convT output viewed as (C, 2W, dy, H, B): box = 64 ch x 16 px x 1 x 16 rows x 1 image (rows 2y+dy of a tile).
+static int make_convt_out_map(CUtensorMap* tm, const void* base, int B, int H, int W, int C) {
+    EncodeTiledFn fn = get_encode_fn();
+    CID_REQUIRE(fn, "cuTensorMapEncodeTiled entry point not available");
+    const cuuint64_t row = static_cast<cuuint64_t>(2 * W) * C * 2;  // bytes of one output row
+    cuuint64_t dims[5] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(2 * W), 2, static_cast<cuuint64_t>(H),
+                          static_cast<cuuint64_t>(B)};
+    cuuint64_t strides[4] = {static_cast<cuuint64_t>(C) * 2, row, 2 * row, 2 * row * H};
+    cuuint32_t box[5] = {64, 16, 1, 16, 1};
+    cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+    CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CID_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(convT out %dx%dx%dx%d) failed: %d", B, H, W, C,
                 static_cast<int>(r));
     return 0;
 }
@@ -244,11 +270,29 @@ static int get_plan(cid_ctx* c, int Bc, int H, int W, const void* ws, cid_plan**
         const int buf = layer_in_buf(l);
         const int lv = kBufLevel[buf];
         const int rows = kLayers[l].kind == L_CONVT ? 16 : 18;
-        const int px = (kLayers[l].kind == L_CONV && c->patch) ? 10 : 8;
+        const int px = kLayers[l].kind == L_CONV ? 10 : 8;
         if (make_act_map(&pl.tmA[l], static_cast<const uint8_t*>(ws) + pl.off[buf], Bc, H >> lv, W >> lv, kBufC[buf],
                          rows, px))
             return 1;
     }
+    static const int out_buf[12] = {B_A0, B_CAT1, B_A2, B_CAT2, B_B0, B_B1, -1, B_U2A, B_U2B, -1, B_U1A, -1};
+    for (int l = 0; l < 12; ++l) {
+        const int ob = out_buf[l];
+        if (ob < 0) continue;
+        const int lv = kBufLevel[ob];
+        if (make_act_map(&pl.tmO[l], static_cast<const uint8_t*>(ws) + pl.off[ob], Bc, H >> lv, W >> lv, kBufC[ob], 16, 8))
+            return 1;
+        if (l == 1 || l == 3) {
+            const int pb = l == 1 ? B_P1 : B_P2;
+            const int plv = kBufLevel[pb];
+            if (make_act_map(&pl.tmO2[l], static_cast<const uint8_t*>(ws) + pl.off[pb], Bc, H >> plv, W >> plv,
+                             kBufC[pb], 8, 4))
+                return 1;
+        }
+    }
+    // convT layers: input resolution (H>>lv_in), output buffer cat2 (L6) / cat1 (L9)
+    if (make_convt_out_map(&pl.tmO[6], static_cast<const uint8_t*>(ws) + pl.off[B_CAT2], Bc, H >> 2, W >> 2, 256)) return 1;
+    if (make_convt_out_map(&pl.tmO[9], static_cast<const uint8_t*>(ws) + pl.off[B_CAT1], Bc, H >> 1, W >> 1, 128)) return 1;
     c->plans.push_back(pl);
     *out = &c->plans.back();
     return 0;
@@ -257,12 +301,12 @@ static int get_plan(cid_ctx* c, int Bc, int H, int W, const void* ws, cid_plan**
 // ---------------------------------------------------------------------------------------------
 // launches
 // ---------------------------------------------------------------------------------------------
-template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0>
-static int launch_conv(cid_ctx* c, int slot, const CUtensorMap& tmA, const CUtensorMap& tmW, ConvParams p,
-                       cudaStream_t st) {
-    using Cfg = ConvCfg<N, TAPS, S, WRES, EPI, PW>;
-    const int budget = c->max_smem - 1024 - 512;
-    int w_stages = WRES ? 1 : 4;
+template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0, int TS = 0>
+static int launch_conv(cid_ctx* c, int slot, const CUtensorMap& tmA, const CUtensorMap& tmW, const CUtensorMap& tmO,
+                       const CUtensorMap& tmO2, ConvParams p, cudaStream_t st) {
+    using Cfg = ConvCfg<N, TAPS, S, WRES, EPI, PW, TS>;
+    const int budget = c->max_smem - 1024 - 512 - Cfg::O_BYTES;
+    int w_stages = WRES ? 1 : (N == 256 && TS ? 3 : 4);
     const int w_bytes = (WRES ? p.kb_count * TAPS : w_stages) * Cfg::W_BYTES;
     int a_stages = std::min(kMaxStages, (budget - w_bytes) / Cfg::A_BYTES);
     CID_REQUIRE(a_stages >= S + 1, "conv<%d,%d,%d>: shared memory too small (%d stages)", N, TAPS, S, a_stages);
@@ -273,13 +317,13 @@ static int launch_conv(cid_ctx* c, int slot, const CUtensorMap& tmA, const CUten
     p.m_tiles = p.B * p.tiles_x * p.tiles_y;
     p.num_work = ((p.m_tiles + S - 1) / S) * p.n_tiles;
     const int smem = Cfg::smem_bytes(p.kb_count, a_stages, w_stages);
-    auto kern = conv_umma_kernel<N, TAPS, S, WRES, EPI, PW>;
+    auto kern = conv_umma_kernel<N, TAPS, S, WRES, EPI, PW, TS>;
     if (!(c->attr_done & (1u << slot))) {
         CID_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c->max_smem));
         c->attr_done |= (1u << slot);
     }
     const int grid = std::min(p.num_work, c->num_sms);
-    kern<<<grid, kConvThreads, smem, st>>>(tmA, tmW, p);
+    kern<<<grid, kConvThreads, smem, st>>>(tmA, tmW, tmO, tmO2, p);
     CID_CHECK_CUDA(cudaGetLastError());
     c->launches++;
     return 0;
@@ -330,9 +374,9 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         }
         const int grid = std::min(fp.m_tiles, c->num_sms);
         if (io.u8)
-            first_conv_umma_kernel<true><<<grid, kFirstThreads, smem, st>>>(fp);
+            first_conv_umma_kernel<true><<<grid, kFirstThreads, smem, st>>>(pl->tmO[0], fp);
         else
-            first_conv_umma_kernel<false><<<grid, kFirstThreads, smem, st>>>(fp);
+            first_conv_umma_kernel<false><<<grid, kFirstThreads, smem, st>>>(pl->tmO[0], fp);
         CID_CHECK_CUDA(cudaGetLastError());
         c->launches++;
     } else {
@@ -377,64 +421,64 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         ConvParams p = base(1, 0);
         p.out = buf(B_CAT1); p.out_cs = 128; p.out_c0 = 64;
         p.out2 = buf(B_P1); p.out2_cs = 64; p.out2_c0 = 0;
-        if ((c->patch ? launch_conv<64, 9, 1, true, EPI_RELU_POOL, 10>(c, 16, pl->tmA[1], c->tmW[1], p, st) : launch_conv<64, 9, 1, true, EPI_RELU_POOL, 0>(c, 0, pl->tmA[1], c->tmW[1], p, st))) return 1;
+        if (launch_conv<64, 9, 1, true, EPI_RELU_POOL, 10, TSV(1)>(c, 0, pl->tmA[1], c->tmW[1], pl->tmO[1], pl->tmO2[1], p, st)) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L2 down2.0 -> a2
         ConvParams p = base(2, 1);
         p.out = buf(B_A2); p.out_cs = 128; p.out_c0 = 0;
-        if ((c->patch ? launch_conv<128, 9, 1, true, EPI_RELU, 10>(c, 17, pl->tmA[2], c->tmW[2], p, st) : launch_conv<128, 9, 1, true, EPI_RELU, 0>(c, 1, pl->tmA[2], c->tmW[2], p, st))) return 1;
+        if (launch_conv<128, 9, 1, true, EPI_RELU, 10, TSV(1)>(c, 1, pl->tmA[2], c->tmW[2], pl->tmO[2], pl->tmO[2], p, st)) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L3 down2.2 -> cat2[:,128:256] + p2
         ConvParams p = base(3, 1);
         p.out = buf(B_CAT2); p.out_cs = 256; p.out_c0 = 128;
         p.out2 = buf(B_P2); p.out2_cs = 128; p.out2_c0 = 0;
-        if ((c->patch ? launch_conv<128, 9, 2, false, EPI_RELU_POOL, 10>(c, 18, pl->tmA[3], c->tmW[3], p, st) : launch_conv<128, 9, 2, false, EPI_RELU_POOL, 0>(c, 2, pl->tmA[3], c->tmW[3], p, st))) return 1;
+        if (launch_conv<128, 9, 2, false, EPI_RELU_POOL, 10, TSV(1)>(c, 2, pl->tmA[3], c->tmW[3], pl->tmO[3], pl->tmO2[3], p, st)) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L4 bottleneck.0 -> b0
         ConvParams p = base(4, 2);
         p.out = buf(B_B0); p.out_cs = 256; p.out_c0 = 0;
-        if ((c->patch ? launch_conv<256, 9, 1, false, EPI_RELU, 10>(c, 19, pl->tmA[4], c->tmW[4], p, st) : launch_conv<256, 9, 1, false, EPI_RELU, 0>(c, 3, pl->tmA[4], c->tmW[4], p, st))) return 1;
+        if (launch_conv<256, 9, 1, false, EPI_RELU, 10, TSV(1)>(c, 3, pl->tmA[4], c->tmW[4], pl->tmO[4], pl->tmO[4], p, st)) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L5 bottleneck.2 -> b1
         ConvParams p = base(5, 2);
         p.out = buf(B_B1); p.out_cs = 256; p.out_c0 = 0;
-        if ((c->patch ? launch_conv<256, 9, 1, false, EPI_RELU, 10>(c, 19, pl->tmA[5], c->tmW[5], p, st) : launch_conv<256, 9, 1, false, EPI_RELU, 0>(c, 3, pl->tmA[5], c->tmW[5], p, st))) return 1;
+        if (launch_conv<256, 9, 1, false, EPI_RELU, 10, TSV(1)>(c, 3, pl->tmA[5], c->tmW[5], pl->tmO[5], pl->tmO[5], p, st)) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L6 up2 (convT) -> cat2[:,0:128]
         ConvParams p = base(6, 2);
         p.n_tiles = 2;  // 4*128 columns in tiles of 256
         p.out = buf(B_CAT2); p.out_cs = 256; p.out_c0 = 0;
-        if (launch_conv<256, 1, 1, false, EPI_CONVT>(c, 4, pl->tmA[6], c->tmW[6], p, st)) return 1;
+        if (launch_conv<256, 1, 1, false, EPI_CONVT, 0, TSV(1)>(c, 4, pl->tmA[6], c->tmW[6], pl->tmO[6], pl->tmO[6], p, st)) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L7 upconv2.0 (reads cat2) -> u2a
         ConvParams p = base(7, 1);
         p.out = buf(B_U2A); p.out_cs = 128; p.out_c0 = 0;
-        if ((c->patch ? launch_conv<128, 9, 2, false, EPI_RELU, 10>(c, 21, pl->tmA[7], c->tmW[7], p, st) : launch_conv<128, 9, 2, false, EPI_RELU, 0>(c, 5, pl->tmA[7], c->tmW[7], p, st))) return 1;
+        if (launch_conv<128, 9, 2, false, EPI_RELU, 10, TSV(1)>(c, 5, pl->tmA[7], c->tmW[7], pl->tmO[7], pl->tmO[7], p, st)) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L8 upconv2.2 -> u2b
         ConvParams p = base(8, 1);
         p.out = buf(B_U2B); p.out_cs = 128; p.out_c0 = 0;
-        if ((c->patch ? launch_conv<128, 9, 2, false, EPI_RELU, 10>(c, 21, pl->tmA[8], c->tmW[8], p, st) : launch_conv<128, 9, 2, false, EPI_RELU, 0>(c, 5, pl->tmA[8], c->tmW[8], p, st))) return 1;
+        if (launch_conv<128, 9, 2, false, EPI_RELU, 10, TSV(1)>(c, 5, pl->tmA[8], c->tmW[8], pl->tmO[8], pl->tmO[8], p, st)) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L9 up1 (convT) -> cat1[:,0:64]
         ConvParams p = base(9, 1);
         p.n_tiles = 1;  // 4*64 columns in one tile of 256
         p.out = buf(B_CAT1); p.out_cs = 128; p.out_c0 = 0;
-        if (launch_conv<256, 1, 1, false, EPI_CONVT>(c, 4, pl->tmA[9], c->tmW[9], p, st)) return 1;
+        if (launch_conv<256, 1, 1, false, EPI_CONVT, 0, TSV(1)>(c, 4, pl->tmA[9], c->tmW[9], pl->tmO[9], pl->tmO[9], p, st)) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L10 upconv1.0 (reads cat1) -> u1a
         ConvParams p = base(10, 0);
         p.out = buf(B_U1A); p.out_cs = 64; p.out_c0 = 0;
-        if ((c->patch ? launch_conv<64, 9, 1, true, EPI_RELU, 10>(c, 22, pl->tmA[10], c->tmW[10], p, st) : launch_conv<64, 9, 1, true, EPI_RELU, 0>(c, 6, pl->tmA[10], c->tmW[10], p, st))) return 1;
+        if (launch_conv<64, 9, 1, true, EPI_RELU, 10, TSV(1)>(c, 6, pl->tmA[10], c->tmW[10], pl->tmO[10], pl->tmO[10], p, st)) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L11 upconv1.2 + tanh -> y
@@ -442,9 +486,9 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         p.out = io.y;
         if (io.u8) {
             p.crop_l = io.pad_l; p.crop_t = io.pad_t; p.out_h = io.in_h; p.out_w = io.in_w;
-            if ((c->patch ? launch_conv<16, 9, 1, true, EPI_TANH_U8, 10>(c, 23, pl->tmA[11], c->tmW[11], p, st) : launch_conv<16, 9, 1, true, EPI_TANH_U8, 0>(c, 7, pl->tmA[11], c->tmW[11], p, st))) return 1;
+            if (launch_conv<16, 9, 1, true, EPI_TANH_U8, 10, TSV(0)>(c, 7, pl->tmA[11], c->tmW[11], pl->tmA[11], pl->tmA[11], p, st)) return 1;
         } else {
-            if ((c->patch ? launch_conv<16, 9, 1, true, EPI_TANH_F32, 10>(c, 24, pl->tmA[11], c->tmW[11], p, st) : launch_conv<16, 9, 1, true, EPI_TANH_F32, 0>(c, 8, pl->tmA[11], c->tmW[11], p, st))) return 1;
+            if (launch_conv<16, 9, 1, true, EPI_TANH_F32, 10, TSV(0)>(c, 8, pl->tmA[11], c->tmW[11], pl->tmA[11], pl->tmA[11], p, st)) return 1;
         }
     }
     if (prof_mark(c, st)) return 1;
@@ -583,11 +627,6 @@ int cid_set_option(cid_handle h, const char* name, int64_t value) {
     }
     if (!strcmp(name, "first_tc")) {
         h->first_tc = value != 0;
-        return 0;
-    }
-    if (!strcmp(name, "patch")) {
-        h->patch = value != 0;
-        h->plans.clear();
         return 0;
     }
     if (!strcmp(name, "debug_flags")) {

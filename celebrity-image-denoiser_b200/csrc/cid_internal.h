@@ -55,6 +55,8 @@ struct cid_plan {
     const void* ws = nullptr;
     size_t off[11] = {0};   // byte offsets of a0,cat1,p1,a2,cat2,p2,b0,b1,u2a,u2b,u1a
     CUtensorMap tmA[12];    // indexed by layer (0 unused)
+    CUtensorMap tmO[12];    // TMA-store maps of each layer's output buffer (box 64ch x 8px x 16 rows)
+    CUtensorMap tmO2[12];   // pooled output (box 64ch x 4px x 8 rows); layers 1 and 3 only
 };
 
 struct cid_ctx {

@@ -56,7 +56,7 @@ struct ConvParams {
 // PW = 10: one halo patch {64 ch, 10 px, 18 rows} per K block; tap (dy,dx) is the same patch read at
 //          start + (dy*PW + dx)*128 B with SBO = PW*128 B (relies on the 128-B swizzle being a
 //          function of the absolute shared-memory address, for TMA writes and UMMA reads alike).
-template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0>
+template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0, int TS = 0>
 struct ConvCfg {
     static_assert(TAPS == 9 || TAPS == 1, "3x3 or 1x1");
     static_assert(N % 16 == 0 && N >= 16 && N <= 256, "UMMA N for M=128");
@@ -76,10 +76,19 @@ struct ConvCfg {
                                      : (2 * ACC_COLS <= 128) ? 128
                                      : (2 * ACC_COLS <= 256) ? 256
                                                              : 512;
+    // TS = 1: the epilogue stages each 64-channel slab of the tile in shared memory (SW128 rows,
+    // same geometry as the A boxes) and writes it with one TMA store instead of per-thread stores.
+    static constexpr int NOB = 2;  // staging buffers in flight
+    static constexpr int O_SLAB = 128 * 128;
+    static constexpr int O2_SLAB = 32 * 128;
+    static constexpr int OT_SLAB = 256 * 128;  // EPI_CONVT: [16 rows][16 px][64 ch] of the 2x-upsampled output
+    static constexpr int O_BYTES = !TS ? 0
+                                   : EPI == EPI_CONVT ? 2 * OT_SLAB
+                                                      : NOB * (O_SLAB + (EPI == EPI_RELU_POOL ? O2_SLAB : 0));
     // dynamic shared memory needed (bytes), including 1 KB of alignment slack
     static int smem_bytes(int kb_count, int a_stages, int w_stages) {
         int w_items = WRES ? kb_count * TAPS : w_stages;
-        return 1024 + w_items * W_BYTES + a_stages * A_BYTES + 512;
+        return 1024 + w_items * W_BYTES + a_stages * A_BYTES + O_BYTES + 512;
     }
 };
 
@@ -117,11 +126,12 @@ __device__ __forceinline__ void for_each_chunk(uint32_t taddr, F&& f) {
     }
 }
 
-template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0>
+template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0, int TS = 0>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                 const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO2,
                  const ConvParams p) {
-    using Cfg = ConvCfg<N, TAPS, S, WRES, EPI, PW>;
+    using Cfg = ConvCfg<N, TAPS, S, WRES, EPI, PW, TS>;
     constexpr int DX = Cfg::DX, DY = Cfg::DY, AL = Cfg::A_LOADS;
     constexpr int DXI = PW ? DX : 1;  // horizontal taps served by one A box
     constexpr int A_BYTES = Cfg::A_BYTES, W_BYTES = Cfg::W_BYTES;
@@ -132,7 +142,9 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int w_items = WRES ? p.kb_count * TAPS : p.w_stages;
     uint8_t* w_smem = smem;
     uint8_t* a_smem = smem + w_items * W_BYTES;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(a_smem + p.a_stages * A_BYTES);
+    uint8_t* o_smem = a_smem + p.a_stages * A_BYTES;               // [NOB][128 rows][128 B]
+    uint8_t* o2_smem = o_smem + Cfg::NOB * Cfg::O_SLAB;            // [NOB][32 rows][128 B] (pool)
+    uint64_t* bars = reinterpret_cast<uint64_t*>(o_smem + Cfg::O_BYTES);
     uint64_t* a_full = bars;
     uint64_t* a_empty = bars + kMaxStages;
     uint64_t* w_full = bars + 2 * kMaxStages;
@@ -149,6 +161,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmW);
+        if (TS) {
+            tma_prefetch_desc(&tmO);
+            if (EPI == EPI_RELU_POOL) tma_prefetch_desc(&tmO2);
+        }
         for (int i = 0; i < kMaxStages; ++i) {
             mbar_init(&a_full[i], 1);
             mbar_init(&a_empty[i], 1);
@@ -307,6 +323,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int yl = row >> 3;
         const int xl = row & 7;
         uint32_t acc_it = 0;
+        uint32_t o_count = 0;  // staged slabs written so far (TS)
         for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
             const int n_tile = work % p.n_tiles;
             const int st = work / p.n_tiles;
@@ -324,7 +341,68 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 if (p.debug_flags & 2) continue;
                 const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * Cfg::ACC_COLS + s * N;
 
-                if constexpr (EPI == EPI_RELU || EPI == EPI_RELU_POOL) {
+                if constexpr ((EPI == EPI_RELU || EPI == EPI_RELU_POOL) && TS) {
+                    // ---- staged: smem slab (SW128) -> one TMA store per 64 channels ----
+                    const bool issuer = (threadIdx.x == 64);  // lane 0 of the first epilogue warp
+                    const int sub = (xl & 1) | ((yl & 1) << 1);
+                    const int prow_i = (yl >> 1) * 4 + (xl >> 1);
+                    for_each_chunk<N / 32>(taddr, [&](int ch, uint32_t (&v)[32]) {
+                        const uint32_t ob = o_count % Cfg::NOB;
+                        if ((ch & 1) == 0) {
+                            // the store that used this buffer NOB slabs ago must have finished READING it
+                            if (issuer) bulk_wait_read<Cfg::NOB - 1>();
+                            named_bar_sync(1, 128);
+                        }
+                        const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_tile * N + ch * 32);
+                        uint32_t pk[16];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 bb = __ldg(b4 + j);
+                            const float f0 = fmaxf(__uint_as_float(v[4 * j + 0]) + bb.x, 0.f);
+                            const float f1 = fmaxf(__uint_as_float(v[4 * j + 1]) + bb.y, 0.f);
+                            const float f2 = fmaxf(__uint_as_float(v[4 * j + 2]) + bb.z, 0.f);
+                            const float f3 = fmaxf(__uint_as_float(v[4 * j + 3]) + bb.w, 0.f);
+                            pk[2 * j + 0] = pack_bf16x2(f0, f1);
+                            pk[2 * j + 1] = pack_bf16x2(f2, f3);
+                        }
+                        uint8_t* rowp = o_smem + ob * Cfg::O_SLAB + row * 128;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const int cj = (ch & 1) * 4 + j;  // 16-byte chunk inside the 128-byte row
+                            st_shared_v4(rowp + ((cj ^ (row & 7)) << 4), pk[4 * j], pk[4 * j + 1], pk[4 * j + 2],
+                                         pk[4 * j + 3]);
+                        }
+                        if constexpr (EPI == EPI_RELU_POOL) {
+                            // 2x2 max: x partner is lane^1, y partner is lane^8 (row = y*8 + x).
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) {
+                                uint32_t m = max_bf16x2(pk[j], __shfl_xor_sync(0xffffffffu, pk[j], 1));
+                                pk[j] = max_bf16x2(m, __shfl_xor_sync(0xffffffffu, m, 8));
+                            }
+                            // each of the 4 lanes of a 2x2 block writes a different 8-channel quarter
+                            const uint32_t o0 = sub == 0 ? pk[0] : sub == 1 ? pk[4] : sub == 2 ? pk[8] : pk[12];
+                            const uint32_t o1 = sub == 0 ? pk[1] : sub == 1 ? pk[5] : sub == 2 ? pk[9] : pk[13];
+                            const uint32_t o2 = sub == 0 ? pk[2] : sub == 1 ? pk[6] : sub == 2 ? pk[10] : pk[14];
+                            const uint32_t o3 = sub == 0 ? pk[3] : sub == 1 ? pk[7] : sub == 2 ? pk[11] : pk[15];
+                            const int cj = (ch & 1) * 4 + sub;
+                            st_shared_v4(o2_smem + ob * Cfg::O2_SLAB + prow_i * 128 + ((cj ^ (prow_i & 7)) << 4), o0,
+                                         o1, o2, o3);
+                        }
+                        if ((ch & 1) == 1) {
+                            fence_proxy_async();
+                            named_bar_sync(1, 128);
+                            if (issuer && !(p.debug_flags & 1)) {
+                                const int c64 = n_tile * N + (ch >> 1) * 64;
+                                tma_store_4d(&tmO, o_smem + ob * Cfg::O_SLAB, p.out_c0 + c64, tc.x0, tc.y0, tc.b);
+                                if constexpr (EPI == EPI_RELU_POOL)
+                                    tma_store_4d(&tmO2, o2_smem + ob * Cfg::O2_SLAB, p.out2_c0 + c64, tc.x0 >> 1,
+                                                 tc.y0 >> 1, tc.b);
+                                bulk_commit();
+                            }
+                            ++o_count;
+                        }
+                    });
+                } else if constexpr (EPI == EPI_RELU || EPI == EPI_RELU_POOL) {
                     __nv_bfloat16* out = static_cast<__nv_bfloat16*>(p.out);
                     const size_t pix = (static_cast<size_t>(tc.b) * p.H + y) * p.W + x;
                     __nv_bfloat16* orow = out + pix * p.out_cs + p.out_c0 + n_tile * N;
@@ -373,6 +451,51 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             if (pvalid) st_global_v4(prow + ch * 32, o0, o1, o2, o3);
                         }
                     });
+                } else if constexpr (EPI == EPI_CONVT && TS) {
+                    // ---- staged transposed conv: GEMM column n = quadrant*cout + c, quadrant = dy*2+dx.
+                    // The tile's 8 chunks fill two slabs [16 y][16 px][64 ch] of output rows 2y+dy
+                    // (cout 64: slab = dy; cout 128: slab = 64-channel half, dy = n_tile), each written by
+                    // one 5-D TMA store over (C, 2W, dy, H, B).
+                    static_assert(N == 256, "staged convT epilogue assumes 8 chunks per tile");
+                    const bool issuer = (threadIdx.x == 64);
+                    const bool c64mode = (p.cout == 64);
+                    if (issuer) bulk_wait_read<0>();  // previous tile's two stores have drained both slabs
+                    named_bar_sync(1, 128);
+                    for_each_chunk<N / 32>(taddr, [&](int ch, uint32_t (&v)[32]) {
+                        const int n = n_tile * N + ch * 32;
+                        const int quad = n / p.cout;
+                        const int c = n - quad * p.cout;
+                        const int slab = c64mode ? (ch >> 2) : ((ch & 3) >> 1);
+                        const float4* b4 = reinterpret_cast<const float4*>(p.bias + c);
+                        uint32_t pk[16];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 bb = __ldg(b4 + j);
+                            pk[2 * j + 0] =
+                                pack_bf16x2(__uint_as_float(v[4 * j + 0]) + bb.x, __uint_as_float(v[4 * j + 1]) + bb.y);
+                            pk[2 * j + 1] =
+                                pack_bf16x2(__uint_as_float(v[4 * j + 2]) + bb.z, __uint_as_float(v[4 * j + 3]) + bb.w);
+                        }
+                        const int orow_i = yl * 16 + 2 * xl + (quad & 1);
+                        uint8_t* rowp = o_smem + slab * Cfg::OT_SLAB + orow_i * 128;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const int cj = (ch & 1) * 4 + j;
+                            st_shared_v4(rowp + ((cj ^ (orow_i & 7)) << 4), pk[4 * j], pk[4 * j + 1], pk[4 * j + 2],
+                                         pk[4 * j + 3]);
+                        }
+                    });
+                    fence_proxy_async();
+                    named_bar_sync(1, 128);
+                    if (issuer && !(p.debug_flags & 1)) {
+#pragma unroll
+                        for (int slab = 0; slab < 2; ++slab) {
+                            const int dy = c64mode ? slab : n_tile;
+                            const int c0 = p.out_c0 + (c64mode ? 0 : slab * 64);
+                            tma_store_5d(&tmO, o_smem + slab * Cfg::OT_SLAB, c0, 2 * tc.x0, dy, tc.y0, tc.b);
+                        }
+                        bulk_commit();
+                    }
                 } else if constexpr (EPI == EPI_CONVT) {
                     // GEMM column n = quadrant*cout + c, quadrant = dy*2+dx; output pixel (2y+dy, 2x+dx).
                     __nv_bfloat16* out = static_cast<__nv_bfloat16*>(p.out);
@@ -437,6 +560,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (lane == 0) mbar_arrive(&acc_empty[buf]);
             ++acc_it;
         }
+        if (TS && threadIdx.x == 64) bulk_wait<0>();  // all TMA stores complete before the CTA exits
     }
 
     tc_fence_before();

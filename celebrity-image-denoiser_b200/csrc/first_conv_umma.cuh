@@ -32,7 +32,8 @@ constexpr int kFirstStages = 8;
 constexpr int kFirstPlane = 180 * 16;          // one K chunk of the 10x18 patch
 constexpr int kFirstStageBytes = 2 * kFirstPlane;
 constexpr int kFirstWBytes = 9 * 2 * 64 * 16;  // [tap][k chunk][cout][8 bf16]
-constexpr int kFirstSmem = 1024 + kFirstWBytes + kFirstStages * kFirstStageBytes + 1024 + 256;
+constexpr int kFirstOutBufs = 2;               // staged output slabs ([128 px][64 ch] bf16, SW128) in flight
+constexpr int kFirstSmem = 1024 + kFirstOutBufs * 16384 + kFirstWBytes + kFirstStages * kFirstStageBytes + 1024 + 256;
 
 struct FirstParams {
     int B, H, W;          // network-input dims (after padding to a multiple of 4)
@@ -59,12 +60,14 @@ __device__ __forceinline__ uint32_t split_hi_lo(float x) {
 }
 
 template <bool U8>
-__global__ void __launch_bounds__(kFirstThreads, 1) first_conv_umma_kernel(const FirstParams p) {
+__global__ void __launch_bounds__(kFirstThreads, 1)
+first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParams p) {
     constexpr int N = 64;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint8_t* w_smem = smem;
-    uint8_t* a_smem = smem + kFirstWBytes;
+    uint8_t* o_smem = smem;  // 1024-aligned staging slabs first
+    uint8_t* w_smem = smem + kFirstOutBufs * 16384;
+    uint8_t* a_smem = w_smem + kFirstWBytes;
     uint32_t* lut = reinterpret_cast<uint32_t*>(a_smem + kFirstStages * kFirstStageBytes);  // 256 x {hi | lo<<16}
     uint64_t* bars = reinterpret_cast<uint64_t*>(lut + 256);
     uint64_t* a_full = bars;
@@ -87,6 +90,7 @@ __global__ void __launch_bounds__(kFirstThreads, 1) first_conv_umma_kernel(const
         lut[threadIdx.x] = split_hi_lo(v);
     }
     if (threadIdx.x == 0) {
+        tma_prefetch_desc(&tmO);
         for (int i = 0; i < kFirstStages; ++i) {
             mbar_init(&a_full[i], 128);
             mbar_init(&a_empty[i], 1);
@@ -191,18 +195,22 @@ __global__ void __launch_bounds__(kFirstThreads, 1) first_conv_umma_kernel(const
         const int row = q * 32 + lane;
         const int yl = row >> 3, xl = row & 7;
         uint32_t acc_it = 0;
+        const bool issuer = (warp == 5 && lane == 0);
+        (void)yl; (void)xl;
         for (int mt = blockIdx.x; mt < p.m_tiles; mt += gridDim.x) {
             const int tx = mt % p.tiles_x;
             const int r2 = mt / p.tiles_x;
             const int ty = r2 % p.tiles_y;
             const int b = r2 / p.tiles_y;
-            const int y = ty * 16 + yl, x = tx * 8 + xl;
-            const bool valid = y < p.H && x < p.W;
             const uint32_t buf = acc_it & 1;
             mbar_wait(&acc_full[buf], (acc_it >> 1) & 1);
             tc_fence_after();
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * N;
-            __nv_bfloat16* orow = p.out + ((static_cast<size_t>(b) * p.H + y) * p.W + x) * 64;
+            const uint32_t ob = acc_it % kFirstOutBufs;
+            // the TMA store that used this slab kFirstOutBufs tiles ago must have finished reading it
+            if (issuer) bulk_wait_read<kFirstOutBufs - 1>();
+            named_bar_sync(1, 128);
+            uint8_t* rowp = o_smem + ob * 16384 + row * 128;
             for_each_chunk<N / 32>(taddr, [&](int ch, uint32_t (&v)[32]) {
                 const float4* b4 = reinterpret_cast<const float4*>(p.bias + ch * 32);
                 uint32_t pk[16];
@@ -214,17 +222,23 @@ __global__ void __launch_bounds__(kFirstThreads, 1) first_conv_umma_kernel(const
                     pk[2 * j + 1] = pack_bf16x2(fmaxf(__uint_as_float(v[4 * j + 2]) + bb.z, 0.f),
                                                 fmaxf(__uint_as_float(v[4 * j + 3]) + bb.w, 0.f));
                 }
-                if (valid) {
 #pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        st_global_v4(orow + ch * 32 + j * 8, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+                for (int j = 0; j < 4; ++j) {
+                    const int cj = ch * 4 + j;
+                    st_shared_v4(rowp + ((cj ^ (row & 7)) << 4), pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
                 }
             });
             tc_fence_before();
-            __syncwarp();
+            fence_proxy_async();
+            named_bar_sync(1, 128);
+            if (issuer) {
+                tma_store_4d(&tmO, o_smem + ob * 16384, 0, tx * 8, ty * 16, b);  // partial tiles are clipped
+                bulk_commit();
+            }
             if (lane == 0) mbar_arrive(&acc_empty[buf]);
             ++acc_it;
         }
+        if (issuer) bulk_wait<0>();
     }
 
     tc_fence_before();
