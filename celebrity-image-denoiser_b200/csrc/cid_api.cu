@@ -23,6 +23,7 @@
 #include "conv_umma.cuh"
 #include "edge_kernels.cuh"
 #include "first_conv_umma.cuh"
+#include "last_conv_umma.cuh"
 
 // TSV(1) layers stage their output in shared memory and write it with TMA stores; build with
 // -DCID_NO_TS to fall back to per-thread global stores (A/B experiments).
@@ -213,7 +214,17 @@ static int pack_layer(cid_ctx* c, int l) {
 
     std::vector<uint16_t> packed;
     int rows = 0;
-    if (L.kind == L_CONV) {
+    int box_rows = layer_n(l);
+    if (l == 11) {
+        // transposed GEMM of last_conv_umma_kernel: one row per (tap, cout), 128 rows of 64 channels
+        rows = box_rows = 128;
+        packed.assign(static_cast<size_t>(rows) * L.cin, 0);
+        for (int co = 0; co < L.cout; ++co)
+            for (int ci = 0; ci < L.cin; ++ci)
+                for (int t = 0; t < 9; ++t)
+                    packed[static_cast<size_t>(last_conv_row(t, co)) * L.cin + ci] =
+                        f32_to_bf16_rne(w[(static_cast<size_t>(co) * L.cin + ci) * 9 + t]);
+    } else if (L.kind == L_CONV) {
         const int npad = std::max(L.cout, 16);
         rows = 9 * npad;
         packed.assign(static_cast<size_t>(rows) * L.cin, 0);
@@ -242,7 +253,7 @@ static int pack_layer(cid_ctx* c, int l) {
     std::copy(b.begin(), b.end(), bp.begin());
     CID_CHECK_CUDA(cudaMalloc(reinterpret_cast<void**>(&c->bias_dev[l]), bp.size() * 4));
     CID_CHECK_CUDA(cudaMemcpy(c->bias_dev[l], bp.data(), bp.size() * 4, cudaMemcpyHostToDevice));
-    return make_weight_map(&c->tmW[l], c->w_dev[l], rows, L.cin, layer_n(l));
+    return make_weight_map(&c->tmW[l], c->w_dev[l], rows, L.cin, box_rows);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -478,18 +489,38 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
     {  // L10 upconv1.0 (reads cat1) -> u1a
         ConvParams p = base(10, 0);
         p.out = buf(B_U1A); p.out_cs = 64; p.out_c0 = 0;
-        if (launch_conv<64, 9, 1, true, EPI_RELU, 10, TSV(1)>(c, 6, pl->tmA[10], c->tmW[10], pl->tmO[10], pl->tmO[10], p, st)) return 1;
+        if (c->variant & 1) {  // weights streamed through a ring, one weight tile feeding 2 pixel tiles
+            if (launch_conv<64, 9, 2, false, EPI_RELU, 10, TSV(1)>(c, 9, pl->tmA[10], c->tmW[10], pl->tmO[10], pl->tmO[10], p, st)) return 1;
+        } else {
+            if (launch_conv<64, 9, 1, true, EPI_RELU, 10, TSV(1)>(c, 6, pl->tmA[10], c->tmW[10], pl->tmO[10], pl->tmO[10], p, st)) return 1;
+        }
     }
     if (prof_mark(c, st)) return 1;
-    {  // L11 upconv1.2 + tanh -> y
-        ConvParams p = base(11, 0);
-        p.out = io.y;
-        if (io.u8) {
-            p.crop_l = io.pad_l; p.crop_t = io.pad_t; p.out_h = io.in_h; p.out_w = io.in_w;
-            if (launch_conv<16, 9, 1, true, EPI_TANH_U8, 10, TSV(0)>(c, 7, pl->tmA[11], c->tmW[11], pl->tmA[11], pl->tmA[11], p, st)) return 1;
-        } else {
-            if (launch_conv<16, 9, 1, true, EPI_TANH_F32, 10, TSV(0)>(c, 8, pl->tmA[11], c->tmW[11], pl->tmA[11], pl->tmA[11], p, st)) return 1;
+    {  // L11 upconv1.2 + tanh -> y   (transposed GEMM: weights on M, the halo patch on N)
+        LastParams lp;
+        memset(&lp, 0, sizeof(lp));
+        lp.B = nb; lp.H = H; lp.W = W;
+        lp.tiles_x = (W + 7) / 8;
+        lp.tiles_y = (H + 15) / 16;
+        lp.m_tiles = nb * lp.tiles_x * lp.tiles_y;
+        lp.stages = std::min(kLastMaxStages, (c->max_smem - last_conv_smem(0)) / kLastStageBytes);
+        CID_REQUIRE(lp.stages >= 2, "last conv: shared memory too small");
+        lp.bias = c->bias_dev[11];
+        lp.out = io.y;
+        lp.crop_l = io.pad_l; lp.crop_t = io.pad_t; lp.out_h = io.in_h; lp.out_w = io.in_w;
+        const int smem = last_conv_smem(lp.stages);
+        if (!(c->attr_done & (1u << 29))) {
+            CID_CHECK_CUDA(cudaFuncSetAttribute(last_conv_umma_kernel<EPI_TANH_U8>, cudaFuncAttributeMaxDynamicSharedMemorySize, c->max_smem));
+            CID_CHECK_CUDA(cudaFuncSetAttribute(last_conv_umma_kernel<EPI_TANH_F32>, cudaFuncAttributeMaxDynamicSharedMemorySize, c->max_smem));
+            c->attr_done |= (1u << 29);
         }
+        const int grid = std::min(lp.m_tiles, c->num_sms);
+        if (io.u8)
+            last_conv_umma_kernel<EPI_TANH_U8><<<grid, kLastThreads, smem, st>>>(pl->tmA[11], c->tmW[11], lp);
+        else
+            last_conv_umma_kernel<EPI_TANH_F32><<<grid, kLastThreads, smem, st>>>(pl->tmA[11], c->tmW[11], lp);
+        CID_CHECK_CUDA(cudaGetLastError());
+        c->launches++;
     }
     if (prof_mark(c, st)) return 1;
     return 0;
@@ -629,6 +660,10 @@ int cid_set_option(cid_handle h, const char* name, int64_t value) {
         h->first_tc = value != 0;
         return 0;
     }
+    if (!strcmp(name, "variant")) {  // bit mask of A/B kernel variants (bring-up experiments)
+        h->variant = static_cast<int>(value);
+        return 0;
+    }
     if (!strcmp(name, "debug_flags")) {
         h->debug_flags = static_cast<int>(value);
         return 0;
@@ -644,7 +679,8 @@ int cid_set_option(cid_handle h, const char* name, int64_t value) {
 
 int cid_workspace_bytes(cid_handle h, int B, int H, int W, size_t* bytes) {
     CID_REQUIRE(h && bytes, "cid_workspace_bytes: null argument");
-    CID_REQUIRE(B >= 1 && H >= 4 && W >= 4 && H % 4 == 0 && W % 4 == 0, "bad shape B=%d H=%d W=%d", B, H, W);
+    CID_REQUIRE(B >= 1 && H >= 4 && W >= 4, "bad shape B=%d H=%d W=%d", B, H, W);
+    CID_REQUIRE(H % 4 == 0 && W % 4 == 0, "network input %dx%d must be multiples of 4 (get_padding, app.py:276)", H, W);
     *bytes = layout_offsets(chunk_of(h, B), H, W, nullptr);
     return 0;
 }

@@ -96,15 +96,18 @@ struct TileCoord {
     int b, y0, x0;
 };
 
-__device__ __forceinline__ TileCoord decode_tile(const ConvParams& p, int mt) {
+__device__ __forceinline__ TileCoord decode_tile(int tiles_x, int tiles_y, int mt) {
     TileCoord t;
-    int tx = mt % p.tiles_x;
-    int r = mt / p.tiles_x;
-    int ty = r % p.tiles_y;
-    t.b = r / p.tiles_y;  // == B for padding tiles past m_tiles: TMA zero-fills, stores are masked
+    int tx = mt % tiles_x;
+    int r = mt / tiles_x;
+    int ty = r % tiles_y;
+    t.b = r / tiles_y;  // == B for padding tiles past m_tiles: TMA zero-fills, stores are masked
     t.y0 = ty * 16;
     t.x0 = tx * 8;
     return t;
+}
+__device__ __forceinline__ TileCoord decode_tile(const ConvParams& p, int mt) {
+    return decode_tile(p.tiles_x, p.tiles_y, mt);
 }
 
 // Walk an accumulator row in 32-column chunks with the next chunk's tcgen05.ld already in

@@ -33,7 +33,7 @@ constexpr int kFirstPlane = 180 * 16;          // one K chunk of the 10x18 patch
 constexpr int kFirstStageBytes = 2 * kFirstPlane;
 constexpr int kFirstWBytes = 9 * 2 * 64 * 16;  // [tap][k chunk][cout][8 bf16]
 constexpr int kFirstOutBufs = 2;               // staged output slabs ([128 px][64 ch] bf16, SW128) in flight
-constexpr int kFirstSmem = 1024 + kFirstOutBufs * 16384 + kFirstWBytes + kFirstStages * kFirstStageBytes + 1024 + 256;
+constexpr int kFirstSmem = 1024 + kFirstOutBufs * 16384 + kFirstWBytes + kFirstStages * kFirstStageBytes + 1024 + 32 + 256;
 
 struct FirstParams {
     int B, H, W;          // network-input dims (after padding to a multiple of 4)
@@ -59,6 +59,26 @@ __device__ __forceinline__ uint32_t split_hi_lo(float x) {
     return static_cast<uint32_t>(__bfloat16_as_ushort(h)) | (static_cast<uint32_t>(__bfloat16_as_ushort(l)) << 16);
 }
 
+// tile coordinates of a linear tile index (x fastest, then y, then image), advanced incrementally
+struct TileWalk {
+    int tx, ty, b;
+    __device__ TileWalk(int tiles_x, int tiles_y, int mt) {
+        tx = mt % tiles_x;
+        const int r = mt / tiles_x;
+        ty = r % tiles_y;
+        b = r / tiles_y;
+    }
+    __device__ __forceinline__ void next(int tiles_x, int tiles_y) {
+        if (++tx == tiles_x) {
+            tx = 0;
+            if (++ty == tiles_y) {
+                ty = 0;
+                ++b;
+            }
+        }
+    }
+};
+
 template <bool U8>
 __global__ void __launch_bounds__(kFirstThreads, 1)
 first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParams p) {
@@ -69,7 +89,7 @@ first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParam
     uint8_t* w_smem = smem + kFirstOutBufs * 16384;
     uint8_t* a_smem = w_smem + kFirstWBytes;
     uint32_t* lut = reinterpret_cast<uint32_t*>(a_smem + kFirstStages * kFirstStageBytes);  // 256 x {hi | lo<<16}
-    uint64_t* bars = reinterpret_cast<uint64_t*>(lut + 256);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(lut + 264);
     uint64_t* a_full = bars;
     uint64_t* a_empty = bars + kFirstStages;
     uint64_t* acc_full = bars + 2 * kFirstStages;
@@ -88,6 +108,10 @@ first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParam
         // ToTensor: u8 -> f32 / 255 ; Normalize: (v - 0.5) / 0.5, each op rounded (backend/app.py:401-406)
         const float v = __fdiv_rn(__fsub_rn(__fdiv_rn(static_cast<float>(threadIdx.x), 255.f), 0.5f), 0.5f);
         lut[threadIdx.x] = split_hi_lo(v);
+        if (threadIdx.x == 0) {
+            lut[256] = 0u;           // conv zero padding
+            lut[257] = 0x0000BF80u;  // Pad(fill=0) before Normalize: (0-0.5)/0.5 = -1, exact in bf16 (hi=-1, lo=0)
+        }
     }
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&tmO);
@@ -108,55 +132,93 @@ first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParam
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
+    // Each CTA walks a CONTIGUOUS range of tiles (x fastest): neighbouring tiles share halo pixels
+    // in L1/L2 and the tile coordinates advance by increments instead of divisions.
+    const int per_cta = (p.m_tiles + gridDim.x - 1) / gridDim.x;
+    const int mt_begin = min(static_cast<int>(blockIdx.x) * per_cta, p.m_tiles);
+    const int mt_end = min(mt_begin + per_cta, p.m_tiles);
+
     if (warp < 4) {
         // ======================= patch producers =======================
-        uint32_t stage = 0, phase = 0;
-        for (int mt = blockIdx.x; mt < p.m_tiles; mt += gridDim.x) {
-            const int tx = mt % p.tiles_x;
-            const int r2 = mt / p.tiles_x;
-            const int ty = r2 % p.tiles_y;
-            const int b = r2 / p.tiles_y;
-            uint4 px[2];
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int t = threadIdx.x + h * 128;  // patch pixel 0..179
-                const int py = t / 10, pxx = t - py * 10;
-                const int yy = ty * 16 - 1 + py, xx = tx * 8 - 1 + pxx;
-                uint32_t l0 = 0u, l1 = 0u, l2 = 0u;  // conv zero padding / outside the frame
-                if (t < 180 && yy >= 0 && yy < p.H && xx >= 0 && xx < p.W) {
-                    if constexpr (U8) {
-                        const int oy = yy - p.pad_t, ox = xx - p.pad_l;
-                        if (oy >= 0 && oy < p.in_h && ox >= 0 && ox < p.in_w) {
-                            const uint8_t* s = static_cast<const uint8_t*>(p.in) +
-                                               ((static_cast<size_t>(b) * p.in_h + oy) * p.in_w + ox) * 3;
-                            l0 = lut[__ldg(s)];
-                            l1 = lut[__ldg(s + 1)];
-                            l2 = lut[__ldg(s + 2)];
-                        } else {
-                            l0 = l1 = l2 = 0x0000BF80u;  // Pad(fill=0) BEFORE Normalize: (0-0.5)/0.5 = -1 (exact in bf16)
-                        }
+        // The raw input values of the next kPF tiles are kept in flight in registers (the loop is
+        // unrolled by kPF so every prefetch slot is a statically named register set): without this
+        // each tile pays a full DRAM latency between its loads and its LUT lookups.
+        constexpr int kPF = 4;
+        constexpr uint32_t kZero = U8 ? 256u : 0u;   // conv zero padding (outside the padded frame)
+        constexpr uint32_t kFrame = 257u;            // u8 mode: Pad(fill=0) BEFORE Normalize -> -1
+        // this thread's (up to) two pixels of the 10 x 18 patch
+        const int t1 = threadIdx.x + 128;
+        const int py0 = threadIdx.x / 10, px0 = threadIdx.x - py0 * 10;
+        const int py1 = t1 / 10, px1 = t1 - py1 * 10;
+        const bool has1 = t1 < 180;
+        auto load_px = [&](int b, int yy, int xx, bool live, uint32_t& l0, uint32_t& l1, uint32_t& l2) {
+            l0 = l1 = l2 = kZero;
+            if (live && yy >= 0 && yy < p.H && xx >= 0 && xx < p.W) {
+                if constexpr (U8) {
+                    const int oy = yy - p.pad_t, ox = xx - p.pad_l;
+                    if (oy >= 0 && oy < p.in_h && ox >= 0 && ox < p.in_w) {
+                        const uint8_t* s = static_cast<const uint8_t*>(p.in) +
+                                           ((static_cast<size_t>(b) * p.in_h + oy) * p.in_w + ox) * 3;
+                        l0 = __ldg(s);
+                        l1 = __ldg(s + 1);
+                        l2 = __ldg(s + 2);
                     } else {
-                        const float* s = static_cast<const float*>(p.in) +
-                                         (static_cast<size_t>(b) * 3 * p.H + yy) * p.W + xx;
-                        const size_t plane = static_cast<size_t>(p.H) * p.W;
-                        l0 = split_hi_lo(__ldg(s));
-                        l1 = split_hi_lo(__ldg(s + plane));
-                        l2 = split_hi_lo(__ldg(s + 2 * plane));
+                        l0 = l1 = l2 = kFrame;
                     }
+                } else {
+                    const float* s = static_cast<const float*>(p.in) + (static_cast<size_t>(b) * 3 * p.H + yy) * p.W + xx;
+                    const size_t plane = static_cast<size_t>(p.H) * p.W;
+                    l0 = __float_as_uint(__ldg(s));
+                    l1 = __float_as_uint(__ldg(s + plane));
+                    l2 = __float_as_uint(__ldg(s + 2 * plane));
                 }
-                // K chunk 0 = [hi0 hi1 hi2 lo0 lo1 lo2 0 0]
-                px[h] = make_uint4((l0 & 0xffffu) | (l1 << 16), (l2 & 0xffffu) | (l0 & 0xffff0000u),
-                                   (l1 >> 16) | (l2 & 0xffff0000u), 0u);
             }
-            mbar_wait(&a_empty[stage], phase ^ 1);
-            uint4* plane0 = reinterpret_cast<uint4*>(a_smem + stage * kFirstStageBytes);
-            plane0[threadIdx.x] = px[0];
-            if (threadIdx.x + 128 < 180) plane0[threadIdx.x + 128] = px[1];
-            fence_proxy_async();  // generic-proxy smem writes -> visible to the tensor core's async proxy
-            mbar_arrive(&a_full[stage]);
-            if (++stage == kFirstStages) {
-                stage = 0;
-                phase ^= 1;
+        };
+        TileWalk pf(p.tiles_x, p.tiles_y, mt_begin);  // prefetch cursor, kPF tiles ahead of the store cursor
+        auto load_raw = [&](uint32_t (&raw)[6]) {
+            const int y0 = pf.ty * 16 - 1, x0 = pf.tx * 8 - 1;
+            load_px(pf.b, y0 + py0, x0 + px0, true, raw[0], raw[1], raw[2]);
+            load_px(pf.b, y0 + py1, x0 + px1, has1, raw[3], raw[4], raw[5]);
+            pf.next(p.tiles_x, p.tiles_y);
+        };
+        uint32_t rq[kPF][6];
+#pragma unroll
+        for (int j = 0; j < kPF; ++j)
+            if (mt_begin + j < mt_end) load_raw(rq[j]);
+        uint32_t stage = 0, phase = 0;
+        for (int base = mt_begin; base < mt_end; base += kPF) {
+#pragma unroll
+            for (int j = 0; j < kPF; ++j) {
+                const int mt = base + j;
+                if (mt >= mt_end) break;
+                uint4 px[2];
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    uint32_t l0, l1, l2;
+                    if constexpr (U8) {
+                        l0 = lut[rq[j][3 * h + 0]];
+                        l1 = lut[rq[j][3 * h + 1]];
+                        l2 = lut[rq[j][3 * h + 2]];
+                    } else {
+                        l0 = split_hi_lo(__uint_as_float(rq[j][3 * h + 0]));
+                        l1 = split_hi_lo(__uint_as_float(rq[j][3 * h + 1]));
+                        l2 = split_hi_lo(__uint_as_float(rq[j][3 * h + 2]));
+                    }
+                    // K chunk 0 = [hi0 hi1 hi2 lo0 lo1 lo2 0 0]
+                    px[h] = make_uint4((l0 & 0xffffu) | (l1 << 16), (l2 & 0xffffu) | (l0 & 0xffff0000u),
+                                       (l1 >> 16) | (l2 & 0xffff0000u), 0u);
+                }
+                if (mt + kPF < mt_end) load_raw(rq[j]);
+                mbar_wait(&a_empty[stage], phase ^ 1);
+                uint4* plane0 = reinterpret_cast<uint4*>(a_smem + stage * kFirstStageBytes);
+                plane0[threadIdx.x] = px[0];
+                if (has1) plane0[t1] = px[1];
+                fence_proxy_async();  // generic-proxy smem writes -> visible to the tensor core's async proxy
+                mbar_arrive(&a_full[stage]);
+                if (++stage == kFirstStages) {
+                    stage = 0;
+                    phase ^= 1;
+                }
             }
         }
     } else if (warp == 4) {
@@ -164,7 +226,7 @@ first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParam
         constexpr uint32_t idesc = umma_idesc_bf16(128, N);
         const uint32_t a0 = smem_u32(a_smem), w0 = smem_u32(w_smem);
         uint32_t stage = 0, phase = 0, acc_it = 0;
-        for (int mt = blockIdx.x; mt < p.m_tiles; mt += gridDim.x) {
+        for (int mt = mt_begin; mt < mt_end; ++mt) {
             const uint32_t buf = acc_it & 1;
             mbar_wait(&acc_empty[buf], ((acc_it >> 1) & 1) ^ 1);
             mbar_wait(&a_full[stage], phase);
@@ -197,11 +259,10 @@ first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParam
         uint32_t acc_it = 0;
         const bool issuer = (warp == 5 && lane == 0);
         (void)yl; (void)xl;
-        for (int mt = blockIdx.x; mt < p.m_tiles; mt += gridDim.x) {
-            const int tx = mt % p.tiles_x;
-            const int r2 = mt / p.tiles_x;
-            const int ty = r2 % p.tiles_y;
-            const int b = r2 / p.tiles_y;
+        TileWalk tw(p.tiles_x, p.tiles_y, mt_begin);
+        for (int mt = mt_begin; mt < mt_end; ++mt) {
+            const int tx = tw.tx, ty = tw.ty, b = tw.b;
+            tw.next(p.tiles_x, p.tiles_y);
             const uint32_t buf = acc_it & 1;
             mbar_wait(&acc_full[buf], (acc_it >> 1) & 1);
             tc_fence_after();

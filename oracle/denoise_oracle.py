@@ -94,6 +94,43 @@ def forward(sd: Dict[str, torch.Tensor], x: torch.Tensor, intermediates: Optiona
     return out
 
 
+def _bf16(t: torch.Tensor) -> torch.Tensor:
+    return t.to(torch.bfloat16).to(torch.float32)
+
+
+def forward_bf16_storage(sd: Dict[str, torch.Tensor], x: torch.Tensor) -> torch.Tensor:
+    """The same network (backend/app.py:80-103) with the STORAGE precision of the CUDA path modelled on
+    the CPU: weights rounded to bf16, every stored activation rounded to bf16, fp32 accumulation and
+    fp32 bias/ReLU/tanh, the network input kept as a hi+lo bf16 pair (~16 mantissa bits). It is a
+    second checker, not a second reference: tests use it to tell a kernel bug from bf16 round-off
+    when amplified weights (gain >= 3) make the net chaotic enough that bf16 storage alone exceeds the
+    north-star tolerance against the fp32 reference."""
+    w = {k: (_bf16(v) if k.endswith(".weight") else v) for k, v in sd.items()}
+
+    def conv(t, name, relu=True, store=True):
+        t = F.conv2d(t, w[name + ".weight"], w[name + ".bias"], padding=1)
+        if relu:
+            t = F.relu(t)
+        return _bf16(t) if store else t
+
+    hi = _bf16(x)
+    xin = hi + _bf16(x - hi)
+    a0 = conv(xin, "down1.0")
+    e1 = conv(a0, "down1.2")
+    p1 = F.max_pool2d(e1, 2, 2)
+    a2 = conv(p1, "down2.0")
+    e2 = conv(a2, "down2.2")
+    p2 = F.max_pool2d(e2, 2, 2)
+    b0 = conv(p2, "bottleneck.0")
+    b1 = conv(b0, "bottleneck.2")
+    d2 = _bf16(F.conv_transpose2d(b1, w["up2.weight"], w["up2.bias"], stride=2))
+    u2a = conv(torch.cat([d2, e2], dim=1), "upconv2.0")
+    u2b = conv(u2a, "upconv2.2")
+    d1 = _bf16(F.conv_transpose2d(u2b, w["up1.weight"], w["up1.bias"], stride=2))
+    u1a = conv(torch.cat([d1, e1], dim=1), "upconv1.0")
+    return torch.tanh(conv(u1a, "upconv1.2", relu=False, store=False))
+
+
 def get_padding(w: int, h: int, divisor: int = 4, scale: int = 1) -> Tuple[int, int, int, int]:
     """get_padding (backend/app.py:276-281) on (width, height): (left, top, right, bottom)."""
     d = divisor * scale

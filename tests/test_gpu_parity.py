@@ -48,6 +48,20 @@ def check_float(y, y_ref, target):
     return err
 
 
+def check_amplified(y, sd, x, y_ref):
+    """Weights amplified beyond x2 make the random net chaotic: bf16 STORAGE alone (modelled on the CPU
+    by orc.forward_bf16_storage) then deviates from the fp32 reference by 0.03-0.2, more than the
+    north-star tolerance, and any two bf16 pipelines diverge from each other by a similar amount. Such
+    cases only require the CUDA path to be no further from the fp32 reference than 2x that model
+    (kernel correctness itself is pinned by test_each_layer_in_isolation, which is gain-independent)."""
+    with torch.no_grad():
+        y_model = orc.forward_bf16_storage(sd, x)
+    model_dev = float((y_model - y_ref).abs().max())
+    dev = float((y - y_ref).abs().max())
+    assert dev <= max(MAX_ABS, 2.0 * model_dev), f"max-abs vs fp32 reference {dev} (bf16-storage model: {model_dev})"
+    assert abs(orc.psnr(y, x) - orc.psnr(y_ref, x)) < PSNR_DIV_DB
+
+
 def test_library_is_loaded_in_process(dev):
     """The driver records which .so files the test process loaded: make sure ours is one of them."""
     net, _ = make_net(dev, 0, 1.0)
@@ -66,7 +80,10 @@ def test_forward_vs_reference_golden(dev, golden_dir, name):
     x = torch.from_numpy(g["x"])
     y = net(x.to(dev)).cpu()
     assert y.shape == x.shape and y.dtype == torch.float32
-    check_float(y, torch.from_numpy(g["y"]), x)
+    if float(g["gain"]) <= 2.0:
+        check_float(y, torch.from_numpy(g["y"]), x)
+    else:
+        check_amplified(y, orc.init_state_dict(int(g["meta"][0]), float(g["gain"])), x, torch.from_numpy(g["y"]))
 
 
 @pytest.mark.parametrize("name", ["route_s0_g2_30x27", "route_s3_g2_33x46", "route_s3_g1_64x64"])
@@ -83,23 +100,31 @@ def test_route_u8_vs_reference_golden(dev, golden_dir, name):
 
 
 @pytest.mark.parametrize("B,H,W,gain", [(1, 4, 4, 1.0), (2, 8, 12, 2.0), (3, 20, 36, 3.0), (1, 132, 128, 2.0),
-                                        (5, 64, 64, 1.0), (2, 100, 52, 4.0), (1, 256, 256, 2.0)])
+                                        (5, 64, 64, 1.0), (2, 100, 52, 2.5), (1, 256, 256, 2.0)])
 def test_forward_vs_oracle_shapes(dev, B, H, W, gain):
     net, sd = make_net(dev, 3, gain)
     x = torch.rand(B, 3, H, W, generator=torch.Generator().manual_seed(B * 1000 + H)) * 2 - 1
     with torch.no_grad():
         y_ref = orc.forward(sd, x)
-    check_float(net(x.to(dev)).cpu(), y_ref, x)
+    if gain <= 2.0:
+        check_float(net(x.to(dev)).cpu(), y_ref, x)
+    else:
+        check_amplified(net(x.to(dev)).cpu(), sd, x, y_ref)
 
 
 def test_saturating_weights_cover_full_tanh_range(dev):
-    """Random init only spans +-0.1 at the output; amplified weights drive tanh towards +-1."""
-    net, sd = make_net(dev, 1, 6.0)
+    """Random init only spans +-0.1 at the output; x2 weights with a x4 last layer drive ~20 % of the
+    outputs into tanh saturation (|y| > 0.99) while the net stays non-chaotic."""
+    sd = orc.init_state_dict(1, 2.0)
+    sd["upconv1.2.weight"] = sd["upconv1.2.weight"] * 4.0
+    net = DenoiseGenerator()
+    net.load_state_dict(sd, strict=True)
+    net = net.to(dev).eval()
     x = torch.rand(2, 3, 32, 32, generator=torch.Generator().manual_seed(9)) * 2 - 1
     with torch.no_grad():
         y_ref = orc.forward(sd, x)
-    assert float(y_ref.abs().max()) > 0.5
-    check_float(net(x.to(dev)).cpu(), y_ref, x)
+    assert float((y_ref.abs() > 0.99).float().mean()) > 0.1
+    check_amplified(net(x.to(dev)).cpu(), sd, x, y_ref)
 
 
 def test_intermediate_activations_layer_by_layer(dev):
@@ -125,6 +150,52 @@ def test_intermediate_activations_layer_by_layer(dev):
         assert got.shape == r.shape, name
         rel = float((got - r).abs().max() / r.abs().max())
         assert rel < 2e-2, f"{name}: rel err {rel}"
+
+
+@pytest.mark.parametrize("gain,B,H,W", [(1.0, 2, 32, 48), (3.0, 1, 36, 20), (2.0, 1, 128, 128)])
+def test_each_layer_in_isolation(dev, gain, B, H, W):
+    """Every kernel on its own: layer l's CUDA output against fp32 torch ops applied to the CUDA path's
+    OWN input of that layer (bf16 weights), so no error propagates between layers and the check is
+    independent of how chaotic the weights are. Allowed: one bf16 rounding of the result
+    (|r| * 2^-7) plus accumulation-order noise; the fused max-pools must be exact."""
+    import torch.nn.functional as F
+
+    net, sd = make_net(dev, 5, gain)
+    x = torch.rand(B, 3, H, W, generator=torch.Generator().manual_seed(17)) * 2 - 1
+    y = net(x.to(dev)).cpu()
+    w = {k: (v.to(torch.bfloat16).float() if k.endswith(".weight") else v) for k, v in sd.items()}
+    act = {n: net.debug_activation(n, (B, 3, H, W)).permute(0, 3, 1, 2).contiguous()
+           for n in ("a0", "cat1", "p1", "a2", "cat2", "p2", "b0", "b1", "u2a", "u2b", "u1a")}
+    d1, e1 = act["cat1"][:, :64], act["cat1"][:, 64:]
+    d2, e2 = act["cat2"][:, :128], act["cat2"][:, 128:]
+
+    def conv(t, name, relu=True):
+        t = F.conv2d(t, w[name + ".weight"], w[name + ".bias"], padding=1)
+        return F.relu(t) if relu else t
+
+    def close(got, ref, what):
+        tol = ref.abs() * 2.0 ** -7 + 2e-4 * float(ref.abs().max()) + 1e-6
+        bad = (got - ref).abs() > tol
+        assert not bool(bad.any()), f"{what}: {int(bad.sum())} elements off, worst {float(((got - ref).abs() - tol).max())}"
+
+    hi = x.to(torch.bfloat16).float()
+    xin = hi + (x - hi).to(torch.bfloat16).float()
+    with torch.no_grad():
+        close(act["a0"], conv(xin, "down1.0"), "down1.0")
+        close(e1, conv(act["a0"], "down1.2"), "down1.2")
+        assert torch.equal(act["p1"], F.max_pool2d(e1, 2, 2)), "pool1"
+        close(act["a2"], conv(act["p1"], "down2.0"), "down2.0")
+        close(e2, conv(act["a2"], "down2.2"), "down2.2")
+        assert torch.equal(act["p2"], F.max_pool2d(e2, 2, 2)), "pool2"
+        close(act["b0"], conv(act["p2"], "bottleneck.0"), "bottleneck.0")
+        close(act["b1"], conv(act["b0"], "bottleneck.2"), "bottleneck.2")
+        close(d2, F.conv_transpose2d(act["b1"], w["up2.weight"], w["up2.bias"], stride=2), "up2")
+        close(act["u2a"], conv(act["cat2"], "upconv2.0"), "upconv2.0")
+        close(act["u2b"], conv(act["u2a"], "upconv2.2"), "upconv2.2")
+        close(d1, F.conv_transpose2d(act["u2b"], w["up1.weight"], w["up1.bias"], stride=2), "up1")
+        close(act["u1a"], conv(act["cat1"], "upconv1.0"), "upconv1.0")
+        y_l = torch.tanh(conv(act["u1a"], "upconv1.2", relu=False))
+        assert float((y - y_l).abs().max()) <= 2e-3, "upconv1.2 + tanh"
 
 
 def test_batch_and_chunk_invariance_bit_exact(dev):
@@ -275,12 +346,12 @@ def test_noiser_philox_statistics(dev):
     # normality: fraction within one sigma
     frac = float(((out - 128).abs() <= 25).float().mean())
     assert abs(frac - 0.6827) < 0.02
-    # salt & pepper: reference hit-rate 5.4-5.9 % of pixels for p = 0.02 + 0.02, and the
-    # last row / column are never hit (randint(0, dim-1))
+    # salt & pepper: n = int(H*W*C*p) draws per kind (the reference counts channels, so ~5.8 % of pixels per
+    # kind for p = 0.02), and the last row / column are never hit (randint(0, dim-1))
     grey = torch.full((4, 128, 128, 3), 100, dtype=torch.uint8, device=dev)
     sp = cu_noiser.add_salt_pepper_noise(grey, 0.02, 0.02, seed=7)
     hit = float((sp[..., 0] != 100).float().mean())
-    assert 0.045 < hit < 0.065
+    assert 0.10 < hit < 0.125      # 2 x 983 draws on 127x127 of 128x128 pixels, minus collisions
     assert bool((sp[:, -1] == 100).all()) and bool((sp[:, :, -1] == 100).all())
     assert set(torch.unique(sp).tolist()) <= {0, 100, 255}
 
