@@ -129,6 +129,24 @@ __device__ __forceinline__ void for_each_chunk(uint32_t taddr, F&& f) {
     }
 }
 
+// Same, over NCH chunks whose 32-column chunk index is given by map(i), i = 0..NCH-1.
+template <int NCH, class M, class F>
+__device__ __forceinline__ void for_each_chunk_mapped(uint32_t taddr, M&& map, F&& f) {
+    uint32_t va[32], vb[32];
+    tmem_ld_32x32(taddr + map(0) * 32, va);
+#pragma unroll
+    for (int i = 0; i < NCH; i += 2) {
+        tmem_ld_wait();
+        if (i + 1 < NCH) tmem_ld_32x32(taddr + map(i + 1) * 32, vb);
+        f(map(i), va);
+        if (i + 1 < NCH) {
+            tmem_ld_wait();
+            if (i + 2 < NCH) tmem_ld_32x32(taddr + map(i + 2) * 32, va);
+            f(map(i + 1), vb);
+        }
+    }
+}
+
 template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0, int TS = 0>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
@@ -462,42 +480,47 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     static_assert(N == 256, "staged convT epilogue assumes 8 chunks per tile");
                     const bool issuer = (threadIdx.x == 64);
                     const bool c64mode = (p.cout == 64);
-                    if (issuer) bulk_wait_read<0>();  // previous tile's two stores have drained both slabs
-                    named_bar_sync(1, 128);
-                    for_each_chunk<N / 32>(taddr, [&](int ch, uint32_t (&v)[32]) {
-                        const int n = n_tile * N + ch * 32;
-                        const int quad = n / p.cout;
-                        const int c = n - quad * p.cout;
-                        const int slab = c64mode ? (ch >> 2) : ((ch & 3) >> 1);
-                        const float4* b4 = reinterpret_cast<const float4*>(p.bias + c);
-                        uint32_t pk[16];
+                    // The two slabs are filled and stored one after the other, so the TMA store of one
+                    // slab overlaps the TMEM reads that fill the other (also across tiles).
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const float4 bb = __ldg(b4 + j);
-                            pk[2 * j + 0] =
-                                pack_bf16x2(__uint_as_float(v[4 * j + 0]) + bb.x, __uint_as_float(v[4 * j + 1]) + bb.y);
-                            pk[2 * j + 1] =
-                                pack_bf16x2(__uint_as_float(v[4 * j + 2]) + bb.z, __uint_as_float(v[4 * j + 3]) + bb.w);
-                        }
-                        const int orow_i = yl * 16 + 2 * xl + (quad & 1);
-                        uint8_t* rowp = o_smem + slab * Cfg::OT_SLAB + orow_i * 128;
+                    for (int slab = 0; slab < 2; ++slab) {
+                        // the store that read this slab two commit groups ago must have drained it
+                        if (issuer) bulk_wait_read<1>();
+                        named_bar_sync(1, 128);
+                        // chunks of this slab: cout 64 -> 4 consecutive (quadrants 2*slab, 2*slab+1);
+                        // cout 128 -> channels [64*slab, 64*slab+64) of both quadrants of this n_tile
+                        auto chunk_of = [&](int i) { return c64mode ? slab * 4 + i : (i >> 1) * 4 + slab * 2 + (i & 1); };
+                        for_each_chunk_mapped<4>(taddr, chunk_of, [&](int ch, uint32_t (&v)[32]) {
+                            const int n = n_tile * N + ch * 32;
+                            const int quad = n / p.cout;
+                            const int c = n - quad * p.cout;
+                            const float4* b4 = reinterpret_cast<const float4*>(p.bias + c);
+                            uint32_t pk[16];
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const int cj = (ch & 1) * 4 + j;
-                            st_shared_v4(rowp + ((cj ^ (orow_i & 7)) << 4), pk[4 * j], pk[4 * j + 1], pk[4 * j + 2],
-                                         pk[4 * j + 3]);
-                        }
-                    });
-                    fence_proxy_async();
-                    named_bar_sync(1, 128);
-                    if (issuer && !(p.debug_flags & 1)) {
+                            for (int j = 0; j < 8; ++j) {
+                                const float4 bb = __ldg(b4 + j);
+                                pk[2 * j + 0] = pack_bf16x2(__uint_as_float(v[4 * j + 0]) + bb.x,
+                                                            __uint_as_float(v[4 * j + 1]) + bb.y);
+                                pk[2 * j + 1] = pack_bf16x2(__uint_as_float(v[4 * j + 2]) + bb.z,
+                                                            __uint_as_float(v[4 * j + 3]) + bb.w);
+                            }
+                            const int orow_i = yl * 16 + 2 * xl + (quad & 1);
+                            uint8_t* rowp = o_smem + slab * Cfg::OT_SLAB + orow_i * 128;
 #pragma unroll
-                        for (int slab = 0; slab < 2; ++slab) {
+                            for (int j = 0; j < 4; ++j) {
+                                const int cj = (ch & 1) * 4 + j;
+                                st_shared_v4(rowp + ((cj ^ (orow_i & 7)) << 4), pk[4 * j], pk[4 * j + 1], pk[4 * j + 2],
+                                             pk[4 * j + 3]);
+                            }
+                        });
+                        fence_proxy_async();
+                        named_bar_sync(1, 128);
+                        if (issuer && !(p.debug_flags & 1)) {
                             const int dy = c64mode ? slab : n_tile;
                             const int c0 = p.out_c0 + (c64mode ? 0 : slab * 64);
                             tma_store_5d(&tmO, o_smem + slab * Cfg::OT_SLAB, c0, 2 * tc.x0, dy, tc.y0, tc.b);
+                            bulk_commit();
                         }
-                        bulk_commit();
                     }
                 } else if constexpr (EPI == EPI_CONVT) {
                     // GEMM column n = quadrant*cout + c, quadrant = dy*2+dx; output pixel (2y+dy, 2x+dx).
