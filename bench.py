@@ -165,7 +165,7 @@ def main():
     ap.add_argument("--sub-batch", type=int, default=64, help="e2e: images per H2D/compute/D2H pipeline slot")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--debug-flags", type=int, default=0, help="bring-up experiments (invalidates results)")
-    ap.add_argument("--variant", type=int, default=0, help="A/B kernel variant bit mask (cid_set_option 'variant')")
+    ap.add_argument("--variant", type=int, default=-1, help="CTA-pair layer bit mask (cid_set_option 'variant'; -1 = library default)")
     ap.add_argument("--layers", action="store_true", help="also print the per-layer table to stderr")
     args = ap.parse_args()
 
@@ -204,7 +204,7 @@ def main():
     net.set_option("profile", 1)
     if args.debug_flags:
         net.set_option("debug_flags", args.debug_flags)
-    if args.variant:
+    if args.variant >= 0:
         net.set_option("variant", args.variant)
 
     host_in = synthetic_noisy_u8(1234 + rank, B, H, W).pin_memory()

@@ -253,6 +253,7 @@ static int pack_layer(cid_ctx* c, int l) {
     std::copy(b.begin(), b.end(), bp.begin());
     CID_CHECK_CUDA(cudaMalloc(reinterpret_cast<void**>(&c->bias_dev[l]), bp.size() * 4));
     CID_CHECK_CUDA(cudaMemcpy(c->bias_dev[l], bp.data(), bp.size() * 4, cudaMemcpyHostToDevice));
+    if (box_rows % 2 == 0 && make_weight_map(&c->tmWh[l], c->w_dev[l], rows, L.cin, box_rows / 2)) return 1;
     return make_weight_map(&c->tmW[l], c->w_dev[l], rows, L.cin, box_rows);
 }
 
@@ -312,10 +313,10 @@ static int get_plan(cid_ctx* c, int Bc, int H, int W, const void* ws, cid_plan**
 // ---------------------------------------------------------------------------------------------
 // launches
 // ---------------------------------------------------------------------------------------------
-template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0, int TS = 0>
+template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0, int TS = 0, int CG = 1>
 static int launch_conv(cid_ctx* c, int slot, const CUtensorMap& tmA, const CUtensorMap& tmW, const CUtensorMap& tmO,
                        const CUtensorMap& tmO2, ConvParams p, cudaStream_t st) {
-    using Cfg = ConvCfg<N, TAPS, S, WRES, EPI, PW, TS>;
+    using Cfg = ConvCfg<N, TAPS, S, WRES, EPI, PW, TS, CG>;
     const int budget = c->max_smem - 1024 - 512 - Cfg::O_BYTES;
     int w_stages = WRES ? 1 : (N == 256 && TS ? 3 : 4);
     const int w_bytes = (WRES ? p.kb_count * TAPS : w_stages) * Cfg::W_BYTES;
@@ -326,15 +327,32 @@ static int launch_conv(cid_ctx* c, int slot, const CUtensorMap& tmA, const CUten
     p.tiles_x = (p.W + 7) / 8;
     p.tiles_y = (p.H + 15) / 16;
     p.m_tiles = p.B * p.tiles_x * p.tiles_y;
-    p.num_work = ((p.m_tiles + S - 1) / S) * p.n_tiles;
+    p.num_work = ((p.m_tiles + S * CG - 1) / (S * CG)) * p.n_tiles;  // work items of one CTA (or CTA pair)
     const int smem = Cfg::smem_bytes(p.kb_count, a_stages, w_stages);
-    auto kern = conv_umma_kernel<N, TAPS, S, WRES, EPI, PW, TS>;
+    auto kern = conv_umma_kernel<N, TAPS, S, WRES, EPI, PW, TS, CG>;
     if (!(c->attr_done & (1u << slot))) {
         CID_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c->max_smem));
         c->attr_done |= (1u << slot);
     }
-    const int grid = std::min(p.num_work, c->num_sms);
-    kern<<<grid, kConvThreads, smem, st>>>(tmA, tmW, tmO, tmO2, p);
+    const int grid = std::min(p.num_work * CG, c->num_sms / CG * CG);
+    if (CG == 1) {
+        kern<<<grid, kConvThreads, smem, st>>>(tmA, tmW, tmO, tmO2, p);
+    } else {
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3(grid);
+        cfg.blockDim = dim3(kConvThreads);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = st;
+        cudaLaunchAttribute attr;
+        attr.id = cudaLaunchAttributeClusterDimension;
+        attr.val.clusterDim.x = CG;
+        attr.val.clusterDim.y = 1;
+        attr.val.clusterDim.z = 1;
+        cfg.attrs = &attr;
+        cfg.numAttrs = 1;
+        CID_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmW, tmO, tmO2, p));
+    }
     CID_CHECK_CUDA(cudaGetLastError());
     c->launches++;
     return 0;
@@ -432,32 +450,52 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         ConvParams p = base(1, 0);
         p.out = buf(B_CAT1); p.out_cs = 128; p.out_c0 = 64;
         p.out2 = buf(B_P1); p.out2_cs = 64; p.out2_c0 = 0;
-        if (launch_conv<64, 9, 1, true, EPI_RELU_POOL, 10, TSV(1)>(c, 0, pl->tmA[1], c->tmW[1], pl->tmO[1], pl->tmO2[1], p, st)) return 1;
+        if (c->variant & 32) {
+            if (launch_conv<64, 9, 1, true, EPI_RELU_POOL, 10, TSV(1), 2>(c, 10, pl->tmA[1], c->tmWh[1], pl->tmO[1], pl->tmO2[1], p, st)) return 1;
+        } else {
+            if (launch_conv<64, 9, 1, true, EPI_RELU_POOL, 10, TSV(1)>(c, 0, pl->tmA[1], c->tmW[1], pl->tmO[1], pl->tmO2[1], p, st)) return 1;
+        }
     }
     if (prof_mark(c, st)) return 1;
     {  // L2 down2.0 -> a2
         ConvParams p = base(2, 1);
         p.out = buf(B_A2); p.out_cs = 128; p.out_c0 = 0;
-        if (launch_conv<128, 9, 1, true, EPI_RELU, 10, TSV(1)>(c, 1, pl->tmA[2], c->tmW[2], pl->tmO[2], pl->tmO[2], p, st)) return 1;
+        if (c->variant & 8) {
+            if (launch_conv<128, 9, 1, true, EPI_RELU, 10, TSV(1), 2>(c, 11, pl->tmA[2], c->tmWh[2], pl->tmO[2], pl->tmO[2], p, st)) return 1;
+        } else {
+            if (launch_conv<128, 9, 1, true, EPI_RELU, 10, TSV(1)>(c, 1, pl->tmA[2], c->tmW[2], pl->tmO[2], pl->tmO[2], p, st)) return 1;
+        }
     }
     if (prof_mark(c, st)) return 1;
     {  // L3 down2.2 -> cat2[:,128:256] + p2
         ConvParams p = base(3, 1);
         p.out = buf(B_CAT2); p.out_cs = 256; p.out_c0 = 128;
         p.out2 = buf(B_P2); p.out2_cs = 128; p.out2_c0 = 0;
-        if (launch_conv<128, 9, 2, false, EPI_RELU_POOL, 10, TSV(1)>(c, 2, pl->tmA[3], c->tmW[3], pl->tmO[3], pl->tmO2[3], p, st)) return 1;
+        if (c->variant & 2) {
+            if (launch_conv<128, 9, 2, false, EPI_RELU_POOL, 10, TSV(1), 2>(c, 12, pl->tmA[3], c->tmWh[3], pl->tmO[3], pl->tmO2[3], p, st)) return 1;
+        } else {
+            if (launch_conv<128, 9, 2, false, EPI_RELU_POOL, 10, TSV(1)>(c, 2, pl->tmA[3], c->tmW[3], pl->tmO[3], pl->tmO2[3], p, st)) return 1;
+        }
     }
     if (prof_mark(c, st)) return 1;
     {  // L4 bottleneck.0 -> b0
         ConvParams p = base(4, 2);
         p.out = buf(B_B0); p.out_cs = 256; p.out_c0 = 0;
-        if (launch_conv<256, 9, 1, false, EPI_RELU, 10, TSV(1)>(c, 3, pl->tmA[4], c->tmW[4], pl->tmO[4], pl->tmO[4], p, st)) return 1;
+        if (c->variant & 16) {
+            if (launch_conv<256, 9, 1, false, EPI_RELU, 10, TSV(1), 2>(c, 13, pl->tmA[4], c->tmWh[4], pl->tmO[4], pl->tmO[4], p, st)) return 1;
+        } else {
+            if (launch_conv<256, 9, 1, false, EPI_RELU, 10, TSV(1)>(c, 3, pl->tmA[4], c->tmW[4], pl->tmO[4], pl->tmO[4], p, st)) return 1;
+        }
     }
     if (prof_mark(c, st)) return 1;
     {  // L5 bottleneck.2 -> b1
         ConvParams p = base(5, 2);
         p.out = buf(B_B1); p.out_cs = 256; p.out_c0 = 0;
-        if (launch_conv<256, 9, 1, false, EPI_RELU, 10, TSV(1)>(c, 3, pl->tmA[5], c->tmW[5], pl->tmO[5], pl->tmO[5], p, st)) return 1;
+        if (c->variant & 16) {
+            if (launch_conv<256, 9, 1, false, EPI_RELU, 10, TSV(1), 2>(c, 13, pl->tmA[5], c->tmWh[5], pl->tmO[5], pl->tmO[5], p, st)) return 1;
+        } else {
+            if (launch_conv<256, 9, 1, false, EPI_RELU, 10, TSV(1)>(c, 3, pl->tmA[5], c->tmW[5], pl->tmO[5], pl->tmO[5], p, st)) return 1;
+        }
     }
     if (prof_mark(c, st)) return 1;
     {  // L6 up2 (convT) -> cat2[:,0:128]
@@ -470,13 +508,21 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
     {  // L7 upconv2.0 (reads cat2) -> u2a
         ConvParams p = base(7, 1);
         p.out = buf(B_U2A); p.out_cs = 128; p.out_c0 = 0;
-        if (launch_conv<128, 9, 2, false, EPI_RELU, 10, TSV(1)>(c, 5, pl->tmA[7], c->tmW[7], pl->tmO[7], pl->tmO[7], p, st)) return 1;
+        if (c->variant & 2) {
+            if (launch_conv<128, 9, 2, false, EPI_RELU, 10, TSV(1), 2>(c, 14, pl->tmA[7], c->tmWh[7], pl->tmO[7], pl->tmO[7], p, st)) return 1;
+        } else {
+            if (launch_conv<128, 9, 2, false, EPI_RELU, 10, TSV(1)>(c, 5, pl->tmA[7], c->tmW[7], pl->tmO[7], pl->tmO[7], p, st)) return 1;
+        }
     }
     if (prof_mark(c, st)) return 1;
     {  // L8 upconv2.2 -> u2b
         ConvParams p = base(8, 1);
         p.out = buf(B_U2B); p.out_cs = 128; p.out_c0 = 0;
-        if (launch_conv<128, 9, 2, false, EPI_RELU, 10, TSV(1)>(c, 5, pl->tmA[8], c->tmW[8], pl->tmO[8], pl->tmO[8], p, st)) return 1;
+        if (c->variant & 2) {
+            if (launch_conv<128, 9, 2, false, EPI_RELU, 10, TSV(1), 2>(c, 14, pl->tmA[8], c->tmWh[8], pl->tmO[8], pl->tmO[8], p, st)) return 1;
+        } else {
+            if (launch_conv<128, 9, 2, false, EPI_RELU, 10, TSV(1)>(c, 5, pl->tmA[8], c->tmW[8], pl->tmO[8], pl->tmO[8], p, st)) return 1;
+        }
     }
     if (prof_mark(c, st)) return 1;
     {  // L9 up1 (convT) -> cat1[:,0:64]
@@ -489,8 +535,8 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
     {  // L10 upconv1.0 (reads cat1) -> u1a
         ConvParams p = base(10, 0);
         p.out = buf(B_U1A); p.out_cs = 64; p.out_c0 = 0;
-        if (c->variant & 1) {  // weights streamed through a ring, one weight tile feeding 2 pixel tiles
-            if (launch_conv<64, 9, 2, false, EPI_RELU, 10, TSV(1)>(c, 9, pl->tmA[10], c->tmW[10], pl->tmO[10], pl->tmO[10], p, st)) return 1;
+        if (c->variant & 4) {
+            if (launch_conv<64, 9, 1, true, EPI_RELU, 10, TSV(1), 2>(c, 15, pl->tmA[10], c->tmWh[10], pl->tmO[10], pl->tmO[10], p, st)) return 1;
         } else {
             if (launch_conv<64, 9, 1, true, EPI_RELU, 10, TSV(1)>(c, 6, pl->tmA[10], c->tmW[10], pl->tmO[10], pl->tmO[10], p, st)) return 1;
         }
@@ -660,7 +706,9 @@ int cid_set_option(cid_handle h, const char* name, int64_t value) {
         h->first_tc = value != 0;
         return 0;
     }
-    if (!strcmp(name, "variant")) {  // bit mask of A/B kernel variants (bring-up experiments)
+    // bit mask of layers that run as CTA pairs (cta_group::2): 2 = down2.2/upconv2.0/upconv2.2, 4 = upconv1.0,
+    // 8 = down2.0, 16 = bottleneck.*, 32 = down1.2. Default 6: the layers where it measured faster.
+    if (!strcmp(name, "variant")) {
         h->variant = static_cast<int>(value);
         return 0;
     }

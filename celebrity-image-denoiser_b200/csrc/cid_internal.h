@@ -70,13 +70,14 @@ struct cid_ctx {
     void* w_dev[12] = {nullptr};      // packed bf16 weights per layer (0 unused)
     float* bias_dev[12] = {nullptr};  // fp32 bias per layer
     CUtensorMap tmW[12];
+    CUtensorMap tmWh[12];             // same weights, box of N/2 rows (CTA-pair kernels load half a tile each)
     void* first_w_host = nullptr;     // cid::FirstConvW (kernel parameter block)
     std::vector<cid_plan> plans;
     uint32_t attr_done = 0;           // bit per kernel instantiation: max-dynamic-smem attribute set
     std::map<uint64_t, void*> resize_coeffs;  // (in_size,out_size) -> device coefficient block
     // per-layer timing ("profile" option): 13 events bracket the 12 layers of every pass
     int debug_flags = 0;
-    int variant = 0;                  // A/B kernel variants ("variant" option)
+    int variant = 6;                  // layers run as CTA pairs ("variant" option, see cid_set_option)
     bool first_tc = true;             // layer 0 on tensor cores (false: CUDA-core direct conv)
     bool patch = true;                // 3x3 layers load one halo patch per K block instead of 3 boxes
     bool profile = false;

@@ -56,8 +56,13 @@ struct ConvParams {
 // PW = 10: one halo patch {64 ch, 10 px, 18 rows} per K block; tap (dy,dx) is the same patch read at
 //          start + (dy*PW + dx)*128 B with SBO = PW*128 B (relies on the 128-B swizzle being a
 //          function of the absolute shared-memory address, for TMA writes and UMMA reads alike).
-template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0, int TS = 0>
+// CG = 2: CTA pairs (cluster of 2, tcgen05 cta_group::2). Each CTA owns its own S pixel tiles (A operand,
+//         accumulators, epilogue) but only HALF of every weight tile (N/2 rows); the leader CTA's MMAs
+//         read both halves, so the per-SM shared-memory traffic of the B operand is halved.
+template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0, int TS = 0, int CG = 1>
 struct ConvCfg {
+    static_assert(CG == 1 || CG == 2, "single CTA or CTA pair");
+    static_assert(CG == 1 || N % 32 == 0, "pair mode: each CTA holds N/2 weight rows, N multiple of 16 for M=256");
     static_assert(TAPS == 9 || TAPS == 1, "3x3 or 1x1");
     static_assert(N % 16 == 0 && N >= 16 && N <= 256, "UMMA N for M=128");
     static_assert(2 * S * N <= 512, "two accumulator buffers must fit TMEM");
@@ -69,7 +74,7 @@ struct ConvCfg {
     static constexpr int A_TX = (PW ? PW : 8) * A_ROWS * 128;   // bytes one box delivers
     static constexpr int A_BYTES = (A_TX + 1023) / 1024 * 1024; // stage pitch (1024-B aligned)
     static constexpr int SBO = (PW ? PW : 8) * 128;
-    static constexpr int W_BYTES = N * 128;
+    static constexpr int W_BYTES = (N / CG) * 128;  // this CTA's share of one weight tile
     static constexpr int ACC_COLS = S * N;
     static constexpr int TMEM_COLS = (2 * ACC_COLS <= 32)    ? 32
                                      : (2 * ACC_COLS <= 64)  ? 64
@@ -147,12 +152,13 @@ __device__ __forceinline__ void for_each_chunk_mapped(uint32_t taddr, M&& map, F
     }
 }
 
-template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0, int TS = 0>
+template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0, int TS = 0, int CG = 1>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                  const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO2,
                  const ConvParams p) {
-    using Cfg = ConvCfg<N, TAPS, S, WRES, EPI, PW, TS>;
+    using Cfg = ConvCfg<N, TAPS, S, WRES, EPI, PW, TS, CG>;
+    constexpr bool PAIR = CG == 2;
     constexpr int DX = Cfg::DX, DY = Cfg::DY, AL = Cfg::A_LOADS;
     constexpr int DXI = PW ? DX : 1;  // horizontal taps served by one A box
     constexpr int A_BYTES = Cfg::A_BYTES, W_BYTES = Cfg::W_BYTES;
@@ -178,6 +184,9 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int lane = threadIdx.x & 31;
     const int AST = p.a_stages;
     const int WST = p.w_stages;
+    const uint32_t rank = PAIR ? cluster_ctarank() : 0u;           // 0 = leader (issues the pair's MMAs)
+    const int unit = PAIR ? (blockIdx.x >> 1) : blockIdx.x;        // CTA (or CTA pair) index
+    const int units = PAIR ? (gridDim.x >> 1) : gridDim.x;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
@@ -186,52 +195,78 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             tma_prefetch_desc(&tmO);
             if (EPI == EPI_RELU_POOL) tma_prefetch_desc(&tmO2);
         }
+        // pair mode: the leader's "full" barriers collect one expect_tx arrival per CTA, its acc_empty
+        // one arrival per epilogue warp of both CTAs; "empty"/acc_full get one multicast commit each.
         for (int i = 0; i < kMaxStages; ++i) {
-            mbar_init(&a_full[i], 1);
+            mbar_init(&a_full[i], CG);
             mbar_init(&a_empty[i], 1);
-            mbar_init(&w_full[i], 1);
+            mbar_init(&w_full[i], CG);
             mbar_init(&w_empty[i], 1);
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&acc_full[i], 1);
-            mbar_init(&acc_empty[i], 4);
+            mbar_init(&acc_empty[i], 4 * CG);
         }
         fence_mbar_init();
     }
     if (warp == 1) {
-        tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+        if (PAIR)
+            tmem_alloc_cg2(tmem_slot, Cfg::TMEM_COLS);
+        else
+            tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
     }
     tc_fence_before();
-    __syncthreads();
+    if (PAIR)
+        cluster_sync_all();  // the peer's barriers are initialised before anything arrives on them
+    else
+        __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
         // ======================= TMA producer =======================
         if (lane == 0) {
+            // completion barrier of a load: this CTA's own, or (pair mode) the LEADER's at the same offset
+            auto full_bar = [&](uint64_t* bar) { return PAIR ? mapa_u32(smem_u32(bar), 0) : smem_u32(bar); };
+            auto expect = [&](uint64_t* bar, uint32_t bytes) {
+                if (PAIR)
+                    mbar_arrive_expect_tx_cluster(full_bar(bar), bytes);
+                else
+                    mbar_arrive_expect_tx(bar, bytes);
+            };
+            auto load_w = [&](void* dst, uint64_t* bar, int c0, int row) {
+                if (PAIR)
+                    tma_load_2d_cg2(dst, &tmW, full_bar(bar), c0, row + static_cast<int>(rank) * (N / CG), kEvictLast);
+                else
+                    tma_load_2d(dst, &tmW, bar, c0, row, kEvictLast);
+            };
             if (WRES) {
-                mbar_arrive_expect_tx(&w_full[0], static_cast<uint32_t>(w_items) * W_BYTES);
+                expect(&w_full[0], static_cast<uint32_t>(w_items) * W_BYTES);
                 for (int kb = 0; kb < p.kb_count; ++kb)
                     for (int tap = 0; tap < TAPS; ++tap)
-                        tma_load_2d(w_smem + (kb * TAPS + tap) * W_BYTES, &tmW, &w_full[0], kb * 64,
-                                    tap * p.w_rows_per_tap, kEvictLast);
+                        load_w(w_smem + (kb * TAPS + tap) * W_BYTES, &w_full[0], kb * 64, tap * p.w_rows_per_tap);
             }
             uint32_t a_stage = 0, a_phase = 0, w_stage = 0, w_phase = 0;
-            for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
+            for (int work = unit; work < p.num_work; work += units) {
                 const int n_tile = work % p.n_tiles;
                 const int st = work / p.n_tiles;
                 TileCoord tc[S];
 #pragma unroll
-                for (int s = 0; s < S; ++s) tc[s] = decode_tile(p, st * S + s);
+                for (int s = 0; s < S; ++s) tc[s] = decode_tile(p, (st * CG + static_cast<int>(rank)) * S + s);
                 for (int kb = 0; kb < p.kb_count; ++kb) {
                     for (int al = 0; al < AL; ++al) {
 #pragma unroll
                         for (int s = 0; s < S; ++s) {
                             mbar_wait(&a_empty[a_stage], a_phase ^ 1);
-                            mbar_arrive_expect_tx(&a_full[a_stage], Cfg::A_TX);
-                            tma_load_4d(a_smem + a_stage * A_BYTES, &tmA, &a_full[a_stage], kb * 64,
-                                        tc[s].x0 + (PW ? 0 : al) - (DX == 3 ? 1 : 0), tc[s].y0 - (DY == 3 ? 1 : 0),
-                                        tc[s].b, kEvictNormal);
+                            expect(&a_full[a_stage], Cfg::A_TX);
+                            if (PAIR)
+                                tma_load_4d_cg2(a_smem + a_stage * A_BYTES, &tmA, full_bar(&a_full[a_stage]), kb * 64,
+                                                tc[s].x0 + (PW ? 0 : al) - (DX == 3 ? 1 : 0),
+                                                tc[s].y0 - (DY == 3 ? 1 : 0), tc[s].b, kEvictNormal);
+                            else
+                                tma_load_4d(a_smem + a_stage * A_BYTES, &tmA, &a_full[a_stage], kb * 64,
+                                            tc[s].x0 + (PW ? 0 : al) - (DX == 3 ? 1 : 0),
+                                            tc[s].y0 - (DY == 3 ? 1 : 0), tc[s].b, kEvictNormal);
                             if (++a_stage == static_cast<uint32_t>(AST)) {
                                 a_stage = 0;
                                 a_phase ^= 1;
@@ -242,9 +277,9 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                 const int dx = PW ? dxi : al;
                                 for (int dy = 0; dy < DY; ++dy) {
                                     mbar_wait(&w_empty[w_stage], w_phase ^ 1);
-                                    mbar_arrive_expect_tx(&w_full[w_stage], W_BYTES);
-                                    tma_load_2d(w_smem + w_stage * W_BYTES, &tmW, &w_full[w_stage], kb * 64,
-                                                (dy * DX + dx) * p.w_rows_per_tap + n_tile * N, kEvictLast);
+                                    expect(&w_full[w_stage], W_BYTES);
+                                    load_w(w_smem + w_stage * W_BYTES, &w_full[w_stage], kb * 64,
+                                           (dy * DX + dx) * p.w_rows_per_tap + n_tile * N);
                                     if (++w_stage == static_cast<uint32_t>(WST)) {
                                         w_stage = 0;
                                         w_phase ^= 1;
@@ -256,22 +291,40 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 }
             }
         }
-    } else if (warp == 1) {
-        // ======================= MMA issuer =======================
+    } else if (warp == 1 && rank == 0) {
+        // ======================= MMA issuer (pair mode: the leader CTA only) =======================
         // The whole warp walks the loop (warp-uniform control flow keeps descriptors in uniform
         // registers); one elected lane issues the MMAs and the commits.
-        constexpr uint32_t idesc = umma_idesc_bf16(128, N);
+        constexpr uint32_t idesc = umma_idesc_bf16(128 * CG, N);
+        auto wait_full = [&](uint64_t* bar, uint32_t parity) {
+            if (PAIR)
+                mbar_wait_cluster(bar, parity);
+            else
+                mbar_wait(bar, parity);
+        };
+        auto mma = [&](uint32_t d, uint64_t ad, uint64_t bd, uint32_t acc) {
+            if (PAIR)
+                umma_bf16_ss_cg2(d, ad, bd, idesc, acc);
+            else
+                umma_bf16_ss(d, ad, bd, idesc, acc);
+        };
+        auto commit = [&](uint64_t* bar) {
+            if (PAIR)
+                umma_commit_cg2(bar);
+            else
+                umma_commit(bar);
+        };
         const uint32_t a_lo0 = umma_desc_lo(smem_u32(a_smem));
         const uint32_t w_lo0 = umma_desc_lo(smem_u32(w_smem));
         uint32_t a_stage = 0, a_phase = 0, w_stage = 0, w_phase = 0, acc_it = 0;
         if (WRES) {
-            mbar_wait(&w_full[0], 0);
+            wait_full(&w_full[0], 0);
             tc_fence_after();
         }
-        for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
+        for (int work = unit; work < p.num_work; work += units) {
             const uint32_t buf = acc_it & 1;
             const uint32_t aph = (acc_it >> 1) & 1;
-            mbar_wait(&acc_empty[buf], aph ^ 1);
+            wait_full(&acc_empty[buf], aph ^ 1);
             tc_fence_after();
             const uint32_t d_base = tmem_base + buf * Cfg::ACC_COLS;
             for (int kb = 0; kb < p.kb_count; ++kb) {
@@ -279,7 +332,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     uint32_t stg[S];
 #pragma unroll
                     for (int s = 0; s < S; ++s) {
-                        mbar_wait(&a_full[a_stage], a_phase);
+                        wait_full(&a_full[a_stage], a_phase);
                         stg[s] = a_stage;
                         if (++a_stage == static_cast<uint32_t>(AST)) {
                             a_stage = 0;
@@ -296,7 +349,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             if (WRES) {
                                 w_lo = w_lo0 + static_cast<uint32_t>(kb * TAPS + dy * DX + dx) * (W_BYTES >> 4);
                             } else {
-                                mbar_wait(&w_full[w_stage], w_phase);
+                                wait_full(&w_full[w_stage], w_phase);
                                 tc_fence_after();
                                 w_lo = w_lo0 + w_stage * (W_BYTES >> 4);
                             }
@@ -310,12 +363,11 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                                           (PW ? (dy * PW + dxi) * (128 >> 4) : dy * (1024 >> 4));
 #pragma unroll
                                     for (int k = 0; k < 4; ++k) {
-                                        umma_bf16_ss(d_base + s * N, umma_desc_join<Cfg::SBO>(a_lo + 2 * k),
-                                                     umma_desc_join<1024>(w_lo + 2 * k), idesc,
-                                                     (first && k == 0) ? 0u : 1u);
+                                        mma(d_base + s * N, umma_desc_join<Cfg::SBO>(a_lo + 2 * k),
+                                            umma_desc_join<1024>(w_lo + 2 * k), (first && k == 0) ? 0u : 1u);
                                     }
                                 }
-                                if (!WRES) umma_commit(&w_empty[w_stage]);
+                                if (!WRES) commit(&w_empty[w_stage]);
                             }
                             __syncwarp();
                             if (!WRES) {
@@ -328,16 +380,16 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     }
                     if (elect_one()) {
 #pragma unroll
-                        for (int s = 0; s < S; ++s) umma_commit(&a_empty[stg[s]]);
+                        for (int s = 0; s < S; ++s) commit(&a_empty[stg[s]]);
                     }
                     __syncwarp();
                 }
             }
-            if (elect_one()) umma_commit(&acc_full[buf]);
+            if (elect_one()) commit(&acc_full[buf]);
             __syncwarp();
             ++acc_it;
         }
-    } else {
+    } else if (warp >= 2) {
         // ======================= epilogue (4 warps) =======================
         const int q = warp & 3;
         const int row = q * 32 + lane;
@@ -345,7 +397,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int xl = row & 7;
         uint32_t acc_it = 0;
         uint32_t o_count = 0;  // staged slabs written so far (TS)
-        for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
+        for (int work = unit; work < p.num_work; work += units) {
             const int n_tile = work % p.n_tiles;
             const int st = work / p.n_tiles;
             const uint32_t buf = acc_it & 1;
@@ -354,7 +406,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             tc_fence_after();
 #pragma unroll
             for (int s = 0; s < S; ++s) {
-                const int mt = st * S + s;
+                const int mt = (st * CG + static_cast<int>(rank)) * S + s;
                 const TileCoord tc = decode_tile(p, mt);
                 const int y = tc.y0 + yl;
                 const int x = tc.x0 + xl;
@@ -583,17 +635,28 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&acc_empty[buf]);
+            if (lane == 0) {
+                if (PAIR)
+                    mbar_arrive_cluster(mapa_u32(smem_u32(&acc_empty[buf]), 0));  // the leader's barrier
+                else
+                    mbar_arrive(&acc_empty[buf]);
+            }
             ++acc_it;
         }
         if (TS && threadIdx.x == 64) bulk_wait<0>();  // all TMA stores complete before the CTA exits
     }
 
     tc_fence_before();
-    __syncthreads();
+    if (PAIR)
+        cluster_sync_all();  // neither CTA leaves while the other may still touch its smem / TMEM / barriers
+    else
+        __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+        if (PAIR)
+            tmem_dealloc_cg2(tmem_base, Cfg::TMEM_COLS);
+        else
+            tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
     }
 }
 
