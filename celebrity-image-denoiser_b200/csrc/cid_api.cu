@@ -25,13 +25,7 @@
 #include "first_conv_umma.cuh"
 #include "last_conv_umma.cuh"
 
-// TSV(1) layers stage their output in shared memory and write it with TMA stores; build with
-// -DCID_NO_TS to fall back to per-thread global stores (A/B experiments).
-#ifdef CID_NO_TS
-#define TSV(x) 0
-#else
 #define TSV(x) x
-#endif
 
 namespace cid {
 
@@ -451,20 +445,17 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         p.out = buf(B_CAT1); p.out_cs = 128; p.out_c0 = 64;
         p.out2 = buf(B_P1); p.out2_cs = 64; p.out2_c0 = 0;
         if (c->variant & 32) {
-            if (launch_conv<64, 9, 1, true, EPI_RELU_POOL, 10, TSV(1), 2>(c, 10, pl->tmA[1], c->tmWh[1], pl->tmO[1], pl->tmO2[1], p, st)) return 1;
+            if (launch_conv<64, 9, 2, true, EPI_RELU_POOL, 10, TSV(1), 2>(c, 10, pl->tmA[1], c->tmWh[1], pl->tmO[1], pl->tmO2[1], p, st)) return 1;
         } else {
-            if (launch_conv<64, 9, 1, true, EPI_RELU_POOL, 10, TSV(1)>(c, 0, pl->tmA[1], c->tmW[1], pl->tmO[1], pl->tmO2[1], p, st)) return 1;
+            if (launch_conv<64, 9, 2, true, EPI_RELU_POOL, 10, TSV(1)>(c, 0, pl->tmA[1], c->tmW[1], pl->tmO[1], pl->tmO2[1], p, st)) return 1;
         }
     }
     if (prof_mark(c, st)) return 1;
     {  // L2 down2.0 -> a2
         ConvParams p = base(2, 1);
         p.out = buf(B_A2); p.out_cs = 128; p.out_c0 = 0;
-        if (c->variant & 8) {
-            if (launch_conv<128, 9, 1, true, EPI_RELU, 10, TSV(1), 2>(c, 11, pl->tmA[2], c->tmWh[2], pl->tmO[2], pl->tmO[2], p, st)) return 1;
-        } else {
-            if (launch_conv<128, 9, 1, true, EPI_RELU, 10, TSV(1)>(c, 1, pl->tmA[2], c->tmW[2], pl->tmO[2], pl->tmO[2], p, st)) return 1;
-        }
+        // CTA pair: the resident weights (147 KB) only fit next to the staging buffers when halved
+        if (launch_conv<128, 9, 1, true, EPI_RELU, 10, TSV(1), 2>(c, 11, pl->tmA[2], c->tmWh[2], pl->tmO[2], pl->tmO[2], p, st)) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L3 down2.2 -> cat2[:,128:256] + p2
@@ -535,11 +526,8 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
     {  // L10 upconv1.0 (reads cat1) -> u1a
         ConvParams p = base(10, 0);
         p.out = buf(B_U1A); p.out_cs = 64; p.out_c0 = 0;
-        if (c->variant & 4) {
-            if (launch_conv<64, 9, 1, true, EPI_RELU, 10, TSV(1), 2>(c, 15, pl->tmA[10], c->tmWh[10], pl->tmO[10], pl->tmO[10], p, st)) return 1;
-        } else {
-            if (launch_conv<64, 9, 1, true, EPI_RELU, 10, TSV(1)>(c, 6, pl->tmA[10], c->tmW[10], pl->tmO[10], pl->tmO[10], p, st)) return 1;
-        }
+        // CTA pair (resident weights halved: 74 KB per CTA)
+        if (launch_conv<64, 9, 1, true, EPI_RELU, 10, TSV(1), 2>(c, 15, pl->tmA[10], c->tmWh[10], pl->tmO[10], pl->tmO[10], p, st)) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L11 upconv1.2 + tanh -> y   (transposed GEMM: weights on M, the halo patch on N)
@@ -706,8 +694,8 @@ int cid_set_option(cid_handle h, const char* name, int64_t value) {
         h->first_tc = value != 0;
         return 0;
     }
-    // bit mask of layers that run as CTA pairs (cta_group::2): 2 = down2.2/upconv2.0/upconv2.2, 4 = upconv1.0,
-    // 8 = down2.0, 16 = bottleneck.*, 32 = down1.2. Default 6: the layers where it measured faster.
+    // bit mask of optional CTA-pair (cta_group::2) layers: 2 = down2.2/upconv2.0/upconv2.2, 16 = bottleneck.*,
+    // 32 = down1.2 (down2.0 and upconv1.0 always run as pairs). Default 2: where it measured faster.
     if (!strcmp(name, "variant")) {
         h->variant = static_cast<int>(value);
         return 0;

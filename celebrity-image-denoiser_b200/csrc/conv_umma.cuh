@@ -28,9 +28,9 @@
 
 namespace cid {
 
-enum : int { EPI_RELU = 0, EPI_RELU_POOL = 1, EPI_CONVT = 2, EPI_TANH_F32 = 3, EPI_TANH_U8 = 4 };
+enum : int { EPI_RELU = 0, EPI_RELU_POOL = 1, EPI_CONVT = 2, EPI_TANH_F32 = 3, EPI_TANH_U8 = 4 };  // TANH_*: last_conv_umma.cuh
 
-constexpr int kConvThreads = 192;
+constexpr int kConvThreads = 320;  // warp 0 TMA, warp 1 MMA, warps 2..9 two epilogue groups
 constexpr int kMaxStages = 8;
 
 struct ConvParams {
@@ -81,15 +81,15 @@ struct ConvCfg {
                                      : (2 * ACC_COLS <= 128) ? 128
                                      : (2 * ACC_COLS <= 256) ? 256
                                                              : 512;
-    // TS = 1: the epilogue stages each 64-channel slab of the tile in shared memory (SW128 rows,
-    // same geometry as the A boxes) and writes it with one TMA store instead of per-thread stores.
-    static constexpr int NOB = 2;  // staging buffers in flight
+    // The epilogue stages each 64-channel slab of a tile in shared memory (SW128 rows, same geometry as
+    // the A boxes) and writes it with one TMA store. Each of the 2 epilogue groups has NOB buffers.
+    static_assert(TS == 1, "all epilogues are staged");
+    static constexpr int NOB = 1;  // staging buffers per group (the other group's buffer gives the overlap)
     static constexpr int O_SLAB = 128 * 128;
     static constexpr int O2_SLAB = 32 * 128;
     static constexpr int OT_SLAB = 256 * 128;  // EPI_CONVT: [16 rows][16 px][64 ch] of the 2x-upsampled output
-    static constexpr int O_BYTES = !TS ? 0
-                                   : EPI == EPI_CONVT ? 2 * OT_SLAB
-                                                      : NOB * (O_SLAB + (EPI == EPI_RELU_POOL ? O2_SLAB : 0));
+    static constexpr int O_GROUP = NOB * (O_SLAB + (EPI == EPI_RELU_POOL ? O2_SLAB : 0));
+    static constexpr int O_BYTES = EPI == EPI_CONVT ? 2 * OT_SLAB : 2 * O_GROUP;
     // dynamic shared memory needed (bytes), including 1 KB of alignment slack
     static int smem_bytes(int kb_count, int a_stages, int w_stages) {
         int w_items = WRES ? kb_count * TAPS : w_stages;
@@ -169,8 +169,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int w_items = WRES ? p.kb_count * TAPS : p.w_stages;
     uint8_t* w_smem = smem;
     uint8_t* a_smem = smem + w_items * W_BYTES;
-    uint8_t* o_smem = a_smem + p.a_stages * A_BYTES;               // [NOB][128 rows][128 B]
-    uint8_t* o2_smem = o_smem + Cfg::NOB * Cfg::O_SLAB;            // [NOB][32 rows][128 B] (pool)
+    uint8_t* o_smem = a_smem + p.a_stages * A_BYTES;               // epilogue staging, Cfg::O_BYTES
     uint64_t* bars = reinterpret_cast<uint64_t*>(o_smem + Cfg::O_BYTES);
     uint64_t* a_full = bars;
     uint64_t* a_empty = bars + kMaxStages;
@@ -205,7 +204,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&acc_full[i], 1);
-            mbar_init(&acc_empty[i], 4 * CG);
+            mbar_init(&acc_empty[i], 8 * CG);
         }
         fence_mbar_init();
     }
@@ -390,13 +389,20 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             ++acc_it;
         }
     } else if (warp >= 2) {
-        // ======================= epilogue (4 warps) =======================
+        // ======================= epilogue: 2 groups x 4 warps =======================
+        // Group g (warps 2+4g .. 5+4g; TMEM lane quarter = warp & 3) owns the 64-channel output slabs
+        // of the work item whose index has parity g, with its own staging buffers, named barrier and
+        // TMA-store issuer, so the two groups drain one accumulator buffer concurrently.
+        const int g = (warp - 2) >> 2;
         const int q = warp & 3;
         const int row = q * 32 + lane;
         const int yl = row >> 3;
         const int xl = row & 7;
+        const bool issuer = (threadIdx.x == 64 + 128 * g);  // lane 0 of the group's first warp
+        const int bar_id = 1 + g;
+        uint8_t* og = o_smem + g * Cfg::O_GROUP;
         uint32_t acc_it = 0;
-        uint32_t o_count = 0;  // staged slabs written so far (TS)
+        uint32_t o_count = 0;  // slabs this group has staged so far
         for (int work = unit; work < p.num_work; work += units) {
             const int n_tile = work % p.n_tiles;
             const int st = work / p.n_tiles;
@@ -404,232 +410,115 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const uint32_t aph = (acc_it >> 1) & 1;
             mbar_wait(&acc_full[buf], aph);
             tc_fence_after();
-#pragma unroll
-            for (int s = 0; s < S; ++s) {
-                const int mt = (st * CG + static_cast<int>(rank)) * S + s;
-                const TileCoord tc = decode_tile(p, mt);
-                const int y = tc.y0 + yl;
-                const int x = tc.x0 + xl;
-                const bool valid = (mt < p.m_tiles) && (y < p.H) && (x < p.W) && !(p.debug_flags & 1);
-                if (p.debug_flags & 2) continue;
-                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * Cfg::ACC_COLS + s * N;
-
-                if constexpr ((EPI == EPI_RELU || EPI == EPI_RELU_POOL) && TS) {
-                    // ---- staged: smem slab (SW128) -> one TMA store per 64 channels ----
-                    const bool issuer = (threadIdx.x == 64);  // lane 0 of the first epilogue warp
+            const uint32_t tbase = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * Cfg::ACC_COLS;
+            if (!(p.debug_flags & 2)) {
+                if constexpr (EPI == EPI_RELU || EPI == EPI_RELU_POOL) {
+                    constexpr int SL = N / 64;  // 64-channel slabs per pixel tile
                     const int sub = (xl & 1) | ((yl & 1) << 1);
                     const int prow_i = (yl >> 1) * 4 + (xl >> 1);
-                    for_each_chunk<N / 32>(taddr, [&](int ch, uint32_t (&v)[32]) {
+#pragma unroll
+                    for (int j = 0; j < S * SL; ++j) {
+                        if ((j & 1) != g) continue;
+                        const int s = j / SL, cs = j % SL;
+                        const TileCoord tc = decode_tile(p, (st * CG + static_cast<int>(rank)) * S + s);
                         const uint32_t ob = o_count % Cfg::NOB;
-                        if ((ch & 1) == 0) {
-                            // the store that used this buffer NOB slabs ago must have finished READING it
-                            if (issuer) bulk_wait_read<Cfg::NOB - 1>();
-                            named_bar_sync(1, 128);
-                        }
-                        const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_tile * N + ch * 32);
-                        uint32_t pk[16];
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const float4 bb = __ldg(b4 + j);
-                            const float f0 = fmaxf(__uint_as_float(v[4 * j + 0]) + bb.x, 0.f);
-                            const float f1 = fmaxf(__uint_as_float(v[4 * j + 1]) + bb.y, 0.f);
-                            const float f2 = fmaxf(__uint_as_float(v[4 * j + 2]) + bb.z, 0.f);
-                            const float f3 = fmaxf(__uint_as_float(v[4 * j + 3]) + bb.w, 0.f);
-                            pk[2 * j + 0] = pack_bf16x2(f0, f1);
-                            pk[2 * j + 1] = pack_bf16x2(f2, f3);
-                        }
-                        uint8_t* rowp = o_smem + ob * Cfg::O_SLAB + row * 128;
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const int cj = (ch & 1) * 4 + j;  // 16-byte chunk inside the 128-byte row
-                            st_shared_v4(rowp + ((cj ^ (row & 7)) << 4), pk[4 * j], pk[4 * j + 1], pk[4 * j + 2],
-                                         pk[4 * j + 3]);
-                        }
-                        if constexpr (EPI == EPI_RELU_POOL) {
-                            // 2x2 max: x partner is lane^1, y partner is lane^8 (row = y*8 + x).
-#pragma unroll
-                            for (int j = 0; j < 16; ++j) {
-                                uint32_t m = max_bf16x2(pk[j], __shfl_xor_sync(0xffffffffu, pk[j], 1));
-                                pk[j] = max_bf16x2(m, __shfl_xor_sync(0xffffffffu, m, 8));
-                            }
-                            // each of the 4 lanes of a 2x2 block writes a different 8-channel quarter
-                            const uint32_t o0 = sub == 0 ? pk[0] : sub == 1 ? pk[4] : sub == 2 ? pk[8] : pk[12];
-                            const uint32_t o1 = sub == 0 ? pk[1] : sub == 1 ? pk[5] : sub == 2 ? pk[9] : pk[13];
-                            const uint32_t o2 = sub == 0 ? pk[2] : sub == 1 ? pk[6] : sub == 2 ? pk[10] : pk[14];
-                            const uint32_t o3 = sub == 0 ? pk[3] : sub == 1 ? pk[7] : sub == 2 ? pk[11] : pk[15];
-                            const int cj = (ch & 1) * 4 + sub;
-                            st_shared_v4(o2_smem + ob * Cfg::O2_SLAB + prow_i * 128 + ((cj ^ (prow_i & 7)) << 4), o0,
-                                         o1, o2, o3);
-                        }
-                        if ((ch & 1) == 1) {
-                            fence_proxy_async();
-                            named_bar_sync(1, 128);
-                            if (issuer && !(p.debug_flags & 1)) {
-                                const int c64 = n_tile * N + (ch >> 1) * 64;
-                                tma_store_4d(&tmO, o_smem + ob * Cfg::O_SLAB, p.out_c0 + c64, tc.x0, tc.y0, tc.b);
-                                if constexpr (EPI == EPI_RELU_POOL)
-                                    tma_store_4d(&tmO2, o2_smem + ob * Cfg::O2_SLAB, p.out2_c0 + c64, tc.x0 >> 1,
-                                                 tc.y0 >> 1, tc.b);
-                                bulk_commit();
-                            }
-                            ++o_count;
-                        }
-                    });
-                } else if constexpr (EPI == EPI_RELU || EPI == EPI_RELU_POOL) {
-                    __nv_bfloat16* out = static_cast<__nv_bfloat16*>(p.out);
-                    const size_t pix = (static_cast<size_t>(tc.b) * p.H + y) * p.W + x;
-                    __nv_bfloat16* orow = out + pix * p.out_cs + p.out_c0 + n_tile * N;
-                    __nv_bfloat16* prow = nullptr;
-                    bool pvalid = false;
-                    int sub = 0;
-                    if constexpr (EPI == EPI_RELU_POOL) {
-                        const int PH = p.H >> 1, PW = p.W >> 1;
-                        pvalid = valid;  // H, W even: a valid pixel's 2x2 block is entirely valid
-                        const size_t ppix = (static_cast<size_t>(tc.b) * PH + (y >> 1)) * PW + (x >> 1);
-                        sub = (xl & 1) | ((yl & 1) << 1);
-                        prow = static_cast<__nv_bfloat16*>(p.out2) + ppix * p.out2_cs + p.out2_c0 + n_tile * N +
-                               sub * 8;
-                    }
-                    for_each_chunk<N / 32>(taddr, [&](int ch, uint32_t (&v)[32]) {
-                        const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_tile * N + ch * 32);
-                        uint32_t pk[16];
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const float4 bb = __ldg(b4 + j);
-                            const float f0 = fmaxf(__uint_as_float(v[4 * j + 0]) + bb.x, 0.f);
-                            const float f1 = fmaxf(__uint_as_float(v[4 * j + 1]) + bb.y, 0.f);
-                            const float f2 = fmaxf(__uint_as_float(v[4 * j + 2]) + bb.z, 0.f);
-                            const float f3 = fmaxf(__uint_as_float(v[4 * j + 3]) + bb.w, 0.f);
-                            pk[2 * j + 0] = pack_bf16x2(f0, f1);
-                            pk[2 * j + 1] = pack_bf16x2(f2, f3);
-                        }
-                        if (valid) {
-#pragma unroll
-                            for (int j = 0; j < 4; ++j)
-                                st_global_v4(orow + ch * 32 + j * 8, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2],
-                                             pk[4 * j + 3]);
-                        }
-                        if constexpr (EPI == EPI_RELU_POOL) {
-                            // 2x2 max: x partner is lane^1, y partner is lane^8 (row = y*8 + x).
-#pragma unroll
-                            for (int j = 0; j < 16; ++j) {
-                                uint32_t m = max_bf16x2(pk[j], __shfl_xor_sync(0xffffffffu, pk[j], 1));
-                                pk[j] = max_bf16x2(m, __shfl_xor_sync(0xffffffffu, m, 8));
-                            }
-                            // each of the 4 lanes of a 2x2 block stores a different 8-channel quarter
-                            const uint32_t o0 = sub == 0 ? pk[0] : sub == 1 ? pk[4] : sub == 2 ? pk[8] : pk[12];
-                            const uint32_t o1 = sub == 0 ? pk[1] : sub == 1 ? pk[5] : sub == 2 ? pk[9] : pk[13];
-                            const uint32_t o2 = sub == 0 ? pk[2] : sub == 1 ? pk[6] : sub == 2 ? pk[10] : pk[14];
-                            const uint32_t o3 = sub == 0 ? pk[3] : sub == 1 ? pk[7] : sub == 2 ? pk[11] : pk[15];
-                            if (pvalid) st_global_v4(prow + ch * 32, o0, o1, o2, o3);
-                        }
-                    });
-                } else if constexpr (EPI == EPI_CONVT && TS) {
-                    // ---- staged transposed conv: GEMM column n = quadrant*cout + c, quadrant = dy*2+dx.
-                    // The tile's 8 chunks fill two slabs [16 y][16 px][64 ch] of output rows 2y+dy
-                    // (cout 64: slab = dy; cout 128: slab = 64-channel half, dy = n_tile), each written by
-                    // one 5-D TMA store over (C, 2W, dy, H, B).
-                    static_assert(N == 256, "staged convT epilogue assumes 8 chunks per tile");
-                    const bool issuer = (threadIdx.x == 64);
-                    const bool c64mode = (p.cout == 64);
-                    // The two slabs are filled and stored one after the other, so the TMA store of one
-                    // slab overlaps the TMEM reads that fill the other (also across tiles).
-#pragma unroll
-                    for (int slab = 0; slab < 2; ++slab) {
-                        // the store that read this slab two commit groups ago must have drained it
-                        if (issuer) bulk_wait_read<1>();
-                        named_bar_sync(1, 128);
-                        // chunks of this slab: cout 64 -> 4 consecutive (quadrants 2*slab, 2*slab+1);
-                        // cout 128 -> channels [64*slab, 64*slab+64) of both quadrants of this n_tile
-                        auto chunk_of = [&](int i) { return c64mode ? slab * 4 + i : (i >> 1) * 4 + slab * 2 + (i & 1); };
-                        for_each_chunk_mapped<4>(taddr, chunk_of, [&](int ch, uint32_t (&v)[32]) {
-                            const int n = n_tile * N + ch * 32;
-                            const int quad = n / p.cout;
-                            const int c = n - quad * p.cout;
-                            const float4* b4 = reinterpret_cast<const float4*>(p.bias + c);
+                        uint8_t* slab = og + ob * Cfg::O_SLAB;
+                        uint8_t* slab2 = og + Cfg::NOB * Cfg::O_SLAB + ob * Cfg::O2_SLAB;
+                        // the store that used this buffer NOB slabs ago must have finished READING it
+                        if (issuer) bulk_wait_read<Cfg::NOB - 1>();
+                        named_bar_sync(bar_id, 128);
+                        for_each_chunk<2>(tbase + s * N + cs * 64, [&](int ch, uint32_t (&v)[32]) {
+                            const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_tile * N + cs * 64 + ch * 32);
                             uint32_t pk[16];
 #pragma unroll
-                            for (int j = 0; j < 8; ++j) {
-                                const float4 bb = __ldg(b4 + j);
-                                pk[2 * j + 0] = pack_bf16x2(__uint_as_float(v[4 * j + 0]) + bb.x,
-                                                            __uint_as_float(v[4 * j + 1]) + bb.y);
-                                pk[2 * j + 1] = pack_bf16x2(__uint_as_float(v[4 * j + 2]) + bb.z,
-                                                            __uint_as_float(v[4 * j + 3]) + bb.w);
+                            for (int jj = 0; jj < 8; ++jj) {
+                                const float4 bb = __ldg(b4 + jj);
+                                const float f0 = fmaxf(__uint_as_float(v[4 * jj + 0]) + bb.x, 0.f);
+                                const float f1 = fmaxf(__uint_as_float(v[4 * jj + 1]) + bb.y, 0.f);
+                                const float f2 = fmaxf(__uint_as_float(v[4 * jj + 2]) + bb.z, 0.f);
+                                const float f3 = fmaxf(__uint_as_float(v[4 * jj + 3]) + bb.w, 0.f);
+                                pk[2 * jj + 0] = pack_bf16x2(f0, f1);
+                                pk[2 * jj + 1] = pack_bf16x2(f2, f3);
                             }
-                            const int orow_i = yl * 16 + 2 * xl + (quad & 1);
-                            uint8_t* rowp = o_smem + slab * Cfg::OT_SLAB + orow_i * 128;
+                            uint8_t* rowp = slab + row * 128;
 #pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-                                const int cj = (ch & 1) * 4 + j;
-                                st_shared_v4(rowp + ((cj ^ (orow_i & 7)) << 4), pk[4 * j], pk[4 * j + 1], pk[4 * j + 2],
-                                             pk[4 * j + 3]);
+                            for (int jj = 0; jj < 4; ++jj) {
+                                const int cj = ch * 4 + jj;  // 16-byte chunk inside the 128-byte row
+                                st_shared_v4(rowp + ((cj ^ (row & 7)) << 4), pk[4 * jj], pk[4 * jj + 1], pk[4 * jj + 2],
+                                             pk[4 * jj + 3]);
+                            }
+                            if constexpr (EPI == EPI_RELU_POOL) {
+                                // 2x2 max: x partner is lane^1, y partner is lane^8 (row = y*8 + x).
+#pragma unroll
+                                for (int jj = 0; jj < 16; ++jj) {
+                                    uint32_t m = max_bf16x2(pk[jj], __shfl_xor_sync(0xffffffffu, pk[jj], 1));
+                                    pk[jj] = max_bf16x2(m, __shfl_xor_sync(0xffffffffu, m, 8));
+                                }
+                                // each of the 4 lanes of a 2x2 block writes a different 8-channel quarter
+                                const uint32_t o0 = sub == 0 ? pk[0] : sub == 1 ? pk[4] : sub == 2 ? pk[8] : pk[12];
+                                const uint32_t o1 = sub == 0 ? pk[1] : sub == 1 ? pk[5] : sub == 2 ? pk[9] : pk[13];
+                                const uint32_t o2 = sub == 0 ? pk[2] : sub == 1 ? pk[6] : sub == 2 ? pk[10] : pk[14];
+                                const uint32_t o3 = sub == 0 ? pk[3] : sub == 1 ? pk[7] : sub == 2 ? pk[11] : pk[15];
+                                const int cj = ch * 4 + sub;
+                                st_shared_v4(slab2 + prow_i * 128 + ((cj ^ (prow_i & 7)) << 4), o0, o1, o2, o3);
                             }
                         });
                         fence_proxy_async();
-                        named_bar_sync(1, 128);
+                        named_bar_sync(bar_id, 128);
                         if (issuer && !(p.debug_flags & 1)) {
-                            const int dy = c64mode ? slab : n_tile;
-                            const int c0 = p.out_c0 + (c64mode ? 0 : slab * 64);
-                            tma_store_5d(&tmO, o_smem + slab * Cfg::OT_SLAB, c0, 2 * tc.x0, dy, tc.y0, tc.b);
+                            const int c64 = n_tile * N + cs * 64;
+                            tma_store_4d(&tmO, slab, p.out_c0 + c64, tc.x0, tc.y0, tc.b);
+                            if constexpr (EPI == EPI_RELU_POOL)
+                                tma_store_4d(&tmO2, slab2, p.out2_c0 + c64, tc.x0 >> 1, tc.y0 >> 1, tc.b);
                             bulk_commit();
                         }
+                        ++o_count;
                     }
-                } else if constexpr (EPI == EPI_CONVT) {
-                    // GEMM column n = quadrant*cout + c, quadrant = dy*2+dx; output pixel (2y+dy, 2x+dx).
-                    __nv_bfloat16* out = static_cast<__nv_bfloat16*>(p.out);
-                    const int OH = p.H * 2, OW = p.W * 2;
-                    for_each_chunk<N / 32>(taddr, [&](int ch, uint32_t (&v)[32]) {
+                } else {
+                    // ---- transposed conv: GEMM column n = quadrant*cout + c, quadrant = dy*2+dx. The tile's 8
+                    // chunks fill two slabs [16 y][16 px][64 ch] of output rows 2y+dy (cout 64: slab = dy;
+                    // cout 128: slab = 64-channel half, dy = n_tile), each written by one 5-D TMA store over
+                    // (C, 2W, dy, H, B). Group g fills and stores slab g.
+                    static_assert(EPI == EPI_CONVT && N == 256 && S == 1, "convT epilogue: 8 chunks per tile");
+                    const TileCoord tc = decode_tile(p, st * CG + static_cast<int>(rank));
+                    const bool c64mode = (p.cout == 64);
+                    const int slab_i = g;
+                    uint8_t* slab = o_smem + slab_i * Cfg::OT_SLAB;
+                    if (issuer) bulk_wait_read<0>();  // this group's previous store has drained the slab
+                    named_bar_sync(bar_id, 128);
+                    // chunks of this slab: cout 64 -> 4 consecutive (quadrants 2*slab, 2*slab+1);
+                    // cout 128 -> channels [64*slab, 64*slab+64) of both quadrants of this n_tile
+                    auto chunk_of = [&](int i) { return c64mode ? slab_i * 4 + i : (i >> 1) * 4 + slab_i * 2 + (i & 1); };
+                    for_each_chunk_mapped<4>(tbase, chunk_of, [&](int ch, uint32_t (&v)[32]) {
                         const int n = n_tile * N + ch * 32;
                         const int quad = n / p.cout;
                         const int c = n - quad * p.cout;
                         const float4* b4 = reinterpret_cast<const float4*>(p.bias + c);
                         uint32_t pk[16];
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const float4 bb = __ldg(b4 + j);
-                            pk[2 * j + 0] =
-                                pack_bf16x2(__uint_as_float(v[4 * j + 0]) + bb.x, __uint_as_float(v[4 * j + 1]) + bb.y);
-                            pk[2 * j + 1] =
-                                pack_bf16x2(__uint_as_float(v[4 * j + 2]) + bb.z, __uint_as_float(v[4 * j + 3]) + bb.w);
+                        for (int jj = 0; jj < 8; ++jj) {
+                            const float4 bb = __ldg(b4 + jj);
+                            pk[2 * jj + 0] = pack_bf16x2(__uint_as_float(v[4 * jj + 0]) + bb.x,
+                                                         __uint_as_float(v[4 * jj + 1]) + bb.y);
+                            pk[2 * jj + 1] = pack_bf16x2(__uint_as_float(v[4 * jj + 2]) + bb.z,
+                                                         __uint_as_float(v[4 * jj + 3]) + bb.w);
                         }
-                        if (valid) {
-                            const size_t pix =
-                                (static_cast<size_t>(tc.b) * OH + (2 * y + (quad >> 1))) * OW + (2 * x + (quad & 1));
-                            __nv_bfloat16* orow = out + pix * p.out_cs + p.out_c0 + c;
+                        const int orow_i = yl * 16 + 2 * xl + (quad & 1);
+                        uint8_t* rowp = slab + orow_i * 128;
 #pragma unroll
-                            for (int j = 0; j < 4; ++j)
-                                st_global_v4(orow + j * 8, pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+                        for (int jj = 0; jj < 4; ++jj) {
+                            const int cj = (ch & 1) * 4 + jj;
+                            st_shared_v4(rowp + ((cj ^ (orow_i & 7)) << 4), pk[4 * jj], pk[4 * jj + 1], pk[4 * jj + 2],
+                                         pk[4 * jj + 3]);
                         }
                     });
-                } else {
-                    // final 64->3 conv: columns 0..2 are real, tanh, then fp32 NCHW or u8 NHWC (cropped)
-                    uint32_t v[4];
-                    tmem_ld_32x4(taddr, v);
-                    tmem_ld_wait();
-                    float t[3];
-#pragma unroll
-                    for (int c = 0; c < 3; ++c) t[c] = tanhf(__uint_as_float(v[c]) + __ldg(p.bias + c));
-                    if (valid) {
-                        if constexpr (EPI == EPI_TANH_F32) {
-                            float* out = static_cast<float*>(p.out);
-#pragma unroll
-                            for (int c = 0; c < 3; ++c)
-                                out[((static_cast<size_t>(tc.b) * 3 + c) * p.H + y) * p.W + x] = t[c];
-                        } else {
-                            // (y*0.5+0.5).clamp(0,1) then ToPILImage: mul(255) and a TRUNCATING byte cast
-                            // (backend/app.py:435,472)
-                            const int oy = y - p.crop_t, ox = x - p.crop_l;
-                            if (oy >= 0 && oy < p.out_h && ox >= 0 && ox < p.out_w) {
-                                uint8_t* out = static_cast<uint8_t*>(p.out) +
-                                               ((static_cast<size_t>(tc.b) * p.out_h + oy) * p.out_w + ox) * 3;
-#pragma unroll
-                                for (int c = 0; c < 3; ++c) {
-                                    float u = __fmaf_rn(t[c], 0.5f, 0.5f);
-                                    u = fminf(fmaxf(u, 0.f), 1.f);
-                                    out[c] = static_cast<uint8_t>(__fmul_rn(u, 255.f));
-                                }
-                            }
-                        }
+                    fence_proxy_async();
+                    named_bar_sync(bar_id, 128);
+                    if (issuer && !(p.debug_flags & 1)) {
+                        const int dy = c64mode ? slab_i : n_tile;
+                        const int c0 = p.out_c0 + (c64mode ? 0 : slab_i * 64);
+                        tma_store_5d(&tmO, slab, c0, 2 * tc.x0, dy, tc.y0, tc.b);
+                        bulk_commit();
                     }
                 }
             }
@@ -643,7 +532,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
             ++acc_it;
         }
-        if (TS && threadIdx.x == 64) bulk_wait<0>();  // all TMA stores complete before the CTA exits
+        if (issuer) bulk_wait<0>();  // all TMA stores complete before the CTA exits
     }
 
     tc_fence_before();
