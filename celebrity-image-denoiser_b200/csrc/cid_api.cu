@@ -24,6 +24,7 @@
 #include "edge_kernels.cuh"
 #include "first_conv_umma.cuh"
 #include "last_conv_umma.cuh"
+#include "cgan_first_conv.cuh"
 
 #define TSV(x) x
 
@@ -156,6 +157,13 @@ static uint16_t f32_to_bf16_rne(float f) {
     return static_cast<uint16_t>(u >> 16);
 }
 
+static float bf16_to_f32(uint16_t h) {
+    const uint32_t u = static_cast<uint32_t>(h) << 16;
+    float f;
+    memcpy(&f, &u, 4);
+    return f;
+}
+
 // per-layer tensor-core tile width N and padded row count per tap
 static int layer_n(int l) {
     switch (l) {
@@ -186,14 +194,17 @@ static int pack_layer(cid_ctx* c, int l) {
         }
         // tensor-core variant: per tap a [cout 64][K 16] tile in the un-swizzled K-major layout
         // [tap][k chunk][cout][8 bf16]; K chunk 0 = [w_r w_g w_b | w_r w_g w_b | 0 0] (the input is
-        // split hi+lo along K), K chunk 1 = 0.
+        // split hi+lo along K), K chunk 1 = [wlo_r wlo_g wlo_b | 0 ...]: the MMA reads the same pixel chunk for
+        // both K chunks (LBO = 0), so chunk 1 adds x_hi * w_lo.
         std::vector<uint16_t> pk(kFirstWBytes / 2, 0);
         for (int tap = 0; tap < 9; ++tap)
             for (int co = 0; co < 64; ++co)
                 for (int ci = 0; ci < 3; ++ci) {
-                    const uint16_t v = f32_to_bf16_rne(w[(static_cast<size_t>(co) * 3 + ci) * 9 + tap]);
+                    const float wf = w[(static_cast<size_t>(co) * 3 + ci) * 9 + tap];
+                    const uint16_t v = f32_to_bf16_rne(wf);
                     pk[((tap * 2 + 0) * 64 + co) * 8 + ci] = v;
                     pk[((tap * 2 + 0) * 64 + co) * 8 + 3 + ci] = v;
+                    pk[((tap * 2 + 1) * 64 + co) * 8 + ci] = f32_to_bf16_rne(wf - bf16_to_f32(v));  // w_lo (x_hi)
                 }
         if (c->w_dev[0]) cudaFree(c->w_dev[0]);
         if (c->bias_dev[0]) cudaFree(c->bias_dev[0]);
@@ -560,13 +571,17 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
     return 0;
 }
 
+}  // namespace cid
+#include "cgan_model.cuh"
+namespace cid {
+
 static int chunk_of(const cid_ctx* c, int B) {
     return (c->chunk > 0 && c->chunk < B) ? static_cast<int>(c->chunk) : B;
 }
 
 static int forward_common(cid_ctx* c, int B, int H, int W, void* ws, size_t ws_bytes, cudaStream_t st,
                           const uint8_t* x, size_t x_img_bytes, uint8_t* y, size_t y_img_bytes, IoSpec io) {
-    CID_REQUIRE(c && c->finalized, "generator not finalized (call cid_set_param for all 24 tensors, then cid_finalize)");
+    CID_REQUIRE(c && c->finalized, "generator not finalized (call cid_set_param for every tensor, then cid_finalize)");
     CID_REQUIRE(B >= 1 && H >= 4 && W >= 4, "bad shape B=%d H=%d W=%d", B, H, W);
     CID_REQUIRE(H % 4 == 0 && W % 4 == 0, "network input %dx%d must be multiples of 4 (get_padding, app.py:276)", H,
                 W);
@@ -575,15 +590,16 @@ static int forward_common(cid_ctx* c, int B, int H, int W, void* ws, size_t ws_b
     DeviceGuard g(c->device);
     CID_REQUIRE(g.ok, "cannot select CUDA device %d", c->device);
     const int Bc = chunk_of(c, B);
-    const size_t need = layout_offsets(Bc, H, W, nullptr);
+    const bool cgan = c->model == CID_MODEL_KERAS_CGAN;
+    const size_t need = cgan ? cgan_layout_offsets(Bc, H, W, nullptr) : layout_offsets(Bc, H, W, nullptr);
     CID_REQUIRE(ws_bytes >= need, "workspace too small: %zu < %zu bytes", ws_bytes, need);
     cid_plan* pl = nullptr;
-    if (get_plan(c, Bc, H, W, ws, &pl)) return 1;
+    if (cgan ? cgan_get_plan(c, Bc, H, W, ws, &pl) : get_plan(c, Bc, H, W, ws, &pl)) return 1;
     for (int b0 = 0; b0 < B; b0 += Bc) {
         const int nb = std::min(Bc, B - b0);
         io.x = x + static_cast<size_t>(b0) * x_img_bytes;
         io.y = y + static_cast<size_t>(b0) * y_img_bytes;
-        if (run_layers(c, pl, nb, io, st)) return 1;
+        if (cgan ? cgan_run_layers(c, pl, nb, io, st) : run_layers(c, pl, nb, io, st)) return 1;
     }
     return 0;
 }
@@ -597,12 +613,19 @@ using namespace cid;
 // =============================================================================================
 extern "C" {
 
-int cid_version(void) { return 1; }
+int cid_version(void) { return 2; }
 
 const char* cid_last_error(void) { return g_err; }
 
-int cid_create(int device, cid_handle* out) {
+int cid_create(int device, cid_handle* out) { return cid_create_model(device, "denoise", out); }
+
+int cid_create_model(int device, const char* model, cid_handle* out) {
     CID_REQUIRE(out, "cid_create: out is NULL");
+    CID_REQUIRE(model, "cid_create_model: model is NULL");
+    int kind = -1;
+    if (!strcmp(model, "denoise")) kind = CID_MODEL_DENOISE;
+    if (!strcmp(model, "keras_cgan")) kind = CID_MODEL_KERAS_CGAN;
+    CID_REQUIRE(kind >= 0, "unknown model '%s' (denoise | keras_cgan)", model);
     *out = nullptr;
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
@@ -615,6 +638,7 @@ int cid_create(int device, cid_handle* out) {
                 prop.major, prop.minor);
     cid_ctx* c = new cid_ctx();
     c->device = device;
+    c->model = kind;
     c->num_sms = prop.multiProcessorCount;
     c->max_smem = static_cast<int>(prop.sharedMemPerBlockOptin);
     *out = c;
@@ -636,6 +660,25 @@ int cid_destroy(cid_handle h) {
 int cid_set_param(cid_handle h, const char* key, const float* data, const int64_t* shape, int ndim) {
     CID_REQUIRE(h && key && data && shape, "cid_set_param: null argument");
     const std::string k(key);
+    if (h->model == CID_MODEL_KERAS_CGAN) {
+        int64_t expect[4];
+        const int en = cgan_param_shape(k, expect);
+        CID_REQUIRE(en > 0, "unknown variable '%s' for the keras_cgan generator", key);
+        CID_REQUIRE(ndim == en, "%s: expected %d dims, got %d", key, en, ndim);
+        size_t n = 1;
+        for (int i = 0; i < en; ++i) {
+            CID_REQUIRE(shape[i] == expect[i], "%s: dim %d is %lld, expected %lld", key, i,
+                        static_cast<long long>(shape[i]), static_cast<long long>(expect[i]));
+            n *= static_cast<size_t>(shape[i]);
+        }
+        DeviceGuard g(h->device);
+        CID_REQUIRE(g.ok, "cannot select CUDA device %d", h->device);
+        std::vector<float> v(n);
+        CID_CHECK_CUDA(cudaMemcpy(v.data(), data, n * 4, cudaMemcpyDefault));
+        h->params[k] = std::move(v);
+        h->finalized = false;
+        return 0;
+    }
     const size_t dot = k.rfind('.');
     CID_REQUIRE(dot != std::string::npos, "unknown parameter key '%s'", key);
     const std::string lname = k.substr(0, dot), what = k.substr(dot + 1);
@@ -677,8 +720,13 @@ int cid_finalize(cid_handle h) {
     DeviceGuard g(h->device);
     CID_REQUIRE(g.ok, "cannot select CUDA device %d", h->device);
     CID_CHECK_CUDA(cudaDeviceSynchronize());  // no forward may still be reading the old packed weights
-    for (int l = 0; l < 12; ++l)
-        if (pack_layer(h, l)) return 1;
+    if (h->model == CID_MODEL_KERAS_CGAN) {
+        if (cgan_pack(h)) return 1;
+    } else {
+        for (int l = 0; l < 12; ++l)
+            if (pack_layer(h, l)) return 1;
+    }
+    h->plans.clear();
     h->finalized = true;
     return 0;
 }
@@ -717,12 +765,26 @@ int cid_workspace_bytes(cid_handle h, int B, int H, int W, size_t* bytes) {
     CID_REQUIRE(h && bytes, "cid_workspace_bytes: null argument");
     CID_REQUIRE(B >= 1 && H >= 4 && W >= 4, "bad shape B=%d H=%d W=%d", B, H, W);
     CID_REQUIRE(H % 4 == 0 && W % 4 == 0, "network input %dx%d must be multiples of 4 (get_padding, app.py:276)", H, W);
-    *bytes = layout_offsets(chunk_of(h, B), H, W, nullptr);
+    *bytes = h->model == CID_MODEL_KERAS_CGAN ? cgan_layout_offsets(chunk_of(h, B), H, W, nullptr)
+                                              : layout_offsets(chunk_of(h, B), H, W, nullptr);
     return 0;
+}
+
+int cid_forward_f32_nhwc(cid_handle h, const float* x, float* y, int B, int H, int W, void* ws, size_t ws_bytes,
+                         void* stream) {
+    CID_REQUIRE(h && h->model == CID_MODEL_KERAS_CGAN, "cid_forward_f32_nhwc is the keras_cgan generator's entry point");
+    IoSpec io;
+    memset(&io, 0, sizeof(io));
+    io.u8 = false;
+    const size_t img = static_cast<size_t>(3) * H * W * 4;
+    return forward_common(h, B, H, W, ws, ws_bytes, static_cast<cudaStream_t>(stream),
+                          reinterpret_cast<const uint8_t*>(x), img, reinterpret_cast<uint8_t*>(y), img, io);
 }
 
 int cid_forward_f32_nchw(cid_handle h, const float* x, float* y, int B, int H, int W, void* ws, size_t ws_bytes,
                          void* stream) {
+    CID_REQUIRE(h && h->model == CID_MODEL_DENOISE, "cid_forward_f32_nchw is the denoise generator's entry point "
+                                                    "(keras_cgan: cid_forward_f32_nhwc)");
     IoSpec io;
     memset(&io, 0, sizeof(io));
     io.u8 = false;
@@ -755,11 +817,12 @@ int cid_profile_read(cid_handle h, double* layer_ms, int64_t* passes) {
     CID_REQUIRE(g.ok, "cannot select CUDA device %d", h->device);
     CID_CHECK_CUDA(cudaDeviceSynchronize());
     for (int l = 0; l < 12; ++l) layer_ms[l] = 0.0;
-    const size_t n = h->prof_used / 13;
+    const int nl = h->model == CID_MODEL_KERAS_CGAN ? 5 : 12;
+    const size_t n = h->prof_used / (nl + 1);
     for (size_t i = 0; i < n; ++i)
-        for (int l = 0; l < 12; ++l) {
+        for (int l = 0; l < nl; ++l) {
             float ms = 0.f;
-            CID_CHECK_CUDA(cudaEventElapsedTime(&ms, h->prof_events[i * 13 + l], h->prof_events[i * 13 + l + 1]));
+            CID_CHECK_CUDA(cudaEventElapsedTime(&ms, h->prof_events[i * (nl + 1) + l], h->prof_events[i * (nl + 1) + l + 1]));
             layer_ms[l] += ms;
         }
     *passes = static_cast<int64_t>(n);
@@ -770,6 +833,27 @@ int cid_profile_read(cid_handle h, double* layer_ms, int64_t* passes) {
 int cid_debug_copy_activation(cid_handle h, const char* name, const void* ws, int B, int H, int W, void* dst_host,
                               size_t dst_bytes, int* channels, int* height, int* width) {
     CID_REQUIRE(h && name && ws && dst_host, "cid_debug_copy_activation: null argument");
+    if (h->model == CID_MODEL_KERAS_CGAN) {
+        static const char* names[CB_COUNT] = {"c0", "c1", "c2", "c3"};
+        int b = -1;
+        for (int i = 0; i < CB_COUNT; ++i)
+            if (!strcmp(name, names[i])) b = i;
+        CID_REQUIRE(b >= 0, "unknown activation '%s'", name);
+        DeviceGuard g(h->device);
+        CID_REQUIRE(g.ok, "cannot select CUDA device %d", h->device);
+        const int Bc = chunk_of(h, B);
+        size_t off[CB_COUNT];
+        cgan_layout_offsets(Bc, H, W, off);
+        const int lv = kCganBufLevel[b];
+        const size_t n = static_cast<size_t>(Bc) * (H >> lv) * (W >> lv) * kCganBufC[b] * 2;
+        CID_REQUIRE(dst_bytes >= n, "destination too small: %zu < %zu", dst_bytes, n);
+        CID_CHECK_CUDA(cudaDeviceSynchronize());
+        CID_CHECK_CUDA(cudaMemcpy(dst_host, static_cast<const uint8_t*>(ws) + off[b], n, cudaMemcpyDeviceToHost));
+        if (channels) *channels = kCganBufC[b];
+        if (height) *height = H >> lv;
+        if (width) *width = W >> lv;
+        return 0;
+    }
     int b = -1;
     for (int i = 0; i < B_COUNT; ++i)
         if (!strcmp(name, kBufNames[i])) b = i;

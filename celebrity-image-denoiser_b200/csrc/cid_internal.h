@@ -59,8 +59,11 @@ struct cid_plan {
     CUtensorMap tmO2[12];   // pooled output (box 64ch x 4px x 8 rows); layers 1 and 3 only
 };
 
+enum { CID_MODEL_DENOISE = 0, CID_MODEL_KERAS_CGAN = 1 };
+
 struct cid_ctx {
     int device = 0;
+    int model = CID_MODEL_DENOISE;
     int num_sms = 0;
     int max_smem = 0;
     int64_t launches = 0;

@@ -28,7 +28,9 @@
 
 namespace cid {
 
-enum : int { EPI_RELU = 0, EPI_RELU_POOL = 1, EPI_CONVT = 2, EPI_TANH_F32 = 3, EPI_TANH_U8 = 4 };  // TANH_*: last_conv_umma.cuh
+enum : int {  // TANH_*: last_conv_umma.cuh; LRELU/T4: the Keras cGAN layers (leaky ReLU with ConvParams::slope)
+    EPI_RELU = 0, EPI_RELU_POOL = 1, EPI_CONVT = 2, EPI_TANH_F32 = 3, EPI_TANH_U8 = 4, EPI_LRELU = 5, EPI_T4 = 6, EPI_TANH_F32_NHWC = 7
+};
 
 constexpr int kConvThreads = 320;  // warp 0 TMA, warp 1 MMA, warps 2..9 two epilogue groups
 constexpr int kMaxStages = 8;
@@ -49,13 +51,22 @@ struct ConvParams {
     void* out2;          // EPI_RELU_POOL: pooled output buffer
     int out2_cs, out2_c0;
     int crop_l, crop_t, out_h, out_w;  // EPI_TANH_U8: crop window into the u8 NHWC result
+    float slope;         // EPI_LRELU / EPI_T4: negative slope of the leaky ReLU
     int debug_flags;     // bring-up experiments only: 1 = epilogue skips global stores, 2 = skips TMEM reads too
 };
 
-// PW = 0: one TMA box per horizontal tap (8 px wide, 1024-B row groups).
-// PW = 10: one halo patch {64 ch, 10 px, 18 rows} per K block; tap (dy,dx) is the same patch read at
-//          start + (dy*PW + dx)*128 B with SBO = PW*128 B (relies on the 128-B swizzle being a
-//          function of the absolute shared-memory address, for TMA writes and UMMA reads alike).
+// Tap geometry (TAPS):
+//   9  = 3x3, pad 1: one halo patch {64 ch, PW=10 px, 18 rows} per K block; tap (dy,dx) is the same patch
+//        read at start + (dy*PW + dx)*128 B with SBO = PW*128 B (relies on the 128-B swizzle being a function
+//        of the absolute shared-memory address, for TMA writes and UMMA reads alike).
+//   1  = 1x1 (the 2x2-stride-2 transposed conv as a GEMM): one box {64 ch, 8 px, 16 rows}.
+//   16 = 4x4 stride 2 pad 1 (Keras Conv2D k4 s2 'same'): a K block is (64 input channels, input phase
+//        (phy,phx)); its patch {64 ch, PW=9 px, 17 rows} is a STRIDE-2 TMA box starting at input pixel
+//        (2*y0-1+phy, 2*x0-1+phx) and serves the 4 taps ky = 2*dy+phy, kx = 2*dx+phx (dy,dx in {0,1}).
+//   8  = 4x4 stride 2 pad 1 TRANSPOSED (Keras Conv2DTranspose k4 s2 'same'): the work item's n_tile is the
+//        output row phase py; the accumulator holds both column phases px (2*N columns). Output
+//        (2y+py, 2x+px) sums input (y-1+ty, x-1+tx) * w[ky = py+3-2ty, kx = px+3-2tx] over ty in {py,py+1}
+//        and the (tx,px) pairs (0,0) (1,0) (1,1) (2,1): 8 MMA steps of width N over the 3x3 halo patch.
 // CG = 2: CTA pairs (cluster of 2, tcgen05 cta_group::2). Each CTA owns its own S pixel tiles (A operand,
 //         accumulators, epilogue) but only HALF of every weight tile (N/2 rows); the leader CTA's MMAs
 //         read both halves, so the per-SM shared-memory traffic of the B operand is halved.
@@ -63,19 +74,23 @@ template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0, int TS = 0, in
 struct ConvCfg {
     static_assert(CG == 1 || CG == 2, "single CTA or CTA pair");
     static_assert(CG == 1 || N % 32 == 0, "pair mode: each CTA holds N/2 weight rows, N multiple of 16 for M=256");
-    static_assert(TAPS == 9 || TAPS == 1, "3x3 or 1x1");
+    static_assert(TAPS == 9 || TAPS == 1 || TAPS == 16 || TAPS == 8, "3x3, 1x1, 4x4 s2 or transposed 4x4 s2");
     static_assert(N % 16 == 0 && N >= 16 && N <= 256, "UMMA N for M=128");
-    static_assert(2 * S * N <= 512, "two accumulator buffers must fit TMEM");
-    static constexpr int DX = TAPS == 9 ? 3 : 1;
+    static constexpr bool K4 = TAPS == 16, T4 = TAPS == 8;
+    static_assert(!(K4 || T4) || !WRES, "4x4 layers stream their weights");
+    static constexpr int DX = (TAPS == 9 || T4) ? 3 : K4 ? 2 : 1;
     static constexpr int DY = DX;
-    static_assert(PW == 0 || TAPS == 9, "halo patches only for 3x3");
-    static constexpr int A_ROWS = TAPS == 9 ? 18 : 16;
-    static constexpr int A_LOADS = PW ? 1 : DX;                 // TMA boxes per K block per tile
+    static_assert(PW == (DX == 1 ? 0 : 8 + DX - 1), "patch width = 8 + DX - 1 (0 = plain box for 1x1)");
+    static constexpr int STEPS = TAPS == 9 ? 9 : K4 ? 4 : T4 ? 8 : 1;  // weight tiles (MMA steps) per K block
+    static constexpr int KSUB = K4 ? 4 : 1;                            // K blocks per 64 input channels
+    static constexpr int A_ROWS = 16 + DY - 1;
     static constexpr int A_TX = (PW ? PW : 8) * A_ROWS * 128;   // bytes one box delivers
     static constexpr int A_BYTES = (A_TX + 1023) / 1024 * 1024; // stage pitch (1024-B aligned)
     static constexpr int SBO = (PW ? PW : 8) * 128;
     static constexpr int W_BYTES = (N / CG) * 128;  // this CTA's share of one weight tile
-    static constexpr int ACC_COLS = S * N;
+    static constexpr int NACC = T4 ? 2 * N : N;     // accumulator columns per pixel tile
+    static constexpr int ACC_COLS = S * NACC;
+    static_assert(2 * ACC_COLS <= 512, "two accumulator buffers must fit TMEM");
     static constexpr int TMEM_COLS = (2 * ACC_COLS <= 32)    ? 32
                                      : (2 * ACC_COLS <= 64)  ? 64
                                      : (2 * ACC_COLS <= 128) ? 128
@@ -87,13 +102,39 @@ struct ConvCfg {
     static constexpr int NOB = 1;  // staging buffers per group (the other group's buffer gives the overlap)
     static constexpr int O_SLAB = 128 * 128;
     static constexpr int O2_SLAB = 32 * 128;
-    static constexpr int OT_SLAB = 256 * 128;  // EPI_CONVT: [16 rows][16 px][64 ch] of the 2x-upsampled output
+    static constexpr int OT_SLAB = 256 * 128;  // transposed convs: [16 rows][16 px][64 ch] of the 2x-upsampled output
     static constexpr int O_GROUP = NOB * (O_SLAB + (EPI == EPI_RELU_POOL ? O2_SLAB : 0));
-    static constexpr int O_BYTES = EPI == EPI_CONVT ? 2 * OT_SLAB : 2 * O_GROUP;
+    static constexpr int O_BYTES = (EPI == EPI_CONVT || EPI == EPI_T4) ? 2 * OT_SLAB : 2 * O_GROUP;
     // dynamic shared memory needed (bytes), including 1 KB of alignment slack
     static int smem_bytes(int kb_count, int a_stages, int w_stages) {
         int w_items = WRES ? kb_count * TAPS : w_stages;
         return 1024 + w_items * W_BYTES + a_stages * A_BYTES + O_BYTES + 512;
+    }
+};
+
+// One MMA step of a K block: which patch offset it reads, which packed weight rows it uses, which accumulator
+// columns it feeds. `sub` = the K block's input phase (K4) ; `nt` = the work item's n_tile (T4: row phase py).
+template <int N, int TAPS, int PW>
+struct StepMap {
+    int a_px;      // patch pixel offset of the tap (x 128 B)
+    int w_tap;     // tap index into the packed weights (rows w_tap * w_rows_per_tap ...)
+    int d_col;     // accumulator column offset inside the tile
+    bool first;    // first MMA step into its accumulator columns within a K block 0
+    __device__ __forceinline__ StepMap(int step, int sub, int nt) {
+        if constexpr (TAPS == 9) {
+            const int dx = step / 3, dy = step - dx * 3;
+            a_px = dy * PW + dx; w_tap = dy * 3 + dx; d_col = 0; first = step == 0;
+        } else if constexpr (TAPS == 16) {
+            const int dy = step >> 1, dx = step & 1;
+            a_px = dy * PW + dx; w_tap = (2 * dy + (sub >> 1)) * 4 + 2 * dx + (sub & 1); d_col = 0; first = step == 0;
+        } else if constexpr (TAPS == 8) {
+            const int ty = nt + (step >> 2), q = step & 3;
+            const int tx = (q + 1) >> 1, px = q >> 1;
+            a_px = ty * PW + tx; w_tap = (nt + 3 - 2 * ty) * 4 + (px + 3 - 2 * tx); d_col = px * N;
+            first = (step == 0 || step == 2);
+        } else {
+            a_px = 0; w_tap = 0; d_col = 0; first = true;
+        }
     }
 };
 
@@ -159,9 +200,9 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                  const ConvParams p) {
     using Cfg = ConvCfg<N, TAPS, S, WRES, EPI, PW, TS, CG>;
     constexpr bool PAIR = CG == 2;
-    constexpr int DX = Cfg::DX, DY = Cfg::DY, AL = Cfg::A_LOADS;
-    constexpr int DXI = PW ? DX : 1;  // horizontal taps served by one A box
+    constexpr int STEPS = Cfg::STEPS, KSUB = Cfg::KSUB;
     constexpr int A_BYTES = Cfg::A_BYTES, W_BYTES = Cfg::W_BYTES;
+    using Step = StepMap<N, TAPS, PW>;
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -246,44 +287,44 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         load_w(w_smem + (kb * TAPS + tap) * W_BYTES, &w_full[0], kb * 64, tap * p.w_rows_per_tap);
             }
             uint32_t a_stage = 0, a_phase = 0, w_stage = 0, w_phase = 0;
+            const int kb_total = p.kb_count * KSUB;
             for (int work = unit; work < p.num_work; work += units) {
                 const int n_tile = work % p.n_tiles;
                 const int st = work / p.n_tiles;
                 TileCoord tc[S];
 #pragma unroll
                 for (int s = 0; s < S; ++s) tc[s] = decode_tile(p, (st * CG + static_cast<int>(rank)) * S + s);
-                for (int kb = 0; kb < p.kb_count; ++kb) {
-                    for (int al = 0; al < AL; ++al) {
+                for (int kb = 0; kb < kb_total; ++kb) {
+                    const int cb = kb / KSUB, sub = kb % KSUB;  // 64-channel block, input phase (4x4 s2 only)
 #pragma unroll
-                        for (int s = 0; s < S; ++s) {
-                            mbar_wait(&a_empty[a_stage], a_phase ^ 1);
-                            expect(&a_full[a_stage], Cfg::A_TX);
-                            if (PAIR)
-                                tma_load_4d_cg2(a_smem + a_stage * A_BYTES, &tmA, full_bar(&a_full[a_stage]), kb * 64,
-                                                tc[s].x0 + (PW ? 0 : al) - (DX == 3 ? 1 : 0),
-                                                tc[s].y0 - (DY == 3 ? 1 : 0), tc[s].b, kEvictNormal);
-                            else
-                                tma_load_4d(a_smem + a_stage * A_BYTES, &tmA, &a_full[a_stage], kb * 64,
-                                            tc[s].x0 + (PW ? 0 : al) - (DX == 3 ? 1 : 0),
-                                            tc[s].y0 - (DY == 3 ? 1 : 0), tc[s].b, kEvictNormal);
-                            if (++a_stage == static_cast<uint32_t>(AST)) {
-                                a_stage = 0;
-                                a_phase ^= 1;
-                            }
+                    for (int s = 0; s < S; ++s) {
+                        // patch origin in the A tensor: 3x3 / transposed 4x4 halo starts one pixel up-left;
+                        // 4x4 s2 reads input phase (phy,phx) of the 2x larger input through a stride-2 box
+                        const int ax = Cfg::K4 ? 2 * tc[s].x0 - 1 + (sub & 1) : tc[s].x0 - (Cfg::DX == 3 ? 1 : 0);
+                        const int ay = Cfg::K4 ? 2 * tc[s].y0 - 1 + (sub >> 1) : tc[s].y0 - (Cfg::DY == 3 ? 1 : 0);
+                        mbar_wait(&a_empty[a_stage], a_phase ^ 1);
+                        expect(&a_full[a_stage], Cfg::A_TX);
+                        if (PAIR)
+                            tma_load_4d_cg2(a_smem + a_stage * A_BYTES, &tmA, full_bar(&a_full[a_stage]), cb * 64, ax, ay,
+                                            tc[s].b, kEvictNormal);
+                        else
+                            tma_load_4d(a_smem + a_stage * A_BYTES, &tmA, &a_full[a_stage], cb * 64, ax, ay, tc[s].b,
+                                        kEvictNormal);
+                        if (++a_stage == static_cast<uint32_t>(AST)) {
+                            a_stage = 0;
+                            a_phase ^= 1;
                         }
-                        if (!WRES) {
-                            for (int dxi = 0; dxi < DXI; ++dxi) {
-                                const int dx = PW ? dxi : al;
-                                for (int dy = 0; dy < DY; ++dy) {
-                                    mbar_wait(&w_empty[w_stage], w_phase ^ 1);
-                                    expect(&w_full[w_stage], W_BYTES);
-                                    load_w(w_smem + w_stage * W_BYTES, &w_full[w_stage], kb * 64,
-                                           (dy * DX + dx) * p.w_rows_per_tap + n_tile * N);
-                                    if (++w_stage == static_cast<uint32_t>(WST)) {
-                                        w_stage = 0;
-                                        w_phase ^= 1;
-                                    }
-                                }
+                    }
+                    if (!WRES) {
+                        for (int step = 0; step < STEPS; ++step) {
+                            const Step sm(step, sub, n_tile);
+                            mbar_wait(&w_empty[w_stage], w_phase ^ 1);
+                            expect(&w_full[w_stage], W_BYTES);
+                            load_w(w_smem + w_stage * W_BYTES, &w_full[w_stage], cb * 64,
+                                   sm.w_tap * p.w_rows_per_tap + (Cfg::T4 ? 0 : n_tile * N));
+                            if (++w_stage == static_cast<uint32_t>(WST)) {
+                                w_stage = 0;
+                                w_phase ^= 1;
                             }
                         }
                     }
@@ -326,63 +367,58 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             wait_full(&acc_empty[buf], aph ^ 1);
             tc_fence_after();
             const uint32_t d_base = tmem_base + buf * Cfg::ACC_COLS;
-            for (int kb = 0; kb < p.kb_count; ++kb) {
-                for (int al = 0; al < AL; ++al) {
-                    uint32_t stg[S];
+            const int n_tile = work % p.n_tiles;
+            const int kb_total = p.kb_count * KSUB;
+            for (int kb = 0; kb < kb_total; ++kb) {
+                const int sub = kb % KSUB;
+                uint32_t stg[S];
 #pragma unroll
-                    for (int s = 0; s < S; ++s) {
-                        wait_full(&a_full[a_stage], a_phase);
-                        stg[s] = a_stage;
-                        if (++a_stage == static_cast<uint32_t>(AST)) {
-                            a_stage = 0;
-                            a_phase ^= 1;
-                        }
+                for (int s = 0; s < S; ++s) {
+                    wait_full(&a_full[a_stage], a_phase);
+                    stg[s] = a_stage;
+                    if (++a_stage == static_cast<uint32_t>(AST)) {
+                        a_stage = 0;
+                        a_phase ^= 1;
                     }
-                    tc_fence_after();
+                }
+                tc_fence_after();
 #pragma unroll
-                    for (int dxi = 0; dxi < DXI; ++dxi) {
-                        const int dx = PW ? dxi : al;
-#pragma unroll
-                        for (int dy = 0; dy < DY; ++dy) {
-                            uint32_t w_lo;
-                            if (WRES) {
-                                w_lo = w_lo0 + static_cast<uint32_t>(kb * TAPS + dy * DX + dx) * (W_BYTES >> 4);
-                            } else {
-                                wait_full(&w_full[w_stage], w_phase);
-                                tc_fence_after();
-                                w_lo = w_lo0 + w_stage * (W_BYTES >> 4);
-                            }
-                            const uint32_t first = (kb == 0 && dx == 0 && dy == 0) ? 1u : 0u;
-                            if (elect_one()) {
-#pragma unroll
-                                for (int s = 0; s < S; ++s) {
-                                    // tap (dy,dx): PW=0 -> box dx, rows shifted by dy groups of 1024 B;
-                                    //              PW>0 -> patch pixel offset dy*PW+dx, 128 B each
-                                    const uint32_t a_lo = a_lo0 + stg[s] * (A_BYTES >> 4) +
-                                                          (PW ? (dy * PW + dxi) * (128 >> 4) : dy * (1024 >> 4));
-#pragma unroll
-                                    for (int k = 0; k < 4; ++k) {
-                                        mma(d_base + s * N, umma_desc_join<Cfg::SBO>(a_lo + 2 * k),
-                                            umma_desc_join<1024>(w_lo + 2 * k), (first && k == 0) ? 0u : 1u);
-                                    }
-                                }
-                                if (!WRES) commit(&w_empty[w_stage]);
-                            }
-                            __syncwarp();
-                            if (!WRES) {
-                                if (++w_stage == static_cast<uint32_t>(WST)) {
-                                    w_stage = 0;
-                                    w_phase ^= 1;
-                                }
-                            }
-                        }
+                for (int step = 0; step < STEPS; ++step) {
+                    const Step sm(step, sub, n_tile);
+                    uint32_t w_lo;
+                    if (WRES) {
+                        w_lo = w_lo0 + static_cast<uint32_t>(kb * TAPS + sm.w_tap) * (W_BYTES >> 4);
+                    } else {
+                        wait_full(&w_full[w_stage], w_phase);
+                        tc_fence_after();
+                        w_lo = w_lo0 + w_stage * (W_BYTES >> 4);
                     }
+                    const uint32_t first = (kb == 0 && sm.first) ? 1u : 0u;
                     if (elect_one()) {
 #pragma unroll
-                        for (int s = 0; s < S; ++s) commit(&a_empty[stg[s]]);
+                        for (int s = 0; s < S; ++s) {
+                            const uint32_t a_lo = a_lo0 + stg[s] * (A_BYTES >> 4) + sm.a_px * (128 >> 4);
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                mma(d_base + s * Cfg::NACC + sm.d_col, umma_desc_join<Cfg::SBO>(a_lo + 2 * k),
+                                    umma_desc_join<1024>(w_lo + 2 * k), (first && k == 0) ? 0u : 1u);
+                            }
+                        }
+                        if (!WRES) commit(&w_empty[w_stage]);
                     }
                     __syncwarp();
+                    if (!WRES) {
+                        if (++w_stage == static_cast<uint32_t>(WST)) {
+                            w_stage = 0;
+                            w_phase ^= 1;
+                        }
+                    }
                 }
+                if (elect_one()) {
+#pragma unroll
+                    for (int s = 0; s < S; ++s) commit(&a_empty[stg[s]]);
+                }
+                __syncwarp();
             }
             if (elect_one()) commit(&acc_full[buf]);
             __syncwarp();
@@ -412,10 +448,16 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             tc_fence_after();
             const uint32_t tbase = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * Cfg::ACC_COLS;
             if (!(p.debug_flags & 2)) {
-                if constexpr (EPI == EPI_RELU || EPI == EPI_RELU_POOL) {
+                if constexpr (EPI == EPI_RELU || EPI == EPI_RELU_POOL || EPI == EPI_LRELU) {
                     constexpr int SL = N / 64;  // 64-channel slabs per pixel tile
                     const int sub = (xl & 1) | ((yl & 1) << 1);
                     const int prow_i = (yl >> 1) * 4 + (xl >> 1);
+                    const float slope = p.slope;
+                    auto act = [&](float x) {  // ReLU, or LeakyReLU(slope) for the Keras layers
+                        if constexpr (EPI == EPI_LRELU) return x > 0.f ? x : x * slope;
+                        return fmaxf(x, 0.f);
+                    };
+                    (void)slope;
 #pragma unroll
                     for (int j = 0; j < S * SL; ++j) {
                         if ((j & 1) != g) continue;
@@ -427,16 +469,16 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         // the store that used this buffer NOB slabs ago must have finished READING it
                         if (issuer) bulk_wait_read<Cfg::NOB - 1>();
                         named_bar_sync(bar_id, 128);
-                        for_each_chunk<2>(tbase + s * N + cs * 64, [&](int ch, uint32_t (&v)[32]) {
+                        for_each_chunk<2>(tbase + s * Cfg::NACC + cs * 64, [&](int ch, uint32_t (&v)[32]) {
                             const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_tile * N + cs * 64 + ch * 32);
                             uint32_t pk[16];
 #pragma unroll
                             for (int jj = 0; jj < 8; ++jj) {
                                 const float4 bb = __ldg(b4 + jj);
-                                const float f0 = fmaxf(__uint_as_float(v[4 * jj + 0]) + bb.x, 0.f);
-                                const float f1 = fmaxf(__uint_as_float(v[4 * jj + 1]) + bb.y, 0.f);
-                                const float f2 = fmaxf(__uint_as_float(v[4 * jj + 2]) + bb.z, 0.f);
-                                const float f3 = fmaxf(__uint_as_float(v[4 * jj + 3]) + bb.w, 0.f);
+                                const float f0 = act(__uint_as_float(v[4 * jj + 0]) + bb.x);
+                                const float f1 = act(__uint_as_float(v[4 * jj + 1]) + bb.y);
+                                const float f2 = act(__uint_as_float(v[4 * jj + 2]) + bb.z);
+                                const float f3 = act(__uint_as_float(v[4 * jj + 3]) + bb.w);
                                 pk[2 * jj + 0] = pack_bf16x2(f0, f1);
                                 pk[2 * jj + 1] = pack_bf16x2(f2, f3);
                             }
@@ -473,6 +515,59 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             bulk_commit();
                         }
                         ++o_count;
+                    }
+                } else if constexpr (EPI == EPI_T4) {
+                    // ---- transposed 4x4 s2: the tile's accumulator is [px][N] for output row phase py = n_tile.
+                    // Slab (s, cs) = channels [64cs, 64cs+64) of tile s, both px: [16 y][16 px][64 ch] of output
+                    // rows 2y+py, one 5-D TMA store over (C, 2W, py, H, B). Slabs alternate between the groups.
+                    constexpr int SL = N / 64;
+                    const float slope = p.slope;
+#pragma unroll
+                    for (int j = 0; j < S * SL; ++j) {
+                        if ((j & 1) != g) continue;
+                        const int s = j / SL, cs = j % SL;
+                        const TileCoord tc = decode_tile(p, (st * CG + static_cast<int>(rank)) * S + s);
+                        uint8_t* slab = o_smem + g * Cfg::OT_SLAB;
+                        if (issuer) bulk_wait_read<0>();
+                        named_bar_sync(bar_id, 128);
+                        // chunk i: px = i >> 1, 32-channel half = i & 1
+                        auto chunk_of = [&](int i) { return ((i >> 1) * N + cs * 64 + (i & 1) * 32) >> 5; };
+                        for_each_chunk_mapped<4>(tbase + s * Cfg::NACC, chunk_of, [&](int ch, uint32_t (&v)[32]) {
+                            const int col = ch * 32;
+                            const int px = col >= N ? 1 : 0;
+                            const int c = col - px * N;  // channel of v[0]
+                            const float4* b4 = reinterpret_cast<const float4*>(p.bias + c);
+                            uint32_t pk[16];
+#pragma unroll
+                            for (int jj = 0; jj < 8; ++jj) {
+                                const float4 bb = __ldg(b4 + jj);
+                                float f0 = __uint_as_float(v[4 * jj + 0]) + bb.x;
+                                float f1 = __uint_as_float(v[4 * jj + 1]) + bb.y;
+                                float f2 = __uint_as_float(v[4 * jj + 2]) + bb.z;
+                                float f3 = __uint_as_float(v[4 * jj + 3]) + bb.w;
+                                f0 = f0 > 0.f ? f0 : f0 * slope;
+                                f1 = f1 > 0.f ? f1 : f1 * slope;
+                                f2 = f2 > 0.f ? f2 : f2 * slope;
+                                f3 = f3 > 0.f ? f3 : f3 * slope;
+                                pk[2 * jj + 0] = pack_bf16x2(f0, f1);
+                                pk[2 * jj + 1] = pack_bf16x2(f2, f3);
+                            }
+                            const int orow_i = yl * 16 + 2 * xl + px;
+                            uint8_t* rowp = slab + orow_i * 128;
+                            const int half = (c >> 5) & 1;
+#pragma unroll
+                            for (int jj = 0; jj < 4; ++jj) {
+                                const int cj = half * 4 + jj;
+                                st_shared_v4(rowp + ((cj ^ (orow_i & 7)) << 4), pk[4 * jj], pk[4 * jj + 1], pk[4 * jj + 2],
+                                             pk[4 * jj + 3]);
+                            }
+                        });
+                        fence_proxy_async();
+                        named_bar_sync(bar_id, 128);
+                        if (issuer && !(p.debug_flags & 1)) {
+                            tma_store_5d(&tmO, slab, p.out_c0 + cs * 64, 2 * tc.x0, n_tile, tc.y0, tc.b);
+                            bulk_commit();
+                        }
                     }
                 } else {
                     // ---- transposed conv: GEMM column n = quadrant*cout + c, quadrant = dy*2+dx. The tile's 8

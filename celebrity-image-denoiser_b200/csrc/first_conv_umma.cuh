@@ -13,7 +13,8 @@
 //
 // The A operand is the tile's 10 x 18 halo patch, one 16-byte K chunk per pixel, stored in the
 // un-swizzled K-major UMMA layout (8-row core matrices: rows 16 B apart, 8-row groups SBO = 160 B
-// apart = one patch row, the second K chunk LBO bytes away in an all-zero plane). Tap (dy,dx) is
+// apart = one patch row). The weights are split w = w_hi + w_lo too: the MMA's second K chunk re-reads
+// the SAME pixel chunk (LBO = 0) against [wlo_r wlo_g wlo_b 0 ...], i.e. x_hi*w_lo. Tap (dy,dx) is
 // the same patch read at start + (dy*10+dx)*16 B, so each input pixel is converted and written
 // to shared memory once per tile (180 writes) instead of 9 times.
 //
@@ -30,7 +31,7 @@ namespace cid {
 constexpr int kFirstThreads = 288;
 constexpr int kFirstStages = 8;
 constexpr int kFirstPlane = 180 * 16;          // one K chunk of the 10x18 patch
-constexpr int kFirstStageBytes = 2 * kFirstPlane;
+constexpr int kFirstStageBytes = kFirstPlane;
 constexpr int kFirstWBytes = 9 * 2 * 64 * 16;  // [tap][k chunk][cout][8 bf16]
 constexpr int kFirstOutBufs = 2;               // staged output slabs ([128 px][64 ch] bf16, SW128) in flight
 constexpr int kFirstSmem = 1024 + kFirstOutBufs * 16384 + kFirstWBytes + kFirstStages * kFirstStageBytes + 1024 + 32 + 256;
@@ -238,7 +239,7 @@ first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParam
 #pragma unroll
                     for (int dx = 0; dx < 3; ++dx) {
                         const int tap = dy * 3 + dx;
-                        umma_bf16_ss(tmem_base + buf * N, umma_desc_nosw(ab + (dy * 10 + dx) * 16, kFirstPlane, 160),
+                        umma_bf16_ss(tmem_base + buf * N, umma_desc_nosw(ab + (dy * 10 + dx) * 16, 0, 160),
                                      umma_desc_nosw(w0 + tap * 2048, 1024, 128), idesc, tap == 0 ? 0u : 1u);
                     }
                 umma_commit(&a_empty[stage]);

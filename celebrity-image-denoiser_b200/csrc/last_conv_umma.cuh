@@ -51,7 +51,7 @@ struct LastParams {
     int tiles_x, tiles_y, m_tiles;
     int stages;
     const float* bias;  // fp32 [3]
-    void* out;          // fp32 NCHW [B,3,H,W]   or   u8 NHWC [B,out_h,out_w,3]
+    void* out;          // fp32 NCHW [B,3,H,W], fp32 NHWC [B,H,W,3]   or   u8 NHWC [B,out_h,out_w,3]
     int crop_l, crop_t, out_h, out_w;  // u8 mode
 };
 
@@ -59,7 +59,7 @@ template <int EPI>
 __global__ void __launch_bounds__(kLastThreads, 1)
 last_conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                       const LastParams p) {
-    static_assert(EPI == EPI_TANH_F32 || EPI == EPI_TANH_U8, "final layer epilogues only");
+    static_assert(EPI == EPI_TANH_F32 || EPI == EPI_TANH_U8 || EPI == EPI_TANH_F32_NHWC, "final layer epilogues only");
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* w_smem = smem;
@@ -209,6 +209,12 @@ last_conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                     float* out = static_cast<float*>(p.out);
 #pragma unroll
                     for (int c = 0; c < 3; ++c) out[((static_cast<size_t>(tc.b) * 3 + c) * p.H + y) * p.W + x] = t[c];
+                } else if constexpr (EPI == EPI_TANH_F32_NHWC) {
+                    // Keras `predict` surface (backend/app.py:458): fp32 NHWC
+                    float* out = static_cast<float*>(p.out) + ((static_cast<size_t>(tc.b) * p.H + y) * p.W + x) * 3;
+                    out[0] = t[0];
+                    out[1] = t[1];
+                    out[2] = t[2];
                 } else {
                     // (y*0.5+0.5).clamp(0,1) then ToPILImage: mul(255) and a TRUNCATING byte cast
                     const int oy = y - p.crop_t, ox = x - p.crop_l;

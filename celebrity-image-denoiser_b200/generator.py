@@ -49,11 +49,12 @@ for _name, _spec, _last_relu in _BLOCKS:
 class _Engine:
     """One C-ABI handle (= one device) plus its cached workspace."""
 
-    def __init__(self, device_index: int):
+    def __init__(self, device_index: int, model: str = "denoise"):
         self.lib = _lib.load()
         self.device_index = device_index
+        self.model = model
         h = C.c_void_p()
-        _lib.check(self.lib.cid_create(device_index, C.byref(h)), "cid_create")
+        _lib.check(self.lib.cid_create_model(device_index, model.encode(), C.byref(h)), "cid_create_model")
         self.handle = h
         self.signature = None
         self._ws: Optional[torch.Tensor] = None
@@ -75,8 +76,8 @@ class _Engine:
         self._ws = None
         self._ws_key = None
 
-    def upload(self, state: Dict[str, torch.Tensor]):
-        for key, shape in STATE_DICT_SHAPES.items():
+    def upload(self, state: Dict[str, torch.Tensor], shapes: Optional[Dict[str, Tuple[int, ...]]] = None):
+        for key, shape in (shapes or STATE_DICT_SHAPES).items():
             t = state[key].detach()
             if t.dtype != torch.float32 or not t.is_contiguous():
                 t = t.float().contiguous()

@@ -12,19 +12,22 @@ from pathlib import Path
 _LIB_PATH = Path(__file__).resolve().parent / "csrc" / "libcid_b200.so"
 _lib = None
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 # name -> (restype, argtypes); mirrors include/cid_b200.h one to one
 _SIGNATURES = {
     "cid_version": (C.c_int, []),
     "cid_last_error": (C.c_char_p, []),
     "cid_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
+    "cid_create_model": (C.c_int, [C.c_int, C.c_char_p, C.POINTER(C.c_void_p)]),
     "cid_destroy": (C.c_int, [C.c_void_p]),
     "cid_set_param": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.POINTER(C.c_int64), C.c_int]),
     "cid_finalize": (C.c_int, [C.c_void_p]),
     "cid_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
     "cid_workspace_bytes": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t)]),
     "cid_forward_f32_nchw": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                       C.c_void_p, C.c_size_t, C.c_void_p]),
+    "cid_forward_f32_nhwc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                        C.c_void_p, C.c_size_t, C.c_void_p]),
     "cid_forward_u8_nhwc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                       C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),

@@ -40,6 +40,20 @@ const char* cid_last_error(void);
 int cid_create(int device, cid_handle* out);
 int cid_destroy(cid_handle h);
 
+/* Same, for a named generator of the reference's model registry (backend/app.py:319-345):
+ *   "denoise"     DenoiseGenerator (backend/app.py:39-103) — what cid_create makes.
+ *   "keras_cgan"  the Keras cGAN generator the reference loads with
+ *                 tf.keras.models.load_model("weights/cgan_epoch_500.keras") (backend/app.py:338-345;
+ *                 architecture backend/trainingcode/cgan_code/training5barrev.py:24-43).
+ * For "keras_cgan" cid_set_param takes the Keras variables under their Keras names and layouts:
+ *   conv2d.kernel [4,4,3,64]  conv2d.bias [64]  conv2d_1.kernel [4,4,64,128]  conv2d_1.bias [128]
+ *   batch_normalization{,_1,_2}.{gamma,beta,moving_mean,moving_variance} [128|128|64]
+ *   conv2d_transpose.kernel [4,4,128,128] (kh,kw,Cout,Cin)  conv2d_transpose.bias [128]
+ *   conv2d_transpose_1.kernel [4,4,64,128]  conv2d_transpose_1.bias [64]
+ *   conv2d_2.kernel [3,3,64,3]  conv2d_2.bias [3]
+ * and cid_finalize folds the inference BatchNormalization (eps 1e-3) into the weights. */
+int cid_create_model(int device, const char* model, cid_handle* out);
+
 /* Replaces `model.load_state_dict(new_state, strict=False)` (backend/app.py:272): hand over one
  * state_dict tensor. `key` is one of the 24 reference keys (down1.0.weight ... upconv1.2.bias,
  * backend/app.py:42-78); `data` is fp32, host or device memory, C-contiguous in the reference's
@@ -66,12 +80,20 @@ int cid_workspace_bytes(cid_handle h, int B, int H, int W, size_t* bytes);
 int cid_forward_f32_nchw(cid_handle h, const float* x, float* y, int B, int H, int W, void* ws, size_t ws_bytes,
                          void* stream);
 
+/* keras_cgan only. Replaces `y_np = KERAS_CGAN.predict(x_np)` (backend/app.py:458):
+ * x: device fp32 NHWC [B,H,W,3] in [-1,1]; y: device fp32 NHWC [B,H,W,3] = tanh output.
+ * H, W multiples of 4. */
+int cid_forward_f32_nhwc(cid_handle h, const float* x, float* y, int B, int H, int W, void* ws, size_t ws_bytes,
+                         void* stream);
+
 /* Replaces the whole denoise branch of the route between PIL decode and PIL encode
  * (backend/app.py:383-385 Pad, :401-406 ToTensor/Normalize, :433 net, :435 denorm+clamp,
  * :472 ToPILImage's truncating x255 cast, :474-480 crop).
  * x: device u8 NHWC [B,H,W,3] (the un-padded image); y: device u8 NHWC [B,H,W,3].
  * (pad_l,pad_t,pad_r,pad_b) is get_padding()'s tuple; H+pad_t+pad_b and W+pad_l+pad_r must be
- * multiples of 4. Workspace is sized for the PADDED dims. */
+ * multiples of 4. Workspace is sized for the PADDED dims.
+ * On a "keras_cgan" handle this is the keras branch of the same route (run_keras_cgan,
+ * backend/app.py:438-467: pad, /255, (x-0.5)/0.5, predict, *0.5+0.5, clip; then :472-480). */
 int cid_forward_u8_nhwc(cid_handle h, const uint8_t* x, uint8_t* y, int B, int H, int W, int pad_l, int pad_t,
                         int pad_r, int pad_b, void* ws, size_t ws_bytes, void* stream);
 
@@ -115,11 +137,14 @@ int64_t cid_kernel_launches(cid_handle h);
  * records 13 CUDA events on the caller's stream (one before each of the 12 layers and one after
  * the last). cid_profile_read synchronises the device, returns the summed milliseconds per layer
  * (layer_ms[12], order: down1.0 down1.2 down2.0 down2.2 bottleneck.0 bottleneck.2 up2 upconv2.0
- * upconv2.2 up1 upconv1.0 upconv1.2) and the number of passes since the previous read. */
+ * upconv2.2 up1 upconv1.0 upconv1.2) and the number of passes since the previous read.
+ * keras_cgan: 6 events per pass, layer_ms[0..4] = conv2d conv2d_1 conv2d_transpose conv2d_transpose_1
+ * conv2d_2 (layer_ms must still hold 12 doubles). */
 int cid_profile_read(cid_handle h, double* layer_ms, int64_t* passes);
 
 /* Test hook: copy one intermediate activation of the most recent forward (same B,H,W,ws) to host
- * as bf16 NHWC. name in {a0,cat1,p1,a2,cat2,p2,b0,b1,u2a,u2b,u1a}; *channels gets its C.
+ * as bf16 NHWC. name in {a0,cat1,p1,a2,cat2,p2,b0,b1,u2a,u2b,u1a} (keras_cgan: {c0,c1,c2,c3});
+ * *channels gets its C.
  * Synchronises the device. */
 int cid_debug_copy_activation(cid_handle h, const char* name, const void* ws, int B, int H, int W, void* dst_host,
                               size_t dst_bytes, int* channels, int* height, int* width);

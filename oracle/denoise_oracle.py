@@ -106,6 +106,8 @@ def forward_bf16_storage(sd: Dict[str, torch.Tensor], x: torch.Tensor) -> torch.
     when amplified weights (gain >= 3) make the net chaotic enough that bf16 storage alone exceeds the
     north-star tolerance against the fp32 reference."""
     w = {k: (_bf16(v) if k.endswith(".weight") else v) for k, v in sd.items()}
+    w0 = sd["down1.0.weight"]
+    w["down1.0.weight"] = _bf16(w0) + _bf16(w0 - _bf16(w0))  # first layer: weights kept as a hi+lo pair too
 
     def conv(t, name, relu=True, store=True):
         t = F.conv2d(t, w[name + ".weight"], w[name + ".bias"], padding=1)

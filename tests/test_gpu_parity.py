@@ -164,6 +164,8 @@ def test_each_layer_in_isolation(dev, gain, B, H, W):
     x = torch.rand(B, 3, H, W, generator=torch.Generator().manual_seed(17)) * 2 - 1
     y = net(x.to(dev)).cpu()
     w = {k: (v.to(torch.bfloat16).float() if k.endswith(".weight") else v) for k, v in sd.items()}
+    w0 = sd["down1.0.weight"]  # the first layer keeps its weights as a hi+lo bf16 pair, like its input
+    w["down1.0.weight"] = w0.to(torch.bfloat16).float() + (w0 - w0.to(torch.bfloat16).float()).to(torch.bfloat16).float()
     act = {n: net.debug_activation(n, (B, 3, H, W)).permute(0, 3, 1, 2).contiguous()
            for n in ("a0", "cat1", "p1", "a2", "cat2", "p2", "b0", "b1", "u2a", "u2b", "u1a")}
     d1, e1 = act["cat1"][:, :64], act["cat1"][:, 64:]
