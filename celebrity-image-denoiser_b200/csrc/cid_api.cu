@@ -406,7 +406,7 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
             CID_CHECK_CUDA(cudaFuncSetAttribute(first_conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
             c->attr_done |= (1u << 30);
         }
-        const int grid = std::min(fp.m_tiles, c->num_sms);
+        const int grid = std::min(fp.m_tiles, c->num_sms * ((c->debug_flags & 4) ? 1 : kFirstCtasPerSm));
         if (io.u8)
             first_conv_umma_kernel<true><<<grid, kFirstThreads, smem, st>>>(pl->tmO[0], fp);
         else

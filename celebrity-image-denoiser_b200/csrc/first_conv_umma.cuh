@@ -30,6 +30,7 @@ namespace cid {
 
 constexpr int kFirstThreads = 288;
 constexpr int kFirstStages = 8;
+constexpr int kFirstCtasPerSm = 2;               // latency-bound roles: two resident CTAs per SM (<= 113 registers)
 constexpr int kFirstPlane = 180 * 16;          // one K chunk of the 10x18 patch
 constexpr int kFirstStageBytes = kFirstPlane;
 constexpr int kFirstWBytes = 9 * 2 * 64 * 16;  // [tap][k chunk][cout][8 bf16]
@@ -81,7 +82,7 @@ struct TileWalk {
 };
 
 template <bool U8>
-__global__ void __launch_bounds__(kFirstThreads, 1)
+__global__ void __launch_bounds__(kFirstThreads, kFirstCtasPerSm)
 first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParams p) {
     constexpr int N = 64;
     extern __shared__ uint8_t smem_raw[];

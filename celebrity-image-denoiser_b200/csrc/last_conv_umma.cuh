@@ -19,8 +19,8 @@
 // The patch arrives by one TMA box load per tile exactly as in conv_umma_kernel (128-byte swizzle,
 // rows = patch pixels), which is already the canonical K-major UMMA layout for a B operand.
 //
-// Warps (224 threads): 0 = TMA producer, 1 = TMEM owner + MMA issuer, 4 = transposer, 2/3/5/6 =
-// pixel warps. The 27 used rows sit in TMEM lanes 0..26, i.e. in lane quarter 0, which only a warp
+// Warps (384 threads): 0 = TMA producer, 1 = TMEM owner + MMA issuer, 4 and 8 = transposers, 2/3/5/6 and
+// 7/9/10/11 = pixel warps: two (transposer, 4 pixel warps) groups take alternate tiles. The 27 used rows sit in TMEM lanes 0..26, i.e. in lane quarter 0, which only a warp
 // with (warp & 3) == 0 may read: reading one quarter instead of all 128 lanes cuts the TMEM
 // traffic 4x (TMEM reads are what bounded the four-quarter version of this kernel). The
 // transposer moves P (TMEM) to shared memory for tile i+1 while the pixel warps gather tile i.
@@ -29,8 +29,7 @@
 
 namespace cid {
 
-constexpr int kLastThreads = 224;
-constexpr int kLastTransposeWarp = 4;
+constexpr int kLastThreads = 384;  // warp 0 TMA, 1 MMA, 4 and 8 transposers, {2,3,5,6} and {7,9,10,11} pixel warps
 constexpr int kLastN = 192;                    // patch pixels per MMA (180 used)
 constexpr int kLastPatchTx = 10 * 18 * 128;    // bytes one patch box delivers
 constexpr int kLastStageBytes = kLastN * 128;  // stage pitch: the MMA reads 192 rows
@@ -38,9 +37,10 @@ constexpr int kLastWBytes = 128 * 128;         // [128 rows][64 ch] bf16
 constexpr int kLastSP = 196;                   // fp32 pitch of one P row in shared memory
 constexpr int kLastSBytes = 27 * kLastSP * 4;  // one P tile
 constexpr int kLastMaxStages = 7;
+constexpr int kLastGroups = 2;                 // tiles alternate between two (transposer, 4 pixel warps) groups
 
 __host__ __device__ constexpr int last_conv_smem(int stages) {
-    return 1024 + kLastWBytes + stages * kLastStageBytes + 2 * kLastSBytes + 320;
+    return 1024 + kLastWBytes + stages * kLastStageBytes + 2 * kLastGroups * kLastSBytes + 320;
 }
 
 // row of the packed weight matrix (= TMEM lane) that holds (tap, c)
@@ -64,16 +64,16 @@ last_conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* w_smem = smem;
     uint8_t* a_smem = smem + kLastWBytes;
-    float* s_smem = reinterpret_cast<float*>(a_smem + p.stages * kLastStageBytes);  // [2][27][kLastSP]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(s_smem) + 2 * kLastSBytes);
+    float* s_smem = reinterpret_cast<float*>(a_smem + p.stages * kLastStageBytes);  // [group][2][27][kLastSP]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(s_smem) + 2 * kLastGroups * kLastSBytes);
     uint64_t* a_full = bars;
     uint64_t* a_empty = bars + kLastMaxStages;
     uint64_t* w_full = bars + 2 * kLastMaxStages;
     uint64_t* acc_full = w_full + 1;
     uint64_t* acc_empty = acc_full + 2;
-    uint64_t* s_full = acc_empty + 2;
-    uint64_t* s_empty = s_full + 2;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_empty + 2);
+    uint64_t* s_full = acc_empty + 2;   // [group][2]
+    uint64_t* s_empty = s_full + 4;     // [group][2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_empty + 4);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -94,6 +94,8 @@ last_conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         for (int i = 0; i < 2; ++i) {
             mbar_init(&acc_full[i], 1);
             mbar_init(&acc_empty[i], 1);
+        }
+        for (int i = 0; i < 4; ++i) {
             mbar_init(&s_full[i], 1);
             mbar_init(&s_empty[i], 4);
         }
@@ -152,17 +154,21 @@ last_conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             }
             ++acc_it;
         }
-    } else if (warp == kLastTransposeWarp) {
-        // ======================= transposer: P rows (TMEM lanes 0..26) -> shared [27][kLastSP] ==========
+    } else if (warp == 4 || warp == 8) {
+        // ======================= transposers: P rows (TMEM lanes 0..26) -> shared [27][kLastSP] ==========
+        // Group g takes the tiles whose per-CTA index has parity g (= accumulator buffer g) and double-buffers
+        // its own P tiles, so the TMEM drain of tile i+2 overlaps the gather of tile i.
+        const uint32_t g = warp == 4 ? 0u : 1u;
         const bool row_used = lane < 27;
         uint32_t it = 0;
-        for (int mt = blockIdx.x; mt < p.m_tiles; mt += gridDim.x) {
-            const uint32_t buf = it & 1, ph = (it >> 1) & 1;
-            mbar_wait(&s_empty[buf], ph ^ 1);
-            mbar_wait(&acc_full[buf], ph);
+        for (int mt = blockIdx.x; mt < p.m_tiles; mt += gridDim.x, ++it) {
+            if ((it & 1) != g) continue;
+            const uint32_t k = it >> 1, sb = k & 1;
+            mbar_wait(&s_empty[g * 2 + sb], ((k >> 1) & 1) ^ 1);
+            mbar_wait(&acc_full[g], k & 1);
             tc_fence_after();
-            float* srow = s_smem + buf * (27 * kLastSP) + lane * kLastSP;
-            for_each_chunk<kLastN / 32>(tmem_base + buf * 256, [&](int ch, uint32_t (&v)[32]) {
+            float* srow = s_smem + (g * 2 + sb) * (27 * kLastSP) + lane * kLastSP;
+            for_each_chunk<kLastN / 32>(tmem_base + g * 256, [&](int ch, uint32_t (&v)[32]) {
                 if (row_used) {
 #pragma unroll
                     for (int j = 0; j < 8; ++j)
@@ -172,23 +178,25 @@ last_conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             tc_fence_before();
             __syncwarp();
             if (lane == 0) {
-                mbar_arrive(&acc_empty[buf]);  // TMEM buffer is free again
-                mbar_arrive(&s_full[buf]);     // release: the stores above are visible to the waiters
+                mbar_arrive(&acc_empty[g]);          // TMEM buffer is free again
+                mbar_arrive(&s_full[g * 2 + sb]);    // release: the stores above are visible to the waiters
             }
-            ++it;
         }
     } else {
-        // ======================= pixel warps (2, 3, 5, 6): one output pixel per thread =======================
-        const int pw = warp < kLastTransposeWarp ? warp - 2 : warp - 3;  // 0..3
-        const int et = pw * 32 + lane;                                    // 0..127
+        // ======================= pixel warps: one output pixel per thread =======================
+        // group 0 = warps 2,3,5,6; group 1 = warps 7,9,10,11
+        const uint32_t g = warp < 7 ? 0u : 1u;
+        const int pw = g == 0 ? (warp < 4 ? warp - 2 : warp - 3) : (warp == 7 ? 0 : warp - 8);  // 0..3
+        const int et = pw * 32 + lane;                                                           // 0..127
         const int yl = et >> 3, xl = et & 7;
         const float b0 = __ldg(p.bias), b1 = __ldg(p.bias + 1), b2 = __ldg(p.bias + 2);
         uint32_t it = 0;
-        for (int mt = blockIdx.x; mt < p.m_tiles; mt += gridDim.x) {
+        for (int mt = blockIdx.x; mt < p.m_tiles; mt += gridDim.x, ++it) {
+            if ((it & 1) != g) continue;
             const TileCoord tc = decode_tile(p.tiles_x, p.tiles_y, mt);
-            const uint32_t buf = it & 1;
-            mbar_wait(&s_full[buf], (it >> 1) & 1);
-            const float* S = s_smem + buf * (27 * kLastSP);
+            const uint32_t k = it >> 1, sb = k & 1;
+            mbar_wait(&s_full[g * 2 + sb], (k >> 1) & 1);
+            const float* S = s_smem + (g * 2 + sb) * (27 * kLastSP);
             // 27-term window gather
             float a0 = b0, a1 = b1, a2 = b2;
 #pragma unroll
@@ -201,7 +209,7 @@ last_conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                     a2 += sp[2 * kLastSP];
                 }
             __syncwarp();
-            if (lane == 0) mbar_arrive(&s_empty[buf]);
+            if (lane == 0) mbar_arrive(&s_empty[g * 2 + sb]);
             const float t[3] = {tanhf(a0), tanhf(a1), tanhf(a2)};
             const int y = tc.y0 + yl, x = tc.x0 + xl;
             if (y < p.H && x < p.W) {
@@ -230,7 +238,6 @@ last_conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                     }
                 }
             }
-            ++it;
         }
     }
 
