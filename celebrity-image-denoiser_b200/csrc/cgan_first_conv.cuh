@@ -26,7 +26,8 @@
 namespace cid {
 
 constexpr int kG0Threads = 288;
-constexpr int kG0Stages = 8;
+constexpr int kG0Stages = 4;
+constexpr int kG0CtasPerSm = 2;               // latency-bound roles: two resident CTAs per SM
 constexpr int kG0Phase = 153 * 16;            // one 9 x 17 phase patch
 constexpr int kG0Plane = 4 * kG0Phase;        // 9792 B: the four phase patches (K chunk 0)
 constexpr int kG0StageBytes = kG0Plane;
@@ -48,7 +49,7 @@ struct G0Params {
 };
 
 template <bool U8>
-__global__ void __launch_bounds__(kG0Threads, 1)
+__global__ void __launch_bounds__(kG0Threads, kG0CtasPerSm)
 cgan_first_conv_kernel(const __grid_constant__ CUtensorMap tmO, const G0Params p) {
     constexpr int N = 64;
     extern __shared__ uint8_t smem_raw[];
@@ -98,6 +99,7 @@ cgan_first_conv_kernel(const __grid_constant__ CUtensorMap tmO, const G0Params p
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_launch_dependents();
 
     const int per_cta = (p.m_tiles + gridDim.x - 1) / gridDim.x;
     const int mt_begin = min(static_cast<int>(blockIdx.x) * per_cta, p.m_tiles);
@@ -140,6 +142,7 @@ cgan_first_conv_kernel(const __grid_constant__ CUtensorMap tmO, const G0Params p
                 }
             }
         };
+        pdl_wait();  // the input image may be the previous kernel's output (noiser, resize, an earlier pass)
         TileWalk pf(p.tiles_x, p.tiles_y, mt_begin);
         auto load_raw = [&](uint32_t (&raw)[3 * kG0PerThread]) {
             const int y0 = 2 * pf.ty * 16 - 1, x0 = 2 * pf.tx * 8 - 1;
@@ -276,7 +279,7 @@ cgan_first_conv_kernel(const __grid_constant__ CUtensorMap tmO, const G0Params p
             if (lane == 0) mbar_arrive(&acc_empty[buf]);
             ++acc_it;
         }
-        if (issuer) bulk_wait<0>();
+        if (issuer) bulk_wait_read<0>();  // shared memory may go; the global writes complete with the grid
     }
 
     tc_fence_before();

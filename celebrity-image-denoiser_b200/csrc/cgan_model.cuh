@@ -211,11 +211,11 @@ static int cgan_run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, c
             CID_CHECK_CUDA(cudaFuncSetAttribute(cgan_first_conv_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kG0Smem));
             c->attr_done |= (1u << 28);
         }
-        const int grid = std::min(gp.m_tiles, c->num_sms);
+        const int grid = std::min(gp.m_tiles, c->num_sms * kG0CtasPerSm);
         if (io.u8)
-            cgan_first_conv_kernel<true><<<grid, kG0Threads, kG0Smem, st>>>(pl->tmO[0], gp);
+            CID_CHECK_CUDA(launch_ex(c, cgan_first_conv_kernel<true>, grid, kG0Threads, kG0Smem, st, 1, pl->tmO[0], gp));
         else
-            cgan_first_conv_kernel<false><<<grid, kG0Threads, kG0Smem, st>>>(pl->tmO[0], gp);
+            CID_CHECK_CUDA(launch_ex(c, cgan_first_conv_kernel<false>, grid, kG0Threads, kG0Smem, st, 1, pl->tmO[0], gp));
         CID_CHECK_CUDA(cudaGetLastError());
         c->launches++;
     }
@@ -275,9 +275,9 @@ static int cgan_run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, c
         }
         const int grid = std::min(lp.m_tiles, c->num_sms);
         if (io.u8)
-            last_conv_umma_kernel<EPI_TANH_U8><<<grid, kLastThreads, smem, st>>>(pl->tmA[4], c->tmW[4], lp);
+            CID_CHECK_CUDA(launch_ex(c, last_conv_umma_kernel<EPI_TANH_U8>, grid, kLastThreads, smem, st, 1, pl->tmA[4], c->tmW[4], lp));
         else
-            last_conv_umma_kernel<EPI_TANH_F32_NHWC><<<grid, kLastThreads, smem, st>>>(pl->tmA[4], c->tmW[4], lp);
+            CID_CHECK_CUDA(launch_ex(c, last_conv_umma_kernel<EPI_TANH_F32_NHWC>, grid, kLastThreads, smem, st, 1, pl->tmA[4], c->tmW[4], lp));
         CID_CHECK_CUDA(cudaGetLastError());
         c->launches++;
     }

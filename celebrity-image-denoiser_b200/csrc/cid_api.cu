@@ -318,6 +318,37 @@ static int get_plan(cid_ctx* c, int Bc, int H, int W, const void* ws, cid_plan**
 // ---------------------------------------------------------------------------------------------
 // launches
 // ---------------------------------------------------------------------------------------------
+// One launch path for every generator kernel: optional cluster dimension (CTA pairs) and the programmatic-
+// dependent-launch attribute, so consecutive layers overlap the next kernel's set-up (barriers, TMEM, resident
+// weights) with the tail of the previous one. The kernels order themselves with griddepcontrol.wait.
+template <class... KArgs, class... Args>
+static cudaError_t launch_ex(const cid_ctx* c, void (*kern)(KArgs...), int grid, int block, int smem, cudaStream_t st,
+                             int cluster, Args&&... args) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    int n = 0;
+    if (cluster > 1) {
+        attr[n].id = cudaLaunchAttributeClusterDimension;
+        attr[n].val.clusterDim.x = cluster;
+        attr[n].val.clusterDim.y = 1;
+        attr[n].val.clusterDim.z = 1;
+        ++n;
+    }
+    if (c->pdl) {
+        attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[n].val.programmaticStreamSerializationAllowed = 1;
+        ++n;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = n;
+    return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
+
 template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0, int TS = 0, int CG = 1>
 static int launch_conv(cid_ctx* c, int slot, const CUtensorMap& tmA, const CUtensorMap& tmW, const CUtensorMap& tmO,
                        const CUtensorMap& tmO2, ConvParams p, cudaStream_t st) {
@@ -340,24 +371,7 @@ static int launch_conv(cid_ctx* c, int slot, const CUtensorMap& tmA, const CUten
         c->attr_done |= (1u << slot);
     }
     const int grid = std::min(p.num_work * CG, c->num_sms / CG * CG);
-    if (CG == 1) {
-        kern<<<grid, kConvThreads, smem, st>>>(tmA, tmW, tmO, tmO2, p);
-    } else {
-        cudaLaunchConfig_t cfg;
-        memset(&cfg, 0, sizeof(cfg));
-        cfg.gridDim = dim3(grid);
-        cfg.blockDim = dim3(kConvThreads);
-        cfg.dynamicSmemBytes = smem;
-        cfg.stream = st;
-        cudaLaunchAttribute attr;
-        attr.id = cudaLaunchAttributeClusterDimension;
-        attr.val.clusterDim.x = CG;
-        attr.val.clusterDim.y = 1;
-        attr.val.clusterDim.z = 1;
-        cfg.attrs = &attr;
-        cfg.numAttrs = 1;
-        CID_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmW, tmO, tmO2, p));
-    }
+    CID_CHECK_CUDA(launch_ex(c, kern, grid, kConvThreads, smem, st, CG, tmA, tmW, tmO, tmO2, p));
     CID_CHECK_CUDA(cudaGetLastError());
     c->launches++;
     return 0;
@@ -408,9 +422,9 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         }
         const int grid = std::min(fp.m_tiles, c->num_sms * ((c->debug_flags & 4) ? 1 : kFirstCtasPerSm));
         if (io.u8)
-            first_conv_umma_kernel<true><<<grid, kFirstThreads, smem, st>>>(pl->tmO[0], fp);
+            CID_CHECK_CUDA(launch_ex(c, first_conv_umma_kernel<true>, grid, kFirstThreads, smem, st, 1, pl->tmO[0], fp));
         else
-            first_conv_umma_kernel<false><<<grid, kFirstThreads, smem, st>>>(pl->tmO[0], fp);
+            CID_CHECK_CUDA(launch_ex(c, first_conv_umma_kernel<false>, grid, kFirstThreads, smem, st, 1, pl->tmO[0], fp));
         CID_CHECK_CUDA(cudaGetLastError());
         c->launches++;
     } else {
@@ -561,9 +575,9 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         }
         const int grid = std::min(lp.m_tiles, c->num_sms);
         if (io.u8)
-            last_conv_umma_kernel<EPI_TANH_U8><<<grid, kLastThreads, smem, st>>>(pl->tmA[11], c->tmW[11], lp);
+            CID_CHECK_CUDA(launch_ex(c, last_conv_umma_kernel<EPI_TANH_U8>, grid, kLastThreads, smem, st, 1, pl->tmA[11], c->tmW[11], lp));
         else
-            last_conv_umma_kernel<EPI_TANH_F32><<<grid, kLastThreads, smem, st>>>(pl->tmA[11], c->tmW[11], lp);
+            CID_CHECK_CUDA(launch_ex(c, last_conv_umma_kernel<EPI_TANH_F32>, grid, kLastThreads, smem, st, 1, pl->tmA[11], c->tmW[11], lp));
         CID_CHECK_CUDA(cudaGetLastError());
         c->launches++;
     }
@@ -746,6 +760,10 @@ int cid_set_option(cid_handle h, const char* name, int64_t value) {
     // 32 = down1.2 (down2.0 and upconv1.0 always run as pairs). Default 2: where it measured faster.
     if (!strcmp(name, "variant")) {
         h->variant = static_cast<int>(value);
+        return 0;
+    }
+    if (!strcmp(name, "pdl")) {  // programmatic dependent launch between consecutive layers (default on)
+        h->pdl = value != 0;
         return 0;
     }
     if (!strcmp(name, "debug_flags")) {

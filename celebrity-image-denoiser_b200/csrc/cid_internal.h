@@ -83,6 +83,7 @@ struct cid_ctx {
     int variant = 34;                 // layers run as CTA pairs ("variant" option, see cid_set_option)
     bool first_tc = true;             // layer 0 on tensor cores (false: CUDA-core direct conv)
     bool patch = true;                // 3x3 layers load one halo patch per K block instead of 3 boxes
+    bool pdl = true;                  // programmatic dependent launch between layers ("pdl" option)
     bool profile = false;
     std::vector<cudaEvent_t> prof_events;  // 13 per recorded pass
     size_t prof_used = 0;                  // events recorded since the last cid_profile_read

@@ -262,6 +262,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_launch_dependents();  // the next layer's CTAs may start their own set-up on SMs that are (or become) free
 
     if (warp == 0) {
         // ======================= TMA producer =======================
@@ -288,6 +289,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
             uint32_t a_stage = 0, a_phase = 0, w_stage = 0, w_phase = 0;
             const int kb_total = p.kb_count * KSUB;
+            pdl_wait();  // activations are the previous layer's output (the resident weights above are constants)
             for (int work = unit; work < p.num_work; work += units) {
                 const int n_tile = work % p.n_tiles;
                 const int st = work / p.n_tiles;
@@ -627,7 +629,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
             ++acc_it;
         }
-        if (issuer) bulk_wait<0>();  // all TMA stores complete before the CTA exits
+        if (issuer) bulk_wait_read<0>();  // the staged slabs have been read; the writes complete with the grid
     }
 
     tc_fence_before();

@@ -133,6 +133,7 @@ first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParam
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_launch_dependents();
 
     // Each CTA walks a CONTIGUOUS range of tiles (x fastest): neighbouring tiles share halo pixels
     // in L1/L2 and the tile coordinates advance by increments instead of divisions.
@@ -176,6 +177,7 @@ first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParam
                 }
             }
         };
+        pdl_wait();  // the input image may be the previous kernel's output (noiser, resize, an earlier pass)
         TileWalk pf(p.tiles_x, p.tiles_y, mt_begin);  // prefetch cursor, kPF tiles ahead of the store cursor
         auto load_raw = [&](uint32_t (&raw)[6]) {
             const int y0 = pf.ty * 16 - 1, x0 = pf.tx * 8 - 1;
@@ -301,7 +303,7 @@ first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParam
             if (lane == 0) mbar_arrive(&acc_empty[buf]);
             ++acc_it;
         }
-        if (issuer) bulk_wait<0>();
+        if (issuer) bulk_wait_read<0>();  // shared memory may go; the global writes complete with the grid
     }
 
     tc_fence_before();

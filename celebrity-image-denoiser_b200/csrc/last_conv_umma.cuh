@@ -107,12 +107,14 @@ last_conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_launch_dependents();
 
     if (warp == 0) {
         // ======================= TMA producer =======================
         if (lane == 0) {
             mbar_arrive_expect_tx(w_full, kLastWBytes);
             tma_load_2d(w_smem, &tmW, w_full, 0, 0, kEvictLast);
+            pdl_wait();  // the activations are the previous layer's output
             uint32_t stage = 0, phase = 0;
             for (int mt = blockIdx.x; mt < p.m_tiles; mt += gridDim.x) {
                 const TileCoord tc = decode_tile(p.tiles_x, p.tiles_y, mt);
