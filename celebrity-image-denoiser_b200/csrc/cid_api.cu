@@ -25,6 +25,8 @@
 #include "first_conv_umma.cuh"
 #include "last_conv_umma.cuh"
 #include "cgan_first_conv.cuh"
+#include "k9_first_conv.cuh"
+#include "k9_last_conv.cuh"
 
 #define TSV(x) x
 
@@ -461,6 +463,7 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         p.bias = c->bias_dev[l];
         p.cout = kLayers[l].cout;
         p.w_rows_per_tap = std::max(kLayers[l].cout, 16);
+        p.slope = 1.f;  // EPI_CONVT: no activation after the transposed convs
         p.debug_flags = c->debug_flags;
         return p;
     };
@@ -587,6 +590,7 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
 
 }  // namespace cid
 #include "cgan_model.cuh"
+#include "sr_model.cuh"
 namespace cid {
 
 static int chunk_of(const cid_ctx* c, int B) {
@@ -596,24 +600,33 @@ static int chunk_of(const cid_ctx* c, int B) {
 static int forward_common(cid_ctx* c, int B, int H, int W, void* ws, size_t ws_bytes, cudaStream_t st,
                           const uint8_t* x, size_t x_img_bytes, uint8_t* y, size_t y_img_bytes, IoSpec io) {
     CID_REQUIRE(c && c->finalized, "generator not finalized (call cid_set_param for every tensor, then cid_finalize)");
-    CID_REQUIRE(B >= 1 && H >= 4 && W >= 4, "bad shape B=%d H=%d W=%d", B, H, W);
-    CID_REQUIRE(H % 4 == 0 && W % 4 == 0, "network input %dx%d must be multiples of 4 (get_padding, app.py:276)", H,
-                W);
+    const bool sr = c->model == CID_MODEL_ESRGAN || c->model == CID_MODEL_SRGAN;
+    if (sr) {  // fully convolutional, stride 1: any size
+        CID_REQUIRE(B >= 1 && H >= 1 && W >= 1, "bad shape B=%d H=%d W=%d", B, H, W);
+    } else {
+        CID_REQUIRE(B >= 1 && H >= 4 && W >= 4, "bad shape B=%d H=%d W=%d", B, H, W);
+        CID_REQUIRE(H % 4 == 0 && W % 4 == 0, "network input %dx%d must be multiples of 4 (get_padding, app.py:276)", H,
+                    W);
+    }
     CID_REQUIRE(x && y && ws, "null pointer argument");
     CID_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 1023) == 0, "workspace must be 1024-byte aligned");
     DeviceGuard g(c->device);
     CID_REQUIRE(g.ok, "cannot select CUDA device %d", c->device);
     const int Bc = chunk_of(c, B);
     const bool cgan = c->model == CID_MODEL_KERAS_CGAN;
-    const size_t need = cgan ? cgan_layout_offsets(Bc, H, W, nullptr) : layout_offsets(Bc, H, W, nullptr);
+    const size_t need = sr     ? sr_layout_offsets(c->model, Bc, H, W, nullptr)
+                        : cgan ? cgan_layout_offsets(Bc, H, W, nullptr)
+                               : layout_offsets(Bc, H, W, nullptr);
     CID_REQUIRE(ws_bytes >= need, "workspace too small: %zu < %zu bytes", ws_bytes, need);
     cid_plan* pl = nullptr;
-    if (cgan ? cgan_get_plan(c, Bc, H, W, ws, &pl) : get_plan(c, Bc, H, W, ws, &pl)) return 1;
+    if (sr ? sr_get_plan(c, Bc, H, W, ws, &pl) : cgan ? cgan_get_plan(c, Bc, H, W, ws, &pl) : get_plan(c, Bc, H, W, ws, &pl))
+        return 1;
     for (int b0 = 0; b0 < B; b0 += Bc) {
         const int nb = std::min(Bc, B - b0);
         io.x = x + static_cast<size_t>(b0) * x_img_bytes;
         io.y = y + static_cast<size_t>(b0) * y_img_bytes;
-        if (cgan ? cgan_run_layers(c, pl, nb, io, st) : run_layers(c, pl, nb, io, st)) return 1;
+        if (sr ? sr_run_layers(c, pl, nb, io, st) : cgan ? cgan_run_layers(c, pl, nb, io, st) : run_layers(c, pl, nb, io, st))
+            return 1;
     }
     return 0;
 }
@@ -627,7 +640,7 @@ using namespace cid;
 // =============================================================================================
 extern "C" {
 
-int cid_version(void) { return 2; }
+int cid_version(void) { return 3; }
 
 const char* cid_last_error(void) { return g_err; }
 
@@ -639,7 +652,9 @@ int cid_create_model(int device, const char* model, cid_handle* out) {
     int kind = -1;
     if (!strcmp(model, "denoise")) kind = CID_MODEL_DENOISE;
     if (!strcmp(model, "keras_cgan")) kind = CID_MODEL_KERAS_CGAN;
-    CID_REQUIRE(kind >= 0, "unknown model '%s' (denoise | keras_cgan)", model);
+    if (!strcmp(model, "esrgan")) kind = CID_MODEL_ESRGAN;
+    if (!strcmp(model, "srgan")) kind = CID_MODEL_SRGAN;
+    CID_REQUIRE(kind >= 0, "unknown model '%s' (denoise | keras_cgan | esrgan | srgan)", model);
     *out = nullptr;
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
@@ -662,7 +677,7 @@ int cid_create_model(int device, const char* model, cid_handle* out) {
 int cid_destroy(cid_handle h) {
     if (!h) return 0;
     DeviceGuard g(h->device);
-    for (int l = 0; l < 12; ++l) {
+    for (int l = 0; l < kMaxLayers; ++l) {
         if (h->w_dev[l]) cudaFree(h->w_dev[l]);
         if (h->bias_dev[l]) cudaFree(h->bias_dev[l]);
     }
@@ -674,10 +689,10 @@ int cid_destroy(cid_handle h) {
 int cid_set_param(cid_handle h, const char* key, const float* data, const int64_t* shape, int ndim) {
     CID_REQUIRE(h && key && data && shape, "cid_set_param: null argument");
     const std::string k(key);
-    if (h->model == CID_MODEL_KERAS_CGAN) {
+    if (h->model != CID_MODEL_DENOISE) {
         int64_t expect[4];
-        const int en = cgan_param_shape(k, expect);
-        CID_REQUIRE(en > 0, "unknown variable '%s' for the keras_cgan generator", key);
+        const int en = h->model == CID_MODEL_KERAS_CGAN ? cgan_param_shape(k, expect) : sr_param_shape(h->model, k, expect);
+        CID_REQUIRE(en > 0, "unknown parameter '%s' for this generator", key);
         CID_REQUIRE(ndim == en, "%s: expected %d dims, got %d", key, en, ndim);
         size_t n = 1;
         for (int i = 0; i < en; ++i) {
@@ -736,6 +751,8 @@ int cid_finalize(cid_handle h) {
     CID_CHECK_CUDA(cudaDeviceSynchronize());  // no forward may still be reading the old packed weights
     if (h->model == CID_MODEL_KERAS_CGAN) {
         if (cgan_pack(h)) return 1;
+    } else if (h->model != CID_MODEL_DENOISE) {
+        if (sr_pack(h)) return 1;
     } else {
         for (int l = 0; l < 12; ++l)
             if (pack_layer(h, l)) return 1;
@@ -781,6 +798,11 @@ int cid_set_option(cid_handle h, const char* name, int64_t value) {
 
 int cid_workspace_bytes(cid_handle h, int B, int H, int W, size_t* bytes) {
     CID_REQUIRE(h && bytes, "cid_workspace_bytes: null argument");
+    if (h->model == CID_MODEL_ESRGAN || h->model == CID_MODEL_SRGAN) {
+        CID_REQUIRE(B >= 1 && H >= 1 && W >= 1, "bad shape B=%d H=%d W=%d", B, H, W);
+        *bytes = sr_layout_offsets(h->model, chunk_of(h, B), H, W, nullptr);
+        return 0;
+    }
     CID_REQUIRE(B >= 1 && H >= 4 && W >= 4, "bad shape B=%d H=%d W=%d", B, H, W);
     CID_REQUIRE(H % 4 == 0 && W % 4 == 0, "network input %dx%d must be multiples of 4 (get_padding, app.py:276)", H, W);
     *bytes = h->model == CID_MODEL_KERAS_CGAN ? cgan_layout_offsets(chunk_of(h, B), H, W, nullptr)
@@ -801,14 +823,15 @@ int cid_forward_f32_nhwc(cid_handle h, const float* x, float* y, int B, int H, i
 
 int cid_forward_f32_nchw(cid_handle h, const float* x, float* y, int B, int H, int W, void* ws, size_t ws_bytes,
                          void* stream) {
-    CID_REQUIRE(h && h->model == CID_MODEL_DENOISE, "cid_forward_f32_nchw is the denoise generator's entry point "
-                                                    "(keras_cgan: cid_forward_f32_nhwc)");
+    CID_REQUIRE(h && h->model != CID_MODEL_KERAS_CGAN, "cid_forward_f32_nchw is the torch generators' (denoise, esrgan, "
+                                                       "srgan) entry point (keras_cgan: cid_forward_f32_nhwc)");
     IoSpec io;
     memset(&io, 0, sizeof(io));
     io.u8 = false;
     const size_t img = static_cast<size_t>(3) * H * W * 4;
+    const size_t out_img = h->model == CID_MODEL_SRGAN ? img * 16 : img;  // SRGAN: [B,3,4H,4W]
     return forward_common(h, B, H, W, ws, ws_bytes, static_cast<cudaStream_t>(stream),
-                          reinterpret_cast<const uint8_t*>(x), img, reinterpret_cast<uint8_t*>(y), img, io);
+                          reinterpret_cast<const uint8_t*>(x), img, reinterpret_cast<uint8_t*>(y), out_img, io);
 }
 
 int cid_forward_u8_nhwc(cid_handle h, const uint8_t* x, uint8_t* y, int B, int H, int W, int pad_l, int pad_t,
@@ -823,8 +846,20 @@ int cid_forward_u8_nhwc(cid_handle h, const uint8_t* x, uint8_t* y, int B, int H
     io.pad_l = pad_l;
     io.pad_t = pad_t;
     const size_t img = static_cast<size_t>(3) * H * W;
+    if (h && h->model == CID_MODEL_ESRGAN) {
+        // the esrgan branch feeds the UN-padded image (preprocess_image, backend/app.py:387-390) and then crops the
+        // un-padded output at the padding offsets (:473-479): PIL fills what falls outside with black
+        if (pad_l || pad_t) {
+            DeviceGuard g(h->device);
+            CID_CHECK_CUDA(cudaMemsetAsync(y, 0, img * B, static_cast<cudaStream_t>(stream)));
+        }
+        return forward_common(h, B, H, W, ws, ws_bytes, static_cast<cudaStream_t>(stream), x, img, y, img, io);
+    }
+    const size_t out_img = (h && h->model == CID_MODEL_SRGAN)
+                               ? static_cast<size_t>(3) * 16 * (H + pad_t + pad_b) * (W + pad_l + pad_r)
+                               : img;  // SRGAN: the 4x output of the PADDED frame, not cropped (:480-485)
     return forward_common(h, B, H + pad_t + pad_b, W + pad_l + pad_r, ws, ws_bytes, static_cast<cudaStream_t>(stream),
-                          x, img, y, img, io);
+                          x, img, y, out_img, io);
 }
 
 int64_t cid_kernel_launches(cid_handle h) { return h ? h->launches : -1; }
@@ -834,8 +869,8 @@ int cid_profile_read(cid_handle h, double* layer_ms, int64_t* passes) {
     DeviceGuard g(h->device);
     CID_REQUIRE(g.ok, "cannot select CUDA device %d", h->device);
     CID_CHECK_CUDA(cudaDeviceSynchronize());
-    for (int l = 0; l < 12; ++l) layer_ms[l] = 0.0;
-    const int nl = h->model == CID_MODEL_KERAS_CGAN ? 5 : 12;
+    for (int l = 0; l < kMaxLayers; ++l) layer_ms[l] = 0.0;
+    const int nl = h->model == CID_MODEL_KERAS_CGAN ? 5 : h->model == CID_MODEL_ESRGAN ? 18 : h->model == CID_MODEL_SRGAN ? 15 : 12;
     const size_t n = h->prof_used / (nl + 1);
     for (size_t i = 0; i < n; ++i)
         for (int l = 0; l < nl; ++l) {

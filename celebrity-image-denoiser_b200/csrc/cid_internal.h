@@ -53,13 +53,14 @@ struct DeviceGuard {
 struct cid_plan {
     int Bc = 0, H = 0, W = 0;
     const void* ws = nullptr;
-    size_t off[11] = {0};   // byte offsets of a0,cat1,p1,a2,cat2,p2,b0,b1,u2a,u2b,u1a
-    CUtensorMap tmA[12];    // indexed by layer (0 unused)
-    CUtensorMap tmO[12];    // TMA-store maps of each layer's output buffer (box 64ch x 8px x 16 rows)
-    CUtensorMap tmO2[12];   // pooled output (box 64ch x 4px x 8 rows); layers 1 and 3 only
+    size_t off[11] = {0};   // byte offsets of a0,cat1,p1,a2,cat2,p2,b0,b1,u2a,u2b,u1a (other models: their own buffers)
+    CUtensorMap tmA[12];    // indexed by layer (0 unused); ESRGAN/SRGAN: indexed by BUFFER (3x3 halo-patch map)
+    CUtensorMap tmO[12];    // TMA-store maps of each layer's output buffer (box 64ch x 8px x 16 rows); SR: by buffer
+    CUtensorMap tmO2[12];   // pooled output (box 64ch x 4px x 8 rows); layers 1 and 3 only; SR: 9x9 window maps by buffer
 };
 
-enum { CID_MODEL_DENOISE = 0, CID_MODEL_KERAS_CGAN = 1 };
+enum { CID_MODEL_DENOISE = 0, CID_MODEL_KERAS_CGAN = 1, CID_MODEL_ESRGAN = 2, CID_MODEL_SRGAN = 3 };
+constexpr int kMaxLayers = 24;  // ESRGAN: 18 convolutions
 
 struct cid_ctx {
     int device = 0;
@@ -70,11 +71,12 @@ struct cid_ctx {
     int64_t chunk = 0;
     bool finalized = false;
     std::map<std::string, std::vector<float>> params;  // host fp32 copies, reference layout
-    void* w_dev[12] = {nullptr};      // packed bf16 weights per layer (0 unused)
-    float* bias_dev[12] = {nullptr};  // fp32 bias per layer
-    CUtensorMap tmW[12];
-    CUtensorMap tmWh[12];             // same weights, box of N/2 rows (CTA-pair kernels load half a tile each)
+    void* w_dev[kMaxLayers] = {nullptr};      // packed bf16 weights per layer (0 unused)
+    float* bias_dev[kMaxLayers] = {nullptr};  // fp32 bias per layer
+    CUtensorMap tmW[kMaxLayers];
+    CUtensorMap tmWh[kMaxLayers];            // same weights, box of N/2 rows (CTA-pair kernels load half a tile each)
     void* first_w_host = nullptr;     // cid::FirstConvW (kernel parameter block)
+    float slopes[kMaxLayers] = {0};   // ESRGAN / SRGAN: PReLU parameter of each layer (1 = none)
     std::vector<cid_plan> plans;
     uint32_t attr_done = 0;           // bit per kernel instantiation: max-dynamic-smem attribute set
     std::map<uint64_t, void*> resize_coeffs;  // (in_size,out_size) -> device coefficient block

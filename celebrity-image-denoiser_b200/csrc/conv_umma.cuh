@@ -29,7 +29,8 @@
 namespace cid {
 
 enum : int {  // TANH_*: last_conv_umma.cuh; LRELU/T4: the Keras cGAN layers (leaky ReLU with ConvParams::slope)
-    EPI_RELU = 0, EPI_RELU_POOL = 1, EPI_CONVT = 2, EPI_TANH_F32 = 3, EPI_TANH_U8 = 4, EPI_LRELU = 5, EPI_T4 = 6, EPI_TANH_F32_NHWC = 7
+    EPI_RELU = 0, EPI_RELU_POOL = 1, EPI_CONVT = 2, EPI_TANH_F32 = 3, EPI_TANH_U8 = 4, EPI_LRELU = 5, EPI_T4 = 6, EPI_TANH_F32_NHWC = 7,
+    EPI_ADD = 8  // bias + residual add(s), no activation (ESRGAN / SRGAN skip connections)
 };
 
 constexpr int kConvThreads = 320;  // warp 0 TMA, warp 1 MMA, warps 2..9 two epilogue groups
@@ -51,7 +52,11 @@ struct ConvParams {
     void* out2;          // EPI_RELU_POOL: pooled output buffer
     int out2_cs, out2_c0;
     int crop_l, crop_t, out_h, out_w;  // EPI_TANH_U8: crop window into the u8 NHWC result
-    float slope;         // EPI_LRELU / EPI_T4: negative slope of the leaky ReLU
+    float slope;         // EPI_LRELU / EPI_T4 / EPI_CONVT: negative slope of the leaky ReLU (PReLU with one parameter)
+    const void* res;     // EPI_ADD: bf16 NHWC residual(s) with the output's spatial dims, res_cs channels per pixel
+    const void* res2;    //          (second one optional)
+    int res_cs, res2_cs;
+    int bias_per_column; // EPI_CONVT as pixel shuffle: bias indexed by GEMM column instead of by channel
     int debug_flags;     // bring-up experiments only: 1 = epilogue skips global stores, 2 = skips TMEM reads too
 };
 
@@ -450,13 +455,14 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             tc_fence_after();
             const uint32_t tbase = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * Cfg::ACC_COLS;
             if (!(p.debug_flags & 2)) {
-                if constexpr (EPI == EPI_RELU || EPI == EPI_RELU_POOL || EPI == EPI_LRELU) {
+                if constexpr (EPI == EPI_RELU || EPI == EPI_RELU_POOL || EPI == EPI_LRELU || EPI == EPI_ADD) {
                     constexpr int SL = N / 64;  // 64-channel slabs per pixel tile
                     const int sub = (xl & 1) | ((yl & 1) << 1);
                     const int prow_i = (yl >> 1) * 4 + (xl >> 1);
                     const float slope = p.slope;
                     auto act = [&](float x) {  // ReLU, or LeakyReLU(slope) for the Keras layers
                         if constexpr (EPI == EPI_LRELU) return x > 0.f ? x : x * slope;
+                        if constexpr (EPI == EPI_ADD) return x;
                         return fmaxf(x, 0.f);
                     };
                     (void)slope;
@@ -471,9 +477,56 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         // the store that used this buffer NOB slabs ago must have finished READING it
                         if (issuer) bulk_wait_read<Cfg::NOB - 1>();
                         named_bar_sync(bar_id, 128);
+                        // EPI_ADD: this thread's 64 residual channels (one 128-byte line per tensor), in flight
+                        // while the accumulator is read
+                        uint4 rv[EPI == EPI_ADD ? 8 : 1], rv2[EPI == EPI_ADD ? 8 : 1];
+                        bool has2 = false;
+                        if constexpr (EPI == EPI_ADD) {
+                            const int yy = tc.y0 + yl, xx = tc.x0 + xl;
+                            const bool live = tc.b < p.B && yy < p.H && xx < p.W;
+                            const size_t pix = (static_cast<size_t>(tc.b) * p.H + yy) * p.W + xx;
+                            const int c64 = n_tile * N + cs * 64;
+                            has2 = p.res2 != nullptr;
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                rv[i] = make_uint4(0u, 0u, 0u, 0u);
+                                rv2[i] = make_uint4(0u, 0u, 0u, 0u);
+                            }
+                            if (live && p.res != nullptr) {
+                                const uint4* r1 = reinterpret_cast<const uint4*>(
+                                    static_cast<const uint16_t*>(p.res) + pix * p.res_cs + c64);
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) rv[i] = __ldg(r1 + i);
+                                if (has2) {
+                                    const uint4* r2 = reinterpret_cast<const uint4*>(
+                                        static_cast<const uint16_t*>(p.res2) + pix * p.res2_cs + c64);
+#pragma unroll
+                                    for (int i = 0; i < 8; ++i) rv2[i] = __ldg(r2 + i);
+                                }
+                            }
+                        }
+                        (void)has2;
                         for_each_chunk<2>(tbase + s * Cfg::NACC + cs * 64, [&](int ch, uint32_t (&v)[32]) {
                             const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_tile * N + cs * 64 + ch * 32);
                             uint32_t pk[16];
+                            if constexpr (EPI == EPI_ADD) {
+                                // v[2i], v[2i+1] += the bf16 pair i of this 32-channel half
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) {
+                                    const uint4 a = rv[ch * 4 + i], b = rv2[ch * 4 + i];
+                                    const uint32_t w[4] = {a.x, a.y, a.z, a.w}, w2[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+                                    for (int e = 0; e < 4; ++e) {
+                                        const int col = (i * 4 + e) * 2;
+                                        float lo = __uint_as_float(v[col]) + __uint_as_float(w[e] << 16);
+                                        float hi = __uint_as_float(v[col + 1]) + __uint_as_float(w[e] & 0xffff0000u);
+                                        lo += __uint_as_float(w2[e] << 16);
+                                        hi += __uint_as_float(w2[e] & 0xffff0000u);
+                                        v[col] = __float_as_uint(lo);
+                                        v[col + 1] = __float_as_uint(hi);
+                                    }
+                                }
+                            }
 #pragma unroll
                             for (int jj = 0; jj < 8; ++jj) {
                                 const float4 bb = __ldg(b4 + jj);
@@ -576,9 +629,11 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     // chunks fill two slabs [16 y][16 px][64 ch] of output rows 2y+dy (cout 64: slab = dy;
                     // cout 128: slab = 64-channel half, dy = n_tile), each written by one 5-D TMA store over
                     // (C, 2W, dy, H, B). Group g fills and stores slab g.
-                    static_assert(EPI == EPI_CONVT && N == 256 && S == 1, "convT epilogue: 8 chunks per tile");
+                    static_assert(EPI == EPI_CONVT && N == 256 && S == 1, "convT / pixel-shuffle epilogue: 8 chunks per tile");
                     const TileCoord tc = decode_tile(p, st * CG + static_cast<int>(rank));
                     const bool c64mode = (p.cout == 64);
+                    const float ct_slope = p.slope;
+                    const bool act_on = ct_slope != 1.f;
                     const int slab_i = g;
                     uint8_t* slab = o_smem + slab_i * Cfg::OT_SLAB;
                     if (issuer) bulk_wait_read<0>();  // this group's previous store has drained the slab
@@ -590,15 +645,22 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         const int n = n_tile * N + ch * 32;
                         const int quad = n / p.cout;
                         const int c = n - quad * p.cout;
-                        const float4* b4 = reinterpret_cast<const float4*>(p.bias + c);
+                        // transposed conv: one bias per output channel; pixel shuffle: one per GEMM column
+                        const float4* b4 = reinterpret_cast<const float4*>(p.bias + (p.bias_per_column ? n : c));
                         uint32_t pk[16];
 #pragma unroll
                         for (int jj = 0; jj < 8; ++jj) {
                             const float4 bb = __ldg(b4 + jj);
-                            pk[2 * jj + 0] = pack_bf16x2(__uint_as_float(v[4 * jj + 0]) + bb.x,
-                                                         __uint_as_float(v[4 * jj + 1]) + bb.y);
-                            pk[2 * jj + 1] = pack_bf16x2(__uint_as_float(v[4 * jj + 2]) + bb.z,
-                                                         __uint_as_float(v[4 * jj + 3]) + bb.w);
+                            float f0 = __uint_as_float(v[4 * jj + 0]) + bb.x, f1 = __uint_as_float(v[4 * jj + 1]) + bb.y;
+                            float f2 = __uint_as_float(v[4 * jj + 2]) + bb.z, f3 = __uint_as_float(v[4 * jj + 3]) + bb.w;
+                            if (act_on) {  // PixelShuffle + PReLU (SRGAN); the plain transposed convs have no activation
+                                f0 = f0 > 0.f ? f0 : f0 * ct_slope;
+                                f1 = f1 > 0.f ? f1 : f1 * ct_slope;
+                                f2 = f2 > 0.f ? f2 : f2 * ct_slope;
+                                f3 = f3 > 0.f ? f3 : f3 * ct_slope;
+                            }
+                            pk[2 * jj + 0] = pack_bf16x2(f0, f1);
+                            pk[2 * jj + 1] = pack_bf16x2(f2, f3);
                         }
                         const int orow_i = yl * 16 + 2 * xl + (quad & 1);
                         uint8_t* rowp = slab + orow_i * 128;

@@ -107,7 +107,7 @@ class _Engine:
         return int(self.lib.cid_kernel_launches(self.handle))
 
     def profile_read(self):
-        ms = (C.c_double * 12)()
+        ms = (C.c_double * 24)()
         n = C.c_int64()
         _lib.check(self.lib.cid_profile_read(self.handle, ms, C.byref(n)), "cid_profile_read")
         return list(ms), int(n.value)

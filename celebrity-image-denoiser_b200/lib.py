@@ -12,7 +12,7 @@ from pathlib import Path
 _LIB_PATH = Path(__file__).resolve().parent / "csrc" / "libcid_b200.so"
 _lib = None
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 # name -> (restype, argtypes); mirrors include/cid_b200.h one to one
 _SIGNATURES = {

@@ -17,8 +17,11 @@ import torch.nn as nn
 
 logger = logging.getLogger("gan_api")
 
-MODEL_CFG: Dict[str, Dict] = {
+MODEL_CFG: Dict[str, Dict] = {  # backend/app.py:228-233
     "denoise": {"normalize": ([0.5] * 3, [0.5] * 3), "activation": "tanh", "pad_divisor": 4, "scale": 1},
+    "cgan": {"normalize": ([0.5] * 3, [0.5] * 3), "activation": "tanh", "pad_divisor": 4, "scale": 1},
+    "srgan": {"normalize": ([0.5] * 3, [0.5] * 3), "activation": "tanh", "pad_divisor": 4, "scale": 4},
+    "esrgan": {"normalize": None, "activation": None, "pad_divisor": 4, "scale": 1},
 }
 
 
@@ -58,17 +61,23 @@ def get_padding(image_or_size, divisor: int, scale: int = 1) -> Tuple[int, int, 
     return (pw // 2, ph // 2, pw - pw // 2, ph - ph // 2)
 
 
-def patch_app(app_module, device=None):
-    """Drop the B200-native generator in behind the reference's routes: replaces
-    `app.PT_MODELS["denoise"]` (backend/app.py:319-320) with a DenoiseGenerator carrying the same
-    weights. The FastAPI routes are untouched (`net(x_pt)` at :433 now runs the CUDA path)."""
+def patch_app(app_module, device=None, models=("denoise", "esrgan", "srgan")):
+    """Drop the B200-native generators in behind the reference's routes: replaces
+    `app.PT_MODELS[name]` (backend/app.py:319-324) with the same-named module of this package carrying the
+    same weights. The FastAPI routes are untouched (`net(x_pt)` at :393 / :433 now runs the CUDA path).
+    Returns the new `PT_MODELS["denoise"]` (or the first swapped model)."""
     from .generator import DenoiseGenerator
+    from .sr_generators import ESRGANGenerator, SRGANGenerator
 
-    old = app_module.PT_MODELS["denoise"]
-    new = DenoiseGenerator()
-    new.load_state_dict(old.state_dict(), strict=True)
+    classes = {"denoise": DenoiseGenerator, "esrgan": ESRGANGenerator, "srgan": SRGANGenerator}
     dev = torch.device(device) if device is not None else torch.device("cuda")
-    new = new.to(dev).eval()
-    app_module.PT_MODELS["denoise"] = new
+    first = None
+    for name in models:
+        old = app_module.PT_MODELS[name]
+        new = classes[name]()
+        new.load_state_dict(old.state_dict(), strict=True)
+        new = new.to(dev).eval()
+        app_module.PT_MODELS[name] = new
+        first = first if first is not None else new
     app_module.DEVICE = dev  # the route moves its input tensor to app.DEVICE (:406)
-    return new
+    return first

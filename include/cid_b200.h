@@ -29,6 +29,8 @@ extern "C" {
 
 typedef struct cid_ctx* cid_handle;
 
+#define CID_MAX_LAYERS 24
+
 /* ABI version of this header (bumped on any signature change). */
 int cid_version(void);
 
@@ -51,7 +53,19 @@ int cid_destroy(cid_handle h);
  *   conv2d_transpose.kernel [4,4,128,128] (kh,kw,Cout,Cin)  conv2d_transpose.bias [128]
  *   conv2d_transpose_1.kernel [4,4,64,128]  conv2d_transpose_1.bias [64]
  *   conv2d_2.kernel [3,3,64,3]  conv2d_2.bias [3]
- * and cid_finalize folds the inference BatchNormalization (eps 1e-3) into the weights. */
+ * and cid_finalize folds the inference BatchNormalization (eps 1e-3) into the weights.
+ *   "esrgan"      ESRGANGenerator (backend/app.py:203-217) and
+ *   "srgan"       SRGANGenerator (backend/app.py:146-184): cid_set_param takes the torch state_dict float tensors
+ *                 under their own keys (initial.0.weight [64,3,9,9], initial.1.weight [1] (PReLU),
+ *                 residuals.N.block.{0,3}.{weight,bias}, residuals.N.block.{1,4}.{weight,bias,running_mean,
+ *                 running_var}, residuals.N.block.2.weight, final.{weight,bias}; srgan: res_blocks.N.{0..4}.*, mid.*,
+ *                 upscale.{0,3}.{weight,bias}, upscale.{2,5}.weight); eval-mode BatchNorm2d (eps 1e-5) is folded at
+ *                 cid_finalize. Any H, W >= 1. cid_forward_f32_nchw: esrgan y = [B,3,H,W] (no activation),
+ *                 srgan y = [B,3,4H,4W] (tanh). cid_forward_u8_nhwc: esrgan = the esrgan branch of the route
+ *                 (ToTensor only, un-padded input, clamp(0,1), truncating x255, then the route's crop of the UN-padded
+ *                 result at the padding offsets, black outside: backend/app.py:387-397, 473-479), y = [B,H,W,3];
+ *                 srgan = Pad/ToTensor/Normalize -> net -> *0.5+0.5, clamp, x255, NOT cropped (:480-485),
+ *                 y = [B, 4(H+pad_t+pad_b), 4(W+pad_l+pad_r), 3]. */
 int cid_create_model(int device, const char* model, cid_handle* out);
 
 /* Replaces `model.load_state_dict(new_state, strict=False)` (backend/app.py:272): hand over one
@@ -139,7 +153,8 @@ int64_t cid_kernel_launches(cid_handle h);
  * (layer_ms[12], order: down1.0 down1.2 down2.0 down2.2 bottleneck.0 bottleneck.2 up2 upconv2.0
  * upconv2.2 up1 upconv1.0 upconv1.2) and the number of passes since the previous read.
  * keras_cgan: 6 events per pass, layer_ms[0..4] = conv2d conv2d_1 conv2d_transpose conv2d_transpose_1
- * conv2d_2 (layer_ms must still hold 12 doubles). */
+ * conv2d_2; esrgan: 18 layers, srgan: 15, in forward order. layer_ms must hold CID_MAX_LAYERS (24) doubles;
+ * unused entries are set to 0. */
 int cid_profile_read(cid_handle h, double* layer_ms, int64_t* passes);
 
 /* Test hook: copy one intermediate activation of the most recent forward (same B,H,W,ws) to host
