@@ -16,9 +16,11 @@ import torch
 
 from cid_b200.generator import DenoiseGenerator
 from cid_b200.keras_cgan import KerasCGANGenerator
+from cid_b200.sr_generators import ESRGANGenerator, SRGANGenerator
 from cid_b200.synth import synthetic_noisy_u8
 from oracle import denoise_oracle as orc
 from oracle import keras_cgan_oracle as ko
+from oracle import sr_oracle as so
 
 DEN_FLOP_PX = 703232
 CGAN_LAYER_FLOP_PX = {"conv2d": 2 * 64 * 48 / 4, "conv2d_1": 2 * 128 * 1024 / 16, "conv2d_transpose": 2 * 128 * 512 / 4,
@@ -89,6 +91,33 @@ def main():
                                   "tflops": B * S * S * CGAN_FLOP_PX / ms / 1e9, "layers": layers,
                                   "cpu_ms_per_image": cpu_ms, "cpu_batch": cb})
         print(out["keras_cgan"][-1], file=sys.stderr)
+    # ESRGAN / SRGAN: FLOPs = 2*M*N*K over their convolutions
+    flop_px = {"esrgan": 2 * (64 * 243 + 16 * 64 * 576 + 3 * 5184),
+               "srgan": 2 * (64 * 243 + 11 * 64 * 576 + 256 * 576 + 4 * 256 * 576 + 16 * 3 * 5184)}
+    out["sr"] = []
+    for model, cls, cases in (("esrgan", ESRGANGenerator, [(1, 128), (256, 128), (32, 256)]),
+                              ("srgan", SRGANGenerator, [(1, 128), (64, 128), (8, 256)])):
+        sd = so.init_state_dict(model, 0)
+        net = cls()
+        net.load_state_dict(sd, strict=True)
+        net = net.to(dev).eval().set_option("profile", 1)
+        for B, S in cases:
+            x = synthetic_noisy_u8(3, B, S, S).to(dev)
+            y = net.forward_u8(x)
+            net.profile_read()
+            ms = time_gpu(lambda: net.forward_u8(x, (0, 0, 0, 0), out=y), 50 if B == 1 else 10, warm=3)
+            layer_ms, passes = net.profile_read()
+            cb = 1
+            xc = synthetic_noisy_u8(3, cb, S, S).numpy()
+            fn = so.esrgan_enhance_u8 if model == "esrgan" else so.srgan_enhance_u8
+            cpu_ms = time_cpu(lambda: fn(sd, xc), budget_s=4.0, max_n=5) / cb
+            out["sr"].append({"model": model, "batch": B, "size": S, "ms": ms, "images_per_s": B / ms * 1e3,
+                              "tflops": B * S * S * flop_px[model] / ms / 1e9,
+                              "layers_ms": {k: v / passes for k, v in layer_ms.items()},
+                              "cpu_ms_per_image": cpu_ms})
+            print({k: v for k, v in out["sr"][-1].items() if k != "layers_ms"}, file=sys.stderr)
+            if B > 1:
+                print("   ", {k: round(v / passes, 4) for k, v in layer_ms.items()}, file=sys.stderr)
     print(json.dumps(out))
 
 
