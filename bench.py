@@ -172,7 +172,7 @@ def main():
     ap.add_argument("--batch", type=int, default=256, help="images per GPU per step")
     ap.add_argument("--size", type=int, default=128)
     ap.add_argument("--chunk", type=int, default=-1, help="images per pass through the layers (-1 = library default)")
-    ap.add_argument("--sub-batch", type=int, default=64, help="e2e: images per H2D/compute/D2H pipeline slot")
+    ap.add_argument("--sub-batch", type=int, default=128, help="e2e: images per H2D/compute/D2H pipeline slot")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--debug-flags", type=int, default=0, help="bring-up experiments (invalidates results)")
     ap.add_argument("--variant", type=int, default=-1, help="CTA-pair layer bit mask (cid_set_option 'variant'; -1 = library default)")
@@ -259,7 +259,8 @@ def main():
     barrier()
     f0.record()
     for _ in range(args.steps):
-        h2d, d2h = pipe.run(host_in, host_out)
+        h2d, d2h = pipe.run(host_in, host_out, join=False)  # a serving loop: batch k+1's upload overlaps batch k's tail
+    pipe.finish()
     f1.record()
     barrier()
     ms_e2e = f0.elapsed_time(f1)

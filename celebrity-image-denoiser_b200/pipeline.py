@@ -38,6 +38,7 @@ class HostPipeline:
         # one generator clone per stream is unnecessary: the workspace is reused strictly in stream
         # order per slot, so each slot gets its own network handle + workspace instead.
         self.nets = [net] + [self._clone(net) for _ in range(depth - 1)]
+        self._open = False
 
     @staticmethod
     def _clone(net: DenoiseGenerator) -> DenoiseGenerator:
@@ -49,12 +50,16 @@ class HostPipeline:
             c.set_option(k, v)
         return c
 
-    def run(self, host_in: torch.Tensor, host_out: torch.Tensor) -> Tuple[int, int]:
-        """host_in/host_out: pinned CPU uint8 [B,H,W,3]. Returns (h2d_bytes, d2h_bytes)."""
+    def run(self, host_in: torch.Tensor, host_out: torch.Tensor, join: bool = True) -> Tuple[int, int]:
+        """host_in/host_out: pinned CPU uint8 [B,H,W,3]. Returns (h2d_bytes, d2h_bytes).
+        join=False streams batch after batch without re-joining the slot streams in between (each slot's staging
+        buffers are reused strictly in its own stream's order); call finish() before reading the last results."""
         B = host_in.shape[0]
         cur = torch.cuda.current_stream(self.device)
-        for s in self.streams:
-            s.wait_stream(cur)
+        if join or not self._open:
+            for s in self.streams:
+                s.wait_stream(cur)
+            self._open = True
         i = 0
         for b0 in range(0, B, self.sub):
             nb = min(self.sub, B - b0)
@@ -64,10 +69,17 @@ class HostPipeline:
                 self.nets[slot].forward_u8(self.d_in[slot][:nb], self.pad, out=self.d_out[slot][:nb])
                 host_out[b0:b0 + nb].copy_(self.d_out[slot][:nb], non_blocking=True)
             i += 1
-        for s in self.streams:
-            cur.wait_stream(s)
+        if join:
+            self.finish()
         n = B * self.H * self.W * 3
         return n, n
+
+    def finish(self) -> None:
+        """Make the caller's current stream wait for everything the slot streams have been given."""
+        cur = torch.cuda.current_stream(self.device)
+        for s in self.streams:
+            cur.wait_stream(s)
+        self._open = False
 
 
 def enhance_batch_host(net: DenoiseGenerator, host_images: torch.Tensor, device="cuda", sub_batch: int = 64,
