@@ -223,7 +223,8 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint64_t* w_empty = bars + 3 * kMaxStages;
     uint64_t* acc_full = bars + 4 * kMaxStages;
     uint64_t* acc_empty = acc_full + 2;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+    uint64_t* res_full = acc_empty + 2;  // EPI_ADD: residual tile of each epilogue group has landed in its slab
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_full + 2);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -238,7 +239,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         tma_prefetch_desc(&tmW);
         if (TS) {
             tma_prefetch_desc(&tmO);
-            if (EPI == EPI_RELU_POOL) tma_prefetch_desc(&tmO2);
+            if (EPI == EPI_RELU_POOL || EPI == EPI_ADD) tma_prefetch_desc(&tmO2);
         }
         // pair mode: the leader's "full" barriers collect one expect_tx arrival per CTA, its acc_empty
         // one arrival per epilogue warp of both CTAs; "empty"/acc_full get one multicast commit each.
@@ -251,6 +252,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int i = 0; i < 2; ++i) {
             mbar_init(&acc_full[i], 1);
             mbar_init(&acc_empty[i], 8 * CG);
+            mbar_init(&res_full[i], 1);
         }
         fence_mbar_init();
     }
@@ -446,6 +448,25 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint8_t* og = o_smem + g * Cfg::O_GROUP;
         uint32_t acc_it = 0;
         uint32_t o_count = 0;  // slabs this group has staged so far
+        // EPI_ADD: the first residual tensor (tmO2 = its tile map, same geometry as the output's) is TMA-loaded into
+        // the group's staging slab one work item ahead: right after the slab's previous TMA store has been read out.
+        // Group g owns exactly slab j = g of every work item (S * N/64 == 2). Out-of-image pixels load as zeros.
+        const bool res_tma = EPI == EPI_ADD && p.res != nullptr;
+        auto issue_residual = [&](int w) {
+            if constexpr (EPI == EPI_ADD) {
+                static_assert(EPI != EPI_ADD || S * (N / 64) == 2, "one slab per group per work item");
+                const int nt = w % p.n_tiles, stw = w / p.n_tiles;
+                const int sj = g / (N / 64), csj = g % (N / 64);
+                const TileCoord tcr = decode_tile(p, (stw * CG + static_cast<int>(rank)) * S + sj);
+                mbar_arrive_expect_tx(&res_full[g], Cfg::O_SLAB);
+                tma_load_4d(og, &tmO2, &res_full[g], nt * N + csj * 64, tcr.x0, tcr.y0, tcr.b, kEvictFirst);
+            }
+        };
+        if (res_tma && issuer && unit < p.num_work) {
+            pdl_wait();  // the residual is an earlier layer's output: under programmatic dependent launch this warp
+                         // may run before those layers have finished (the TMA producer's wait does not cover it)
+            issue_residual(unit);
+        }
         for (int work = unit; work < p.num_work; work += units) {
             const int n_tile = work % p.n_tiles;
             const int st = work / p.n_tiles;
@@ -477,35 +498,23 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         // the store that used this buffer NOB slabs ago must have finished READING it
                         if (issuer) bulk_wait_read<Cfg::NOB - 1>();
                         named_bar_sync(bar_id, 128);
-                        // EPI_ADD: this thread's 64 residual channels (one 128-byte line per tensor), in flight
-                        // while the accumulator is read
-                        uint4 rv[EPI == EPI_ADD ? 8 : 1], rv2[EPI == EPI_ADD ? 8 : 1];
-                        bool has2 = false;
+                        // EPI_ADD: the optional SECOND residual (ESRGAN's long skip, last block only) comes straight from
+                        // global memory, this thread's pixel = one 128-byte line
+                        uint4 rv2[EPI == EPI_ADD ? 8 : 1];
                         if constexpr (EPI == EPI_ADD) {
                             const int yy = tc.y0 + yl, xx = tc.x0 + xl;
                             const bool live = tc.b < p.B && yy < p.H && xx < p.W;
-                            const size_t pix = (static_cast<size_t>(tc.b) * p.H + yy) * p.W + xx;
-                            const int c64 = n_tile * N + cs * 64;
-                            has2 = p.res2 != nullptr;
 #pragma unroll
-                            for (int i = 0; i < 8; ++i) {
-                                rv[i] = make_uint4(0u, 0u, 0u, 0u);
-                                rv2[i] = make_uint4(0u, 0u, 0u, 0u);
+                            for (int i = 0; i < 8; ++i) rv2[i] = make_uint4(0u, 0u, 0u, 0u);
+                            if (live && p.res2 != nullptr) {
+                                const size_t pix = (static_cast<size_t>(tc.b) * p.H + yy) * p.W + xx;
+                                const uint4* r2 = reinterpret_cast<const uint4*>(
+                                    static_cast<const uint16_t*>(p.res2) + pix * p.res2_cs + n_tile * N + cs * 64);
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) rv2[i] = __ldg(r2 + i);
                             }
-                            if (live && p.res != nullptr) {
-                                const uint4* r1 = reinterpret_cast<const uint4*>(
-                                    static_cast<const uint16_t*>(p.res) + pix * p.res_cs + c64);
-#pragma unroll
-                                for (int i = 0; i < 8; ++i) rv[i] = __ldg(r1 + i);
-                                if (has2) {
-                                    const uint4* r2 = reinterpret_cast<const uint4*>(
-                                        static_cast<const uint16_t*>(p.res2) + pix * p.res2_cs + c64);
-#pragma unroll
-                                    for (int i = 0; i < 8; ++i) rv2[i] = __ldg(r2 + i);
-                                }
-                            }
+                            if (res_tma) mbar_wait(&res_full[g], acc_it & 1);  // the residual tile is in `slab`
                         }
-                        (void)has2;
                         for_each_chunk<2>(tbase + s * Cfg::NACC + cs * 64, [&](int ch, uint32_t (&v)[32]) {
                             const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_tile * N + cs * 64 + ch * 32);
                             uint32_t pk[16];
@@ -513,7 +522,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                 // v[2i], v[2i+1] += the bf16 pair i of this 32-channel half
 #pragma unroll
                                 for (int i = 0; i < 4; ++i) {
-                                    const uint4 a = rv[ch * 4 + i], b = rv2[ch * 4 + i];
+                                    const int cjr = ch * 4 + i;
+                                    const uint4 a = res_tma ? ld_shared_v4(slab + row * 128 + ((cjr ^ (row & 7)) << 4))
+                                                            : make_uint4(0u, 0u, 0u, 0u);
+                                    const uint4 b = rv2[ch * 4 + i];
                                     const uint32_t w[4] = {a.x, a.y, a.z, a.w}, w2[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
                                     for (int e = 0; e < 4; ++e) {
@@ -568,6 +580,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             if constexpr (EPI == EPI_RELU_POOL)
                                 tma_store_4d(&tmO2, slab2, p.out2_c0 + c64, tc.x0 >> 1, tc.y0 >> 1, tc.b);
                             bulk_commit();
+                        }
+                        if (res_tma && issuer && work + units < p.num_work) {
+                            bulk_wait_read<0>();  // the store above has read the slab: it can take the next residual tile
+                            issue_residual(work + units);
                         }
                         ++o_count;
                     }

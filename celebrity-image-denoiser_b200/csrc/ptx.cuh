@@ -143,6 +143,12 @@ __device__ __forceinline__ void st_shared_v4(void* p, uint32_t a, uint32_t b, ui
                  : "memory");
 }
 
+__device__ __forceinline__ uint4 ld_shared_v4(const void* p) {
+    uint4 v;
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_u32(p)) : "memory");
+    return v;
+}
+
 // ----------------------------------------------------------------------------------------------
 // tcgen05: tensor memory + 5th-gen tensor-core MMA
 // ----------------------------------------------------------------------------------------------

@@ -331,7 +331,9 @@ static int sr_run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cud
                 p.res = l.res_buf >= 0 ? buf(l.res_buf) : nullptr;
                 p.res2 = l.res2_buf >= 0 ? buf(l.res2_buf) : nullptr;
                 p.res_cs = p.res2_cs = 64;
-                if (launch_conv<64, 9, 2, true, EPI_ADD, 10, 1, 2>(c, 17, tmA, c->tmWh[li], tmO, tmO, p, st)) return 1;
+                // tmO2 slot = tile map of the first residual tensor (TMA-loaded into the epilogue's staging slab)
+                const CUtensorMap& tmR = l.res_buf >= 0 ? pl->tmO[l.res_buf] : tmO;
+                if (launch_conv<64, 9, 2, true, EPI_ADD, 10, 1, 2>(c, 17, tmA, c->tmWh[li], tmO, tmR, p, st)) return 1;
             } else {
                 p.bias_per_column = 1;
                 if (launch_conv<256, 9, 1, false, EPI_CONVT, 10, 1>(c, 18, tmA, c->tmW[li], tmO, tmO, p, st)) return 1;
