@@ -640,7 +640,7 @@ using namespace cid;
 // =============================================================================================
 extern "C" {
 
-int cid_version(void) { return 3; }
+int cid_version(void) { return 4; }
 
 const char* cid_last_error(void) { return g_err; }
 

@@ -91,6 +91,89 @@ __global__ void __launch_bounds__(256) gaussian_u8_kernel(const uint8_t* __restr
     }
 }
 
+// The other element-wise noise types of the reference's generator (noise_generation.py:24-39), same skeleton:
+//   KIND 1 speckle  clip(x + x * N(mean, sigma), 0, 255)       p0 = mean, p1 = sigma; draws = the normal array
+//   KIND 2 uniform  clip(x + U(low, high), 0, 255)             p0 = low,  p1 = high;  draws = the uniform array
+//   KIND 3 poisson  np.random.poisson(x).astype(np.uint8)      draws = the Poisson counts (int64 -> u8 WRAPS mod 256)
+// Philox mode (draws == NULL) gives statistical parity: Poisson counts by sequential inversion for lambda < 24 and by
+// the rounded normal approximation above.
+template <int KIND>
+__global__ void __launch_bounds__(256) elementwise_noise_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out,
+                                                                size_t n, float p0, float p1,
+                                                                const double* __restrict__ draws, uint64_t seed,
+                                                                uint64_t offset) {
+    const size_t t = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const size_t base = t * 16;
+    if (base >= n) return;
+    const bool full = base + 16 <= n && ((reinterpret_cast<uintptr_t>(in + base) | reinterpret_cast<uintptr_t>(out + base)) & 15) == 0;
+    uint8_t px[16];
+    if (full) {
+        *reinterpret_cast<uint4*>(px) = __ldg(reinterpret_cast<const uint4*>(in + base));
+    } else {
+        for (int i = 0; i < 16; ++i) px[i] = base + i < n ? in[base + i] : 0;
+    }
+    double d[16];
+    if (draws) {
+        for (int i = 0; i < 16; ++i) d[i] = base + i < n ? draws[base + i] : 0.0;
+    } else {
+        const uint2 key = make_uint2(static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            const uint64_t ctr = offset + t * 4 + g;
+            const uint4 r = philox4x32_10(make_uint4(static_cast<uint32_t>(ctr), static_cast<uint32_t>(ctr >> 32), 2u + KIND, 0u), key);
+            const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+            if (KIND == 1) {
+                float z0, z1, z2, z3;
+                box_muller(r.x, r.y, z0, z1);
+                box_muller(r.z, r.w, z2, z3);
+                d[4 * g + 0] = static_cast<double>(fmaf(p1, z0, p0));
+                d[4 * g + 1] = static_cast<double>(fmaf(p1, z1, p0));
+                d[4 * g + 2] = static_cast<double>(fmaf(p1, z2, p0));
+                d[4 * g + 3] = static_cast<double>(fmaf(p1, z3, p0));
+            } else if (KIND == 2) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                    d[4 * g + e] = static_cast<double>(p0) + static_cast<double>(p1 - p0) * (static_cast<double>(w[e]) * (1.0 / 4294967296.0));
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float lam = static_cast<float>(px[4 * g + e]);
+                    const float u = u32_to_unit_open(w[e]);
+                    float k;
+                    if (lam < 24.f) {  // inversion: smallest k with CDF(k) >= u
+                        float pk = expf(-lam), cdf = pk;
+                        k = 0.f;
+                        while (cdf < u && k < 96.f) {
+                            k += 1.f;
+                            pk *= lam / k;
+                            cdf += pk;
+                        }
+                    } else {           // N(lam, lam) rounded; the second uniform comes from a scrambled copy of the word
+                        float z0, z1;
+                        box_muller(w[e], w[e] * 2654435761u + 0x9E3779B9u, z0, z1);
+                        k = fmaxf(floorf(lam + sqrtf(lam) * z0 + 0.5f), 0.f);
+                    }
+                    d[4 * g + e] = static_cast<double>(k);
+                }
+            }
+        }
+    }
+    uint8_t o[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const double x = static_cast<double>(px[i]);
+        if (KIND == 1) o[i] = clip_trunc_u8(x + x * d[i]);
+        else if (KIND == 2) o[i] = clip_trunc_u8(x + d[i]);
+        else o[i] = static_cast<uint8_t>(static_cast<long long>(d[i]) & 0xff);  // int64 -> uint8 wraps
+    }
+    if (full) {
+        *reinterpret_cast<uint4*>(out + base) = *reinterpret_cast<const uint4*>(o);
+    } else {
+        for (int i = 0; i < 16; ++i)
+            if (base + i < n) out[base + i] = o[i];
+    }
+}
+
 __global__ void __launch_bounds__(256) copy_u8_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, size_t n) {
     const size_t base = (static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 16;
     if (base >= n) return;
@@ -143,6 +226,28 @@ int cid_noise_gaussian_u8(cid_handle h, const uint8_t* in, uint8_t* out, size_t 
     const size_t threads = (n + 15) / 16;
     const unsigned grid = static_cast<unsigned>((threads + 255) / 256);
     gaussian_u8_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(in, out, n, mean, sigma, noise, seed, offset);
+    CID_CHECK_CUDA(cudaGetLastError());
+    h->launches++;
+    return 0;
+}
+
+int cid_noise_elementwise_u8(cid_handle h, const uint8_t* in, uint8_t* out, size_t n, int kind, float p0, float p1,
+                             const double* draws, uint64_t seed, uint64_t offset, void* stream) {
+    CID_REQUIRE(h && in && out, "cid_noise_elementwise_u8: null argument");
+    CID_REQUIRE(kind >= 0 && kind <= 3, "unknown noise kind %d (0 gaussian, 1 speckle, 2 uniform, 3 poisson)", kind);
+    if (kind == 0) return cid_noise_gaussian_u8(h, in, out, n, p0, p1, draws, seed, offset, stream);
+    if (n == 0) return 0;
+    DeviceGuard g(h->device);
+    CID_REQUIRE(g.ok, "cannot select CUDA device %d", h->device);
+    const size_t threads = (n + 15) / 16;
+    const unsigned grid = static_cast<unsigned>((threads + 255) / 256);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (kind == 1)
+        elementwise_noise_kernel<1><<<grid, 256, 0, st>>>(in, out, n, p0, p1, draws, seed, offset);
+    else if (kind == 2)
+        elementwise_noise_kernel<2><<<grid, 256, 0, st>>>(in, out, n, p0, p1, draws, seed, offset);
+    else
+        elementwise_noise_kernel<3><<<grid, 256, 0, st>>>(in, out, n, p0, p1, draws, seed, offset);
     CID_CHECK_CUDA(cudaGetLastError());
     h->launches++;
     return 0;

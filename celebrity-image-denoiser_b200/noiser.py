@@ -49,6 +49,45 @@ def add_gaussian_noise(image: torch.Tensor, mean: float = 0.0, sigma: float = 25
     return out
 
 
+def _elementwise(image: torch.Tensor, kind: int, p0: float, p1: float, seed: int, offset: int,
+                 draws: Optional[torch.Tensor]) -> torch.Tensor:
+    eng = _engine(image.device)
+    x = image.contiguous()
+    if x.dtype != torch.uint8:
+        raise RuntimeError("image must be uint8")
+    out = torch.empty_like(x)
+    dptr = None
+    if draws is not None:
+        draws = draws.to(device=x.device, dtype=torch.float64).contiguous()
+        if draws.numel() != x.numel():
+            raise RuntimeError("draws must have the image's number of elements")
+        dptr = C.c_void_p(draws.data_ptr())
+    stream = torch.cuda.current_stream(x.device).cuda_stream
+    _lib.check(eng.lib.cid_noise_elementwise_u8(eng.handle, C.c_void_p(x.data_ptr()), C.c_void_p(out.data_ptr()),
+                                                x.numel(), kind, float(p0), float(p1), dptr, seed, offset,
+                                                C.c_void_p(stream)), "cid_noise_elementwise_u8")
+    return out
+
+
+def add_speckle_noise(image: torch.Tensor, mean: float = 0.0, sigma: float = 0.1, *, seed: int = 0, offset: int = 0,
+                      noise: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """u8(clip(image + image * N(mean, sigma), 0, 255)) (noise_generation.py:24-28). `noise`: the normal draws."""
+    return _elementwise(image, 1, mean, sigma, seed, offset, noise)
+
+
+def add_uniform_noise(image: torch.Tensor, low: float = 0.0, high: float = 25.0, *, seed: int = 0, offset: int = 0,
+                      noise: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """u8(clip(image + U(low, high), 0, 255)) (noise_generation.py:35-39). `noise`: the uniform draws."""
+    return _elementwise(image, 2, low, high, seed, offset, noise)
+
+
+def add_poisson_noise(image: torch.Tensor, *, seed: int = 0, offset: int = 0,
+                      counts: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """np.random.poisson(image).astype(np.uint8) (noise_generation.py:30-33; counts above 255 wrap).
+    `counts`: the reference's own Poisson draws."""
+    return _elementwise(image, 3, 0.0, 0.0, seed, offset, counts)
+
+
 def add_salt_pepper_noise(image: torch.Tensor, salt_prob: float = 0.02, pepper_prob: float = 0.02, *, seed: int = 0,
                           offset: int = 0, coords: Optional[torch.Tensor] = None) -> torch.Tensor:
     """image: CUDA uint8 [H,W,C] or [B,H,W,C]. coords: optional CUDA int32 [B, n_salt+n_pepper, 2]

@@ -121,6 +121,16 @@ int cid_forward_u8_nhwc(cid_handle h, const uint8_t* x, uint8_t* y, int B, int H
 int cid_noise_gaussian_u8(cid_handle h, const uint8_t* in, uint8_t* out, size_t n, float mean, float sigma,
                           const double* noise, uint64_t seed, uint64_t offset, void* stream);
 
+/* The generator's other element-wise noise types (noise_generation.py:24-39), float64 arithmetic as numpy:
+ *   kind 0 gaussian (p0 = mean, p1 = sigma)  = cid_noise_gaussian_u8
+ *   kind 1 speckle  add_speckle_noise (:24-28)  u8(clip(x + x * N(p0, p1), 0, 255))
+ *   kind 2 uniform  add_uniform_noise (:35-39)  u8(clip(x + U(p0, p1), 0, 255))
+ *   kind 3 poisson  add_poisson_noise (:30-33)  np.random.poisson(x).astype(np.uint8)  (int64 -> u8 wraps mod 256)
+ * draws (device float64, n values) = the reference's own random array (normal / uniform / the Poisson counts) for
+ * bit-exact parity; NULL = Philox4x32-10 on the device (statistical parity). */
+int cid_noise_elementwise_u8(cid_handle h, const uint8_t* in, uint8_t* out, size_t n, int kind, float p0, float p1,
+                             const double* draws, uint64_t seed, uint64_t offset, void* stream);
+
 /* Salt & pepper: replaces add_salt_pepper_noise (noise_generation.py:12-22). Per image
  * [H,W,C]: n_salt = int(H*W*C*salt_prob) pixel coordinates set to 255 on all channels, then
  * n_pepper set to 0. If coords (device int32 [B][n_salt+n_pepper][2] = (row,col)) is non-NULL

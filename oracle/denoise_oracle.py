@@ -191,6 +191,21 @@ def gaussian_noise_apply(image: np.ndarray, noise: np.ndarray) -> np.ndarray:
     return np.clip(image + noise.astype(np.float64), 0, 255).astype(np.uint8)
 
 
+def speckle_noise_apply(image: np.ndarray, noise: np.ndarray) -> np.ndarray:
+    """add_speckle_noise (:24-28) with the normal draws made explicit: clip(x + x * noise, 0, 255).astype(u8)."""
+    return np.clip(image + image * noise, 0, 255).astype(np.uint8)
+
+
+def uniform_noise_apply(image: np.ndarray, noise: np.ndarray) -> np.ndarray:
+    """add_uniform_noise (:35-39) with the uniform draws made explicit."""
+    return np.clip(image + noise, 0, 255).astype(np.uint8)
+
+
+def poisson_noise_apply(counts: np.ndarray) -> np.ndarray:
+    """add_poisson_noise (:30-33): np.random.poisson(image).astype(np.uint8) — the int64 counts WRAP mod 256."""
+    return counts.astype(np.uint8)
+
+
 def salt_pepper_counts(shape_hwc: Tuple[int, int, int], salt_prob: float, pepper_prob: float) -> Tuple[int, int]:
     """num_salt / num_pepper = int(image_array.size * prob) (:15-17) — size counts channels."""
     total = shape_hwc[0] * shape_hwc[1] * shape_hwc[2]

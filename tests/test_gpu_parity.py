@@ -334,6 +334,34 @@ def test_noiser_supplied_draws_bit_exact(dev, golden_dir, name):
     assert np.array_equal(sp.cpu().numpy(), g["sp_out"])
 
 
+@pytest.mark.parametrize("name", ["noise_more_32x32", "noise_more_17x23"])
+def test_more_noise_types_supplied_draws_bit_exact(dev, golden_dir, name):
+    """speckle / uniform / poisson (noise_generation.py:24-39) with the reference's own draws: bit-exact,
+    including the uint8 wrap of Poisson counts above 255."""
+    g = np.load(golden_dir / (name + ".npz"))
+    img = torch.from_numpy(g["image"]).to(dev)
+    out = cu_noiser.add_speckle_noise(img, noise=torch.from_numpy(g["speckle_draws"]).to(dev))
+    assert np.array_equal(out.cpu().numpy(), g["speckle_out"])
+    out = cu_noiser.add_uniform_noise(img, noise=torch.from_numpy(g["uniform_draws"]).to(dev))
+    assert np.array_equal(out.cpu().numpy(), g["uniform_out"])
+    out = cu_noiser.add_poisson_noise(img, counts=torch.from_numpy(g["poisson_counts"]).to(dev))
+    assert np.array_equal(out.cpu().numpy(), g["poisson_out"])
+
+
+def test_more_noise_types_philox_statistics(dev):
+    flat = torch.full((4, 256, 256, 3), 100, dtype=torch.uint8, device=dev)
+    spk = cu_noiser.add_speckle_noise(flat, 0.0, 0.1, seed=3).float()      # 100 + 100*N(0,0.1): std 10
+    assert abs(float(spk.mean()) - 99.5) < 0.3 and abs(float(spk.std()) - 10.0) < 0.3
+    uni = cu_noiser.add_uniform_noise(flat, 0.0, 25.0, seed=4).float()      # 100 + U(0,25), truncated
+    assert float(uni.min()) >= 100 and float(uni.max()) <= 124 and abs(float(uni.mean()) - 112.0) < 0.3
+    for lam in (3, 40, 200):
+        img = torch.full((4, 256, 256, 3), lam, dtype=torch.uint8, device=dev)
+        poi = cu_noiser.add_poisson_noise(img, seed=5 + lam).float()
+        assert abs(float(poi.mean()) - lam) < 0.05 * lam ** 0.5 + 0.1       # mean = lambda
+        assert abs(float(poi.var()) - lam) < 0.05 * lam + 0.2               # variance = lambda
+    assert torch.equal(cu_noiser.add_poisson_noise(flat, seed=1), cu_noiser.add_poisson_noise(flat, seed=1))
+
+
 def test_noiser_philox_statistics(dev):
     """Statistical parity of the on-device RNG: sigma=25 on a flat 128 image gives mean ~127.1 and
     std ~24.8 after the truncating cast (SURVEY.md §8c probe of the reference)."""

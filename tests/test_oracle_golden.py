@@ -78,6 +78,15 @@ def test_noiser_bit_exact(golden_dir, name):
     assert g["salt_rc"][:, 0].max() < img.shape[0] - 1 and g["salt_rc"][:, 1].max() < img.shape[1] - 1
 
 
+@pytest.mark.parametrize("name", ["noise_more_32x32", "noise_more_17x23"])
+def test_more_noise_types_bit_exact(golden_dir, name):
+    g = _load(golden_dir, name + ".npz")
+    img = g["image"]
+    assert np.array_equal(orc.speckle_noise_apply(img, g["speckle_draws"]), g["speckle_out"])
+    assert np.array_equal(orc.uniform_noise_apply(img, g["uniform_draws"]), g["uniform_out"])
+    assert np.array_equal(orc.poisson_noise_apply(g["poisson_counts"]), g["poisson_out"])
+
+
 def test_resize_bit_exact_vs_pillow(golden_dir):
     files = sorted(glob.glob(str(golden_dir / "resize_*.npz")))
     assert len(files) >= 5
