@@ -47,12 +47,12 @@ LAYER_FLOP_PER_PIXEL = {
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch at batch 256 of 128x128, from the committed
-# `ncu --set full` capture profiles/r01d_ncu_full_batch256.md (MB); scaled linearly for other batches/sizes.
+# `ncu --set full` capture profiles/r01i_ncu_full_batch256.md (MB); scaled linearly for other batches/sizes.
 NCU_TRAFFIC_MB_B256_128 = {
-    "down1.0": 13.00 + 476.66, "down1.2": 537.11 + 616.16, "down2.0": 134.44 + 208.38, "down2.2": 268.89 + 284.23,
-    "bottleneck.0": 67.77 + 76.30, "bottleneck.2": 135.45 + 89.83, "up2": 134.53 + 210.12,
-    "upconv2.0": 537.52 + 238.15, "upconv2.2": 268.82 + 222.97, "up1": 268.53 + 479.22,
-    "upconv1.0": 1075.0 + 506.73, "upconv1.2": 536.99 + 7.87,
+    "down1.0": 13.41 + 476.60, "down1.2": 537.07 + 616.13, "down2.0": 134.45 + 208.42, "down2.2": 268.86 + 284.56,
+    "bottleneck.0": 67.77 + 76.91, "bottleneck.2": 135.45 + 89.74, "up2": 134.51 + 210.47,
+    "upconv2.0": 537.52 + 238.86, "upconv2.2": 268.82 + 223.15, "up1": 268.53 + 478.73,
+    "upconv1.0": 1074.0 + 506.96, "upconv1.2": 536.94 + 8.01,
 }
 
 
@@ -296,7 +296,7 @@ def main():
         roofline = {"bound": "tensor", "kernel": f"conv_umma_kernel[{dom}]", "achieved": achieved,
                     "peak": peaks["bf16"], "unit": "TFLOP/s", "frac": achieved / peaks["bf16"],
                     "traffic": NCU_TRAFFIC_MB_B256_128[dom] * 1e6 * (imgs_per_pass * H * W) / (256 * 128 * 128),
-                    "traffic_source": "dram__bytes_read+write per launch, ncu --set full (profiles/r01d_ncu_full_batch256.md), "
+                    "traffic_source": "dram__bytes_read+write per launch, ncu --set full (profiles/r01i_ncu_full_batch256.md), "
                                       "scaled to this launch's pixel count",
                     "peak_source": f"{peaks['source']} burst bf16 (MEASURED_PEAKS.json bf16_tflops)",
                     "flops_per_launch": dom_flops, "ms_per_launch": dom_ms}
