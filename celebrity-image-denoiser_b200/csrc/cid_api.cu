@@ -591,6 +591,7 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
 }  // namespace cid
 #include "cgan_model.cuh"
 #include "sr_model.cuh"
+#include "train_model.cuh"
 namespace cid {
 
 static int chunk_of(const cid_ctx* c, int B) {
@@ -640,7 +641,7 @@ using namespace cid;
 // =============================================================================================
 extern "C" {
 
-int cid_version(void) { return 4; }
+int cid_version(void) { return 5; }
 
 const char* cid_last_error(void) { return g_err; }
 
@@ -924,6 +925,230 @@ int cid_debug_copy_activation(cid_handle h, const char* name, const void* ws, in
     if (channels) *channels = kBufC[b];
     if (height) *height = H >> lv;
     if (width) *width = W >> lv;
+    return 0;
+}
+
+
+// =============================================================================================
+// training step
+// =============================================================================================
+int cid_train_create(int device, cid_train_handle* out) {
+    CID_REQUIRE(out, "cid_train_create: out is NULL");
+    *out = nullptr;
+    cid_handle g = nullptr;
+    if (cid_create_model(device, "denoise", &g)) return 1;
+    cid_train* t = new cid_train();
+    t->g = g;
+    t->device = device;
+    t->num_sms = g->num_sms;
+    t->max_smem = g->max_smem;
+    train_build_table(t);
+    DeviceGuard dg(device);
+    if (!dg.ok || train_alloc_packs(t)) {
+        cid_train_destroy(t);
+        return 1;
+    }
+    *out = t;
+    return 0;
+}
+
+int cid_train_destroy(cid_train_handle t) {
+    if (!t) return 0;
+    {
+        DeviceGuard dg(t->device);
+        for (int l = 0; l < 12; ++l)
+            if (t->gd_w[l]) cudaFree(t->gd_w[l]);
+        for (int l = 0; l < 4; ++l) {
+            if (t->df_w[l]) cudaFree(t->df_w[l]);
+            if (t->dd_w[l]) cudaFree(t->dd_w[l]);
+            if (t->d_bias_pad[l]) cudaFree(t->d_bias_pad[l]);
+        }
+        if (t->zero_bias) cudaFree(t->zero_bias);
+        if (t->dsc) cudaFree(t->dsc);
+        if (t->fsc) cudaFree(t->fsc);
+    }
+    cid_destroy(t->g);
+    delete t;
+    return 0;
+}
+
+int cid_train_state_floats(cid_train_handle t, size_t* n) {
+    CID_REQUIRE(t && n, "cid_train_state_floats: null argument");
+    *n = 4 * train_P(t) + t->n_buf;
+    return 0;
+}
+
+int cid_train_bind_state(cid_train_handle t, float* state, size_t n) {
+    CID_REQUIRE(t && state, "cid_train_bind_state: null argument");
+    CID_REQUIRE(n >= 4 * train_P(t) + t->n_buf, "state buffer too small: %zu < %zu floats", n, 4 * train_P(t) + t->n_buf);
+    CID_REQUIRE((reinterpret_cast<uintptr_t>(state) & 15) == 0, "state buffer must be 16-byte aligned");
+    t->state = state;
+    t->state_floats = n;
+    return 0;
+}
+
+int cid_train_tensor(cid_train_handle t, const char* key, int section, size_t* offset, size_t* numel) {
+    CID_REQUIRE(t && key && offset && numel, "cid_train_tensor: null argument");
+    CID_REQUIRE(section >= 0 && section < 4, "section %d out of range (0 params, 1 grads, 2 adam m, 3 adam v)", section);
+    const TrainTensor* x = train_find(t, key);
+    CID_REQUIRE(x, "unknown training tensor '%s'", key);
+    CID_REQUIRE(!x->buffer || section == 0, "'%s' is a buffer: it has no gradient or Adam state", key);
+    *offset = x->buffer ? 4 * train_P(t) + x->off : section * train_P(t) + x->off;
+    *numel = x->n;
+    return 0;
+}
+
+int cid_train_tensor_count(cid_train_handle t) { return t ? static_cast<int>(t->tensors.size()) : -1; }
+
+const char* cid_train_tensor_name(cid_train_handle t, int index) {
+    if (!t || index < 0 || index >= static_cast<int>(t->tensors.size())) return nullptr;
+    return t->tensors[index].key.c_str();
+}
+
+int cid_train_section(cid_train_handle t, const char* net, int section, size_t* offset, size_t* numel) {
+    CID_REQUIRE(t && net && offset && numel, "cid_train_section: null argument");
+    CID_REQUIRE(section >= 0 && section < 4, "section %d out of range", section);
+    const bool g = !strcmp(net, "generator"), d = !strcmp(net, "discriminator");
+    CID_REQUIRE(g || d, "unknown network '%s' (generator | discriminator)", net);
+    *offset = section * train_P(t) + (g ? 0 : t->n_g);
+    *numel = g ? t->n_g : t->n_d;
+    return 0;
+}
+
+int cid_train_sync_weights(cid_train_handle t, void* stream) {
+    CID_REQUIRE(t && t->state, "cid_train_sync_weights: state not bound");
+    DeviceGuard dg(t->device);
+    CID_REQUIRE(dg.ok, "cannot select CUDA device %d", t->device);
+    return train_repack(t, 3, static_cast<cudaStream_t>(stream));
+}
+
+int cid_train_workspace_bytes(cid_train_handle t, int B, int H, int W, size_t* bytes) {
+    CID_REQUIRE(t && bytes, "cid_train_workspace_bytes: null argument");
+    CID_REQUIRE(B >= 1 && H >= 4 && W >= 4 && H % 4 == 0 && W % 4 == 0, "bad shape B=%d H=%d W=%d", B, H, W);
+    *bytes = train_layout(B, H, W, nullptr);
+    return 0;
+}
+
+int cid_train_d_backward(cid_train_handle t, const float* noisy, const float* clean, int B, int H, int W, void* ws,
+                         size_t ws_bytes, void* stream) {
+    CID_REQUIRE(t && noisy && clean, "cid_train_d_backward: null argument");
+    DeviceGuard dg(t->device);
+    CID_REQUIRE(dg.ok, "cannot select CUDA device %d", t->device);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    TrainRun r;
+    if (train_make_run(t, B, H, W, ws, ws_bytes, st, &r)) return 1;
+    t->B = B; t->H = H; t->W = W; t->ws = ws;
+    CID_CHECK_CUDA(cudaMemsetAsync(t->state + train_P(t) + t->n_g, 0, t->n_d * 4, st));
+    CID_CHECK_CUDA(cudaMemsetAsync(t->dsc + DS_LOSS, 0, 2 * 8, st));
+    // denoised = G(noisy)  (training.py:411)
+    cid_plan* pl = nullptr;
+    if (get_plan(t->g, B, H, W, ws, &pl)) return 1;
+    IoSpec io;
+    memset(&io, 0, sizeof(io));
+    io.u8 = false;
+    io.x = noisy;
+    io.y = r.tbuf(TB_Y);
+    const int64_t l0 = t->g->launches;
+    if (run_layers(t->g, pl, B, io, st)) return 1;
+    t->launches += t->g->launches - l0;
+    // d_loss = BCE(D(clean), 1) + BCE(D(denoised.detach()), 0)  (:412-415)
+    if (d_forward(r, clean)) return 1;
+    if (d_backward(r, clean, 1.f, 1.f, 0, true, false)) return 1;
+    const float* fake = static_cast<const float*>(r.tbuf(TB_Y));
+    if (d_forward(r, fake)) return 1;
+    if (d_backward(r, fake, 0.f, 1.f, 1, true, false)) return 1;
+    return 0;
+}
+
+int cid_train_g_backward(cid_train_handle t, const float* noisy, const float* clean, int B, int H, int W, void* ws,
+                         size_t ws_bytes, void* stream) {
+    CID_REQUIRE(t && noisy && clean, "cid_train_g_backward: null argument");
+    CID_REQUIRE(t->ws == ws && t->B == B && t->H == H && t->W == W,
+                "cid_train_g_backward continues the cid_train_d_backward call of the same batch and workspace");
+    DeviceGuard dg(t->device);
+    CID_REQUIRE(dg.ok, "cannot select CUDA device %d", t->device);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    TrainRun r;
+    if (train_make_run(t, B, H, W, ws, ws_bytes, st, &r)) return 1;
+    CID_CHECK_CUDA(cudaMemsetAsync(t->state + train_P(t), 0, t->n_g * 4, st));
+    CID_CHECK_CUDA(cudaMemsetAsync(t->dsc + DS_LOSS + 2, 0, 2 * 8, st));
+    // fake_pred = D(denoised); adv = BCE(fake_pred, 1); g_loss = MSE + 0.001 * adv  (:419-423)
+    const float* fake = static_cast<const float*>(r.tbuf(TB_Y));
+    if (d_forward(r, fake)) return 1;
+    if (d_backward(r, fake, 1.f, 0.001f, 2, false, true)) return 1;
+    {
+        GLossParams p;
+        p.B = B; p.H = H; p.W = W;
+        p.y = fake;
+        p.clean = clean;
+        p.gx = static_cast<const float*>(r.tbuf(TB_GX));
+        p.gz = static_cast<float*>(r.tbuf(TB_GZ));
+        p.loss_sum = t->dsc + DS_LOSS + 3;
+        p.bias_grad = train_ptr(t, "generator.upconv1.2.bias", 1);
+        p.inv_n = 1.f / (static_cast<float>(B) * 3.f * H * W);
+        gloss_kernel<<<static_cast<unsigned>((r.pixels(0) + 255) / 256), 256, 0, st>>>(p);
+        CID_CHECK_CUDA(cudaGetLastError());
+        t->launches++;
+    }
+    return g_backward_layers(r, noisy);
+}
+
+int cid_train_adam(cid_train_handle t, int which, float lr, float beta1, float beta2, float eps, void* stream) {
+    CID_REQUIRE(t && t->state, "cid_train_adam: state not bound");
+    CID_REQUIRE(which == 0 || which == 1, "which = 0 (generator) or 1 (discriminator)");
+    DeviceGuard dg(t->device);
+    CID_REQUIRE(dg.ok, "cannot select CUDA device %d", t->device);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t P = train_P(t), off = which ? t->n_g : 0, n = which ? t->n_d : t->n_g;
+    const int64_t step = which ? ++t->step_d : ++t->step_g;
+    const float bc1 = 1.f - powf(beta1, static_cast<float>(step));
+    const float bc2 = sqrtf(1.f - powf(beta2, static_cast<float>(step)));
+    adam_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(t->state + off, t->state + P + off, t->state + 2 * P + off,
+                                                                        t->state + 3 * P + off, n, lr, beta1, beta2, eps, bc1, bc2);
+    CID_CHECK_CUDA(cudaGetLastError());
+    t->launches++;
+    return train_repack(t, which ? 2 : 1, st);
+}
+
+int cid_train_losses(cid_train_handle t, double* out4) {
+    CID_REQUIRE(t && out4, "cid_train_losses: null argument");
+    DeviceGuard dg(t->device);
+    CID_REQUIRE(dg.ok, "cannot select CUDA device %d", t->device);
+    double h[4];
+    CID_CHECK_CUDA(cudaDeviceSynchronize());
+    CID_CHECK_CUDA(cudaMemcpy(h, t->dsc + DS_LOSS, sizeof(h), cudaMemcpyDeviceToHost));
+    out4[0] = h[0] + h[1];          // d_loss
+    out4[1] = h[3] + 0.001 * h[2];  // g_loss
+    out4[2] = h[3];                 // content (MSE)
+    out4[3] = h[2];                 // adversarial (BCE)
+    return 0;
+}
+
+int64_t cid_train_kernel_launches(cid_train_handle t) { return t ? t->launches : -1; }
+
+int cid_train_debug_buffer(cid_train_handle t, const char* name, const void* ws, int B, int H, int W, void* dst_host,
+                           size_t dst_bytes, int* channels, int* level, int* elem_size) {
+    CID_REQUIRE(t && name && ws && dst_host, "cid_train_debug_buffer: null argument");
+    static const char* names[TB_COUNT] = {"y", "gz", "gx", "dz10", "gcat1", "dz8", "dz7", "gcat2", "dz5", "dz4", "gp2", "dz3", "dz2",
+                                          "gp1", "dz1", "dz0", "d_a0", "d_z1", "d_a1", "d_z2", "d_a2", "d_z3", "d_a3", "d_g3", "d_g2",
+                                          "d_g1", "d_g0"};
+    int b = -1;
+    for (int i = 0; i < TB_COUNT; ++i)
+        if (!strcmp(name, names[i])) b = i;
+    CID_REQUIRE(b >= 0, "unknown training buffer '%s'", name);
+    DeviceGuard dg(t->device);
+    CID_REQUIRE(dg.ok, "cannot select CUDA device %d", t->device);
+    size_t toff[TB_COUNT];
+    train_layout(B, H, W, toff);
+    const int lv = kTBufLevel[b];
+    const size_t es = b <= TB_GX ? 4 : 2;
+    const size_t n = static_cast<size_t>(B) * (H >> lv) * (W >> lv) * kTBufC[b] * es;
+    CID_REQUIRE(dst_bytes >= n, "destination too small: %zu < %zu", dst_bytes, n);
+    CID_CHECK_CUDA(cudaDeviceSynchronize());
+    CID_CHECK_CUDA(cudaMemcpy(dst_host, static_cast<const uint8_t*>(ws) + toff[b], n, cudaMemcpyDeviceToHost));
+    if (channels) *channels = kTBufC[b];
+    if (level) *level = lv;
+    if (elem_size) *elem_size = static_cast<int>(es);
     return 0;
 }
 

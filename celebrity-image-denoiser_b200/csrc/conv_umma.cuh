@@ -30,7 +30,9 @@ namespace cid {
 
 enum : int {  // TANH_*: last_conv_umma.cuh; LRELU/T4: the Keras cGAN layers (leaky ReLU with ConvParams::slope)
     EPI_RELU = 0, EPI_RELU_POOL = 1, EPI_CONVT = 2, EPI_TANH_F32 = 3, EPI_TANH_U8 = 4, EPI_LRELU = 5, EPI_T4 = 6, EPI_TANH_F32_NHWC = 7,
-    EPI_ADD = 8  // bias + residual add(s), no activation (ESRGAN / SRGAN skip connections)
+    EPI_ADD = 8,  // bias + residual add(s), no activation (ESRGAN / SRGAN skip connections)
+    EPI_DGRAD = 9  // training: data gradient = bias-free linear output, optionally masked by the ReLU of the layer's
+                   // own input activation (ConvParams::res2 = that activation, > 0 keeps the gradient)
 };
 
 constexpr int kConvThreads = 320;  // warp 0 TMA, warp 1 MMA, warps 2..9 two epilogue groups
@@ -72,6 +74,9 @@ struct ConvParams {
 //        output row phase py; the accumulator holds both column phases px (2*N columns). Output
 //        (2y+py, 2x+px) sums input (y-1+ty, x-1+tx) * w[ky = py+3-2ty, kx = px+3-2tx] over ty in {py,py+1}
 //        and the (tx,px) pairs (0,0) (1,0) (1,1) (2,1): 8 MMA steps of width N over the 3x3 halo patch.
+//   4  = 2x2 stride 2 pad 0 (the data gradient of ConvTranspose2d k2 s2, training only): a K block is (64 input
+//        channels, input phase (phy,phx)); its box {64 ch, 8 px, 16 rows} is a stride-2 TMA box starting at input pixel
+//        (2*y0+phy, 2*x0+phx) and serves the single tap (phy,phx).
 // CG = 2: CTA pairs (cluster of 2, tcgen05 cta_group::2). Each CTA owns its own S pixel tiles (A operand,
 //         accumulators, epilogue) but only HALF of every weight tile (N/2 rows); the leader CTA's MMAs
 //         read both halves, so the per-SM shared-memory traffic of the B operand is halved.
@@ -79,15 +84,15 @@ template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0, int TS = 0, in
 struct ConvCfg {
     static_assert(CG == 1 || CG == 2, "single CTA or CTA pair");
     static_assert(CG == 1 || N % 32 == 0, "pair mode: each CTA holds N/2 weight rows, N multiple of 16 for M=256");
-    static_assert(TAPS == 9 || TAPS == 1 || TAPS == 16 || TAPS == 8, "3x3, 1x1, 4x4 s2 or transposed 4x4 s2");
+    static_assert(TAPS == 9 || TAPS == 1 || TAPS == 16 || TAPS == 8 || TAPS == 4, "3x3, 1x1, 4x4 s2, transposed 4x4 s2 or 2x2 s2");
     static_assert(N % 16 == 0 && N >= 16 && N <= 256, "UMMA N for M=128");
-    static constexpr bool K4 = TAPS == 16, T4 = TAPS == 8;
-    static_assert(!(K4 || T4) || !WRES, "4x4 layers stream their weights");
+    static constexpr bool K4 = TAPS == 16, T4 = TAPS == 8, K2 = TAPS == 4;
+    static_assert(!(K4 || T4 || K2) || !WRES, "stride-2 layers stream their weights");
     static constexpr int DX = (TAPS == 9 || T4) ? 3 : K4 ? 2 : 1;
     static constexpr int DY = DX;
     static_assert(PW == (DX == 1 ? 0 : 8 + DX - 1), "patch width = 8 + DX - 1 (0 = plain box for 1x1)");
     static constexpr int STEPS = TAPS == 9 ? 9 : K4 ? 4 : T4 ? 8 : 1;  // weight tiles (MMA steps) per K block
-    static constexpr int KSUB = K4 ? 4 : 1;                            // K blocks per 64 input channels
+    static constexpr int KSUB = (K4 || K2) ? 4 : 1;                    // K blocks per 64 input channels
     static constexpr int A_ROWS = 16 + DY - 1;
     static constexpr int A_TX = (PW ? PW : 8) * A_ROWS * 128;   // bytes one box delivers
     static constexpr int A_BYTES = (A_TX + 1023) / 1024 * 1024; // stage pitch (1024-B aligned)
@@ -137,6 +142,8 @@ struct StepMap {
             const int tx = (q + 1) >> 1, px = q >> 1;
             a_px = ty * PW + tx; w_tap = (nt + 3 - 2 * ty) * 4 + (px + 3 - 2 * tx); d_col = px * N;
             first = (step == 0 || step == 2);
+        } else if constexpr (TAPS == 4) {
+            a_px = 0; w_tap = sub; d_col = 0; first = true;
         } else {
             a_px = 0; w_tap = 0; d_col = 0; first = true;
         }
@@ -309,8 +316,12 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     for (int s = 0; s < S; ++s) {
                         // patch origin in the A tensor: 3x3 / transposed 4x4 halo starts one pixel up-left;
                         // 4x4 s2 reads input phase (phy,phx) of the 2x larger input through a stride-2 box
-                        const int ax = Cfg::K4 ? 2 * tc[s].x0 - 1 + (sub & 1) : tc[s].x0 - (Cfg::DX == 3 ? 1 : 0);
-                        const int ay = Cfg::K4 ? 2 * tc[s].y0 - 1 + (sub >> 1) : tc[s].y0 - (Cfg::DY == 3 ? 1 : 0);
+                        const int ax = Cfg::K4   ? 2 * tc[s].x0 - 1 + (sub & 1)
+                                       : Cfg::K2 ? 2 * tc[s].x0 + (sub & 1)
+                                                 : tc[s].x0 - (Cfg::DX == 3 ? 1 : 0);
+                        const int ay = Cfg::K4   ? 2 * tc[s].y0 - 1 + (sub >> 1)
+                                       : Cfg::K2 ? 2 * tc[s].y0 + (sub >> 1)
+                                                 : tc[s].y0 - (Cfg::DY == 3 ? 1 : 0);
                         mbar_wait(&a_empty[a_stage], a_phase ^ 1);
                         expect(&a_full[a_stage], Cfg::A_TX);
                         if (PAIR)
@@ -476,14 +487,14 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             tc_fence_after();
             const uint32_t tbase = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * Cfg::ACC_COLS;
             if (!(p.debug_flags & 2)) {
-                if constexpr (EPI == EPI_RELU || EPI == EPI_RELU_POOL || EPI == EPI_LRELU || EPI == EPI_ADD) {
+                if constexpr (EPI == EPI_RELU || EPI == EPI_RELU_POOL || EPI == EPI_LRELU || EPI == EPI_ADD || EPI == EPI_DGRAD) {
                     constexpr int SL = N / 64;  // 64-channel slabs per pixel tile
                     const int sub = (xl & 1) | ((yl & 1) << 1);
                     const int prow_i = (yl >> 1) * 4 + (xl >> 1);
                     const float slope = p.slope;
                     auto act = [&](float x) {  // ReLU, or LeakyReLU(slope) for the Keras layers
                         if constexpr (EPI == EPI_LRELU) return x > 0.f ? x : x * slope;
-                        if constexpr (EPI == EPI_ADD) return x;
+                        if constexpr (EPI == EPI_ADD || EPI == EPI_DGRAD) return x;
                         return fmaxf(x, 0.f);
                     };
                     (void)slope;
@@ -500,7 +511,21 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         named_bar_sync(bar_id, 128);
                         // EPI_ADD: the optional SECOND residual (ESRGAN's long skip, last block only) comes straight from
                         // global memory, this thread's pixel = one 128-byte line
-                        uint4 rv2[EPI == EPI_ADD ? 8 : 1];
+                        uint4 rv2[(EPI == EPI_ADD || EPI == EPI_DGRAD) ? 8 : 1];
+                        if constexpr (EPI == EPI_DGRAD) {
+                            // ReLU mask: this thread's pixel of the layer's input activation, one 128-byte line
+                            const int yy = tc.y0 + yl, xx = tc.x0 + xl;
+                            const bool live = tc.b < p.B && yy < p.H && xx < p.W;
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) rv2[i] = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
+                            if (live && p.res2 != nullptr) {
+                                const size_t pix = (static_cast<size_t>(tc.b) * p.H + yy) * p.W + xx;
+                                const uint4* r2 = reinterpret_cast<const uint4*>(
+                                    static_cast<const uint16_t*>(p.res2) + pix * p.res2_cs + n_tile * N + cs * 64);
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) rv2[i] = __ldg(r2 + i);
+                            }
+                        }
                         if constexpr (EPI == EPI_ADD) {
                             const int yy = tc.y0 + yl, xx = tc.x0 + xl;
                             const bool live = tc.b < p.B && yy < p.H && xx < p.W;
@@ -539,9 +564,23 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                     }
                                 }
                             }
+                            if constexpr (EPI == EPI_DGRAD) {
+                                // zero the gradient where the activation (bf16, post-ReLU: >= 0) is not positive
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) {
+                                    const uint4 m = rv2[ch * 4 + i];
+                                    const uint32_t w[4] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+                                    for (int e = 0; e < 4; ++e) {
+                                        const int col = (i * 4 + e) * 2;
+                                        if (!(__uint_as_float(w[e] << 16) > 0.f)) v[col] = 0u;
+                                        if (!(__uint_as_float(w[e] & 0xffff0000u) > 0.f)) v[col + 1] = 0u;
+                                    }
+                                }
+                            }
 #pragma unroll
                             for (int jj = 0; jj < 8; ++jj) {
-                                const float4 bb = __ldg(b4 + jj);
+                                const float4 bb = EPI == EPI_DGRAD ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldg(b4 + jj);
                                 const float f0 = act(__uint_as_float(v[4 * jj + 0]) + bb.x);
                                 const float f1 = act(__uint_as_float(v[4 * jj + 1]) + bb.y);
                                 const float f2 = act(__uint_as_float(v[4 * jj + 2]) + bb.z);

@@ -1,0 +1,683 @@
+// Memory-bound and small kernels of the training step: the 3-channel edge layers on CUDA cores,
+// MaxPool / ReLU / LeakyReLU / tanh backward, train-mode BatchNorm (statistics by block reductions), the
+// discriminator head with BCELoss, bias gradients (column sums), Adam and the fp32 -> bf16 weight re-pack.
+//
+// Reference ops (file:line in /root/reference/backend/trainingcode/denoise_gan_code/training.py):
+//   DenoiseDiscriminator                      :77-98   (Conv k3, LeakyReLU(0.2), Conv k3 s2, BatchNorm2d, AdaptiveAvgPool2d,
+//                                                       Conv k1, Sigmoid)
+//   nn.MSELoss / nn.BCELoss                   :234-235, 413-423
+//   optim.Adam(lr=1e-4, betas=(0.9,0.999))    :237-238, 416, 425
+//   autograd of DenoiseGenerator.forward      :19-74 (MaxPool2d, ReLU, tanh, torch.cat backward)
+#pragma once
+#include <cuda_bf16.h>
+
+#include "ptx.cuh"
+
+namespace cid {
+
+__device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
+
+__device__ __forceinline__ float block_sum(float v, float* red /* >= 32 floats */) {
+    __syncthreads();
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    const int nw = (blockDim.x + 31) >> 5;
+    float s = (threadIdx.x < nw) ? red[threadIdx.x] : 0.f;
+    if (threadIdx.x < 32) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    }
+    return s;  // valid in thread 0
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// 3 -> 64 3x3 convolution, pad 1 (CUDA cores): one thread = one pixel x 64 channels.
+//   forward (dgrad = 0): discriminator model.0 + LeakyReLU(0.2); w = [64][3][3][3], input fp32 NCHW.
+//   dgrad = 1: the data gradient of the generator's last conv (64 -> 3): a 3 -> 64 conv of the fp32 NHWC-3 gradient
+//   with tap-flipped weights w = [3][64][3][3], masked by the ReLU of that conv's input activation.
+// ---------------------------------------------------------------------------------------------------------------------
+struct Conv3to64Params {
+    int B, H, W;
+    const float* in;
+    int in_nchw;
+    const float* w;
+    const float* bias;            // may be null
+    float slope;                  // leaky slope (forward)
+    int dgrad;
+    const __nv_bfloat16* mask;    // dgrad: activation whose sign gates the gradient (NHWC 64), may be null
+    __nv_bfloat16* out;           // NHWC [B,H,W,64]
+};
+
+__global__ void __launch_bounds__(128) conv3to64_kernel(const Conv3to64Params p) {
+    __shared__ float ws[27][64];
+    __shared__ float bs[64];
+    for (int i = threadIdx.x; i < 27 * 64; i += 128) {
+        const int t = i >> 6, co = i & 63, ci = t / 9, tap = t % 9;
+        ws[t][co] = p.dgrad ? p.w[(ci * 64 + co) * 9 + 8 - tap] : p.w[(co * 3 + ci) * 9 + tap];
+    }
+    if (threadIdx.x < 64) bs[threadIdx.x] = p.bias ? p.bias[threadIdx.x] : 0.f;
+    __syncthreads();
+    const size_t total = static_cast<size_t>(p.B) * p.H * p.W;
+    const size_t pix = static_cast<size_t>(blockIdx.x) * 128 + threadIdx.x;
+    if (pix >= total) return;
+    const int x = static_cast<int>(pix % p.W);
+    const int y = static_cast<int>((pix / p.W) % p.H);
+    const int b = static_cast<int>(pix / (static_cast<size_t>(p.W) * p.H));
+    float in[27];
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) {
+            const int yy = y + ky - 1, xx = x + kx - 1;
+            const bool inside = yy >= 0 && yy < p.H && xx >= 0 && xx < p.W;
+#pragma unroll
+            for (int ci = 0; ci < 3; ++ci) {
+                float v = 0.f;
+                if (inside)
+                    v = p.in_nchw ? p.in[((static_cast<size_t>(b) * 3 + ci) * p.H + yy) * p.W + xx]
+                                  : p.in[((static_cast<size_t>(b) * p.H + yy) * p.W + xx) * 3 + ci];
+                in[ci * 9 + ky * 3 + kx] = v;
+            }
+        }
+    __nv_bfloat16* orow = p.out + pix * 64;
+    const uint4* mrow = p.mask ? reinterpret_cast<const uint4*>(p.mask + pix * 64) : nullptr;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+        float acc[32];
+#pragma unroll
+        for (int c = 0; c < 32; ++c) acc[c] = bs[half * 32 + c];
+#pragma unroll
+        for (int t = 0; t < 27; ++t)
+#pragma unroll
+            for (int c = 0; c < 32; ++c) acc[c] = fmaf(in[t], ws[t][half * 32 + c], acc[c]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float f[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) f[i] = acc[8 * j + i];
+            if (p.dgrad) {
+                if (mrow) {
+                    const uint4 m = __ldg(mrow + half * 4 + j);
+                    const uint32_t mw[4] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        if (!(bf16_lo(mw[i]) > 0.f)) f[2 * i] = 0.f;
+                        if (!(bf16_hi(mw[i]) > 0.f)) f[2 * i + 1] = 0.f;
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) f[i] = f[i] > 0.f ? f[i] : f[i] * p.slope;
+            }
+            st_global_v4(orow + half * 32 + j * 8, pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]),
+                         pack_bf16x2(f[6], f[7]));
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// 64 -> 3 data gradient of the discriminator's first conv: gx[p][ci] = sum_{tap,co} dz[p + 1 - tap][co] * w[co][ci][tap].
+// One thread = one pixel; fp32 NHWC-3 output.
+// ---------------------------------------------------------------------------------------------------------------------
+struct Conv64to3Params {
+    int B, H, W;
+    const __nv_bfloat16* dz;  // NHWC 64
+    const float* w;           // [64][3][3][3]
+    float* out;               // NHWC 3
+};
+
+__global__ void __launch_bounds__(128) conv64to3_dgrad_kernel(const Conv64to3Params p) {
+    __shared__ float ws[9][64][3];
+    for (int i = threadIdx.x; i < 9 * 64 * 3; i += 128) {
+        const int tap = i / 192, r = i % 192, co = r / 3, ci = r % 3;
+        ws[tap][co][ci] = p.w[(co * 3 + ci) * 9 + tap];
+    }
+    __syncthreads();
+    const size_t total = static_cast<size_t>(p.B) * p.H * p.W;
+    const size_t pix = static_cast<size_t>(blockIdx.x) * 128 + threadIdx.x;
+    if (pix >= total) return;
+    const int x = static_cast<int>(pix % p.W);
+    const int y = static_cast<int>((pix / p.W) % p.H);
+    const int b = static_cast<int>(pix / (static_cast<size_t>(p.W) * p.H));
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) {
+            const int yy = y + 1 - ky, xx = x + 1 - kx;
+            if (yy < 0 || yy >= p.H || xx < 0 || xx >= p.W) continue;
+            const uint4* src = reinterpret_cast<const uint4*>(p.dz + ((static_cast<size_t>(b) * p.H + yy) * p.W + xx) * 64);
+            const int tap = ky * 3 + kx;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const uint4 v = __ldg(src + j);
+                const uint32_t vw[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float lo = bf16_lo(vw[i]), hi = bf16_hi(vw[i]);
+                    const int c = j * 8 + 2 * i;
+                    a0 = fmaf(lo, ws[tap][c][0], a0); a1 = fmaf(lo, ws[tap][c][1], a1); a2 = fmaf(lo, ws[tap][c][2], a2);
+                    a0 = fmaf(hi, ws[tap][c + 1][0], a0); a1 = fmaf(hi, ws[tap][c + 1][1], a1); a2 = fmaf(hi, ws[tap][c + 1][2], a2);
+                }
+            }
+        }
+    p.out[pix * 3 + 0] = a0;
+    p.out[pix * 3 + 1] = a1;
+    p.out[pix * 3 + 2] = a2;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Weight gradient of the 3-channel layers: R[c64][c3][tap] = sum_p V64[p][c64] * V3[p + sign * (tap - centre)][c3].
+//   sign +1, out_mode 0: Conv2d(3,64) (generator down1.0, discriminator model.0): V64 = dZ, V3 = the layer's fp32 input.
+//   sign -1, out_mode 1: Conv2d(64,3) (generator upconv1.2): V64 = the layer's input activation, V3 = dZ (fp32 NHWC-3).
+// Block = 256 threads = 64 channels x 4 pixel groups over a strip of pixels; shared-memory reduce, then fp32 atomics.
+// ---------------------------------------------------------------------------------------------------------------------
+struct WgSmallParams {
+    int B, H, W;
+    const __nv_bfloat16* v64;
+    const float* v3;
+    int v3_nchw;
+    int sign;
+    float* out;
+    int out_mode;  // 0: out[(c64*3 + c3)*9 + tap]   1: out[(c3*64 + c64)*9 + tap]
+    int ppb;       // pixels per block
+};
+
+__global__ void __launch_bounds__(256) wgrad_small_kernel(const WgSmallParams p) {
+    __shared__ float red[4][27][64];
+    const int c = threadIdx.x & 63, grp = threadIdx.x >> 6;
+    const size_t total = static_cast<size_t>(p.B) * p.H * p.W;
+    const size_t p0 = static_cast<size_t>(blockIdx.x) * p.ppb;
+    const size_t p1 = min(total, p0 + p.ppb);
+    float acc[27];
+#pragma unroll
+    for (int i = 0; i < 27; ++i) acc[i] = 0.f;
+    for (size_t pix = p0 + grp; pix < p1; pix += 4) {
+        const float v = __bfloat162float(p.v64[pix * 64 + c]);
+        const int x = static_cast<int>(pix % p.W);
+        const int y = static_cast<int>((pix / p.W) % p.H);
+        const int b = static_cast<int>(pix / (static_cast<size_t>(p.W) * p.H));
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) {
+                const int yy = y + p.sign * (ky - 1), xx = x + p.sign * (kx - 1);
+                if (yy < 0 || yy >= p.H || xx < 0 || xx >= p.W) continue;
+#pragma unroll
+                for (int ci = 0; ci < 3; ++ci) {
+                    const float u = p.v3_nchw ? __ldg(p.v3 + ((static_cast<size_t>(b) * 3 + ci) * p.H + yy) * p.W + xx)
+                                              : __ldg(p.v3 + ((static_cast<size_t>(b) * p.H + yy) * p.W + xx) * 3 + ci);
+                    acc[ci * 9 + ky * 3 + kx] = fmaf(v, u, acc[ci * 9 + ky * 3 + kx]);
+                }
+            }
+    }
+#pragma unroll
+    for (int i = 0; i < 27; ++i) red[grp][i][c] = acc[i];
+    __syncthreads();
+    for (int i = threadIdx.x; i < 27 * 64; i += 256) {
+        const int t = i >> 6, cc = i & 63, ci = t / 9, tap = t % 9;
+        const float s = red[0][t][cc] + red[1][t][cc] + red[2][t][cc] + red[3][t][cc];
+        float* dst = p.out_mode ? p.out + (ci * 64 + cc) * 9 + tap : p.out + (cc * 3 + ci) * 9 + tap;
+        atomicAdd(dst, s);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Generator loss head: content = MSE(y, clean); gz = (2 (y - clean) / n + gx) * (1 - y^2) = gradient w.r.t. the last
+// conv's pre-tanh output (gx = the discriminator's data gradient, already scaled by 0.001 / B through the BCE head).
+// Also the last conv's bias gradient (sum of gz per channel).
+// ---------------------------------------------------------------------------------------------------------------------
+struct GLossParams {
+    int B, H, W;
+    const float* y;      // fp32 NCHW generator output
+    const float* clean;  // fp32 NCHW
+    const float* gx;     // fp32 NHWC-3 or null
+    float* gz;           // fp32 NHWC-3
+    double* loss_sum;    // += sum (y - clean)^2 / n
+    float* bias_grad;    // [3] +=
+    float inv_n;
+};
+
+__global__ void __launch_bounds__(256) gloss_kernel(const GLossParams p) {
+    __shared__ float red[32];
+    const size_t total = static_cast<size_t>(p.B) * p.H * p.W;
+    const size_t pix = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
+    float sq = 0.f, g[3] = {0.f, 0.f, 0.f};
+    if (pix < total) {
+        const size_t hw = static_cast<size_t>(p.H) * p.W;
+        const size_t b = pix / hw, yx = pix % hw;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float yv = p.y[(b * 3 + c) * hw + yx];
+            const float d = yv - p.clean[(b * 3 + c) * hw + yx];
+            sq += d * d;
+            float gr = 2.f * d * p.inv_n;
+            if (p.gx) gr += p.gx[pix * 3 + c];
+            g[c] = gr * (1.f - yv * yv);
+            p.gz[pix * 3 + c] = g[c];
+        }
+    }
+    const float s = block_sum(sq, red);
+    if (threadIdx.x == 0) atomicAdd(p.loss_sum, static_cast<double>(s) * p.inv_n);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const float sg = block_sum(g[c], red);
+        if (threadIdx.x == 0) atomicAdd(p.bias_grad + c, sg);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Column sums of an NHWC bf16 tensor slice: out[c] += sum_p v[p][c0 + c] (bias gradients), optionally also the sums of
+// squares (BatchNorm batch statistics, accumulated in double).
+// ---------------------------------------------------------------------------------------------------------------------
+template <bool SQ>
+__global__ void __launch_bounds__(256) colsum_kernel(const __nv_bfloat16* v, size_t P, int cs, int c0, int C, float* out,
+                                                     double* dsum, double* dsq, int ppb) {
+    __shared__ float red[256 * 2];
+    __shared__ float red2[256 * 2];
+    const int pairs = C >> 1;             // bf16x2 per pixel
+    const int rpi = 256 / pairs;          // rows per iteration (C <= 512)
+    const int cp = threadIdx.x % pairs, rg = threadIdx.x / pairs;
+    const size_t p0 = static_cast<size_t>(blockIdx.x) * ppb, p1 = min(P, p0 + ppb);
+    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+    if (rg < rpi)
+        for (size_t pix = p0 + rg; pix < p1; pix += rpi) {
+            const uint32_t w = *reinterpret_cast<const uint32_t*>(v + pix * cs + c0 + 2 * cp);
+            const float lo = bf16_lo(w), hi = bf16_hi(w);
+            s0 += lo; s1 += hi;
+            if (SQ) { q0 = fmaf(lo, lo, q0); q1 = fmaf(hi, hi, q1); }
+        }
+    red[threadIdx.x * 2] = s0; red[threadIdx.x * 2 + 1] = s1;
+    if (SQ) { red2[threadIdx.x * 2] = q0; red2[threadIdx.x * 2 + 1] = q1; }
+    __syncthreads();
+    if (threadIdx.x < C) {
+        const int c = threadIdx.x, pr = c >> 1, e = c & 1;
+        float s = 0.f, q = 0.f;
+        for (int r = 0; r < rpi; ++r) {
+            s += red[(r * pairs + pr) * 2 + e];
+            if (SQ) q += red2[(r * pairs + pr) * 2 + e];
+        }
+        if (SQ) {
+            atomicAdd(dsum + c, static_cast<double>(s));
+            atomicAdd(dsq + c, static_cast<double>(q));
+        } else {
+            atomicAdd(out + c, s);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// MaxPool2d(2,2) backward fused with the skip-connection add and the ReLU mask of the pooled activation e:
+//   dz[p][c] = (e[p][c] > 0) ? gskip[p][c] + (p is the first arg-max of its 2x2 window ? gpool[p/2][c] : 0) : 0
+// e and gskip live in channel slices of the concat buffers (stride cs, first channel c0). 8 channels per thread.
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) poolbwd_kernel(const __nv_bfloat16* e, const __nv_bfloat16* gskip, int cs, int c0,
+                                                      const __nv_bfloat16* gpool, __nv_bfloat16* dz, int B, int H, int W, int C) {
+    const int chunks = C >> 3;
+    const size_t total = static_cast<size_t>(B) * H * W * chunks;
+    const size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
+    if (i >= total) return;
+    const int ck = static_cast<int>(i % chunks);
+    const size_t pix = i / chunks;
+    const int x = static_cast<int>(pix % W);
+    const int y = static_cast<int>((pix / W) % H);
+    const size_t b = pix / (static_cast<size_t>(W) * H);
+    const int k = (y & 1) * 2 + (x & 1);
+    const int wy = y & ~1, wx = x & ~1;
+    uint4 ev[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const size_t q = (b * H + wy + (j >> 1)) * W + wx + (j & 1);
+        ev[j] = __ldg(reinterpret_cast<const uint4*>(e + q * cs + c0 + ck * 8));
+    }
+    const uint4 gs = __ldg(reinterpret_cast<const uint4*>(gskip + pix * cs + c0 + ck * 8));
+    const size_t pp = (b * (H >> 1) + (y >> 1)) * (W >> 1) + (x >> 1);
+    const uint4 gp = __ldg(reinterpret_cast<const uint4*>(gpool + pp * C + ck * 8));
+    const uint32_t gsw[4] = {gs.x, gs.y, gs.z, gs.w}, gpw[4] = {gp.x, gp.y, gp.z, gp.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int wi = 0; wi < 4; ++wi) {
+        float r[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            float ej[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t w = wi == 0 ? ev[j].x : wi == 1 ? ev[j].y : wi == 2 ? ev[j].z : ev[j].w;
+                ej[j] = h ? bf16_hi(w) : bf16_lo(w);
+            }
+            const float mx = fmaxf(fmaxf(ej[0], ej[1]), fmaxf(ej[2], ej[3]));
+            int first = 3;
+#pragma unroll
+            for (int j = 3; j >= 0; --j)
+                if (ej[j] == mx) first = j;
+            const float mine = ej[k == 0 ? 0 : k == 1 ? 1 : k == 2 ? 2 : 3];
+            float gsum = h ? bf16_hi(gsw[wi]) : bf16_lo(gsw[wi]);
+            if (first == k) gsum += h ? bf16_hi(gpw[wi]) : bf16_lo(gpw[wi]);
+            r[h] = mine > 0.f ? gsum : 0.f;
+        }
+        o[wi] = pack_bf16x2(r[0], r[1]);
+    }
+    st_global_v4(dz + pix * C + ck * 8, o[0], o[1], o[2], o[3]);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Train-mode BatchNorm2d (eps 1e-5, momentum 0.1) + LeakyReLU(0.2)
+// ---------------------------------------------------------------------------------------------------------------------
+// stats[c] = {mean, invstd}; running statistics updated as torch does (unbiased variance)
+__global__ void bn_finalize_kernel(const double* dsum, const double* dsq, double n, int C, float eps, float momentum,
+                                   float* stats, float* running_mean, float* running_var, float* nbt) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const double mean = dsum[c] / n;
+    double var = dsq[c] / n - mean * mean;
+    if (var < 0) var = 0;
+    stats[2 * c] = static_cast<float>(mean);
+    stats[2 * c + 1] = static_cast<float>(1.0 / sqrt(var + static_cast<double>(eps)));
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * static_cast<float>(mean);
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * static_cast<float>(var * n / (n - 1.0));
+    if (c == 0) nbt[0] += 1.f;
+}
+
+// a = lrelu(gamma * (z - mean) * invstd + beta); 8 channels per thread
+__global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* z, __nv_bfloat16* a, size_t P, int C,
+                                                       const float* stats, const float* gamma, const float* beta,
+                                                       float slope) {
+    const int chunks = C >> 3;
+    const size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
+    if (i >= P * chunks) return;
+    const int c8 = static_cast<int>(i % chunks) * 8;
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(z + i * 8));
+    const uint32_t vw[4] = {v.x, v.y, v.z, v.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        float f[2] = {bf16_lo(vw[j]), bf16_hi(vw[j])};
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int c = c8 + 2 * j + h;
+            float yv = gamma[c] * (f[h] - stats[2 * c]) * stats[2 * c + 1] + beta[c];
+            f[h] = yv > 0.f ? yv : yv * slope;
+        }
+        o[j] = pack_bf16x2(f[0], f[1]);
+    }
+    st_global_v4(a + i * 8, o[0], o[1], o[2], o[3]);
+}
+
+// dY = dA * lrelu'(y); sums[c] += {sum dY, sum dY * xhat}. dA comes from a tensor (da) or, for the layer under the
+// average pool, is broadcast from dpool[b][c] (already divided by H*W).
+__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const __nv_bfloat16* z, const __nv_bfloat16* da,
+                                                            const float* dpool, size_t P, size_t hw, int C,
+                                                            const float* stats, const float* gamma, const float* beta,
+                                                            float slope, double* sums, int ppb) {
+    __shared__ float red[256 * 2];
+    __shared__ float red2[256 * 2];
+    const int pairs = C >> 1, rpi = 256 / pairs;
+    const int cp = threadIdx.x % pairs, rg = threadIdx.x / pairs;
+    const size_t p0 = static_cast<size_t>(blockIdx.x) * ppb, p1 = min(P, p0 + ppb);
+    float s[2] = {0.f, 0.f}, q[2] = {0.f, 0.f};
+    const int c = 2 * cp;
+    const float mean[2] = {stats[2 * c], stats[2 * c + 2]}, istd[2] = {stats[2 * c + 1], stats[2 * c + 3]};
+    const float ga[2] = {gamma[c], gamma[c + 1]}, be[2] = {beta[c], beta[c + 1]};
+    if (rg < rpi)
+        for (size_t pix = p0 + rg; pix < p1; pix += rpi) {
+            const uint32_t zw = *reinterpret_cast<const uint32_t*>(z + pix * C + c);
+            const float zz[2] = {bf16_lo(zw), bf16_hi(zw)};
+            float dd[2];
+            if (da) {
+                const uint32_t dw = *reinterpret_cast<const uint32_t*>(da + pix * C + c);
+                dd[0] = bf16_lo(dw); dd[1] = bf16_hi(dw);
+            } else {
+                const size_t b = pix / hw;
+                dd[0] = dpool[b * C + c]; dd[1] = dpool[b * C + c + 1];
+            }
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const float xh = (zz[h] - mean[h]) * istd[h];
+                const float yv = ga[h] * xh + be[h];
+                const float dy = yv > 0.f ? dd[h] : dd[h] * slope;
+                s[h] += dy;
+                q[h] = fmaf(dy, xh, q[h]);
+            }
+        }
+    red[threadIdx.x * 2] = s[0]; red[threadIdx.x * 2 + 1] = s[1];
+    red2[threadIdx.x * 2] = q[0]; red2[threadIdx.x * 2 + 1] = q[1];
+    __syncthreads();
+    if (threadIdx.x < C) {
+        const int cc = threadIdx.x, pr = cc >> 1, e = cc & 1;
+        float a = 0.f, b2 = 0.f;
+        for (int r = 0; r < rpi; ++r) {
+            a += red[(r * pairs + pr) * 2 + e];
+            b2 += red2[(r * pairs + pr) * 2 + e];
+        }
+        atomicAdd(sums + cc, static_cast<double>(a));
+        atomicAdd(sums + C + cc, static_cast<double>(b2));
+    }
+}
+
+// dZ = gamma * invstd * (dY - sum_dy / n - xhat * sum_dyxhat / n)
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* z, const __nv_bfloat16* da,
+                                                           const float* dpool, __nv_bfloat16* dz, size_t P, size_t hw,
+                                                           int C, const float* stats, const float* gamma,
+                                                           const float* beta, float slope, const double* sums, double n) {
+    const int chunks = C >> 3;
+    const size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
+    if (i >= P * chunks) return;
+    const int c8 = static_cast<int>(i % chunks) * 8;
+    const size_t pix = i / chunks;
+    const uint4 zv = __ldg(reinterpret_cast<const uint4*>(z + i * 8));
+    const uint32_t zw[4] = {zv.x, zv.y, zv.z, zv.w};
+    uint32_t dw[4] = {0u, 0u, 0u, 0u};
+    if (da) {
+        const uint4 dv = __ldg(reinterpret_cast<const uint4*>(da + i * 8));
+        dw[0] = dv.x; dw[1] = dv.y; dw[2] = dv.z; dw[3] = dv.w;
+    }
+    const size_t b = pix / hw;
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        float r[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int c = c8 + 2 * j + h;
+            const float zz = h ? bf16_hi(zw[j]) : bf16_lo(zw[j]);
+            const float dd = da ? (h ? bf16_hi(dw[j]) : bf16_lo(dw[j])) : dpool[b * C + c];
+            const float xh = (zz - stats[2 * c]) * stats[2 * c + 1];
+            const float yv = gamma[c] * xh + beta[c];
+            const float dy = yv > 0.f ? dd : dd * slope;
+            const float sdy = static_cast<float>(sums[c] / n), sdx = static_cast<float>(sums[C + c] / n);
+            r[h] = gamma[c] * stats[2 * c + 1] * (dy - sdy - xh * sdx);
+        }
+        o[j] = pack_bf16x2(r[0], r[1]);
+    }
+    st_global_v4(dz + i * 8, o[0], o[1], o[2], o[3]);
+}
+
+// grads of gamma / beta: += {sum dY xhat, sum dY}
+__global__ void bn_param_grad_kernel(const double* sums, int C, float* ggamma, float* gbeta) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    gbeta[c] += static_cast<float>(sums[c]);
+    ggamma[c] += static_cast<float>(sums[C + c]);
+}
+
+// g *= lrelu'(a) in place (a is post-activation: its sign is the pre-activation's)
+__global__ void __launch_bounds__(256) lrelu_bwd_kernel(__nv_bfloat16* g, const __nv_bfloat16* a, size_t n8, float slope) {
+    const size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
+    if (i >= n8) return;
+    const uint4 gv = *reinterpret_cast<const uint4*>(g + i * 8);
+    const uint4 av = __ldg(reinterpret_cast<const uint4*>(a + i * 8));
+    const uint32_t gw[4] = {gv.x, gv.y, gv.z, gv.w}, aw[4] = {av.x, av.y, av.z, av.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float lo = bf16_lo(aw[j]) > 0.f ? bf16_lo(gw[j]) : bf16_lo(gw[j]) * slope;
+        const float hi = bf16_hi(aw[j]) > 0.f ? bf16_hi(gw[j]) : bf16_hi(gw[j]) * slope;
+        o[j] = pack_bf16x2(lo, hi);
+    }
+    st_global_v4(g + i * 8, o[0], o[1], o[2], o[3]);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Discriminator head: AdaptiveAvgPool2d(1) -> Conv2d(128,1,k1) -> Sigmoid -> BCELoss(mean) and its backward.
+// ---------------------------------------------------------------------------------------------------------------------
+// pooled[b][c] = mean over hw of a[b][.][c];  grid = B, block = C
+__global__ void avgpool_kernel(const __nv_bfloat16* a, float* pooled, int hw, int C) {
+    const int b = blockIdx.x, c = threadIdx.x;
+    const __nv_bfloat16* src = a + static_cast<size_t>(b) * hw * C + c;
+    float s = 0.f;
+    for (int i = 0; i < hw; ++i) s += __bfloat162float(src[static_cast<size_t>(i) * C]);
+    pooled[b * C + c] = s / static_cast<float>(hw);
+}
+
+// One block of 128 threads (C = 128). loss_sum += BCE(sigmoid(w.pooled + b), target) (mean over B);
+// dlogit = scale * (p - target) / B; dpool[b][c] = dlogit[b] * w[c] / hw; with_param_grads: gw += dlogit^T pooled, gb += sum.
+__global__ void __launch_bounds__(128) dhead_kernel(const float* pooled, const float* w, const float* bias, int B, int hw,
+                                                    float target, float scale, double* loss_sum, float* dpool, float* gw,
+                                                    float* gb, float* probs, int with_param_grads) {
+    extern __shared__ float dl[];  // [B]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float lsum = 0.f;
+    for (int b = warp; b < B; b += 4) {
+        float s = 0.f;
+        for (int c = lane; c < 128; c += 32) s = fmaf(w[c], pooled[b * 128 + c], s);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        const float logit = s + bias[0];
+        const float pr = 1.f / (1.f + expf(-logit));
+        if (lane == 0) {
+            const float l1 = fmaxf(logf(pr), -100.f), l0 = fmaxf(log1pf(-pr), -100.f);
+            lsum += -(target * l1 + (1.f - target) * l0);
+            dl[b] = scale * (pr - target) / static_cast<float>(B);
+            if (probs) probs[b] = pr;
+        }
+    }
+    __shared__ float red[32];
+    const float tot = block_sum(lsum, red);
+    if (threadIdx.x == 0) atomicAdd(loss_sum, static_cast<double>(tot) / B);
+    __syncthreads();
+    const int c = threadIdx.x;
+    float g = 0.f;
+    const float wc = w[c], inv_hw = 1.f / static_cast<float>(hw);
+    for (int b = 0; b < B; ++b) {
+        g = fmaf(dl[b], pooled[b * 128 + c], g);
+        dpool[b * 128 + c] = dl[b] * wc * inv_hw;
+    }
+    if (with_param_grads) {
+        gw[c] += g;
+        if (c == 0) {
+            float sb = 0.f;
+            for (int b = 0; b < B; ++b) sb += dl[b];
+            gb[0] += sb;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Adam (torch.optim.Adam defaults: eps 1e-8, no weight decay, no amsgrad) over a flat parameter range
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) adam_kernel(float* w, const float* g, float* m, float* v, size_t n, float lr,
+                                                   float b1, float b2, float eps, float bc1, float bc2_sqrt) {
+    const size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
+    if (i >= n) return;
+    const float gi = g[i];
+    const float mi = b1 * m[i] + (1.f - b1) * gi;
+    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    const float denom = sqrtf(vi) / bc2_sqrt + eps;
+    w[i] -= (lr / bc1) * (mi / denom);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// fp32 master weights (reference layout) -> the bf16 operand layouts of the tensor-core kernels
+// ---------------------------------------------------------------------------------------------------------------------
+enum RepackMode {
+    RP_CONV9_FWD = 0,    // dst[(t*npad + co)*cin + ci]        = w[(co*cin + ci)*9 + t]
+    RP_CONV9_DGRAD = 1,  // dst[(t*cin + ci)*cout + co]        = w[(co*cin + ci)*9 + 8 - t]
+    RP_CONVT_FWD = 2,    // dst[(q*cout + co)*cin + ci]        = w[(ci*cout + co)*4 + q]
+    RP_CONVT_DGRAD = 3,  // dst[(q*cin + ci)*cout + co]        = w[(ci*cout + co)*4 + q]
+    RP_K4_FWD = 4,       // dst[((ky*4+kx)*cout + co)*cin + ci] = ky,kx < 3 ? w[(co*cin + ci)*9 + ky*3 + kx] : 0
+    RP_T4_DGRAD = 5,     // dst[((ky*4+kx)*cin + ci)*cout + co] = same value
+    RP_FIRST = 6,        // first_conv_umma.cuh operand: [tap][k chunk][cout 64][8] with hi/lo split
+    RP_LAST = 7          // last_conv_umma.cuh operand: row tap*3 + co of 128 rows x 64 channels
+};
+
+__global__ void __launch_bounds__(256) repack_kernel(int mode, const float* w, __nv_bfloat16* dst, int cin, int cout,
+                                                     int npad, size_t n) {
+    const size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
+    if (i >= n) return;
+    float val = 0.f;
+    switch (mode) {
+        case RP_CONV9_FWD: {
+            const int ci = static_cast<int>(i % cin);
+            const int co = static_cast<int>((i / cin) % npad);
+            const int t = static_cast<int>(i / (static_cast<size_t>(cin) * npad));
+            if (co < cout) val = w[(static_cast<size_t>(co) * cin + ci) * 9 + t];
+            break;
+        }
+        case RP_CONV9_DGRAD: {
+            const int co = static_cast<int>(i % cout);
+            const int ci = static_cast<int>((i / cout) % cin);
+            const int t = static_cast<int>(i / (static_cast<size_t>(cin) * cout));
+            val = w[(static_cast<size_t>(co) * cin + ci) * 9 + 8 - t];
+            break;
+        }
+        case RP_CONVT_FWD: {
+            const int ci = static_cast<int>(i % cin);
+            const int co = static_cast<int>((i / cin) % cout);
+            const int q = static_cast<int>(i / (static_cast<size_t>(cin) * cout));
+            val = w[(static_cast<size_t>(ci) * cout + co) * 4 + q];
+            break;
+        }
+        case RP_CONVT_DGRAD: {
+            const int co = static_cast<int>(i % cout);
+            const int ci = static_cast<int>((i / cout) % cin);
+            const int q = static_cast<int>(i / (static_cast<size_t>(cin) * cout));
+            val = w[(static_cast<size_t>(ci) * cout + co) * 4 + q];
+            break;
+        }
+        case RP_K4_FWD: {
+            const int ci = static_cast<int>(i % cin);
+            const int co = static_cast<int>((i / cin) % cout);
+            const int t = static_cast<int>(i / (static_cast<size_t>(cin) * cout));
+            const int ky = t >> 2, kx = t & 3;
+            if (ky < 3 && kx < 3) val = w[(static_cast<size_t>(co) * cin + ci) * 9 + ky * 3 + kx];
+            break;
+        }
+        case RP_T4_DGRAD: {
+            const int co = static_cast<int>(i % cout);
+            const int ci = static_cast<int>((i / cout) % cin);
+            const int t = static_cast<int>(i / (static_cast<size_t>(cin) * cout));
+            const int ky = t >> 2, kx = t & 3;
+            if (ky < 3 && kx < 3) val = w[(static_cast<size_t>(co) * cin + ci) * 9 + ky * 3 + kx];
+            break;
+        }
+        case RP_FIRST: {
+            const int e = static_cast<int>(i & 7);
+            const int co = static_cast<int>((i >> 3) & 63);
+            const int chunk = static_cast<int>((i >> 9) & 1);
+            const int tap = static_cast<int>(i >> 10);
+            if (chunk == 0) {
+                if (e < 6) val = w[(co * 3 + (e % 3)) * 9 + tap];
+            } else if (e < 3) {
+                const float wf = w[(co * 3 + e) * 9 + tap];
+                val = wf - __bfloat162float(__float2bfloat16_rn(wf));
+            }
+            break;
+        }
+        case RP_LAST: {
+            const int ci = static_cast<int>(i & 63);
+            const int row = static_cast<int>(i >> 6);
+            const int tap = row / 3, co = row % 3;
+            if (tap < 9) val = w[(static_cast<size_t>(co) * 64 + ci) * 9 + tap];
+            break;
+        }
+    }
+    dst[i] = __float2bfloat16_rn(val);
+}
+
+}  // namespace cid

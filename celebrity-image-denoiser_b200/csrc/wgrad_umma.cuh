@@ -1,0 +1,216 @@
+// K3: weight gradients of the convolutions on tcgen05 tensor cores (training step).
+//
+// Reference ops this replaces (autograd's conv weight-gradient under `g_loss.backward()` / `d_loss.backward()`,
+// backend/trainingcode/denoise_gan_code/training.py:410-425):
+//   dW[co][ci][ky][kx] = sum over (b,y,x) of dZ[b,y,x,co] * X[b, s*y-1+ky, s*x-1+kx, ci]      Conv2d k3 p1, stride s
+//   dW[ci][co][dy][dx] = sum over (b,y,x) of X[b,y,x,ci]  * dY[b, 2y+dy, 2x+dx, co]            ConvTranspose2d k2 s2
+//
+// Both are GEMMs whose K dimension is the PIXEL index, with NHWC bf16 operands whose contiguous dimension is the
+// channel = the GEMM's M / N dimension: both operands are "MN-major" UMMA operands (instruction-descriptor bits 15/16),
+// read straight from the same TMA boxes the forward kernels use:
+//   * operand A (M = 128 rows): a plain 8 px x 16 row pixel tile {64 ch, 8 px, 16 rows} per 64-channel atom. With only 64
+//     channels the second atom re-reads the first (LBO = 0) and accumulator rows 64..127 are ignored.
+//   * operand B (N = 64 or 128 columns): a patch {64 ch, PW px, 16 rows} (PW = 8 + halo) per 64-channel atom; the T taps of
+//     one role are the same patch read at start + t * 128 B (one pixel to the right) - the absolute-address 128-byte
+//     swizzle makes the shifted reads legal, exactly as in conv_umma.cuh. For stride-2 layers the patch is a stride-2
+//     TMA box (the operand with twice the resolution).
+// One MMA covers K = 16 pixels = two tile rows: 8 consecutive pixels are 8 consecutive 128-byte lines (one swizzle atom
+// of the canonical MN-major SW128 layout ((8,n),(8,k)):((16B,LBO),(128B,SBO))), the second row sits SBO = PW*128 B further.
+//
+// Work split. A ROLE fixes (M channel block, N channel block, tap row): its T accumulators [128 x N] stay in TMEM for
+// the CTA's whole life (split-K over pixel tiles: CTA (role, slice) walks its contiguous share of the tiles), and the
+// epilogue adds them into the fp32 gradient tensor (reference layout) with red.global.add.f32.
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer, warps 2..5 = epilogue.
+#pragma once
+#include "ptx.cuh"
+
+namespace cid {
+
+constexpr int kWgThreads = 192;
+constexpr int kWgMaxRoles = 48;
+constexpr int kWgMaxStages = 6;
+
+struct WgRole {
+    int a_c0, b_c0;  // first channel of this role's M / N block (coordinates in the TMA maps' channel dimension)
+    int m0, n0;      // the same blocks as indices of the gradient tensor
+    int oy, ox;      // patch origin = scale * (tile y0, x0) + (oy, ox)
+    int tap[3];      // gradient tap index of MMA tap t (patch pixel offset t); -1 = computed but dropped
+};
+
+struct WgParams {
+    int B, H, W;  // pixel grid of operand A (tiles of 8 x 16)
+    int tiles_x, tiles_y, m_tiles;
+    int n_roles, slices;
+    int scale;    // 1, or 2: operand B has twice the resolution and is read through a stride-2 box
+    int pw;       // patch pixels per row (B operand)
+    int stages;
+    float* out;   // out[((m0 + row) * s_m + n0 + col) * kk + tap]
+    int s_m, kk;
+    int m_valid;  // rows of the 128-row accumulator that are real channels (64 or 128)
+    WgRole roles[kWgMaxRoles];
+};
+
+// MN-major SW128 shared-memory descriptor (same bit layout as the K-major one; majorness lives in the instruction
+// descriptor): start[0,14) lbo[16,30) sbo[32,46) version[46,48)=1 layout[61,64)=2.
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);
+    d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32;
+    d |= static_cast<uint64_t>(1) << 46;
+    d |= static_cast<uint64_t>(2) << 61;
+    return d;
+}
+
+// kind::f16 instruction descriptor, bf16 x bf16 -> fp32, BOTH operands MN-major.
+__host__ __device__ constexpr uint32_t umma_idesc_bf16_mn(int m, int n) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | (static_cast<uint32_t>(n >> 3) << 17) |
+           (static_cast<uint32_t>(m >> 4) << 24);
+}
+
+__device__ __forceinline__ void red_add_f32(float* p, float v) {
+    asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+
+// NA: 64-channel atoms of operand A that are real (1: rows 64..127 duplicate rows 0..63), NB: atoms of operand B
+// (N = 64 * NB), T: taps per role (accumulators).
+template <int NA, int NB, int T>
+__global__ void __launch_bounds__(kWgThreads, 1)
+wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                  const __grid_constant__ WgParams p) {
+    static_assert(NA == 1 || NA == 2, "M = 128");
+    static_assert(NB == 1 || NB == 2, "N = 64 or 128");
+    static_assert(T >= 1 && T <= 3 && T * NB * 64 <= 512, "accumulators must fit TMEM");
+    constexpr int N = 64 * NB;
+    constexpr int A_ATOM = 128 * 128;  // one 64-channel atom of the pixel tile
+    constexpr uint32_t TMEM_COLS = (T * N <= 64) ? 64 : (T * N <= 128) ? 128 : (T * N <= 256) ? 256 : 512;
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int pb = (p.pw * 16 * 128 + 1023) & ~1023;  // bytes of one B atom (patch), 1024-aligned pitch
+    const int stage_bytes = NA * A_ATOM + NB * pb;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.stages * stage_bytes);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + kWgMaxStages;
+    uint64_t* acc_full = bars + 2 * kWgMaxStages;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int role_i = blockIdx.x % p.n_roles;
+    const int slice = blockIdx.x / p.n_roles;
+    const WgRole& role = p.roles[role_i];
+    const int per = (p.m_tiles + p.slices - 1) / p.slices;
+    const int t_begin = slice * per;
+    const int t_end = min(p.m_tiles, t_begin + per);
+    const bool has_work = t_begin < t_end;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+        for (int i = 0; i < kWgMaxStages; ++i) {
+            mbar_init(&full[i], 1);
+            mbar_init(&empty[i], 1);
+        }
+        mbar_init(acc_full, 1);
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0 && has_work) {
+            pdl_wait();
+            uint32_t stage = 0, phase = 0;
+            for (int mt = t_begin; mt < t_end; ++mt) {
+                const int tx = mt % p.tiles_x;
+                const int r = mt / p.tiles_x;
+                const int ty = r % p.tiles_y;
+                const int b = r / p.tiles_y;
+                const int y0 = ty * 16, x0 = tx * 8;
+                uint8_t* sa = smem + stage * stage_bytes;
+                uint8_t* sb = sa + NA * A_ATOM;
+                mbar_wait(&empty[stage], phase ^ 1);
+                mbar_arrive_expect_tx(&full[stage], NA * A_ATOM + NB * p.pw * 16 * 128);
+#pragma unroll
+                for (int a = 0; a < NA; ++a)
+                    tma_load_4d(sa + a * A_ATOM, &tmA, &full[stage], role.a_c0 + a * 64, x0, y0, b, kEvictNormal);
+#pragma unroll
+                for (int q = 0; q < NB; ++q)
+                    tma_load_4d(sb + q * pb, &tmB, &full[stage], role.b_c0 + q * 64, p.scale * x0 + role.ox,
+                                p.scale * y0 + role.oy, b, kEvictNormal);
+                if (++stage == static_cast<uint32_t>(p.stages)) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (has_work) {
+            constexpr uint32_t idesc = umma_idesc_bf16_mn(128, N);
+            const uint32_t sbo_b = static_cast<uint32_t>(p.pw) * 128u;
+            uint32_t stage = 0, phase = 0;
+            for (int mt = t_begin; mt < t_end; ++mt) {
+                mbar_wait(&full[stage], phase);
+                tc_fence_after();
+                const uint32_t sa = smem_u32(smem + stage * stage_bytes);
+                const uint32_t sb = sa + NA * A_ATOM;
+                if (elect_one()) {
+#pragma unroll
+                    for (int k8 = 0; k8 < 8; ++k8) {
+                        // K = 16 pixels = tile rows 2*k8 and 2*k8+1
+                        const uint64_t ad = umma_desc_mn_sw128(sa + k8 * 2048, NA == 2 ? A_ATOM : 0, 1024);
+#pragma unroll
+                        for (int t = 0; t < T; ++t) {
+                            const uint64_t bd =
+                                umma_desc_mn_sw128(sb + (k8 * 2 * p.pw + t) * 128, static_cast<uint32_t>(pb), sbo_b);
+                            umma_bf16_ss(tmem_base + t * N, ad, bd, idesc, (mt == t_begin && k8 == 0) ? 0u : 1u);
+                        }
+                    }
+                    umma_commit(&empty[stage]);
+                }
+                __syncwarp();
+                if (++stage == static_cast<uint32_t>(p.stages)) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+            if (elect_one()) umma_commit(acc_full);
+            __syncwarp();
+        }
+    } else if (has_work) {
+        // epilogue: TMEM lane quarter = warp & 3; lane = accumulator row = M channel
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        mbar_wait(acc_full, 0);
+        tc_fence_after();
+        if (q * 32 < p.m_valid) {  // warp-uniform: quarters that hold duplicate rows do nothing
+            float* orow = p.out + (static_cast<size_t>(role.m0 + row) * p.s_m + role.n0) * p.kk;
+#pragma unroll
+            for (int t = 0; t < T; ++t) {
+                const int tap = role.tap[t];
+                if (tap < 0) continue;
+#pragma unroll
+                for (int ch = 0; ch < N / 32; ++ch) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + t * N + ch * 32, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) red_add_f32(orow + static_cast<size_t>(ch * 32 + j) * p.kk + tap, __uint_as_float(v[j]));
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, TMEM_COLS);
+    }
+}
+
+}  // namespace cid

@@ -12,7 +12,7 @@ from pathlib import Path
 _LIB_PATH = Path(__file__).resolve().parent / "csrc" / "libcid_b200.so"
 _lib = None
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 # name -> (restype, argtypes); mirrors include/cid_b200.h one to one
 _SIGNATURES = {
@@ -46,6 +46,26 @@ _SIGNATURES = {
     "cid_debug_copy_activation": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                             C.c_void_p, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int),
                                             C.POINTER(C.c_int)]),
+    # training step
+    "cid_train_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
+    "cid_train_destroy": (C.c_int, [C.c_void_p]),
+    "cid_train_state_floats": (C.c_int, [C.c_void_p, C.POINTER(C.c_size_t)]),
+    "cid_train_bind_state": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
+    "cid_train_tensor": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
+    "cid_train_tensor_count": (C.c_int, [C.c_void_p]),
+    "cid_train_tensor_name": (C.c_char_p, [C.c_void_p, C.c_int]),
+    "cid_train_section": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
+    "cid_train_sync_weights": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "cid_train_workspace_bytes": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t)]),
+    "cid_train_d_backward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                       C.c_size_t, C.c_void_p]),
+    "cid_train_g_backward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                       C.c_size_t, C.c_void_p]),
+    "cid_train_adam": (C.c_int, [C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p]),
+    "cid_train_losses": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
+    "cid_train_kernel_launches": (C.c_int64, [C.c_void_p]),
+    "cid_train_debug_buffer": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                         C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

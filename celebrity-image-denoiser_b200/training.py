@@ -1,0 +1,204 @@
+"""Host mirror of the reference's denoise-GAN training step, on the C-ABI training entry points.
+
+Reference: backend/trainingcode/denoise_gan_code/training.py
+    DenoiseDiscriminator        :77-98   (same module tree -> same state_dict keys)
+    DenoiseGANTrainer.__init__  :230-242 (Adam lr 1e-4, betas (0.9, 0.999); BCELoss + MSELoss)
+    DenoiseGANTrainer.train     :403-427 (one iteration = `DenoiseGANTrainStep.step`)
+
+The arithmetic runs in libcid_b200.so (cid_train_*, include/cid_b200.h). PyTorch supplies the device buffers, the
+stream and - when torch.distributed is initialised with world size > 1 - the NCCL all-reduce of the flat gradient
+sections between each backward pass and its Adam update (BASELINE config #5; the reference itself is single-GPU).
+There is no CPU or PyTorch compute path here.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Optional
+
+import torch
+import torch.nn as nn
+
+from . import lib as _lib
+from .generator import DenoiseGenerator
+
+
+class DenoiseDiscriminator(nn.Module):
+    """Parameter container with the reference's module tree (training.py:77-98). The forward pass only exists inside
+    the training step (train-mode BatchNorm on the tensor-core path); calling the module directly raises."""
+
+    def __init__(self):
+        super().__init__()
+        self.model = nn.Sequential(
+            nn.Conv2d(3, 64, kernel_size=3, padding=1),
+            nn.LeakyReLU(0.2),
+            nn.Conv2d(64, 64, kernel_size=3, stride=2, padding=1),
+            nn.BatchNorm2d(64),
+            nn.LeakyReLU(0.2),
+            nn.Conv2d(64, 128, kernel_size=3, padding=1),
+            nn.BatchNorm2d(128),
+            nn.LeakyReLU(0.2),
+            nn.Conv2d(128, 128, kernel_size=3, stride=2, padding=1),
+            nn.BatchNorm2d(128),
+            nn.LeakyReLU(0.2),
+            nn.AdaptiveAvgPool2d(1),
+            nn.Conv2d(128, 1, kernel_size=1),
+            nn.Sigmoid(),
+        )
+
+    def forward(self, x):  # pragma: no cover - by design
+        raise RuntimeError("DenoiseDiscriminator runs inside DenoiseGANTrainStep (cid_train_*); it has no standalone "
+                           "forward and no PyTorch fallback")
+
+
+class DenoiseGANTrainStep:
+    """One data-parallel replica of the reference's training iteration.
+
+    `generator` / `discriminator` provide the initial parameters (their state_dict keys are the reference's); the
+    training state then lives in ONE flat fp32 device buffer (parameters | gradients | Adam exp_avg | exp_avg_sq |
+    BatchNorm running statistics) that the C library updates in place. `export_state_dicts()` copies it back.
+    """
+
+    def __init__(self, generator: nn.Module, discriminator: nn.Module, device="cuda", lr: float = 1e-4,
+                 betas=(0.9, 0.999), eps: float = 1e-8, process_group=None):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("the training step runs on a CUDA device (sm_100a); there is no CPU fallback")
+        self.index = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.lib = _lib.load()
+        self.lr, self.betas, self.eps = float(lr), (float(betas[0]), float(betas[1])), float(eps)
+        self.group = process_group
+        h = C.c_void_p()
+        _lib.check(self.lib.cid_train_create(self.index, C.byref(h)), "cid_train_create")
+        self.handle = h
+        n = C.c_size_t()
+        _lib.check(self.lib.cid_train_state_floats(h, C.byref(n)), "cid_train_state_floats")
+        self.state = torch.zeros(n.value, dtype=torch.float32, device=self.device)
+        _lib.check(self.lib.cid_train_bind_state(h, C.c_void_p(self.state.data_ptr()), n.value), "cid_train_bind_state")
+        self.names = [self.lib.cid_train_tensor_name(h, i).decode() for i in range(self.lib.cid_train_tensor_count(h))]
+        self._ws: Optional[torch.Tensor] = None
+        self._ws_key = None
+        self.load_state_dicts(generator.state_dict(), discriminator.state_dict())
+
+    # ---- state ------------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "handle", None):
+            torch.cuda.synchronize(self.device)
+            self.lib.cid_train_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):  # best effort
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def view(self, key: str, section: int = 0) -> torch.Tensor:
+        """Flat view of one named tensor inside the state buffer (section 0 params, 1 grads, 2 exp_avg, 3 exp_avg_sq)."""
+        off, n = C.c_size_t(), C.c_size_t()
+        _lib.check(self.lib.cid_train_tensor(self.handle, key.encode(), section, C.byref(off), C.byref(n)), "cid_train_tensor")
+        return self.state[off.value:off.value + n.value]
+
+    def section(self, net: str, section: int) -> torch.Tensor:
+        off, n = C.c_size_t(), C.c_size_t()
+        _lib.check(self.lib.cid_train_section(self.handle, net.encode(), section, C.byref(off), C.byref(n)), "cid_train_section")
+        return self.state[off.value:off.value + n.value]
+
+    def load_state_dicts(self, g_sd: Dict[str, torch.Tensor], d_sd: Dict[str, torch.Tensor]) -> None:
+        for name in self.names:
+            net, key = name.split(".", 1)
+            src = (g_sd if net == "generator" else d_sd)[key]
+            self.view(name).copy_(src.detach().to(self.device, torch.float32).reshape(-1))
+        _lib.check(self.lib.cid_train_sync_weights(self.handle, C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)),
+                   "cid_train_sync_weights")
+
+    def export_state_dicts(self, generator: nn.Module, discriminator: nn.Module) -> None:
+        """Copy the trained parameters and BatchNorm statistics back into the two modules."""
+        for name in self.names:
+            net, key = name.split(".", 1)
+            dst = (generator if net == "generator" else discriminator).state_dict()[key]
+            v = self.view(name)
+            dst.copy_(v.reshape(dst.shape).to(dst.dtype) if dst.dim() else v[0].to(dst.dtype))
+
+    def grads(self, net: str) -> Dict[str, torch.Tensor]:
+        out = {}
+        for name in self.names:
+            n, key = name.split(".", 1)
+            if n == net and "running_" not in key and "num_batches" not in key:
+                out[key] = self.view(name, 1).clone()
+        return out
+
+    # ---- one iteration ----------------------------------------------------------------------
+    def _workspace(self, B: int, H: int, W: int):
+        key = (B, H, W)
+        if self._ws_key != key:
+            n = C.c_size_t()
+            _lib.check(self.lib.cid_train_workspace_bytes(self.handle, B, H, W, C.byref(n)), "cid_train_workspace_bytes")
+            self._ws = None
+            self._ws = torch.empty(n.value + 1024, dtype=torch.uint8, device=self.device)
+            self._ws_key = key
+        p = (self._ws.data_ptr() + 1023) & ~1023
+        return p, self._ws.numel() - (p - self._ws.data_ptr())
+
+    def _allreduce(self, flat: torch.Tensor) -> None:
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            world = dist.get_world_size(self.group)
+            if world > 1:
+                dist.all_reduce(flat, group=self.group)
+                flat.mul_(1.0 / world)
+
+    def d_backward(self, noisy: torch.Tensor, clean: torch.Tensor) -> None:
+        B, H, W, ws, wsn, st = self._args(noisy, clean)
+        _lib.check(self.lib.cid_train_d_backward(self.handle, C.c_void_p(noisy.data_ptr()), C.c_void_p(clean.data_ptr()), B, H, W,
+                                                 C.c_void_p(ws), wsn, st), "cid_train_d_backward")
+
+    def g_backward(self, noisy: torch.Tensor, clean: torch.Tensor) -> None:
+        B, H, W, ws, wsn, st = self._args(noisy, clean)
+        _lib.check(self.lib.cid_train_g_backward(self.handle, C.c_void_p(noisy.data_ptr()), C.c_void_p(clean.data_ptr()), B, H, W,
+                                                 C.c_void_p(ws), wsn, st), "cid_train_g_backward")
+
+    def adam(self, which: int) -> None:
+        st = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        _lib.check(self.lib.cid_train_adam(self.handle, which, self.lr, self.betas[0], self.betas[1], self.eps, st), "cid_train_adam")
+
+    def _args(self, noisy, clean):
+        for t in (noisy, clean):
+            if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.dim() == 4 and t.shape[1] == 3):
+                raise RuntimeError("noisy / clean must be contiguous float32 CUDA tensors [B,3,H,W]")
+        if noisy.shape != clean.shape or noisy.device != clean.device or noisy.device.index != self.index:
+            raise RuntimeError("noisy and clean must have the same shape and live on the trainer's device")
+        B, _, H, W = noisy.shape
+        ws, wsn = self._workspace(B, H, W)
+        return B, H, W, ws, wsn, C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def step(self, noisy: torch.Tensor, clean: torch.Tensor, read_losses: bool = True):
+        """training.py:409-427: D step then G step. Returns {d_loss, g_loss, content, adv} (synchronises) or None."""
+        self.d_backward(noisy, clean)
+        self._allreduce(self.section("discriminator", 1))
+        self.adam(1)
+        self.g_backward(noisy, clean)
+        self._allreduce(self.section("generator", 1))
+        self.adam(0)
+        return self.losses() if read_losses else None
+
+    def losses(self) -> Dict[str, float]:
+        out = (C.c_double * 4)()
+        _lib.check(self.lib.cid_train_losses(self.handle, out), "cid_train_losses")
+        return {"d_loss": out[0], "g_loss": out[1], "content": out[2], "adv": out[3]}
+
+    def kernel_launches(self) -> int:
+        return int(self.lib.cid_train_kernel_launches(self.handle))
+
+    def debug_buffer(self, name: str, B: int, H: int, W: int) -> torch.Tensor:
+        """Test hook: a named training workspace buffer of the last step as a float32 CPU tensor (NHWC, or NCHW for 'y')."""
+        ws, _ = self._workspace(B, H, W)
+        c, lv, es = C.c_int(), C.c_int(), C.c_int()
+        host = torch.empty(B * H * W * 256 * 2 + 16, dtype=torch.uint8)
+        _lib.check(self.lib.cid_train_debug_buffer(self.handle, name.encode(), C.c_void_p(ws), B, H, W, C.c_void_p(host.data_ptr()),
+                                                   host.numel(), C.byref(c), C.byref(lv), C.byref(es)), "cid_train_debug_buffer")
+        h, w = H >> lv.value, W >> lv.value
+        n = B * h * w * c.value
+        if es.value == 4:
+            t = host[:n * 4].view(torch.float32)
+            return t.reshape(B, 3, h, w).clone() if name == "y" else t.reshape(B, h, w, c.value).clone()
+        return host[:n * 2].view(torch.bfloat16).reshape(B, h, w, c.value).float()

@@ -174,6 +174,58 @@ int cid_profile_read(cid_handle h, double* layer_ms, int64_t* passes);
 int cid_debug_copy_activation(cid_handle h, const char* name, const void* ws, int B, int H, int W, void* dst_host,
                               size_t dst_bytes, int* channels, int* height, int* width);
 
+/* ---------------------------------------------------------------------------------------------
+ * Training step of the denoise GAN (BASELINE config #5). Replaces one iteration of
+ * DenoiseGANTrainer.train (backend/trainingcode/denoise_gan_code/training.py:403-427): generator
+ * (training.py:19-74 = backend/app.py:39-103) and DenoiseDiscriminator (:77-98) forward, BCELoss / MSELoss
+ * (:234-235), both backward passes and torch.optim.Adam (:237-238). The step is split into the phases a
+ * data-parallel caller needs, so gradients can be all-reduced (NCCL, by the caller) before each Adam update:
+ *
+ *   cid_train_d_backward -> [all-reduce D grads] -> cid_train_adam(which=1)
+ *   cid_train_g_backward -> [all-reduce G grads] -> cid_train_adam(which=0)
+ *
+ * State: ONE caller-owned fp32 device buffer of cid_train_state_floats() floats, laid out as four sections of
+ * P = n_generator + n_discriminator floats - parameters (reference layout of every state_dict tensor), gradients,
+ * Adam exp_avg, Adam exp_avg_sq - followed by the BatchNorm running statistics. cid_train_tensor() gives the offset
+ * of one named tensor ("generator.down1.0.weight", "discriminator.model.3.running_mean", ...), cid_train_section()
+ * the contiguous range of a whole network inside a section (what the caller all-reduces). The caller writes the
+ * initial parameters (and zeros elsewhere; running_var = 1) into the buffer, then calls cid_train_sync_weights.
+ * Activations and activation gradients are bf16 NHWC in the caller's workspace; accumulation is fp32.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct cid_train* cid_train_handle;
+
+int cid_train_create(int device, cid_train_handle* out);
+int cid_train_destroy(cid_train_handle t);
+int cid_train_state_floats(cid_train_handle t, size_t* n);
+int cid_train_bind_state(cid_train_handle t, float* state_dev, size_t n);
+/* section: 0 parameters, 1 gradients, 2 Adam exp_avg, 3 Adam exp_avg_sq. Offsets are in floats from state_dev. */
+int cid_train_tensor(cid_train_handle t, const char* key, int section, size_t* offset, size_t* numel);
+int cid_train_tensor_count(cid_train_handle t);
+const char* cid_train_tensor_name(cid_train_handle t, int index);
+/* net: "generator" | "discriminator" */
+int cid_train_section(cid_train_handle t, const char* net, int section, size_t* offset, size_t* numel);
+/* Re-build the bf16 tensor-core operands from the fp32 parameters (after the caller changed them). */
+int cid_train_sync_weights(cid_train_handle t, void* stream);
+int cid_train_workspace_bytes(cid_train_handle t, int B, int H, int W, size_t* bytes);
+/* noisy, clean: fp32 NCHW [B,3,H,W] in [-1,1] on the device (the DataLoader batch, training.py:406-408).
+ * Computes denoised = G(noisy) and the discriminator gradients of d_loss (:410-415). */
+int cid_train_d_backward(cid_train_handle t, const float* noisy, const float* clean, int B, int H, int W, void* ws,
+                         size_t ws_bytes, void* stream);
+/* Continues the same batch: generator gradients of g_loss = MSE + 0.001 * BCE(D(denoised), 1) (:418-424). */
+int cid_train_g_backward(cid_train_handle t, const float* noisy, const float* clean, int B, int H, int W, void* ws,
+                         size_t ws_bytes, void* stream);
+/* optimizer.step() of one network (which: 0 generator, 1 discriminator) on the gradients section as it stands,
+ * then re-packs that network's tensor-core operands. Reference values: lr 1e-4, betas (0.9, 0.999), eps 1e-8. */
+int cid_train_adam(cid_train_handle t, int which, float lr, float beta1, float beta2, float eps, void* stream);
+/* Synchronises; out4 = {d_loss, g_loss, content (MSE), adversarial (BCE)} of the last step. */
+int cid_train_losses(cid_train_handle t, double* out4);
+int64_t cid_train_kernel_launches(cid_train_handle t);
+/* Test hook: copy a named training buffer of the last step to the host. Names: y gz gx (fp32, 3 channels; y is
+ * NCHW, gz/gx NHWC), dz10 gcat1 dz8 dz7 gcat2 dz5 dz4 gp2 dz3 dz2 gp1 dz1 dz0 (generator activation gradients,
+ * bf16 NHWC), d_a0 d_z1 d_a1 d_z2 d_a2 d_z3 d_a3 d_g3 d_g2 d_g1 d_g0 (discriminator). */
+int cid_train_debug_buffer(cid_train_handle t, const char* name, const void* ws, int B, int H, int W, void* dst_host,
+                           size_t dst_bytes, int* channels, int* level, int* elem_size);
+
 #ifdef __cplusplus
 }
 #endif
