@@ -1141,7 +1141,7 @@ int cid_train_debug_buffer(cid_train_handle t, const char* name, const void* ws,
     size_t toff[TB_COUNT];
     train_layout(B, H, W, toff);
     const int lv = kTBufLevel[b];
-    const size_t es = b <= TB_GX ? 4 : 2;
+    const size_t es = tbuf_elem(b);
     const size_t n = static_cast<size_t>(B) * (H >> lv) * (W >> lv) * kTBufC[b] * es;
     CID_REQUIRE(dst_bytes >= n, "destination too small: %zu < %zu", dst_bytes, n);
     CID_CHECK_CUDA(cudaDeviceSynchronize());

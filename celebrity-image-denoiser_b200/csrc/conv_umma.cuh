@@ -59,6 +59,8 @@ struct ConvParams {
     const void* res2;    //          (second one optional)
     int res_cs, res2_cs;
     int bias_per_column; // EPI_CONVT as pixel shuffle: bias indexed by GEMM column instead of by channel
+    float* out_f32;      // EPI_LRELU only: if set, the result is written as fp32 NHWC straight from registers (no bf16
+                         // staging / TMA store): the discriminator's pre-BatchNorm outputs, whose mean >> std
     int debug_flags;     // bring-up experiments only: 1 = epilogue skips global stores, 2 = skips TMEM reads too
 };
 
@@ -587,6 +589,16 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                 const float f3 = act(__uint_as_float(v[4 * jj + 3]) + bb.w);
                                 pk[2 * jj + 0] = pack_bf16x2(f0, f1);
                                 pk[2 * jj + 1] = pack_bf16x2(f2, f3);
+                                if constexpr (EPI == EPI_LRELU) {
+                                    if (p.out_f32 != nullptr) {
+                                        const int yy = tc.y0 + yl, xx = tc.x0 + xl;
+                                        if (tc.b < p.B && yy < p.H && xx < p.W) {
+                                            const size_t pix = (static_cast<size_t>(tc.b) * p.H + yy) * p.W + xx;
+                                            float* dst = p.out_f32 + pix * p.out_cs + p.out_c0 + n_tile * N + cs * 64 + ch * 32 + 4 * jj;
+                                            *reinterpret_cast<float4*>(dst) = make_float4(f0, f1, f2, f3);
+                                        }
+                                    }
+                                }
                             }
                             uint8_t* rowp = slab + row * 128;
 #pragma unroll
@@ -613,7 +625,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         });
                         fence_proxy_async();
                         named_bar_sync(bar_id, 128);
-                        if (issuer && !(p.debug_flags & 1)) {
+                        if (issuer && !(p.debug_flags & 1) && !(EPI == EPI_LRELU && p.out_f32 != nullptr)) {
                             const int c64 = n_tile * N + cs * 64;
                             tma_store_4d(&tmO, slab, p.out_c0 + c64, tc.x0, tc.y0, tc.b);
                             if constexpr (EPI == EPI_RELU_POOL)

@@ -18,6 +18,26 @@ namespace cid {
 __device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
 
+// two / eight consecutive channels of a bf16 or fp32 NHWC tensor as floats
+__device__ __forceinline__ void load2(const __nv_bfloat16* p, float (&f)[2]) {
+    const uint32_t w = *reinterpret_cast<const uint32_t*>(p);
+    f[0] = bf16_lo(w); f[1] = bf16_hi(w);
+}
+__device__ __forceinline__ void load2(const float* p, float (&f)[2]) {
+    const float2 v = *reinterpret_cast<const float2*>(p);
+    f[0] = v.x; f[1] = v.y;
+}
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&f)[8]) {
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { f[2 * j] = bf16_lo(w[j]); f[2 * j + 1] = bf16_hi(w[j]); }
+}
+__device__ __forceinline__ void load8(const float* p, float (&f)[8]) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+    f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+
 __device__ __forceinline__ float block_sum(float v, float* red /* >= 32 floats */) {
     __syncthreads();
 #pragma unroll
@@ -273,8 +293,8 @@ __global__ void __launch_bounds__(256) gloss_kernel(const GLossParams p) {
 // Column sums of an NHWC bf16 tensor slice: out[c] += sum_p v[p][c0 + c] (bias gradients), optionally also the sums of
 // squares (BatchNorm batch statistics, accumulated in double).
 // ---------------------------------------------------------------------------------------------------------------------
-template <bool SQ>
-__global__ void __launch_bounds__(256) colsum_kernel(const __nv_bfloat16* v, size_t P, int cs, int c0, int C, float* out,
+template <bool SQ, typename ZT>
+__global__ void __launch_bounds__(256) colsum_kernel(const ZT* v, size_t P, int cs, int c0, int C, float* out,
                                                      double* dsum, double* dsq, int ppb) {
     __shared__ float red[256 * 2];
     __shared__ float red2[256 * 2];
@@ -285,8 +305,9 @@ __global__ void __launch_bounds__(256) colsum_kernel(const __nv_bfloat16* v, siz
     float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
     if (rg < rpi)
         for (size_t pix = p0 + rg; pix < p1; pix += rpi) {
-            const uint32_t w = *reinterpret_cast<const uint32_t*>(v + pix * cs + c0 + 2 * cp);
-            const float lo = bf16_lo(w), hi = bf16_hi(w);
+            float f2[2];
+            load2(v + pix * cs + c0 + 2 * cp, f2);
+            const float lo = f2[0], hi = f2[1];
             s0 += lo; s1 += hi;
             if (SQ) { q0 = fmaf(lo, lo, q0); q1 = fmaf(hi, hi, q1); }
         }
@@ -383,19 +404,20 @@ __global__ void bn_finalize_kernel(const double* dsum, const double* dsq, double
 }
 
 // a = lrelu(gamma * (z - mean) * invstd + beta); 8 channels per thread
-__global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* z, __nv_bfloat16* a, size_t P, int C,
+template <typename ZT>
+__global__ void __launch_bounds__(256) bn_apply_kernel(const ZT* z, __nv_bfloat16* a, size_t P, int C,
                                                        const float* stats, const float* gamma, const float* beta,
                                                        float slope) {
     const int chunks = C >> 3;
     const size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
     if (i >= P * chunks) return;
     const int c8 = static_cast<int>(i % chunks) * 8;
-    const uint4 v = __ldg(reinterpret_cast<const uint4*>(z + i * 8));
-    const uint32_t vw[4] = {v.x, v.y, v.z, v.w};
+    float zf[8];
+    load8(z + i * 8, zf);
     uint32_t o[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-        float f[2] = {bf16_lo(vw[j]), bf16_hi(vw[j])};
+        float f[2] = {zf[2 * j], zf[2 * j + 1]};
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const int c = c8 + 2 * j + h;
@@ -409,7 +431,8 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* z, _
 
 // dY = dA * lrelu'(y); sums[c] += {sum dY, sum dY * xhat}. dA comes from a tensor (da) or, for the layer under the
 // average pool, is broadcast from dpool[b][c] (already divided by H*W).
-__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const __nv_bfloat16* z, const __nv_bfloat16* da,
+template <typename ZT>
+__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const ZT* z, const __nv_bfloat16* da,
                                                             const float* dpool, size_t P, size_t hw, int C,
                                                             const float* stats, const float* gamma, const float* beta,
                                                             float slope, double* sums, int ppb) {
@@ -424,8 +447,8 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const __nv_bfloat16*
     const float ga[2] = {gamma[c], gamma[c + 1]}, be[2] = {beta[c], beta[c + 1]};
     if (rg < rpi)
         for (size_t pix = p0 + rg; pix < p1; pix += rpi) {
-            const uint32_t zw = *reinterpret_cast<const uint32_t*>(z + pix * C + c);
-            const float zz[2] = {bf16_lo(zw), bf16_hi(zw)};
+            float zz[2];
+            load2(z + pix * C + c, zz);
             float dd[2];
             if (da) {
                 const uint32_t dw = *reinterpret_cast<const uint32_t*>(da + pix * C + c);
@@ -459,7 +482,8 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const __nv_bfloat16*
 }
 
 // dZ = gamma * invstd * (dY - sum_dy / n - xhat * sum_dyxhat / n)
-__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* z, const __nv_bfloat16* da,
+template <typename ZT>
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const ZT* z, const __nv_bfloat16* da,
                                                            const float* dpool, __nv_bfloat16* dz, size_t P, size_t hw,
                                                            int C, const float* stats, const float* gamma,
                                                            const float* beta, float slope, const double* sums, double n) {
@@ -468,8 +492,8 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
     if (i >= P * chunks) return;
     const int c8 = static_cast<int>(i % chunks) * 8;
     const size_t pix = i / chunks;
-    const uint4 zv = __ldg(reinterpret_cast<const uint4*>(z + i * 8));
-    const uint32_t zw[4] = {zv.x, zv.y, zv.z, zv.w};
+    float zf[8];
+    load8(z + i * 8, zf);
     uint32_t dw[4] = {0u, 0u, 0u, 0u};
     if (da) {
         const uint4 dv = __ldg(reinterpret_cast<const uint4*>(da + i * 8));
@@ -483,7 +507,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const int c = c8 + 2 * j + h;
-            const float zz = h ? bf16_hi(zw[j]) : bf16_lo(zw[j]);
+            const float zz = zf[2 * j + h];
             const float dd = da ? (h ? bf16_hi(dw[j]) : bf16_lo(dw[j])) : dpool[b * C + c];
             const float xh = (zz - stats[2 * c]) * stats[2 * c + 1];
             const float yv = gamma[c] * xh + beta[c];

@@ -140,9 +140,12 @@ static float* train_ptr(const cid_train* t, const std::string& key, int section)
 // ---------------------------------------------------------------------------------------------------------------------
 // workspace
 // ---------------------------------------------------------------------------------------------------------------------
+// fp32: the 3-channel image-side tensors and the discriminator's pre-BatchNorm conv outputs (mean >> std on smooth
+// images: bf16 storage would cost ~3 % of a standard deviation per layer in the normalised value)
+static size_t tbuf_elem(int b) { return (b <= TB_GX || b == TB_DZ1D || b == TB_DZ2D || b == TB_DZ3D) ? 4 : 2; }
 static size_t tbuf_bytes(int b, int B, int H, int W) {
     const int lv = kTBufLevel[b];
-    const size_t es = b <= TB_GX ? 4 : 2;
+    const size_t es = tbuf_elem(b);
     const size_t n = static_cast<size_t>(B) * (H >> lv) * (W >> lv) * kTBufC[b] * es;
     return (n + 1023) & ~static_cast<size_t>(1023);
 }
@@ -305,7 +308,7 @@ static int wgrad(cid_train* t, int geom, const void* A, int a_C, int m_ch, const
 
 static int colsum(cid_train* t, const void* v, size_t P, int cs, int c0, int C, float* out, cudaStream_t st) {
     const int ppb = 2048;
-    colsum_kernel<false><<<static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, st>>>(
+    colsum_kernel<false, __nv_bfloat16><<<static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, st>>>(
         static_cast<const __nv_bfloat16*>(v), P, cs, c0, C, out, nullptr, nullptr, ppb);
     CID_CHECK_CUDA(cudaGetLastError());
     t->launches++;
@@ -501,14 +504,14 @@ static int bn_forward(const TrainRun& r, int l, const void* z, void* a, int lv) 
     const std::string bn = "discriminator.model." + std::to_string(kDBnIdx[l]);
     CID_CHECK_CUDA(cudaMemsetAsync(sums, 0, 256 * 8, r.st));
     const int ppb = 1024;
-    colsum_kernel<true><<<static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, r.st>>>(
-        static_cast<const __nv_bfloat16*>(z), P, C, 0, C, nullptr, sums, sums + 128, ppb);
+    colsum_kernel<true, float><<<static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, r.st>>>(
+        static_cast<const float*>(z), P, C, 0, C, nullptr, sums, sums + 128, ppb);
     bn_finalize_kernel<<<1, 128, 0, r.st>>>(sums, sums + 128, static_cast<double>(P), C, 1e-5f, 0.1f, stats,
                                             train_ptr(t, bn + ".running_mean", 0), train_ptr(t, bn + ".running_var", 0),
                                             train_ptr(t, bn + ".num_batches_tracked", 0));
     const size_t n8 = P * C / 8;
-    bn_apply_kernel<<<static_cast<unsigned>((n8 + 255) / 256), 256, 0, r.st>>>(
-        static_cast<const __nv_bfloat16*>(z), static_cast<__nv_bfloat16*>(a), P, C, stats, train_ptr(t, bn + ".weight", 0),
+    bn_apply_kernel<float><<<static_cast<unsigned>((n8 + 255) / 256), 256, 0, r.st>>>(
+        static_cast<const float*>(z), static_cast<__nv_bfloat16*>(a), P, C, stats, train_ptr(t, bn + ".weight", 0),
         train_ptr(t, bn + ".bias", 0), 0.2f);
     CID_CHECK_CUDA(cudaGetLastError());
     t->launches += 3;
@@ -538,6 +541,7 @@ static int d_forward(const TrainRun& r, const float* img) {
         ConvParams p = conv_base(r, 1, 64, 64);
         p.bias = t->d_bias_pad[1];
         p.out = r.tbuf(TB_DZ1D); p.out_cs = 64;
+        p.out_f32 = static_cast<float*>(r.tbuf(TB_DZ1D));
         if (launch_conv_t<64, 16, 2, false, EPI_LRELU, 9, 1>(t, *tmA, t->df_tm[1], *tmO, p, r.st)) return 1;
     }
     if (bn_forward(r, 1, r.tbuf(TB_DZ1D), r.tbuf(TB_DA1), 1)) return 1;
@@ -548,6 +552,7 @@ static int d_forward(const TrainRun& r, const float* img) {
         ConvParams p = conv_base(r, 1, 64, 128);
         p.bias = t->d_bias_pad[2];
         p.out = r.tbuf(TB_DZ2D); p.out_cs = 128;
+        p.out_f32 = static_cast<float*>(r.tbuf(TB_DZ2D));
         if (launch_conv_t<128, 9, 2, false, EPI_LRELU, 10, 1>(t, *tmA, t->df_tm[2], *tmO, p, r.st)) return 1;
     }
     if (bn_forward(r, 2, r.tbuf(TB_DZ2D), r.tbuf(TB_DA2), 1)) return 1;
@@ -558,6 +563,7 @@ static int d_forward(const TrainRun& r, const float* img) {
         ConvParams p = conv_base(r, 2, 128, 128);
         p.bias = t->d_bias_pad[3];
         p.out = r.tbuf(TB_DZ3D); p.out_cs = 128;
+        p.out_f32 = static_cast<float*>(r.tbuf(TB_DZ3D));
         if (launch_conv_t<128, 16, 2, false, EPI_LRELU, 9, 1>(t, *tmA, t->df_tm[3], *tmO, p, r.st)) return 1;
     }
     if (bn_forward(r, 3, r.tbuf(TB_DZ3D), r.tbuf(TB_DA3), 2)) return 1;
@@ -581,12 +587,12 @@ static int bn_backward(const TrainRun& r, int l, const void* z, const void* da, 
     const float* beta = train_ptr(t, bn + ".bias", 0);
     CID_CHECK_CUDA(cudaMemsetAsync(sums, 0, 256 * 8, r.st));
     const int ppb = 1024;
-    bn_bwd_reduce_kernel<<<static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, r.st>>>(
-        static_cast<const __nv_bfloat16*>(z), static_cast<const __nv_bfloat16*>(da), t->fsc + FS_DPOOL, P, hw, C, stats, gamma,
+    bn_bwd_reduce_kernel<float><<<static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, r.st>>>(
+        static_cast<const float*>(z), static_cast<const __nv_bfloat16*>(da), t->fsc + FS_DPOOL, P, hw, C, stats, gamma,
         beta, 0.2f, sums, ppb);
     const size_t n8 = P * C / 8;
-    bn_bwd_apply_kernel<<<static_cast<unsigned>((n8 + 255) / 256), 256, 0, r.st>>>(
-        static_cast<const __nv_bfloat16*>(z), static_cast<const __nv_bfloat16*>(da), t->fsc + FS_DPOOL,
+    bn_bwd_apply_kernel<float><<<static_cast<unsigned>((n8 + 255) / 256), 256, 0, r.st>>>(
+        static_cast<const float*>(z), static_cast<const __nv_bfloat16*>(da), t->fsc + FS_DPOOL,
         static_cast<__nv_bfloat16*>(dz), P, hw, C, stats, gamma, beta, 0.2f, sums, static_cast<double>(P));
     t->launches += 2;
     if (param_grads) {
