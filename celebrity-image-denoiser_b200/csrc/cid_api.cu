@@ -1131,7 +1131,7 @@ int cid_train_debug_buffer(cid_train_handle t, const char* name, const void* ws,
     CID_REQUIRE(t && name && ws && dst_host, "cid_train_debug_buffer: null argument");
     static const char* names[TB_COUNT] = {"y", "gz", "gx", "dz10", "gcat1", "dz8", "dz7", "gcat2", "dz5", "dz4", "gp2", "dz3", "dz2",
                                           "gp1", "dz1", "dz0", "d_a0", "d_z1", "d_a1", "d_z2", "d_a2", "d_z3", "d_a3", "d_g3", "d_g2",
-                                          "d_g1", "d_g0"};
+                                          "d_g1", "d_g0", "u"};
     int b = -1;
     for (int i = 0; i < TB_COUNT; ++i)
         if (!strcmp(name, names[i])) b = i;

@@ -246,6 +246,51 @@ __global__ void __launch_bounds__(256) wgrad_small_kernel(const WgSmallParams p)
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
+// Tensor-core route for the same 3-channel weight gradients: U[p][ci*9 + tap] = V3[p + sign*(tap - centre)][ci] as a
+// 64-channel bf16 NHWC tensor (27 real channels, the rest zero), so that R = V64^T U is ONE plain weight-gradient GEMM of
+// wgrad_umma.cuh (T = 1, no halo); wg27_scatter_kernel then adds the 64 x 27 result into the gradient tensor.
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) im2col3_kernel(const float* v3, int v3_nchw, int sign, __nv_bfloat16* u, int B, int H,
+                                                      int W) {
+    const size_t total = static_cast<size_t>(B) * H * W;
+    const size_t pix = static_cast<size_t>(blockIdx.x) * 128 + threadIdx.x;
+    if (pix >= total) return;
+    const int x = static_cast<int>(pix % W);
+    const int y = static_cast<int>((pix / W) % H);
+    const int b = static_cast<int>(pix / (static_cast<size_t>(W) * H));
+    float f[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) f[i] = 0.f;
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) {
+            const int yy = y + sign * (ky - 1), xx = x + sign * (kx - 1);
+            if (yy < 0 || yy >= H || xx < 0 || xx >= W) continue;
+#pragma unroll
+            for (int ci = 0; ci < 3; ++ci)
+                f[ci * 9 + ky * 3 + kx] = v3_nchw ? __ldg(v3 + ((static_cast<size_t>(b) * 3 + ci) * H + yy) * W + xx)
+                                                  : __ldg(v3 + ((static_cast<size_t>(b) * H + yy) * W + xx) * 3 + ci);
+        }
+    __nv_bfloat16* dst = u + pix * 64;
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+        st_global_v4(dst + j * 8, pack_bf16x2(f[8 * j], f[8 * j + 1]), pack_bf16x2(f[8 * j + 2], f[8 * j + 3]),
+                     pack_bf16x2(f[8 * j + 4], f[8 * j + 5]), pack_bf16x2(f[8 * j + 6], f[8 * j + 7]));
+#pragma unroll
+    for (int j = 4; j < 8; ++j) st_global_v4(dst + j * 8, 0u, 0u, 0u, 0u);
+}
+
+// scratch[c64][j] (64 x 64 fp32, j = ci*9 + tap < 27) -> out[(c64*3 + ci)*9 + tap] (mode 0) / out[(ci*64 + c64)*9 + tap]
+__global__ void wg27_scatter_kernel(const float* scratch, float* out, int out_mode) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 64 * 27) return;
+    const int c = i / 27, j = i % 27, ci = j / 9, tap = j % 9;
+    float* dst = out_mode ? out + (ci * 64 + c) * 9 + tap : out + (c * 3 + ci) * 9 + tap;
+    *dst += scratch[c * 64 + j];
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
 // Generator loss head: content = MSE(y, clean); gz = (2 (y - clean) / n + gx) * (1 - y^2) = gradient w.r.t. the last
 // conv's pre-tanh output (gx = the discriminator's data gradient, already scaled by 0.001 / B through the BCE head).
 // Also the last conv's bias gradient (sum of gz per channel).
@@ -296,36 +341,44 @@ __global__ void __launch_bounds__(256) gloss_kernel(const GLossParams p) {
 template <bool SQ, typename ZT>
 __global__ void __launch_bounds__(256) colsum_kernel(const ZT* v, size_t P, int cs, int c0, int C, float* out,
                                                      double* dsum, double* dsq, int ppb) {
-    __shared__ float red[256 * 2];
-    __shared__ float red2[256 * 2];
-    const int pairs = C >> 1;             // bf16x2 per pixel
-    const int rpi = 256 / pairs;          // rows per iteration (C <= 512)
-    const int cp = threadIdx.x % pairs, rg = threadIdx.x / pairs;
+    // thread = (8-channel chunk, pixel row group); C/8 chunks (8, 16 or 32) -> 32, 16 or 8 pixels per iteration
+    __shared__ float red[256 * 8];
+    __shared__ float red2[SQ ? 256 * 8 : 8];
+    const int chunks = C >> 3;
+    const int rpi = 256 / chunks;
+    const int ck = threadIdx.x % chunks, rg = threadIdx.x / chunks;
     const size_t p0 = static_cast<size_t>(blockIdx.x) * ppb, p1 = min(P, p0 + ppb);
-    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
-    if (rg < rpi)
-        for (size_t pix = p0 + rg; pix < p1; pix += rpi) {
-            float f2[2];
-            load2(v + pix * cs + c0 + 2 * cp, f2);
-            const float lo = f2[0], hi = f2[1];
-            s0 += lo; s1 += hi;
-            if (SQ) { q0 = fmaf(lo, lo, q0); q1 = fmaf(hi, hi, q1); }
+    float s[8], q[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s[j] = 0.f; q[j] = 0.f; }
+#pragma unroll 4
+    for (size_t pix = p0 + rg; pix < p1; pix += rpi) {
+        float f[8];
+        load8(v + pix * cs + c0 + 8 * ck, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            s[j] += f[j];
+            if (SQ) q[j] = fmaf(f[j], f[j], q[j]);
         }
-    red[threadIdx.x * 2] = s0; red[threadIdx.x * 2 + 1] = s1;
-    if (SQ) { red2[threadIdx.x * 2] = q0; red2[threadIdx.x * 2 + 1] = q1; }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        red[(rg * chunks + ck) * 8 + j] = s[j];
+        if (SQ) red2[(rg * chunks + ck) * 8 + j] = q[j];
+    }
     __syncthreads();
     if (threadIdx.x < C) {
-        const int c = threadIdx.x, pr = c >> 1, e = c & 1;
-        float s = 0.f, q = 0.f;
+        const int c = threadIdx.x;
+        float a = 0.f, b = 0.f;
         for (int r = 0; r < rpi; ++r) {
-            s += red[(r * pairs + pr) * 2 + e];
-            if (SQ) q += red2[(r * pairs + pr) * 2 + e];
+            a += red[r * C + c];
+            if (SQ) b += red2[r * C + c];
         }
         if (SQ) {
-            atomicAdd(dsum + c, static_cast<double>(s));
-            atomicAdd(dsq + c, static_cast<double>(q));
+            atomicAdd(dsum + c, static_cast<double>(a));
+            atomicAdd(dsq + c, static_cast<double>(b));
         } else {
-            atomicAdd(out + c, s);
+            atomicAdd(out + c, a);
         }
     }
 }
@@ -430,54 +483,73 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const ZT* z, __nv_bfloat1
 }
 
 // dY = dA * lrelu'(y); sums[c] += {sum dY, sum dY * xhat}. dA comes from a tensor (da) or, for the layer under the
-// average pool, is broadcast from dpool[b][c] (already divided by H*W).
+// average pool, is broadcast from dpool[b][c] (already divided by H*W). 8 channels per thread.
 template <typename ZT>
 __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const ZT* z, const __nv_bfloat16* da,
                                                             const float* dpool, size_t P, size_t hw, int C,
                                                             const float* stats, const float* gamma, const float* beta,
                                                             float slope, double* sums, int ppb) {
-    __shared__ float red[256 * 2];
-    __shared__ float red2[256 * 2];
-    const int pairs = C >> 1, rpi = 256 / pairs;
-    const int cp = threadIdx.x % pairs, rg = threadIdx.x / pairs;
+    __shared__ float red[256 * 8];
+    __shared__ float red2[256 * 8];
+    const int chunks = C >> 3, rpi = 256 / chunks;
+    const int ck = threadIdx.x % chunks, rg = threadIdx.x / chunks;
     const size_t p0 = static_cast<size_t>(blockIdx.x) * ppb, p1 = min(P, p0 + ppb);
-    float s[2] = {0.f, 0.f}, q[2] = {0.f, 0.f};
-    const int c = 2 * cp;
-    const float mean[2] = {stats[2 * c], stats[2 * c + 2]}, istd[2] = {stats[2 * c + 1], stats[2 * c + 3]};
-    const float ga[2] = {gamma[c], gamma[c + 1]}, be[2] = {beta[c], beta[c + 1]};
-    if (rg < rpi)
-        for (size_t pix = p0 + rg; pix < p1; pix += rpi) {
-            float zz[2];
-            load2(z + pix * C + c, zz);
-            float dd[2];
-            if (da) {
-                const uint32_t dw = *reinterpret_cast<const uint32_t*>(da + pix * C + c);
-                dd[0] = bf16_lo(dw); dd[1] = bf16_hi(dw);
-            } else {
-                const size_t b = pix / hw;
-                dd[0] = dpool[b * C + c]; dd[1] = dpool[b * C + c + 1];
-            }
+    const int c8 = ck * 8;
+    float mean[8], istd[8], ga[8], be[8], s[8], q[8];
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const float xh = (zz[h] - mean[h]) * istd[h];
-                const float yv = ga[h] * xh + be[h];
-                const float dy = yv > 0.f ? dd[h] : dd[h] * slope;
-                s[h] += dy;
-                q[h] = fmaf(dy, xh, q[h]);
-            }
+    for (int j = 0; j < 8; ++j) {
+        mean[j] = stats[2 * (c8 + j)]; istd[j] = stats[2 * (c8 + j) + 1];
+        ga[j] = gamma[c8 + j]; be[j] = beta[c8 + j];
+        s[j] = 0.f; q[j] = 0.f;
+    }
+#pragma unroll 2
+    for (size_t pix = p0 + rg; pix < p1; pix += rpi) {
+        float zz[8], dd[8];
+        load8(z + pix * C + c8, zz);
+        if (da) {
+            load8(da + pix * C + c8, dd);
+        } else {
+            const size_t b = pix / hw;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) dd[j] = dpool[b * C + c8 + j];
         }
-    red[threadIdx.x * 2] = s[0]; red[threadIdx.x * 2 + 1] = s[1];
-    red2[threadIdx.x * 2] = q[0]; red2[threadIdx.x * 2 + 1] = q[1];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float xh = (zz[j] - mean[j]) * istd[j];
+            const float yv = ga[j] * xh + be[j];
+            const float dy = yv > 0.f ? dd[j] : dd[j] * slope;
+            s[j] += dy;
+            q[j] = fmaf(dy, xh, q[j]);
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        red[(rg * chunks + ck) * 8 + j] = s[j];
+        red2[(rg * chunks + ck) * 8 + j] = q[j];
+    }
     __syncthreads();
     if (threadIdx.x < C) {
-        const int cc = threadIdx.x, pr = cc >> 1, e = cc & 1;
+        const int cc = threadIdx.x;
         float a = 0.f, b2 = 0.f;
         for (int r = 0; r < rpi; ++r) {
-            a += red[(r * pairs + pr) * 2 + e];
-            b2 += red2[(r * pairs + pr) * 2 + e];
+            a += red[r * C + cc];
+            b2 += red2[r * C + cc];
         }
         atomicAdd(sums + cc, static_cast<double>(a));
         atomicAdd(sums + C + cc, static_cast<double>(b2));
+    }
+}
+
+// per-channel float coefficients of the backward: coef[c] = {sum_dy / n, sum_dyxhat / n}; optionally the gradients of
+// gamma / beta: += {sum dY xhat, sum dY}
+__global__ void bn_bwd_finalize_kernel(const double* sums, int C, double n, float* coef, float* ggamma, float* gbeta) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    coef[2 * c] = static_cast<float>(sums[c] / n);
+    coef[2 * c + 1] = static_cast<float>(sums[C + c] / n);
+    if (ggamma) {
+        gbeta[c] += static_cast<float>(sums[c]);
+        ggamma[c] += static_cast<float>(sums[C + c]);
     }
 }
 
@@ -486,46 +558,33 @@ template <typename ZT>
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const ZT* z, const __nv_bfloat16* da,
                                                            const float* dpool, __nv_bfloat16* dz, size_t P, size_t hw,
                                                            int C, const float* stats, const float* gamma,
-                                                           const float* beta, float slope, const double* sums, double n) {
+                                                           const float* beta, float slope, const float* coef) {
     const int chunks = C >> 3;
     const size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
     if (i >= P * chunks) return;
     const int c8 = static_cast<int>(i % chunks) * 8;
     const size_t pix = i / chunks;
-    float zf[8];
+    float zf[8], dd[8];
     load8(z + i * 8, zf);
-    uint32_t dw[4] = {0u, 0u, 0u, 0u};
     if (da) {
-        const uint4 dv = __ldg(reinterpret_cast<const uint4*>(da + i * 8));
-        dw[0] = dv.x; dw[1] = dv.y; dw[2] = dv.z; dw[3] = dv.w;
-    }
-    const size_t b = pix / hw;
-    uint32_t o[4];
+        load8(da + i * 8, dd);
+    } else {
+        const size_t b = pix / hw;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        float r[2];
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const int c = c8 + 2 * j + h;
-            const float zz = zf[2 * j + h];
-            const float dd = da ? (h ? bf16_hi(dw[j]) : bf16_lo(dw[j])) : dpool[b * C + c];
-            const float xh = (zz - stats[2 * c]) * stats[2 * c + 1];
-            const float yv = gamma[c] * xh + beta[c];
-            const float dy = yv > 0.f ? dd : dd * slope;
-            const float sdy = static_cast<float>(sums[c] / n), sdx = static_cast<float>(sums[C + c] / n);
-            r[h] = gamma[c] * stats[2 * c + 1] * (dy - sdy - xh * sdx);
-        }
-        o[j] = pack_bf16x2(r[0], r[1]);
+        for (int j = 0; j < 8; ++j) dd[j] = dpool[b * C + c8 + j];
     }
-    st_global_v4(dz + i * 8, o[0], o[1], o[2], o[3]);
-}
-
-// grads of gamma / beta: += {sum dY xhat, sum dY}
-__global__ void bn_param_grad_kernel(const double* sums, int C, float* ggamma, float* gbeta) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
-    gbeta[c] += static_cast<float>(sums[c]);
-    ggamma[c] += static_cast<float>(sums[C + c]);
+    float r[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int c = c8 + j;
+        const float istd = stats[2 * c + 1];
+        const float xh = (zf[j] - stats[2 * c]) * istd;
+        const float ga = gamma[c];
+        const float yv = ga * xh + beta[c];
+        const float dy = yv > 0.f ? dd[j] : dd[j] * slope;
+        r[j] = ga * istd * (dy - coef[2 * c] - xh * coef[2 * c + 1]);
+    }
+    st_global_v4(dz + i * 8, pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]), pack_bf16x2(r[4], r[5]), pack_bf16x2(r[6], r[7]));
 }
 
 // g *= lrelu'(a) in place (a is post-activation: its sign is the pre-activation's)
@@ -549,12 +608,16 @@ __global__ void __launch_bounds__(256) lrelu_bwd_kernel(__nv_bfloat16* g, const 
 // Discriminator head: AdaptiveAvgPool2d(1) -> Conv2d(128,1,k1) -> Sigmoid -> BCELoss(mean) and its backward.
 // ---------------------------------------------------------------------------------------------------------------------
 // pooled[b][c] = mean over hw of a[b][.][c];  grid = B, block = C
+// (pooled must be zeroed first: grid.y pixel slices accumulate with atomics)
 __global__ void avgpool_kernel(const __nv_bfloat16* a, float* pooled, int hw, int C) {
     const int b = blockIdx.x, c = threadIdx.x;
+    const int per = (hw + gridDim.y - 1) / gridDim.y;
+    const int i0 = blockIdx.y * per, i1 = min(hw, i0 + per);
     const __nv_bfloat16* src = a + static_cast<size_t>(b) * hw * C + c;
     float s = 0.f;
-    for (int i = 0; i < hw; ++i) s += __bfloat162float(src[static_cast<size_t>(i) * C]);
-    pooled[b * C + c] = s / static_cast<float>(hw);
+#pragma unroll 8
+    for (int i = i0; i < i1; ++i) s += __bfloat162float(src[static_cast<size_t>(i) * C]);
+    atomicAdd(pooled + b * C + c, s / static_cast<float>(hw));
 }
 
 // One block of 128 threads (C = 128). loss_sum += BCE(sigmoid(w.pooled + b), target) (mean over B);

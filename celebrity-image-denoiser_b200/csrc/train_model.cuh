@@ -39,12 +39,13 @@ enum TBuf {
     TB_Y, TB_GZ, TB_GX,                                                             // fp32, 3 channels, level 0
     TB_DZ10, TB_GCAT1, TB_DZ8, TB_DZ7, TB_GCAT2, TB_DZ5, TB_DZ4, TB_GP2, TB_DZ3, TB_DZ2, TB_GP1, TB_DZ1, TB_DZ0,
     TB_DA0, TB_DZ1D, TB_DA1, TB_DZ2D, TB_DA2, TB_DZ3D, TB_DA3, TB_DG3, TB_DG2, TB_DG1, TB_DG0,
+    TB_U,  // im2col of a 3-channel tensor (27 of 64 channels used): operand of the edge layers' weight gradients
     TB_COUNT
 };
 static const int kTBufC[TB_COUNT] = {3, 3, 3, 64, 128, 128, 128, 256, 256, 256, 128, 128, 128, 64, 64, 64,
-                                     64, 64, 64, 128, 128, 128, 128, 128, 128, 64, 64};
+                                     64, 64, 64, 128, 128, 128, 128, 128, 128, 64, 64, 64};
 static const int kTBufLevel[TB_COUNT] = {0, 0, 0, 0, 0, 1, 1, 1, 2, 2, 2, 1, 1, 1, 0, 0,
-                                         0, 1, 1, 1, 1, 2, 2, 2, 1, 1, 0};
+                                         0, 1, 1, 1, 1, 2, 2, 2, 1, 1, 0, 0};
 
 }  // namespace cid
 
@@ -80,7 +81,7 @@ namespace cid {
 enum { DS_BN = 0 /* 3 layers x 2 x 128 */, DS_BWD = 768 /* 3 x 2 x 128 */, DS_LOSS = 1536 /* 8 */, DS_COUNT = 1544 };
 // float scratch layout
 enum { FS_STATS = 0 /* 3 x 256 */, FS_POOLED = 768 /* B*128 */, FS_DPOOL = 768 + 128 * 1024, FS_PROBS = 768 + 2 * 128 * 1024,
-       FS_COUNT = 768 + 2 * 128 * 1024 + 1024 };
+       FS_COEF = FS_PROBS + 1024 /* 3 x 256 */, FS_WG27 = FS_COEF + 768 /* 64 x 64 */, FS_COUNT = FS_WG27 + 4096 };
 constexpr int kTrainMaxBatch = 1024;
 
 static void train_build_table(cid_train* t) {
@@ -253,7 +254,8 @@ static int launch_wgrad(cid_train* t, const CUtensorMap& tmA, const CUtensorMap&
 }
 
 // geometry of a weight gradient: 0 = 3x3 stride 1, 1 = 3x3 stride 2 (operand B = the 2x larger layer input),
-// 2 = ConvTranspose k2 s2 (operand A = the layer input, operand B = the 2x larger output gradient)
+// 2 = ConvTranspose k2 s2 (operand A = the layer input, operand B = the 2x larger output gradient),
+// 3 = plain product A^T B of two tensors of the same resolution (the im2col route of the 3-channel layers)
 static void wgrad_roles(WgParams& p, int geom, int m_ch, int n_ch, int NA, int NB) {
     p.n_roles = 0;
     for (int mb = 0; mb < m_ch / (64 * NA); ++mb)
@@ -272,13 +274,15 @@ static void wgrad_roles(WgParams& p, int geom, int m_ch, int n_ch, int NA, int N
                     push(ky - 1, -1, ky * 3 + 0, ky * 3 + 2, -1);  // even columns of the 2x input: kx = 0 (px 0), kx = 2 (px 1)
                     push(ky - 1, 0, ky * 3 + 1, -1, -1);           // odd columns: kx = 1
                 }
-            } else {
+            } else if (geom == 2) {
                 for (int q = 0; q < 4; ++q) push(q >> 1, q & 1, q, -1, -1);
+            } else {
+                push(0, 0, 0, -1, -1);
             }
         }
-    p.scale = geom == 0 ? 1 : 2;
+    p.scale = (geom == 0 || geom == 3) ? 1 : 2;
     p.pw = geom == 0 ? 10 : geom == 1 ? 9 : 8;
-    p.kk = geom == 2 ? 4 : 9;
+    p.kk = geom == 2 ? 4 : geom == 3 ? 1 : 9;
     p.s_m = n_ch;
 }
 
@@ -293,25 +297,42 @@ static int wgrad(cid_train* t, int geom, const void* A, int a_C, int m_ch, const
     const int NA = m_ch >= 128 ? 2 : 1, NB = n_ch >= 128 ? 2 : 1;
     wgrad_roles(p, geom, m_ch, n_ch, NA, NB);
     const CUtensorMap* tmA = tmap(t, A, B, H, W, a_C, 16, 8, 0);
-    const CUtensorMap* tmB = geom == 0 ? tmap(t, Bt, B, H, W, b_C, 16, 10, 0) : tmap(t, Bt, B, 2 * H, 2 * W, b_C, 16, p.pw, 1);
+    const CUtensorMap* tmB = geom == 0   ? tmap(t, Bt, B, H, W, b_C, 16, 10, 0)
+                             : geom == 3 ? tmap(t, Bt, B, H, W, b_C, 16, 8, 0)
+                                         : tmap(t, Bt, B, 2 * H, 2 * W, b_C, 16, p.pw, 1);
     if (!tmA || !tmB) return 1;
     const int T = geom == 0 ? 3 : geom == 1 ? 2 : 1;
 #define CID_WG(na, nb, tt) \
     if (NA == na && NB == nb && T == tt) return launch_wgrad<na, nb, tt>(t, *tmA, *tmB, p, st);
     CID_WG(1, 1, 3) CID_WG(1, 2, 3) CID_WG(2, 1, 3) CID_WG(2, 2, 3)
     CID_WG(1, 1, 2) CID_WG(2, 2, 2)
-    CID_WG(2, 1, 1) CID_WG(2, 2, 1)
+    CID_WG(2, 1, 1) CID_WG(2, 2, 1) CID_WG(1, 1, 1)
 #undef CID_WG
     set_error("wgrad: no kernel for NA=%d NB=%d T=%d", NA, NB, T);
     return 1;
 }
 
 static int colsum(cid_train* t, const void* v, size_t P, int cs, int c0, int C, float* out, cudaStream_t st) {
-    const int ppb = 2048;
+    const int ppb = 1024;
     colsum_kernel<false, __nv_bfloat16><<<static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, st>>>(
         static_cast<const __nv_bfloat16*>(v), P, cs, c0, C, out, nullptr, nullptr, ppb);
     CID_CHECK_CUDA(cudaGetLastError());
     t->launches++;
+    return 0;
+}
+
+// weight gradient of a 3-channel layer: R[c64][ci*9+tap] = sum_p v64[p][c64] * v3[p + sign*(tap - centre)][ci]
+static int wgrad_edge(cid_train* t, const void* v64, const float* v3, int v3_nchw, int sign, float* out, int out_mode,
+                      void* ubuf, int B, int H, int W, cudaStream_t st) {
+    const size_t P = static_cast<size_t>(B) * H * W;
+    im2col3_kernel<<<static_cast<unsigned>((P + 127) / 128), 128, 0, st>>>(v3, v3_nchw, sign, static_cast<__nv_bfloat16*>(ubuf), B, H, W);
+    CID_CHECK_CUDA(cudaGetLastError());
+    float* scratch = t->fsc + FS_WG27;
+    CID_CHECK_CUDA(cudaMemsetAsync(scratch, 0, 4096 * 4, st));
+    if (wgrad(t, 3, v64, 64, 64, ubuf, 64, 64, B, H, W, scratch, st)) return 1;
+    wg27_scatter_kernel<<<(64 * 27 + 255) / 256, 256, 0, st>>>(scratch, out, out_mode);
+    CID_CHECK_CUDA(cudaGetLastError());
+    t->launches += 2;
     return 0;
 }
 
@@ -567,8 +588,9 @@ static int d_forward(const TrainRun& r, const float* img) {
         if (launch_conv_t<128, 16, 2, false, EPI_LRELU, 9, 1>(t, *tmA, t->df_tm[3], *tmO, p, r.st)) return 1;
     }
     if (bn_forward(r, 3, r.tbuf(TB_DZ3D), r.tbuf(TB_DA3), 2)) return 1;
-    avgpool_kernel<<<B, 128, 0, r.st>>>(static_cast<const __nv_bfloat16*>(r.tbuf(TB_DA3)), t->fsc + FS_POOLED,
-                                        (H >> 2) * (W >> 2), 128);
+    CID_CHECK_CUDA(cudaMemsetAsync(t->fsc + FS_POOLED, 0, static_cast<size_t>(B) * 128 * 4, r.st));
+    avgpool_kernel<<<dim3(B, 16), 128, 0, r.st>>>(static_cast<const __nv_bfloat16*>(r.tbuf(TB_DA3)), t->fsc + FS_POOLED,
+                                                  (H >> 2) * (W >> 2), 128);
     CID_CHECK_CUDA(cudaGetLastError());
     t->launches++;
     return 0;
@@ -590,15 +612,15 @@ static int bn_backward(const TrainRun& r, int l, const void* z, const void* da, 
     bn_bwd_reduce_kernel<float><<<static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, r.st>>>(
         static_cast<const float*>(z), static_cast<const __nv_bfloat16*>(da), t->fsc + FS_DPOOL, P, hw, C, stats, gamma,
         beta, 0.2f, sums, ppb);
+    float* coef = t->fsc + FS_COEF + (l - 1) * 256;
+    bn_bwd_finalize_kernel<<<1, 128, 0, r.st>>>(sums, C, static_cast<double>(P), coef,
+                                                param_grads ? train_ptr(t, bn + ".weight", 1) : nullptr,
+                                                param_grads ? train_ptr(t, bn + ".bias", 1) : nullptr);
     const size_t n8 = P * C / 8;
     bn_bwd_apply_kernel<float><<<static_cast<unsigned>((n8 + 255) / 256), 256, 0, r.st>>>(
         static_cast<const float*>(z), static_cast<const __nv_bfloat16*>(da), t->fsc + FS_DPOOL,
-        static_cast<__nv_bfloat16*>(dz), P, hw, C, stats, gamma, beta, 0.2f, sums, static_cast<double>(P));
-    t->launches += 2;
-    if (param_grads) {
-        bn_param_grad_kernel<<<1, 128, 0, r.st>>>(sums, C, train_ptr(t, bn + ".weight", 1), train_ptr(t, bn + ".bias", 1));
-        t->launches++;
-    }
+        static_cast<__nv_bfloat16*>(dz), P, hw, C, stats, gamma, beta, 0.2f, coef);
+    t->launches += 3;
     CID_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -666,15 +688,7 @@ static int d_backward(const TrainRun& r, const float* img, float target, float s
     }
     if (param_grads) {
         if (colsum(t, r.tbuf(TB_DG0), r.pixels(0), 64, 0, 64, gradp(0, ".bias"), r.st)) return 1;
-        WgSmallParams p;
-        memset(&p, 0, sizeof(p));
-        p.B = B; p.H = H; p.W = W;
-        p.v64 = static_cast<const __nv_bfloat16*>(r.tbuf(TB_DG0));
-        p.v3 = img; p.v3_nchw = 1; p.sign = 1;
-        p.out = gradp(0, ".weight"); p.out_mode = 0; p.ppb = 1024;
-        wgrad_small_kernel<<<static_cast<unsigned>((r.pixels(0) + p.ppb - 1) / p.ppb), 256, 0, r.st>>>(p);
-        CID_CHECK_CUDA(cudaGetLastError());
-        t->launches++;
+        if (wgrad_edge(t, r.tbuf(TB_DG0), img, 1, 1, gradp(0, ".weight"), 0, r.tbuf(TB_U), B, H, W, r.st)) return 1;
     }
     if (want_gx) {
         Conv64to3Params p;
@@ -706,13 +720,8 @@ static int g_backward_layers(const TrainRun& r, const float* noisy) {
     };
     // L11 upconv1.2 (64 -> 3): bias gradient came with gz
     {
-        WgSmallParams p;
-        memset(&p, 0, sizeof(p));
-        p.B = B; p.H = H; p.W = W;
-        p.v64 = static_cast<const __nv_bfloat16*>(r.gbuf(B_U1A));
-        p.v3 = static_cast<const float*>(r.tbuf(TB_GZ)); p.v3_nchw = 0; p.sign = -1;
-        p.out = gw(11); p.out_mode = 1; p.ppb = 1024;
-        wgrad_small_kernel<<<static_cast<unsigned>((r.pixels(0) + p.ppb - 1) / p.ppb), 256, 0, r.st>>>(p);
+        if (wgrad_edge(t, r.gbuf(B_U1A), static_cast<const float*>(r.tbuf(TB_GZ)), 0, -1, gw(11), 1, r.tbuf(TB_U), B, H, W, r.st))
+            return 1;
         Conv3to64Params q;
         memset(&q, 0, sizeof(q));
         q.B = B; q.H = H; q.W = W;
@@ -723,7 +732,7 @@ static int g_backward_layers(const TrainRun& r, const float* noisy) {
         q.out = static_cast<__nv_bfloat16*>(r.tbuf(TB_DZ10));
         conv3to64_kernel<<<static_cast<unsigned>((r.pixels(0) + 127) / 128), 128, 0, r.st>>>(q);
         CID_CHECK_CUDA(cudaGetLastError());
-        t->launches += 2;
+        t->launches++;
     }
     // L10 upconv1.0 (cat1 128 -> 64)
     if (colsum(t, r.tbuf(TB_DZ10), r.pixels(0), 64, 0, 64, gb(10), r.st)) return 1;
@@ -772,15 +781,7 @@ static int g_backward_layers(const TrainRun& r, const float* noisy) {
     // L0 down1.0 (3 -> 64)
     if (colsum(t, r.tbuf(TB_DZ0), r.pixels(0), 64, 0, 64, gb(0), r.st)) return 1;
     {
-        WgSmallParams p;
-        memset(&p, 0, sizeof(p));
-        p.B = B; p.H = H; p.W = W;
-        p.v64 = static_cast<const __nv_bfloat16*>(r.tbuf(TB_DZ0));
-        p.v3 = noisy; p.v3_nchw = 1; p.sign = 1;
-        p.out = gw(0); p.out_mode = 0; p.ppb = 1024;
-        wgrad_small_kernel<<<static_cast<unsigned>((r.pixels(0) + p.ppb - 1) / p.ppb), 256, 0, r.st>>>(p);
-        CID_CHECK_CUDA(cudaGetLastError());
-        t->launches++;
+        if (wgrad_edge(t, r.tbuf(TB_DZ0), noisy, 1, 1, gw(0), 0, r.tbuf(TB_U), B, H, W, r.st)) return 1;
     }
     return 0;
 }
