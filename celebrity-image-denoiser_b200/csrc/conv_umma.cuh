@@ -31,6 +31,7 @@ namespace cid {
 enum : int {  // TANH_*: last_conv_umma.cuh; LRELU/T4: the Keras cGAN layers (leaky ReLU with ConvParams::slope)
     EPI_RELU = 0, EPI_RELU_POOL = 1, EPI_CONVT = 2, EPI_TANH_F32 = 3, EPI_TANH_U8 = 4, EPI_LRELU = 5, EPI_T4 = 6, EPI_TANH_F32_NHWC = 7,
     EPI_ADD = 8,  // bias + residual add(s), no activation (ESRGAN / SRGAN skip connections)
+    EPI_LINEAR_F32_NHWC = 10,  // last_conv_umma.cuh without tanh: the discriminator's 64 -> 3 input gradient
     EPI_DGRAD = 9  // training: data gradient = bias-free linear output, optionally masked by the ReLU of the layer's
                    // own input activation (ConvParams::res2 = that activation, > 0 keeps the gradient)
 };

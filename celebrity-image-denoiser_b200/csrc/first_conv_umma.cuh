@@ -46,6 +46,7 @@ struct FirstParams {
     const float* bias;    // fp32 [64]
     __nv_bfloat16* out;   // NHWC [B,H,W,64]
     int tiles_x, tiles_y, m_tiles;
+    float slope;          // negative slope of the activation: 0 = ReLU (generator), 0.2 = the discriminator's LeakyReLU
 };
 
 // un-swizzled K-major descriptor: start[0,14) LBO[16,30) SBO[32,46) version[46,48)=1 layout[61,64)=0
@@ -282,10 +283,11 @@ first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParam
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     const float4 bb = __ldg(b4 + j);
-                    pk[2 * j + 0] = pack_bf16x2(fmaxf(__uint_as_float(v[4 * j + 0]) + bb.x, 0.f),
-                                                fmaxf(__uint_as_float(v[4 * j + 1]) + bb.y, 0.f));
-                    pk[2 * j + 1] = pack_bf16x2(fmaxf(__uint_as_float(v[4 * j + 2]) + bb.z, 0.f),
-                                                fmaxf(__uint_as_float(v[4 * j + 3]) + bb.w, 0.f));
+                    // max(x,0) + slope * min(x,0): exactly ReLU for slope 0 (+0 + -0 = +0)
+                    const float x0 = __uint_as_float(v[4 * j + 0]) + bb.x, x1 = __uint_as_float(v[4 * j + 1]) + bb.y;
+                    const float x2 = __uint_as_float(v[4 * j + 2]) + bb.z, x3 = __uint_as_float(v[4 * j + 3]) + bb.w;
+                    pk[2 * j + 0] = pack_bf16x2(fmaxf(x0, 0.f) + p.slope * fminf(x0, 0.f), fmaxf(x1, 0.f) + p.slope * fminf(x1, 0.f));
+                    pk[2 * j + 1] = pack_bf16x2(fmaxf(x2, 0.f) + p.slope * fminf(x2, 0.f), fmaxf(x3, 0.f) + p.slope * fminf(x3, 0.f));
                 }
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {

@@ -59,7 +59,8 @@ template <int EPI>
 __global__ void __launch_bounds__(kLastThreads, 1)
 last_conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                       const LastParams p) {
-    static_assert(EPI == EPI_TANH_F32 || EPI == EPI_TANH_U8 || EPI == EPI_TANH_F32_NHWC, "final layer epilogues only");
+    static_assert(EPI == EPI_TANH_F32 || EPI == EPI_TANH_U8 || EPI == EPI_TANH_F32_NHWC || EPI == EPI_LINEAR_F32_NHWC,
+                  "final layer epilogues only");
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* w_smem = smem;
@@ -212,14 +213,15 @@ last_conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                 }
             __syncwarp();
             if (lane == 0) mbar_arrive(&s_empty[g * 2 + sb]);
-            const float t[3] = {tanhf(a0), tanhf(a1), tanhf(a2)};
+            const float t[3] = {EPI == EPI_LINEAR_F32_NHWC ? a0 : tanhf(a0), EPI == EPI_LINEAR_F32_NHWC ? a1 : tanhf(a1),
+                                EPI == EPI_LINEAR_F32_NHWC ? a2 : tanhf(a2)};
             const int y = tc.y0 + yl, x = tc.x0 + xl;
             if (y < p.H && x < p.W) {
                 if constexpr (EPI == EPI_TANH_F32) {
                     float* out = static_cast<float*>(p.out);
 #pragma unroll
                     for (int c = 0; c < 3; ++c) out[((static_cast<size_t>(tc.b) * 3 + c) * p.H + y) * p.W + x] = t[c];
-                } else if constexpr (EPI == EPI_TANH_F32_NHWC) {
+                } else if constexpr (EPI == EPI_TANH_F32_NHWC || EPI == EPI_LINEAR_F32_NHWC) {
                     // Keras `predict` surface (backend/app.py:458): fp32 NHWC
                     float* out = static_cast<float*>(p.out) + ((static_cast<size_t>(tc.b) * p.H + y) * p.W + x) * 3;
                     out[0] = t[0];

@@ -443,43 +443,42 @@ __global__ void __launch_bounds__(256) poolbwd_kernel(const __nv_bfloat16* e, co
 // ---------------------------------------------------------------------------------------------------------------------
 // stats[c] = {mean, invstd}; running statistics updated as torch does (unbiased variance)
 __global__ void bn_finalize_kernel(const double* dsum, const double* dsq, double n, int C, float eps, float momentum,
-                                   float* stats, float* running_mean, float* running_var, float* nbt) {
+                                   float* stats, float* running_mean, float* running_var, float* nbt, const float* gamma,
+                                   const float* beta, float* tab) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     const double mean = dsum[c] / n;
     double var = dsq[c] / n - mean * mean;
     if (var < 0) var = 0;
     stats[2 * c] = static_cast<float>(mean);
-    stats[2 * c + 1] = static_cast<float>(1.0 / sqrt(var + static_cast<double>(eps)));
+    const float istd = static_cast<float>(1.0 / sqrt(var + static_cast<double>(eps)));
+    stats[2 * c + 1] = istd;
+    tab[2 * c] = gamma[c] * istd;
+    tab[2 * c + 1] = beta[c] - gamma[c] * istd * static_cast<float>(mean);
     running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * static_cast<float>(mean);
     running_var[c] = (1.f - momentum) * running_var[c] + momentum * static_cast<float>(var * n / (n - 1.0));
     if (c == 0) nbt[0] += 1.f;
 }
 
-// a = lrelu(gamma * (z - mean) * invstd + beta); 8 channels per thread
+// a = lrelu(z * a2 + b2) with tab[c] = {a2 = gamma * invstd, b2 = beta - gamma * mean * invstd}; 8 channels per thread
 template <typename ZT>
-__global__ void __launch_bounds__(256) bn_apply_kernel(const ZT* z, __nv_bfloat16* a, size_t P, int C,
-                                                       const float* stats, const float* gamma, const float* beta,
+__global__ void __launch_bounds__(256) bn_apply_kernel(const ZT* z, __nv_bfloat16* a, size_t P, int C, const float* tab,
                                                        float slope) {
+    __shared__ float st[2 * 256];
+    for (int i = threadIdx.x; i < 2 * C; i += 256) st[i] = tab[i];
+    __syncthreads();
     const int chunks = C >> 3;
     const size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
     if (i >= P * chunks) return;
     const int c8 = static_cast<int>(i % chunks) * 8;
-    float zf[8];
+    float zf[8], r[8];
     load8(z + i * 8, zf);
-    uint32_t o[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        float f[2] = {zf[2 * j], zf[2 * j + 1]};
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const int c = c8 + 2 * j + h;
-            float yv = gamma[c] * (f[h] - stats[2 * c]) * stats[2 * c + 1] + beta[c];
-            f[h] = yv > 0.f ? yv : yv * slope;
-        }
-        o[j] = pack_bf16x2(f[0], f[1]);
+    for (int j = 0; j < 8; ++j) {
+        const float yv = fmaf(zf[j], st[2 * (c8 + j)], st[2 * (c8 + j) + 1]);
+        r[j] = yv > 0.f ? yv : yv * slope;
     }
-    st_global_v4(a + i * 8, o[0], o[1], o[2], o[3]);
+    st_global_v4(a + i * 8, pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]), pack_bf16x2(r[4], r[5]), pack_bf16x2(r[6], r[7]));
 }
 
 // dY = dA * lrelu'(y); sums[c] += {sum dY, sum dY * xhat}. dA comes from a tensor (da) or, for the layer under the
@@ -540,25 +539,34 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const ZT* z, const _
     }
 }
 
-// per-channel float coefficients of the backward: coef[c] = {sum_dy / n, sum_dyxhat / n}; optionally the gradients of
-// gamma / beta: += {sum dY xhat, sum dY}
-__global__ void bn_bwd_finalize_kernel(const double* sums, int C, double n, float* coef, float* ggamma, float* gbeta) {
+// per-channel table of the backward apply: with xh = (z - mean) * istd, y = z * a2 + b2, dy = dA * lrelu'(y):
+//   dz = gamma * istd * (dy - sum_dy / n - xh * sum_dyxh / n) = k0 * dy - c1 - z * c2
+// btab[c] = {a2, b2, k0, c1, c2}; optionally the gradients of gamma / beta: += {sum dY xhat, sum dY}
+__global__ void bn_bwd_finalize_kernel(const double* sums, int C, double n, const float* stats, const float* gamma,
+                                       const float* beta, float* btab, float* ggamma, float* gbeta) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
-    coef[2 * c] = static_cast<float>(sums[c] / n);
-    coef[2 * c + 1] = static_cast<float>(sums[C + c] / n);
+    const float mean = stats[2 * c], istd = stats[2 * c + 1], ga = gamma[c];
+    const float m_dy = static_cast<float>(sums[c] / n), m_dyx = static_cast<float>(sums[C + c] / n);
+    const float k0 = ga * istd;
+    btab[5 * c + 0] = ga * istd;
+    btab[5 * c + 1] = beta[c] - ga * istd * mean;
+    btab[5 * c + 2] = k0;
+    btab[5 * c + 3] = k0 * (m_dy - m_dyx * mean * istd);
+    btab[5 * c + 4] = k0 * m_dyx * istd;
     if (ggamma) {
         gbeta[c] += static_cast<float>(sums[c]);
         ggamma[c] += static_cast<float>(sums[C + c]);
     }
 }
 
-// dZ = gamma * invstd * (dY - sum_dy / n - xhat * sum_dyxhat / n)
 template <typename ZT>
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const ZT* z, const __nv_bfloat16* da,
                                                            const float* dpool, __nv_bfloat16* dz, size_t P, size_t hw,
-                                                           int C, const float* stats, const float* gamma,
-                                                           const float* beta, float slope, const float* coef) {
+                                                           int C, float slope, const float* btab) {
+    __shared__ float st[5 * 256];
+    for (int i = threadIdx.x; i < 5 * C; i += 256) st[i] = btab[i];
+    __syncthreads();
     const int chunks = C >> 3;
     const size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
     if (i >= P * chunks) return;
@@ -570,19 +578,16 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const ZT* z, const __
         load8(da + i * 8, dd);
     } else {
         const size_t b = pix / hw;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) dd[j] = dpool[b * C + c8 + j];
+        const float4 d0 = *reinterpret_cast<const float4*>(dpool + b * C + c8), d1 = *reinterpret_cast<const float4*>(dpool + b * C + c8 + 4);
+        dd[0] = d0.x; dd[1] = d0.y; dd[2] = d0.z; dd[3] = d0.w; dd[4] = d1.x; dd[5] = d1.y; dd[6] = d1.z; dd[7] = d1.w;
     }
     float r[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        const int c = c8 + j;
-        const float istd = stats[2 * c + 1];
-        const float xh = (zf[j] - stats[2 * c]) * istd;
-        const float ga = gamma[c];
-        const float yv = ga * xh + beta[c];
+        const float* t5 = st + 5 * (c8 + j);
+        const float yv = fmaf(zf[j], t5[0], t5[1]);
         const float dy = yv > 0.f ? dd[j] : dd[j] * slope;
-        r[j] = ga * istd * (dy - coef[2 * c] - xh * coef[2 * c + 1]);
+        r[j] = fmaf(t5[2], dy, -t5[3]) - zf[j] * t5[4];
     }
     st_global_v4(dz + i * 8, pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]), pack_bf16x2(r[4], r[5]), pack_bf16x2(r[6], r[7]));
 }
@@ -690,7 +695,8 @@ enum RepackMode {
     RP_K4_FWD = 4,       // dst[((ky*4+kx)*cout + co)*cin + ci] = ky,kx < 3 ? w[(co*cin + ci)*9 + ky*3 + kx] : 0
     RP_T4_DGRAD = 5,     // dst[((ky*4+kx)*cin + ci)*cout + co] = same value
     RP_FIRST = 6,        // first_conv_umma.cuh operand: [tap][k chunk][cout 64][8] with hi/lo split
-    RP_LAST = 7          // last_conv_umma.cuh operand: row tap*3 + co of 128 rows x 64 channels
+    RP_LAST = 7,         // last_conv_umma.cuh operand: row tap*3 + co of 128 rows x 64 channels
+    RP_LAST_DGRAD = 8    // the same operand for the data gradient of a Conv2d(3,64): row tap*3 + ci = w[co][ci][8 - tap]
 };
 
 __global__ void __launch_bounds__(256) repack_kernel(int mode, const float* w, __nv_bfloat16* dst, int cin, int cout,
@@ -761,6 +767,13 @@ __global__ void __launch_bounds__(256) repack_kernel(int mode, const float* w, _
             const int row = static_cast<int>(i >> 6);
             const int tap = row / 3, co = row % 3;
             if (tap < 9) val = w[(static_cast<size_t>(co) * 64 + ci) * 9 + tap];
+            break;
+        }
+        case RP_LAST_DGRAD: {
+            const int co = static_cast<int>(i & 63);
+            const int row = static_cast<int>(i >> 6);
+            const int tap = row / 3, ci = row % 3;
+            if (tap < 9) val = w[(static_cast<size_t>(co) * 3 + ci) * 9 + 8 - tap];
             break;
         }
     }

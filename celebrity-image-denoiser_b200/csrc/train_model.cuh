@@ -81,7 +81,8 @@ namespace cid {
 enum { DS_BN = 0 /* 3 layers x 2 x 128 */, DS_BWD = 768 /* 3 x 2 x 128 */, DS_LOSS = 1536 /* 8 */, DS_COUNT = 1544 };
 // float scratch layout
 enum { FS_STATS = 0 /* 3 x 256 */, FS_POOLED = 768 /* B*128 */, FS_DPOOL = 768 + 128 * 1024, FS_PROBS = 768 + 2 * 128 * 1024,
-       FS_COEF = FS_PROBS + 1024 /* 3 x 256 */, FS_WG27 = FS_COEF + 768 /* 64 x 64 */, FS_COUNT = FS_WG27 + 4096 };
+       FS_TAB = FS_PROBS + 1024 /* 3 x 256: forward affine table */, FS_BTAB = FS_TAB + 768 /* 3 x 5 x 128 */,
+       FS_WG27 = FS_BTAB + 1920 /* 64 x 64 */, FS_COUNT = FS_WG27 + 4096 };
 constexpr int kTrainMaxBatch = 1024;
 
 static void train_build_table(cid_train* t) {
@@ -366,6 +367,9 @@ static int train_alloc_packs(cid_train* t) {
         if (make_weight_map(&t->df_tm[l], t->df_w[l], (s2 ? 16 : 9) * cout, cin, cout)) return 1;
         if (make_weight_map(&t->dd_tm[l], t->dd_w[l], (s2 ? 16 : 9) * cin, cout, cin)) return 1;
     }
+    CID_CHECK_CUDA(cudaMalloc(&t->df_w[0], kFirstWBytes));      // first_conv_umma operand of model.0
+    CID_CHECK_CUDA(cudaMalloc(&t->dd_w[0], 128 * 64 * 2));      // last_conv_umma operand of model.0's data gradient
+    if (make_weight_map(&t->dd_tm[0], t->dd_w[0], 128, 64, 128)) return 1;
     for (int l = 0; l < 4; ++l) {
         CID_CHECK_CUDA(cudaMalloc(reinterpret_cast<void**>(&t->d_bias_pad[l]), 256 * 4));
         CID_CHECK_CUDA(cudaMemset(t->d_bias_pad[l], 0, 256 * 4));
@@ -437,7 +441,11 @@ static int train_repack(cid_train* t, int which, cudaStream_t st) {
             const float* w = train_ptr(t, base + ".weight", 0);
             const float* b = train_ptr(t, base + ".bias", 0);
             CID_CHECK_CUDA(cudaMemcpyAsync(t->d_bias_pad[l], b, kDCout[l] * 4, cudaMemcpyDeviceToDevice, st));
-            if (l == 0) continue;  // conv0 runs on CUDA cores from the fp32 master
+            if (l == 0) {
+                if (repack(t, RP_FIRST, w, t->df_w[0], 3, 64, 64, kFirstWBytes / 2, st)) return 1;
+                if (repack(t, RP_LAST_DGRAD, w, t->dd_w[0], 3, 64, 64, 128 * 64, st)) return 1;
+                continue;
+            }
             const int cin = kDCin[l], cout = kDCout[l];
             const bool s2 = l != DL_CONV2;
             const size_t n = static_cast<size_t>(s2 ? 16 : 9) * cin * cout;
@@ -527,13 +535,14 @@ static int bn_forward(const TrainRun& r, int l, const void* z, void* a, int lv) 
     const int ppb = 1024;
     colsum_kernel<true, float><<<static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, r.st>>>(
         static_cast<const float*>(z), P, C, 0, C, nullptr, sums, sums + 128, ppb);
+    float* tab = t->fsc + FS_TAB + (l - 1) * 256;
     bn_finalize_kernel<<<1, 128, 0, r.st>>>(sums, sums + 128, static_cast<double>(P), C, 1e-5f, 0.1f, stats,
                                             train_ptr(t, bn + ".running_mean", 0), train_ptr(t, bn + ".running_var", 0),
-                                            train_ptr(t, bn + ".num_batches_tracked", 0));
+                                            train_ptr(t, bn + ".num_batches_tracked", 0), train_ptr(t, bn + ".weight", 0),
+                                            train_ptr(t, bn + ".bias", 0), tab);
     const size_t n8 = P * C / 8;
     bn_apply_kernel<float><<<static_cast<unsigned>((n8 + 255) / 256), 256, 0, r.st>>>(
-        static_cast<const float*>(z), static_cast<__nv_bfloat16*>(a), P, C, stats, train_ptr(t, bn + ".weight", 0),
-        train_ptr(t, bn + ".bias", 0), 0.2f);
+        static_cast<const float*>(z), static_cast<__nv_bfloat16*>(a), P, C, tab, 0.2f);
     CID_CHECK_CUDA(cudaGetLastError());
     t->launches += 3;
     return 0;
@@ -542,16 +551,23 @@ static int bn_forward(const TrainRun& r, int l, const void* z, void* a, int lv) 
 static int d_forward(const TrainRun& r, const float* img) {
     cid_train* t = r.t;
     const int B = r.B, H = r.H, W = r.W;
-    {  // model.0 + LeakyReLU(0.2)
-        Conv3to64Params p;
-        memset(&p, 0, sizeof(p));
-        p.B = B; p.H = H; p.W = W;
-        p.in = img; p.in_nchw = 1;
-        p.w = train_ptr(t, "discriminator.model.0.weight", 0);
-        p.bias = train_ptr(t, "discriminator.model.0.bias", 0);
-        p.slope = 0.2f;
-        p.out = static_cast<__nv_bfloat16*>(r.tbuf(TB_DA0));
-        conv3to64_kernel<<<static_cast<unsigned>((r.pixels(0) + 127) / 128), 128, 0, r.st>>>(p);
+    {  // model.0 + LeakyReLU(0.2): the generator's first-conv kernel (hi/lo-split input and weights) with slope 0.2
+        const CUtensorMap* tmO = tmap(t, r.tbuf(TB_DA0), B, H, W, 64, 16, 8, 0);
+        if (!tmO) return 1;
+        FirstParams fp;
+        memset(&fp, 0, sizeof(fp));
+        fp.B = B; fp.H = H; fp.W = W;
+        fp.in = img;
+        fp.bias = t->d_bias_pad[0];
+        fp.out = static_cast<__nv_bfloat16*>(r.tbuf(TB_DA0));
+        fp.tiles_x = (W + 7) / 8;
+        fp.tiles_y = (H + 15) / 16;
+        fp.m_tiles = B * fp.tiles_x * fp.tiles_y;
+        fp.w_packed = static_cast<const uint4*>(t->df_w[0]);
+        fp.slope = 0.2f;
+        CID_CHECK_CUDA(cudaFuncSetAttribute(first_conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFirstSmem));
+        const int grid = std::min(fp.m_tiles, t->num_sms * kFirstCtasPerSm);
+        CID_CHECK_CUDA(launch_ex(t->g, first_conv_umma_kernel<false>, grid, kFirstThreads, kFirstSmem, r.st, 1, *tmO, fp));
         CID_CHECK_CUDA(cudaGetLastError());
         t->launches++;
     }
@@ -612,14 +628,14 @@ static int bn_backward(const TrainRun& r, int l, const void* z, const void* da, 
     bn_bwd_reduce_kernel<float><<<static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, r.st>>>(
         static_cast<const float*>(z), static_cast<const __nv_bfloat16*>(da), t->fsc + FS_DPOOL, P, hw, C, stats, gamma,
         beta, 0.2f, sums, ppb);
-    float* coef = t->fsc + FS_COEF + (l - 1) * 256;
-    bn_bwd_finalize_kernel<<<1, 128, 0, r.st>>>(sums, C, static_cast<double>(P), coef,
+    float* btab = t->fsc + FS_BTAB + (l - 1) * 640;
+    bn_bwd_finalize_kernel<<<1, 128, 0, r.st>>>(sums, C, static_cast<double>(P), stats, gamma, beta, btab,
                                                 param_grads ? train_ptr(t, bn + ".weight", 1) : nullptr,
                                                 param_grads ? train_ptr(t, bn + ".bias", 1) : nullptr);
     const size_t n8 = P * C / 8;
     bn_bwd_apply_kernel<float><<<static_cast<unsigned>((n8 + 255) / 256), 256, 0, r.st>>>(
         static_cast<const float*>(z), static_cast<const __nv_bfloat16*>(da), t->fsc + FS_DPOOL,
-        static_cast<__nv_bfloat16*>(dz), P, hw, C, stats, gamma, beta, 0.2f, coef);
+        static_cast<__nv_bfloat16*>(dz), P, hw, C, 0.2f, btab);
     t->launches += 3;
     CID_CHECK_CUDA(cudaGetLastError());
     return 0;
@@ -691,12 +707,23 @@ static int d_backward(const TrainRun& r, const float* img, float target, float s
         if (wgrad_edge(t, r.tbuf(TB_DG0), img, 1, 1, gradp(0, ".weight"), 0, r.tbuf(TB_U), B, H, W, r.st)) return 1;
     }
     if (want_gx) {
-        Conv64to3Params p;
-        p.B = B; p.H = H; p.W = W;
-        p.dz = static_cast<const __nv_bfloat16*>(r.tbuf(TB_DG0));
-        p.w = train_ptr(t, "discriminator.model.0.weight", 0);
-        p.out = static_cast<float*>(r.tbuf(TB_GX));
-        conv64to3_dgrad_kernel<<<static_cast<unsigned>((r.pixels(0) + 127) / 128), 128, 0, r.st>>>(p);
+        // 64 -> 3 data gradient on the last-conv kernel (transposed GEMM) with a linear fp32 NHWC epilogue
+        const CUtensorMap* tmA = tmap(t, r.tbuf(TB_DG0), B, H, W, 64, 18, 10, 0);
+        if (!tmA) return 1;
+        LastParams lp;
+        memset(&lp, 0, sizeof(lp));
+        lp.B = B; lp.H = H; lp.W = W;
+        lp.tiles_x = (W + 7) / 8;
+        lp.tiles_y = (H + 15) / 16;
+        lp.m_tiles = B * lp.tiles_x * lp.tiles_y;
+        lp.stages = std::min(kLastMaxStages, (t->max_smem - last_conv_smem(0)) / kLastStageBytes);
+        CID_REQUIRE(lp.stages >= 2, "last conv: shared memory too small");
+        lp.bias = t->zero_bias;
+        lp.out = r.tbuf(TB_GX);
+        const int smem = last_conv_smem(lp.stages);
+        CID_CHECK_CUDA(cudaFuncSetAttribute(last_conv_umma_kernel<EPI_LINEAR_F32_NHWC>, cudaFuncAttributeMaxDynamicSharedMemorySize, t->max_smem));
+        const int grid = std::min(lp.m_tiles, t->num_sms);
+        CID_CHECK_CUDA(launch_ex(t->g, last_conv_umma_kernel<EPI_LINEAR_F32_NHWC>, grid, kLastThreads, smem, r.st, 1, *tmA, t->dd_tm[0], lp));
         CID_CHECK_CUDA(cudaGetLastError());
         t->launches++;
     }
