@@ -9,13 +9,14 @@ ap = argparse.ArgumentParser()
 ap.add_argument("csv")
 ap.add_argument("--start", default="first_conv_umma")
 ap.add_argument("--top", type=int, default=60)
+ap.add_argument("--last", type=int, default=0, help="take the last N launches instead")
 a = ap.parse_args()
 with open(a.csv) as f:
     lines = [l for l in f if not l.startswith("==")]
 rows = list(csv.DictReader(lines))
 names = [x["Kernel Name"] for x in rows]
 idx = [i for i, n in enumerate(names) if a.start in n]
-step = rows[idx[-1]:] if idx else rows
+step = rows[-a.last:] if a.last else (rows[idx[-1]:] if idx else rows)
 agg, tot = collections.OrderedDict(), 0.0
 for x in step:
     v = float(x["Metric Value"].replace(",", ""))
