@@ -60,10 +60,11 @@ struct cid_train {
     // bf16 operand packs owned by the library
     void* gd_w[12] = {nullptr};       // generator data-gradient packs (layers 1..10)
     CUtensorMap gd_tm[12];
+    CUtensorMap gd_tmh[12];           // same packs, box of N/2 rows (CTA-pair kernels load half a weight tile each)
     int gd_n[12] = {0};               // tile width N of the pack's tensor map
     void* df_w[4] = {nullptr};        // discriminator forward packs (conv1..3)
     void* dd_w[4] = {nullptr};        // discriminator data-gradient packs (conv1..3)
-    CUtensorMap df_tm[4], dd_tm[4];
+    CUtensorMap df_tm[4], dd_tm[4], dd_tmh[4];
     float* zero_bias = nullptr;       // 512 zeros
     float* d_bias_pad[4] = {nullptr}; // fp32 conv biases padded for float4 epilogue loads
     double* dsc = nullptr;            // double scratch: BN sums, backward sums, losses
@@ -261,12 +262,15 @@ static void wgrad_roles(WgParams& p, int geom, int m_ch, int n_ch, int NA, int N
     p.n_roles = 0;
     for (int mb = 0; mb < m_ch / (64 * NA); ++mb)
         for (int nb = 0; nb < n_ch / (64 * NB); ++nb) {
+            bool first_of_block = true;
             auto push = [&](int oy, int ox, int t0, int t1, int t2) {
                 WgRole& r = p.roles[p.n_roles++];
                 r.a_c0 = r.m0 = mb * 64 * NA;
                 r.b_c0 = r.n0 = nb * 64 * NB;
                 r.oy = oy; r.ox = ox;
                 r.tap[0] = t0; r.tap[1] = t1; r.tap[2] = t2;
+                r.bias = (nb == 0 && first_of_block) ? 1 : 0;
+                first_of_block = false;
             };
             if (geom == 0) {
                 for (int ky = 0; ky < 3; ++ky) push(ky - 1, -1, ky * 3, ky * 3 + 1, ky * 3 + 2);
@@ -290,11 +294,12 @@ static void wgrad_roles(WgParams& p, int geom, int m_ch, int n_ch, int NA, int N
 // dW += wgrad. A: [B,H,W,a_C] (tile operand, m_ch channels used from channel 0), Bt: operand with the taps
 // ([B,H*scale,W*scale,b_C], n_ch channels used from channel 0).
 static int wgrad(cid_train* t, int geom, const void* A, int a_C, int m_ch, const void* Bt, int b_C, int n_ch, int B, int H,
-                 int W, float* out, cudaStream_t st) {
+                 int W, float* out, cudaStream_t st, float* bias_out = nullptr) {
     WgParams p;
     memset(&p, 0, sizeof(p));
     p.B = B; p.H = H; p.W = W;
     p.out = out;
+    p.bias_out = bias_out;
     const int NA = m_ch >= 128 ? 2 : 1, NB = n_ch >= 128 ? 2 : 1;
     wgrad_roles(p, geom, m_ch, n_ch, NA, NB);
     const CUtensorMap* tmA = tmap(t, A, B, H, W, a_C, 16, 8, 0);
@@ -313,8 +318,16 @@ static int wgrad(cid_train* t, int geom, const void* A, int a_C, int m_ch, const
     return 1;
 }
 
+// pixels per block of the column reductions: ~8 blocks per SM (small tensors were latency-bound with few blocks)
+static int reduce_ppb(const cid_train* t, size_t P) {
+    const size_t target = static_cast<size_t>(t->num_sms) * 8;
+    size_t ppb = (P + target - 1) / target;
+    ppb = (ppb + 31) / 32 * 32;
+    return static_cast<int>(std::min<size_t>(std::max<size_t>(ppb, 64), 4096));
+}
+
 static int colsum(cid_train* t, const void* v, size_t P, int cs, int c0, int C, float* out, cudaStream_t st) {
-    const int ppb = 1024;
+    const int ppb = reduce_ppb(t, P);
     colsum_kernel<false, __nv_bfloat16><<<static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, st>>>(
         static_cast<const __nv_bfloat16*>(v), P, cs, c0, C, out, nullptr, nullptr, ppb);
     CID_CHECK_CUDA(cudaGetLastError());
@@ -324,13 +337,13 @@ static int colsum(cid_train* t, const void* v, size_t P, int cs, int c0, int C, 
 
 // weight gradient of a 3-channel layer: R[c64][ci*9+tap] = sum_p v64[p][c64] * v3[p + sign*(tap - centre)][ci]
 static int wgrad_edge(cid_train* t, const void* v64, const float* v3, int v3_nchw, int sign, float* out, int out_mode,
-                      void* ubuf, int B, int H, int W, cudaStream_t st) {
+                      void* ubuf, int B, int H, int W, cudaStream_t st, float* bias_out = nullptr) {
     const size_t P = static_cast<size_t>(B) * H * W;
     im2col3_kernel<<<static_cast<unsigned>((P + 127) / 128), 128, 0, st>>>(v3, v3_nchw, sign, static_cast<__nv_bfloat16*>(ubuf), B, H, W);
     CID_CHECK_CUDA(cudaGetLastError());
     float* scratch = t->fsc + FS_WG27;
     CID_CHECK_CUDA(cudaMemsetAsync(scratch, 0, 4096 * 4, st));
-    if (wgrad(t, 3, v64, 64, 64, ubuf, 64, 64, B, H, W, scratch, st)) return 1;
+    if (wgrad(t, 3, v64, 64, 64, ubuf, 64, 64, B, H, W, scratch, st, bias_out)) return 1;
     wg27_scatter_kernel<<<(64 * 27 + 255) / 256, 256, 0, st>>>(scratch, out, out_mode);
     CID_CHECK_CUDA(cudaGetLastError());
     t->launches += 2;
@@ -357,6 +370,7 @@ static int train_alloc_packs(cid_train* t) {
         // data-gradient operand: rows = taps * Cin (the gradient's output channels), row length Cout
         t->gd_n[l] = std::min(L.cin, 256);
         if (make_weight_map(&t->gd_tm[l], t->gd_w[l], static_cast<int>(taps) * L.cin, L.cout, t->gd_n[l])) return 1;
+        if (make_weight_map(&t->gd_tmh[l], t->gd_w[l], static_cast<int>(taps) * L.cin, L.cout, t->gd_n[l] / 2)) return 1;
     }
     for (int l = 1; l < 4; ++l) {
         const int cin = kDCin[l], cout = kDCout[l];
@@ -366,6 +380,7 @@ static int train_alloc_packs(cid_train* t) {
         CID_CHECK_CUDA(cudaMalloc(&t->dd_w[l], n * 2));
         if (make_weight_map(&t->df_tm[l], t->df_w[l], (s2 ? 16 : 9) * cout, cin, cout)) return 1;
         if (make_weight_map(&t->dd_tm[l], t->dd_w[l], (s2 ? 16 : 9) * cin, cout, cin)) return 1;
+        if (make_weight_map(&t->dd_tmh[l], t->dd_w[l], (s2 ? 16 : 9) * cin, cout, cin / 2)) return 1;
     }
     CID_CHECK_CUDA(cudaMalloc(&t->df_w[0], kFirstWBytes));      // first_conv_umma operand of model.0
     CID_CHECK_CUDA(cudaMalloc(&t->dd_w[0], 128 * 64 * 2));      // last_conv_umma operand of model.0's data gradient
@@ -488,7 +503,7 @@ static ConvParams conv_base(const TrainRun& r, int lv, int k_ch, int n_ch) {
 
 // data gradient of a 3x3 stride-1 conv: dX[B,h,w,n_ch] = conv(dZ[B,h,w,k_ch], flipped W^T), optionally ReLU-masked
 static int dgrad3x3(const TrainRun& r, int lv, const void* dz, int k_ch, const CUtensorMap& tmW, void* dx, int n_ch,
-                    const void* mask, int mask_cs) {
+                    const void* mask, int mask_cs, const CUtensorMap* tmWh = nullptr) {
     cid_train* t = r.t;
     const int h = r.H >> lv, w = r.W >> lv;
     const CUtensorMap* tmA = tmap(t, dz, r.B, h, w, k_ch, 18, 10, 0);
@@ -497,8 +512,17 @@ static int dgrad3x3(const TrainRun& r, int lv, const void* dz, int k_ch, const C
     ConvParams p = conv_base(r, lv, k_ch, n_ch);
     p.out = dx; p.out_cs = n_ch; p.out_c0 = 0;
     p.res2 = mask; p.res2_cs = mask_cs;
-    if (n_ch == 64) return launch_conv_t<64, 9, 2, false, EPI_DGRAD, 10, 1>(t, *tmA, tmW, *tmO, p, r.st);
-    if (n_ch == 128) return launch_conv_t<128, 9, 2, false, EPI_DGRAD, 10, 1>(t, *tmA, tmW, *tmO, p, r.st);
+    const int pair = t->g->variant;  // bit 64: N = 64 layers with resident weights (pairs for K = 128), bit 128: N = 128 as pairs
+    if (n_ch == 64) {
+        // resident weights as the forward's N = 64 layers: 74 KB for K = 64; K = 128 only fits halved, as a CTA pair
+        if ((pair & 64) && k_ch == 64) return launch_conv_t<64, 9, 2, true, EPI_DGRAD, 10, 1>(t, *tmA, tmW, *tmO, p, r.st);
+        if ((pair & 64) && k_ch == 128 && tmWh) return launch_conv_t<64, 9, 2, true, EPI_DGRAD, 10, 1, 2>(t, *tmA, *tmWh, *tmO, p, r.st);
+        return launch_conv_t<64, 9, 2, false, EPI_DGRAD, 10, 1>(t, *tmA, tmW, *tmO, p, r.st);
+    }
+    if (n_ch == 128) {
+        if ((pair & 128) && tmWh) return launch_conv_t<128, 9, 2, false, EPI_DGRAD, 10, 1, 2>(t, *tmA, *tmWh, *tmO, p, r.st);
+        return launch_conv_t<128, 9, 2, false, EPI_DGRAD, 10, 1>(t, *tmA, tmW, *tmO, p, r.st);
+    }
     if (n_ch == 256) return launch_conv_t<256, 9, 1, false, EPI_DGRAD, 10, 1>(t, *tmA, tmW, *tmO, p, r.st);
     set_error("dgrad3x3: unsupported width %d", n_ch);
     return 1;
@@ -532,7 +556,7 @@ static int bn_forward(const TrainRun& r, int l, const void* z, void* a, int lv) 
     float* stats = t->fsc + FS_STATS + (l - 1) * 256;
     const std::string bn = "discriminator.model." + std::to_string(kDBnIdx[l]);
     CID_CHECK_CUDA(cudaMemsetAsync(sums, 0, 256 * 8, r.st));
-    const int ppb = 1024;
+    const int ppb = reduce_ppb(t, P);
     colsum_kernel<true, float><<<static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, r.st>>>(
         static_cast<const float*>(z), P, C, 0, C, nullptr, sums, sums + 128, ppb);
     float* tab = t->fsc + FS_TAB + (l - 1) * 256;
@@ -624,7 +648,7 @@ static int bn_backward(const TrainRun& r, int l, const void* z, const void* da, 
     const float* gamma = train_ptr(t, bn + ".weight", 0);
     const float* beta = train_ptr(t, bn + ".bias", 0);
     CID_CHECK_CUDA(cudaMemsetAsync(sums, 0, 256 * 8, r.st));
-    const int ppb = 1024;
+    const int ppb = reduce_ppb(t, P);
     bn_bwd_reduce_kernel<float><<<static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, r.st>>>(
         static_cast<const float*>(z), static_cast<const __nv_bfloat16*>(da), t->fsc + FS_DPOOL, P, hw, C, stats, gamma,
         beta, 0.2f, sums, ppb);
@@ -660,8 +684,7 @@ static int d_backward(const TrainRun& r, const float* img, float target, float s
     // layer 3 (model.8 / model.9)
     if (bn_backward(r, 3, r.tbuf(TB_DZ3D), nullptr, r.tbuf(TB_DG3), 2, param_grads)) return 1;
     if (param_grads) {
-        if (colsum(t, r.tbuf(TB_DG3), r.pixels(2), 128, 0, 128, gradp(3, ".bias"), r.st)) return 1;
-        if (wgrad(t, 1, r.tbuf(TB_DG3), 128, 128, r.tbuf(TB_DA2), 128, 128, B, H >> 2, W >> 2, gradp(3, ".weight"), r.st)) return 1;
+            if (wgrad(t, 1, r.tbuf(TB_DG3), 128, 128, r.tbuf(TB_DA2), 128, 128, B, H >> 2, W >> 2, gradp(3, ".weight"), r.st, gradp(3, ".bias"))) return 1;
     }
     {  // data gradient: transposed 4x4 stride 2 (zero-padded taps) -> dA2
         const CUtensorMap* tmA = tmap(t, r.tbuf(TB_DG3), B, H >> 2, W >> 2, 128, 18, 10, 0);
@@ -675,15 +698,13 @@ static int d_backward(const TrainRun& r, const float* img, float target, float s
     // layer 2 (model.5 / model.6)
     if (bn_backward(r, 2, r.tbuf(TB_DZ2D), r.tbuf(TB_DG2), r.tbuf(TB_DG2), 1, param_grads)) return 1;
     if (param_grads) {
-        if (colsum(t, r.tbuf(TB_DG2), r.pixels(1), 128, 0, 128, gradp(2, ".bias"), r.st)) return 1;
-        if (wgrad(t, 0, r.tbuf(TB_DG2), 128, 128, r.tbuf(TB_DA1), 64, 64, B, H >> 1, W >> 1, gradp(2, ".weight"), r.st)) return 1;
+            if (wgrad(t, 0, r.tbuf(TB_DG2), 128, 128, r.tbuf(TB_DA1), 64, 64, B, H >> 1, W >> 1, gradp(2, ".weight"), r.st, gradp(2, ".bias"))) return 1;
     }
-    if (dgrad3x3(r, 1, r.tbuf(TB_DG2), 128, t->dd_tm[2], r.tbuf(TB_DG1), 64, nullptr, 0)) return 1;
+    if (dgrad3x3(r, 1, r.tbuf(TB_DG2), 128, t->dd_tm[2], r.tbuf(TB_DG1), 64, nullptr, 0, &t->dd_tmh[2])) return 1;
     // layer 1 (model.2 / model.3)
     if (bn_backward(r, 1, r.tbuf(TB_DZ1D), r.tbuf(TB_DG1), r.tbuf(TB_DG1), 1, param_grads)) return 1;
     if (param_grads) {
-        if (colsum(t, r.tbuf(TB_DG1), r.pixels(1), 64, 0, 64, gradp(1, ".bias"), r.st)) return 1;
-        if (wgrad(t, 1, r.tbuf(TB_DG1), 64, 64, r.tbuf(TB_DA0), 64, 64, B, H >> 1, W >> 1, gradp(1, ".weight"), r.st)) return 1;
+            if (wgrad(t, 1, r.tbuf(TB_DG1), 64, 64, r.tbuf(TB_DA0), 64, 64, B, H >> 1, W >> 1, gradp(1, ".weight"), r.st, gradp(1, ".bias"))) return 1;
     }
     {  // data gradient -> dA0
         const CUtensorMap* tmA = tmap(t, r.tbuf(TB_DG1), B, H >> 1, W >> 1, 64, 18, 10, 0);
@@ -703,8 +724,7 @@ static int d_backward(const TrainRun& r, const float* img, float target, float s
         t->launches++;
     }
     if (param_grads) {
-        if (colsum(t, r.tbuf(TB_DG0), r.pixels(0), 64, 0, 64, gradp(0, ".bias"), r.st)) return 1;
-        if (wgrad_edge(t, r.tbuf(TB_DG0), img, 1, 1, gradp(0, ".weight"), 0, r.tbuf(TB_U), B, H, W, r.st)) return 1;
+                if (wgrad_edge(t, r.tbuf(TB_DG0), img, 1, 1, gradp(0, ".weight"), 0, r.tbuf(TB_U), B, H, W, r.st, gradp(0, ".bias"))) return 1;
     }
     if (want_gx) {
         // 64 -> 3 data gradient on the last-conv kernel (transposed GEMM) with a linear fp32 NHWC epilogue
@@ -762,53 +782,44 @@ static int g_backward_layers(const TrainRun& r, const float* noisy) {
         t->launches++;
     }
     // L10 upconv1.0 (cat1 128 -> 64)
-    if (colsum(t, r.tbuf(TB_DZ10), r.pixels(0), 64, 0, 64, gb(10), r.st)) return 1;
-    if (wgrad(t, 0, r.tbuf(TB_DZ10), 64, 64, r.gbuf(B_CAT1), 128, 128, B, H, W, gw(10), r.st)) return 1;
-    if (dgrad3x3(r, 0, r.tbuf(TB_DZ10), 64, t->gd_tm[10], r.tbuf(TB_GCAT1), 128, nullptr, 0)) return 1;
+    if (wgrad(t, 0, r.tbuf(TB_DZ10), 64, 64, r.gbuf(B_CAT1), 128, 128, B, H, W, gw(10), r.st, gb(10))) return 1;
+    if (dgrad3x3(r, 0, r.tbuf(TB_DZ10), 64, t->gd_tm[10], r.tbuf(TB_GCAT1), 128, nullptr, 0, &t->gd_tmh[10])) return 1;
     // L9 up1 (ConvT 128 -> 64, u2b -> cat1[:, 0:64])
     if (colsum(t, r.tbuf(TB_GCAT1), r.pixels(0), 128, 0, 64, gb(9), r.st)) return 1;
     if (wgrad(t, 2, r.gbuf(B_U2B), 128, 128, r.tbuf(TB_GCAT1), 128, 64, B, H >> 1, W >> 1, gw(9), r.st)) return 1;
     if (dgrad_convt(r, 1, r.tbuf(TB_GCAT1), 128, 64, t->gd_tm[9], r.tbuf(TB_DZ8), 128, r.gbuf(B_U2B))) return 1;
     // L8 upconv2.2 (u2a 128 -> 128)
-    if (colsum(t, r.tbuf(TB_DZ8), r.pixels(1), 128, 0, 128, gb(8), r.st)) return 1;
-    if (wgrad(t, 0, r.tbuf(TB_DZ8), 128, 128, r.gbuf(B_U2A), 128, 128, B, H >> 1, W >> 1, gw(8), r.st)) return 1;
-    if (dgrad3x3(r, 1, r.tbuf(TB_DZ8), 128, t->gd_tm[8], r.tbuf(TB_DZ7), 128, r.gbuf(B_U2A), 128)) return 1;
+    if (wgrad(t, 0, r.tbuf(TB_DZ8), 128, 128, r.gbuf(B_U2A), 128, 128, B, H >> 1, W >> 1, gw(8), r.st, gb(8))) return 1;
+    if (dgrad3x3(r, 1, r.tbuf(TB_DZ8), 128, t->gd_tm[8], r.tbuf(TB_DZ7), 128, r.gbuf(B_U2A), 128, &t->gd_tmh[8])) return 1;
     // L7 upconv2.0 (cat2 256 -> 128)
-    if (colsum(t, r.tbuf(TB_DZ7), r.pixels(1), 128, 0, 128, gb(7), r.st)) return 1;
-    if (wgrad(t, 0, r.tbuf(TB_DZ7), 128, 128, r.gbuf(B_CAT2), 256, 256, B, H >> 1, W >> 1, gw(7), r.st)) return 1;
-    if (dgrad3x3(r, 1, r.tbuf(TB_DZ7), 128, t->gd_tm[7], r.tbuf(TB_GCAT2), 256, nullptr, 0)) return 1;
+    if (wgrad(t, 0, r.tbuf(TB_DZ7), 128, 128, r.gbuf(B_CAT2), 256, 256, B, H >> 1, W >> 1, gw(7), r.st, gb(7))) return 1;
+    if (dgrad3x3(r, 1, r.tbuf(TB_DZ7), 128, t->gd_tm[7], r.tbuf(TB_GCAT2), 256, nullptr, 0, &t->gd_tmh[7])) return 1;
     // L6 up2 (ConvT 256 -> 128, b1 -> cat2[:, 0:128])
     if (colsum(t, r.tbuf(TB_GCAT2), r.pixels(1), 256, 0, 128, gb(6), r.st)) return 1;
     if (wgrad(t, 2, r.gbuf(B_B1), 256, 256, r.tbuf(TB_GCAT2), 256, 128, B, H >> 2, W >> 2, gw(6), r.st)) return 1;
     if (dgrad_convt(r, 2, r.tbuf(TB_GCAT2), 256, 128, t->gd_tm[6], r.tbuf(TB_DZ5), 256, r.gbuf(B_B1))) return 1;
     // L5 bottleneck.2 (b0 256 -> 256)
-    if (colsum(t, r.tbuf(TB_DZ5), r.pixels(2), 256, 0, 256, gb(5), r.st)) return 1;
-    if (wgrad(t, 0, r.tbuf(TB_DZ5), 256, 256, r.gbuf(B_B0), 256, 256, B, H >> 2, W >> 2, gw(5), r.st)) return 1;
-    if (dgrad3x3(r, 2, r.tbuf(TB_DZ5), 256, t->gd_tm[5], r.tbuf(TB_DZ4), 256, r.gbuf(B_B0), 256)) return 1;
+    if (wgrad(t, 0, r.tbuf(TB_DZ5), 256, 256, r.gbuf(B_B0), 256, 256, B, H >> 2, W >> 2, gw(5), r.st, gb(5))) return 1;
+    if (dgrad3x3(r, 2, r.tbuf(TB_DZ5), 256, t->gd_tm[5], r.tbuf(TB_DZ4), 256, r.gbuf(B_B0), 256, &t->gd_tmh[5])) return 1;
     // L4 bottleneck.0 (p2 128 -> 256)
-    if (colsum(t, r.tbuf(TB_DZ4), r.pixels(2), 256, 0, 256, gb(4), r.st)) return 1;
-    if (wgrad(t, 0, r.tbuf(TB_DZ4), 256, 256, r.gbuf(B_P2), 128, 128, B, H >> 2, W >> 2, gw(4), r.st)) return 1;
-    if (dgrad3x3(r, 2, r.tbuf(TB_DZ4), 256, t->gd_tm[4], r.tbuf(TB_GP2), 128, nullptr, 0)) return 1;
+    if (wgrad(t, 0, r.tbuf(TB_DZ4), 256, 256, r.gbuf(B_P2), 128, 128, B, H >> 2, W >> 2, gw(4), r.st, gb(4))) return 1;
+    if (dgrad3x3(r, 2, r.tbuf(TB_DZ4), 256, t->gd_tm[4], r.tbuf(TB_GP2), 128, nullptr, 0, &t->gd_tmh[4])) return 1;
     // pool2 + skip: e2 = cat2[:, 128:256]
     pool_bwd(B_CAT2, 128, 1, TB_GCAT2, TB_GP2, TB_DZ3);
     // L3 down2.2 (a2 128 -> 128)
-    if (colsum(t, r.tbuf(TB_DZ3), r.pixels(1), 128, 0, 128, gb(3), r.st)) return 1;
-    if (wgrad(t, 0, r.tbuf(TB_DZ3), 128, 128, r.gbuf(B_A2), 128, 128, B, H >> 1, W >> 1, gw(3), r.st)) return 1;
-    if (dgrad3x3(r, 1, r.tbuf(TB_DZ3), 128, t->gd_tm[3], r.tbuf(TB_DZ2), 128, r.gbuf(B_A2), 128)) return 1;
+    if (wgrad(t, 0, r.tbuf(TB_DZ3), 128, 128, r.gbuf(B_A2), 128, 128, B, H >> 1, W >> 1, gw(3), r.st, gb(3))) return 1;
+    if (dgrad3x3(r, 1, r.tbuf(TB_DZ3), 128, t->gd_tm[3], r.tbuf(TB_DZ2), 128, r.gbuf(B_A2), 128, &t->gd_tmh[3])) return 1;
     // L2 down2.0 (p1 64 -> 128)
-    if (colsum(t, r.tbuf(TB_DZ2), r.pixels(1), 128, 0, 128, gb(2), r.st)) return 1;
-    if (wgrad(t, 0, r.tbuf(TB_DZ2), 128, 128, r.gbuf(B_P1), 64, 64, B, H >> 1, W >> 1, gw(2), r.st)) return 1;
-    if (dgrad3x3(r, 1, r.tbuf(TB_DZ2), 128, t->gd_tm[2], r.tbuf(TB_GP1), 64, nullptr, 0)) return 1;
+    if (wgrad(t, 0, r.tbuf(TB_DZ2), 128, 128, r.gbuf(B_P1), 64, 64, B, H >> 1, W >> 1, gw(2), r.st, gb(2))) return 1;
+    if (dgrad3x3(r, 1, r.tbuf(TB_DZ2), 128, t->gd_tm[2], r.tbuf(TB_GP1), 64, nullptr, 0, &t->gd_tmh[2])) return 1;
     // pool1 + skip: e1 = cat1[:, 64:128]
     pool_bwd(B_CAT1, 64, 0, TB_GCAT1, TB_GP1, TB_DZ1);
     // L1 down1.2 (a0 64 -> 64)
-    if (colsum(t, r.tbuf(TB_DZ1), r.pixels(0), 64, 0, 64, gb(1), r.st)) return 1;
-    if (wgrad(t, 0, r.tbuf(TB_DZ1), 64, 64, r.gbuf(B_A0), 64, 64, B, H, W, gw(1), r.st)) return 1;
-    if (dgrad3x3(r, 0, r.tbuf(TB_DZ1), 64, t->gd_tm[1], r.tbuf(TB_DZ0), 64, r.gbuf(B_A0), 64)) return 1;
+    if (wgrad(t, 0, r.tbuf(TB_DZ1), 64, 64, r.gbuf(B_A0), 64, 64, B, H, W, gw(1), r.st, gb(1))) return 1;
+    if (dgrad3x3(r, 0, r.tbuf(TB_DZ1), 64, t->gd_tm[1], r.tbuf(TB_DZ0), 64, r.gbuf(B_A0), 64, &t->gd_tmh[1])) return 1;
     // L0 down1.0 (3 -> 64)
-    if (colsum(t, r.tbuf(TB_DZ0), r.pixels(0), 64, 0, 64, gb(0), r.st)) return 1;
-    {
-        if (wgrad_edge(t, r.tbuf(TB_DZ0), noisy, 1, 1, gw(0), 0, r.tbuf(TB_U), B, H, W, r.st)) return 1;
+        {
+        if (wgrad_edge(t, r.tbuf(TB_DZ0), noisy, 1, 1, gw(0), 0, r.tbuf(TB_U), B, H, W, r.st, gb(0))) return 1;
     }
     return 0;
 }

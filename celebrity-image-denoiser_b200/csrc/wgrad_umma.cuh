@@ -20,7 +20,8 @@
 // Work split. A ROLE fixes (M channel block, N channel block, tap row): its T accumulators [128 x N] stay in TMEM for
 // the CTA's whole life (split-K over pixel tiles: CTA (role, slice) walks its contiguous share of the tiles), and the
 // epilogue adds them into the fp32 gradient tensor (reference layout) with red.global.add.f32.
-// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer, warps 2..5 = epilogue.
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer, warps 2..5 = epilogue; while the
+// main loop runs they also sum the dZ tiles over the pixels (the layer's bias gradient) straight from shared memory.
 #pragma once
 #include "ptx.cuh"
 
@@ -35,6 +36,7 @@ struct WgRole {
     int m0, n0;      // the same blocks as indices of the gradient tensor
     int oy, ox;      // patch origin = scale * (tile y0, x0) + (oy, ox)
     int tap[3];      // gradient tap index of MMA tap t (patch pixel offset t); -1 = computed but dropped
+    int bias;        // this role also reduces its A tiles over the pixels: bias_out[m0 + c] += sum_p A[p][c]
 };
 
 struct WgParams {
@@ -47,6 +49,8 @@ struct WgParams {
     float* out;   // out[((m0 + row) * s_m + n0 + col) * kk + tap]
     int s_m, kk;
     int m_valid;  // rows of the 128-row accumulator that are real channels (64 or 128)
+    float* bias_out;  // bias gradient (column sums of operand A = dZ), reduced by the otherwise idle epilogue warps of
+                      // the roles flagged WgRole::bias while the MMAs run; may be null
     WgRole roles[kWgMaxRoles];
 };
 
@@ -104,13 +108,14 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const int t_begin = slice * per;
     const int t_end = min(p.m_tiles, t_begin + per);
     const bool has_work = t_begin < t_end;
+    const bool do_bias = role.bias != 0 && p.bias_out != nullptr;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
         for (int i = 0; i < kWgMaxStages; ++i) {
             mbar_init(&full[i], 1);
-            mbar_init(&empty[i], 1);
+            mbar_init(&empty[i], do_bias ? 5 : 1);  // MMA commit (+ one arrival per bias-reducing warp)
         }
         mbar_init(acc_full, 1);
         fence_mbar_init();
@@ -185,6 +190,49 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         // epilogue: TMEM lane quarter = warp & 3; lane = accumulator row = M channel
         const int q = warp & 3;
         const int row = q * 32 + lane;
+        if (do_bias) {
+            // column sums of the A tiles: thread = (16-byte channel chunk j, pixel-row group rg of 16)
+            const int et = (warp - 2) * 32 + lane;
+            const int j = et & 7, rg = et >> 3;
+            float acc[NA][8];
+#pragma unroll
+            for (int a = 0; a < NA; ++a)
+#pragma unroll
+                for (int e = 0; e < 8; ++e) acc[a][e] = 0.f;
+            uint32_t stage = 0, phase = 0;
+            for (int mt = t_begin; mt < t_end; ++mt) {
+                mbar_wait(&full[stage], phase);
+                const uint8_t* sa = smem + stage * stage_bytes;
+#pragma unroll
+                for (int a = 0; a < NA; ++a)
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int r = rg + 16 * i;
+                        const uint4 v = ld_shared_v4(sa + a * A_ATOM + r * 128 + ((j ^ (r & 7)) << 4));
+                        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            acc[a][2 * e] += __uint_as_float(w[e] << 16);
+                            acc[a][2 * e + 1] += __uint_as_float(w[e] & 0xffff0000u);
+                        }
+                    }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&empty[stage]);
+                if (++stage == static_cast<uint32_t>(p.stages)) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+#pragma unroll
+            for (int a = 0; a < NA; ++a)
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    float v = acc[a][e];
+                    v += __shfl_xor_sync(0xffffffffu, v, 8);
+                    v += __shfl_xor_sync(0xffffffffu, v, 16);
+                    if (lane < 8) red_add_f32(p.bias_out + role.m0 + a * 64 + j * 8 + e, v);
+                }
+        }
         mbar_wait(acc_full, 0);
         tc_fence_after();
         if (q * 32 < p.m_valid) {  // warp-uniform: quarters that hold duplicate rows do nothing

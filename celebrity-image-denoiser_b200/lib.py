@@ -49,6 +49,7 @@ _SIGNATURES = {
     # training step
     "cid_train_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
     "cid_train_destroy": (C.c_int, [C.c_void_p]),
+    "cid_train_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64]),
     "cid_train_state_floats": (C.c_int, [C.c_void_p, C.POINTER(C.c_size_t)]),
     "cid_train_bind_state": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "cid_train_tensor": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),

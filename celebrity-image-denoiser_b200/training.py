@@ -106,6 +106,9 @@ class DenoiseGANTrainStep:
         except Exception:
             pass
 
+    def set_option(self, name: str, value: int) -> None:
+        _lib.check(self.lib.cid_train_set_option(self.handle, name.encode(), int(value)), "cid_train_set_option")
+
     def view(self, key: str, section: int = 0) -> torch.Tensor:
         """Flat view of one named tensor inside the state buffer (section 0 params, 1 grads, 2 exp_avg, 3 exp_avg_sq)."""
         off, n = C.c_size_t(), C.c_size_t()

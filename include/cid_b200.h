@@ -196,6 +196,9 @@ typedef struct cid_train* cid_train_handle;
 
 int cid_train_create(int device, cid_train_handle* out);
 int cid_train_destroy(cid_train_handle t);
+/* Options of the underlying generator context (cid_set_option); "variant" bits 64 / 128 select the resident-weight /
+ * CTA-pair forms of the N = 64 / N = 128 data-gradient kernels. */
+int cid_train_set_option(cid_train_handle t, const char* name, int64_t value);
 int cid_train_state_floats(cid_train_handle t, size_t* n);
 int cid_train_bind_state(cid_train_handle t, float* state_dev, size_t n);
 /* section: 0 parameters, 1 gradients, 2 Adam exp_avg, 3 Adam exp_avg_sq. Offsets are in floats from state_dev. */
