@@ -329,6 +329,27 @@ __device__ __forceinline__ void umma_commit_cg2(uint64_t* bar) {
 }
 
 // ----------------------------------------------------------------------------------------------
+// clusters of single-CTA MMAs (wgrad_umma.cuh): one TMA load delivered to the same shared-memory offset (and
+// signalled on the mbarrier at the same offset) of every CTA in `mask`; one commit arriving on the same barrier of
+// every CTA in `mask`.
+// ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ void tma_load_4d_mc(void* smem, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2,
+                                               int c3, uint16_t mask, uint64_t hint) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster.L2::cache_hint"
+        " [%0], [%1, {%3, %4, %5, %6}], [%2], %7, %8;" ::"r"(smem_u32(smem)),
+        "l"(m), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "h"(mask), "l"(hint)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_mc(uint64_t* bar, uint16_t mask) {
+    asm volatile(
+        "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+            smem_u32(bar)),
+        "h"(mask)
+        : "memory");
+}
+
+// ----------------------------------------------------------------------------------------------
 // programmatic dependent launch: a kernel launched with the programmatic-stream-serialization attribute may
 // start while its predecessor in the stream is still running; everything that reads or writes memory the
 // predecessor touches must come after pdl_wait() (= predecessor complete, its writes visible).

@@ -229,27 +229,62 @@ static int launch_conv_t(cid_train* t, const CUtensorMap& tmA, const CUtensorMap
     return 0;
 }
 
-template <int NA, int NB, int T>
+template <int NA, int NB, int T, int CL = 1>
 static int launch_wgrad(cid_train* t, const CUtensorMap& tmA, const CUtensorMap& tmB, WgParams p, cudaStream_t st) {
     p.tiles_x = (p.W + 7) / 8;
     p.tiles_y = (p.H + 15) / 16;
     p.m_tiles = p.B * p.tiles_x * p.tiles_y;
-    CID_REQUIRE(p.n_roles >= 1 && p.n_roles <= kWgMaxRoles, "wgrad: %d roles", p.n_roles);
-    p.slices = std::max(1, std::min(t->num_sms / p.n_roles, p.m_tiles));
+    CID_REQUIRE(p.n_roles >= 1 && p.n_roles <= kWgMaxRoles && p.n_roles % CL == 0, "wgrad: %d roles", p.n_roles);
     p.m_valid = 64 * NA;
-    const int pb = (p.pw * 16 * 128 + 1023) & ~1023;
+    const int pb = (p.pw * (CL == 3 ? 18 : 16) * 128 + 1023) & ~1023;
     const int stage_bytes = NA * 16384 + NB * pb;
     p.stages = std::min(kWgMaxStages, (t->max_smem - 2048) / stage_bytes);
     CID_REQUIRE(p.stages >= 2, "wgrad: shared memory too small");
     // > half of the SM's shared memory: one CTA per SM (each CTA allocates up to all 512 TMEM columns)
     const int smem = std::max(p.stages * stage_bytes + 1024 + 256, 120 * 1024);
-    auto kern = wgrad_umma_kernel<NA, NB, T>;
+    auto kern = wgrad_umma_kernel<NA, NB, T, CL>;
     static bool attr_set = false;
+    static int max_units = 0;  // co-resident CTAs (CL = 1) or clusters (CL = 3)
     if (!attr_set) {
         CID_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, t->max_smem));
+        max_units = t->num_sms;
+        if (CL > 1) {
+            cudaLaunchConfig_t cfg;
+            memset(&cfg, 0, sizeof(cfg));
+            cfg.gridDim = dim3(t->num_sms / CL * CL);
+            cfg.blockDim = dim3(kWgThreads);
+            cfg.dynamicSmemBytes = t->max_smem;
+            cudaLaunchAttribute at;
+            at.id = cudaLaunchAttributeClusterDimension;
+            at.val.clusterDim.x = CL; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
+            cfg.attrs = &at;
+            cfg.numAttrs = 1;
+            int n = 0;
+            CID_CHECK_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
+            CID_REQUIRE(n >= 1, "wgrad: no cluster of %d CTAs fits", CL);
+            max_units = n;
+        }
         attr_set = true;
     }
-    kern<<<p.n_roles * p.slices, kWgThreads, smem, st>>>(tmA, tmB, p);
+    const int n_units = p.n_roles / CL;
+    p.slices = std::max(1, std::min(max_units / n_units, p.m_tiles));
+    const int grid = n_units * p.slices * CL;
+    if (CL > 1) {
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3(grid);
+        cfg.blockDim = dim3(kWgThreads);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = st;
+        cudaLaunchAttribute at;
+        at.id = cudaLaunchAttributeClusterDimension;
+        at.val.clusterDim.x = CL; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
+        cfg.attrs = &at;
+        cfg.numAttrs = 1;
+        CID_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, p));
+    } else {
+        kern<<<grid, kWgThreads, smem, st>>>(tmA, tmB, p);
+    }
     CID_CHECK_CUDA(cudaGetLastError());
     t->launches++;
     return 0;
@@ -300,14 +335,22 @@ static int wgrad(cid_train* t, int geom, const void* A, int a_C, int m_ch, const
     p.B = B; p.H = H; p.W = W;
     p.out = out;
     p.bias_out = bias_out;
-    const int NA = m_ch >= 128 ? 2 : 1, NB = n_ch >= 128 ? 2 : 1;
+    // "variant" bit 256: 3x3 stride-1 layers as clusters of 3 CTAs with TMA multicast; bit 512: ... with N = 64 per CTA
+    const bool cl3 = geom == 0 && (t->g->variant & 256);
+    const int NA = m_ch >= 128 ? 2 : 1, NB = (n_ch >= 128 && !(cl3 && (t->g->variant & 512))) ? 2 : 1;
     wgrad_roles(p, geom, m_ch, n_ch, NA, NB);
     const CUtensorMap* tmA = tmap(t, A, B, H, W, a_C, 16, 8, 0);
-    const CUtensorMap* tmB = geom == 0   ? tmap(t, Bt, B, H, W, b_C, 16, 10, 0)
+    const CUtensorMap* tmB = geom == 0   ? tmap(t, Bt, B, H, W, b_C, cl3 ? 18 : 16, 10, 0)
                              : geom == 3 ? tmap(t, Bt, B, H, W, b_C, 16, 8, 0)
                                          : tmap(t, Bt, B, 2 * H, 2 * W, b_C, 16, p.pw, 1);
     if (!tmA || !tmB) return 1;
     const int T = geom == 0 ? 3 : geom == 1 ? 2 : 1;
+    if (cl3) {
+#define CID_WG3(na, nb) \
+    if (NA == na && NB == nb) return launch_wgrad<na, nb, 3, 3>(t, *tmA, *tmB, p, st);
+        CID_WG3(1, 1) CID_WG3(1, 2) CID_WG3(2, 1) CID_WG3(2, 2)
+#undef CID_WG3
+    }
 #define CID_WG(na, nb, tt) \
     if (NA == na && NB == nb && T == tt) return launch_wgrad<na, nb, tt>(t, *tmA, *tmB, p, st);
     CID_WG(1, 1, 3) CID_WG(1, 2, 3) CID_WG(2, 1, 3) CID_WG(2, 2, 3)

@@ -78,7 +78,12 @@ __device__ __forceinline__ void red_add_f32(float* p, float v) {
 
 // NA: 64-channel atoms of operand A that are real (1: rows 64..127 duplicate rows 0..63), NB: atoms of operand B
 // (N = 64 * NB), T: taps per role (accumulators).
-template <int NA, int NB, int T>
+// CL = 3 (3x3 stride-1 layers): the three tap-row roles of one (M block, N block) run as a CLUSTER of 3 CTAs on the same
+// pixel tiles. Every operand tile is fetched from L2 ONCE per cluster and TMA-multicast into all three CTAs (rank 0 loads
+// the A atoms, ranks 1 / 2 the B atoms: the full 18-row halo patch, of which CTA `rank` reads rows rank .. rank+15), so
+// the L2 -> SM traffic per FLOP drops 2.8x; a stage is re-filled only after all three CTAs' MMAs (and the bias-reducing
+// warps) have released it (multicast commits onto every CTA's "empty" barrier).
+template <int NA, int NB, int T, int CL = 1>
 __global__ void __launch_bounds__(kWgThreads, 1)
 wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ WgParams p) {
@@ -91,7 +96,9 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    const int pb = (p.pw * 16 * 128 + 1023) & ~1023;  // bytes of one B atom (patch), 1024-aligned pitch
+    static_assert(CL == 1 || (CL == 3 && T == 3), "cluster mode = the three tap rows of a 3x3 layer");
+    constexpr int PROWS = CL == 3 ? 18 : 16;           // patch rows per B atom
+    const int pb = (p.pw * PROWS * 128 + 1023) & ~1023;  // bytes of one B atom (patch), 1024-aligned pitch
     const int stage_bytes = NA * A_ATOM + NB * pb;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.stages * stage_bytes);
     uint64_t* full = bars;
@@ -101,28 +108,36 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int role_i = blockIdx.x % p.n_roles;
-    const int slice = blockIdx.x / p.n_roles;
+    const uint32_t rank = CL == 3 ? cluster_ctarank() : 0u;
+    const int unit = blockIdx.x / CL;                  // CTA (or cluster) index
+    const int n_units = p.n_roles / CL;                // role blocks
+    const int role_i = (unit % n_units) * CL + static_cast<int>(rank);
+    const int slice = unit / n_units;
     const WgRole& role = p.roles[role_i];
     const int per = (p.m_tiles + p.slices - 1) / p.slices;
     const int t_begin = slice * per;
     const int t_end = min(p.m_tiles, t_begin + per);
     const bool has_work = t_begin < t_end;
     const bool do_bias = role.bias != 0 && p.bias_out != nullptr;
+    // cluster mode: the bias role is rank 0; its four warps release a stage in ALL three CTAs
+    const bool blk_bias = CL == 3 ? (p.roles[(unit % n_units) * CL].bias != 0 && p.bias_out != nullptr) : do_bias;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
         for (int i = 0; i < kWgMaxStages; ++i) {
             mbar_init(&full[i], 1);
-            mbar_init(&empty[i], do_bias ? 5 : 1);  // MMA commit (+ one arrival per bias-reducing warp)
+            mbar_init(&empty[i], CL + (blk_bias ? 4 : 0));  // MMA commit(s) (+ one arrival per bias-reducing warp)
         }
         mbar_init(acc_full, 1);
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
     tc_fence_before();
-    __syncthreads();
+    if (CL == 3)
+        cluster_sync_all();  // the peers' barriers are initialised before anything arrives on them
+    else
+        __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
@@ -139,14 +154,26 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 uint8_t* sa = smem + stage * stage_bytes;
                 uint8_t* sb = sa + NA * A_ATOM;
                 mbar_wait(&empty[stage], phase ^ 1);
-                mbar_arrive_expect_tx(&full[stage], NA * A_ATOM + NB * p.pw * 16 * 128);
+                mbar_arrive_expect_tx(&full[stage], NA * A_ATOM + NB * p.pw * PROWS * 128);
+                if constexpr (CL == 3) {
+                    // each rank fetches its share once and multicasts it to the whole cluster
+                    if (rank == 0) {
 #pragma unroll
-                for (int a = 0; a < NA; ++a)
-                    tma_load_4d(sa + a * A_ATOM, &tmA, &full[stage], role.a_c0 + a * 64, x0, y0, b, kEvictNormal);
+                        for (int a = 0; a < NA; ++a)
+                            tma_load_4d_mc(sa + a * A_ATOM, &tmA, &full[stage], role.a_c0 + a * 64, x0, y0, b, 7, kEvictNormal);
+                    } else if (static_cast<int>(rank) <= NB) {
+                        const int q = static_cast<int>(rank) - 1;
+                        tma_load_4d_mc(sb + q * pb, &tmB, &full[stage], role.b_c0 + q * 64, x0 - 1, y0 - 1, b, 7, kEvictNormal);
+                    }
+                } else {
 #pragma unroll
-                for (int q = 0; q < NB; ++q)
-                    tma_load_4d(sb + q * pb, &tmB, &full[stage], role.b_c0 + q * 64, p.scale * x0 + role.ox,
-                                p.scale * y0 + role.oy, b, kEvictNormal);
+                    for (int a = 0; a < NA; ++a)
+                        tma_load_4d(sa + a * A_ATOM, &tmA, &full[stage], role.a_c0 + a * 64, x0, y0, b, kEvictNormal);
+#pragma unroll
+                    for (int q = 0; q < NB; ++q)
+                        tma_load_4d(sb + q * pb, &tmB, &full[stage], role.b_c0 + q * 64, p.scale * x0 + role.ox,
+                                    p.scale * y0 + role.oy, b, kEvictNormal);
+                }
                 if (++stage == static_cast<uint32_t>(p.stages)) {
                     stage = 0;
                     phase ^= 1;
@@ -171,11 +198,15 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
                         for (int t = 0; t < T; ++t) {
                             const uint64_t bd =
-                                umma_desc_mn_sw128(sb + (k8 * 2 * p.pw + t) * 128, static_cast<uint32_t>(pb), sbo_b);
+                                umma_desc_mn_sw128(sb + ((k8 * 2 + (CL == 3 ? static_cast<int>(rank) : 0)) * p.pw + t) * 128,
+                                                   static_cast<uint32_t>(pb), sbo_b);
                             umma_bf16_ss(tmem_base + t * N, ad, bd, idesc, (mt == t_begin && k8 == 0) ? 0u : 1u);
                         }
                     }
-                    umma_commit(&empty[stage]);
+                    if (CL == 3)
+                        umma_commit_mc(&empty[stage], 7);
+                    else
+                        umma_commit(&empty[stage]);
                 }
                 __syncwarp();
                 if (++stage == static_cast<uint32_t>(p.stages)) {
@@ -217,7 +248,14 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                         }
                     }
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&empty[stage]);
+                if (lane == 0) {
+                    if (CL == 3) {
+#pragma unroll
+                        for (uint32_t r = 0; r < 3; ++r) mbar_arrive_cluster(mapa_u32(smem_u32(&empty[stage]), r));
+                    } else {
+                        mbar_arrive(&empty[stage]);
+                    }
+                }
                 if (++stage == static_cast<uint32_t>(p.stages)) {
                     stage = 0;
                     phase ^= 1;
@@ -254,7 +292,10 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
 
     tc_fence_before();
-    __syncthreads();
+    if (CL == 3)
+        cluster_sync_all();  // no CTA leaves while a peer may still multicast into its smem or arrive on its barriers
+    else
+        __syncthreads();
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, TMEM_COLS);
