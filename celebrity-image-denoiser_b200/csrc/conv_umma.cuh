@@ -60,6 +60,8 @@ struct ConvParams {
     const void* res2;    //          (second one optional)
     int res_cs, res2_cs;
     int bias_per_column; // EPI_CONVT as pixel shuffle: bias indexed by GEMM column instead of by channel
+    float mask_slope;    // EPI_T4 with res2 set (training): the output gradient is multiplied by the LeakyReLU derivative of
+                         // the activation res2 at the OUTPUT pixel (1 where it is positive, mask_slope elsewhere)
     float* out_f32;      // EPI_LRELU only: if set, the result is written as fp32 NHWC straight from registers (no bf16
                          // staging / TMA store): the discriminator's pre-BatchNorm outputs, whose mean >> std
     int debug_flags;     // bring-up experiments only: 1 = epilogue skips global stores, 2 = skips TMEM reads too
@@ -661,6 +663,28 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             const int c = col - px * N;  // channel of v[0]
                             const float4* b4 = reinterpret_cast<const float4*>(p.bias + c);
                             uint32_t pk[16];
+                            if (p.res2 != nullptr) {
+                                // LeakyReLU backward of the layer below, fused: 32 channels of the activation at this
+                                // thread's output pixel (2y+py, 2x+px)
+                                const int oy = 2 * (tc.y0 + yl) + n_tile, ox = 2 * (tc.x0 + xl) + px;
+                                if (tc.b < p.B && oy < 2 * p.H && ox < 2 * p.W) {
+                                    const size_t pix = (static_cast<size_t>(tc.b) * (2 * p.H) + oy) * (2 * p.W) + ox;
+                                    const uint4* m4 = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.res2) +
+                                                                                      pix * p.res2_cs + c);
+#pragma unroll
+                                    for (int i = 0; i < 4; ++i) {
+                                        const uint4 m = __ldg(m4 + i);
+                                        const uint32_t w[4] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+                                        for (int e = 0; e < 4; ++e) {
+                                            const int k = (i * 4 + e) * 2;
+                                            if (!(__uint_as_float(w[e] << 16) > 0.f)) v[k] = __float_as_uint(__uint_as_float(v[k]) * p.mask_slope);
+                                            if (!(__uint_as_float(w[e] & 0xffff0000u) > 0.f))
+                                                v[k + 1] = __float_as_uint(__uint_as_float(v[k + 1]) * p.mask_slope);
+                                        }
+                                    }
+                                }
+                            }
 #pragma unroll
                             for (int jj = 0; jj < 8; ++jj) {
                                 const float4 bb = __ldg(b4 + jj);

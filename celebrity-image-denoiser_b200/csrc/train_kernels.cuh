@@ -625,16 +625,19 @@ __global__ void avgpool_kernel(const __nv_bfloat16* a, float* pooled, int hw, in
     atomicAdd(pooled + b * C + c, s / static_cast<float>(hw));
 }
 
-// One block of 128 threads (C = 128). loss_sum += BCE(sigmoid(w.pooled + b), target) (mean over B);
+// One block of 1024 threads (C = 128). loss_sum += BCE(sigmoid(w.pooled + b), target) (mean over B);
 // dlogit = scale * (p - target) / B; dpool[b][c] = dlogit[b] * w[c] / hw; with_param_grads: gw += dlogit^T pooled, gb += sum.
-__global__ void __launch_bounds__(128) dhead_kernel(const float* pooled, const float* w, const float* bias, int B, int hw,
-                                                    float target, float scale, double* loss_sum, float* dpool, float* gw,
-                                                    float* gb, float* probs, int with_param_grads) {
+__global__ void __launch_bounds__(1024) dhead_kernel(const float* pooled, const float* w, const float* bias, int B, int hw,
+                                                     float target, float scale, double* loss_sum, float* dpool, float* gw,
+                                                     float* gb, float* probs, int with_param_grads) {
     extern __shared__ float dl[];  // [B]
+    __shared__ float red[32];
+    __shared__ float gpart[8][128];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float lsum = 0.f;
-    for (int b = warp; b < B; b += 4) {
+    for (int b = warp; b < B; b += 32) {
         float s = 0.f;
+#pragma unroll
         for (int c = lane; c < 128; c += 32) s = fmaf(w[c], pooled[b * 128 + c], s);
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
@@ -647,19 +650,23 @@ __global__ void __launch_bounds__(128) dhead_kernel(const float* pooled, const f
             if (probs) probs[b] = pr;
         }
     }
-    __shared__ float red[32];
     const float tot = block_sum(lsum, red);
     if (threadIdx.x == 0) atomicAdd(loss_sum, static_cast<double>(tot) / B);
     __syncthreads();
-    const int c = threadIdx.x;
+    const int c = threadIdx.x & 127, bg = threadIdx.x >> 7;
     float g = 0.f;
     const float wc = w[c], inv_hw = 1.f / static_cast<float>(hw);
-    for (int b = 0; b < B; ++b) {
+    for (int b = bg; b < B; b += 8) {
         g = fmaf(dl[b], pooled[b * 128 + c], g);
         dpool[b * 128 + c] = dl[b] * wc * inv_hw;
     }
-    if (with_param_grads) {
-        gw[c] += g;
+    gpart[bg][c] = g;
+    __syncthreads();
+    if (with_param_grads && threadIdx.x < 128) {
+        float t = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t += gpart[k][c];
+        gw[c] += t;
         if (c == 0) {
             float sb = 0.f;
             for (int b = 0; b < B; ++b) sb += dl[b];
@@ -699,10 +706,7 @@ enum RepackMode {
     RP_LAST_DGRAD = 8    // the same operand for the data gradient of a Conv2d(3,64): row tap*3 + ci = w[co][ci][8 - tap]
 };
 
-__global__ void __launch_bounds__(256) repack_kernel(int mode, const float* w, __nv_bfloat16* dst, int cin, int cout,
-                                                     int npad, size_t n) {
-    const size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
-    if (i >= n) return;
+__device__ __forceinline__ float repack_value(int mode, const float* w, size_t i, int cin, int cout, int npad) {
     float val = 0.f;
     switch (mode) {
         case RP_CONV9_FWD: {
@@ -777,7 +781,37 @@ __global__ void __launch_bounds__(256) repack_kernel(int mode, const float* w, _
             break;
         }
     }
-    dst[i] = __float2bfloat16_rn(val);
+    return val;
+}
+
+// One launch re-packs a whole network: job j covers global elements [start_j, start_j + n_j). RP_COPY_F32 jobs copy
+// fp32 biases into their padded device arrays.
+constexpr int kRepackMaxJobs = 40;
+enum { RP_COPY_F32 = 100 };
+struct RepackJob {
+    const float* w;
+    void* dst;
+    int mode, cin, cout, npad;
+    unsigned n, start;
+};
+struct RepackJobs {
+    int count;
+    unsigned total;
+    RepackJob job[kRepackMaxJobs];
+};
+
+__global__ void __launch_bounds__(256) repack_multi_kernel(const __grid_constant__ RepackJobs jobs) {
+    const unsigned gi = blockIdx.x * 256u + threadIdx.x;
+    if (gi >= jobs.total) return;
+    int j = 0;
+    while (j + 1 < jobs.count && gi >= jobs.job[j + 1].start) ++j;
+    const RepackJob& J = jobs.job[j];
+    const size_t i = gi - J.start;
+    if (J.mode == RP_COPY_F32) {
+        static_cast<float*>(J.dst)[i] = J.w[i];
+        return;
+    }
+    static_cast<__nv_bfloat16*>(J.dst)[i] = __float2bfloat16_rn(repack_value(J.mode, J.w, i, J.cin, J.cout, J.npad));
 }
 
 }  // namespace cid

@@ -393,13 +393,27 @@ static int wgrad_edge(cid_train* t, const void* v64, const float* v3, int v3_nch
     return 0;
 }
 
-static int repack(cid_train* t, int mode, const float* w, void* dst, int cin, int cout, int npad, size_t n, cudaStream_t st) {
-    repack_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(mode, w, static_cast<__nv_bfloat16*>(dst), cin,
-                                                                          cout, npad, n);
-    CID_CHECK_CUDA(cudaGetLastError());
-    t->launches++;
-    return 0;
-}
+// job list of one repack_multi_kernel launch
+struct RepackList {
+    RepackJobs jobs;
+    RepackList() { jobs.count = 0; jobs.total = 0; }
+    int add(int mode, const float* w, void* dst, int cin, int cout, int npad, size_t n) {
+        CID_REQUIRE(jobs.count < kRepackMaxJobs, "repack: too many jobs");
+        RepackJob& J = jobs.job[jobs.count++];
+        J.w = w; J.dst = dst; J.mode = mode; J.cin = cin; J.cout = cout; J.npad = npad;
+        J.n = static_cast<unsigned>(n);
+        J.start = jobs.total;
+        jobs.total += static_cast<unsigned>(n);
+        return 0;
+    }
+    int launch(cid_train* t, cudaStream_t st) {
+        if (!jobs.count) return 0;
+        repack_multi_kernel<<<(jobs.total + 255) / 256, 256, 0, st>>>(jobs);
+        CID_CHECK_CUDA(cudaGetLastError());
+        t->launches++;
+        return 0;
+    }
+};
 
 // ---------------------------------------------------------------------------------------------------------------------
 // weight packs: fp32 masters (state buffer) -> bf16 operands
@@ -445,7 +459,8 @@ static int train_alloc_packs(cid_train* t) {
 static int train_repack(cid_train* t, int which, cudaStream_t st) {
     cid_ctx* c = t->g;
     if (which & 1) {
-        if (!t->g_ready) {
+        const bool first_time = !t->g_ready;
+        if (first_time) {
             // first time: build the forward packs, biases and TMA maps through the inference path (host pack)
             CID_CHECK_CUDA(cudaStreamSynchronize(st));
             for (int l = 0; l < 12; ++l) {
@@ -467,49 +482,54 @@ static int train_repack(cid_train* t, int which, cudaStream_t st) {
             }
             if (cid_finalize(c)) return 1;
             t->g_ready = true;
-        } else {
+        }
+        RepackList rl;
+        if (!first_time) {
             for (int l = 0; l < 12; ++l) {
                 const LayerDesc& L = kLayers[l];
                 const float* w = train_ptr(t, std::string("generator.") + L.name + ".weight", 0);
                 const float* b = train_ptr(t, std::string("generator.") + L.name + ".bias", 0);
                 if (l == 0) {
-                    if (repack(t, RP_FIRST, w, c->w_dev[0], 3, 64, 64, kFirstWBytes / 2, st)) return 1;
+                    if (rl.add(RP_FIRST, w, c->w_dev[0], 3, 64, 64, kFirstWBytes / 2)) return 1;
                 } else if (l == 11) {
-                    if (repack(t, RP_LAST, w, c->w_dev[11], 64, 3, 128, 128 * 64, st)) return 1;
+                    if (rl.add(RP_LAST, w, c->w_dev[11], 64, 3, 128, 128 * 64)) return 1;
                 } else if (L.kind == L_CONV) {
-                    if (repack(t, RP_CONV9_FWD, w, c->w_dev[l], L.cin, L.cout, L.cout, static_cast<size_t>(9) * L.cin * L.cout, st)) return 1;
+                    if (rl.add(RP_CONV9_FWD, w, c->w_dev[l], L.cin, L.cout, L.cout, static_cast<size_t>(9) * L.cin * L.cout)) return 1;
                 } else {
-                    if (repack(t, RP_CONVT_FWD, w, c->w_dev[l], L.cin, L.cout, L.cout, static_cast<size_t>(4) * L.cin * L.cout, st)) return 1;
+                    if (rl.add(RP_CONVT_FWD, w, c->w_dev[l], L.cin, L.cout, L.cout, static_cast<size_t>(4) * L.cin * L.cout)) return 1;
                 }
-                CID_CHECK_CUDA(cudaMemcpyAsync(c->bias_dev[l], b, L.cout * 4, cudaMemcpyDeviceToDevice, st));
+                if (rl.add(RP_COPY_F32, b, c->bias_dev[l], 0, 0, 0, L.cout)) return 1;
             }
         }
         for (int l = 1; l <= 10; ++l) {
             const LayerDesc& L = kLayers[l];
             const float* w = train_ptr(t, std::string("generator.") + L.name + ".weight", 0);
             const size_t taps = L.kind == L_CONVT ? 4 : 9;
-            if (repack(t, L.kind == L_CONVT ? RP_CONVT_DGRAD : RP_CONV9_DGRAD, w, t->gd_w[l], L.cin, L.cout, L.cout,
-                       taps * L.cin * L.cout, st))
+            if (rl.add(L.kind == L_CONVT ? RP_CONVT_DGRAD : RP_CONV9_DGRAD, w, t->gd_w[l], L.cin, L.cout, L.cout,
+                       taps * L.cin * L.cout))
                 return 1;
         }
+        if (rl.launch(t, st)) return 1;
     }
     if (which & 2) {
+        RepackList rl;
         for (int l = 0; l < 4; ++l) {
             const std::string base = "discriminator.model." + std::to_string(kDIdx[l]);
             const float* w = train_ptr(t, base + ".weight", 0);
             const float* b = train_ptr(t, base + ".bias", 0);
-            CID_CHECK_CUDA(cudaMemcpyAsync(t->d_bias_pad[l], b, kDCout[l] * 4, cudaMemcpyDeviceToDevice, st));
+            if (rl.add(RP_COPY_F32, b, t->d_bias_pad[l], 0, 0, 0, kDCout[l])) return 1;
             if (l == 0) {
-                if (repack(t, RP_FIRST, w, t->df_w[0], 3, 64, 64, kFirstWBytes / 2, st)) return 1;
-                if (repack(t, RP_LAST_DGRAD, w, t->dd_w[0], 3, 64, 64, 128 * 64, st)) return 1;
+                if (rl.add(RP_FIRST, w, t->df_w[0], 3, 64, 64, kFirstWBytes / 2)) return 1;
+                if (rl.add(RP_LAST_DGRAD, w, t->dd_w[0], 3, 64, 64, 128 * 64)) return 1;
                 continue;
             }
             const int cin = kDCin[l], cout = kDCout[l];
             const bool s2 = l != DL_CONV2;
             const size_t n = static_cast<size_t>(s2 ? 16 : 9) * cin * cout;
-            if (repack(t, s2 ? RP_K4_FWD : RP_CONV9_FWD, w, t->df_w[l], cin, cout, cout, n, st)) return 1;
-            if (repack(t, s2 ? RP_T4_DGRAD : RP_CONV9_DGRAD, w, t->dd_w[l], cin, cout, cout, n, st)) return 1;
+            if (rl.add(s2 ? RP_K4_FWD : RP_CONV9_FWD, w, t->df_w[l], cin, cout, cout, n)) return 1;
+            if (rl.add(s2 ? RP_T4_DGRAD : RP_CONV9_DGRAD, w, t->dd_w[l], cin, cout, cout, n)) return 1;
         }
+        if (rl.launch(t, st)) return 1;
     }
     return 0;
 }
@@ -714,7 +734,7 @@ static int d_backward(const TrainRun& r, const float* img, float target, float s
                       bool want_gx) {
     cid_train* t = r.t;
     const int B = r.B, H = r.H, W = r.W;
-    dhead_kernel<<<1, 128, B * sizeof(float), r.st>>>(
+    dhead_kernel<<<1, 1024, B * sizeof(float), r.st>>>(
         t->fsc + FS_POOLED, train_ptr(t, "discriminator.model.12.weight", 0), train_ptr(t, "discriminator.model.12.bias", 0), B,
         (H >> 2) * (W >> 2), target, scale, t->dsc + DS_LOSS + loss_slot, t->fsc + FS_DPOOL,
         train_ptr(t, "discriminator.model.12.weight", 1), train_ptr(t, "discriminator.model.12.bias", 1), t->fsc + FS_PROBS,
@@ -756,15 +776,9 @@ static int d_backward(const TrainRun& r, const float* img, float target, float s
         ConvParams p = conv_base(r, 1, 64, 64);
         p.n_tiles = 2;
         p.out = r.tbuf(TB_DG0); p.out_cs = 64;
+        // layer 0's LeakyReLU backward rides in the epilogue: g *= lrelu'(a0) (a0 is post-activation: same sign)
+        p.res2 = r.tbuf(TB_DA0); p.res2_cs = 64; p.mask_slope = 0.2f;
         if (launch_conv_t<64, 8, 2, false, EPI_T4, 10, 1>(t, *tmA, t->dd_tm[1], *tmO, p, r.st)) return 1;
-    }
-    // layer 0 (model.0 + LeakyReLU)
-    {
-        const size_t n8 = r.pixels(0) * 64 / 8;
-        lrelu_bwd_kernel<<<static_cast<unsigned>((n8 + 255) / 256), 256, 0, r.st>>>(
-            static_cast<__nv_bfloat16*>(r.tbuf(TB_DG0)), static_cast<const __nv_bfloat16*>(r.tbuf(TB_DA0)), n8, 0.2f);
-        CID_CHECK_CUDA(cudaGetLastError());
-        t->launches++;
     }
     if (param_grads) {
                 if (wgrad_edge(t, r.tbuf(TB_DG0), img, 1, 1, gradp(0, ".weight"), 0, r.tbuf(TB_U), B, H, W, r.st, gradp(0, ".bias"))) return 1;
