@@ -62,6 +62,10 @@ struct ConvParams {
     int bias_per_column; // EPI_CONVT as pixel shuffle: bias indexed by GEMM column instead of by channel
     float mask_slope;    // EPI_T4 with res2 set (training): the output gradient is multiplied by the LeakyReLU derivative of
                          // the activation res2 at the OUTPUT pixel (1 where it is positive, mask_slope elsewhere)
+    double* stats;       // EPI_LRELU with out_f32 (training): per-channel sum (stats[c]) and sum of squares (stats[128 + c])
+                         // of the fp32 outputs over all real pixels = the batch statistics of the BatchNorm that follows,
+                         // reduced in the epilogue (warp transpose-sum, per-CTA register accumulators, one double atomic
+                         // per channel per warp at the end); may be null
     float* out_f32;      // EPI_LRELU only: if set, the result is written as fp32 NHWC straight from registers (no bf16
                          // staging / TMA store): the discriminator's pre-BatchNorm outputs, whose mean >> std
     int debug_flags;     // bring-up experiments only: 1 = epilogue skips global stores, 2 = skips TMEM reads too
@@ -190,6 +194,21 @@ __device__ __forceinline__ void for_each_chunk(uint32_t taddr, F&& f) {
             f(ch + 1, vb);
         }
     }
+}
+
+// x[c] per lane (32 values) -> the sum over the warp's 32 lanes of x[lane]: recursive halving, 31 shuffles.
+__device__ __forceinline__ float warp_transpose_sum(float (&x)[32], int lane) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < off; ++i) {
+            const float send = up ? x[i] : x[i + off];
+            const float keep = up ? x[i + off] : x[i];
+            x[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+    }
+    return x[0];
 }
 
 // Same, over NCH chunks whose 32-column chunk index is given by map(i), i = 0..NCH-1.
@@ -464,6 +483,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint8_t* og = o_smem + g * Cfg::O_GROUP;
         uint32_t acc_it = 0;
         uint32_t o_count = 0;  // slabs this group has staged so far
+        // BatchNorm statistics (EPI_LRELU + stats): lane = channel inside a 32-channel chunk
+        float st_sum[EPI == EPI_LRELU ? N / 32 : 1], st_sq[EPI == EPI_LRELU ? N / 32 : 1];
+#pragma unroll
+        for (int i = 0; i < (EPI == EPI_LRELU ? N / 32 : 1); ++i) st_sum[i] = st_sq[i] = 0.f;
         // EPI_ADD: the first residual tensor (tmO2 = its tile map, same geometry as the output's) is TMA-loaded into
         // the group's staging slab one work item ahead: right after the slab's previous TMA store has been read out.
         // Group g owns exactly slab j = g of every work item (S * N/64 == 2). Out-of-image pixels load as zeros.
@@ -548,6 +571,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         for_each_chunk<2>(tbase + s * Cfg::NACC + cs * 64, [&](int ch, uint32_t (&v)[32]) {
                             const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_tile * N + cs * 64 + ch * 32);
                             uint32_t pk[16];
+                            float fv[EPI == EPI_LRELU ? 32 : 1];
                             if constexpr (EPI == EPI_ADD) {
                                 // v[2i], v[2i+1] += the bf16 pair i of this 32-channel half
 #pragma unroll
@@ -593,6 +617,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                 pk[2 * jj + 0] = pack_bf16x2(f0, f1);
                                 pk[2 * jj + 1] = pack_bf16x2(f2, f3);
                                 if constexpr (EPI == EPI_LRELU) {
+                                    fv[4 * jj + 0] = f0; fv[4 * jj + 1] = f1; fv[4 * jj + 2] = f2; fv[4 * jj + 3] = f3;
                                     if (p.out_f32 != nullptr) {
                                         const int yy = tc.y0 + yl, xx = tc.x0 + xl;
                                         if (tc.b < p.B && yy < p.H && xx < p.W) {
@@ -601,6 +626,19 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                             *reinterpret_cast<float4*>(dst) = make_float4(f0, f1, f2, f3);
                                         }
                                     }
+                                }
+                            }
+                            if constexpr (EPI == EPI_LRELU) {
+                                if (p.stats != nullptr) {
+                                    const bool live = tc.b < p.B && tc.y0 + yl < p.H && tc.x0 + xl < p.W;
+                                    float sq[32];
+#pragma unroll
+                                    for (int i = 0; i < 32; ++i) {
+                                        fv[i] = live ? fv[i] : 0.f;
+                                        sq[i] = fv[i] * fv[i];
+                                    }
+                                    st_sum[cs * 2 + ch] += warp_transpose_sum(fv, lane);
+                                    st_sq[cs * 2 + ch] += warp_transpose_sum(sq, lane);
                                 }
                             }
                             uint8_t* rowp = slab + row * 128;
@@ -782,6 +820,18 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     mbar_arrive(&acc_empty[buf]);
             }
             ++acc_it;
+        }
+        if constexpr (EPI == EPI_LRELU) {
+            if (p.stats != nullptr) {
+#pragma unroll
+                for (int i = 0; i < N / 32; ++i) {
+                    // (n_tiles == 1 on this path: chunk i = channels 32 i .. 32 i + 31)
+                    if (st_sum[i] != 0.f || st_sq[i] != 0.f) {
+                        atomicAdd(p.stats + i * 32 + lane, static_cast<double>(st_sum[i]));
+                        atomicAdd(p.stats + 128 + i * 32 + lane, static_cast<double>(st_sq[i]));
+                    }
+                }
+            }
         }
         if (issuer) bulk_wait_read<0>();  // the staged slabs have been read; the writes complete with the grid
     }

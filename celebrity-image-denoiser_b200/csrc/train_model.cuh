@@ -618,10 +618,6 @@ static int bn_forward(const TrainRun& r, int l, const void* z, void* a, int lv) 
     double* sums = t->dsc + DS_BN + (l - 1) * 256;
     float* stats = t->fsc + FS_STATS + (l - 1) * 256;
     const std::string bn = "discriminator.model." + std::to_string(kDBnIdx[l]);
-    CID_CHECK_CUDA(cudaMemsetAsync(sums, 0, 256 * 8, r.st));
-    const int ppb = reduce_ppb(t, P);
-    colsum_kernel<true, float><<<static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, r.st>>>(
-        static_cast<const float*>(z), P, C, 0, C, nullptr, sums, sums + 128, ppb);
     float* tab = t->fsc + FS_TAB + (l - 1) * 256;
     bn_finalize_kernel<<<1, 128, 0, r.st>>>(sums, sums + 128, static_cast<double>(P), C, 1e-5f, 0.1f, stats,
                                             train_ptr(t, bn + ".running_mean", 0), train_ptr(t, bn + ".running_var", 0),
@@ -631,7 +627,7 @@ static int bn_forward(const TrainRun& r, int l, const void* z, void* a, int lv) 
     bn_apply_kernel<float><<<static_cast<unsigned>((n8 + 255) / 256), 256, 0, r.st>>>(
         static_cast<const float*>(z), static_cast<__nv_bfloat16*>(a), P, C, tab, 0.2f);
     CID_CHECK_CUDA(cudaGetLastError());
-    t->launches += 3;
+    t->launches += 2;
     return 0;
 }
 
@@ -666,6 +662,8 @@ static int d_forward(const TrainRun& r, const float* img) {
         p.bias = t->d_bias_pad[1];
         p.out = r.tbuf(TB_DZ1D); p.out_cs = 64;
         p.out_f32 = static_cast<float*>(r.tbuf(TB_DZ1D));
+        p.stats = t->dsc + DS_BN + 0 * 256;  // batch statistics reduced in the epilogue
+        CID_CHECK_CUDA(cudaMemsetAsync(p.stats, 0, 256 * 8, r.st));
         if (launch_conv_t<64, 16, 2, false, EPI_LRELU, 9, 1>(t, *tmA, t->df_tm[1], *tmO, p, r.st)) return 1;
     }
     if (bn_forward(r, 1, r.tbuf(TB_DZ1D), r.tbuf(TB_DA1), 1)) return 1;
@@ -677,6 +675,8 @@ static int d_forward(const TrainRun& r, const float* img) {
         p.bias = t->d_bias_pad[2];
         p.out = r.tbuf(TB_DZ2D); p.out_cs = 128;
         p.out_f32 = static_cast<float*>(r.tbuf(TB_DZ2D));
+        p.stats = t->dsc + DS_BN + 1 * 256;  // batch statistics reduced in the epilogue
+        CID_CHECK_CUDA(cudaMemsetAsync(p.stats, 0, 256 * 8, r.st));
         if (launch_conv_t<128, 9, 2, false, EPI_LRELU, 10, 1>(t, *tmA, t->df_tm[2], *tmO, p, r.st)) return 1;
     }
     if (bn_forward(r, 2, r.tbuf(TB_DZ2D), r.tbuf(TB_DA2), 1)) return 1;
@@ -688,6 +688,8 @@ static int d_forward(const TrainRun& r, const float* img) {
         p.bias = t->d_bias_pad[3];
         p.out = r.tbuf(TB_DZ3D); p.out_cs = 128;
         p.out_f32 = static_cast<float*>(r.tbuf(TB_DZ3D));
+        p.stats = t->dsc + DS_BN + 2 * 256;  // batch statistics reduced in the epilogue
+        CID_CHECK_CUDA(cudaMemsetAsync(p.stats, 0, 256 * 8, r.st));
         if (launch_conv_t<128, 16, 2, false, EPI_LRELU, 9, 1>(t, *tmA, t->df_tm[3], *tmO, p, r.st)) return 1;
     }
     if (bn_forward(r, 3, r.tbuf(TB_DZ3D), r.tbuf(TB_DA3), 2)) return 1;
