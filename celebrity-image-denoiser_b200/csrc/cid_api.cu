@@ -939,7 +939,9 @@ int cid_train_create(int device, cid_train_handle* out) {
     if (cid_create_model(device, "denoise", &g)) return 1;
     cid_train* t = new cid_train();
     t->g = g;
-    g->variant |= 64 | 128;  // data-gradient kernels: resident weights / CTA pairs (measured 7.07 -> 6.96 ms per iteration)
+    // data-gradient kernels with resident weights / as CTA pairs (measured 7.07 -> 6.96 ms per iteration), weight-gradient
+    // MMAs tap-fused to N = 192 (6.34 -> 6.23 ms)
+    g->variant |= 64 | 128 | 1024;
     t->device = device;
     t->num_sms = g->num_sms;
     t->max_smem = g->max_smem;
@@ -1089,6 +1091,7 @@ int cid_train_g_backward(cid_train_handle t, const float* noisy, const float* cl
         p.clean = clean;
         p.gx = static_cast<const float*>(r.tbuf(TB_GX));
         p.gz = static_cast<float*>(r.tbuf(TB_GZ));
+        p.gz_nchw = static_cast<float*>(r.tbuf(TB_GZC));
         p.loss_sum = t->dsc + DS_LOSS + 3;
         p.bias_grad = train_ptr(t, "generator.upconv1.2.bias", 1);
         p.inv_n = 1.f / (static_cast<float>(B) * 3.f * H * W);
@@ -1137,7 +1140,7 @@ int cid_train_debug_buffer(cid_train_handle t, const char* name, const void* ws,
     CID_REQUIRE(t && name && ws && dst_host, "cid_train_debug_buffer: null argument");
     static const char* names[TB_COUNT] = {"y", "gz", "gx", "dz10", "gcat1", "dz8", "dz7", "gcat2", "dz5", "dz4", "gp2", "dz3", "dz2",
                                           "gp1", "dz1", "dz0", "d_a0", "d_z1", "d_a1", "d_z2", "d_a2", "d_z3", "d_a3", "d_g3", "d_g2",
-                                          "d_g1", "d_g0", "u"};
+                                          "d_g1", "d_g0", "gz_nchw", "u"};
     int b = -1;
     for (int i = 0; i < TB_COUNT; ++i)
         if (!strcmp(name, names[i])) b = i;

@@ -47,6 +47,8 @@ struct FirstParams {
     __nv_bfloat16* out;   // NHWC [B,H,W,64]
     int tiles_x, tiles_y, m_tiles;
     float slope;          // negative slope of the activation: 0 = ReLU (generator), 0.2 = the discriminator's LeakyReLU
+    const __nv_bfloat16* mask;  // training (data gradient of the generator's LAST conv run as a 3 -> 64 conv, slope 1):
+                                // NHWC-64 activation; the output is zeroed where it is not positive (ReLU backward)
 };
 
 // un-swizzled K-major descriptor: start[0,14) LBO[16,30) SBO[32,46) version[46,48)=1 layout[61,64)=0
@@ -288,6 +290,25 @@ first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParam
                     const float x2 = __uint_as_float(v[4 * j + 2]) + bb.z, x3 = __uint_as_float(v[4 * j + 3]) + bb.w;
                     pk[2 * j + 0] = pack_bf16x2(fmaxf(x0, 0.f) + p.slope * fminf(x0, 0.f), fmaxf(x1, 0.f) + p.slope * fminf(x1, 0.f));
                     pk[2 * j + 1] = pack_bf16x2(fmaxf(x2, 0.f) + p.slope * fminf(x2, 0.f), fmaxf(x3, 0.f) + p.slope * fminf(x3, 0.f));
+                }
+                if (p.mask != nullptr) {
+                    const int yy = ty * 16 + yl, xx = tx * 8 + xl;
+                    if (b < p.B && yy < p.H && xx < p.W) {
+                        const uint4* m4 = reinterpret_cast<const uint4*>(
+                            p.mask + ((static_cast<size_t>(b) * p.H + yy) * p.W + xx) * 64 + ch * 32);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const uint4 m = __ldg(m4 + i);
+                            const uint32_t w[4] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                uint32_t keep = 0u;
+                                if (__uint_as_float(w[e] << 16) > 0.f) keep |= 0x0000ffffu;
+                                if (__uint_as_float(w[e] & 0xffff0000u) > 0.f) keep |= 0xffff0000u;
+                                pk[i * 4 + e] &= keep;
+                            }
+                        }
+                    }
                 }
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {

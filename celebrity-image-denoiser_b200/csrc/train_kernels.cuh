@@ -1,6 +1,6 @@
-// Memory-bound and small kernels of the training step: the 3-channel edge layers on CUDA cores,
-// MaxPool / ReLU / LeakyReLU / tanh backward, train-mode BatchNorm (statistics by block reductions), the
-// discriminator head with BCELoss, bias gradients (column sums), Adam and the fp32 -> bf16 weight re-pack.
+// Memory-bound and small kernels of the training step: im2col of the 3-channel tensors (operand of the
+// edge layers' tensor-core weight gradients), MaxPool / ReLU / tanh backward, train-mode BatchNorm apply and backward,
+// the discriminator head with BCELoss, column sums, Adam and the fp32 -> bf16 weight re-pack.
 //
 // Reference ops (file:line in /root/reference/backend/trainingcode/denoise_gan_code/training.py):
 //   DenoiseDiscriminator                      :77-98   (Conv k3, LeakyReLU(0.2), Conv k3 s2, BatchNorm2d, AdaptiveAvgPool2d,
@@ -54,199 +54,9 @@ __device__ __forceinline__ float block_sum(float v, float* red /* >= 32 floats *
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// 3 -> 64 3x3 convolution, pad 1 (CUDA cores): one thread = one pixel x 64 channels.
-//   forward (dgrad = 0): discriminator model.0 + LeakyReLU(0.2); w = [64][3][3][3], input fp32 NCHW.
-//   dgrad = 1: the data gradient of the generator's last conv (64 -> 3): a 3 -> 64 conv of the fp32 NHWC-3 gradient
-//   with tap-flipped weights w = [3][64][3][3], masked by the ReLU of that conv's input activation.
-// ---------------------------------------------------------------------------------------------------------------------
-struct Conv3to64Params {
-    int B, H, W;
-    const float* in;
-    int in_nchw;
-    const float* w;
-    const float* bias;            // may be null
-    float slope;                  // leaky slope (forward)
-    int dgrad;
-    const __nv_bfloat16* mask;    // dgrad: activation whose sign gates the gradient (NHWC 64), may be null
-    __nv_bfloat16* out;           // NHWC [B,H,W,64]
-};
-
-__global__ void __launch_bounds__(128) conv3to64_kernel(const Conv3to64Params p) {
-    __shared__ float ws[27][64];
-    __shared__ float bs[64];
-    for (int i = threadIdx.x; i < 27 * 64; i += 128) {
-        const int t = i >> 6, co = i & 63, ci = t / 9, tap = t % 9;
-        ws[t][co] = p.dgrad ? p.w[(ci * 64 + co) * 9 + 8 - tap] : p.w[(co * 3 + ci) * 9 + tap];
-    }
-    if (threadIdx.x < 64) bs[threadIdx.x] = p.bias ? p.bias[threadIdx.x] : 0.f;
-    __syncthreads();
-    const size_t total = static_cast<size_t>(p.B) * p.H * p.W;
-    const size_t pix = static_cast<size_t>(blockIdx.x) * 128 + threadIdx.x;
-    if (pix >= total) return;
-    const int x = static_cast<int>(pix % p.W);
-    const int y = static_cast<int>((pix / p.W) % p.H);
-    const int b = static_cast<int>(pix / (static_cast<size_t>(p.W) * p.H));
-    float in[27];
-#pragma unroll
-    for (int ky = 0; ky < 3; ++ky)
-#pragma unroll
-        for (int kx = 0; kx < 3; ++kx) {
-            const int yy = y + ky - 1, xx = x + kx - 1;
-            const bool inside = yy >= 0 && yy < p.H && xx >= 0 && xx < p.W;
-#pragma unroll
-            for (int ci = 0; ci < 3; ++ci) {
-                float v = 0.f;
-                if (inside)
-                    v = p.in_nchw ? p.in[((static_cast<size_t>(b) * 3 + ci) * p.H + yy) * p.W + xx]
-                                  : p.in[((static_cast<size_t>(b) * p.H + yy) * p.W + xx) * 3 + ci];
-                in[ci * 9 + ky * 3 + kx] = v;
-            }
-        }
-    __nv_bfloat16* orow = p.out + pix * 64;
-    const uint4* mrow = p.mask ? reinterpret_cast<const uint4*>(p.mask + pix * 64) : nullptr;
-#pragma unroll
-    for (int half = 0; half < 2; ++half) {
-        float acc[32];
-#pragma unroll
-        for (int c = 0; c < 32; ++c) acc[c] = bs[half * 32 + c];
-#pragma unroll
-        for (int t = 0; t < 27; ++t)
-#pragma unroll
-            for (int c = 0; c < 32; ++c) acc[c] = fmaf(in[t], ws[t][half * 32 + c], acc[c]);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            float f[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) f[i] = acc[8 * j + i];
-            if (p.dgrad) {
-                if (mrow) {
-                    const uint4 m = __ldg(mrow + half * 4 + j);
-                    const uint32_t mw[4] = {m.x, m.y, m.z, m.w};
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        if (!(bf16_lo(mw[i]) > 0.f)) f[2 * i] = 0.f;
-                        if (!(bf16_hi(mw[i]) > 0.f)) f[2 * i + 1] = 0.f;
-                    }
-                }
-            } else {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) f[i] = f[i] > 0.f ? f[i] : f[i] * p.slope;
-            }
-            st_global_v4(orow + half * 32 + j * 8, pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]),
-                         pack_bf16x2(f[6], f[7]));
-        }
-    }
-}
-
-// ---------------------------------------------------------------------------------------------------------------------
-// 64 -> 3 data gradient of the discriminator's first conv: gx[p][ci] = sum_{tap,co} dz[p + 1 - tap][co] * w[co][ci][tap].
-// One thread = one pixel; fp32 NHWC-3 output.
-// ---------------------------------------------------------------------------------------------------------------------
-struct Conv64to3Params {
-    int B, H, W;
-    const __nv_bfloat16* dz;  // NHWC 64
-    const float* w;           // [64][3][3][3]
-    float* out;               // NHWC 3
-};
-
-__global__ void __launch_bounds__(128) conv64to3_dgrad_kernel(const Conv64to3Params p) {
-    __shared__ float ws[9][64][3];
-    for (int i = threadIdx.x; i < 9 * 64 * 3; i += 128) {
-        const int tap = i / 192, r = i % 192, co = r / 3, ci = r % 3;
-        ws[tap][co][ci] = p.w[(co * 3 + ci) * 9 + tap];
-    }
-    __syncthreads();
-    const size_t total = static_cast<size_t>(p.B) * p.H * p.W;
-    const size_t pix = static_cast<size_t>(blockIdx.x) * 128 + threadIdx.x;
-    if (pix >= total) return;
-    const int x = static_cast<int>(pix % p.W);
-    const int y = static_cast<int>((pix / p.W) % p.H);
-    const int b = static_cast<int>(pix / (static_cast<size_t>(p.W) * p.H));
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f;
-#pragma unroll
-    for (int ky = 0; ky < 3; ++ky)
-#pragma unroll
-        for (int kx = 0; kx < 3; ++kx) {
-            const int yy = y + 1 - ky, xx = x + 1 - kx;
-            if (yy < 0 || yy >= p.H || xx < 0 || xx >= p.W) continue;
-            const uint4* src = reinterpret_cast<const uint4*>(p.dz + ((static_cast<size_t>(b) * p.H + yy) * p.W + xx) * 64);
-            const int tap = ky * 3 + kx;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const uint4 v = __ldg(src + j);
-                const uint32_t vw[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float lo = bf16_lo(vw[i]), hi = bf16_hi(vw[i]);
-                    const int c = j * 8 + 2 * i;
-                    a0 = fmaf(lo, ws[tap][c][0], a0); a1 = fmaf(lo, ws[tap][c][1], a1); a2 = fmaf(lo, ws[tap][c][2], a2);
-                    a0 = fmaf(hi, ws[tap][c + 1][0], a0); a1 = fmaf(hi, ws[tap][c + 1][1], a1); a2 = fmaf(hi, ws[tap][c + 1][2], a2);
-                }
-            }
-        }
-    p.out[pix * 3 + 0] = a0;
-    p.out[pix * 3 + 1] = a1;
-    p.out[pix * 3 + 2] = a2;
-}
-
-// ---------------------------------------------------------------------------------------------------------------------
-// Weight gradient of the 3-channel layers: R[c64][c3][tap] = sum_p V64[p][c64] * V3[p + sign * (tap - centre)][c3].
-//   sign +1, out_mode 0: Conv2d(3,64) (generator down1.0, discriminator model.0): V64 = dZ, V3 = the layer's fp32 input.
-//   sign -1, out_mode 1: Conv2d(64,3) (generator upconv1.2): V64 = the layer's input activation, V3 = dZ (fp32 NHWC-3).
-// Block = 256 threads = 64 channels x 4 pixel groups over a strip of pixels; shared-memory reduce, then fp32 atomics.
-// ---------------------------------------------------------------------------------------------------------------------
-struct WgSmallParams {
-    int B, H, W;
-    const __nv_bfloat16* v64;
-    const float* v3;
-    int v3_nchw;
-    int sign;
-    float* out;
-    int out_mode;  // 0: out[(c64*3 + c3)*9 + tap]   1: out[(c3*64 + c64)*9 + tap]
-    int ppb;       // pixels per block
-};
-
-__global__ void __launch_bounds__(256) wgrad_small_kernel(const WgSmallParams p) {
-    __shared__ float red[4][27][64];
-    const int c = threadIdx.x & 63, grp = threadIdx.x >> 6;
-    const size_t total = static_cast<size_t>(p.B) * p.H * p.W;
-    const size_t p0 = static_cast<size_t>(blockIdx.x) * p.ppb;
-    const size_t p1 = min(total, p0 + p.ppb);
-    float acc[27];
-#pragma unroll
-    for (int i = 0; i < 27; ++i) acc[i] = 0.f;
-    for (size_t pix = p0 + grp; pix < p1; pix += 4) {
-        const float v = __bfloat162float(p.v64[pix * 64 + c]);
-        const int x = static_cast<int>(pix % p.W);
-        const int y = static_cast<int>((pix / p.W) % p.H);
-        const int b = static_cast<int>(pix / (static_cast<size_t>(p.W) * p.H));
-#pragma unroll
-        for (int ky = 0; ky < 3; ++ky)
-#pragma unroll
-            for (int kx = 0; kx < 3; ++kx) {
-                const int yy = y + p.sign * (ky - 1), xx = x + p.sign * (kx - 1);
-                if (yy < 0 || yy >= p.H || xx < 0 || xx >= p.W) continue;
-#pragma unroll
-                for (int ci = 0; ci < 3; ++ci) {
-                    const float u = p.v3_nchw ? __ldg(p.v3 + ((static_cast<size_t>(b) * 3 + ci) * p.H + yy) * p.W + xx)
-                                              : __ldg(p.v3 + ((static_cast<size_t>(b) * p.H + yy) * p.W + xx) * 3 + ci);
-                    acc[ci * 9 + ky * 3 + kx] = fmaf(v, u, acc[ci * 9 + ky * 3 + kx]);
-                }
-            }
-    }
-#pragma unroll
-    for (int i = 0; i < 27; ++i) red[grp][i][c] = acc[i];
-    __syncthreads();
-    for (int i = threadIdx.x; i < 27 * 64; i += 256) {
-        const int t = i >> 6, cc = i & 63, ci = t / 9, tap = t % 9;
-        const float s = red[0][t][cc] + red[1][t][cc] + red[2][t][cc] + red[3][t][cc];
-        float* dst = p.out_mode ? p.out + (ci * 64 + cc) * 9 + tap : p.out + (cc * 3 + ci) * 9 + tap;
-        atomicAdd(dst, s);
-    }
-}
-
-// ---------------------------------------------------------------------------------------------------------------------
-// Tensor-core route for the same 3-channel weight gradients: U[p][ci*9 + tap] = V3[p + sign*(tap - centre)][ci] as a
+// Weight gradients of the 3-channel layers on tensor cores: R[c64][ci*9 + tap] = sum_p V64[p][c64] * V3[p + sign*(tap - centre)][ci]
+// (sign +1: Conv2d(3,64), V64 = dZ, V3 = the layer input; sign -1: Conv2d(64,3), V64 = the layer input, V3 = dZ).
+// U[p][ci*9 + tap] = V3[p + sign*(tap - centre)][ci] as a
 // 64-channel bf16 NHWC tensor (27 real channels, the rest zero), so that R = V64^T U is ONE plain weight-gradient GEMM of
 // wgrad_umma.cuh (T = 1, no halo); wg27_scatter_kernel then adds the 64 x 27 result into the gradient tensor.
 // ---------------------------------------------------------------------------------------------------------------------
@@ -300,7 +110,8 @@ struct GLossParams {
     const float* y;      // fp32 NCHW generator output
     const float* clean;  // fp32 NCHW
     const float* gx;     // fp32 NHWC-3 or null
-    float* gz;           // fp32 NHWC-3
+    float* gz;           // fp32 NHWC-3 ...
+    float* gz_nchw;      // ... and the same as NCHW (input layout of the first-conv kernel that computes the data gradient)
     double* loss_sum;    // += sum (y - clean)^2 / n
     float* bias_grad;    // [3] +=
     float inv_n;
@@ -323,6 +134,7 @@ __global__ void __launch_bounds__(256) gloss_kernel(const GLossParams p) {
             if (p.gx) gr += p.gx[pix * 3 + c];
             g[c] = gr * (1.f - yv * yv);
             p.gz[pix * 3 + c] = g[c];
+            p.gz_nchw[(b * 3 + c) * hw + yx] = g[c];
         }
     }
     const float s = block_sum(sq, red);
@@ -592,23 +404,6 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const ZT* z, const __
     st_global_v4(dz + i * 8, pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]), pack_bf16x2(r[4], r[5]), pack_bf16x2(r[6], r[7]));
 }
 
-// g *= lrelu'(a) in place (a is post-activation: its sign is the pre-activation's)
-__global__ void __launch_bounds__(256) lrelu_bwd_kernel(__nv_bfloat16* g, const __nv_bfloat16* a, size_t n8, float slope) {
-    const size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
-    if (i >= n8) return;
-    const uint4 gv = *reinterpret_cast<const uint4*>(g + i * 8);
-    const uint4 av = __ldg(reinterpret_cast<const uint4*>(a + i * 8));
-    const uint32_t gw[4] = {gv.x, gv.y, gv.z, gv.w}, aw[4] = {av.x, av.y, av.z, av.w};
-    uint32_t o[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const float lo = bf16_lo(aw[j]) > 0.f ? bf16_lo(gw[j]) : bf16_lo(gw[j]) * slope;
-        const float hi = bf16_hi(aw[j]) > 0.f ? bf16_hi(gw[j]) : bf16_hi(gw[j]) * slope;
-        o[j] = pack_bf16x2(lo, hi);
-    }
-    st_global_v4(g + i * 8, o[0], o[1], o[2], o[3]);
-}
-
 // ---------------------------------------------------------------------------------------------------------------------
 // Discriminator head: AdaptiveAvgPool2d(1) -> Conv2d(128,1,k1) -> Sigmoid -> BCELoss(mean) and its backward.
 // ---------------------------------------------------------------------------------------------------------------------
@@ -703,6 +498,8 @@ enum RepackMode {
     RP_T4_DGRAD = 5,     // dst[((ky*4+kx)*cin + ci)*cout + co] = same value
     RP_FIRST = 6,        // first_conv_umma.cuh operand: [tap][k chunk][cout 64][8] with hi/lo split
     RP_LAST = 7,         // last_conv_umma.cuh operand: row tap*3 + co of 128 rows x 64 channels
+    RP_FIRST_DGRAD = 9,  // first_conv_umma.cuh operand for the data gradient of a Conv2d(64,3): the 3 -> 64 conv with
+                         // weight(ci3 -> co64, tap) = w[ci3][co64][8 - tap]
     RP_LAST_DGRAD = 8    // the same operand for the data gradient of a Conv2d(3,64): row tap*3 + ci = w[co][ci][8 - tap]
 };
 
@@ -762,6 +559,19 @@ __device__ __forceinline__ float repack_value(int mode, const float* w, size_t i
                 if (e < 6) val = w[(co * 3 + (e % 3)) * 9 + tap];
             } else if (e < 3) {
                 const float wf = w[(co * 3 + e) * 9 + tap];
+                val = wf - __bfloat162float(__float2bfloat16_rn(wf));
+            }
+            break;
+        }
+        case RP_FIRST_DGRAD: {
+            const int e = static_cast<int>(i & 7);
+            const int co = static_cast<int>((i >> 3) & 63);
+            const int chunk = static_cast<int>((i >> 9) & 1);
+            const int tap = static_cast<int>(i >> 10);
+            if (chunk == 0) {
+                if (e < 6) val = w[((e % 3) * 64 + co) * 9 + 8 - tap];
+            } else if (e < 3) {
+                const float wf = w[(e * 64 + co) * 9 + 8 - tap];
                 val = wf - __bfloat162float(__float2bfloat16_rn(wf));
             }
             break;

@@ -39,13 +39,14 @@ enum TBuf {
     TB_Y, TB_GZ, TB_GX,                                                             // fp32, 3 channels, level 0
     TB_DZ10, TB_GCAT1, TB_DZ8, TB_DZ7, TB_GCAT2, TB_DZ5, TB_DZ4, TB_GP2, TB_DZ3, TB_DZ2, TB_GP1, TB_DZ1, TB_DZ0,
     TB_DA0, TB_DZ1D, TB_DA1, TB_DZ2D, TB_DA2, TB_DZ3D, TB_DA3, TB_DG3, TB_DG2, TB_DG1, TB_DG0,
+    TB_GZC,  // gz as fp32 NCHW
     TB_U,  // im2col of a 3-channel tensor (27 of 64 channels used): operand of the edge layers' weight gradients
     TB_COUNT
 };
 static const int kTBufC[TB_COUNT] = {3, 3, 3, 64, 128, 128, 128, 256, 256, 256, 128, 128, 128, 64, 64, 64,
-                                     64, 64, 64, 128, 128, 128, 128, 128, 128, 64, 64, 64};
+                                     64, 64, 64, 128, 128, 128, 128, 128, 128, 64, 64, 3, 64};
 static const int kTBufLevel[TB_COUNT] = {0, 0, 0, 0, 0, 1, 1, 1, 2, 2, 2, 1, 1, 1, 0, 0,
-                                         0, 1, 1, 1, 1, 2, 2, 2, 1, 1, 0, 0};
+                                         0, 1, 1, 1, 1, 2, 2, 2, 1, 1, 0, 0, 0};
 
 }  // namespace cid
 
@@ -58,7 +59,7 @@ struct cid_train {
     size_t n_g = 0, n_d = 0, n_buf = 0;
     bool g_ready = false;
     // bf16 operand packs owned by the library
-    void* gd_w[12] = {nullptr};       // generator data-gradient packs (layers 1..10)
+    void* gd_w[12] = {nullptr};       // generator data-gradient packs (layers 1..10; 11 = first-conv operand of upconv1.2's)
     CUtensorMap gd_tm[12];
     CUtensorMap gd_tmh[12];           // same packs, box of N/2 rows (CTA-pair kernels load half a weight tile each)
     int gd_n[12] = {0};               // tile width N of the pack's tensor map
@@ -145,7 +146,7 @@ static float* train_ptr(const cid_train* t, const std::string& key, int section)
 // ---------------------------------------------------------------------------------------------------------------------
 // fp32: the 3-channel image-side tensors and the discriminator's pre-BatchNorm conv outputs (mean >> std on smooth
 // images: bf16 storage would cost ~3 % of a standard deviation per layer in the normalised value)
-static size_t tbuf_elem(int b) { return (b <= TB_GX || b == TB_DZ1D || b == TB_DZ2D || b == TB_DZ3D) ? 4 : 2; }
+static size_t tbuf_elem(int b) { return (b <= TB_GX || b == TB_DZ1D || b == TB_DZ2D || b == TB_DZ3D || b == TB_GZC) ? 4 : 2; }
 static size_t tbuf_bytes(int b, int B, int H, int W) {
     const int lv = kTBufLevel[b];
     const size_t es = tbuf_elem(b);
@@ -335,6 +336,7 @@ static int wgrad(cid_train* t, int geom, const void* A, int a_C, int m_ch, const
     p.B = B; p.H = H; p.W = W;
     p.out = out;
     p.bias_out = bias_out;
+    p.fuse_taps = (geom == 0 && (t->g->variant & 1024)) ? 1 : 0;  // "variant" bit 1024: N = 192 tap-fused MMAs
     // "variant" bit 256: 3x3 stride-1 layers as clusters of 3 CTAs with TMA multicast; bit 512: ... with N = 64 per CTA
     const bool cl3 = geom == 0 && (t->g->variant & 256);
     const int NA = m_ch >= 128 ? 2 : 1, NB = (n_ch >= 128 && !(cl3 && (t->g->variant & 512))) ? 2 : 1;
@@ -439,6 +441,7 @@ static int train_alloc_packs(cid_train* t) {
         if (make_weight_map(&t->dd_tm[l], t->dd_w[l], (s2 ? 16 : 9) * cin, cout, cin)) return 1;
         if (make_weight_map(&t->dd_tmh[l], t->dd_w[l], (s2 ? 16 : 9) * cin, cout, cin / 2)) return 1;
     }
+    CID_CHECK_CUDA(cudaMalloc(&t->gd_w[11], kFirstWBytes));     // first_conv_umma operand of upconv1.2's data gradient
     CID_CHECK_CUDA(cudaMalloc(&t->df_w[0], kFirstWBytes));      // first_conv_umma operand of model.0
     CID_CHECK_CUDA(cudaMalloc(&t->dd_w[0], 128 * 64 * 2));      // last_conv_umma operand of model.0's data gradient
     if (make_weight_map(&t->dd_tm[0], t->dd_w[0], 128, 64, 128)) return 1;
@@ -509,6 +512,7 @@ static int train_repack(cid_train* t, int which, cudaStream_t st) {
                        taps * L.cin * L.cout))
                 return 1;
         }
+        if (rl.add(RP_FIRST_DGRAD, train_ptr(t, "generator.upconv1.2.weight", 0), t->gd_w[11], 64, 3, 64, kFirstWBytes / 2)) return 1;
         if (rl.launch(t, st)) return 1;
     }
     if (which & 2) {
@@ -828,15 +832,23 @@ static int g_backward_layers(const TrainRun& r, const float* noisy) {
     {
         if (wgrad_edge(t, r.gbuf(B_U1A), static_cast<const float*>(r.tbuf(TB_GZ)), 0, -1, gw(11), 1, r.tbuf(TB_U), B, H, W, r.st))
             return 1;
-        Conv3to64Params q;
-        memset(&q, 0, sizeof(q));
-        q.B = B; q.H = H; q.W = W;
-        q.in = static_cast<const float*>(r.tbuf(TB_GZ)); q.in_nchw = 0;
-        q.w = train_ptr(t, "generator.upconv1.2.weight", 0);
-        q.dgrad = 1;
-        q.mask = static_cast<const __nv_bfloat16*>(r.gbuf(B_U1A));
-        q.out = static_cast<__nv_bfloat16*>(r.tbuf(TB_DZ10));
-        conv3to64_kernel<<<static_cast<unsigned>((r.pixels(0) + 127) / 128), 128, 0, r.st>>>(q);
+        // data gradient (3 -> 64 conv of gz with flipped weights, masked by u1a > 0) on the tensor-core first-conv kernel
+        const CUtensorMap* tmO = tmap(t, r.tbuf(TB_DZ10), B, H, W, 64, 16, 8, 0);
+        if (!tmO) return 1;
+        FirstParams fp;
+        memset(&fp, 0, sizeof(fp));
+        fp.B = B; fp.H = H; fp.W = W;
+        fp.in = r.tbuf(TB_GZC);
+        fp.bias = t->zero_bias;
+        fp.out = static_cast<__nv_bfloat16*>(r.tbuf(TB_DZ10));
+        fp.tiles_x = (W + 7) / 8;
+        fp.tiles_y = (H + 15) / 16;
+        fp.m_tiles = B * fp.tiles_x * fp.tiles_y;
+        fp.w_packed = static_cast<const uint4*>(t->gd_w[11]);
+        fp.slope = 1.f;
+        fp.mask = static_cast<const __nv_bfloat16*>(r.gbuf(B_U1A));
+        const int grid = std::min(fp.m_tiles, t->num_sms * kFirstCtasPerSm);
+        CID_CHECK_CUDA(launch_ex(t->g, first_conv_umma_kernel<false>, grid, kFirstThreads, kFirstSmem, r.st, 1, *tmO, fp));
         CID_CHECK_CUDA(cudaGetLastError());
         t->launches++;
     }

@@ -49,6 +49,9 @@ struct WgParams {
     float* out;   // out[((m0 + row) * s_m + n0 + col) * kk + tap]
     int s_m, kk;
     int m_valid;  // rows of the 128-row accumulator that are real channels (64 or 128)
+    int fuse_taps;  // T = 3 only: the three taps of a row are ONE MMA of N = 192 per 64-channel B atom (the atoms of the
+                    // MN-major operand are the same patch one pixel = 128 B apart: LBO = 128), so operand A is read from
+                    // shared memory once per K step instead of three times. Accumulator column = q*192 + t*64 + c.
     float* bias_out;  // bias gradient (column sums of operand A = dZ), reduced by the otherwise idle epilogue warps of
                       // the roles flagged WgRole::bias while the MMAs run; may be null
     WgRole roles[kWgMaxRoles];
@@ -195,12 +198,22 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     for (int k8 = 0; k8 < 8; ++k8) {
                         // K = 16 pixels = tile rows 2*k8 and 2*k8+1
                         const uint64_t ad = umma_desc_mn_sw128(sa + k8 * 2048, NA == 2 ? A_ATOM : 0, 1024);
+                        if (T == 3 && p.fuse_taps) {
+                            constexpr uint32_t idesc3 = umma_idesc_bf16_mn(128, 192);
 #pragma unroll
-                        for (int t = 0; t < T; ++t) {
-                            const uint64_t bd =
-                                umma_desc_mn_sw128(sb + ((k8 * 2 + (CL == 3 ? static_cast<int>(rank) : 0)) * p.pw + t) * 128,
-                                                   static_cast<uint32_t>(pb), sbo_b);
-                            umma_bf16_ss(tmem_base + t * N, ad, bd, idesc, (mt == t_begin && k8 == 0) ? 0u : 1u);
+                            for (int q = 0; q < NB; ++q) {
+                                const uint64_t bd = umma_desc_mn_sw128(
+                                    sb + q * pb + ((k8 * 2 + (CL == 3 ? static_cast<int>(rank) : 0)) * p.pw) * 128, 128, sbo_b);
+                                umma_bf16_ss(tmem_base + q * 192, ad, bd, idesc3, (mt == t_begin && k8 == 0) ? 0u : 1u);
+                            }
+                        } else {
+#pragma unroll
+                            for (int t = 0; t < T; ++t) {
+                                const uint64_t bd = umma_desc_mn_sw128(
+                                    sb + ((k8 * 2 + (CL == 3 ? static_cast<int>(rank) : 0)) * p.pw + t) * 128,
+                                    static_cast<uint32_t>(pb), sbo_b);
+                                umma_bf16_ss(tmem_base + t * N, ad, bd, idesc, (mt == t_begin && k8 == 0) ? 0u : 1u);
+                            }
                         }
                     }
                     if (CL == 3)
@@ -282,7 +295,9 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
                 for (int ch = 0; ch < N / 32; ++ch) {
                     uint32_t v[32];
-                    tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + t * N + ch * 32, v);
+                    // column of (tap t, channel chunk ch): t*N + 32 ch, or q*192 + t*64 + ... in the fused-tap layout
+                    const int col = (T == 3 && p.fuse_taps) ? (ch >> 1) * 192 + t * 64 + (ch & 1) * 32 : t * N + ch * 32;
+                    tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + col, v);
                     tmem_ld_wait();
 #pragma unroll
                     for (int j = 0; j < 32; ++j) red_add_f32(orow + static_cast<size_t>(ch * 32 + j) * p.kk + tap, __uint_as_float(v[j]));
