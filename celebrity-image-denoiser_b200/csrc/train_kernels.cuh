@@ -198,56 +198,59 @@ __global__ void __launch_bounds__(256) colsum_kernel(const ZT* v, size_t P, int 
 // ---------------------------------------------------------------------------------------------------------------------
 // MaxPool2d(2,2) backward fused with the skip-connection add and the ReLU mask of the pooled activation e:
 //   dz[p][c] = (e[p][c] > 0) ? gskip[p][c] + (p is the first arg-max of its 2x2 window ? gpool[p/2][c] : 0) : 0
-// e and gskip live in channel slices of the concat buffers (stride cs, first channel c0). 8 channels per thread.
+// e and gskip live in channel slices of the concat buffers (stride cs, first channel c0).
 // ---------------------------------------------------------------------------------------------------------------------
+// One thread = one 2x2 window x 8 channels: 4 e + 4 gskip + 1 gpool loads, 4 stores (H, W even).
 __global__ void __launch_bounds__(256) poolbwd_kernel(const __nv_bfloat16* e, const __nv_bfloat16* gskip, int cs, int c0,
                                                       const __nv_bfloat16* gpool, __nv_bfloat16* dz, int B, int H, int W, int C) {
     const int chunks = C >> 3;
-    const size_t total = static_cast<size_t>(B) * H * W * chunks;
+    const int Hp = H >> 1, Wp = W >> 1;
+    const size_t total = static_cast<size_t>(B) * Hp * Wp * chunks;
     const size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
     if (i >= total) return;
     const int ck = static_cast<int>(i % chunks);
-    const size_t pix = i / chunks;
-    const int x = static_cast<int>(pix % W);
-    const int y = static_cast<int>((pix / W) % H);
-    const size_t b = pix / (static_cast<size_t>(W) * H);
-    const int k = (y & 1) * 2 + (x & 1);
-    const int wy = y & ~1, wx = x & ~1;
-    uint4 ev[4];
+    const size_t pp = i / chunks;  // pooled pixel
+    const int xp = static_cast<int>(pp % Wp);
+    const int yp = static_cast<int>((pp / Wp) % Hp);
+    const size_t b = pp / (static_cast<size_t>(Wp) * Hp);
+    size_t q[4];
+    uint4 ev[4], gv[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-        const size_t q = (b * H + wy + (j >> 1)) * W + wx + (j & 1);
-        ev[j] = __ldg(reinterpret_cast<const uint4*>(e + q * cs + c0 + ck * 8));
+        q[j] = (b * H + 2 * yp + (j >> 1)) * W + 2 * xp + (j & 1);
+        ev[j] = __ldg(reinterpret_cast<const uint4*>(e + q[j] * cs + c0 + ck * 8));
+        gv[j] = __ldg(reinterpret_cast<const uint4*>(gskip + q[j] * cs + c0 + ck * 8));
     }
-    const uint4 gs = __ldg(reinterpret_cast<const uint4*>(gskip + pix * cs + c0 + ck * 8));
-    const size_t pp = (b * (H >> 1) + (y >> 1)) * (W >> 1) + (x >> 1);
     const uint4 gp = __ldg(reinterpret_cast<const uint4*>(gpool + pp * C + ck * 8));
-    const uint32_t gsw[4] = {gs.x, gs.y, gs.z, gs.w}, gpw[4] = {gp.x, gp.y, gp.z, gp.w};
-    uint32_t o[4];
+    const uint32_t gpw[4] = {gp.x, gp.y, gp.z, gp.w};
+    uint32_t o[4][4];
 #pragma unroll
     for (int wi = 0; wi < 4; ++wi) {
-        float r[2];
+        float r[4][2];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-            float ej[4];
+            float ej[4], gj[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const uint32_t w = wi == 0 ? ev[j].x : wi == 1 ? ev[j].y : wi == 2 ? ev[j].z : ev[j].w;
+                const uint32_t g = wi == 0 ? gv[j].x : wi == 1 ? gv[j].y : wi == 2 ? gv[j].z : gv[j].w;
                 ej[j] = h ? bf16_hi(w) : bf16_lo(w);
+                gj[j] = h ? bf16_hi(g) : bf16_lo(g);
             }
             const float mx = fmaxf(fmaxf(ej[0], ej[1]), fmaxf(ej[2], ej[3]));
-            int first = 3;
+            int first = 3;  // torch's MaxPool2d keeps the first maximum in scan order
 #pragma unroll
             for (int j = 3; j >= 0; --j)
                 if (ej[j] == mx) first = j;
-            const float mine = ej[k == 0 ? 0 : k == 1 ? 1 : k == 2 ? 2 : 3];
-            float gsum = h ? bf16_hi(gsw[wi]) : bf16_lo(gsw[wi]);
-            if (first == k) gsum += h ? bf16_hi(gpw[wi]) : bf16_lo(gpw[wi]);
-            r[h] = mine > 0.f ? gsum : 0.f;
+            const float gpv = h ? bf16_hi(gpw[wi]) : bf16_lo(gpw[wi]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) r[j][h] = ej[j] > 0.f ? gj[j] + (first == j ? gpv : 0.f) : 0.f;
         }
-        o[wi] = pack_bf16x2(r[0], r[1]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) o[j][wi] = pack_bf16x2(r[j][0], r[j][1]);
     }
-    st_global_v4(dz + pix * C + ck * 8, o[0], o[1], o[2], o[3]);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) st_global_v4(dz + q[j] * C + ck * 8, o[j][0], o[j][1], o[j][2], o[j][3]);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------

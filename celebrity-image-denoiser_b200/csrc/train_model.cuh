@@ -822,7 +822,7 @@ static int g_backward_layers(const TrainRun& r, const float* noisy) {
     auto gw = [&](int l) { return train_ptr(t, std::string("generator.") + kLayers[l].name + ".weight", 1); };
     auto gb = [&](int l) { return train_ptr(t, std::string("generator.") + kLayers[l].name + ".bias", 1); };
     auto pool_bwd = [&](int cat, int C, int lv, int gcat, int gpool, int dz) {
-        const size_t total = r.pixels(lv) * (C / 8);
+        const size_t total = r.pixels(lv) / 4 * (C / 8);  // one thread per 2x2 window x 8 channels
         poolbwd_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, r.st>>>(
             static_cast<const __nv_bfloat16*>(r.gbuf(cat)), static_cast<const __nv_bfloat16*>(r.tbuf(gcat)), 2 * C, C,
             static_cast<const __nv_bfloat16*>(r.tbuf(gpool)), static_cast<__nv_bfloat16*>(r.tbuf(dz)), B, H >> lv, W >> lv, C);
