@@ -102,7 +102,8 @@ def train_iteration(g: nn.Module, d: nn.Module, g_opt, d_opt, noisy: torch.Tenso
         g_loss.backward()
         g_grads = {k: p.grad.detach().clone() for k, p in g.named_parameters()}
         g_opt.step()
-    return {"d_loss": float(d_loss), "g_loss": float(g_loss), "content": float(content), "adv": float(adv),
+    return {"d_loss": float(d_loss.detach()), "g_loss": float(g_loss.detach()), "content": float(content.detach()),
+            "adv": float(adv.detach()),
             "d_grads": d_grads, "g_grads": g_grads, "denoised": denoised.detach()}
 
 
@@ -185,5 +186,6 @@ def instrumented_gradients(g: DenoiseGenerator, d: DenoiseDiscriminator, noisy: 
     acts.update({n[4:]: nhwc(t) for n, t in keep.items() if n.startswith("fwd_")})
     acts["gx"] = nhwc(gx)
     acts["y"] = y.detach()
-    return {"d_loss": float(d_loss), "g_loss": float(g_loss), "content": float(content), "adv": float(adv),
+    return {"d_loss": float(d_loss.detach()), "g_loss": float(g_loss.detach()), "content": float(content.detach()),
+            "adv": float(adv.detach()),
             "d_grads": d_grads, "g_grads": g_grads, "acts": acts}
