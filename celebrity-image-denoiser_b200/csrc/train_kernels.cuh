@@ -276,24 +276,31 @@ __global__ void bn_finalize_kernel(const double* dsum, const double* dsq, double
 }
 
 // a = lrelu(z * a2 + b2) with tab[c] = {a2 = gamma * invstd, b2 = beta - gamma * mean * invstd}; 8 channels per thread
+constexpr int kBnIter = 8;  // items (8 channels of one pixel) per thread of the BatchNorm apply kernels
+
 template <typename ZT>
 __global__ void __launch_bounds__(256) bn_apply_kernel(const ZT* z, __nv_bfloat16* a, size_t P, int C, const float* tab,
                                                        float slope) {
-    __shared__ float st[2 * 256];
-    for (int i = threadIdx.x; i < 2 * C; i += 256) st[i] = tab[i];
-    __syncthreads();
+    // 256 is a multiple of C/8: a thread keeps the same 8 channels over its items, their table entries in registers
     const int chunks = C >> 3;
-    const size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
-    if (i >= P * chunks) return;
-    const int c8 = static_cast<int>(i % chunks) * 8;
-    float zf[8], r[8];
-    load8(z + i * 8, zf);
+    const int c8 = static_cast<int>(threadIdx.x % chunks) * 8;
+    float a2[8], b2[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        const float yv = fmaf(zf[j], st[2 * (c8 + j)], st[2 * (c8 + j) + 1]);
-        r[j] = yv > 0.f ? yv : yv * slope;
+    for (int j = 0; j < 8; ++j) { a2[j] = tab[2 * (c8 + j)]; b2[j] = tab[2 * (c8 + j) + 1]; }
+    const size_t n = P * chunks;
+    size_t i = static_cast<size_t>(blockIdx.x) * (256 * kBnIter) + threadIdx.x;
+#pragma unroll 4
+    for (int it = 0; it < kBnIter; ++it, i += 256) {
+        if (i >= n) break;
+        float zf[8], r[8];
+        load8(z + i * 8, zf);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float yv = fmaf(zf[j], a2[j], b2[j]);
+            r[j] = yv > 0.f ? yv : yv * slope;
+        }
+        st_global_v4(a + i * 8, pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]), pack_bf16x2(r[4], r[5]), pack_bf16x2(r[6], r[7]));
     }
-    st_global_v4(a + i * 8, pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]), pack_bf16x2(r[4], r[5]), pack_bf16x2(r[6], r[7]));
 }
 
 // dY = dA * lrelu'(y); sums[c] += {sum dY, sum dY * xhat}. dA comes from a tensor (da) or, for the layer under the
@@ -379,32 +386,37 @@ template <typename ZT>
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const ZT* z, const __nv_bfloat16* da,
                                                            const float* dpool, __nv_bfloat16* dz, size_t P, size_t hw,
                                                            int C, float slope, const float* btab) {
-    __shared__ float st[5 * 256];
-    for (int i = threadIdx.x; i < 5 * C; i += 256) st[i] = btab[i];
-    __syncthreads();
     const int chunks = C >> 3;
-    const size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
-    if (i >= P * chunks) return;
-    const int c8 = static_cast<int>(i % chunks) * 8;
-    const size_t pix = i / chunks;
-    float zf[8], dd[8];
-    load8(z + i * 8, zf);
-    if (da) {
-        load8(da + i * 8, dd);
-    } else {
-        const size_t b = pix / hw;
-        const float4 d0 = *reinterpret_cast<const float4*>(dpool + b * C + c8), d1 = *reinterpret_cast<const float4*>(dpool + b * C + c8 + 4);
-        dd[0] = d0.x; dd[1] = d0.y; dd[2] = d0.z; dd[3] = d0.w; dd[4] = d1.x; dd[5] = d1.y; dd[6] = d1.z; dd[7] = d1.w;
-    }
-    float r[8];
+    const int c8 = static_cast<int>(threadIdx.x % chunks) * 8;
+    float t0[8], t1[8], t2[8], t3[8], t4[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        const float* t5 = st + 5 * (c8 + j);
-        const float yv = fmaf(zf[j], t5[0], t5[1]);
-        const float dy = yv > 0.f ? dd[j] : dd[j] * slope;
-        r[j] = fmaf(t5[2], dy, -t5[3]) - zf[j] * t5[4];
+        const float* t5 = btab + 5 * (c8 + j);
+        t0[j] = t5[0]; t1[j] = t5[1]; t2[j] = t5[2]; t3[j] = t5[3]; t4[j] = t5[4];
     }
-    st_global_v4(dz + i * 8, pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]), pack_bf16x2(r[4], r[5]), pack_bf16x2(r[6], r[7]));
+    const size_t n = P * chunks;
+    size_t i = static_cast<size_t>(blockIdx.x) * (256 * kBnIter) + threadIdx.x;
+#pragma unroll 4
+    for (int it = 0; it < kBnIter; ++it, i += 256) {
+        if (i >= n) break;
+        float zf[8], dd[8];
+        load8(z + i * 8, zf);
+        if (da) {
+            load8(da + i * 8, dd);
+        } else {
+            const size_t b = (i / chunks) / hw;
+            const float4 d0 = *reinterpret_cast<const float4*>(dpool + b * C + c8), d1 = *reinterpret_cast<const float4*>(dpool + b * C + c8 + 4);
+            dd[0] = d0.x; dd[1] = d0.y; dd[2] = d0.z; dd[3] = d0.w; dd[4] = d1.x; dd[5] = d1.y; dd[6] = d1.z; dd[7] = d1.w;
+        }
+        float r[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float yv = fmaf(zf[j], t0[j], t1[j]);
+            const float dy = yv > 0.f ? dd[j] : dd[j] * slope;
+            r[j] = fmaf(t2[j], dy, -t3[j]) - zf[j] * t4[j];
+        }
+        st_global_v4(dz + i * 8, pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]), pack_bf16x2(r[4], r[5]), pack_bf16x2(r[6], r[7]));
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------------------

@@ -188,8 +188,7 @@ static const CUtensorMap* tmap(cid_train* t, const void* base, int B, int H, int
     snprintf(key, sizeof(key), "%p/%d/%d/%d/%d/%d/%d/%d", base, B, H, W, C, rows, px, kind);
     auto it = t->maps.find(key);
     if (it != t->maps.end()) return &it->second;
-    if (t->maps.size() > 512) t->maps.clear();
-    CUtensorMap tm;
+    CUtensorMap tm;  // (the cache is trimmed only between steps, train_make_run: pointers handed out stay valid)
     int rc = kind == 0   ? make_act_map(&tm, base, B, H, W, C, rows, px)
              : kind == 1 ? make_act_map_s2(&tm, base, B, H, W, C, rows, px)
                          : make_convt_out_map(&tm, base, B, H, W, C);
@@ -218,10 +217,10 @@ static int launch_conv_t(cid_train* t, const CUtensorMap& tmA, const CUtensorMap
     p.num_work = ((p.m_tiles + S * CG - 1) / (S * CG)) * p.n_tiles;
     const int smem = Cfg::smem_bytes(p.kb_count, a_stages, w_stages);
     auto kern = conv_umma_kernel<N, TAPS, S, WRES, EPI, PW, TS, CG>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static uint64_t attr_set = 0;  // bit per device: function attributes are per device
+    if (!(attr_set >> (c->device & 63) & 1)) {
         CID_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c->max_smem));
-        attr_set = true;
+        attr_set |= 1ull << (c->device & 63);
     }
     const int grid = std::min(p.num_work * CG, c->num_sms / CG * CG);
     CID_CHECK_CUDA(launch_ex(c, kern, grid, kConvThreads, smem, st, CG, tmA, tmW, tmO, tmO, p));
@@ -244,9 +243,9 @@ static int launch_wgrad(cid_train* t, const CUtensorMap& tmA, const CUtensorMap&
     // > half of the SM's shared memory: one CTA per SM (each CTA allocates up to all 512 TMEM columns)
     const int smem = std::max(p.stages * stage_bytes + 1024 + 256, 120 * 1024);
     auto kern = wgrad_umma_kernel<NA, NB, T, CL>;
-    static bool attr_set = false;
-    static int max_units = 0;  // co-resident CTAs (CL = 1) or clusters (CL = 3)
-    if (!attr_set) {
+    static uint64_t attr_set = 0;  // bit per device
+    static int max_units = 0;      // co-resident CTAs (CL = 1) or clusters (CL = 3); same on every B200 of the box
+    if (!(attr_set >> (t->device & 63) & 1)) {
         CID_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, t->max_smem));
         max_units = t->num_sms;
         if (CL > 1) {
@@ -265,7 +264,7 @@ static int launch_wgrad(cid_train* t, const CUtensorMap& tmA, const CUtensorMap&
             CID_REQUIRE(n >= 1, "wgrad: no cluster of %d CTAs fits", CL);
             max_units = n;
         }
-        attr_set = true;
+        attr_set |= 1ull << (t->device & 63);
     }
     const int n_units = p.n_roles / CL;
     p.slices = std::max(1, std::min(max_units / n_units, p.m_tiles));
@@ -628,7 +627,7 @@ static int bn_forward(const TrainRun& r, int l, const void* z, void* a, int lv) 
                                             train_ptr(t, bn + ".num_batches_tracked", 0), train_ptr(t, bn + ".weight", 0),
                                             train_ptr(t, bn + ".bias", 0), tab);
     const size_t n8 = P * C / 8;
-    bn_apply_kernel<float><<<static_cast<unsigned>((n8 + 255) / 256), 256, 0, r.st>>>(
+    bn_apply_kernel<float><<<static_cast<unsigned>((n8 + 256 * kBnIter - 1) / (256 * kBnIter)), 256, 0, r.st>>>(
         static_cast<const float*>(z), static_cast<__nv_bfloat16*>(a), P, C, tab, 0.2f);
     CID_CHECK_CUDA(cudaGetLastError());
     t->launches += 2;
@@ -726,7 +725,7 @@ static int bn_backward(const TrainRun& r, int l, const void* z, const void* da, 
                                                 param_grads ? train_ptr(t, bn + ".weight", 1) : nullptr,
                                                 param_grads ? train_ptr(t, bn + ".bias", 1) : nullptr);
     const size_t n8 = P * C / 8;
-    bn_bwd_apply_kernel<float><<<static_cast<unsigned>((n8 + 255) / 256), 256, 0, r.st>>>(
+    bn_bwd_apply_kernel<float><<<static_cast<unsigned>((n8 + 256 * kBnIter - 1) / (256 * kBnIter)), 256, 0, r.st>>>(
         static_cast<const float*>(z), static_cast<const __nv_bfloat16*>(da), t->fsc + FS_DPOOL,
         static_cast<__nv_bfloat16*>(dz), P, hw, C, 0.2f, btab);
     t->launches += 3;
@@ -902,6 +901,7 @@ static int train_make_run(cid_train* t, int B, int H, int W, void* ws, size_t ws
                 kTrainMaxBatch);
     CID_REQUIRE(H >= 16 && W >= 16 && H % 4 == 0 && W % 4 == 0, "training image %dx%d must be multiples of 4, >= 16", H, W);
     CID_REQUIRE(ws && (reinterpret_cast<uintptr_t>(ws) & 1023) == 0, "workspace must be 1024-byte aligned");
+    if (t->maps.size() > 384) t->maps.clear();  // many (shape, workspace) combinations seen: start over
     r->t = t; r->B = B; r->H = H; r->W = W;
     r->ws = static_cast<uint8_t*>(ws);
     r->st = st;
