@@ -641,7 +641,7 @@ using namespace cid;
 // =============================================================================================
 extern "C" {
 
-int cid_version(void) { return 5; }
+int cid_version(void) { return 6; }
 
 const char* cid_last_error(void) { return g_err; }
 
@@ -967,6 +967,7 @@ int cid_train_destroy(cid_train_handle t) {
             if (t->d_bias_pad[l]) cudaFree(t->d_bias_pad[l]);
         }
         if (t->zero_bias) cudaFree(t->zero_bias);
+        if (t->peer_err) cudaFree(t->peer_err);
         if (t->dsc) cudaFree(t->dsc);
         if (t->fsc) cudaFree(t->fsc);
     }
@@ -1112,11 +1113,54 @@ int cid_train_adam(cid_train_handle t, int which, float lr, float beta1, float b
     const int64_t step = which ? ++t->step_d : ++t->step_g;
     const float bc1 = 1.f - powf(beta1, static_cast<float>(step));
     const float bc2 = sqrtf(1.f - powf(beta2, static_cast<float>(step)));
-    adam_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(t->state + off, t->state + P + off, t->state + 2 * P + off,
-                                                                        t->state + 3 * P + off, n, lr, beta1, beta2, eps, bc1, bc2);
+    if (t->peer_world > 1) {
+        // gradient all-reduce fused into the optimiser step over NVLink peer memory (adam_allreduce_kernel)
+        PeerSet ps;
+        memset(&ps, 0, sizeof(ps));
+        ps.world = t->peer_world;
+        ps.rank = t->peer_rank;
+        for (int r = 0; r < t->peer_world; ++r) {
+            ps.grads[r] = t->peer_state[r] + P + off;
+            ps.flags[r] = t->peer_flags[r];
+        }
+        adam_allreduce_kernel<<<kPeerBlocks, 256, 0, st>>>(t->state + off, t->state + 2 * P + off, t->state + 3 * P + off, n, ps,
+                                                           ++t->peer_epoch, t->peer_err, lr, beta1, beta2, eps, bc1, bc2);
+    } else {
+        adam_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(t->state + off, t->state + P + off, t->state + 2 * P + off,
+                                                                            t->state + 3 * P + off, n, lr, beta1, beta2, eps, bc1, bc2);
+    }
     CID_CHECK_CUDA(cudaGetLastError());
     t->launches++;
     return train_repack(t, which ? 2 : 1, st);
+}
+
+int cid_train_peer_flag_ints(void) { return 2 * kPeerMax * kPeerBlocks; }
+
+int cid_train_set_peers(cid_train_handle t, int world, int rank, const void* const* state_ptrs, void* const* flag_ptrs) {
+    CID_REQUIRE(t && t->state, "cid_train_set_peers: state not bound");
+    if (world <= 1) {
+        t->peer_world = 0;
+        return 0;
+    }
+    CID_REQUIRE(world <= kPeerMax, "cid_train_set_peers: at most %d ranks (one NVLink domain)", kPeerMax);
+    CID_REQUIRE(rank >= 0 && rank < world && state_ptrs && flag_ptrs, "cid_train_set_peers: bad rank / null pointer table");
+    CID_REQUIRE(state_ptrs[rank] == static_cast<const void*>(t->state),
+                "cid_train_set_peers: state_ptrs[rank] must be the bound state buffer (allocate it as symmetric memory)");
+    DeviceGuard dg(t->device);
+    CID_REQUIRE(dg.ok, "cannot select CUDA device %d", t->device);
+    for (int r = 0; r < world; ++r) {
+        CID_REQUIRE(state_ptrs[r] && flag_ptrs[r], "cid_train_set_peers: null peer pointer for rank %d", r);
+        t->peer_state[r] = static_cast<const float*>(state_ptrs[r]);
+        t->peer_flags[r] = static_cast<int*>(flag_ptrs[r]);
+    }
+    if (!t->peer_err) {
+        CID_CHECK_CUDA(cudaMalloc(reinterpret_cast<void**>(&t->peer_err), sizeof(int)));
+        CID_CHECK_CUDA(cudaMemset(t->peer_err, 0, sizeof(int)));
+    }
+    t->peer_world = world;
+    t->peer_rank = rank;
+    t->peer_epoch = 0;
+    return 0;
 }
 
 int cid_train_losses(cid_train_handle t, double* out4) {
@@ -1126,6 +1170,11 @@ int cid_train_losses(cid_train_handle t, double* out4) {
     double h[4];
     CID_CHECK_CUDA(cudaDeviceSynchronize());
     CID_CHECK_CUDA(cudaMemcpy(h, t->dsc + DS_LOSS, sizeof(h), cudaMemcpyDeviceToHost));
+    if (t->peer_err) {
+        int e = 0;
+        CID_CHECK_CUDA(cudaMemcpy(&e, t->peer_err, sizeof(int), cudaMemcpyDeviceToHost));
+        CID_REQUIRE(e == 0, "a data-parallel peer did not reach the fused all-reduce barrier (timeout); the replicas have diverged");
+    }
     out4[0] = h[0] + h[1];          // d_loss
     out4[1] = h[3] + 0.001 * h[2];  // g_loss
     out4[2] = h[3];                 // content (MSE)

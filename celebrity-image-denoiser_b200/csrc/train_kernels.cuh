@@ -502,6 +502,107 @@ __global__ void __launch_bounds__(256) adam_kernel(float* w, const float* g, flo
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
+// Data-parallel Adam: gradient all-reduce FUSED into the optimiser step over NVLink peer memory (one launch instead of
+// all-reduce + scale + Adam). Every rank's state buffer is symmetric memory mapped into every peer: each rank reads the
+// gradient section of all ranks (rank 0 .. world-1 in that fixed order, so all replicas compute bit-identical sums),
+// averages, and applies Adam to its own replica of the weights. One-shot is the right shape at this size (7.3 MB / 1 MB
+// sections: launch latency, not link bandwidth). Cross-GPU ordering = two flag barriers per launch, per block index:
+//   start: "my gradients are complete" (stream order puts this launch after the backward pass) -> peers may read them
+//   end:   "I have finished reading yours"                                                    -> peers may overwrite them
+// flags[phase][rank][block] live in a symmetric int buffer and hold the epoch of the last launch that passed (monotonic).
+// A spin that exceeds kPeerSpinNs records an error (err[0] = 1) and moves on instead of hanging the GPU.
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int kPeerMax = 8;
+constexpr int kPeerBlocks = 296;                       // all co-resident: the barriers are per block index
+constexpr unsigned long long kPeerSpinNs = 4000000000ull;
+struct PeerSet {
+    const float* grads[kPeerMax];  // peers' gradient sections (this network), rank order
+    int* flags[kPeerMax];          // peers' flag buffers [2][kPeerMax][kPeerBlocks]
+    int world, rank;
+};
+__device__ __forceinline__ void st_release_sys(int* p, int v) { asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ int ld_acquire_sys(const int* p) {
+    int v;
+    asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float ld_sys_f32(const float* p) {
+    float v;
+    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float4 ld_sys_v4(const float* p) {
+    float4 v;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void peer_barrier(const PeerSet& ps, int phase, int epoch, int* err) {
+    __syncthreads();
+    if (threadIdx.x < ps.world) {
+        const int slot = (phase * kPeerMax) * kPeerBlocks + blockIdx.x;
+        st_release_sys(ps.flags[threadIdx.x] + slot + ps.rank * kPeerBlocks, epoch);
+        const int* mine = ps.flags[ps.rank] + slot + threadIdx.x * kPeerBlocks;
+        const unsigned long long t0 = global_ns();
+        while (ld_acquire_sys(mine) < epoch) {
+            if (global_ns() - t0 > kPeerSpinNs) {
+                *err = 1;
+                break;
+            }
+        }
+    }
+    __syncthreads();
+}
+__device__ __forceinline__ void adam_update(float& w, float& m, float& v, float g, float lr_bc1, float b1, float b2, float eps,
+                                            float bc2_sqrt) {
+    m = b1 * m + (1.f - b1) * g;
+    v = b2 * v + (1.f - b2) * g * g;
+    w -= lr_bc1 * (m / (sqrtf(v) / bc2_sqrt + eps));
+}
+__global__ void __launch_bounds__(256) adam_allreduce_kernel(float* w, float* m, float* v, size_t n, const __grid_constant__ PeerSet ps,
+                                                             int epoch, int* err, float lr, float b1, float b2, float eps,
+                                                             float bc1, float bc2_sqrt) {
+    peer_barrier(ps, 0, epoch, err);
+    const float inv_world = 1.f / static_cast<float>(ps.world), lr_bc1 = lr / bc1;
+    // the four sections share their alignment modulo 16 bytes: scalar head up to it, float4 body, scalar tail
+    const size_t head = min(n, static_cast<size_t>((4 - ((reinterpret_cast<uintptr_t>(w) >> 2) & 3)) & 3));
+    const size_t n4 = (n - head) / 4, tail0 = head + n4 * 4;
+    const size_t tid = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x, nth = static_cast<size_t>(gridDim.x) * 256;
+    for (size_t i = tid; i < n4; i += nth) {
+        const size_t e = head + i * 4;
+        float4 g[kPeerMax];
+#pragma unroll
+        for (int r = 0; r < kPeerMax; ++r)
+            if (r < ps.world) g[r] = ld_sys_v4(ps.grads[r] + e);
+        float4 s = g[0];
+#pragma unroll
+        for (int r = 1; r < kPeerMax; ++r)
+            if (r < ps.world) { s.x += g[r].x; s.y += g[r].y; s.z += g[r].z; s.w += g[r].w; }
+        float4 wv = *reinterpret_cast<float4*>(w + e), mv = *reinterpret_cast<float4*>(m + e), vv = *reinterpret_cast<float4*>(v + e);
+        adam_update(wv.x, mv.x, vv.x, s.x * inv_world, lr_bc1, b1, b2, eps, bc2_sqrt);
+        adam_update(wv.y, mv.y, vv.y, s.y * inv_world, lr_bc1, b1, b2, eps, bc2_sqrt);
+        adam_update(wv.z, mv.z, vv.z, s.z * inv_world, lr_bc1, b1, b2, eps, bc2_sqrt);
+        adam_update(wv.w, mv.w, vv.w, s.w * inv_world, lr_bc1, b1, b2, eps, bc2_sqrt);
+        *reinterpret_cast<float4*>(w + e) = wv;
+        *reinterpret_cast<float4*>(m + e) = mv;
+        *reinterpret_cast<float4*>(v + e) = vv;
+    }
+    if (blockIdx.x == 0 && threadIdx.x < 8) {  // at most 3 + 3 unaligned elements
+        const size_t e = threadIdx.x < 4 ? threadIdx.x : tail0 + (threadIdx.x - 4);
+        if (threadIdx.x < 4 ? e < head : e < n) {
+            float s = 0.f;
+            for (int r = 0; r < ps.world; ++r) s += ld_sys_f32(ps.grads[r] + e);
+            adam_update(w[e], m[e], v[e], s * inv_world, lr_bc1, b1, b2, eps, bc2_sqrt);
+        }
+    }
+    peer_barrier(ps, 1, epoch, err);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
 // fp32 master weights (reference layout) -> the bf16 operand layouts of the tensor-core kernels
 // ---------------------------------------------------------------------------------------------------------------------
 enum RepackMode {

@@ -72,6 +72,11 @@ struct cid_train {
     float* fsc = nullptr;             // float scratch: BN stats, pooled, dpool, probs
     std::map<std::string, CUtensorMap> maps;
     int64_t step_g = 0, step_d = 0;
+    // data-parallel peers (cid_train_set_peers): symmetric state / flag buffers of every rank, mapped into this process
+    int peer_world = 0, peer_rank = 0, peer_epoch = 0;
+    const float* peer_state[8] = {nullptr};
+    int* peer_flags[8] = {nullptr};
+    int* peer_err = nullptr;          // device int: a peer barrier timed out
     int64_t launches = 0;
     int B = 0, H = 0, W = 0;          // shape of the last d_backward (g_backward continues from it)
     const void* ws = nullptr;

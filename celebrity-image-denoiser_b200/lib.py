@@ -12,7 +12,7 @@ from pathlib import Path
 _LIB_PATH = Path(__file__).resolve().parent / "csrc" / "libcid_b200.so"
 _lib = None
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 # name -> (restype, argtypes); mirrors include/cid_b200.h one to one
 _SIGNATURES = {
@@ -64,6 +64,8 @@ _SIGNATURES = {
                                        C.c_size_t, C.c_void_p]),
     "cid_train_adam": (C.c_int, [C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p]),
     "cid_train_losses": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
+    "cid_train_peer_flag_ints": (C.c_int, []),
+    "cid_train_set_peers": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]),
     "cid_train_kernel_launches": (C.c_int64, [C.c_void_p]),
     "cid_train_debug_buffer": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                          C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),

@@ -13,6 +13,7 @@ There is no CPU or PyTorch compute path here.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Dict, Optional
 
 import torch
@@ -73,7 +74,7 @@ class DenoiseGANTrainStep:
     """
 
     def __init__(self, generator: nn.Module, discriminator: nn.Module, device="cuda", lr: float = 1e-4,
-                 betas=(0.9, 0.999), eps: float = 1e-8, process_group=None):
+                 betas=(0.9, 0.999), eps: float = 1e-8, process_group=None, peer_allreduce: bool = True):
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("the training step runs on a CUDA device (sm_100a); there is no CPU fallback")
@@ -86,12 +87,71 @@ class DenoiseGANTrainStep:
         self.handle = h
         n = C.c_size_t()
         _lib.check(self.lib.cid_train_state_floats(h, C.byref(n)), "cid_train_state_floats")
-        self.state = torch.zeros(n.value, dtype=torch.float32, device=self.device)
+        self.peer_fused = False
+        self._symm = None
+        self._peer_error = None
+        peers = self._symmetric_state(n.value) if peer_allreduce else None
+        self.state = peers[0] if peers else torch.zeros(n.value, dtype=torch.float32, device=self.device)
         _lib.check(self.lib.cid_train_bind_state(h, C.c_void_p(self.state.data_ptr()), n.value), "cid_train_bind_state")
+        if peers:
+            self._bind_peers(*peers)
         self.names = [self.lib.cid_train_tensor_name(h, i).decode() for i in range(self.lib.cid_train_tensor_count(h))]
         self._ws: Optional[torch.Tensor] = None
         self._ws_key = None
         self.load_state_dicts(generator.state_dict(), discriminator.state_dict())
+
+    # ---- data-parallel peers -----------------------------------------------------------------
+    def _symmetric_state(self, n: int):
+        """With >1 ranks on one NVLink domain: allocate the state (and the barrier flags) as torch symmetric memory so
+        that cid_train_adam can run the gradient all-reduce inside the optimiser kernel (include/cid_b200.h,
+        cid_train_set_peers). Returns (state, flags, state_handle, flags_handle) or None; every rank takes the same
+        decision (a MIN all-reduce of the outcome), otherwise the NCCL all-reduce path of `step` is used."""
+        import torch.distributed as dist
+        if not (dist.is_available() and dist.is_initialized()) or os.environ.get("CID_PEER_ALLREDUCE", "1") == "0":
+            return None
+        group = self.group if self.group is not None else dist.group.WORLD
+        world = dist.get_world_size(group)
+        if world < 2 or dist.get_backend(group) != "nccl":
+            return None
+        out, ok = None, 1
+        try:
+            import torch.distributed._symmetric_memory as symm
+            if world > 8:
+                raise RuntimeError("more than 8 ranks")
+            with torch.cuda.device(self.device):
+                state = symm.empty(n, dtype=torch.float32, device=self.device)
+                flags = symm.empty(int(self.lib.cid_train_peer_flag_ints()), dtype=torch.int32, device=self.device)
+                state.zero_()
+                flags.zero_()
+                torch.cuda.synchronize(self.device)
+                hs = symm.rendezvous(state, group)
+                hf = symm.rendezvous(flags, group)
+            if len(hs.buffer_ptrs) != world or hs.buffer_ptrs[hs.rank] != state.data_ptr():
+                raise RuntimeError("unexpected symmetric-memory pointer table")
+            out = (state, flags, hs, hf)
+        except Exception as e:  # symmetric memory unavailable (no P2P, old driver, ...): NCCL path
+            self._peer_error = repr(e)
+            ok = 0
+        agree = torch.tensor([ok], dtype=torch.int32, device=self.device)
+        dist.all_reduce(agree, op=dist.ReduceOp.MIN, group=group)  # also orders the zeroing above before any peer's first flag write
+        return out if int(agree.item()) == 1 else None
+
+    def _bind_peers(self, state, flags, hs, hf) -> None:
+        world = hs.world_size
+        sp = (C.c_void_p * world)(*[C.c_void_p(int(p)) for p in hs.buffer_ptrs])
+        fp = (C.c_void_p * world)(*[C.c_void_p(int(p)) for p in hf.buffer_ptrs])
+        _lib.check(self.lib.cid_train_set_peers(self.handle, world, hs.rank, sp, fp), "cid_train_set_peers")
+        self._symm = (flags, hs, hf)  # keep the mappings alive
+        self.peer_fused = True
+
+    def bind_peers_raw(self, world: int, rank: int, state_ptrs, flag_ptrs, keep_alive=None) -> None:
+        """cid_train_set_peers with caller-provided device pointers (rank order). For callers that map the peers' buffers
+        themselves (CUDA IPC, several replicas inside one process); `flag_ptrs[r]` = cid_train_peer_flag_ints() zeroed ints."""
+        sp = (C.c_void_p * world)(*[C.c_void_p(int(p)) for p in state_ptrs])
+        fp = (C.c_void_p * world)(*[C.c_void_p(int(p)) for p in flag_ptrs])
+        _lib.check(self.lib.cid_train_set_peers(self.handle, world, rank, sp, fp), "cid_train_set_peers")
+        self._symm = keep_alive
+        self.peer_fused = world > 1
 
     # ---- state ------------------------------------------------------------------------------
     def close(self):
@@ -157,7 +217,8 @@ class DenoiseGANTrainStep:
         return p, self._ws.numel() - (p - self._ws.data_ptr())
 
     def _allreduce(self, flat: torch.Tensor) -> None:
-        allreduce_mean_(flat, self.group)
+        if not self.peer_fused:  # fused: cid_train_adam reads every rank's gradients itself
+            allreduce_mean_(flat, self.group)
 
     def d_backward(self, noisy: torch.Tensor, clean: torch.Tensor) -> None:
         B, H, W, ws, wsn, st = self._args(noisy, clean)

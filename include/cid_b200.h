@@ -183,6 +183,7 @@ int cid_debug_copy_activation(cid_handle h, const char* name, const void* ws, in
  *
  *   cid_train_d_backward -> [all-reduce D grads] -> cid_train_adam(which=1)
  *   cid_train_g_backward -> [all-reduce G grads] -> cid_train_adam(which=0)
+ * (or, with cid_train_set_peers, no caller-side collective at all: the all-reduce runs inside cid_train_adam)
  *
  * State: ONE caller-owned fp32 device buffer of cid_train_state_floats() floats, laid out as four sections of
  * P = n_generator + n_discriminator floats - parameters (reference layout of every state_dict tensor), gradients,
@@ -220,6 +221,18 @@ int cid_train_g_backward(cid_train_handle t, const float* noisy, const float* cl
 /* optimizer.step() of one network (which: 0 generator, 1 discriminator) on the gradients section as it stands,
  * then re-packs that network's tensor-core operands. Reference values: lr 1e-4, betas (0.9, 0.999), eps 1e-8. */
 int cid_train_adam(cid_train_handle t, int which, float lr, float beta1, float beta2, float eps, void* stream);
+/* Data-parallel replicas on one NVLink domain (the reference trains on one device, training.py:394-437; this is the
+ * exchange step of SURVEY §8(e) for config #5). With peers set, cid_train_adam FUSES the gradient all-reduce into the
+ * optimiser step: one kernel reads the gradient section of every rank through peer memory (rank order, so every
+ * replica computes the same bits), averages, and applies Adam; two cross-GPU flag barriers inside the kernel order it
+ * against the peers' backward passes. No separate collective is then needed (or allowed) between *_backward and adam,
+ * and the gradients section keeps the rank-LOCAL gradients. Requirements: the bound state buffer and one int buffer of
+ * cid_train_peer_flag_ints() zeroed ints are symmetric allocations mapped into every rank (e.g. torch symmetric memory);
+ * state_ptrs[r] / flag_ptrs[r] are rank r's buffers as THIS process addresses them; every rank calls cid_train_adam the
+ * same number of times in the same order. world <= 8; world <= 1 switches the fused path off. A peer that does not
+ * arrive within 4 s makes the next cid_train_losses fail instead of hanging the GPU. */
+int cid_train_peer_flag_ints(void);
+int cid_train_set_peers(cid_train_handle t, int world, int rank, const void* const* state_ptrs, void* const* flag_ptrs);
 /* Synchronises; out4 = {d_loss, g_loss, content (MSE), adversarial (BCE)} of the last step. */
 int cid_train_losses(cid_train_handle t, double* out4);
 int64_t cid_train_kernel_launches(cid_train_handle t);

@@ -189,3 +189,44 @@ def test_full_size_gradient_is_the_loss_derivative():
     g3 = tr.section("generator", 1)
     assert float((g2 - g3).norm() / g2.norm()) < 1e-3
     tr.close()
+
+
+def test_fused_allreduce_adam_two_replicas_one_gpu():
+    """cid_train_set_peers: two replicas (here both on cuda:0, each launch on its own stream so that the in-kernel
+    barriers can meet) average their gradients inside the optimiser kernel. Against torch.optim.Adam on the mean
+    gradient, both replicas bit-identical to each other, three steps."""
+    from cid_b200 import lib as cid_lib
+    lib = cid_lib.load()
+    g, d = DenoiseGenerator(), DenoiseDiscriminator()
+    reps = [DenoiseGANTrainStep(g, d, device="cuda:0") for _ in range(2)]
+    flags = [torch.zeros(lib.cid_train_peer_flag_ints(), dtype=torch.int32, device="cuda:0") for _ in range(2)]
+    for r, tr in enumerate(reps):
+        tr.bind_peers_raw(2, r, [t.state.data_ptr() for t in reps], [f.data_ptr() for f in flags], keep_alive=flags)
+        assert tr.peer_fused
+    streams = [torch.cuda.Stream(device="cuda:0") for _ in range(2)]
+    gen = torch.Generator().manual_seed(11)
+    for which, net in ((1, "discriminator"), (0, "generator")):
+        w0 = reps[0].section(net, 0).clone()
+        ref_w = torch.nn.Parameter(w0.double().cpu())
+        opt = torch.optim.Adam([ref_w], lr=1e-4, betas=(0.9, 0.999), eps=1e-8)
+        for step in range(3):
+            grads = [torch.randn(w0.numel(), generator=gen) * (10.0 ** -step) for _ in range(2)]
+            for tr, gr in zip(reps, grads):
+                tr.section(net, 1).copy_(gr.cuda())
+            torch.cuda.synchronize()
+            for tr, st in zip(reps, streams):
+                with torch.cuda.stream(st):
+                    tr.adam(which)
+            torch.cuda.synchronize()
+            reps[0].losses()                      # raises if a barrier timed out
+            ref_w.grad = ((grads[0].float() + grads[1].float()) * 0.5).double()
+            opt.step()
+            a, b = reps[0].section(net, 0), reps[1].section(net, 0)
+            assert torch.equal(a, b), "replicas diverged"
+            assert torch.equal(reps[0].section(net, 2), reps[1].section(net, 2))
+            err = (a.cpu().double() - ref_w.detach()).abs().max().item()
+            assert err < 2e-6, (net, step, err)
+            # the gradient section keeps the rank-local gradients
+            assert torch.equal(reps[1].section(net, 1).cpu(), grads[1])
+    for tr in reps:
+        tr.close()

@@ -30,6 +30,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--variant", type=int, default=-1, help="cid 'variant' option (CTA-pair bit mask)")
     ap.add_argument("--phases", action="store_true", help="also time the four phases separately")
+    ap.add_argument("--nccl", action="store_true", help="N > 1: NCCL all-reduce + Adam instead of the fused peer-memory kernel")
+    ap.add_argument("--check", action="store_true", help="N > 1: run 3 steps on both all-reduce paths and compare the weights")
     a = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -45,7 +47,7 @@ def main():
         os.dup2(saved, 1)
     torch.manual_seed(0)
     g, d = DenoiseGenerator(), DenoiseDiscriminator()
-    tr = DenoiseGANTrainStep(g, d, device=dev)
+    tr = DenoiseGANTrainStep(g, d, device=dev, peer_allreduce=not a.nccl)
     if a.variant >= 0:
         tr.set_option("variant", a.variant)
     gen = torch.Generator(device="cpu").manual_seed(1234 + rank)
@@ -53,6 +55,32 @@ def main():
     clean = torch.nn.functional.interpolate(clean, size=(a.H, a.W), mode="bicubic", align_corners=False).clamp(0, 1)
     noisy = (clean + 0.1 * torch.randn(a.B, 3, a.H, a.W, generator=gen)).clamp(0, 1)
     noisy, clean = ((noisy - 0.5) / 0.5).to(dev).contiguous(), ((clean - 0.5) / 0.5).to(dev).contiguous()
+    if a.check and world > 1:
+        ref = DenoiseGANTrainStep(g, d, device=dev, peer_allreduce=False)
+        worst = 0.0
+        # the optimiser paths are compared on the SAME rank-local gradients (two backward passes of one trainer differ in
+        # the last bits - atomics order in the weight-gradient kernels - and Adam turns the sign of a ~0 gradient into +-lr)
+        for it in range(3):
+            for which, net, backward in ((1, "discriminator", tr.d_backward), (0, "generator", tr.g_backward)):
+                backward(noisy, clean)
+                ref.section(net, 1).copy_(tr.section(net, 1))
+                tr.adam(which)
+                ref._allreduce(ref.section(net, 1))
+                ref.adam(which)
+                x, y = tr.section(net, 0), ref.section(net, 0)
+                worst = max(worst, float((x - y).abs().max()))
+                mine = x.clone()
+                dist.broadcast(mine, src=0)
+                assert torch.equal(mine, x), f"rank {rank}: replicas diverged ({net}, step {it})"
+        tr.losses()
+        t = torch.tensor([worst], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            print(json.dumps({"check": "fused peer-memory all-reduce + Adam vs NCCL all-reduce + Adam, 3 steps",
+                              "fused_path": bool(tr.peer_fused), "fallback_reason": tr._peer_error,
+                              "max_abs_weight_diff": float(t.item()), "replicas_bit_identical": True, "n_gpus": world}))
+        assert float(t.item()) < 1e-7
+        ref.close()
     for _ in range(a.warmup):
         tr.step(noisy, clean, read_losses=False)
     torch.cuda.synchronize()
@@ -91,7 +119,7 @@ def main():
     if rank == 0:
         gflop = GFLOP_PER_IMAGE_128 * (a.H * a.W / 16384.0)
         ips = world * a.B / (ms * 1e-3)
-        print(json.dumps({"metric": "training images/sec (G+D step, Adam" + (", NCCL grad all-reduce" if world > 1 else "") + ")",
+        print(json.dumps({"metric": "training images/sec (G+D step, Adam" + ((", gradient all-reduce fused into Adam over NVLink peer memory" if tr.peer_fused else ", NCCL grad all-reduce") if world > 1 else "") + ")",
                           "value": ips, "unit": "images/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
                           "ms_per_step": ms, "tflops_per_gpu": a.B * gflop / ms, "gflop_per_image": gflop,
                           "gpu_launches_per_step": launches, "dtype": "bf16 (fp32 accumulate, fp32 master weights)",
