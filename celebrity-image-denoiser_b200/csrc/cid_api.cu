@@ -208,6 +208,12 @@ static int pack_layer(cid_ctx* c, int l) {
                     pk[((tap * 2 + 0) * 64 + co) * 8 + 3 + ci] = v;
                     pk[((tap * 2 + 1) * 64 + co) * 8 + ci] = f32_to_bf16_rne(wf - bf16_to_f32(v));  // w_lo (x_hi)
                 }
+        // the bias as two more K rows of the centre tap: pixel slot 6 is 1.0 (first_conv_umma.cuh)
+        for (int co = 0; co < 64; ++co) {
+            const uint16_t bh = f32_to_bf16_rne(b[co]);
+            pk[((4 * 2 + 0) * 64 + co) * 8 + 6] = bh;
+            pk[((4 * 2 + 1) * 64 + co) * 8 + 6] = f32_to_bf16_rne(b[co] - bf16_to_f32(bh));
+        }
         if (c->w_dev[0]) cudaFree(c->w_dev[0]);
         if (c->bias_dev[0]) cudaFree(c->bias_dev[0]);
         c->w_dev[0] = nullptr;
@@ -410,7 +416,6 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         memset(&fp, 0, sizeof(fp));
         fp.B = nb; fp.H = H; fp.W = W;
         fp.in = io.x; fp.in_h = io.in_h; fp.in_w = io.in_w; fp.pad_l = io.pad_l; fp.pad_t = io.pad_t;
-        fp.bias = c->bias_dev[0];
         fp.out = buf(B_A0);
         fp.tiles_x = (W + 7) / 8;
         fp.tiles_y = (H + 15) / 16;

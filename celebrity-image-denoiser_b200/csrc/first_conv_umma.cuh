@@ -18,8 +18,14 @@
 // the same patch read at start + (dy*10+dx)*16 B, so each input pixel is converted and written
 // to shared memory once per tile (180 writes) instead of 9 times.
 //
+// The bias rides in the MMA too: K slot 6 of every pixel chunk holds 1.0 and the CENTRE tap's weight tile holds
+// bias_hi in slot 6 of K chunk 0 and bias_lo in slot 6 of K chunk 1 (the centre tap reads the output pixel's own
+// chunk, which always lies inside the frame), so the epilogue is ReLU on packed bf16 pairs: one cvt + one max per two
+// outputs instead of bias loads, adds and a min/max/fma per output - the epilogue warps' issue slots were what kept
+// this layer at 44 % of DRAM bandwidth.
+//
 // Warps (288 threads): 0..3 build patches (u8 mode: 3 byte loads + 3 LUT lookups + one 16-B
-// store per pixel); warp 4 owns TMEM and issues 9 MMAs per tile; warps 5..8 run the bias+ReLU
+// store per pixel); warp 4 owns TMEM and issues 9 MMAs per tile; warps 5..8 run the ReLU
 // epilogue (TMEM lane quarter = warp & 3) and store bf16 NHWC.
 #pragma once
 #include <cuda_bf16.h>
@@ -43,7 +49,6 @@ struct FirstParams {
     int in_h, in_w;       // u8 mode: un-padded image size
     int pad_l, pad_t;     // u8 mode: where the image sits inside the padded frame
     const uint4* w_packed;  // kFirstWBytes of bf16 in the shared-memory layout above
-    const float* bias;    // fp32 [64]
     __nv_bfloat16* out;   // NHWC [B,H,W,64]
     int tiles_x, tiles_y, m_tiles;
     float slope;          // negative slope of the activation: 0 = ReLU (generator), 0.2 = the discriminator's LeakyReLU
@@ -212,8 +217,9 @@ first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParam
                         l2 = split_hi_lo(__uint_as_float(rq[j][3 * h + 2]));
                     }
                     // K chunk 0 = [hi0 hi1 hi2 lo0 lo1 lo2 0 0]
+                    // K chunk 0 = [hi0 hi1 hi2 lo0 lo1 lo2 1.0 0]: slot 6 multiplies the bias rows of the centre tap
                     px[h] = make_uint4((l0 & 0xffffu) | (l1 << 16), (l2 & 0xffffu) | (l0 & 0xffff0000u),
-                                       (l1 >> 16) | (l2 & 0xffff0000u), 0u);
+                                       (l1 >> 16) | (l2 & 0xffff0000u), 0x00003f80u);
                 }
                 if (mt + kPF < mt_end) load_raw(rq[j]);
                 mbar_wait(&a_empty[stage], phase ^ 1);
@@ -259,7 +265,7 @@ first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParam
             ++acc_it;
         }
     } else {
-        // ======================= epilogue: bias + ReLU -> bf16 NHWC =======================
+        // ======================= epilogue: (Leaky)ReLU -> bf16 NHWC (the bias came through the MMA) =======================
         const int q = warp & 3;
         const int row = q * 32 + lane;
         const int yl = row >> 3, xl = row & 7;
@@ -279,17 +285,27 @@ first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParam
             if (issuer) bulk_wait_read<kFirstOutBufs - 1>();
             named_bar_sync(1, 128);
             uint8_t* rowp = o_smem + ob * 16384 + row * 128;
+            const bool plain_relu = p.slope == 0.f && p.mask == nullptr;
             for_each_chunk<N / 32>(taddr, [&](int ch, uint32_t (&v)[32]) {
-                const float4* b4 = reinterpret_cast<const float4*>(p.bias + ch * 32);
                 uint32_t pk[16];
+                if (plain_relu) {
+                    // ReLU after rounding == rounding after ReLU: max on packed bf16 pairs
+                    const __nv_bfloat162 zero2 = __float2bfloat162_rn(0.f);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const float4 bb = __ldg(b4 + j);
-                    // max(x,0) + slope * min(x,0): exactly ReLU for slope 0 (+0 + -0 = +0)
-                    const float x0 = __uint_as_float(v[4 * j + 0]) + bb.x, x1 = __uint_as_float(v[4 * j + 1]) + bb.y;
-                    const float x2 = __uint_as_float(v[4 * j + 2]) + bb.z, x3 = __uint_as_float(v[4 * j + 3]) + bb.w;
-                    pk[2 * j + 0] = pack_bf16x2(fmaxf(x0, 0.f) + p.slope * fminf(x0, 0.f), fmaxf(x1, 0.f) + p.slope * fminf(x1, 0.f));
-                    pk[2 * j + 1] = pack_bf16x2(fmaxf(x2, 0.f) + p.slope * fminf(x2, 0.f), fmaxf(x3, 0.f) + p.slope * fminf(x3, 0.f));
+                    for (int j = 0; j < 16; ++j) {
+                        const uint32_t w2 = pack_bf16x2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+                        const __nv_bfloat162 r2 = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&w2), zero2);
+                        pk[j] = *reinterpret_cast<const uint32_t*>(&r2);
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        // max(x,0) + slope * min(x,0): LeakyReLU, exactly ReLU for slope 0 (+0 + -0 = +0)
+                        const float x0 = __uint_as_float(v[4 * j + 0]), x1 = __uint_as_float(v[4 * j + 1]);
+                        const float x2 = __uint_as_float(v[4 * j + 2]), x3 = __uint_as_float(v[4 * j + 3]);
+                        pk[2 * j + 0] = pack_bf16x2(fmaxf(x0, 0.f) + p.slope * fminf(x0, 0.f), fmaxf(x1, 0.f) + p.slope * fminf(x1, 0.f));
+                        pk[2 * j + 1] = pack_bf16x2(fmaxf(x2, 0.f) + p.slope * fminf(x2, 0.f), fmaxf(x3, 0.f) + p.slope * fminf(x3, 0.f));
+                    }
                 }
                 if (p.mask != nullptr) {
                     const int yy = ty * 16 + yl, xx = tx * 8 + xl;

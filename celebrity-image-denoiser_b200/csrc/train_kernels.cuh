@@ -619,7 +619,8 @@ enum RepackMode {
     RP_LAST_DGRAD = 8    // the same operand for the data gradient of a Conv2d(3,64): row tap*3 + ci = w[co][ci][8 - tap]
 };
 
-__device__ __forceinline__ float repack_value(int mode, const float* w, size_t i, int cin, int cout, int npad) {
+__device__ __forceinline__ float repack_value(int mode, const float* w, size_t i, int cin, int cout, int npad,
+                                              const float* aux = nullptr) {
     float val = 0.f;
     switch (mode) {
         case RP_CONV9_FWD: {
@@ -671,7 +672,9 @@ __device__ __forceinline__ float repack_value(int mode, const float* w, size_t i
             const int co = static_cast<int>((i >> 3) & 63);
             const int chunk = static_cast<int>((i >> 9) & 1);
             const int tap = static_cast<int>(i >> 10);
-            if (chunk == 0) {
+            if (e == 6) {  // bias rows of the centre tap (pixel slot 6 = 1.0): hi in chunk 0, lo in chunk 1
+                if (tap == 4 && aux) val = chunk == 0 ? aux[co] : aux[co] - __bfloat162float(__float2bfloat16_rn(aux[co]));
+            } else if (chunk == 0) {
                 if (e < 6) val = w[(co * 3 + (e % 3)) * 9 + tap];
             } else if (e < 3) {
                 const float wf = w[(co * 3 + e) * 9 + tap];
@@ -716,6 +719,7 @@ constexpr int kRepackMaxJobs = 40;
 enum { RP_COPY_F32 = 100 };
 struct RepackJob {
     const float* w;
+    const float* aux;  // RP_FIRST: the layer's bias (folded into the centre tap's K slot 6), else unused
     void* dst;
     int mode, cin, cout, npad;
     unsigned n, start;
@@ -737,7 +741,7 @@ __global__ void __launch_bounds__(256) repack_multi_kernel(const __grid_constant
         static_cast<float*>(J.dst)[i] = J.w[i];
         return;
     }
-    static_cast<__nv_bfloat16*>(J.dst)[i] = __float2bfloat16_rn(repack_value(J.mode, J.w, i, J.cin, J.cout, J.npad));
+    static_cast<__nv_bfloat16*>(J.dst)[i] = __float2bfloat16_rn(repack_value(J.mode, J.w, i, J.cin, J.cout, J.npad, J.aux));
 }
 
 }  // namespace cid

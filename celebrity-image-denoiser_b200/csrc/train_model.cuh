@@ -403,10 +403,10 @@ static int wgrad_edge(cid_train* t, const void* v64, const float* v3, int v3_nch
 struct RepackList {
     RepackJobs jobs;
     RepackList() { jobs.count = 0; jobs.total = 0; }
-    int add(int mode, const float* w, void* dst, int cin, int cout, int npad, size_t n) {
+    int add(int mode, const float* w, void* dst, int cin, int cout, int npad, size_t n, const float* aux = nullptr) {
         CID_REQUIRE(jobs.count < kRepackMaxJobs, "repack: too many jobs");
         RepackJob& J = jobs.job[jobs.count++];
-        J.w = w; J.dst = dst; J.mode = mode; J.cin = cin; J.cout = cout; J.npad = npad;
+        J.w = w; J.aux = aux; J.dst = dst; J.mode = mode; J.cin = cin; J.cout = cout; J.npad = npad;
         J.n = static_cast<unsigned>(n);
         J.start = jobs.total;
         jobs.total += static_cast<unsigned>(n);
@@ -497,7 +497,7 @@ static int train_repack(cid_train* t, int which, cudaStream_t st) {
                 const float* w = train_ptr(t, std::string("generator.") + L.name + ".weight", 0);
                 const float* b = train_ptr(t, std::string("generator.") + L.name + ".bias", 0);
                 if (l == 0) {
-                    if (rl.add(RP_FIRST, w, c->w_dev[0], 3, 64, 64, kFirstWBytes / 2)) return 1;
+                    if (rl.add(RP_FIRST, w, c->w_dev[0], 3, 64, 64, kFirstWBytes / 2, b)) return 1;
                 } else if (l == 11) {
                     if (rl.add(RP_LAST, w, c->w_dev[11], 64, 3, 128, 128 * 64)) return 1;
                 } else if (L.kind == L_CONV) {
@@ -527,7 +527,7 @@ static int train_repack(cid_train* t, int which, cudaStream_t st) {
             const float* b = train_ptr(t, base + ".bias", 0);
             if (rl.add(RP_COPY_F32, b, t->d_bias_pad[l], 0, 0, 0, kDCout[l])) return 1;
             if (l == 0) {
-                if (rl.add(RP_FIRST, w, t->df_w[0], 3, 64, 64, kFirstWBytes / 2)) return 1;
+                if (rl.add(RP_FIRST, w, t->df_w[0], 3, 64, 64, kFirstWBytes / 2, b)) return 1;
                 if (rl.add(RP_LAST_DGRAD, w, t->dd_w[0], 3, 64, 64, 128 * 64)) return 1;
                 continue;
             }
@@ -649,7 +649,6 @@ static int d_forward(const TrainRun& r, const float* img) {
         memset(&fp, 0, sizeof(fp));
         fp.B = B; fp.H = H; fp.W = W;
         fp.in = img;
-        fp.bias = t->d_bias_pad[0];
         fp.out = static_cast<__nv_bfloat16*>(r.tbuf(TB_DA0));
         fp.tiles_x = (W + 7) / 8;
         fp.tiles_y = (H + 15) / 16;
@@ -843,7 +842,6 @@ static int g_backward_layers(const TrainRun& r, const float* noisy) {
         memset(&fp, 0, sizeof(fp));
         fp.B = B; fp.H = H; fp.W = W;
         fp.in = r.tbuf(TB_GZC);
-        fp.bias = t->zero_bias;
         fp.out = static_cast<__nv_bfloat16*>(r.tbuf(TB_DZ10));
         fp.tiles_x = (W + 7) / 8;
         fp.tiles_y = (H + 15) / 16;
