@@ -362,7 +362,9 @@ static int launch_conv(cid_ctx* c, int slot, const CUtensorMap& tmA, const CUten
                        const CUtensorMap& tmO2, ConvParams p, cudaStream_t st) {
     using Cfg = ConvCfg<N, TAPS, S, WRES, EPI, PW, TS, CG>;
     const int budget = c->max_smem - 1024 - 512 - Cfg::O_BYTES;
-    int w_stages = WRES ? 1 : (N == 256 && TS ? 3 : 4);
+    // (transposed conv as a CTA pair: half-size weight stages, so twice as many fit - the layer is bound by weight-tile
+    // latency x stages in flight, not by bytes)
+    int w_stages = WRES ? 1 : (N == 256 && TS ? (CG == 2 && TAPS == 1 ? 6 : 3) : 4);
     const int w_bytes = (WRES ? p.kb_count * TAPS : w_stages) * Cfg::W_BYTES;
     int a_stages = std::min(kMaxStages, (budget - w_bytes) / Cfg::A_BYTES);
     CID_REQUIRE(a_stages >= S + 1, "conv<%d,%d,%d>: shared memory too small (%d stages)", N, TAPS, S, a_stages);
@@ -526,7 +528,11 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         ConvParams p = base(6, 2);
         p.n_tiles = 2;  // 4*128 columns in tiles of 256
         p.out = buf(B_CAT2); p.out_cs = 256; p.out_c0 = 0;
-        if (launch_conv<256, 1, 1, false, EPI_CONVT, 0, TSV(1)>(c, 4, pl->tmA[6], c->tmW[6], pl->tmO[6], pl->tmO[6], p, st)) return 1;
+        if (c->variant & 4096) {  // CTA pair: each CTA streams half of the 256 KB weight matrix per tile pair
+            if (launch_conv<256, 1, 1, false, EPI_CONVT, 0, TSV(1), 2>(c, 20, pl->tmA[6], c->tmWh[6], pl->tmO[6], pl->tmO[6], p, st)) return 1;
+        } else {
+            if (launch_conv<256, 1, 1, false, EPI_CONVT, 0, TSV(1)>(c, 4, pl->tmA[6], c->tmW[6], pl->tmO[6], pl->tmO[6], p, st)) return 1;
+        }
     }
     if (prof_mark(c, st)) return 1;
     {  // L7 upconv2.0 (reads cat2) -> u2a
@@ -553,7 +559,11 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         ConvParams p = base(9, 1);
         p.n_tiles = 1;  // 4*64 columns in one tile of 256
         p.out = buf(B_CAT1); p.out_cs = 128; p.out_c0 = 0;
-        if (launch_conv<256, 1, 1, false, EPI_CONVT, 0, TSV(1)>(c, 4, pl->tmA[9], c->tmW[9], pl->tmO[9], pl->tmO[9], p, st)) return 1;
+        if (c->variant & 8192) {
+            if (launch_conv<256, 1, 1, false, EPI_CONVT, 0, TSV(1), 2>(c, 20, pl->tmA[9], c->tmWh[9], pl->tmO[9], pl->tmO[9], p, st)) return 1;
+        } else {
+            if (launch_conv<256, 1, 1, false, EPI_CONVT, 0, TSV(1)>(c, 4, pl->tmA[9], c->tmW[9], pl->tmO[9], pl->tmO[9], p, st)) return 1;
+        }
     }
     if (prof_mark(c, st)) return 1;
     {  // L10 upconv1.0 (reads cat1) -> u1a
@@ -780,7 +790,8 @@ int cid_set_option(cid_handle h, const char* name, int64_t value) {
         return 0;
     }
     // bit mask of optional CTA-pair (cta_group::2) layers: 2 = down2.2/upconv2.0/upconv2.2, 16 = bottleneck.*,
-    // 32 = down1.2 (down2.0 and upconv1.0 always run as pairs). Default 2: where it measured faster.
+    // 32 = down1.2 (down2.0 and upconv1.0 always run as pairs), 4096 / 8192 = the transposed convs up2 / up1 (pair = half-size
+    // weight stages, twice as many in flight). Default 2 | 32 | 4096: where it measured faster.
     if (!strcmp(name, "variant")) {
         h->variant = static_cast<int>(value);
         return 0;

@@ -177,6 +177,27 @@ __device__ __forceinline__ TileCoord decode_tile(const ConvParams& p, int mt) {
     return decode_tile(p.tiles_x, p.tiles_y, mt);
 }
 
+// Tile cursor for kernels whose CTAs walk a contiguous range of tiles (x fastest): increments instead of divisions.
+struct TileWalk {
+    int tx, ty, b;
+    __device__ TileWalk(int tiles_x, int tiles_y, int mt) {
+        tx = mt % tiles_x;
+        const int r = mt / tiles_x;
+        ty = r % tiles_y;
+        b = r / tiles_y;
+    }
+    __device__ __forceinline__ void next(int tiles_x, int tiles_y) {
+        if (++tx == tiles_x) {
+            tx = 0;
+            if (++ty == tiles_y) {
+                ty = 0;
+                ++b;
+            }
+        }
+    }
+};
+
+
 // Walk an accumulator row in 32-column chunks with the next chunk's tcgen05.ld already in
 // flight while the current one is processed (two register buffers, fully unrolled).
 template <int NCH, class F>

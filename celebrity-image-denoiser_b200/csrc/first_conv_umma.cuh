@@ -70,25 +70,6 @@ __device__ __forceinline__ uint32_t split_hi_lo(float x) {
 }
 
 // tile coordinates of a linear tile index (x fastest, then y, then image), advanced incrementally
-struct TileWalk {
-    int tx, ty, b;
-    __device__ TileWalk(int tiles_x, int tiles_y, int mt) {
-        tx = mt % tiles_x;
-        const int r = mt / tiles_x;
-        ty = r % tiles_y;
-        b = r / tiles_y;
-    }
-    __device__ __forceinline__ void next(int tiles_x, int tiles_y) {
-        if (++tx == tiles_x) {
-            tx = 0;
-            if (++ty == tiles_y) {
-                ty = 0;
-                ++b;
-            }
-        }
-    }
-};
-
 template <bool U8>
 __global__ void __launch_bounds__(kFirstThreads, kFirstCtasPerSm)
 first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParams p) {

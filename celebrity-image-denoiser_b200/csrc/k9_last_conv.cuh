@@ -182,9 +182,9 @@ k9_last_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             named_bar_sync(1, 128);  // every gather is done before the next tile overwrites the buffer
             float t[3] = {a0, a1, a2};
             if constexpr (MODE == L9_TANH_F32 || MODE == L9_TANH_U8) {
-                t[0] = tanhf(a0);
-                t[1] = tanhf(a1);
-                t[2] = tanhf(a2);
+                t[0] = tanh_fast(a0);
+                t[1] = tanh_fast(a1);
+                t[2] = tanh_fast(a2);
             }
             const int y = tc.y0 + yl, x = tc.x0 + xl;
             if (y < p.H && x < p.W) {

@@ -109,6 +109,11 @@ last_conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     pdl_launch_dependents();
+    // Each CTA walks a CONTIGUOUS range of tiles (x fastest): neighbouring tiles share halo rows in L2 and the pixel
+    // warps advance their tile coordinates by increments instead of divisions.
+    const int per_cta = (p.m_tiles + gridDim.x - 1) / gridDim.x;
+    const int mt_begin = min(static_cast<int>(blockIdx.x) * per_cta, p.m_tiles);
+    const int mt_end = min(mt_begin + per_cta, p.m_tiles);
 
     if (warp == 0) {
         // ======================= TMA producer =======================
@@ -117,11 +122,13 @@ last_conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             tma_load_2d(w_smem, &tmW, w_full, 0, 0, kEvictLast);
             pdl_wait();  // the activations are the previous layer's output
             uint32_t stage = 0, phase = 0;
-            for (int mt = blockIdx.x; mt < p.m_tiles; mt += gridDim.x) {
-                const TileCoord tc = decode_tile(p.tiles_x, p.tiles_y, mt);
+            TileWalk tw(p.tiles_x, p.tiles_y, mt_begin);
+            for (int mt = mt_begin; mt < mt_end; ++mt) {
+                const int tx0 = tw.tx * 8, ty0 = tw.ty * 16, tb = tw.b;
+                tw.next(p.tiles_x, p.tiles_y);
                 mbar_wait(&a_empty[stage], phase ^ 1);
                 mbar_arrive_expect_tx(&a_full[stage], kLastPatchTx);
-                tma_load_4d(a_smem + stage * kLastStageBytes, &tmA, &a_full[stage], 0, tc.x0 - 1, tc.y0 - 1, tc.b,
+                tma_load_4d(a_smem + stage * kLastStageBytes, &tmA, &a_full[stage], 0, tx0 - 1, ty0 - 1, tb,
                             kEvictFirst);
                 if (++stage == static_cast<uint32_t>(p.stages)) {
                     stage = 0;
@@ -136,7 +143,7 @@ last_conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         const uint32_t a_lo0 = umma_desc_lo(smem_u32(a_smem));
         uint32_t stage = 0, phase = 0, acc_it = 0;
         mbar_wait(w_full, 0);
-        for (int mt = blockIdx.x; mt < p.m_tiles; mt += gridDim.x) {
+        for (int mt = mt_begin; mt < mt_end; ++mt) {
             const uint32_t buf = acc_it & 1;
             mbar_wait(&acc_empty[buf], ((acc_it >> 1) & 1) ^ 1);
             mbar_wait(&a_full[stage], phase);
@@ -164,7 +171,7 @@ last_conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         const uint32_t g = warp == 4 ? 0u : 1u;
         const bool row_used = lane < 27;
         uint32_t it = 0;
-        for (int mt = blockIdx.x; mt < p.m_tiles; mt += gridDim.x, ++it) {
+        for (int mt = mt_begin; mt < mt_end; ++mt, ++it) {
             if ((it & 1) != g) continue;
             const uint32_t k = it >> 1, sb = k & 1;
             mbar_wait(&s_empty[g * 2 + sb], ((k >> 1) & 1) ^ 1);
@@ -194,9 +201,11 @@ last_conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         const int yl = et >> 3, xl = et & 7;
         const float b0 = __ldg(p.bias), b1 = __ldg(p.bias + 1), b2 = __ldg(p.bias + 2);
         uint32_t it = 0;
-        for (int mt = blockIdx.x; mt < p.m_tiles; mt += gridDim.x, ++it) {
+        TileWalk tw(p.tiles_x, p.tiles_y, mt_begin);
+        for (int mt = mt_begin; mt < mt_end; ++mt, ++it) {
+            struct { int x0, y0, b; } tc = {tw.tx * 8, tw.ty * 16, tw.b};
+            tw.next(p.tiles_x, p.tiles_y);
             if ((it & 1) != g) continue;
-            const TileCoord tc = decode_tile(p.tiles_x, p.tiles_y, mt);
             const uint32_t k = it >> 1, sb = k & 1;
             mbar_wait(&s_full[g * 2 + sb], (k >> 1) & 1);
             const float* S = s_smem + (g * 2 + sb) * (27 * kLastSP);
@@ -213,8 +222,8 @@ last_conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                 }
             __syncwarp();
             if (lane == 0) mbar_arrive(&s_empty[g * 2 + sb]);
-            const float t[3] = {EPI == EPI_LINEAR_F32_NHWC ? a0 : tanhf(a0), EPI == EPI_LINEAR_F32_NHWC ? a1 : tanhf(a1),
-                                EPI == EPI_LINEAR_F32_NHWC ? a2 : tanhf(a2)};
+            const float t[3] = {EPI == EPI_LINEAR_F32_NHWC ? a0 : tanh_fast(a0), EPI == EPI_LINEAR_F32_NHWC ? a1 : tanh_fast(a1),
+                                EPI == EPI_LINEAR_F32_NHWC ? a2 : tanh_fast(a2)};
             const int y = tc.y0 + yl, x = tc.x0 + xl;
             if (y < p.H && x < p.W) {
                 if constexpr (EPI == EPI_TANH_F32) {

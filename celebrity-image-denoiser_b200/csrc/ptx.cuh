@@ -360,6 +360,11 @@ __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepc
 // ----------------------------------------------------------------------------------------------
 // misc
 // ----------------------------------------------------------------------------------------------
+// tanh(x) = 1 - 2 / (exp(2x) + 1) on the SFU (ex2.approx + rcp.approx, no branches): absolute error < 3e-7, exact
+// saturation at +-1 (exp -> inf / 0). libdevice's tanhf costs ~25 instructions with two branches per call, which the
+// last conv's one-pixel-per-thread epilogue cannot hide.
+__device__ __forceinline__ float tanh_fast(float x) { return 1.f - __fdividef(2.f, __expf(2.f * x) + 1.f); }
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     uint32_t r;
     asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
