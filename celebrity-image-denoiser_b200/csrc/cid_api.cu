@@ -559,8 +559,8 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         ConvParams p = base(9, 1);
         p.n_tiles = 1;  // 4*64 columns in one tile of 256
         p.out = buf(B_CAT1); p.out_cs = 128; p.out_c0 = 0;
-        if (c->variant & 8192) {
-            if (launch_conv<256, 1, 1, false, EPI_CONVT, 0, TSV(1), 2>(c, 20, pl->tmA[9], c->tmWh[9], pl->tmO[9], pl->tmO[9], p, st)) return 1;
+        if (c->variant & 8192) {  // the whole 128 x 256 weight matrix (64 KB) stays in shared memory
+            if (launch_conv<256, 1, 1, true, EPI_CONVT, 0, TSV(1)>(c, 21, pl->tmA[9], c->tmW[9], pl->tmO[9], pl->tmO[9], p, st)) return 1;
         } else {
             if (launch_conv<256, 1, 1, false, EPI_CONVT, 0, TSV(1)>(c, 4, pl->tmA[9], c->tmW[9], pl->tmO[9], pl->tmO[9], p, st)) return 1;
         }
@@ -790,8 +790,9 @@ int cid_set_option(cid_handle h, const char* name, int64_t value) {
         return 0;
     }
     // bit mask of optional CTA-pair (cta_group::2) layers: 2 = down2.2/upconv2.0/upconv2.2, 16 = bottleneck.*,
-    // 32 = down1.2 (down2.0 and upconv1.0 always run as pairs), 4096 / 8192 = the transposed convs up2 / up1 (pair = half-size
-    // weight stages, twice as many in flight). Default 2 | 32 | 4096: where it measured faster.
+    // 32 = down1.2 (down2.0 and upconv1.0 always run as pairs), 4096 = the transposed conv up2 as a pair (half-size weight
+    // stages, twice as many in flight), 8192 = up1 with its 64 KB of weights resident in shared memory. Default
+    // 2 | 32 | 4096 | 8192: where it measured faster.
     if (!strcmp(name, "variant")) {
         h->variant = static_cast<int>(value);
         return 0;

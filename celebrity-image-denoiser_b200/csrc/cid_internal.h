@@ -82,7 +82,7 @@ struct cid_ctx {
     std::map<uint64_t, void*> resize_coeffs;  // (in_size,out_size) -> device coefficient block
     // per-layer timing ("profile" option): 13 events bracket the 12 layers of every pass
     int debug_flags = 0;
-    int variant = 34 | 4096;                // layers run as CTA pairs ("variant" option, see cid_set_option)
+    int variant = 34 | 4096 | 8192;                // layers run as CTA pairs ("variant" option, see cid_set_option)
     bool first_tc = true;             // layer 0 on tensor cores (false: CUDA-core direct conv)
     bool patch = true;                // 3x3 layers load one halo patch per K block instead of 3 boxes
     bool pdl = true;                  // programmatic dependent launch between layers ("pdl" option)
