@@ -357,6 +357,26 @@ static cudaError_t launch_ex(const cid_ctx* c, void (*kern)(KArgs...), int grid,
     return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
 }
 
+// The small kernels of the training step (reductions, BatchNorm, Adam, re-pack ...) launch with the same
+// programmatic-dependent-launch attribute: each begins with griddepcontrol.launch_dependents + griddepcontrol.wait, so the
+// launch latency and set-up of the NEXT kernel overlap this one's tail while the memory ordering stays that of the stream.
+// Launch errors surface through the caller's cudaGetLastError().
+template <class... KArgs, class... Args>
+static void launch_k(bool pdl, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    (void)cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
+
 template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0, int TS = 0, int CG = 1>
 static int launch_conv(cid_ctx* c, int slot, const CUtensorMap& tmA, const CUtensorMap& tmW, const CUtensorMap& tmO,
                        const CUtensorMap& tmO2, ConvParams p, cudaStream_t st) {
@@ -1113,7 +1133,7 @@ int cid_train_g_backward(cid_train_handle t, const float* noisy, const float* cl
         p.loss_sum = t->dsc + DS_LOSS + 3;
         p.bias_grad = train_ptr(t, "generator.upconv1.2.bias", 1);
         p.inv_n = 1.f / (static_cast<float>(B) * 3.f * H * W);
-        gloss_kernel<<<static_cast<unsigned>((r.pixels(0) + 255) / 256), 256, 0, st>>>(p);
+        launch_k(t->g->pdl, gloss_kernel, static_cast<unsigned>((r.pixels(0) + 255) / 256), 256, 0, st, p);
         CID_CHECK_CUDA(cudaGetLastError());
         t->launches++;
     }
@@ -1143,7 +1163,7 @@ int cid_train_adam(cid_train_handle t, int which, float lr, float beta1, float b
         adam_allreduce_kernel<<<kPeerBlocks, 256, 0, st>>>(t->state + off, t->state + 2 * P + off, t->state + 3 * P + off, n, ps,
                                                            ++t->peer_epoch, t->peer_err, lr, beta1, beta2, eps, bc1, bc2);
     } else {
-        adam_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(t->state + off, t->state + P + off, t->state + 2 * P + off,
+        launch_k(t->g->pdl, adam_kernel, static_cast<unsigned>((n + 255) / 256), 256, 0, st, t->state + off, t->state + P + off, t->state + 2 * P + off,
                                                                             t->state + 3 * P + off, n, lr, beta1, beta2, eps, bc1, bc2);
     }
     CID_CHECK_CUDA(cudaGetLastError());

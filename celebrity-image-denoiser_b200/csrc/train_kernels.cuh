@@ -62,6 +62,9 @@ __device__ __forceinline__ float block_sum(float v, float* red /* >= 32 floats *
 // ---------------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) im2col3_kernel(const float* v3, int v3_nchw, int sign, __nv_bfloat16* u, int B, int H,
                                                       int W) {
+    // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
+    pdl_launch_dependents();
+    pdl_wait();
     const size_t total = static_cast<size_t>(B) * H * W;
     const size_t pix = static_cast<size_t>(blockIdx.x) * 128 + threadIdx.x;
     if (pix >= total) return;
@@ -93,6 +96,9 @@ __global__ void __launch_bounds__(128) im2col3_kernel(const float* v3, int v3_nc
 
 // scratch[c64][j] (64 x 64 fp32, j = ci*9 + tap < 27) -> out[(c64*3 + ci)*9 + tap] (mode 0) / out[(ci*64 + c64)*9 + tap]
 __global__ void wg27_scatter_kernel(const float* scratch, float* out, int out_mode) {
+    // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
+    pdl_launch_dependents();
+    pdl_wait();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= 64 * 27) return;
     const int c = i / 27, j = i % 27, ci = j / 9, tap = j % 9;
@@ -118,6 +124,9 @@ struct GLossParams {
 };
 
 __global__ void __launch_bounds__(256) gloss_kernel(const GLossParams p) {
+    // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float red[32];
     const size_t total = static_cast<size_t>(p.B) * p.H * p.W;
     const size_t pix = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
@@ -153,6 +162,9 @@ __global__ void __launch_bounds__(256) gloss_kernel(const GLossParams p) {
 template <bool SQ, typename ZT>
 __global__ void __launch_bounds__(256) colsum_kernel(const ZT* v, size_t P, int cs, int c0, int C, float* out,
                                                      double* dsum, double* dsq, int ppb) {
+    // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
+    pdl_launch_dependents();
+    pdl_wait();
     // thread = (8-channel chunk, pixel row group); C/8 chunks (8, 16 or 32) -> 32, 16 or 8 pixels per iteration
     __shared__ float red[256 * 8];
     __shared__ float red2[SQ ? 256 * 8 : 8];
@@ -203,6 +215,9 @@ __global__ void __launch_bounds__(256) colsum_kernel(const ZT* v, size_t P, int 
 // One thread = one 2x2 window x 8 channels: 4 e + 4 gskip + 1 gpool loads, 4 stores (H, W even).
 __global__ void __launch_bounds__(256) poolbwd_kernel(const __nv_bfloat16* e, const __nv_bfloat16* gskip, int cs, int c0,
                                                       const __nv_bfloat16* gpool, __nv_bfloat16* dz, int B, int H, int W, int C) {
+    // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
+    pdl_launch_dependents();
+    pdl_wait();
     const int chunks = C >> 3;
     const int Hp = H >> 1, Wp = W >> 1;
     const size_t total = static_cast<size_t>(B) * Hp * Wp * chunks;
@@ -260,6 +275,9 @@ __global__ void __launch_bounds__(256) poolbwd_kernel(const __nv_bfloat16* e, co
 __global__ void bn_finalize_kernel(const double* dsum, const double* dsq, double n, int C, float eps, float momentum,
                                    float* stats, float* running_mean, float* running_var, float* nbt, const float* gamma,
                                    const float* beta, float* tab) {
+    // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
+    pdl_launch_dependents();
+    pdl_wait();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     const double mean = dsum[c] / n;
@@ -281,6 +299,9 @@ constexpr int kBnIter = 8;  // items (8 channels of one pixel) per thread of the
 template <typename ZT>
 __global__ void __launch_bounds__(256) bn_apply_kernel(const ZT* z, __nv_bfloat16* a, size_t P, int C, const float* tab,
                                                        float slope) {
+    // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
+    pdl_launch_dependents();
+    pdl_wait();
     // 256 is a multiple of C/8: a thread keeps the same 8 channels over its items, their table entries in registers
     const int chunks = C >> 3;
     const int c8 = static_cast<int>(threadIdx.x % chunks) * 8;
@@ -310,6 +331,9 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const ZT* z, const _
                                                             const float* dpool, size_t P, size_t hw, int C,
                                                             const float* stats, const float* gamma, const float* beta,
                                                             float slope, double* sums, int ppb) {
+    // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float red[256 * 8];
     __shared__ float red2[256 * 8];
     const int chunks = C >> 3, rpi = 256 / chunks;
@@ -366,6 +390,9 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const ZT* z, const _
 // btab[c] = {a2, b2, k0, c1, c2}; optionally the gradients of gamma / beta: += {sum dY xhat, sum dY}
 __global__ void bn_bwd_finalize_kernel(const double* sums, int C, double n, const float* stats, const float* gamma,
                                        const float* beta, float* btab, float* ggamma, float* gbeta) {
+    // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
+    pdl_launch_dependents();
+    pdl_wait();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     const float mean = stats[2 * c], istd = stats[2 * c + 1], ga = gamma[c];
@@ -386,6 +413,9 @@ template <typename ZT>
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const ZT* z, const __nv_bfloat16* da,
                                                            const float* dpool, __nv_bfloat16* dz, size_t P, size_t hw,
                                                            int C, float slope, const float* btab) {
+    // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
+    pdl_launch_dependents();
+    pdl_wait();
     const int chunks = C >> 3;
     const int c8 = static_cast<int>(threadIdx.x % chunks) * 8;
     float t0[8], t1[8], t2[8], t3[8], t4[8];
@@ -425,6 +455,9 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const ZT* z, const __
 // pooled[b][c] = mean over hw of a[b][.][c];  grid = B, block = C
 // (pooled must be zeroed first: grid.y pixel slices accumulate with atomics)
 __global__ void avgpool_kernel(const __nv_bfloat16* a, float* pooled, int hw, int C) {
+    // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
+    pdl_launch_dependents();
+    pdl_wait();
     const int b = blockIdx.x, c = threadIdx.x;
     const int per = (hw + gridDim.y - 1) / gridDim.y;
     const int i0 = blockIdx.y * per, i1 = min(hw, i0 + per);
@@ -440,6 +473,9 @@ __global__ void avgpool_kernel(const __nv_bfloat16* a, float* pooled, int hw, in
 __global__ void __launch_bounds__(1024) dhead_kernel(const float* pooled, const float* w, const float* bias, int B, int hw,
                                                      float target, float scale, double* loss_sum, float* dpool, float* gw,
                                                      float* gb, float* probs, int with_param_grads) {
+    // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
+    pdl_launch_dependents();
+    pdl_wait();
     extern __shared__ float dl[];  // [B]
     __shared__ float red[32];
     __shared__ float gpart[8][128];
@@ -490,6 +526,9 @@ __global__ void __launch_bounds__(1024) dhead_kernel(const float* pooled, const 
 // ---------------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) adam_kernel(float* w, const float* g, float* m, float* v, size_t n, float lr,
                                                    float b1, float b2, float eps, float bc1, float bc2_sqrt) {
+    // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
+    pdl_launch_dependents();
+    pdl_wait();
     const size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
     if (i >= n) return;
     const float gi = g[i];
@@ -731,6 +770,9 @@ struct RepackJobs {
 };
 
 __global__ void __launch_bounds__(256) repack_multi_kernel(const __grid_constant__ RepackJobs jobs) {
+    // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
+    pdl_launch_dependents();
+    pdl_wait();
     const unsigned gi = blockIdx.x * 256u + threadIdx.x;
     if (gi >= jobs.total) return;
     int j = 0;

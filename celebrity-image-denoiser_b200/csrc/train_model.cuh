@@ -288,7 +288,7 @@ static int launch_wgrad(cid_train* t, const CUtensorMap& tmA, const CUtensorMap&
         cfg.numAttrs = 1;
         CID_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, p));
     } else {
-        kern<<<grid, kWgThreads, smem, st>>>(tmA, tmB, p);
+        launch_k(t->g->pdl, kern, grid, kWgThreads, smem, st, tmA, tmB, p);
     }
     CID_CHECK_CUDA(cudaGetLastError());
     t->launches++;
@@ -377,7 +377,7 @@ static int reduce_ppb(const cid_train* t, size_t P) {
 
 static int colsum(cid_train* t, const void* v, size_t P, int cs, int c0, int C, float* out, cudaStream_t st) {
     const int ppb = reduce_ppb(t, P);
-    colsum_kernel<false, __nv_bfloat16><<<static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, st>>>(
+    launch_k(t->g->pdl, colsum_kernel<false, __nv_bfloat16>, static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, st, 
         static_cast<const __nv_bfloat16*>(v), P, cs, c0, C, out, nullptr, nullptr, ppb);
     CID_CHECK_CUDA(cudaGetLastError());
     t->launches++;
@@ -388,12 +388,12 @@ static int colsum(cid_train* t, const void* v, size_t P, int cs, int c0, int C, 
 static int wgrad_edge(cid_train* t, const void* v64, const float* v3, int v3_nchw, int sign, float* out, int out_mode,
                       void* ubuf, int B, int H, int W, cudaStream_t st, float* bias_out = nullptr) {
     const size_t P = static_cast<size_t>(B) * H * W;
-    im2col3_kernel<<<static_cast<unsigned>((P + 127) / 128), 128, 0, st>>>(v3, v3_nchw, sign, static_cast<__nv_bfloat16*>(ubuf), B, H, W);
+    launch_k(t->g->pdl, im2col3_kernel, static_cast<unsigned>((P + 127) / 128), 128, 0, st, v3, v3_nchw, sign, static_cast<__nv_bfloat16*>(ubuf), B, H, W);
     CID_CHECK_CUDA(cudaGetLastError());
     float* scratch = t->fsc + FS_WG27;
     CID_CHECK_CUDA(cudaMemsetAsync(scratch, 0, 4096 * 4, st));
     if (wgrad(t, 3, v64, 64, 64, ubuf, 64, 64, B, H, W, scratch, st, bias_out)) return 1;
-    wg27_scatter_kernel<<<(64 * 27 + 255) / 256, 256, 0, st>>>(scratch, out, out_mode);
+    launch_k(t->g->pdl, wg27_scatter_kernel, (64 * 27 + 255) / 256, 256, 0, st, scratch, out, out_mode);
     CID_CHECK_CUDA(cudaGetLastError());
     t->launches += 2;
     return 0;
@@ -414,7 +414,7 @@ struct RepackList {
     }
     int launch(cid_train* t, cudaStream_t st) {
         if (!jobs.count) return 0;
-        repack_multi_kernel<<<(jobs.total + 255) / 256, 256, 0, st>>>(jobs);
+        launch_k(t->g->pdl, repack_multi_kernel, (jobs.total + 255) / 256, 256, 0, st, jobs);
         CID_CHECK_CUDA(cudaGetLastError());
         t->launches++;
         return 0;
@@ -627,12 +627,12 @@ static int bn_forward(const TrainRun& r, int l, const void* z, void* a, int lv) 
     float* stats = t->fsc + FS_STATS + (l - 1) * 256;
     const std::string bn = "discriminator.model." + std::to_string(kDBnIdx[l]);
     float* tab = t->fsc + FS_TAB + (l - 1) * 256;
-    bn_finalize_kernel<<<1, 128, 0, r.st>>>(sums, sums + 128, static_cast<double>(P), C, 1e-5f, 0.1f, stats,
+    launch_k(t->g->pdl, bn_finalize_kernel, 1, 128, 0, r.st, sums, sums + 128, static_cast<double>(P), C, 1e-5f, 0.1f, stats,
                                             train_ptr(t, bn + ".running_mean", 0), train_ptr(t, bn + ".running_var", 0),
                                             train_ptr(t, bn + ".num_batches_tracked", 0), train_ptr(t, bn + ".weight", 0),
                                             train_ptr(t, bn + ".bias", 0), tab);
     const size_t n8 = P * C / 8;
-    bn_apply_kernel<float><<<static_cast<unsigned>((n8 + 256 * kBnIter - 1) / (256 * kBnIter)), 256, 0, r.st>>>(
+    launch_k(t->g->pdl, bn_apply_kernel<float>, static_cast<unsigned>((n8 + 256 * kBnIter - 1) / (256 * kBnIter)), 256, 0, r.st, 
         static_cast<const float*>(z), static_cast<__nv_bfloat16*>(a), P, C, tab, 0.2f);
     CID_CHECK_CUDA(cudaGetLastError());
     t->launches += 2;
@@ -701,7 +701,7 @@ static int d_forward(const TrainRun& r, const float* img) {
     }
     if (bn_forward(r, 3, r.tbuf(TB_DZ3D), r.tbuf(TB_DA3), 2)) return 1;
     CID_CHECK_CUDA(cudaMemsetAsync(t->fsc + FS_POOLED, 0, static_cast<size_t>(B) * 128 * 4, r.st));
-    avgpool_kernel<<<dim3(B, 16), 128, 0, r.st>>>(static_cast<const __nv_bfloat16*>(r.tbuf(TB_DA3)), t->fsc + FS_POOLED,
+    launch_k(t->g->pdl, avgpool_kernel, dim3(B, 16), 128, 0, r.st, static_cast<const __nv_bfloat16*>(r.tbuf(TB_DA3)), t->fsc + FS_POOLED,
                                                   (H >> 2) * (W >> 2), 128);
     CID_CHECK_CUDA(cudaGetLastError());
     t->launches++;
@@ -721,15 +721,15 @@ static int bn_backward(const TrainRun& r, int l, const void* z, const void* da, 
     const float* beta = train_ptr(t, bn + ".bias", 0);
     CID_CHECK_CUDA(cudaMemsetAsync(sums, 0, 256 * 8, r.st));
     const int ppb = reduce_ppb(t, P);
-    bn_bwd_reduce_kernel<float><<<static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, r.st>>>(
+    launch_k(t->g->pdl, bn_bwd_reduce_kernel<float>, static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, r.st, 
         static_cast<const float*>(z), static_cast<const __nv_bfloat16*>(da), t->fsc + FS_DPOOL, P, hw, C, stats, gamma,
         beta, 0.2f, sums, ppb);
     float* btab = t->fsc + FS_BTAB + (l - 1) * 640;
-    bn_bwd_finalize_kernel<<<1, 128, 0, r.st>>>(sums, C, static_cast<double>(P), stats, gamma, beta, btab,
+    launch_k(t->g->pdl, bn_bwd_finalize_kernel, 1, 128, 0, r.st, sums, C, static_cast<double>(P), stats, gamma, beta, btab,
                                                 param_grads ? train_ptr(t, bn + ".weight", 1) : nullptr,
                                                 param_grads ? train_ptr(t, bn + ".bias", 1) : nullptr);
     const size_t n8 = P * C / 8;
-    bn_bwd_apply_kernel<float><<<static_cast<unsigned>((n8 + 256 * kBnIter - 1) / (256 * kBnIter)), 256, 0, r.st>>>(
+    launch_k(t->g->pdl, bn_bwd_apply_kernel<float>, static_cast<unsigned>((n8 + 256 * kBnIter - 1) / (256 * kBnIter)), 256, 0, r.st, 
         static_cast<const float*>(z), static_cast<const __nv_bfloat16*>(da), t->fsc + FS_DPOOL,
         static_cast<__nv_bfloat16*>(dz), P, hw, C, 0.2f, btab);
     t->launches += 3;
@@ -743,7 +743,7 @@ static int d_backward(const TrainRun& r, const float* img, float target, float s
                       bool want_gx) {
     cid_train* t = r.t;
     const int B = r.B, H = r.H, W = r.W;
-    dhead_kernel<<<1, 1024, B * sizeof(float), r.st>>>(
+    launch_k(t->g->pdl, dhead_kernel, 1, 1024, B * sizeof(float), r.st, 
         t->fsc + FS_POOLED, train_ptr(t, "discriminator.model.12.weight", 0), train_ptr(t, "discriminator.model.12.bias", 0), B,
         (H >> 2) * (W >> 2), target, scale, t->dsc + DS_LOSS + loss_slot, t->fsc + FS_DPOOL,
         train_ptr(t, "discriminator.model.12.weight", 1), train_ptr(t, "discriminator.model.12.bias", 1), t->fsc + FS_PROBS,
@@ -826,7 +826,7 @@ static int g_backward_layers(const TrainRun& r, const float* noisy) {
     auto gb = [&](int l) { return train_ptr(t, std::string("generator.") + kLayers[l].name + ".bias", 1); };
     auto pool_bwd = [&](int cat, int C, int lv, int gcat, int gpool, int dz) {
         const size_t total = r.pixels(lv) / 4 * (C / 8);  // one thread per 2x2 window x 8 channels
-        poolbwd_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, r.st>>>(
+        launch_k(t->g->pdl, poolbwd_kernel, static_cast<unsigned>((total + 255) / 256), 256, 0, r.st, 
             static_cast<const __nv_bfloat16*>(r.gbuf(cat)), static_cast<const __nv_bfloat16*>(r.tbuf(gcat)), 2 * C, C,
             static_cast<const __nv_bfloat16*>(r.tbuf(gpool)), static_cast<__nv_bfloat16*>(r.tbuf(dz)), B, H >> lv, W >> lv, C);
         t->launches++;

@@ -143,6 +143,7 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_launch_dependents();  // the next kernel may begin its set-up; it orders itself with griddepcontrol.wait
 
     if (warp == 0) {
         if (lane == 0 && has_work) {
