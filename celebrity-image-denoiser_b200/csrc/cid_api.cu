@@ -1084,6 +1084,7 @@ int cid_train_d_backward(cid_train_handle t, const float* noisy, const float* cl
     TrainRun r;
     if (train_make_run(t, B, H, W, ws, ws_bytes, st, &r)) return 1;
     t->B = B; t->H = H; t->W = W; t->ws = ws;
+    t->u_upper_zeroed = false;
     CID_CHECK_CUDA(cudaMemsetAsync(t->state + train_P(t) + t->n_g, 0, t->n_d * 4, st));
     CID_CHECK_CUDA(cudaMemsetAsync(t->dsc + DS_LOSS, 0, 2 * 8, st));
     // denoised = G(noisy)  (training.py:411)

@@ -60,8 +60,9 @@ __device__ __forceinline__ float block_sum(float v, float* red /* >= 32 floats *
 // 64-channel bf16 NHWC tensor (27 real channels, the rest zero), so that R = V64^T U is ONE plain weight-gradient GEMM of
 // wgrad_umma.cuh (T = 1, no halo); wg27_scatter_kernel then adds the 64 x 27 result into the gradient tensor.
 // ---------------------------------------------------------------------------------------------------------------------
+// zero_upper: also write the 32 always-zero upper channels (needed once per workspace use, see wgrad_edge).
 __global__ void __launch_bounds__(128) im2col3_kernel(const float* v3, int v3_nchw, int sign, __nv_bfloat16* u, int B, int H,
-                                                      int W) {
+                                                      int W, int zero_upper) {
     // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
     pdl_launch_dependents();
     pdl_wait();
@@ -90,8 +91,10 @@ __global__ void __launch_bounds__(128) im2col3_kernel(const float* v3, int v3_nc
     for (int j = 0; j < 4; ++j)
         st_global_v4(dst + j * 8, pack_bf16x2(f[8 * j], f[8 * j + 1]), pack_bf16x2(f[8 * j + 2], f[8 * j + 3]),
                      pack_bf16x2(f[8 * j + 4], f[8 * j + 5]), pack_bf16x2(f[8 * j + 6], f[8 * j + 7]));
+    if (zero_upper) {
 #pragma unroll
-    for (int j = 4; j < 8; ++j) st_global_v4(dst + j * 8, 0u, 0u, 0u, 0u);
+        for (int j = 4; j < 8; ++j) st_global_v4(dst + j * 8, 0u, 0u, 0u, 0u);
+    }
 }
 
 // scratch[c64][j] (64 x 64 fp32, j = ci*9 + tap < 27) -> out[(c64*3 + ci)*9 + tap] (mode 0) / out[(ci*64 + c64)*9 + tap]

@@ -72,6 +72,7 @@ struct cid_train {
     float* fsc = nullptr;             // float scratch: BN stats, pooled, dpool, probs
     std::map<std::string, CUtensorMap> maps;
     int64_t step_g = 0, step_d = 0;
+    bool u_upper_zeroed = false;      // the im2col buffer's zero half has been written in this iteration (reset by d_backward)
     // data-parallel peers (cid_train_set_peers): symmetric state / flag buffers of every rank, mapped into this process
     int peer_world = 0, peer_rank = 0, peer_epoch = 0;
     const float* peer_state[8] = {nullptr};
@@ -388,7 +389,8 @@ static int colsum(cid_train* t, const void* v, size_t P, int cs, int c0, int C, 
 static int wgrad_edge(cid_train* t, const void* v64, const float* v3, int v3_nchw, int sign, float* out, int out_mode,
                       void* ubuf, int B, int H, int W, cudaStream_t st, float* bias_out = nullptr) {
     const size_t P = static_cast<size_t>(B) * H * W;
-    launch_k(t->g->pdl, im2col3_kernel, static_cast<unsigned>((P + 127) / 128), 128, 0, st, v3, v3_nchw, sign, static_cast<__nv_bfloat16*>(ubuf), B, H, W);
+    launch_k(t->g->pdl, im2col3_kernel, static_cast<unsigned>((P + 127) / 128), 128, 0, st, v3, v3_nchw, sign, static_cast<__nv_bfloat16*>(ubuf), B, H, W, t->u_upper_zeroed ? 0 : 1);
+    t->u_upper_zeroed = true;  // channels 32..63 of U stay zero for the rest of this iteration (4 launches share the buffer)
     CID_CHECK_CUDA(cudaGetLastError());
     float* scratch = t->fsc + FS_WG27;
     CID_CHECK_CUDA(cudaMemsetAsync(scratch, 0, 4096 * 4, st));
