@@ -8,11 +8,21 @@ One "step" = one pass of the hot path over one batch of synthetic noisy faces (B
 configs[1]: batch 256 of 128x128 RGB per GPU, random-init generator weights with the reference's
 state_dict layout, bf16 tensor-core arithmetic). Prints ONE JSON line (rank 0).
 
-  value      images/s with the uint8 inputs already resident in HBM (cid_forward_u8_nhwc)
+  value      images/s with the uint8 inputs already resident in HBM (cid_forward_u8_nhwc), timed with
+             the per-layer profiling events OFF (the configuration a user runs: the layers chain
+             through programmatic dependent launch)
   e2e        images/s through the public API with HOST buffers: pinned uint8 in -> H2D ->
-             generator -> D2H -> pinned uint8 out, all inside the timed region
+             generator -> D2H -> pinned uint8 out, all inside the timed region (three-stage
+             pipeline); e2e.breakdown times the copies alone and the kernels alone
   roofline   dominant kernel (the tcgen05 conv of the slowest layer): algorithmic FLOPs / CUDA-event
-             time measured live in this run (per-layer events recorded by the library)
+             time measured live in a separate profiled pass (per-layer events recorded by the library);
+             traffic = dram bytes of that kernel from the newest profiles/r*_ncu_traffic.json
+  sustained  the headline loop repeated for >= 3 s with its own clock samples
+  latency    BASELINE configs[3]: batch 1 and 32 at 128^2 / 256^2 / 512^2 (the upload route's shape)
+  strong_2048  BASELINE configs[2]: 2048 images split contiguously over the N ranks
+  train      BASELINE configs[4]: one G+D+Adam iteration at batch 64 per GPU (gradient all-reduce
+             fused into Adam over NVLink peer memory, or NCCL) through cid_train_*
+  membound   achieved HBM GB/s of the pre-processing kernels (noiser, resize, normalise)
   cpu_baseline  the oracle port of the reference's PyTorch CPU path on this box's host cores
                 (rank 0, N=1 only, bounded sample)
 
@@ -23,6 +33,7 @@ travel to the GPU box) on the same metric/config.
 from __future__ import annotations
 
 import argparse
+import hashlib
 import json
 import os
 import statistics
@@ -44,16 +55,9 @@ LAYER_FLOP_PER_PIXEL = {
     "upconv2.0": 2 * 128 * 2304 / 4, "upconv2.2": 2 * 128 * 1152 / 4, "up1": 2 * 256 * 128 / 4,
     "upconv1.0": 2 * 64 * 1152, "upconv1.2": 2 * 3 * 576,
 }
-
-
-# dram__bytes_read.sum + dram__bytes_write.sum per launch at batch 256 of 128x128, from the committed
-# `ncu --set full` capture profiles/r01i_ncu_full_batch256.md (MB); scaled linearly for other batches/sizes.
-NCU_TRAFFIC_MB_B256_128 = {
-    "down1.0": 13.41 + 476.60, "down1.2": 537.07 + 616.13, "down2.0": 134.45 + 208.42, "down2.2": 268.86 + 284.56,
-    "bottleneck.0": 67.77 + 76.91, "bottleneck.2": 135.45 + 89.74, "up2": 134.51 + 210.47,
-    "upconv2.0": 537.52 + 238.86, "upconv2.2": 268.82 + 223.15, "up1": 268.53 + 478.73,
-    "upconv1.0": 1074.0 + 506.96, "upconv1.2": 536.94 + 8.01,
-}
+# conv-only FLOPs (2*M*N*K) of one training iteration per 128x128 image: G fwd 11.52 + G bwd 22.99
+# + 3 D fwd x 1.265 + 2 D bwd (data + weight gradients) x 2.47 + 1 D bwd (data gradient only) x 1.265
+TRAIN_GFLOP_PER_IMAGE_128 = 11.5218 + 22.987 + 3 * 1.265 + 2 * 2.473 + 1.265
 
 
 def load_peaks():
@@ -61,15 +65,33 @@ def load_peaks():
     if p.exists():
         d = json.loads(p.read_text())
         return {"bf16": float(d["bf16_tflops"]), "bf16_sustained": float(d.get("bf16_tflops_sustained", 0.0)),
-                "hbm": float(d["hbm_gbs"]), "source": "measured"}
-    return {"bf16": 1590.0, "bf16_sustained": 1400.0, "hbm": 6650.0, "source": "fallback"}
+                "hbm": float(d["hbm_gbs"]), "source": "measured (MEASURED_PEAKS.json)"}
+    return {"bf16": 1590.0, "bf16_sustained": 1400.0, "hbm": 6650.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+def load_ncu_traffic():
+    """Newest profiles/r*_ncu_traffic.json (written by tools/ncu_summary.py --traffic-json from an `ncu --set full`
+    capture of one batch-256 forward): per-layer dram__bytes_read + dram__bytes_write and the hash of the library it
+    was captured with."""
+    files = sorted((ROOT / "profiles").glob("r*_ncu_traffic.json"))
+    if not files:
+        return None
+    d = json.loads(files[-1].read_text())
+    d["file"] = f"profiles/{files[-1].name}"
+    return d
+
+
+def library_sha():
+    p = ROOT / "celebrity-image-denoiser_b200" / "csrc" / "libcid_b200.so"
+    return hashlib.sha256(p.read_bytes()).hexdigest()[:16] if p.exists() else None
 
 
 class ClockSampler:
     """Samples SM clock / throttle reasons through NVML while the timed region runs."""
 
-    def __init__(self, index: int):
+    def __init__(self, index: int, period_s: float = 0.004):
         self.samples, self.reasons, self.max_mhz = [], set(), None
+        self.period = period_s
         self._stop = threading.Event()
         self._thread = None
         try:
@@ -102,12 +124,13 @@ class ClockSampler:
                         self.reasons.add(k)
             except Exception:
                 pass
-            time.sleep(0.004)
+            time.sleep(self.period)
 
     def start(self):
         if self.nv is not None:
             self._thread = threading.Thread(target=self._loop, daemon=True)
             self._thread.start()
+        return self
 
     def stop(self):
         self._stop.set()
@@ -163,6 +186,83 @@ def run_reference(args, rank: int, world: int):
     print(json.dumps(line), flush=True)
 
 
+class Timer:
+    """CUDA-event timing of a region on the current stream, with the barrier + synchronize bracket of the contract.
+    Every region's milliseconds are collected and reduced (MAX over ranks) in one all-reduce at the end."""
+
+    def __init__(self, torch, dist, dev, world):
+        self.torch, self.dist, self.dev, self.world = torch, dist, dev, world
+        self.ms = {}
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize(self.dev)
+
+    def region(self, name, fn, iters, warm=0, sync_first=True):
+        for _ in range(warm):
+            fn()
+        e0, e1 = self.torch.cuda.Event(enable_timing=True), self.torch.cuda.Event(enable_timing=True)
+        if sync_first:
+            self.barrier()
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        self.barrier()
+        self.ms[name] = e0.elapsed_time(e1)
+        return self.ms[name]
+
+    def reduce_max(self):
+        names = sorted(self.ms)
+        t = self.torch.tensor([self.ms[n] for n in names], dtype=self.torch.float64, device=self.dev)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        self.ms = {n: float(v) for n, v in zip(names, t.tolist())}
+        return self.ms
+
+
+def bench_membound(torch, dev, tm: Timer):
+    """Achieved HBM GB/s of the memory-bound pre-processing kernels (north star: 'achieved HBM GB/s against peak for the
+    elementwise and norm kernels'). Inputs are far larger than the 126 MB L2, so every pass streams from DRAM.
+    Algorithmic bytes: noiser 1 B read + 1 B written per element; resize input + output bytes (the intermediate of the
+    two-pass resampler is extra traffic, not algorithmic); normalise 1 B read + 4 B written per element."""
+    from cid_b200 import noiser as nz
+
+    out = []
+    g = torch.Generator(device=dev).manual_seed(5)
+    big = torch.randint(0, 256, (1024, 512, 512, 3), dtype=torch.uint8, device=dev, generator=g)   # 805 MB
+    n = big.numel()
+    cases = [
+        ("gaussian_u8_kernel (Philox4x32-10 + Box-Muller)", lambda: nz.add_gaussian_noise(big, 0.0, 25.0, seed=1), 2 * n),
+        ("elementwise_noise_kernel<uniform> (Philox)", lambda: nz.add_uniform_noise(big, 0.0, 25.0, seed=2), 2 * n),
+        ("elementwise_noise_kernel<speckle> (Philox)", lambda: nz.add_speckle_noise(big, 0.0, 0.1, seed=3), 2 * n),
+        ("copy_u8_kernel + impulse_kernel (salt & pepper 2 % + 2 %)",
+         lambda: nz.add_salt_pepper_noise(big, 0.02, 0.02, seed=4), 2 * n),
+    ]
+    if hasattr(nz, "add_gaussian_unit"):
+        cases.append(("unit_noise_kernel<gaussian> ([0,1] domain, sigma 0.1, Philox)",
+                      lambda: nz.add_gaussian_unit(big, seed=6), 2 * n))
+    for name, fn, nbytes in cases:
+        ms = tm.region("mb:" + name, fn, 5, warm=2) / 5
+        out.append({"kernel": name, "bytes": nbytes, "ms_key": "mb:" + name, "iters": 5})
+        del ms
+    del big
+    torch.cuda.empty_cache()
+    src = torch.randint(0, 256, (256, 512, 512, 3), dtype=torch.uint8, device=dev, generator=g)    # 201 MB
+    name = "resample_u8_kernel<H> + <V> (PIL bicubic 512^2 -> 256^2, batch 256)"
+    tm.region("mb:" + name, lambda: nz.resize_bicubic(src, (256, 256)), 5, warm=2)
+    out.append({"kernel": name, "bytes": src.numel() + 256 * 256 * 256 * 3, "ms_key": "mb:" + name, "iters": 5})
+    del src
+    img = torch.randint(0, 256, (4096, 128, 128, 3), dtype=torch.uint8, device=dev, generator=g)   # 201 MB in, 805 MB out
+    name = "normalize_kernel (ToTensor + Normalize, u8 NHWC -> f32 NCHW, batch 4096 @128^2)"
+    tm.region("mb:" + name, lambda: nz.normalize_to_tensor(img), 5, warm=2)
+    out.append({"kernel": name, "bytes": img.numel() * 5, "ms_key": "mb:" + name, "iters": 5})
+    del img
+    torch.cuda.empty_cache()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -172,11 +272,13 @@ def main():
     ap.add_argument("--batch", type=int, default=256, help="images per GPU per step")
     ap.add_argument("--size", type=int, default=128)
     ap.add_argument("--chunk", type=int, default=-1, help="images per pass through the layers (-1 = library default)")
-    ap.add_argument("--sub-batch", type=int, default=128, help="e2e: images per H2D/compute/D2H pipeline slot")
+    ap.add_argument("--sub-batch", type=int, default=64, help="e2e: images per H2D/compute/D2H pipeline slot")
+    ap.add_argument("--depth", type=int, default=4, help="e2e: staging slots of the three-stage pipeline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--debug-flags", type=int, default=0, help="bring-up experiments (invalidates results)")
-    ap.add_argument("--variant", type=int, default=-1, help="CTA-pair layer bit mask (cid_set_option 'variant'; -1 = library default)")
     ap.add_argument("--layers", action="store_true", help="also print the per-layer table to stderr")
+    ap.add_argument("--only", default="", help="comma list of extra sections to run (default: all): "
+                                               "sustained,latency,strong,train,membound")
+    ap.add_argument("--sustained-seconds", type=float, default=3.0)
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -191,12 +293,14 @@ def main():
     import torch.distributed as dist
 
     from cid_b200.generator import DenoiseGenerator
-    from cid_b200.pipeline import HostPipeline
+    from cid_b200.pipeline import HostPipeline, set_rank_affinity
     from cid_b200.synth import synthetic_noisy_u8
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the generator path has no CPU fallback "
                          "(use --impl reference for the CPU baseline)")
+    sections = set(s for s in args.only.split(",") if s) or {"sustained", "latency", "strong", "train", "membound"}
+    affinity = set_rank_affinity(local_rank, world) if world > 1 else None
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
@@ -216,118 +320,233 @@ def main():
             os.close(saved_stdout)
 
     B, H, W = args.batch, args.size, args.size
+    K, Wm = max(args.steps, 1), max(args.warmup, 3)
     peaks = load_peaks()
+    tm = Timer(torch, dist, dev, world)
 
     # random-init generator with the reference's state_dict layout (the shipped .pth is not in the tree)
     torch.manual_seed(0)
     net = DenoiseGenerator().to(dev).eval()
     if args.chunk >= 0:
         net.set_option("chunk", args.chunk)
-    net.set_option("profile", 1)
-    if args.debug_flags:
-        net.set_option("debug_flags", args.debug_flags)
-    if args.variant >= 0:
-        net.set_option("variant", args.variant)
 
     host_in = synthetic_noisy_u8(1234 + rank, B, H, W).pin_memory()
     host_out = torch.empty_like(host_in).pin_memory()
     x = host_in.to(dev)
     y = torch.empty_like(x)
     pad = (0, 0, 0, 0)
+    step = lambda: net.forward_u8(x, pad, out=y)  # noqa: E731
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
-
-    # ---------------- device-resident throughput ----------------
-    for _ in range(max(args.warmup, 3)):
-        net.forward_u8(x, pad, out=y)
+    # ---------------- device-resident throughput (profiling events off) ----------------
+    for _ in range(Wm):
+        step()
     torch.cuda.synchronize(dev)
-    net.profile_read()
     launches0 = net.kernel_launches()
-    sampler = ClockSampler(local_rank)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    sampler.start()
-    e0.record()
-    for _ in range(args.steps):
-        net.forward_u8(x, pad, out=y)
-    e1.record()
-    barrier()
+    sampler = ClockSampler(local_rank).start()
+    tm.region("value", step, K)
     clocks = sampler.stop()
-    ms_total = e0.elapsed_time(e1)
     launches = net.kernel_launches() - launches0
-    layer_ms, passes = net.profile_read()
 
     # ---------------- end to end through the public host API ----------------
-    pipe = HostPipeline(net, dev, min(args.sub_batch, B), H, W, depth=2)
-    for _ in range(3):
-        pipe.run(host_in, host_out)
-    torch.cuda.synchronize(dev)
-    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    f0.record()
-    for _ in range(args.steps):
-        h2d, d2h = pipe.run(host_in, host_out, join=False)  # a serving loop: batch k+1's upload overlaps batch k's tail
-    pipe.finish()
-    f1.record()
-    barrier()
-    ms_e2e = f0.elapsed_time(f1)
-    checksum = int(host_out.view(-1)[::4099].to(torch.int64).sum())  # the D2H result is really read
+    pipe = HostPipeline(net, dev, min(args.sub_batch, B), H, W, depth=args.depth)
+    io_bytes = [0, 0]
+    for stage, key in (("all", "e2e"), ("copy", "e2e_copy"), ("compute", "e2e_compute")):
+        for _ in range(3):
+            pipe.run(host_in, host_out, stage=stage)
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        tm.barrier()
+        e0.record()
+        for _ in range(K):  # a serving loop: batch k+1's upload overlaps batch k's tail
+            h2d, d2h = pipe.run(host_in, host_out, join=False, stage=stage)
+        pipe.finish()
+        e1.record()
+        tm.barrier()
+        tm.ms[key] = e0.elapsed_time(e1)
+        if stage == "all":
+            io_bytes = [h2d, d2h]
+            checksum = int(host_out.view(-1)[::4099].to(torch.int64).sum())  # the D2H result is really read
 
-    t = torch.tensor([ms_total, ms_e2e], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, ms_e2e = float(t[0]), float(t[1])
+    # ---------------- per-layer profiled pass (cudaEventRecord between layers: not the headline) ----------------
+    net.set_option("profile", 1)
+    for _ in range(2):
+        step()
+    torch.cuda.synchronize(dev)
+    net.profile_read()
+    tm.region("profiled", step, K)
+    layer_ms, passes = net.profile_read()
+    net.set_option("profile", 0)
+
+    # ---------------- sustained: the headline loop for >= 3 s ----------------
+    sustained = None
+    if "sustained" in sections:
+        est = max(tm.ms["value"] / K, 1e-3)
+        n_sus = max(int(args.sustained_seconds * 1e3 / est) + 1, K)
+        sus_sampler = ClockSampler(local_rank, period_s=0.02).start()
+        tm.region("sustained", step, n_sus)
+        sustained = {"steps": n_sus, "clocks": sus_sampler.stop()}
+
+    # ---------------- BASELINE configs[3]: latency path ----------------
+    latency = []
+    if "latency" in sections:
+        for (lb, ls) in ((1, 128), (32, 128), (1, 256), (32, 256), (1, 512), (32, 512)):
+            xi = synthetic_noisy_u8(77, min(lb, 4), ls, ls)
+            xi = xi.repeat((lb + xi.shape[0] - 1) // xi.shape[0], 1, 1, 1)[:lb].contiguous().to(dev)
+            yo = torch.empty_like(xi)
+            iters = 200 if lb == 1 else 20
+            key = f"lat:{lb}x{ls}"
+            tm.region(key, lambda: net.forward_u8(xi, pad, out=yo), iters, warm=5)
+            latency.append({"batch": lb, "size": ls, "iters": iters, "ms_key": key})
+            del xi, yo
+        net.release_workspace()
+        torch.cuda.empty_cache()
+
+    # ---------------- BASELINE configs[2]: 2048 images split over the ranks ----------------
+    strong = None
+    if "strong" in sections:
+        from cid_b200.sharding import shard_range
+        a, b = shard_range(2048, rank, world)
+        xs = x.repeat((b - a + B - 1) // B, 1, 1, 1)[: b - a].contiguous()
+        ys = torch.empty_like(xs)
+        net.set_option("chunk", 256)
+        tm.region("strong", lambda: net.forward_u8(xs, pad, out=ys), 5, warm=2)
+        net.set_option("chunk", max(args.chunk, 0))
+        strong = {"images": 2048, "images_this_rank": b - a, "iters": 5}
+        del xs, ys
+        torch.cuda.empty_cache()
+
+    # ---------------- memory-bound pre-processing kernels ----------------
+    membound = bench_membound(torch, dev, tm) if "membound" in sections else []
+
+    # ---------------- BASELINE configs[4]: training step ----------------
+    train = None
+    if "train" in sections:
+        from cid_b200.training import DenoiseDiscriminator, DenoiseGANTrainStep
+        torch.manual_seed(0)
+        tr = DenoiseGANTrainStep(DenoiseGenerator(), DenoiseDiscriminator(), device=dev)
+        TB = 64
+        gen = torch.Generator(device="cpu").manual_seed(4321 + rank)
+        clean = torch.rand(TB, 3, H // 8, W // 8, generator=gen)
+        clean = torch.nn.functional.interpolate(clean, size=(H, W), mode="bicubic", align_corners=False).clamp(0, 1)
+        noisy = (clean + 0.1 * torch.randn(TB, 3, H, W, generator=gen)).clamp(0, 1)
+        noisy, clean = ((noisy - 0.5) / 0.5).to(dev).contiguous(), ((clean - 0.5) / 0.5).to(dev).contiguous()
+        tstep = lambda: tr.step(noisy, clean, read_losses=False)  # noqa: E731
+        for _ in range(3):
+            tstep()
+        torch.cuda.synchronize(dev)
+        l0 = tr.kernel_launches()
+        tm.region("train", tstep, 10)
+        t_launch = (tr.kernel_launches() - l0) // 10
+        losses = tr.losses()
+        train = {"batch_per_gpu": TB, "iters": 10, "gpu_launches_per_step": t_launch, "losses": losses,
+                 "allreduce": ("fused into Adam over NVLink peer memory (adam_allreduce_kernel)" if tr.peer_fused
+                               else "nccl all_reduce" if world > 1 else "none (1 GPU)")}
+        tr.close()
+        del tr, noisy, clean
+        torch.cuda.empty_cache()
+
+    ms = tm.reduce_max()
 
     if rank == 0:
-        imgs = B * world * args.steps
+        ms_total, ms_e2e = ms["value"], ms["e2e"]
+        imgs = B * world * K
         value = imgs / (ms_total * 1e-3)
         e2e_value = imgs / (ms_e2e * 1e-3)
-        # dominant kernel = the tensor-core conv layer with the largest share of the step
-        conv_layers = [k for k in layer_ms if k != "down1.0"]
+        step_ms = ms_total / K
+        # dominant kernel = the tensor-core conv layer with the largest share of the (profiled) step
+        conv_layers = [k for k in layer_ms if k != "down1.0" and layer_ms[k] > 0]
         dom = max(conv_layers, key=lambda k: layer_ms[k])
         dom_ms = layer_ms[dom] / max(passes, 1)
-        launches_per_pass = passes / max(args.steps, 1)
+        launches_per_pass = passes / K
         imgs_per_pass = B / max(launches_per_pass, 1)
         dom_flops = LAYER_FLOP_PER_PIXEL[dom] * H * W * imgs_per_pass
         achieved = dom_flops / (dom_ms * 1e-3) / 1e12
+        traffic, traffic_src = None, "no profiles/r*_ncu_traffic.json committed for this build"
+        ncu = load_ncu_traffic()
+        if ncu and dom in ncu.get("layers", {}):
+            lay = ncu["layers"][dom]
+            scale = (imgs_per_pass * H * W) / (ncu["batch"] * ncu["height"] * ncu["width"])
+            traffic = (lay["dram_read_bytes"] + lay["dram_write_bytes"]) * scale
+            same = ncu.get("library_sha") == library_sha()
+            traffic_src = (f"dram__bytes_read+write per launch, ncu --set full, {ncu['file']} "
+                           f"({'captured with this build of libcid_b200.so' if same else 'captured with an OLDER build of the library'})"
+                           ", scaled to this launch's pixel count")
         roofline = {"bound": "tensor", "kernel": f"conv_umma_kernel[{dom}]", "achieved": achieved,
                     "peak": peaks["bf16"], "unit": "TFLOP/s", "frac": achieved / peaks["bf16"],
-                    "traffic": NCU_TRAFFIC_MB_B256_128[dom] * 1e6 * (imgs_per_pass * H * W) / (256 * 128 * 128),
-                    "traffic_source": "dram__bytes_read+write per launch, ncu --set full (profiles/r01i_ncu_full_batch256.md), "
-                                      "scaled to this launch's pixel count",
-                    "peak_source": f"{peaks['source']} burst bf16 (MEASURED_PEAKS.json bf16_tflops)",
+                    "traffic": traffic, "traffic_source": traffic_src,
+                    "peak_source": f"{peaks['source']} burst bf16 (bf16_tflops)",
                     "flops_per_launch": dom_flops, "ms_per_launch": dom_ms}
-        net_tflops = value * FLOP_PER_PIXEL * H * W / 1e12
-        step_ms = ms_total / args.steps
-        per_layer = {k: {"ms": layer_ms[k] / args.steps,
-                         "tflops": LAYER_FLOP_PER_PIXEL[k] * H * W * B / (layer_ms[k] / args.steps * 1e-3) / 1e12,
-                         "share": layer_ms[k] / args.steps / step_ms} for k in layer_ms}
+        prof_step_ms = ms["profiled"] / K
+        per_layer = {k: {"ms": layer_ms[k] / K,
+                         "tflops": (LAYER_FLOP_PER_PIXEL[k] * H * W * B / (layer_ms[k] / K * 1e-3) / 1e12) if layer_ms[k] > 0 else None,
+                         "share": layer_ms[k] / K / prof_step_ms} for k in layer_ms}
+        per_gpu_tflops = value / world * FLOP_PER_PIXEL * H * W / 1e12
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak",
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
+            "warmup": Wm, "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": f"generator forward, batch {B} of {H}x{W} RGB per GPU, random-init weights "
                                    f"(BASELINE.json configs[1]); u8 NHWC in -> u8 NHWC out",
                        "batch_per_gpu": B, "height": H, "width": W, "parallelism": f"batch-sharded x{world}, no collective",
-                       "l2": "per-step activation working set (~4 GB at batch 256) exceeds the 126 MB L2; no flush needed"},
+                       "l2": "per-step activation working set (~7 GB at batch 256) exceeds the 126 MB L2; no flush needed",
+                       "host_affinity": (f"{len(affinity)} CPUs from {affinity[0]}" if affinity else None)},
             "clocks": clocks,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms_e2e / args.steps, "checksum": checksum},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": io_bytes[0], "d2h_bytes_per_step": io_bytes[1],
+                    "ms_per_step": ms_e2e / K, "checksum": checksum,
+                    "pipeline": f"3 stages (H2D / kernels / D2H streams), {args.depth} slots of {min(args.sub_batch, B)} images",
+                    "breakdown": {"copy_only_ms_per_step": ms["e2e_copy"] / K, "compute_only_ms_per_step": ms["e2e_compute"] / K,
+                                  "note": "same pipeline with the kernels (copy_only) or the copies (compute_only) left out; "
+                                          "max over ranks"}},
             "gpu_launches": launches,
             "roofline": roofline,
-            "net_tensor": {"achieved_tflops": net_tflops, "frac_of_burst_peak": net_tflops / peaks["bf16"],
-                           "frac_of_sustained_peak": (net_tflops / peaks["bf16_sustained"]) if peaks["bf16_sustained"] else None},
+            "net_tensor": {"achieved_tflops_per_gpu": per_gpu_tflops, "frac_of_burst_peak": per_gpu_tflops / peaks["bf16"],
+                           "frac_of_sustained_peak": (per_gpu_tflops / peaks["bf16_sustained"]) if peaks["bf16_sustained"] else None},
+            "profiled_pass": {"ms_per_step": prof_step_ms, "note": "per-layer cudaEventRecord between the layers; "
+                                                                   "`layers` and `roofline` come from this pass, `value` does not"},
             "layers": per_layer,
         }
+        if sustained:
+            s_ms = ms["sustained"] / sustained["steps"]
+            s_tf = B * FLOP_PER_PIXEL * H * W / (s_ms * 1e-3) / 1e12
+            sustained.update({"seconds": ms["sustained"] * 1e-3, "ms_per_step": s_ms, "value": B * world / (s_ms * 1e-3),
+                              "unit": UNIT, "tflops_per_gpu": s_tf, "frac_of_burst_peak": s_tf / peaks["bf16"],
+                              "frac_of_sustained_peak": (s_tf / peaks["bf16_sustained"]) if peaks["bf16_sustained"] else None})
+            line["sustained"] = sustained
+        if latency:
+            for e in latency:
+                t = ms[e.pop("ms_key")] / e["iters"]
+                tf = e["batch"] * e["size"] ** 2 * FLOP_PER_PIXEL / (t * 1e-3) / 1e12
+                e.update({"us": t * 1e3, "images_per_s": e["batch"] / (t * 1e-3), "tflops": tf,
+                          "frac_of_burst_peak": tf / peaks["bf16"]})
+            line["latency"] = {"config": "BASELINE.json configs[3]: forward_u8 calls back to back on one stream, u8 in -> u8 out "
+                                         "resident in HBM, per call (max over ranks)", "cases": latency}
+        if strong:
+            t = ms["strong"] / strong["iters"]
+            strong.update({"ms": t, "value": 2048 / (t * 1e-3), "unit": UNIT, "scaling": "strong",
+                           "config": "BASELINE.json configs[2]: 2048 images of 128x128 split contiguously over the ranks, "
+                                     "256 images per pass"})
+            line["strong_2048"] = strong
+        if train:
+            t = ms["train"] / train["iters"]
+            gflop = TRAIN_GFLOP_PER_IMAGE_128 * (H * W / 16384.0)
+            tf = train["batch_per_gpu"] * gflop / t
+            train.update({"ms_per_step": t, "value": world * train["batch_per_gpu"] / (t * 1e-3), "unit": "images/s",
+                          "tflops_per_gpu": tf, "frac_of_burst_peak": tf / peaks["bf16"], "gflop_per_image": gflop,
+                          "config": f"BASELINE.json configs[4]: denoise GAN G+D+Adam iteration, batch {train['batch_per_gpu']}/GPU "
+                                    f"@{H}x{W} (training.py:409-427), weak scaling"})
+            line["train"] = train
+        if membound:
+            for e in membound:
+                t = ms[e.pop("ms_key")] / e.pop("iters")
+                gbs = e["bytes"] / (t * 1e-3) / 1e9
+                e.update({"ms": t, "gbs": gbs, "frac_of_hbm_peak": gbs / peaks["hbm"]})
+            line["membound"] = {"peak_gbs": peaks["hbm"], "peak_source": peaks["source"], "kernels": membound}
         if world == 1 and not args.no_cpu_baseline:
             cb = cpu_forward_baseline(H, W, 32, budget_s=15.0)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
         if args.layers:
             for k, v in per_layer.items():
-                print(f"  {k:14s} {v['ms']:8.4f} ms  {v['tflops']:8.1f} TFLOP/s  {100 * v['share']:5.1f} %", file=sys.stderr)
+                print(f"  {k:14s} {v['ms']:8.4f} ms  {v['tflops'] or 0:8.1f} TFLOP/s  {100 * v['share']:5.1f} %", file=sys.stderr)
         print(json.dumps(line), flush=True)
 
     if world > 1:

@@ -165,7 +165,7 @@ static int cgan_get_plan(cid_ctx* c, int Bc, int H, int W, const void* ws, cid_p
             *out = &pl;
             return 0;
         }
-    if (c->plans.size() >= 64) c->plans.clear();
+    if (c->plans.size() >= 64) clear_plans(c);
     cid_plan pl;
     pl.Bc = Bc;
     pl.H = H;
@@ -231,7 +231,6 @@ static int cgan_run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, c
         p.cout = kCganCout[l];
         p.w_rows_per_tap = kCganCout[l];
         p.slope = kCganSlope;
-        p.debug_flags = c->debug_flags;
         return p;
     };
     {  // G1: 4x4 s2 conv 64 -> 128

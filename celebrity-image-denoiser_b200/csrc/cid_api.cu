@@ -2,7 +2,7 @@
 // layer-by-layer launch sequence of the denoise generator.
 //
 // Layer table (reference: backend/app.py:42-78, forward :80-103):
-//   L0  down1.0       conv3x3   3->64   +ReLU            first_conv_kernel      -> a0
+//   L0  down1.0       conv3x3   3->64   +ReLU            first_conv_umma_kernel -> a0
 //   L1  down1.2       conv3x3  64->64   +ReLU +pool      <64 ,9,1,WRES,POOL>    -> cat1[:,64:128], p1
 //   L2  down2.0       conv3x3  64->128  +ReLU            <128,9,1,WRES,RELU>    -> a2
 //   L3  down2.2       conv3x3 128->128  +ReLU +pool      <128,9,2,ring,POOL>    -> cat2[:,128:256], p2
@@ -21,7 +21,6 @@
 
 #include "cid_internal.h"
 #include "conv_umma.cuh"
-#include "edge_kernels.cuh"
 #include "first_conv_umma.cuh"
 #include "last_conv_umma.cuh"
 #include "cgan_first_conv.cuh"
@@ -39,6 +38,20 @@ void set_error(const char* fmt, ...) {
     va_start(ap, fmt);
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
+}
+
+static void graph_release(cid_graph& g) {
+    if (g.exec) cudaGraphExecDestroy(static_cast<cudaGraphExec_t>(g.exec));
+    if (g.graph) cudaGraphDestroy(static_cast<cudaGraph_t>(g.graph));
+    g = cid_graph();
+}
+
+void clear_plans(cid_ctx* c) {
+    for (auto& pl : c->plans) {
+        graph_release(pl.graph[0]);
+        graph_release(pl.graph[1]);
+    }
+    c->plans.clear();
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -188,13 +201,7 @@ static int pack_layer(cid_ctx* c, int l) {
     const std::vector<float>& b = bi->second;
 
     if (L.kind == L_FIRST) {
-        if (!c->first_w_host) c->first_w_host = new FirstConvW();
-        FirstConvW* fw = static_cast<FirstConvW*>(c->first_w_host);
-        for (int co = 0; co < 64; ++co) {
-            for (int t = 0; t < 27; ++t) fw->w[t][co] = w[static_cast<size_t>(co) * 27 + t];  // [co][ci][ky][kx]
-            fw->b[co] = b[co];
-        }
-        // tensor-core variant: per tap a [cout 64][K 16] tile in the un-swizzled K-major layout
+        // per tap a [cout 64][K 16] tile in the un-swizzled K-major layout
         // [tap][k chunk][cout][8 bf16]; K chunk 0 = [w_r w_g w_b | w_r w_g w_b | 0 0] (the input is
         // split hi+lo along K), K chunk 1 = [wlo_r wlo_g wlo_b | 0 ...]: the MMA reads the same pixel chunk for
         // both K chunks (LBO = 0), so chunk 1 adds x_hi * w_lo.
@@ -267,6 +274,8 @@ static int pack_layer(cid_ctx* c, int l) {
     CID_CHECK_CUDA(cudaMalloc(reinterpret_cast<void**>(&c->bias_dev[l]), bp.size() * 4));
     CID_CHECK_CUDA(cudaMemcpy(c->bias_dev[l], bp.data(), bp.size() * 4, cudaMemcpyHostToDevice));
     if (box_rows % 2 == 0 && make_weight_map(&c->tmWh[l], c->w_dev[l], rows, L.cin, box_rows / 2)) return 1;
+    // 64-row boxes: the N-split form of the 128 / 256-wide layers (small batches, see pick_split)
+    if (L.kind == L_CONV && l != 11 && make_weight_map(&c->tmW64[l], c->w_dev[l], rows, L.cin, 64)) return 1;
     return make_weight_map(&c->tmW[l], c->w_dev[l], rows, L.cin, box_rows);
 }
 
@@ -284,7 +293,7 @@ static int get_plan(cid_ctx* c, int Bc, int H, int W, const void* ws, cid_plan**
             *out = &pl;
             return 0;
         }
-    if (c->plans.size() >= 64) c->plans.clear();
+    if (c->plans.size() >= 64) clear_plans(c);
     cid_plan pl;
     pl.Bc = Bc;
     pl.H = H;
@@ -396,9 +405,11 @@ static int launch_conv(cid_ctx* c, int slot, const CUtensorMap& tmA, const CUten
     p.num_work = ((p.m_tiles + S * CG - 1) / (S * CG)) * p.n_tiles;  // work items of one CTA (or CTA pair)
     const int smem = Cfg::smem_bytes(p.kb_count, a_stages, w_stages);
     auto kern = conv_umma_kernel<N, TAPS, S, WRES, EPI, PW, TS, CG>;
-    if (!(c->attr_done & (1u << slot))) {
+    (void)slot;
+    static uint64_t attr_set = 0;  // bit per device: function attributes are per device and per instantiation
+    if (!(attr_set >> (c->device & 63) & 1)) {
         CID_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, c->max_smem));
-        c->attr_done |= (1u << slot);
+        attr_set |= 1ull << (c->device & 63);
     }
     const int grid = std::min(p.num_work * CG, c->num_sms / CG * CG);
     CID_CHECK_CUDA(launch_ex(c, kern, grid, kConvThreads, smem, st, CG, tmA, tmW, tmO, tmO2, p));
@@ -425,55 +436,75 @@ static int prof_mark(cid_ctx* c, cudaStream_t st) {
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Small batches (the upload route runs batch 1, backend/app.py:406): a layer whose pixel tiles do not fill
+// the 148 SMs in its batch-256 configuration (S tiles per work item, CTA pairs, N = Cout) runs instead as
+// N = 64 column blocks of single tiles (n_tiles = Cout / 64 work items per pixel tile, one CTA each), so up
+// to 4x as many SMs share the layer. Both forms accumulate every output in the same order: bit-identical.
+// Cost model: waves x work-item time, time ~ S * N columns, N = 64 MMAs pay ~1.25x (they sit on the
+// shared-memory roofline). `S`, `CG` describe the large form of the layer.
+// ---------------------------------------------------------------------------------------------
+static bool pick_split(const cid_ctx* c, int m_tiles, int n, int S, int CG) {
+    if (c->regime == 1) return false;
+    if (c->regime == 2) return true;
+    const int slots = c->num_sms;
+    auto waves = [](int items, int sl) { return (items + sl - 1) / sl; };
+    const int large_items = (m_tiles + S * CG - 1) / (S * CG);
+    const double large = waves(large_items, slots / CG) * static_cast<double>(S * n) * (n == 64 ? 1.25 : 1.0);
+    const double split = waves(m_tiles * (n / 64), slots) * 64.0 * 1.25;
+    return split < large;
+}
+
+static FirstParams make_first_params(const cid_ctx* c, const cid_plan* pl, int nb, const IoSpec& io) {
+    uint8_t* ws = static_cast<uint8_t*>(const_cast<void*>(pl->ws));
+    FirstParams fp;
+    memset(&fp, 0, sizeof(fp));
+    fp.B = nb; fp.H = pl->H; fp.W = pl->W;
+    fp.in = io.x; fp.in_h = io.in_h; fp.in_w = io.in_w; fp.pad_l = io.pad_l; fp.pad_t = io.pad_t;
+    fp.out = reinterpret_cast<__nv_bfloat16*>(ws + pl->off[B_A0]);
+    fp.tiles_x = (pl->W + 7) / 8;
+    fp.tiles_y = (pl->H + 15) / 16;
+    fp.m_tiles = nb * fp.tiles_x * fp.tiles_y;
+    fp.w_packed = static_cast<const uint4*>(c->w_dev[0]);
+    return fp;
+}
+
+static int make_last_params(const cid_ctx* c, const cid_plan* pl, int nb, const IoSpec& io, LastParams* out) {
+    LastParams lp;
+    memset(&lp, 0, sizeof(lp));
+    lp.B = nb; lp.H = pl->H; lp.W = pl->W;
+    lp.tiles_x = (pl->W + 7) / 8;
+    lp.tiles_y = (pl->H + 15) / 16;
+    lp.m_tiles = nb * lp.tiles_x * lp.tiles_y;
+    lp.stages = std::min(kLastMaxStages, (c->max_smem - last_conv_smem(0)) / kLastStageBytes);
+    CID_REQUIRE(lp.stages >= 2, "last conv: shared memory too small");
+    lp.bias = c->bias_dev[11];
+    lp.out = io.y;
+    lp.crop_l = io.pad_l; lp.crop_t = io.pad_t; lp.out_h = io.in_h; lp.out_w = io.in_w;
+    *out = lp;
+    return 0;
+}
+
 // one pass of nb (<= plan.Bc) images through the 12 layers
 static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaStream_t st) {
     const int H = pl->H, W = pl->W;
     uint8_t* ws = static_cast<uint8_t*>(const_cast<void*>(pl->ws));
     auto buf = [&](int b) { return reinterpret_cast<__nv_bfloat16*>(ws + pl->off[b]); };
+    auto tiles = [&](int lv) { return nb * (((W >> lv) + 7) / 8) * (((H >> lv) + 15) / 16); };
 
     if (prof_mark(c, st)) return 1;
-    // L0
-    if (c->first_tc) {
-        FirstParams fp;
-        memset(&fp, 0, sizeof(fp));
-        fp.B = nb; fp.H = H; fp.W = W;
-        fp.in = io.x; fp.in_h = io.in_h; fp.in_w = io.in_w; fp.pad_l = io.pad_l; fp.pad_t = io.pad_t;
-        fp.out = buf(B_A0);
-        fp.tiles_x = (W + 7) / 8;
-        fp.tiles_y = (H + 15) / 16;
-        fp.m_tiles = nb * fp.tiles_x * fp.tiles_y;
-        const int smem = kFirstSmem;
-        fp.w_packed = static_cast<const uint4*>(c->w_dev[0]);
+    {  // L0 down1.0 (+ Pad / ToTensor / Normalize) -> a0
+        const FirstParams fp = make_first_params(c, pl, nb, io);
         if (!(c->attr_done & (1u << 30))) {
-            CID_CHECK_CUDA(cudaFuncSetAttribute(first_conv_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-            CID_CHECK_CUDA(cudaFuncSetAttribute(first_conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            CID_CHECK_CUDA(cudaFuncSetAttribute(first_conv_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFirstSmem));
+            CID_CHECK_CUDA(cudaFuncSetAttribute(first_conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFirstSmem));
             c->attr_done |= (1u << 30);
         }
-        const int grid = std::min(fp.m_tiles, c->num_sms * ((c->debug_flags & 4) ? 1 : kFirstCtasPerSm));
+        const int grid = std::min(fp.m_tiles, c->num_sms * kFirstCtasPerSm);
         if (io.u8)
-            CID_CHECK_CUDA(launch_ex(c, first_conv_umma_kernel<true>, grid, kFirstThreads, smem, st, 1, pl->tmO[0], fp));
+            CID_CHECK_CUDA(launch_ex(c, first_conv_umma_kernel<true>, grid, kFirstThreads, kFirstSmem, st, 1, pl->tmO[0], fp));
         else
-            CID_CHECK_CUDA(launch_ex(c, first_conv_umma_kernel<false>, grid, kFirstThreads, smem, st, 1, pl->tmO[0], fp));
-        CID_CHECK_CUDA(cudaGetLastError());
-        c->launches++;
-    } else {
-        FirstConvParams fp;
-        fp.B = nb;
-        fp.H = H;
-        fp.W = W;
-        fp.in = io.x;
-        fp.in_h = io.in_h;
-        fp.in_w = io.in_w;
-        fp.pad_l = io.pad_l;
-        fp.pad_t = io.pad_t;
-        fp.out = buf(B_A0);
-        const size_t total = static_cast<size_t>(nb) * H * W;
-        const unsigned grid = static_cast<unsigned>((total + 127) / 128);
-        const FirstConvW& fw = *static_cast<const FirstConvW*>(c->first_w_host);
-        if (io.u8)
-            first_conv_kernel<true><<<grid, 128, 0, st>>>(fw, fp);
-        else
-            first_conv_kernel<false><<<grid, 128, 0, st>>>(fw, fp);
+            CID_CHECK_CUDA(launch_ex(c, first_conv_umma_kernel<false>, grid, kFirstThreads, kFirstSmem, st, 1, pl->tmO[0], fp));
         CID_CHECK_CUDA(cudaGetLastError());
         c->launches++;
     }
@@ -491,120 +522,93 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         p.cout = kLayers[l].cout;
         p.w_rows_per_tap = std::max(kLayers[l].cout, 16);
         p.slope = 1.f;  // EPI_CONVT: no activation after the transposed convs
-        p.debug_flags = c->debug_flags;
         return p;
+    };
+    // N-split form of a 3x3 layer: column blocks of 64 through the streamed-weight single-CTA kernel
+    auto split_relu = [&](int l, ConvParams p) {
+        p.n_tiles = kLayers[l].cout / 64;
+        return launch_conv<64, 9, 1, false, EPI_RELU, 10, 1>(c, 22, pl->tmA[l], c->tmW64[l], pl->tmO[l], pl->tmO[l], p, st);
+    };
+    auto split_pool = [&](int l, ConvParams p) {
+        p.n_tiles = kLayers[l].cout / 64;
+        return launch_conv<64, 9, 1, false, EPI_RELU_POOL, 10, 1>(c, 23, pl->tmA[l], c->tmW64[l], pl->tmO[l], pl->tmO2[l], p, st);
     };
 
     {  // L1 down1.2 -> cat1[:,64:128] + p1
         ConvParams p = base(1, 0);
         p.out = buf(B_CAT1); p.out_cs = 128; p.out_c0 = 64;
         p.out2 = buf(B_P1); p.out2_cs = 64; p.out2_c0 = 0;
-        if (c->variant & 32) {
-            if (launch_conv<64, 9, 2, true, EPI_RELU_POOL, 10, TSV(1), 2>(c, 10, pl->tmA[1], c->tmWh[1], pl->tmO[1], pl->tmO2[1], p, st)) return 1;
+        if (pick_split(c, tiles(0), 64, 2, 2)) {  // one tile per CTA, weights resident
+            if (launch_conv<64, 9, 1, true, EPI_RELU_POOL, 10, 1>(c, 24, pl->tmA[1], c->tmW[1], pl->tmO[1], pl->tmO2[1], p, st)) return 1;
         } else {
-            if (launch_conv<64, 9, 2, true, EPI_RELU_POOL, 10, TSV(1)>(c, 0, pl->tmA[1], c->tmW[1], pl->tmO[1], pl->tmO2[1], p, st)) return 1;
+            if (launch_conv<64, 9, 2, true, EPI_RELU_POOL, 10, 1, 2>(c, 10, pl->tmA[1], c->tmWh[1], pl->tmO[1], pl->tmO2[1], p, st)) return 1;
         }
     }
     if (prof_mark(c, st)) return 1;
     {  // L2 down2.0 -> a2
         ConvParams p = base(2, 1);
         p.out = buf(B_A2); p.out_cs = 128; p.out_c0 = 0;
-        // CTA pair: the resident weights (147 KB) only fit next to the staging buffers when halved
-        if (launch_conv<128, 9, 1, true, EPI_RELU, 10, TSV(1), 2>(c, 11, pl->tmA[2], c->tmWh[2], pl->tmO[2], pl->tmO[2], p, st)) return 1;
+        if (pick_split(c, tiles(1), 128, 1, 2)) {
+            if (split_relu(2, p)) return 1;
+        } else {  // CTA pair: the resident weights (147 KB) only fit next to the staging buffers when halved
+            if (launch_conv<128, 9, 1, true, EPI_RELU, 10, 1, 2>(c, 11, pl->tmA[2], c->tmWh[2], pl->tmO[2], pl->tmO[2], p, st)) return 1;
+        }
     }
     if (prof_mark(c, st)) return 1;
     {  // L3 down2.2 -> cat2[:,128:256] + p2
         ConvParams p = base(3, 1);
         p.out = buf(B_CAT2); p.out_cs = 256; p.out_c0 = 128;
         p.out2 = buf(B_P2); p.out2_cs = 128; p.out2_c0 = 0;
-        if (c->variant & 2) {
-            if (launch_conv<128, 9, 2, false, EPI_RELU_POOL, 10, TSV(1), 2>(c, 12, pl->tmA[3], c->tmWh[3], pl->tmO[3], pl->tmO2[3], p, st)) return 1;
+        if (pick_split(c, tiles(1), 128, 2, 2)) {
+            if (split_pool(3, p)) return 1;
         } else {
-            if (launch_conv<128, 9, 2, false, EPI_RELU_POOL, 10, TSV(1)>(c, 2, pl->tmA[3], c->tmW[3], pl->tmO[3], pl->tmO2[3], p, st)) return 1;
+            if (launch_conv<128, 9, 2, false, EPI_RELU_POOL, 10, 1, 2>(c, 12, pl->tmA[3], c->tmWh[3], pl->tmO[3], pl->tmO2[3], p, st)) return 1;
         }
     }
     if (prof_mark(c, st)) return 1;
-    {  // L4 bottleneck.0 -> b0
-        ConvParams p = base(4, 2);
-        p.out = buf(B_B0); p.out_cs = 256; p.out_c0 = 0;
-        if (c->variant & 16) {
-            if (launch_conv<256, 9, 1, false, EPI_RELU, 10, TSV(1), 2>(c, 13, pl->tmA[4], c->tmWh[4], pl->tmO[4], pl->tmO[4], p, st)) return 1;
+    for (int l = 4; l <= 5; ++l) {  // L4 bottleneck.0 -> b0, L5 bottleneck.2 -> b1
+        ConvParams p = base(l, 2);
+        p.out = buf(l == 4 ? B_B0 : B_B1); p.out_cs = 256; p.out_c0 = 0;
+        if (pick_split(c, tiles(2), 256, 1, 1)) {
+            if (split_relu(l, p)) return 1;
         } else {
-            if (launch_conv<256, 9, 1, false, EPI_RELU, 10, TSV(1)>(c, 3, pl->tmA[4], c->tmW[4], pl->tmO[4], pl->tmO[4], p, st)) return 1;
+            if (launch_conv<256, 9, 1, false, EPI_RELU, 10, 1>(c, 3, pl->tmA[l], c->tmW[l], pl->tmO[l], pl->tmO[l], p, st)) return 1;
         }
+        if (prof_mark(c, st)) return 1;
     }
-    if (prof_mark(c, st)) return 1;
-    {  // L5 bottleneck.2 -> b1
-        ConvParams p = base(5, 2);
-        p.out = buf(B_B1); p.out_cs = 256; p.out_c0 = 0;
-        if (c->variant & 16) {
-            if (launch_conv<256, 9, 1, false, EPI_RELU, 10, TSV(1), 2>(c, 13, pl->tmA[5], c->tmWh[5], pl->tmO[5], pl->tmO[5], p, st)) return 1;
-        } else {
-            if (launch_conv<256, 9, 1, false, EPI_RELU, 10, TSV(1)>(c, 3, pl->tmA[5], c->tmW[5], pl->tmO[5], pl->tmO[5], p, st)) return 1;
-        }
-    }
-    if (prof_mark(c, st)) return 1;
-    {  // L6 up2 (convT) -> cat2[:,0:128]
+    {  // L6 up2 (convT) -> cat2[:,0:128]; CTA pair: each CTA streams half of the 256 KB weight matrix per tile pair
         ConvParams p = base(6, 2);
         p.n_tiles = 2;  // 4*128 columns in tiles of 256
         p.out = buf(B_CAT2); p.out_cs = 256; p.out_c0 = 0;
-        if (c->variant & 4096) {  // CTA pair: each CTA streams half of the 256 KB weight matrix per tile pair
-            if (launch_conv<256, 1, 1, false, EPI_CONVT, 0, TSV(1), 2>(c, 20, pl->tmA[6], c->tmWh[6], pl->tmO[6], pl->tmO[6], p, st)) return 1;
-        } else {
-            if (launch_conv<256, 1, 1, false, EPI_CONVT, 0, TSV(1)>(c, 4, pl->tmA[6], c->tmW[6], pl->tmO[6], pl->tmO[6], p, st)) return 1;
-        }
+        if (launch_conv<256, 1, 1, false, EPI_CONVT, 0, 1, 2>(c, 20, pl->tmA[6], c->tmWh[6], pl->tmO[6], pl->tmO[6], p, st)) return 1;
     }
     if (prof_mark(c, st)) return 1;
-    {  // L7 upconv2.0 (reads cat2) -> u2a
-        ConvParams p = base(7, 1);
-        p.out = buf(B_U2A); p.out_cs = 128; p.out_c0 = 0;
-        if (c->variant & 2) {
-            if (launch_conv<128, 9, 2, false, EPI_RELU, 10, TSV(1), 2>(c, 14, pl->tmA[7], c->tmWh[7], pl->tmO[7], pl->tmO[7], p, st)) return 1;
+    for (int l = 7; l <= 8; ++l) {  // L7 upconv2.0 (reads cat2) -> u2a, L8 upconv2.2 -> u2b
+        ConvParams p = base(l, 1);
+        p.out = buf(l == 7 ? B_U2A : B_U2B); p.out_cs = 128; p.out_c0 = 0;
+        if (pick_split(c, tiles(1), 128, 2, 2)) {
+            if (split_relu(l, p)) return 1;
         } else {
-            if (launch_conv<128, 9, 2, false, EPI_RELU, 10, TSV(1)>(c, 5, pl->tmA[7], c->tmW[7], pl->tmO[7], pl->tmO[7], p, st)) return 1;
+            if (launch_conv<128, 9, 2, false, EPI_RELU, 10, 1, 2>(c, 14, pl->tmA[l], c->tmWh[l], pl->tmO[l], pl->tmO[l], p, st)) return 1;
         }
+        if (prof_mark(c, st)) return 1;
     }
-    if (prof_mark(c, st)) return 1;
-    {  // L8 upconv2.2 -> u2b
-        ConvParams p = base(8, 1);
-        p.out = buf(B_U2B); p.out_cs = 128; p.out_c0 = 0;
-        if (c->variant & 2) {
-            if (launch_conv<128, 9, 2, false, EPI_RELU, 10, TSV(1), 2>(c, 14, pl->tmA[8], c->tmWh[8], pl->tmO[8], pl->tmO[8], p, st)) return 1;
-        } else {
-            if (launch_conv<128, 9, 2, false, EPI_RELU, 10, TSV(1)>(c, 5, pl->tmA[8], c->tmW[8], pl->tmO[8], pl->tmO[8], p, st)) return 1;
-        }
-    }
-    if (prof_mark(c, st)) return 1;
-    {  // L9 up1 (convT) -> cat1[:,0:64]
+    {  // L9 up1 (convT) -> cat1[:,0:64]; the whole 128 x 256 weight matrix (64 KB) stays in shared memory
         ConvParams p = base(9, 1);
         p.n_tiles = 1;  // 4*64 columns in one tile of 256
         p.out = buf(B_CAT1); p.out_cs = 128; p.out_c0 = 0;
-        if (c->variant & 8192) {  // the whole 128 x 256 weight matrix (64 KB) stays in shared memory
-            if (launch_conv<256, 1, 1, true, EPI_CONVT, 0, TSV(1)>(c, 21, pl->tmA[9], c->tmW[9], pl->tmO[9], pl->tmO[9], p, st)) return 1;
-        } else {
-            if (launch_conv<256, 1, 1, false, EPI_CONVT, 0, TSV(1)>(c, 4, pl->tmA[9], c->tmW[9], pl->tmO[9], pl->tmO[9], p, st)) return 1;
-        }
+        if (launch_conv<256, 1, 1, true, EPI_CONVT, 0, 1>(c, 21, pl->tmA[9], c->tmW[9], pl->tmO[9], pl->tmO[9], p, st)) return 1;
     }
     if (prof_mark(c, st)) return 1;
-    {  // L10 upconv1.0 (reads cat1) -> u1a
+    {  // L10 upconv1.0 (reads cat1) -> u1a; CTA pair (resident weights halved: 74 KB per CTA)
         ConvParams p = base(10, 0);
         p.out = buf(B_U1A); p.out_cs = 64; p.out_c0 = 0;
-        // CTA pair (resident weights halved: 74 KB per CTA)
-        if (launch_conv<64, 9, 1, true, EPI_RELU, 10, TSV(1), 2>(c, 15, pl->tmA[10], c->tmWh[10], pl->tmO[10], pl->tmO[10], p, st)) return 1;
+        if (launch_conv<64, 9, 1, true, EPI_RELU, 10, 1, 2>(c, 15, pl->tmA[10], c->tmWh[10], pl->tmO[10], pl->tmO[10], p, st)) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L11 upconv1.2 + tanh -> y   (transposed GEMM: weights on M, the halo patch on N)
         LastParams lp;
-        memset(&lp, 0, sizeof(lp));
-        lp.B = nb; lp.H = H; lp.W = W;
-        lp.tiles_x = (W + 7) / 8;
-        lp.tiles_y = (H + 15) / 16;
-        lp.m_tiles = nb * lp.tiles_x * lp.tiles_y;
-        lp.stages = std::min(kLastMaxStages, (c->max_smem - last_conv_smem(0)) / kLastStageBytes);
-        CID_REQUIRE(lp.stages >= 2, "last conv: shared memory too small");
-        lp.bias = c->bias_dev[11];
-        lp.out = io.y;
-        lp.crop_l = io.pad_l; lp.crop_t = io.pad_t; lp.out_h = io.in_h; lp.out_w = io.in_w;
+        if (make_last_params(c, pl, nb, io, &lp)) return 1;
         const int smem = last_conv_smem(lp.stages);
         if (!(c->attr_done & (1u << 29))) {
             CID_CHECK_CUDA(cudaFuncSetAttribute(last_conv_umma_kernel<EPI_TANH_U8>, cudaFuncAttributeMaxDynamicSharedMemorySize, c->max_smem));
@@ -620,6 +624,126 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         c->launches++;
     }
     if (prof_mark(c, st)) return 1;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// CUDA-graph replay of one pass (small batches only). A batch-1 forward is 12 launches of a few microseconds
+// each: the host's launch calls, not the kernels, would set the pace. The first pass of a plan runs eagerly
+// (it also sets the kernels' attributes), the second is captured on the context's own stream - with the
+// programmatic-dependent-launch edges between the layers - and from then on a pass is ONE cudaGraphLaunch into
+// the caller's stream. The caller's input / output pointers and padding live in the parameters of the first and
+// last kernel node: when they change, those two nodes are updated in the instantiated graph (no re-capture).
+// ---------------------------------------------------------------------------------------------
+static bool same_io(const IoSpec& a, const IoSpec& b) {
+    return a.u8 == b.u8 && a.x == b.x && a.y == b.y && a.in_h == b.in_h && a.in_w == b.in_w && a.pad_l == b.pad_l &&
+           a.pad_t == b.pad_t;
+}
+
+static bool graph_wanted(const cid_ctx* c, const cid_plan* pl, int nb) {
+    if (!c->use_graph || c->profile || c->graph_broken || nb != pl->Bc) return false;
+    return static_cast<size_t>(nb) * pl->H * pl->W <= (1u << 20);  // longer passes are not launch-bound
+}
+
+static int graph_capture(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cid_graph* g) {
+    if (!c->capture_stream) CID_CHECK_CUDA(cudaStreamCreateWithFlags(reinterpret_cast<cudaStream_t*>(&c->capture_stream), cudaStreamNonBlocking));
+    cudaStream_t cs = static_cast<cudaStream_t>(c->capture_stream);
+    cudaGraph_t graph = nullptr;
+    const int64_t l0 = c->launches;
+    CID_CHECK_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+    const int rc = run_layers(c, pl, nb, io, cs);
+    const cudaError_t ee = cudaStreamEndCapture(cs, &graph);
+    g->launches = static_cast<int>(c->launches - l0);
+    c->launches = l0;
+    if (rc) {
+        if (graph) cudaGraphDestroy(graph);
+        return 1;
+    }
+    CID_CHECK_CUDA(ee);
+    cudaGraphExec_t exec = nullptr;
+    cudaError_t e = cudaGraphInstantiate(&exec, graph, 0);
+    if (e != cudaSuccess) {
+        cudaGraphDestroy(graph);
+        CID_CHECK_CUDA(e);
+    }
+    g->graph = graph;
+    g->exec = exec;
+    // the nodes that carry the caller's pointers: the first and the last kernel of the pass
+    size_t n = 0;
+    CID_CHECK_CUDA(cudaGraphGetNodes(graph, nullptr, &n));
+    std::vector<cudaGraphNode_t> nodes(n);
+    CID_CHECK_CUDA(cudaGraphGetNodes(graph, nodes.data(), &n));
+    const void* f_first = io.u8 ? reinterpret_cast<const void*>(first_conv_umma_kernel<true>)
+                                : reinterpret_cast<const void*>(first_conv_umma_kernel<false>);
+    const void* f_last = io.u8 ? reinterpret_cast<const void*>(last_conv_umma_kernel<EPI_TANH_U8>)
+                               : reinterpret_cast<const void*>(last_conv_umma_kernel<EPI_TANH_F32>);
+    int found = 0;
+    for (size_t i = 0; i < n; ++i) {
+        cudaGraphNodeType ty;
+        if (cudaGraphNodeGetType(nodes[i], &ty) != cudaSuccess || ty != cudaGraphNodeTypeKernel) continue;
+        cudaKernelNodeParams kp;
+        if (cudaGraphKernelNodeGetParams(nodes[i], &kp) != cudaSuccess) continue;
+        if (kp.func == f_first) { g->first = nodes[i]; ++found; }
+        if (kp.func == f_last) { g->last = nodes[i]; ++found; }
+    }
+    CID_REQUIRE(found == 2 && g->first && g->last, "graph: could not identify the first / last kernel node (%d)", found);
+    g->io_u8 = io.u8; g->x = io.x; g->y = io.y; g->in_h = io.in_h; g->in_w = io.in_w; g->pad_l = io.pad_l; g->pad_t = io.pad_t;
+    return 0;
+}
+
+static int graph_rebind(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cid_graph* g) {
+    cudaGraphExec_t exec = static_cast<cudaGraphExec_t>(g->exec);
+    {
+        FirstParams fp = make_first_params(c, pl, nb, io);
+        CUtensorMap tmO = pl->tmO[0];
+        void* args[2] = {&tmO, &fp};
+        cudaKernelNodeParams kp;
+        CID_CHECK_CUDA(cudaGraphKernelNodeGetParams(static_cast<cudaGraphNode_t>(g->first), &kp));
+        kp.kernelParams = args;
+        kp.extra = nullptr;
+        CID_CHECK_CUDA(cudaGraphExecKernelNodeSetParams(exec, static_cast<cudaGraphNode_t>(g->first), &kp));
+    }
+    {
+        LastParams lp;
+        if (make_last_params(c, pl, nb, io, &lp)) return 1;
+        CUtensorMap tmA = pl->tmA[11], tmW = c->tmW[11];
+        void* args[3] = {&tmA, &tmW, &lp};
+        cudaKernelNodeParams kp;
+        CID_CHECK_CUDA(cudaGraphKernelNodeGetParams(static_cast<cudaGraphNode_t>(g->last), &kp));
+        kp.kernelParams = args;
+        kp.extra = nullptr;
+        CID_CHECK_CUDA(cudaGraphExecKernelNodeSetParams(exec, static_cast<cudaGraphNode_t>(g->last), &kp));
+    }
+    g->x = io.x; g->y = io.y; g->in_h = io.in_h; g->in_w = io.in_w; g->pad_l = io.pad_l; g->pad_t = io.pad_t;
+    return 0;
+}
+
+// run_layers, or its graph replay when the pass is launch-bound
+static int run_pass(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaStream_t st) {
+    if (!graph_wanted(c, pl, nb)) return run_layers(c, pl, nb, io, st);
+    cid_graph& g = pl->graph[io.u8 ? 1 : 0];
+    if (!g.exec) {
+        if (g.eager_runs++ == 0) return run_layers(c, pl, nb, io, st);  // first pass: eager (sets kernel attributes)
+        if (graph_capture(c, pl, nb, io, &g)) {
+            // capture is an optimisation: fall back to eager launches for good, keep the reason for cid_last_error readers
+            graph_release(g);
+            c->graph_broken = true;
+            cudaGetLastError();
+            return run_layers(c, pl, nb, io, st);
+        }
+    } else {
+        IoSpec baked;
+        baked.u8 = g.io_u8; baked.x = g.x; baked.y = g.y; baked.in_h = g.in_h; baked.in_w = g.in_w; baked.pad_l = g.pad_l; baked.pad_t = g.pad_t;
+        if (!same_io(baked, io) && graph_rebind(c, pl, nb, io, &g)) {
+            graph_release(g);
+            c->graph_broken = true;
+            cudaGetLastError();
+            return run_layers(c, pl, nb, io, st);
+        }
+    }
+    CID_CHECK_CUDA(cudaGraphLaunch(static_cast<cudaGraphExec_t>(g.exec), st));
+    c->launches += g.launches;
+    c->graph_replays++;
     return 0;
 }
 
@@ -661,7 +785,7 @@ static int forward_common(cid_ctx* c, int B, int H, int W, void* ws, size_t ws_b
         const int nb = std::min(Bc, B - b0);
         io.x = x + static_cast<size_t>(b0) * x_img_bytes;
         io.y = y + static_cast<size_t>(b0) * y_img_bytes;
-        if (sr ? sr_run_layers(c, pl, nb, io, st) : cgan ? cgan_run_layers(c, pl, nb, io, st) : run_layers(c, pl, nb, io, st))
+        if (sr ? sr_run_layers(c, pl, nb, io, st) : cgan ? cgan_run_layers(c, pl, nb, io, st) : run_pass(c, pl, nb, io, st))
             return 1;
     }
     return 0;
@@ -676,7 +800,7 @@ using namespace cid;
 // =============================================================================================
 extern "C" {
 
-int cid_version(void) { return 6; }
+int cid_version(void) { return 7; }
 
 const char* cid_last_error(void) { return g_err; }
 
@@ -713,11 +837,12 @@ int cid_create_model(int device, const char* model, cid_handle* out) {
 int cid_destroy(cid_handle h) {
     if (!h) return 0;
     DeviceGuard g(h->device);
+    clear_plans(h);
+    if (h->capture_stream) cudaStreamDestroy(static_cast<cudaStream_t>(h->capture_stream));
     for (int l = 0; l < kMaxLayers; ++l) {
         if (h->w_dev[l]) cudaFree(h->w_dev[l]);
         if (h->bias_dev[l]) cudaFree(h->bias_dev[l]);
     }
-    delete static_cast<FirstConvW*>(h->first_w_host);
     delete h;
     return 0;
 }
@@ -793,7 +918,7 @@ int cid_finalize(cid_handle h) {
         for (int l = 0; l < 12; ++l)
             if (pack_layer(h, l)) return 1;
     }
-    h->plans.clear();
+    clear_plans(h);
     h->finalized = true;
     return 0;
 }
@@ -805,24 +930,20 @@ int cid_set_option(cid_handle h, const char* name, int64_t value) {
         h->chunk = value;
         return 0;
     }
-    if (!strcmp(name, "first_tc")) {
-        h->first_tc = value != 0;
+    // 0 = choose per layer (pick_split), 1 = always the batch-256 configuration, 2 = always the N-split small-batch form
+    // (the two are bit-identical; the tests use 1 / 2 to compare them at any size)
+    if (!strcmp(name, "regime")) {
+        CID_REQUIRE(value >= 0 && value <= 2, "regime must be 0 (auto), 1 (large) or 2 (split)");
+        h->regime = static_cast<int>(value);
+        for (auto& pl : h->plans) { graph_release(pl.graph[0]); graph_release(pl.graph[1]); }
         return 0;
     }
-    // bit mask of optional CTA-pair (cta_group::2) layers: 2 = down2.2/upconv2.0/upconv2.2, 16 = bottleneck.*,
-    // 32 = down1.2 (down2.0 and upconv1.0 always run as pairs), 4096 = the transposed conv up2 as a pair (half-size weight
-    // stages, twice as many in flight), 8192 = up1 with its 64 KB of weights resident in shared memory. Default
-    // 2 | 32 | 4096 | 8192: where it measured faster.
-    if (!strcmp(name, "variant")) {
-        h->variant = static_cast<int>(value);
+    if (!strcmp(name, "graph")) {  // CUDA-graph replay of launch-bound passes (default on)
+        h->use_graph = value != 0;
         return 0;
     }
     if (!strcmp(name, "pdl")) {  // programmatic dependent launch between consecutive layers (default on)
         h->pdl = value != 0;
-        return 0;
-    }
-    if (!strcmp(name, "debug_flags")) {
-        h->debug_flags = static_cast<int>(value);
         return 0;
     }
     if (!strcmp(name, "profile")) {
@@ -969,6 +1090,10 @@ int cid_debug_copy_activation(cid_handle h, const char* name, const void* ws, in
 // =============================================================================================
 // training step
 // =============================================================================================
+static const char* const kPeerFaultMsg =
+    "a data-parallel peer did not reach the fused all-reduce barrier in time: that optimiser step and every later one were "
+    "skipped (weights untouched from the fault on); the replicas may differ - restore a checkpoint on every rank";
+
 int cid_train_create(int device, cid_train_handle* out) {
     CID_REQUIRE(out, "cid_train_create: out is NULL");
     *out = nullptr;
@@ -976,9 +1101,7 @@ int cid_train_create(int device, cid_train_handle* out) {
     if (cid_create_model(device, "denoise", &g)) return 1;
     cid_train* t = new cid_train();
     t->g = g;
-    // data-gradient kernels with resident weights / as CTA pairs (measured 7.07 -> 6.96 ms per iteration), weight-gradient
-    // MMAs tap-fused to N = 192 (6.34 -> 6.23 ms)
-    g->variant |= 64 | 128 | 1024;
+    g->use_graph = false;  // the training step launches run_layers directly (its buffers are read back by the backward pass)
     t->device = device;
     t->num_sms = g->num_sms;
     t->max_smem = g->max_smem;
@@ -1005,6 +1128,7 @@ int cid_train_destroy(cid_train_handle t) {
         }
         if (t->zero_bias) cudaFree(t->zero_bias);
         if (t->peer_err) cudaFree(t->peer_err);
+        if (t->peer_err_host) cudaFreeHost(t->peer_err_host);
         if (t->dsc) cudaFree(t->dsc);
         if (t->fsc) cudaFree(t->fsc);
     }
@@ -1015,7 +1139,12 @@ int cid_train_destroy(cid_train_handle t) {
 
 int cid_train_set_option(cid_train_handle t, const char* name, int64_t value) {
     CID_REQUIRE(t && name, "cid_train_set_option: null argument");
-    return cid_set_option(t->g, name, value);  // "variant" (bits 64 / 128: data-gradient kernels as CTA pairs), "pdl", ...
+    if (!strcmp(name, "peer_timeout_ms")) {  // fused all-reduce: how long a block waits for a peer before it reports a fault
+        CID_REQUIRE(value >= 1, "peer_timeout_ms must be >= 1");
+        t->peer_spin_ns = static_cast<unsigned long long>(value) * 1000000ull;
+        return 0;
+    }
+    return cid_set_option(t->g, name, value);  // "pdl", ...
 }
 
 int cid_train_state_floats(cid_train_handle t, size_t* n) {
@@ -1153,6 +1282,7 @@ int cid_train_adam(cid_train_handle t, int which, float lr, float beta1, float b
     const float bc2 = sqrtf(1.f - powf(beta2, static_cast<float>(step)));
     if (t->peer_world > 1) {
         // gradient all-reduce fused into the optimiser step over NVLink peer memory (adam_allreduce_kernel)
+        CID_REQUIRE(*reinterpret_cast<volatile int*>(t->peer_err_host) == 0, "%s", kPeerFaultMsg);
         PeerSet ps;
         memset(&ps, 0, sizeof(ps));
         ps.world = t->peer_world;
@@ -1162,7 +1292,8 @@ int cid_train_adam(cid_train_handle t, int which, float lr, float beta1, float b
             ps.flags[r] = t->peer_flags[r];
         }
         adam_allreduce_kernel<<<kPeerBlocks, 256, 0, st>>>(t->state + off, t->state + 2 * P + off, t->state + 3 * P + off, n, ps,
-                                                           ++t->peer_epoch, t->peer_err, lr, beta1, beta2, eps, bc1, bc2);
+                                                           ++t->peer_epoch, t->peer_spin_ns, t->peer_err, t->peer_err_host_dev, lr, beta1, beta2, eps, bc1,
+                                                           bc2);
     } else {
         launch_k(t->g->pdl, adam_kernel, static_cast<unsigned>((n + 255) / 256), 256, 0, st, t->state + off, t->state + P + off, t->state + 2 * P + off,
                                                                             t->state + 3 * P + off, n, lr, beta1, beta2, eps, bc1, bc2);
@@ -1191,10 +1322,19 @@ int cid_train_set_peers(cid_train_handle t, int world, int rank, const void* con
         t->peer_state[r] = static_cast<const float*>(state_ptrs[r]);
         t->peer_flags[r] = static_cast<int*>(flag_ptrs[r]);
     }
+    {   // the per-block-index barriers need every block of every rank resident at once
+        int per_sm = 0;
+        CID_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, adam_allreduce_kernel, 256, 0));
+        CID_REQUIRE(per_sm * t->num_sms >= kPeerBlocks, "fused all-reduce: %d blocks cannot be co-resident on this device (%d x %d)",
+                    kPeerBlocks, per_sm, t->num_sms);
+    }
     if (!t->peer_err) {
         CID_CHECK_CUDA(cudaMalloc(reinterpret_cast<void**>(&t->peer_err), sizeof(int)));
-        CID_CHECK_CUDA(cudaMemset(t->peer_err, 0, sizeof(int)));
+        CID_CHECK_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&t->peer_err_host), sizeof(int), cudaHostAllocMapped));
+        CID_CHECK_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&t->peer_err_host_dev), t->peer_err_host, 0));
     }
+    CID_CHECK_CUDA(cudaMemset(t->peer_err, 0, sizeof(int)));
+    *t->peer_err_host = 0;
     t->peer_world = world;
     t->peer_rank = rank;
     t->peer_epoch = 0;
@@ -1211,7 +1351,7 @@ int cid_train_losses(cid_train_handle t, double* out4) {
     if (t->peer_err) {
         int e = 0;
         CID_CHECK_CUDA(cudaMemcpy(&e, t->peer_err, sizeof(int), cudaMemcpyDeviceToHost));
-        CID_REQUIRE(e == 0, "a data-parallel peer did not reach the fused all-reduce barrier (timeout); the replicas have diverged");
+        CID_REQUIRE(e == 0 && *reinterpret_cast<volatile int*>(t->peer_err_host) == 0, "%s", kPeerFaultMsg);
     }
     out4[0] = h[0] + h[1];          // d_loss
     out4[1] = h[3] + 0.001 * h[2];  // g_loss

@@ -48,6 +48,26 @@ struct DeviceGuard {
 
 }  // namespace cid
 
+struct cid_ctx;
+namespace cid {
+void clear_plans(cid_ctx* c);  // releases the plans' graphs, then the plans
+}
+
+// CUDA-graph replay of one pass of a plan (denoise generator, small batches; cid_api.cu run_pass). Handles are kept as
+// void* so that this header stays free of graph types for the files that do not use them.
+struct cid_graph {
+    void* graph = nullptr;   // cudaGraph_t
+    void* exec = nullptr;    // cudaGraphExec_t
+    void* first = nullptr;   // cudaGraphNode_t of the first / last kernel: they carry the caller's pointers
+    void* last = nullptr;
+    int launches = 0;        // kernels per replay
+    int eager_runs = 0;
+    bool io_u8 = false;      // what is baked into those two nodes
+    const void* x = nullptr;
+    void* y = nullptr;
+    int in_h = 0, in_w = 0, pad_l = 0, pad_t = 0;
+};
+
 // One (chunk, H, W, workspace) execution plan: buffer offsets and the TMA descriptors of every
 // tensor-core layer's activation operand.
 struct cid_plan {
@@ -57,6 +77,7 @@ struct cid_plan {
     CUtensorMap tmA[12];    // indexed by layer (0 unused); ESRGAN/SRGAN: indexed by BUFFER (3x3 halo-patch map)
     CUtensorMap tmO[12];    // TMA-store maps of each layer's output buffer (box 64ch x 8px x 16 rows); SR: by buffer
     CUtensorMap tmO2[12];   // pooled output (box 64ch x 4px x 8 rows); layers 1 and 3 only; SR: 9x9 window maps by buffer
+    cid_graph graph[2];     // [fp32 NCHW entry point, u8 NHWC entry point]; released by cid::clear_plans
 };
 
 enum { CID_MODEL_DENOISE = 0, CID_MODEL_KERAS_CGAN = 1, CID_MODEL_ESRGAN = 2, CID_MODEL_SRGAN = 3 };
@@ -75,16 +96,17 @@ struct cid_ctx {
     float* bias_dev[kMaxLayers] = {nullptr};  // fp32 bias per layer
     CUtensorMap tmW[kMaxLayers];
     CUtensorMap tmWh[kMaxLayers];            // same weights, box of N/2 rows (CTA-pair kernels load half a tile each)
-    void* first_w_host = nullptr;     // cid::FirstConvW (kernel parameter block)
+    CUtensorMap tmW64[kMaxLayers];           // same weights, box of 64 rows (N-split small-batch form of the 3x3 layers)
     float slopes[kMaxLayers] = {0};   // ESRGAN / SRGAN: PReLU parameter of each layer (1 = none)
     std::vector<cid_plan> plans;
     uint32_t attr_done = 0;           // bit per kernel instantiation: max-dynamic-smem attribute set
     std::map<uint64_t, void*> resize_coeffs;  // (in_size,out_size) -> device coefficient block
+    int regime = 0;                   // "regime" option: 0 per-layer choice, 1 batch-256 configuration, 2 N-split form
+    bool use_graph = true;            // "graph" option: CUDA-graph replay of launch-bound passes
+    bool graph_broken = false;        // capture / node update failed once: eager launches from then on
+    void* capture_stream = nullptr;   // cudaStream_t the graphs are captured on (nothing ever executes on it)
+    int64_t graph_replays = 0;
     // per-layer timing ("profile" option): 13 events bracket the 12 layers of every pass
-    int debug_flags = 0;
-    int variant = 34 | 4096 | 8192;                // layers run as CTA pairs ("variant" option, see cid_set_option)
-    bool first_tc = true;             // layer 0 on tensor cores (false: CUDA-core direct conv)
-    bool patch = true;                // 3x3 layers load one halo patch per K block instead of 3 boxes
     bool pdl = true;                  // programmatic dependent launch between layers ("pdl" option)
     bool profile = false;
     std::vector<cudaEvent_t> prof_events;  // 13 per recorded pass

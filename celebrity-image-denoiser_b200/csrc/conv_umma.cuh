@@ -68,7 +68,6 @@ struct ConvParams {
                          // per channel per warp at the end); may be null
     float* out_f32;      // EPI_LRELU only: if set, the result is written as fp32 NHWC straight from registers (no bf16
                          // staging / TMA store): the discriminator's pre-BatchNorm outputs, whose mean >> std
-    int debug_flags;     // bring-up experiments only: 1 = epilogue skips global stores, 2 = skips TMEM reads too
 };
 
 // Tap geometry (TAPS):
@@ -535,7 +534,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             mbar_wait(&acc_full[buf], aph);
             tc_fence_after();
             const uint32_t tbase = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * Cfg::ACC_COLS;
-            if (!(p.debug_flags & 2)) {
+            {
                 if constexpr (EPI == EPI_RELU || EPI == EPI_RELU_POOL || EPI == EPI_LRELU || EPI == EPI_ADD || EPI == EPI_DGRAD) {
                     constexpr int SL = N / 64;  // 64-channel slabs per pixel tile
                     const int sub = (xl & 1) | ((yl & 1) << 1);
@@ -687,7 +686,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         });
                         fence_proxy_async();
                         named_bar_sync(bar_id, 128);
-                        if (issuer && !(p.debug_flags & 1) && !(EPI == EPI_LRELU && p.out_f32 != nullptr)) {
+                        if (issuer && !(EPI == EPI_LRELU && p.out_f32 != nullptr)) {
                             const int c64 = n_tile * N + cs * 64;
                             tma_store_4d(&tmO, slab, p.out_c0 + c64, tc.x0, tc.y0, tc.b);
                             if constexpr (EPI == EPI_RELU_POOL)
@@ -770,7 +769,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         });
                         fence_proxy_async();
                         named_bar_sync(bar_id, 128);
-                        if (issuer && !(p.debug_flags & 1)) {
+                        if (issuer) {
                             tma_store_5d(&tmO, slab, p.out_c0 + cs * 64, 2 * tc.x0, n_tile, tc.y0, tc.b);
                             bulk_commit();
                         }
@@ -824,7 +823,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     });
                     fence_proxy_async();
                     named_bar_sync(bar_id, 128);
-                    if (issuer && !(p.debug_flags & 1)) {
+                    if (issuer) {
                         const int dy = c64mode ? slab_i : n_tile;
                         const int c0 = p.out_c0 + (c64mode ? 0 : slab_i * 64);
                         tma_store_5d(&tmO, slab, c0, 2 * tc.x0, dy, tc.y0, tc.b);

@@ -254,8 +254,8 @@ int cid_noise_elementwise_u8(cid_handle h, const uint8_t* in, uint8_t* out, size
 }
 
 int cid_noise_salt_pepper_u8(cid_handle h, const uint8_t* in, uint8_t* out, int B, int H, int W, int C,
-                             float salt_prob, float pepper_prob, const int32_t* coords, uint64_t seed,
-                             uint64_t offset, void* stream) {
+                             double salt_prob, double pepper_prob, const int32_t* coords, int64_t coords_per_image,
+                             uint64_t seed, uint64_t offset, void* stream) {
     CID_REQUIRE(h && in && out, "cid_noise_salt_pepper_u8: null argument");
     CID_REQUIRE(B >= 0 && H >= 2 && W >= 2 && C >= 1, "bad shape B=%d H=%d W=%d C=%d", B, H, W, C);
     if (B == 0) return 0;
@@ -263,9 +263,14 @@ int cid_noise_salt_pepper_u8(cid_handle h, const uint8_t* in, uint8_t* out, int 
     CID_REQUIRE(g.ok, "cannot select CUDA device %d", h->device);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const size_t n = static_cast<size_t>(B) * H * W * C;
-    // int(total_pixels * prob) with total_pixels = image_array.size = H*W*C, float64 product
-    const int n_salt = static_cast<int>(static_cast<double>(static_cast<size_t>(H) * W * C) * static_cast<double>(salt_prob));
-    const int n_pepper = static_cast<int>(static_cast<double>(static_cast<size_t>(H) * W * C) * static_cast<double>(pepper_prob));
+    // int(total_pixels * prob) with total_pixels = image_array.size = H*W*C: a float64 product of the caller's float64
+    // probabilities, as the reference computes it (a float32 0.02 gives 599 instead of 600 draws for 100x100x3)
+    const int n_salt = static_cast<int>(static_cast<double>(static_cast<size_t>(H) * W * C) * salt_prob);
+    const int n_pepper = static_cast<int>(static_cast<double>(static_cast<size_t>(H) * W * C) * pepper_prob);
+    CID_REQUIRE(n_salt >= 0 && n_pepper >= 0, "negative salt / pepper probability");
+    CID_REQUIRE(!coords || coords_per_image == static_cast<int64_t>(n_salt) + n_pepper,
+                "coords holds %lld draws per image; this image size and these probabilities need %d salt + %d pepper",
+                static_cast<long long>(coords_per_image), n_salt, n_pepper);
     if (in != out) {
         const size_t threads = (n + 15) / 16;
         copy_u8_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, st>>>(in, out, n);

@@ -211,7 +211,7 @@ static int sr_get_plan(cid_ctx* c, int Bc, int H, int W, const void* ws, cid_pla
             *out = &pl;
             return 0;
         }
-    if (c->plans.size() >= 64) c->plans.clear();
+    if (c->plans.size() >= 64) clear_plans(c);
     cid_plan pl;
     pl.Bc = Bc;
     pl.H = H;
@@ -319,7 +319,6 @@ static int sr_run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cud
             p.cout = 64;  // SR_SHUFFLE: channels per quadrant
             p.w_rows_per_tap = l.op == SR_SHUFFLE ? 256 : 64;
             p.slope = c->slopes[li];
-            p.debug_flags = c->debug_flags;
             p.out_cs = 64;
             p.out_c0 = 0;
             p.out = buf(l.out_buf);

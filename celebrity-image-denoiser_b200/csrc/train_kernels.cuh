@@ -552,11 +552,17 @@ __global__ void __launch_bounds__(256) adam_kernel(float* w, const float* g, flo
 //   start: "my gradients are complete" (stream order puts this launch after the backward pass) -> peers may read them
 //   end:   "I have finished reading yours"                                                    -> peers may overwrite them
 // flags[phase][rank][block] live in a symmetric int buffer and hold the epoch of the last launch that passed (monotonic).
-// A spin that exceeds kPeerSpinNs records an error (err[0] = 1) and moves on instead of hanging the GPU.
+// The barriers are per block index, so all kPeerBlocks blocks of every rank must be co-resident (2 per SM on 148 SMs;
+// cid_train_set_peers checks the occupancy). A peer that has not arrived after `spin_ns` (default 10 minutes, in the
+// range of NCCL's watchdog; cid_train_set_option "peer_timeout_ms") is a fault: the block records it in the sticky
+// error words (device + pinned host mirror) and RETURNS WITHOUT TOUCHING weights, exp_avg or exp_avg_sq; every later launch
+// sees the sticky word and does nothing either, so its peers time out in turn and the error reaches every rank. The
+// host checks the mirror at every cid_train_adam / cid_train_losses call. The replicas may differ after such a fault
+// (blocks that had already passed the barrier applied their update): the caller restores a checkpoint.
 // ---------------------------------------------------------------------------------------------------------------------
 constexpr int kPeerMax = 8;
 constexpr int kPeerBlocks = 296;                       // all co-resident: the barriers are per block index
-constexpr unsigned long long kPeerSpinNs = 4000000000ull;
+constexpr unsigned long long kPeerSpinNsDefault = 600ull * 1000000000ull;
 struct PeerSet {
     const float* grads[kPeerMax];  // peers' gradient sections (this network), rank order
     int* flags[kPeerMax];          // peers' flag buffers [2][kPeerMax][kPeerBlocks]
@@ -583,7 +589,11 @@ __device__ __forceinline__ unsigned long long global_ns() {
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
 }
-__device__ __forceinline__ void peer_barrier(const PeerSet& ps, int phase, int epoch, int* err) {
+// returns false (block-uniform) if a peer did not arrive in time
+__device__ __forceinline__ bool peer_barrier(const PeerSet& ps, int phase, int epoch, unsigned long long spin_ns, int* err_dev,
+                                             int* err_host) {
+    __shared__ int timed_out;
+    if (threadIdx.x == 0) timed_out = 0;
     __syncthreads();
     if (threadIdx.x < ps.world) {
         const int slot = (phase * kPeerMax) * kPeerBlocks + blockIdx.x;
@@ -591,13 +601,17 @@ __device__ __forceinline__ void peer_barrier(const PeerSet& ps, int phase, int e
         const int* mine = ps.flags[ps.rank] + slot + threadIdx.x * kPeerBlocks;
         const unsigned long long t0 = global_ns();
         while (ld_acquire_sys(mine) < epoch) {
-            if (global_ns() - t0 > kPeerSpinNs) {
-                *err = 1;
+            if (global_ns() - t0 > spin_ns) {
+                timed_out = 1;
+                *err_dev = 1;
+                *reinterpret_cast<volatile int*>(err_host) = 1;
+                __threadfence_system();
                 break;
             }
         }
     }
     __syncthreads();
+    return timed_out == 0;
 }
 __device__ __forceinline__ void adam_update(float& w, float& m, float& v, float g, float lr_bc1, float b1, float b2, float eps,
                                             float bc2_sqrt) {
@@ -606,9 +620,10 @@ __device__ __forceinline__ void adam_update(float& w, float& m, float& v, float 
     w -= lr_bc1 * (m / (sqrtf(v) / bc2_sqrt + eps));
 }
 __global__ void __launch_bounds__(256) adam_allreduce_kernel(float* w, float* m, float* v, size_t n, const __grid_constant__ PeerSet ps,
-                                                             int epoch, int* err, float lr, float b1, float b2, float eps,
-                                                             float bc1, float bc2_sqrt) {
-    peer_barrier(ps, 0, epoch, err);
+                                                             int epoch, unsigned long long spin_ns, int* err_dev, int* err_host,
+                                                             float lr, float b1, float b2, float eps, float bc1, float bc2_sqrt) {
+    if (*reinterpret_cast<volatile int*>(err_dev) != 0) return;        // sticky: an earlier exchange failed
+    if (!peer_barrier(ps, 0, epoch, spin_ns, err_dev, err_host)) return;  // no update on a fault (see above)
     const float inv_world = 1.f / static_cast<float>(ps.world), lr_bc1 = lr / bc1;
     // the four sections share their alignment modulo 16 bytes: scalar head up to it, float4 body, scalar tail
     const size_t head = min(n, static_cast<size_t>((4 - ((reinterpret_cast<uintptr_t>(w) >> 2) & 3)) & 3));
@@ -641,7 +656,7 @@ __global__ void __launch_bounds__(256) adam_allreduce_kernel(float* w, float* m,
             adam_update(w[e], m[e], v[e], s * inv_world, lr_bc1, b1, b2, eps, bc2_sqrt);
         }
     }
-    peer_barrier(ps, 1, epoch, err);
+    peer_barrier(ps, 1, epoch, spin_ns, err_dev, err_host);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------

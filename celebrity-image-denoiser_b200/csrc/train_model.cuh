@@ -77,7 +77,10 @@ struct cid_train {
     int peer_world = 0, peer_rank = 0, peer_epoch = 0;
     const float* peer_state[8] = {nullptr};
     int* peer_flags[8] = {nullptr};
-    int* peer_err = nullptr;          // device int: a peer barrier timed out
+    int* peer_err = nullptr;          // device int, sticky: a peer barrier timed out (the fused optimiser then does nothing)
+    int* peer_err_host = nullptr;     // its pinned, device-mapped host mirror: read by the host without synchronising
+    int* peer_err_host_dev = nullptr; // the mirror's device address
+    unsigned long long peer_spin_ns = 600ull * 1000000000ull;  // = kPeerSpinNsDefault (train_kernels.cuh)
     int64_t launches = 0;
     int B = 0, H = 0, W = 0;          // shape of the last d_backward (g_backward continues from it)
     const void* ws = nullptr;
@@ -341,23 +344,15 @@ static int wgrad(cid_train* t, int geom, const void* A, int a_C, int m_ch, const
     p.B = B; p.H = H; p.W = W;
     p.out = out;
     p.bias_out = bias_out;
-    p.fuse_taps = (geom == 0 && (t->g->variant & 1024)) ? 1 : 0;  // "variant" bit 1024: N = 192 tap-fused MMAs
-    // "variant" bit 256: 3x3 stride-1 layers as clusters of 3 CTAs with TMA multicast; bit 512: ... with N = 64 per CTA
-    const bool cl3 = geom == 0 && (t->g->variant & 256);
-    const int NA = m_ch >= 128 ? 2 : 1, NB = (n_ch >= 128 && !(cl3 && (t->g->variant & 512))) ? 2 : 1;
+    p.fuse_taps = geom == 0 ? 1 : 0;  // 3x3 stride-1 layers: the three taps of a patch row as ONE N = 192 MMA (6.34 -> 6.23 ms)
+    const int NA = m_ch >= 128 ? 2 : 1, NB = n_ch >= 128 ? 2 : 1;
     wgrad_roles(p, geom, m_ch, n_ch, NA, NB);
     const CUtensorMap* tmA = tmap(t, A, B, H, W, a_C, 16, 8, 0);
-    const CUtensorMap* tmB = geom == 0   ? tmap(t, Bt, B, H, W, b_C, cl3 ? 18 : 16, 10, 0)
+    const CUtensorMap* tmB = geom == 0   ? tmap(t, Bt, B, H, W, b_C, 16, 10, 0)
                              : geom == 3 ? tmap(t, Bt, B, H, W, b_C, 16, 8, 0)
                                          : tmap(t, Bt, B, 2 * H, 2 * W, b_C, 16, p.pw, 1);
     if (!tmA || !tmB) return 1;
     const int T = geom == 0 ? 3 : geom == 1 ? 2 : 1;
-    if (cl3) {
-#define CID_WG3(na, nb) \
-    if (NA == na && NB == nb) return launch_wgrad<na, nb, 3, 3>(t, *tmA, *tmB, p, st);
-        CID_WG3(1, 1) CID_WG3(1, 2) CID_WG3(2, 1) CID_WG3(2, 2)
-#undef CID_WG3
-    }
 #define CID_WG(na, nb, tt) \
     if (NA == na && NB == nb && T == tt) return launch_wgrad<na, nb, tt>(t, *tmA, *tmB, p, st);
     CID_WG(1, 1, 3) CID_WG(1, 2, 3) CID_WG(2, 1, 3) CID_WG(2, 2, 3)
@@ -585,15 +580,15 @@ static int dgrad3x3(const TrainRun& r, int lv, const void* dz, int k_ch, const C
     ConvParams p = conv_base(r, lv, k_ch, n_ch);
     p.out = dx; p.out_cs = n_ch; p.out_c0 = 0;
     p.res2 = mask; p.res2_cs = mask_cs;
-    const int pair = t->g->variant;  // bit 64: N = 64 layers with resident weights (pairs for K = 128), bit 128: N = 128 as pairs
+    // (resident weights / CTA pairs where the forward's layers use them: measured 7.07 -> 6.96 ms per iteration)
     if (n_ch == 64) {
         // resident weights as the forward's N = 64 layers: 74 KB for K = 64; K = 128 only fits halved, as a CTA pair
-        if ((pair & 64) && k_ch == 64) return launch_conv_t<64, 9, 2, true, EPI_DGRAD, 10, 1>(t, *tmA, tmW, *tmO, p, r.st);
-        if ((pair & 64) && k_ch == 128 && tmWh) return launch_conv_t<64, 9, 2, true, EPI_DGRAD, 10, 1, 2>(t, *tmA, *tmWh, *tmO, p, r.st);
+        if (k_ch == 64) return launch_conv_t<64, 9, 2, true, EPI_DGRAD, 10, 1>(t, *tmA, tmW, *tmO, p, r.st);
+        if (k_ch == 128 && tmWh) return launch_conv_t<64, 9, 2, true, EPI_DGRAD, 10, 1, 2>(t, *tmA, *tmWh, *tmO, p, r.st);
         return launch_conv_t<64, 9, 2, false, EPI_DGRAD, 10, 1>(t, *tmA, tmW, *tmO, p, r.st);
     }
     if (n_ch == 128) {
-        if ((pair & 128) && tmWh) return launch_conv_t<128, 9, 2, false, EPI_DGRAD, 10, 1, 2>(t, *tmA, *tmWh, *tmO, p, r.st);
+        if (tmWh) return launch_conv_t<128, 9, 2, false, EPI_DGRAD, 10, 1, 2>(t, *tmA, *tmWh, *tmO, p, r.st);
         return launch_conv_t<128, 9, 2, false, EPI_DGRAD, 10, 1>(t, *tmA, tmW, *tmO, p, r.st);
     }
     if (n_ch == 256) return launch_conv_t<256, 9, 1, false, EPI_DGRAD, 10, 1>(t, *tmA, tmW, *tmO, p, r.st);

@@ -77,6 +77,10 @@ class _Engine:
         self._ws_key = None
 
     def upload(self, state: Dict[str, torch.Tensor], shapes: Optional[Dict[str, Tuple[int, ...]]] = None):
+        # cid_set_param copies with a blocking cudaMemcpy (legacy default stream); parameters written on the caller's
+        # current non-blocking side stream (load_state_dict / an optimizer step / .to() under torch.cuda.stream) must
+        # have landed before that copy reads them
+        torch.cuda.current_stream(self.device_index).synchronize()
         for key, shape in (shapes or STATE_DICT_SHAPES).items():
             t = state[key].detach()
             if t.dtype != torch.float32 or not t.is_contiguous():
@@ -113,7 +117,148 @@ class _Engine:
         return list(ms), int(n.value)
 
 
-class DenoiseGenerator(nn.Module):
+class _CudaGenerator(nn.Module):
+    """Engine plumbing shared by the generators of PT_MODELS (backend/app.py:319-324): one C-ABI handle per
+    device, lazy re-pack of the parameters when they change, `net(x)` and the fused uint8 route path."""
+
+    MODEL = "denoise"     # cid_create_model name
+    OUT_SCALE = 1         # spatial scale of the output
+    PADS_INPUT = True     # forward_u8 feeds the padded frame (ESRGAN feeds the un-padded image, backend/app.py:387-390)
+    EVAL_ONLY = False     # modules with BatchNorm: only the eval-mode (folded) form exists
+    LAYER_NAMES: Tuple[str, ...] = ()
+    PARAM_SHAPES: Optional[Dict[str, Tuple[int, ...]]] = None  # None: every floating-point state_dict entry
+
+    def _init_engine_state(self):
+        self._engines: Dict[int, _Engine] = {}
+        self._options: Dict[str, int] = {}
+        self._slots = None
+
+    # ---- change detection ------------------------------------------------------------------------
+    # forward() re-packs the weights when a parameter was loaded, moved or modified since the last pack. The check
+    # walks a cached list of (owner dict, name) slots - tensor identity, storage pointer and version counter - instead
+    # of rebuilding state_dict() on every call (that alone cost tens of microseconds on a ~100 us batch-1 forward).
+    def _param_slots(self):
+        if self._slots is None:
+            slots = []
+            for prefix, mod in self.named_modules():
+                for store in (mod._parameters, mod._buffers):
+                    for name, t in store.items():
+                        if t is None or not t.dtype.is_floating_point:
+                            continue
+                        key = f"{prefix}.{name}" if prefix else name
+                        if self.PARAM_SHAPES is None or key in self.PARAM_SHAPES:
+                            slots.append((key, store, name))
+            self._slots = slots
+        return self._slots
+
+    def _signature(self):
+        sig = []
+        for _, store, name in self._param_slots():
+            t = store[name]
+            sig.append((id(t), t.data_ptr(), t._version))
+        return tuple(sig)
+
+    def _float_state(self) -> Dict[str, torch.Tensor]:
+        return {key: store[name].detach() for key, store, name in self._param_slots()}
+
+    def _engine(self, device: torch.device) -> _Engine:
+        if device.type != "cuda":
+            raise RuntimeError(f"{type(self).__name__} (B200-native) runs only on CUDA tensors; there is no CPU fallback")
+        if self.EVAL_ONLY and self.training:
+            raise RuntimeError(f"{type(self).__name__} (B200-native) implements eval-mode BatchNorm only; call .eval() "
+                               "as the route does (backend/app.py:391, 423)")
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        eng = self._engines.get(idx)
+        if eng is None:
+            eng = _Engine(idx, self.MODEL)
+            for k, v in self._options.items():
+                eng.set_option(k, v)
+            self._engines[idx] = eng
+        sig = self._signature()
+        if eng.signature != sig:  # parameters were loaded / moved / modified since the last pack
+            state = self._float_state()
+            eng.upload(state, self.PARAM_SHAPES or {k: tuple(v.shape) for k, v in state.items()})
+            eng.signature = sig
+        return eng
+
+    def set_option(self, name: str, value: int):
+        """Forwarded to cid_set_option (e.g. "chunk")."""
+        self._options[name] = int(value)
+        for eng in self._engines.values():
+            eng.set_option(name, value)
+        return self
+
+    def kernel_launches(self) -> int:
+        return sum(e.launches() for e in self._engines.values())
+
+    def release_workspace(self) -> None:
+        """Drop the cached activation workspace(s); the next forward allocates what it needs."""
+        for e in self._engines.values():
+            e._ws, e._ws_key = None, None
+
+    def profile_read(self):
+        """(per-layer summed ms dict, passes) since the last read; needs set_option("profile", 1)."""
+        eng = next(iter(self._engines.values()))
+        ms, n = eng.profile_read()
+        return dict(zip(self.LAYER_NAMES, ms)), n
+
+    # ---- the reference's call: y = net(x) (backend/app.py:393, 433) --------------------------------
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if x.dim() != 4 or x.size(1) != 3:
+            raise RuntimeError(f"expected input [B,3,H,W], got {tuple(x.shape)}")
+        eng = self._engine(x.device)
+        if x.dtype != torch.float32 or not x.is_contiguous():
+            x = x.float().contiguous()
+        B, _, H, W = x.shape
+        s = self.OUT_SCALE
+        y = torch.empty((B, 3, H * s, W * s), dtype=torch.float32, device=x.device)
+        if B == 0 or H == 0 or W == 0:
+            return y
+        ws = eng.workspace(B, H, W)
+        wp, wn = eng.ws_ptr(ws)
+        stream = torch.cuda.current_stream(x.device).cuda_stream
+        with torch.cuda.device(x.device):
+            _lib.check(eng.lib.cid_forward_f32_nchw(eng.handle, C.c_void_p(x.data_ptr()), C.c_void_p(y.data_ptr()),
+                                                    B, H, W, C.c_void_p(wp), wn, C.c_void_p(stream)),
+                       "cid_forward_f32_nchw")
+        return y
+
+    # ---- fused route path: u8 NHWC image(s) in -> u8 NHWC image(s) out -----------------------------
+    def forward_u8(self, x: torch.Tensor, padding: Tuple[int, int, int, int] = (0, 0, 0, 0),
+                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """x: CUDA uint8 NHWC [B,H,W,3] (the un-padded upload); padding = get_padding()'s (l,t,r,b) for this model.
+        denoise: returns [B,H,W,3] = pad -> normalise -> generator -> denorm -> clamp -> truncating x255 -> crop, as
+        backend/app.py:383-480 does. ESRGAN: returns [B,H,W,3] - the route feeds the un-padded image and crops the
+        result at the padding offsets (:387-397, 473-479). SRGAN: returns [B,4(H+t+b),4(W+l+r),3], not cropped (:480-485)."""
+        if x.dim() != 4 or x.size(3) != 3 or x.dtype != torch.uint8:
+            raise RuntimeError(f"expected uint8 input [B,H,W,3], got {x.dtype} {tuple(x.shape)}")
+        eng = self._engine(x.device)
+        x = x.contiguous()
+        B, H, W, _ = x.shape
+        l, t, r, b = (int(v) for v in padding)
+        s = self.OUT_SCALE
+        shape = (B, H, W, 3) if s == 1 else (B, s * (H + t + b), s * (W + l + r), 3)
+        y = out if out is not None else torch.empty(shape, dtype=torch.uint8, device=x.device)
+        if tuple(y.shape) != shape or y.dtype != torch.uint8 or not y.is_contiguous() or y.device != x.device:
+            raise RuntimeError(f"out must be a contiguous uint8 tensor of shape {shape} on the input's device")
+        if B == 0:
+            return y
+        ws = eng.workspace(B, H + t + b, W + l + r) if self.PADS_INPUT else eng.workspace(B, H, W)
+        wp, wn = eng.ws_ptr(ws)
+        stream = torch.cuda.current_stream(x.device).cuda_stream
+        with torch.cuda.device(x.device):
+            _lib.check(eng.lib.cid_forward_u8_nhwc(eng.handle, C.c_void_p(x.data_ptr()), C.c_void_p(y.data_ptr()),
+                                                   B, H, W, l, t, r, b, C.c_void_p(wp), wn, C.c_void_p(stream)),
+                       "cid_forward_u8_nhwc")
+        return y
+
+
+class DenoiseGenerator(_CudaGenerator):
+    MODEL = "denoise"
+    PARAM_SHAPES = STATE_DICT_SHAPES
+    LAYER_NAMES = ("down1.0", "down1.2", "down2.0", "down2.2", "bottleneck.0", "bottleneck.2", "up2", "upconv2.0",
+                   "upconv2.2", "up1", "upconv1.0", "upconv1.2")
+
     def __init__(self):
         super().__init__()
         for name, spec, last_relu in _BLOCKS:
@@ -126,95 +271,7 @@ class DenoiseGenerator(nn.Module):
                 if last_relu or i + 1 < len(spec):
                     mods.append(nn.ReLU())
             self.add_module(name, nn.Sequential(*mods))
-        self._engines: Dict[int, _Engine] = {}
-        self._options: Dict[str, int] = {}
-
-    # ---- engine plumbing -------------------------------------------------------------------
-    def _signature(self):
-        return tuple((k, v.data_ptr(), v._version) for k, v in self.state_dict(keep_vars=True).items())
-
-    def _engine(self, device: torch.device) -> _Engine:
-        if device.type != "cuda":
-            raise RuntimeError(
-                "DenoiseGenerator (B200-native) runs only on CUDA tensors; there is no CPU fallback")
-        idx = device.index if device.index is not None else torch.cuda.current_device()
-        eng = self._engines.get(idx)
-        if eng is None:
-            eng = _Engine(idx)
-            for k, v in self._options.items():
-                eng.set_option(k, v)
-            self._engines[idx] = eng
-        sig = self._signature()
-        if eng.signature != sig:  # parameters were loaded / moved / modified since the last pack
-            eng.upload(self.state_dict())
-            eng.signature = sig
-        return eng
-
-    def set_option(self, name: str, value: int) -> "DenoiseGenerator":
-        """Forwarded to cid_set_option (e.g. "chunk")."""
-        self._options[name] = int(value)
-        for eng in self._engines.values():
-            eng.set_option(name, value)
-        return self
-
-    def kernel_launches(self) -> int:
-        return sum(e.launches() for e in self._engines.values())
-
-    LAYER_NAMES = ("down1.0", "down1.2", "down2.0", "down2.2", "bottleneck.0", "bottleneck.2", "up2", "upconv2.0",
-                   "upconv2.2", "up1", "upconv1.0", "upconv1.2")
-
-    def profile_read(self):
-        """(per-layer summed ms dict, passes) since the last read; needs set_option("profile", 1)."""
-        eng = next(iter(self._engines.values()))
-        ms, n = eng.profile_read()
-        return dict(zip(self.LAYER_NAMES, ms)), n
-
-    # ---- the reference's call: y = net(x) (backend/app.py:433) -----------------------------
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
-        if x.dim() != 4 or x.size(1) != 3:
-            raise RuntimeError(f"expected input [B,3,H,W], got {tuple(x.shape)}")
-        eng = self._engine(x.device)
-        if x.dtype != torch.float32 or not x.is_contiguous():
-            x = x.float().contiguous()
-        B, _, H, W = x.shape
-        y = torch.empty_like(x)
-        if B == 0:
-            return y
-        ws = eng.workspace(B, H, W)
-        wp, wn = eng.ws_ptr(ws)
-        stream = torch.cuda.current_stream(x.device).cuda_stream
-        with torch.cuda.device(x.device):
-            _lib.check(eng.lib.cid_forward_f32_nchw(eng.handle, C.c_void_p(x.data_ptr()), C.c_void_p(y.data_ptr()),
-                                                    B, H, W, C.c_void_p(wp), wn, C.c_void_p(stream)),
-                       "cid_forward_f32_nchw")
-        return y
-
-    # ---- fused route path: u8 image(s) in -> u8 image(s) out -------------------------------
-    def forward_u8(self, x: torch.Tensor, padding: Tuple[int, int, int, int] = (0, 0, 0, 0),
-                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """x: CUDA uint8 NHWC [B,H,W,3] (un-padded). padding = get_padding()'s (l,t,r,b).
-        Returns uint8 NHWC [B,H,W,3]: pad -> normalise -> generator -> denorm -> clamp ->
-        truncating x255 -> crop, as backend/app.py:383-480 does for model=denoise."""
-        if x.dim() != 4 or x.size(3) != 3 or x.dtype != torch.uint8:
-            raise RuntimeError(f"expected uint8 input [B,H,W,3], got {x.dtype} {tuple(x.shape)}")
-        eng = self._engine(x.device)
-        x = x.contiguous()
-        B, H, W, _ = x.shape
-        l, t, r, b = (int(v) for v in padding)
-        y = out if out is not None else torch.empty_like(x)
-        if out is not None and (out.shape != x.shape or out.dtype != torch.uint8 or not out.is_contiguous()
-                                or out.device != x.device):
-            raise RuntimeError("out must be a contiguous uint8 tensor shaped like x on the same device")
-        if B == 0:
-            return y
-        ws = eng.workspace(B, H + t + b, W + l + r)
-        wp, wn = eng.ws_ptr(ws)
-        stream = torch.cuda.current_stream(x.device).cuda_stream
-        with torch.cuda.device(x.device):
-            _lib.check(eng.lib.cid_forward_u8_nhwc(eng.handle, C.c_void_p(x.data_ptr()), C.c_void_p(y.data_ptr()),
-                                                   B, H, W, l, t, r, b, C.c_void_p(wp), wn, C.c_void_p(stream)),
-                       "cid_forward_u8_nhwc")
-        return y
+        self._init_engine_state()
 
     def debug_activation(self, name: str, x_shape: Tuple[int, int, int, int]) -> torch.Tensor:
         """Test hook: intermediate activation `name` of the last forward with input [B,3,H,W], as a

@@ -12,7 +12,7 @@ from pathlib import Path
 _LIB_PATH = Path(__file__).resolve().parent / "csrc" / "libcid_b200.so"
 _lib = None
 
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 # name -> (restype, argtypes); mirrors include/cid_b200.h one to one
 _SIGNATURES = {
@@ -36,7 +36,8 @@ _SIGNATURES = {
     "cid_noise_elementwise_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_float, C.c_float,
                                            C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p]),
     "cid_noise_salt_pepper_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
-                                           C.c_float, C.c_float, C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p]),
+                                           C.c_double, C.c_double, C.c_void_p, C.c_int64, C.c_uint64, C.c_uint64,
+                                           C.c_void_p]),
     "cid_resize_bicubic_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                         C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "cid_normalize_u8_to_f32_nchw": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,

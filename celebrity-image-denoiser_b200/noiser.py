@@ -98,14 +98,18 @@ def add_salt_pepper_noise(image: torch.Tensor, salt_prob: float = 0.02, pepper_p
         raise RuntimeError("image must be uint8 [H,W,C] or [B,H,W,C]")
     B, H, W, Cc = (1, *x.shape) if x.dim() == 3 else x.shape
     out = torch.empty_like(x)
-    cptr = None
+    cptr, per_image = None, 0
     if coords is not None:
         coords = coords.to(device=x.device, dtype=torch.int32).contiguous()
-        cptr = C.c_void_p(coords.data_ptr())
+        if coords.dim() == 2:
+            coords = coords[None]
+        if coords.dim() != 3 or coords.shape[0] != B or coords.shape[2] != 2:
+            raise RuntimeError(f"coords must be int32 [B, n_salt+n_pepper, 2], got {tuple(coords.shape)}")
+        cptr, per_image = C.c_void_p(coords.data_ptr()), int(coords.shape[1])
     stream = torch.cuda.current_stream(x.device).cuda_stream
     _lib.check(eng.lib.cid_noise_salt_pepper_u8(eng.handle, C.c_void_p(x.data_ptr()), C.c_void_p(out.data_ptr()),
-                                                B, H, W, Cc, float(salt_prob), float(pepper_prob), cptr, seed, offset,
-                                                C.c_void_p(stream)), "cid_noise_salt_pepper_u8")
+                                                B, H, W, Cc, float(salt_prob), float(pepper_prob), cptr, per_image,
+                                                seed, offset, C.c_void_p(stream)), "cid_noise_salt_pepper_u8")
     return out
 
 

@@ -7,7 +7,8 @@ CUDA kernels (cid_forward_u8_nhwc); the host only moves uint8 pixels.
 """
 from __future__ import annotations
 
-from typing import List, Optional, Sequence, Tuple
+import os
+from typing import Optional, Tuple
 
 import numpy as np
 import torch
@@ -24,60 +25,110 @@ def enhance_batch_u8(net: DenoiseGenerator, images: torch.Tensor, out: Optional[
     return net.forward_u8(images, pad, out=out)
 
 
+def set_rank_affinity(local_rank: int, local_world: int, device_index: Optional[int] = None) -> Optional[list]:
+    """Give this rank's host threads their own slice of the CPUs next to its GPU, so the pinned staging
+    buffers are first-touched on that NUMA node and the launch threads of the ranks of one box do not pile
+    up on the same cores. The CPU set comes from NVML's per-GPU affinity mask (the whole allowed set when
+    NVML is unavailable); ranks that share a set split it evenly. Returns the chosen CPUs (None if the
+    platform has no sched_setaffinity)."""
+    if not hasattr(os, "sched_setaffinity"):
+        return None
+    allowed = sorted(os.sched_getaffinity(0))
+    near = allowed
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local_rank if device_index is None else device_index)
+        words = (len(os.sched_getaffinity(0)) + 63) // 64 + 8
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = [w * 64 + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1]
+        cpus = [c for c in cpus if c in set(allowed)]
+        if cpus:
+            near = cpus
+    except Exception:
+        pass
+    if local_world > 1 and len(near) >= 2 * local_world:
+        per = len(near) // local_world
+        near = near[local_rank * per:(local_rank + 1) * per]
+    try:
+        os.sched_setaffinity(0, near)
+    except OSError:
+        return None
+    return near
+
+
 class HostPipeline:
-    """End-to-end batches from HOST memory: pinned staging, H2D, generator, D2H, double-buffered
-    over `depth` CUDA streams so the copies of one sub-batch overlap the kernels of another."""
+    """End-to-end batches from HOST memory as a three-stage pipeline: pinned host uint8 -> H2D (copy
+    stream) -> generator (compute stream) -> D2H (second copy stream) -> pinned host uint8, over
+    `depth` staging slots. The three stages of different sub-batches overlap (the two copy directions
+    use the GPU's two copy engines); one sub-batch's stages are ordered by events. All kernels run on
+    ONE compute stream, so a single generator handle / workspace serves every slot and consecutive
+    sub-batches keep the programmatic-dependent-launch chain of the layers intact.
 
-    def __init__(self, net: DenoiseGenerator, device: torch.device, sub_batch: int, H: int, W: int, depth: int = 2):
-        self.net, self.device, self.sub, self.H, self.W, self.depth = net, torch.device(device), sub_batch, H, W, depth
+    One cudaMemcpyAsync per sub-batch and direction; stage = "all" | "copy" | "compute" selects what
+    `run` really does (the last two are the copy-only / compute-only diagnostics of bench.py)."""
+
+    def __init__(self, net: DenoiseGenerator, device: torch.device, sub_batch: int, H: int, W: int, depth: int = 3):
+        self.net, self.device, self.sub, self.H, self.W = net, torch.device(device), sub_batch, H, W
+        self.depth = max(int(depth), 1)
         self.pad = get_padding((W, H), 4, 1)
-        self.streams = [torch.cuda.Stream(self.device) for _ in range(depth)]
+        self.s_in = torch.cuda.Stream(self.device)
+        self.s_run = torch.cuda.Stream(self.device)
+        self.s_out = torch.cuda.Stream(self.device)
         shape = (sub_batch, H, W, 3)
-        self.d_in = [torch.empty(shape, dtype=torch.uint8, device=self.device) for _ in range(depth)]
-        self.d_out = [torch.empty(shape, dtype=torch.uint8, device=self.device) for _ in range(depth)]
-        # one generator clone per stream is unnecessary: the workspace is reused strictly in stream
-        # order per slot, so each slot gets its own network handle + workspace instead.
-        self.nets = [net] + [self._clone(net) for _ in range(depth - 1)]
+        self.d_in = [torch.empty(shape, dtype=torch.uint8, device=self.device) for _ in range(self.depth)]
+        self.d_out = [torch.empty(shape, dtype=torch.uint8, device=self.device) for _ in range(self.depth)]
+        mk = lambda: [torch.cuda.Event() for _ in range(self.depth)]  # noqa: E731
+        self.in_ready, self.run_done, self.out_done = mk(), mk(), mk()
+        self._used = [False] * self.depth
         self._open = False
+        self._i = 0
 
-    @staticmethod
-    def _clone(net: DenoiseGenerator) -> DenoiseGenerator:
-        c = DenoiseGenerator()
-        c.load_state_dict(net.state_dict(), strict=True)
-        p = next(net.parameters())
-        c = c.to(p.device).eval()
-        for k, v in net._options.items():
-            c.set_option(k, v)
-        return c
-
-    def run(self, host_in: torch.Tensor, host_out: torch.Tensor, join: bool = True) -> Tuple[int, int]:
+    def run(self, host_in: torch.Tensor, host_out: torch.Tensor, join: bool = True, stage: str = "all") -> Tuple[int, int]:
         """host_in/host_out: pinned CPU uint8 [B,H,W,3]. Returns (h2d_bytes, d2h_bytes).
-        join=False streams batch after batch without re-joining the slot streams in between (each slot's staging
-        buffers are reused strictly in its own stream's order); call finish() before reading the last results."""
+        join=False streams batch after batch without re-joining the pipeline in between (each slot's staging
+        buffers are reused strictly in event order); call finish() before reading the last results."""
         B = host_in.shape[0]
+        if B == 0:
+            return 0, 0
+        do_copy, do_run = stage in ("all", "copy"), stage in ("all", "compute")
         cur = torch.cuda.current_stream(self.device)
         if join or not self._open:
-            for s in self.streams:
+            for s in (self.s_in, self.s_run, self.s_out):
                 s.wait_stream(cur)
             self._open = True
-        i = 0
         for b0 in range(0, B, self.sub):
             nb = min(self.sub, B - b0)
-            slot = i % self.depth
-            with torch.cuda.stream(self.streams[slot]):
-                self.d_in[slot][:nb].copy_(host_in[b0:b0 + nb], non_blocking=True)
-                self.nets[slot].forward_u8(self.d_in[slot][:nb], self.pad, out=self.d_out[slot][:nb])
-                host_out[b0:b0 + nb].copy_(self.d_out[slot][:nb], non_blocking=True)
-            i += 1
+            k = self._i % self.depth
+            self._i += 1
+            with torch.cuda.stream(self.s_in):
+                if self._used[k]:
+                    self.s_in.wait_event(self.run_done[k])   # the kernels that read d_in[k] last time are done
+                if do_copy:
+                    self.d_in[k][:nb].copy_(host_in[b0:b0 + nb], non_blocking=True)
+                self.in_ready[k].record(self.s_in)
+            with torch.cuda.stream(self.s_run):
+                self.s_run.wait_event(self.in_ready[k])
+                if self._used[k]:
+                    self.s_run.wait_event(self.out_done[k])  # d_out[k]'s previous result has left the device
+                if do_run:
+                    self.net.forward_u8(self.d_in[k][:nb], self.pad, out=self.d_out[k][:nb])
+                self.run_done[k].record(self.s_run)
+            with torch.cuda.stream(self.s_out):
+                self.s_out.wait_event(self.run_done[k])
+                if do_copy:
+                    host_out[b0:b0 + nb].copy_(self.d_out[k][:nb], non_blocking=True)
+                self.out_done[k].record(self.s_out)
+            self._used[k] = True
         if join:
             self.finish()
         n = B * self.H * self.W * 3
-        return n, n
+        return (n, n) if do_copy else (0, 0)
 
     def finish(self) -> None:
-        """Make the caller's current stream wait for everything the slot streams have been given."""
+        """Make the caller's current stream wait for everything the pipeline has been given."""
         cur = torch.cuda.current_stream(self.device)
-        for s in self.streams:
+        for s in (self.s_in, self.s_run, self.s_out):
             cur.wait_stream(s)
         self._open = False
 
@@ -87,7 +138,11 @@ def enhance_batch_host(net: DenoiseGenerator, host_images: torch.Tensor, device=
     """host_images: CPU uint8 [B,H,W,3] (pinned for full speed). Returns CPU uint8 [B,H,W,3]."""
     B, H, W, _ = host_images.shape
     if host_out is None:
-        host_out = torch.empty_like(host_images).pin_memory()
+        host_out = torch.empty_like(host_images)
+        if B:
+            host_out = host_out.pin_memory()
+    if B == 0:
+        return host_out
     pipe = HostPipeline(net, torch.device(device), min(sub_batch, B), H, W)
     pipe.run(host_images, host_out)
     torch.cuda.current_stream(torch.device(device)).synchronize()

@@ -27,24 +27,17 @@ class DenoiseDiscriminator(nn.Module):
     """Parameter container with the reference's module tree (training.py:77-98). The forward pass only exists inside
     the training step (train-mode BatchNorm on the tensor-core path); calling the module directly raises."""
 
+    # (kind, arguments) per Sequential slot: the indices - hence the state_dict keys model.0.weight ... model.12.bias -
+    # are the reference's (training.py:79-94)
+    _SPEC = (("conv", 3, 64, 1), ("lrelu",), ("conv", 64, 64, 2), ("bn", 64), ("lrelu",), ("conv", 64, 128, 1), ("bn", 128),
+             ("lrelu",), ("conv", 128, 128, 2), ("bn", 128), ("lrelu",), ("pool",), ("head", 128, 1), ("sigmoid",))
+
     def __init__(self):
         super().__init__()
-        self.model = nn.Sequential(
-            nn.Conv2d(3, 64, kernel_size=3, padding=1),
-            nn.LeakyReLU(0.2),
-            nn.Conv2d(64, 64, kernel_size=3, stride=2, padding=1),
-            nn.BatchNorm2d(64),
-            nn.LeakyReLU(0.2),
-            nn.Conv2d(64, 128, kernel_size=3, padding=1),
-            nn.BatchNorm2d(128),
-            nn.LeakyReLU(0.2),
-            nn.Conv2d(128, 128, kernel_size=3, stride=2, padding=1),
-            nn.BatchNorm2d(128),
-            nn.LeakyReLU(0.2),
-            nn.AdaptiveAvgPool2d(1),
-            nn.Conv2d(128, 1, kernel_size=1),
-            nn.Sigmoid(),
-        )
+        make = {"conv": lambda ci, co, s: nn.Conv2d(ci, co, kernel_size=3, stride=s, padding=1),
+                "lrelu": lambda: nn.LeakyReLU(0.2), "bn": nn.BatchNorm2d, "pool": lambda: nn.AdaptiveAvgPool2d(1),
+                "head": lambda ci, co: nn.Conv2d(ci, co, kernel_size=1), "sigmoid": nn.Sigmoid}
+        self.model = nn.Sequential(*[make[kind](*a) for kind, *a in self._SPEC])
 
     def forward(self, x):  # pragma: no cover - by design
         raise RuntimeError("DenoiseDiscriminator runs inside DenoiseGANTrainStep (cid_train_*); it has no standalone "
@@ -63,6 +56,20 @@ def allreduce_mean_(flat: torch.Tensor, group=None) -> torch.Tensor:
             dist.all_reduce(flat, group=group)
             flat.mul_(1.0 / world)
     return flat
+
+
+def sync_replicas_(tensors, group=None, src: int = 0) -> None:
+    """Make every data-parallel rank start from rank `src`'s values (parameters, BatchNorm running statistics), in place.
+    Both gradient-exchange paths average gradients and assume the replicas hold identical weights; modules constructed
+    per process are randomly initialised per process, so without this step unseeded ranks would silently train
+    different weights on the averaged gradients. A no-op without an initialised process group / with world size 1."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) < 2:
+        return
+    g = group if group is not None else dist.group.WORLD
+    root = dist.get_global_rank(g, src) if group is not None else src
+    for t in tensors:
+        dist.broadcast(t, src=root, group=group)
 
 
 class DenoiseGANTrainStep:
@@ -176,17 +183,30 @@ class DenoiseGANTrainStep:
         return self.state[off.value:off.value + n.value]
 
     def section(self, net: str, section: int) -> torch.Tensor:
-        off, n = C.c_size_t(), C.c_size_t()
-        _lib.check(self.lib.cid_train_section(self.handle, net.encode(), section, C.byref(off), C.byref(n)), "cid_train_section")
-        return self.state[off.value:off.value + n.value]
+        off, n = self._section_range(net, section)
+        return self.state[off:off + n]
 
     def load_state_dicts(self, g_sd: Dict[str, torch.Tensor], d_sd: Dict[str, torch.Tensor]) -> None:
         for name in self.names:
             net, key = name.split(".", 1)
             src = (g_sd if net == "generator" else d_sd)[key]
             self.view(name).copy_(src.detach().to(self.device, torch.float32).reshape(-1))
+        self._sync_replicas()
         _lib.check(self.lib.cid_train_sync_weights(self.handle, C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)),
                    "cid_train_sync_weights")
+
+    def _sync_replicas(self) -> None:
+        """Rank 0's parameters and BatchNorm statistics become everybody's (see sync_replicas_)."""
+        g_off, g_n = self._section_range("generator", 0)
+        d_off, d_n = self._section_range("discriminator", 0)
+        P = g_n + d_n
+        assert g_off == 0 and d_off == g_n
+        sync_replicas_([self.state[:P], self.state[4 * P:]], self.group)
+
+    def _section_range(self, net: str, section: int):
+        off, n = C.c_size_t(), C.c_size_t()
+        _lib.check(self.lib.cid_train_section(self.handle, net.encode(), section, C.byref(off), C.byref(n)), "cid_train_section")
+        return off.value, n.value
 
     def export_state_dicts(self, generator: nn.Module, discriminator: nn.Module) -> None:
         """Copy the trained parameters and BatchNorm statistics back into the two modules."""

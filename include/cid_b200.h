@@ -81,7 +81,13 @@ int cid_set_param(cid_handle h, const char* key, const float* data, const int64_
 int cid_finalize(cid_handle h);
 
 /* Tunables. "chunk": images processed per pass through the layers (0 = whole batch); bounds the
- * activation working set (and the workspace). "profile": 1 = record per-layer CUDA events. */
+ * activation working set (and the workspace). "profile": 1 = record per-layer CUDA events (switches the
+ * graph replay off while set). "pdl": programmatic dependent launch between consecutive layers (default 1).
+ * denoise generator only - "regime": 0 (default) = per layer, run the batch-256 tile configuration or, when its
+ * pixel tiles would leave SMs idle (batch 1, the upload route's shape, backend/app.py:406), the N-split form
+ * (64-column blocks of single tiles); 1 / 2 force one form (they are bit-identical). "graph": 1 (default) =
+ * passes of at most 2^20 pixels are replayed as ONE CUDA graph launch from the second call of a plan on; the
+ * caller's pointers are updated in the graph's first / last kernel node when they change. */
 int cid_set_option(cid_handle h, const char* name, int64_t value);
 
 /* Bytes of device scratch a forward of B images of H x W (network-input size, multiples of 4)
@@ -134,11 +140,13 @@ int cid_noise_elementwise_u8(cid_handle h, const uint8_t* in, uint8_t* out, size
 /* Salt & pepper: replaces add_salt_pepper_noise (noise_generation.py:12-22). Per image
  * [H,W,C]: n_salt = int(H*W*C*salt_prob) pixel coordinates set to 255 on all channels, then
  * n_pepper set to 0. If coords (device int32 [B][n_salt+n_pepper][2] = (row,col)) is non-NULL
- * it is used verbatim (parity mode); otherwise coordinates are Philox draws in
- * [0,H-1) x [0,W-1) — the reference's randint(0, dim-1) excludes the last row/col. */
+ * it is used verbatim (parity mode; coords_per_image must equal n_salt+n_pepper, else an error); otherwise
+ * coordinates are Philox draws in [0,H-1) x [0,W-1) — the reference's randint(0, dim-1) excludes the last
+ * row/col. The probabilities are float64 like the reference's Python floats: the draw counts are the
+ * float64 product int(H*W*C*prob). */
 int cid_noise_salt_pepper_u8(cid_handle h, const uint8_t* in, uint8_t* out, int B, int H, int W, int C,
-                             float salt_prob, float pepper_prob, const int32_t* coords, uint64_t seed,
-                             uint64_t offset, void* stream);
+                             double salt_prob, double pepper_prob, const int32_t* coords, int64_t coords_per_image,
+                             uint64_t seed, uint64_t offset, void* stream);
 
 /* Resize + normalise data-prep: replaces Image.resize(size, BICUBIC) (noise_generation.py:61,
  * denoisegan_eval.py:89) = Pillow's two-pass separable fixed-point bicubic (a = -0.5, support
@@ -197,8 +205,7 @@ typedef struct cid_train* cid_train_handle;
 
 int cid_train_create(int device, cid_train_handle* out);
 int cid_train_destroy(cid_train_handle t);
-/* Options of the underlying generator context (cid_set_option); "variant" bits 64 / 128 select the resident-weight /
- * CTA-pair forms of the N = 64 / N = 128 data-gradient kernels. */
+/* Options of the underlying generator context (cid_set_option), plus "peer_timeout_ms": see cid_train_set_peers. */
 int cid_train_set_option(cid_train_handle t, const char* name, int64_t value);
 int cid_train_state_floats(cid_train_handle t, size_t* n);
 int cid_train_bind_state(cid_train_handle t, float* state_dev, size_t n);
@@ -229,8 +236,11 @@ int cid_train_adam(cid_train_handle t, int which, float lr, float beta1, float b
  * and the gradients section keeps the rank-LOCAL gradients. Requirements: the bound state buffer and one int buffer of
  * cid_train_peer_flag_ints() zeroed ints are symmetric allocations mapped into every rank (e.g. torch symmetric memory);
  * state_ptrs[r] / flag_ptrs[r] are rank r's buffers as THIS process addresses them; every rank calls cid_train_adam the
- * same number of times in the same order. world <= 8; world <= 1 switches the fused path off. A peer that does not
- * arrive within 4 s makes the next cid_train_losses fail instead of hanging the GPU. */
+ * same number of times in the same order. world <= 8; world <= 1 switches the fused path off. All
+ * cid_train_peer_flag_ints()/16 blocks of the kernel must be co-resident (checked here). A peer that does not arrive
+ * within the timeout (cid_train_set_option "peer_timeout_ms", default 600000 = 10 min, the order of NCCL's watchdog) is a
+ * fault: the optimiser update is SKIPPED from then on (sticky), the peers time out in turn, and every following
+ * cid_train_adam / cid_train_losses call on every rank fails; the caller restores a checkpoint. */
 int cid_train_peer_flag_ints(void);
 int cid_train_set_peers(cid_train_handle t, int world, int rank, const void* const* state_ptrs, void* const* flag_ptrs);
 /* Synchronises; out4 = {d_loss, g_loss, content (MSE), adversarial (BCE)} of the last step. */

@@ -36,7 +36,7 @@ def main():
     net.load_state_dict(sd, strict=True)
     net = net.to("cuda").eval()
     import os
-    for opt in ("first_tc", "variant"):
+    for opt in ("regime", "graph"):
         if os.environ.get("CID_" + opt.upper()):
             net.set_option(opt, int(os.environ["CID_" + opt.upper()]))
     t0 = time.time()

@@ -25,7 +25,6 @@ def main():
     ap.add_argument("--H", type=int, default=32)
     ap.add_argument("--W", type=int, default=32)
     ap.add_argument("--seed", type=int, default=7)
-    ap.add_argument("--variant", type=int, default=-1)
     a = ap.parse_args()
     og, od = to.make_models(a.seed)
     noisy, clean = to.synthetic_pair(11, a.B, a.H, a.W)
@@ -33,8 +32,6 @@ def main():
     g, d = DenoiseGenerator(), DenoiseDiscriminator()
     g.load_state_dict(og.state_dict()); d.load_state_dict(od.state_dict())
     tr = DenoiseGANTrainStep(g, d, device="cuda:0")
-    if a.variant >= 0:
-        tr.set_option("variant", a.variant)
     nz, cl = noisy.cuda().contiguous(), clean.cuda().contiguous()
     tr.d_backward(nz, cl)
     torch.cuda.synchronize()
