@@ -272,8 +272,8 @@ def main():
     ap.add_argument("--batch", type=int, default=256, help="images per GPU per step")
     ap.add_argument("--size", type=int, default=128)
     ap.add_argument("--chunk", type=int, default=-1, help="images per pass through the layers (-1 = library default)")
-    ap.add_argument("--sub-batch", type=int, default=64, help="e2e: images per H2D/compute/D2H pipeline slot")
-    ap.add_argument("--depth", type=int, default=4, help="e2e: staging slots of the three-stage pipeline")
+    ap.add_argument("--sub-batch", type=int, default=128, help="e2e: images per H2D/compute/D2H pipeline slot")
+    ap.add_argument("--depth", type=int, default=3, help="e2e: staging slots of the three-stage pipeline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--layers", action="store_true", help="also print the per-layer table to stderr")
     ap.add_argument("--only", default="", help="comma list of extra sections to run (default: all): "

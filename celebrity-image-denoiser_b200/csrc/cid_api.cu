@@ -1023,6 +1023,8 @@ int cid_forward_u8_nhwc(cid_handle h, const uint8_t* x, uint8_t* y, int B, int H
 
 int64_t cid_kernel_launches(cid_handle h) { return h ? h->launches : -1; }
 
+int64_t cid_graph_replays(cid_handle h) { return h ? h->graph_replays : -1; }
+
 int cid_profile_read(cid_handle h, double* layer_ms, int64_t* passes) {
     CID_REQUIRE(h && layer_ms && passes, "cid_profile_read: null argument");
     DeviceGuard g(h->device);

@@ -1,4 +1,5 @@
-// Synthetic noiser: Gaussian and salt-and-pepper corruption of u8 images, HBM-bound.
+// Synthetic noiser: Gaussian and salt-and-pepper corruption of u8 images (plus the reference's other noise types), in the
+// u8 domain of noise_generation.py and in the [0,1] domain of esrgan_addNoise.py.
 //
 // Reference (file:line in /root/reference):
 //   add_gaussian_noise     backend/trainingcode/denoise_gan_code/noise_generation.py:6-10
@@ -42,6 +43,69 @@ __device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, fl
     z1 = r * s;
 }
 
+// ---- fast normals for the Philox modes (statistical parity only; the supplied-draw modes keep float64) ----
+// One 32-bit Philox word gives TWO normals: the high half is the radius uniform, the low half the angle (Box-Muller on
+// 16-bit uniforms (k + 0.5) / 65536: tails reach 4.86 sigma). Everything runs on the special-function unit's approx
+// instructions (lg2, sqrt, sin, cos: 2 MUFU per normal) and full-rate ALU ops - the kernels were ALU-bound, not HBM-bound,
+// with libdevice's logf / sincospif and float64 clipping (round 1: no GB/s figure; see profiles/r02*_membound*).
+__device__ __forceinline__ float u16_to_float(uint32_t word, bool high) {
+    // (0x4B000000 | k) is the float 8388608 + k: integer -> float without the conversion pipe
+    const uint32_t m = __byte_perm(word, 0x4B000000u, high ? 0x7632u : 0x7610u);
+    return __uint_as_float(m);
+}
+__device__ __forceinline__ void normals_from_word(uint32_t word, float& z0, float& z1) {
+    constexpr float kBias = 8388608.0f - 0.5f;
+    const float u = (u16_to_float(word, true) - kBias) * (1.0f / 65536.0f);             // (0, 1)
+    const float a = (u16_to_float(word, false) - kBias) * (6.283185307179586f / 65536.0f);  // (0, 2 pi)
+    float l, r, sn, cs;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l) : "f"(u));
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(l * -1.3862943611198906f));      // sqrt(-2 ln u)
+    asm("sin.approx.ftz.f32 %0, %1;" : "=f"(sn) : "f"(a));
+    asm("cos.approx.ftz.f32 %0, %1;" : "=f"(cs) : "f"(a));
+    z0 = r * cs;
+    z1 = r * sn;
+}
+// 16 standard normals for thread-counter t (two Philox4x32-10 calls)
+__device__ __forceinline__ void normals16(uint64_t seed, uint64_t ctr0, uint32_t stream, float (&z)[16]) {
+    const uint2 key = make_uint2(static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+#pragma unroll
+    for (int g = 0; g < 2; ++g) {
+        const uint64_t ctr = ctr0 + g;
+        const uint4 r = philox4x32_10(make_uint4(static_cast<uint32_t>(ctr), static_cast<uint32_t>(ctr >> 32), stream, 0u), key);
+        normals_from_word(r.x, z[8 * g + 0], z[8 * g + 1]);
+        normals_from_word(r.y, z[8 * g + 2], z[8 * g + 3]);
+        normals_from_word(r.z, z[8 * g + 4], z[8 * g + 5]);
+        normals_from_word(r.w, z[8 * g + 6], z[8 * g + 7]);
+    }
+}
+// 16 uniforms in [0, 1) with 16 bits each
+__device__ __forceinline__ void uniforms16(uint64_t seed, uint64_t ctr0, uint32_t stream, float (&u)[16]) {
+    const uint2 key = make_uint2(static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+#pragma unroll
+    for (int g = 0; g < 2; ++g) {
+        const uint64_t ctr = ctr0 + g;
+        const uint4 r = philox4x32_10(make_uint4(static_cast<uint32_t>(ctr), static_cast<uint32_t>(ctr >> 32), stream, 0u), key);
+        const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            u[8 * g + 2 * e + 0] = (u16_to_float(w[e], true) - 8388608.0f) * (1.0f / 65536.0f);
+            u[8 * g + 2 * e + 1] = (u16_to_float(w[e], false) - 8388608.0f) * (1.0f / 65536.0f);
+        }
+    }
+}
+// pixel byte i of a packed word as a float, without the conversion pipe
+__device__ __forceinline__ float byte_to_float(uint32_t word, int i) {
+    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440u | static_cast<uint32_t>(i))) - 8388608.0f;
+}
+// clip to [0, hi] and truncate: the float path of u8(np.clip(v, 0, 255)); returns the integer in the low byte
+__device__ __forceinline__ uint32_t clip_trunc_bits(float v, float hi) {
+    v = fminf(fmaxf(v, 0.f), hi);
+    return __float_as_uint(__fadd_rz(v, 8388608.0f));  // 8388608 + floor(v): the low byte is the result
+}
+__device__ __forceinline__ uint32_t pack4_low_bytes(uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    return __byte_perm(__byte_perm(a, b, 0x0040u), __byte_perm(c, d, 0x0040u), 0x5410u);
+}
+
 __device__ __forceinline__ uint8_t clip_trunc_u8(double v) {
     v = fmin(fmax(v, 0.0), 255.0);
     return static_cast<uint8_t>(v);  // truncation, like ndarray.astype(np.uint8) on [0,255]
@@ -56,33 +120,31 @@ __global__ void __launch_bounds__(256) gaussian_u8_kernel(const uint8_t* __restr
     const size_t base = t * 16;
     if (base >= n) return;
     const bool full = base + 16 <= n && ((reinterpret_cast<uintptr_t>(in + base) | reinterpret_cast<uintptr_t>(out + base)) & 15) == 0;
-    uint8_t px[16];
+    __align__(16) uint8_t px[16];
     if (full) {
         *reinterpret_cast<uint4*>(px) = __ldg(reinterpret_cast<const uint4*>(in + base));
     } else {
         for (int i = 0; i < 16; ++i) px[i] = base + i < n ? in[base + i] : 0;
     }
-    double nz[16];
+    __align__(16) uint8_t o[16];
     if (noise) {
+        double nz[16];
         for (int i = 0; i < 16; ++i) nz[i] = base + i < n ? noise[base + i] : 0.0;
-    } else {
-        const uint2 key = make_uint2(static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-            const uint64_t ctr = offset + t * 4 + g;
-            const uint4 r = philox4x32_10(make_uint4(static_cast<uint32_t>(ctr), static_cast<uint32_t>(ctr >> 32), 0u, 0u), key);
-            float z0, z1, z2, z3;
-            box_muller(r.x, r.y, z0, z1);
-            box_muller(r.z, r.w, z2, z3);
-            nz[4 * g + 0] = static_cast<double>(fmaf(sigma, z0, mean));
-            nz[4 * g + 1] = static_cast<double>(fmaf(sigma, z1, mean));
-            nz[4 * g + 2] = static_cast<double>(fmaf(sigma, z2, mean));
-            nz[4 * g + 3] = static_cast<double>(fmaf(sigma, z3, mean));
+        for (int i = 0; i < 16; ++i) o[i] = clip_trunc_u8(static_cast<double>(px[i]) + nz[i]);
+    } else {
+        float z[16];
+        normals16(seed, offset + t * 2, 0u, z);
+        const uint32_t* pw = reinterpret_cast<const uint32_t*>(px);
+        uint32_t* ow = reinterpret_cast<uint32_t*>(o);
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            uint32_t b[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) b[e] = clip_trunc_bits(fmaf(sigma, z[4 * w + e], byte_to_float(pw[w], e) + mean), 255.f);
+            ow[w] = pack4_low_bytes(b[0], b[1], b[2], b[3]);
         }
     }
-    uint8_t o[16];
-#pragma unroll
-    for (int i = 0; i < 16; ++i) o[i] = clip_trunc_u8(static_cast<double>(px[i]) + nz[i]);
     if (full) {
         *reinterpret_cast<uint4*>(out + base) = *reinterpret_cast<const uint4*>(o);
     } else {
@@ -106,11 +168,38 @@ __global__ void __launch_bounds__(256) elementwise_noise_kernel(const uint8_t* _
     const size_t base = t * 16;
     if (base >= n) return;
     const bool full = base + 16 <= n && ((reinterpret_cast<uintptr_t>(in + base) | reinterpret_cast<uintptr_t>(out + base)) & 15) == 0;
-    uint8_t px[16];
+    __align__(16) uint8_t px[16];
     if (full) {
         *reinterpret_cast<uint4*>(px) = __ldg(reinterpret_cast<const uint4*>(in + base));
     } else {
         for (int i = 0; i < 16; ++i) px[i] = base + i < n ? in[base + i] : 0;
+    }
+    if (draws == nullptr && (KIND == 1 || KIND == 2)) {
+        // Philox mode (statistical parity): fp32 arithmetic, 16-bit-uniform Box-Muller (see normals_from_word)
+        float r[16];
+        if (KIND == 1) normals16(seed, offset + t * 2, 2u + KIND, r);
+        else uniforms16(seed, offset + t * 2, 2u + KIND, r);
+        const uint32_t* pw = reinterpret_cast<const uint32_t*>(px);
+        __align__(16) uint32_t ow[4];
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            uint32_t b[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float x = byte_to_float(pw[w], e);
+                const float d = KIND == 1 ? fmaf(p1, r[4 * w + e], p0) : fmaf(p1 - p0, r[4 * w + e], p0);
+                b[e] = clip_trunc_bits(KIND == 1 ? fmaf(x, d, x) : x + d, 255.f);
+            }
+            ow[w] = pack4_low_bytes(b[0], b[1], b[2], b[3]);
+        }
+        if (full) {
+            *reinterpret_cast<uint4*>(out + base) = *reinterpret_cast<const uint4*>(ow);
+        } else {
+            const uint8_t* ob = reinterpret_cast<const uint8_t*>(ow);
+            for (int i = 0; i < 16; ++i)
+                if (base + i < n) out[base + i] = ob[i];
+        }
+        return;
     }
     double d[16];
     if (draws) {
@@ -172,6 +261,94 @@ __global__ void __launch_bounds__(256) elementwise_noise_kernel(const uint8_t* _
         for (int i = 0; i < 16; ++i)
             if (base + i < n) out[base + i] = o[i];
     }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// [0,1]-domain noiser of the ESRGAN data-prep script (backend/trainingcode/esrgan_code/esrgan_addNoise.py), u8 in -> u8 out
+// including the script's own conversions: img = u8 / 255.0 (:66), noise function, (noisy * 255).astype(np.uint8) (:79).
+//   KIND 0 add_gaussian (:7-13)   clip(img + N(p0, p1), 0, 1)      reference: mean 0, sigma = sqrt(0.01) = 0.1 - the sigma
+//                                                                  BASELINE.json configs[0] names for the synthetic faces
+//   KIND 1 add_speckle  (:27-30)  clip(img + img * N(p0, p1), 0, 1)  reference: randn = N(0, 1)
+//   KIND 2 add_uniform  (:38-41)  clip(img + U(p0, p1), 0, 1)        reference: U(-0.05, 0.05)
+// draws (float64, the reference's own random array) -> float64 arithmetic as numpy, bit-exact; NULL -> Philox, fp32.
+// ---------------------------------------------------------------------------------------------------------------------
+template <int KIND>
+__global__ void __launch_bounds__(256) unit_noise_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, size_t n,
+                                                         float p0, float p1, const double* __restrict__ draws, uint64_t seed,
+                                                         uint64_t offset) {
+    const size_t t = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const size_t base = t * 16;
+    if (base >= n) return;
+    const bool full = base + 16 <= n && ((reinterpret_cast<uintptr_t>(in + base) | reinterpret_cast<uintptr_t>(out + base)) & 15) == 0;
+    __align__(16) uint8_t px[16];
+    if (full) {
+        *reinterpret_cast<uint4*>(px) = __ldg(reinterpret_cast<const uint4*>(in + base));
+    } else {
+        for (int i = 0; i < 16; ++i) px[i] = base + i < n ? in[base + i] : 0;
+    }
+    __align__(16) uint8_t o[16];
+    if (draws) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const double x = static_cast<double>(px[i]) / 255.0;
+            const double d = base + i < n ? draws[base + i] : 0.0;
+            double v = KIND == 1 ? x + x * d : x + d;
+            v = fmin(fmax(v, 0.0), 1.0);
+            o[i] = static_cast<uint8_t>(v * 255.0);  // (noisy * 255).astype(np.uint8): truncation
+        }
+    } else {
+        float r[16];
+        if (KIND == 2) uniforms16(seed, offset + t * 2, 8u + KIND, r);
+        else normals16(seed, offset + t * 2, 8u + KIND, r);
+        const uint32_t* pw = reinterpret_cast<const uint32_t*>(px);
+        uint32_t* ow = reinterpret_cast<uint32_t*>(o);
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            uint32_t b[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float x = byte_to_float(pw[w], e) * (1.0f / 255.0f);
+                const float d = KIND == 2 ? fmaf(p1 - p0, r[4 * w + e], p0) : fmaf(p1, r[4 * w + e], p0);
+                const float v = fminf(fmaxf(KIND == 1 ? fmaf(x, d, x) : x + d, 0.f), 1.f);
+                b[e] = clip_trunc_bits(v * 255.0f, 255.f);
+            }
+            ow[w] = pack4_low_bytes(b[0], b[1], b[2], b[3]);
+        }
+    }
+    if (full) {
+        *reinterpret_cast<uint4*>(out + base) = *reinterpret_cast<const uint4*>(o);
+    } else {
+        for (int i = 0; i < 16; ++i)
+            if (base + i < n) out[base + i] = o[i];
+    }
+}
+
+// add_salt_pepper (esrgan_addNoise.py:15-25): ceil(amount * img.size * 0.5) ELEMENT coordinates (row, col, channel) from
+// randint(0, dim) - the full range, unlike the denoise variant - set to 1 (-> 255), then as many set to 0.
+// one thread per (image, draw); coords int32 [B][2 * count][3], salt draws first.
+__global__ void __launch_bounds__(256) unit_impulse_kernel(uint8_t* __restrict__ out, int B, int H, int W, int C, int count,
+                                                           int first, int stride, uint8_t value,
+                                                           const int32_t* __restrict__ coords, uint64_t seed, uint64_t offset) {
+    const size_t t = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (t >= static_cast<size_t>(B) * count) return;
+    const int b = static_cast<int>(t / count);
+    const int i = static_cast<int>(t % count);
+    int row, col, ch;
+    if (coords) {
+        const int32_t* cc = coords + (static_cast<size_t>(b) * stride + first + i) * 3;
+        row = cc[0];
+        col = cc[1];
+        ch = cc[2];
+    } else {
+        const uint2 key = make_uint2(static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+        const uint64_t ctr = offset + static_cast<uint64_t>(b) * stride + first + i;
+        const uint4 r = philox4x32_10(make_uint4(static_cast<uint32_t>(ctr), static_cast<uint32_t>(ctr >> 32), 7u, 0u), key);
+        row = static_cast<int>(__umulhi(r.x, static_cast<uint32_t>(H)));
+        col = static_cast<int>(__umulhi(r.y, static_cast<uint32_t>(W)));
+        ch = static_cast<int>(__umulhi(r.z, static_cast<uint32_t>(C)));
+    }
+    if (row < 0 || row >= H || col < 0 || col >= W || ch < 0 || ch >= C) return;
+    out[((static_cast<size_t>(b) * H + row) * W + col) * C + ch] = value;
 }
 
 __global__ void __launch_bounds__(256) copy_u8_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, size_t n) {
@@ -291,6 +468,60 @@ int cid_noise_salt_pepper_u8(cid_handle h, const uint8_t* in, uint8_t* out, int 
                                                                                0, coords, seed, offset);
         CID_CHECK_CUDA(cudaGetLastError());
         h->launches++;
+    }
+    return 0;
+}
+
+int cid_noise_unit_u8(cid_handle h, const uint8_t* in, uint8_t* out, size_t n, int kind, float p0, float p1,
+                      const double* draws, uint64_t seed, uint64_t offset, void* stream) {
+    CID_REQUIRE(h && in && out, "cid_noise_unit_u8: null argument");
+    CID_REQUIRE(kind >= 0 && kind <= 2, "unknown [0,1]-domain noise kind %d (0 gaussian, 1 speckle, 2 uniform)", kind);
+    if (n == 0) return 0;
+    DeviceGuard g(h->device);
+    CID_REQUIRE(g.ok, "cannot select CUDA device %d", h->device);
+    const size_t threads = (n + 15) / 16;
+    const unsigned grid = static_cast<unsigned>((threads + 255) / 256);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (kind == 0)
+        unit_noise_kernel<0><<<grid, 256, 0, st>>>(in, out, n, p0, p1, draws, seed, offset);
+    else if (kind == 1)
+        unit_noise_kernel<1><<<grid, 256, 0, st>>>(in, out, n, p0, p1, draws, seed, offset);
+    else
+        unit_noise_kernel<2><<<grid, 256, 0, st>>>(in, out, n, p0, p1, draws, seed, offset);
+    CID_CHECK_CUDA(cudaGetLastError());
+    h->launches++;
+    return 0;
+}
+
+int cid_noise_salt_pepper_unit_u8(cid_handle h, const uint8_t* in, uint8_t* out, int B, int H, int W, int C, double amount,
+                                  const int32_t* coords, int64_t coords_per_image, uint64_t seed, uint64_t offset,
+                                  void* stream) {
+    CID_REQUIRE(h && in && out, "cid_noise_salt_pepper_unit_u8: null argument");
+    CID_REQUIRE(B >= 0 && H >= 1 && W >= 1 && C >= 1, "bad shape B=%d H=%d W=%d C=%d", B, H, W, C);
+    CID_REQUIRE(amount >= 0.0, "negative amount");
+    if (B == 0) return 0;
+    DeviceGuard g(h->device);
+    CID_REQUIRE(g.ok, "cannot select CUDA device %d", h->device);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t n = static_cast<size_t>(B) * H * W * C;
+    // np.ceil(amount * img.size * 0.5), float64, for salt and again for pepper (esrgan_addNoise.py:17, 21)
+    const int count = static_cast<int>(ceil(amount * static_cast<double>(static_cast<size_t>(H) * W * C) * 0.5));
+    CID_REQUIRE(!coords || coords_per_image == 2 * static_cast<int64_t>(count),
+                "coords holds %lld draws per image; this image size and amount need %d salt + %d pepper",
+                static_cast<long long>(coords_per_image), count, count);
+    if (in != out) {
+        const size_t threads = (n + 15) / 16;
+        copy_u8_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, st>>>(in, out, n);
+        CID_CHECK_CUDA(cudaGetLastError());
+        h->launches++;
+    }
+    if (count > 0) {
+        const size_t t = static_cast<size_t>(B) * count;
+        const unsigned grid = static_cast<unsigned>((t + 255) / 256);
+        unit_impulse_kernel<<<grid, 256, 0, st>>>(out, B, H, W, C, count, 0, 2 * count, 255, coords, seed, offset);
+        unit_impulse_kernel<<<grid, 256, 0, st>>>(out, B, H, W, C, count, count, 2 * count, 0, coords, seed, offset);
+        CID_CHECK_CUDA(cudaGetLastError());
+        h->launches += 2;
     }
     return 0;
 }

@@ -191,6 +191,10 @@ class _CudaGenerator(nn.Module):
     def kernel_launches(self) -> int:
         return sum(e.launches() for e in self._engines.values())
 
+    def graph_replays(self) -> int:
+        """Passes that ran as one CUDA-graph launch (small batches; cid_set_option "graph")."""
+        return sum(int(e.lib.cid_graph_replays(e.handle)) for e in self._engines.values())
+
     def release_workspace(self) -> None:
         """Drop the cached activation workspace(s); the next forward allocates what it needs."""
         for e in self._engines.values():

@@ -38,11 +38,16 @@ _SIGNATURES = {
     "cid_noise_salt_pepper_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                            C.c_double, C.c_double, C.c_void_p, C.c_int64, C.c_uint64, C.c_uint64,
                                            C.c_void_p]),
+    "cid_noise_unit_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_float, C.c_float,
+                                    C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p]),
+    "cid_noise_salt_pepper_unit_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                                                C.c_double, C.c_void_p, C.c_int64, C.c_uint64, C.c_uint64, C.c_void_p]),
     "cid_resize_bicubic_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                         C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "cid_normalize_u8_to_f32_nchw": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                                C.c_float, C.c_float, C.c_void_p]),
     "cid_kernel_launches": (C.c_int64, [C.c_void_p]),
+    "cid_graph_replays": (C.c_int64, [C.c_void_p]),
     "cid_profile_read": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "cid_debug_copy_activation": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                             C.c_void_p, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int),

@@ -148,6 +148,23 @@ int cid_noise_salt_pepper_u8(cid_handle h, const uint8_t* in, uint8_t* out, int 
                              double salt_prob, double pepper_prob, const int32_t* coords, int64_t coords_per_image,
                              uint64_t seed, uint64_t offset, void* stream);
 
+/* The [0,1]-domain noiser of the ESRGAN data-prep script (backend/trainingcode/esrgan_code/esrgan_addNoise.py), u8 in -> u8
+ * out including the script's conversions img = u8 / 255.0 (:66) and (noisy * 255).astype(np.uint8) (:79):
+ *   kind 0 add_gaussian (:7-13)  clip(img + N(p0, p1), 0, 1)   reference p0 = 0, p1 = sqrt(0.01) = 0.1 (the sigma
+ *                                                              BASELINE.json configs[0] names)
+ *   kind 1 add_speckle (:27-30)  clip(img + img * N(p0, p1), 0, 1)   reference N(0, 1)
+ *   kind 2 add_uniform (:38-41)  clip(img + U(p0, p1), 0, 1)         reference U(-0.05, 0.05)
+ * draws (device float64, n values) = the reference's own random array -> float64 arithmetic, bit-exact; NULL = Philox. */
+int cid_noise_unit_u8(cid_handle h, const uint8_t* in, uint8_t* out, size_t n, int kind, float p0, float p1,
+                      const double* draws, uint64_t seed, uint64_t offset, void* stream);
+
+/* add_salt_pepper (esrgan_addNoise.py:15-25): per image ceil(amount * H*W*C * 0.5) ELEMENT coordinates (row, col, channel)
+ * drawn from the full randint(0, dim) range are set to 1 (255), then as many to 0. coords (device int32
+ * [B][2*count][3], salt draws first; coords_per_image must be 2*count) = the reference's own draws; NULL = Philox. */
+int cid_noise_salt_pepper_unit_u8(cid_handle h, const uint8_t* in, uint8_t* out, int B, int H, int W, int C, double amount,
+                                  const int32_t* coords, int64_t coords_per_image, uint64_t seed, uint64_t offset,
+                                  void* stream);
+
 /* Resize + normalise data-prep: replaces Image.resize(size, BICUBIC) (noise_generation.py:61,
  * denoisegan_eval.py:89) = Pillow's two-pass separable fixed-point bicubic (a = -0.5, support
  * scaled by the down-sampling factor), u8 NHWC in -> u8 NHWC out. tmp: device scratch of
@@ -164,6 +181,10 @@ int cid_normalize_u8_to_f32_nchw(cid_handle h, const uint8_t* in, float* out, in
 
 /* Number of kernels this handle has launched so far (bench.py's gpu_launches evidence). */
 int64_t cid_kernel_launches(cid_handle h);
+
+/* Number of passes this handle has run as ONE CUDA-graph launch (cid_set_option "graph"; replayed kernels are counted
+ * in cid_kernel_launches as well). */
+int64_t cid_graph_replays(cid_handle h);
 
 /* Per-layer device timing. After cid_set_option(h, "profile", 1) every pass through the layers
  * records 13 CUDA events on the caller's stream (one before each of the 12 layers and one after

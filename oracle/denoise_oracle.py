@@ -232,6 +232,30 @@ def salt_pepper_apply(image: np.ndarray, salt_rc: np.ndarray, pepper_rc: np.ndar
 
 
 # --------------------------------------------------------------------------------------------
+# [0,1]-domain noiser of the ESRGAN data-prep script (backend/trainingcode/esrgan_code/esrgan_addNoise.py), with the
+# random draws made explicit and the script's own conversions (:66 img = u8 / 255.0, :79 (noisy * 255).astype(uint8))
+# --------------------------------------------------------------------------------------------
+def unit_noise_apply(image_u8: np.ndarray, kind: str, draws: np.ndarray) -> np.ndarray:
+    """add_gaussian (:7-13) / add_speckle (:27-30) / add_uniform (:38-41) given the function's own random array."""
+    img = image_u8 / 255.0
+    noisy = img + img * draws if kind == "speckle" else img + draws
+    return (np.clip(noisy, 0, 1) * 255).astype(np.uint8)
+
+
+def unit_salt_pepper_count(size: int, amount: float = 0.004) -> int:
+    """np.ceil(amount * img.size * 0.5) (:17, :21), the same number for salt and for pepper."""
+    return int(np.ceil(amount * size * 0.5))
+
+
+def unit_salt_pepper_apply(image_u8: np.ndarray, salt_idx: np.ndarray, pepper_idx: np.ndarray) -> np.ndarray:
+    """add_salt_pepper (:15-25): salt_idx / pepper_idx are int arrays [n,3] of (row, col, channel) ELEMENT coordinates."""
+    out = image_u8 / 255.0
+    out[salt_idx[:, 0], salt_idx[:, 1], salt_idx[:, 2]] = 1
+    out[pepper_idx[:, 0], pepper_idx[:, 1], pepper_idx[:, 2]] = 0
+    return (out * 255).astype(np.uint8)
+
+
+# --------------------------------------------------------------------------------------------
 # PIL bicubic resize (Pillow src/libImaging/Resample.c; called at noise_generation.py:61)
 # --------------------------------------------------------------------------------------------
 _PRECISION_BITS = 32 - 8 - 2

@@ -110,3 +110,24 @@ def test_oracle_against_live_reference_when_present():
     x = torch.rand(2, 3, 20, 12, generator=torch.Generator().manual_seed(3)) * 2 - 1
     with torch.no_grad():
         assert float((net(x) - orc.forward(sd, x)).abs().max()) <= 1e-6
+
+
+def test_salt_pepper_integer_product_edge_100x100(golden_dir):
+    """100x100x3 * 0.02 is exactly 600 in float64 (599 with a float32 probability); batch of two images."""
+    g = _load(golden_dir, "noiser_100x100.npz")
+    ns, npp = orc.salt_pepper_counts(g["image"][0].shape, 0.02, 0.02)
+    assert (ns, npp) == (600, 600) == (g["salt_rc"].shape[1], g["pepper_rc"].shape[1])
+    for i in range(2):
+        assert np.array_equal(orc.salt_pepper_apply(g["image"][i], g["salt_rc"][i], g["pepper_rc"][i]), g["sp_out"][i])
+
+
+@pytest.mark.parametrize("name", ["unit_noise_24x40", "unit_noise_33x17"])
+def test_unit_domain_noiser_bit_exact(golden_dir, name):
+    """esrgan_addNoise.py:7-41 through the script's u8 -> [0,1] -> u8 conversions, with the reference's own draws."""
+    g = _load(golden_dir, name + ".npz")
+    img = g["image"]
+    for kind in ("gaussian", "speckle", "uniform"):
+        assert np.array_equal(orc.unit_noise_apply(img, kind, g[kind + "_draws"]), g[kind + "_out"]), kind
+    n = orc.unit_salt_pepper_count(img.size)
+    assert n == len(g["salt_idx"]) == len(g["pepper_idx"])
+    assert np.array_equal(orc.unit_salt_pepper_apply(img, g["salt_idx"], g["pepper_idx"]), g["sp_out"])
