@@ -276,6 +276,8 @@ def main():
     ap.add_argument("--depth", type=int, default=3, help="e2e: staging slots of the three-stage pipeline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--layers", action="store_true", help="also print the per-layer table to stderr")
+    ap.add_argument("--opt", action="append", default=[], metavar="NAME=VALUE",
+                    help="cid_set_option on the generator (A/B experiments, e.g. --opt direct_store=3)")
     ap.add_argument("--only", default="", help="comma list of extra sections to run (default: all): "
                                                "sustained,latency,strong,train,membound")
     ap.add_argument("--sustained-seconds", type=float, default=3.0)
@@ -329,6 +331,9 @@ def main():
     net = DenoiseGenerator().to(dev).eval()
     if args.chunk >= 0:
         net.set_option("chunk", args.chunk)
+    for kv in args.opt:
+        name, val = kv.split("=", 1)
+        net.set_option(name, int(val))
 
     host_in = synthetic_noisy_u8(1234 + rank, B, H, W).pin_memory()
     host_out = torch.empty_like(host_in).pin_memory()

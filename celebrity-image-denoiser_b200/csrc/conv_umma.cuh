@@ -37,7 +37,8 @@ enum : int {  // TANH_*: last_conv_umma.cuh; LRELU/T4: the Keras cGAN layers (le
 };
 
 constexpr int kConvThreads = 320;  // warp 0 TMA, warp 1 MMA, warps 2..9 two epilogue groups
-constexpr int kMaxStages = 8;
+constexpr int kMaxStages = 8;    // A-operand ring (halo patches)
+constexpr int kMaxWStages = 16;  // streamed-weight ring
 
 struct ConvParams {
     int B, H, W;         // A-operand activation: batch, height, width (pixels)
@@ -116,17 +117,21 @@ struct ConvCfg {
                                                              : 512;
     // The epilogue stages each 64-channel slab of a tile in shared memory (SW128 rows, same geometry as
     // the A boxes) and writes it with one TMA store. Each of the 2 epilogue groups has NOB buffers.
-    static_assert(TS == 1, "all epilogues are staged");
+    // TS = 1: the epilogue stages each output slab in shared memory and writes it with one TMA store. TS = 0 (EPI_RELU /
+    // EPI_RELU_POOL only): every thread writes its pixel's channels straight from registers with 16-byte global stores -
+    // the N = 64 layers sit on the shared-memory roofline, and staging costs 32-40 KB of shared-memory
+    // traffic per tile (write + TMA read) on top of the ~200 KB the MMAs need.
+    static_assert(TS == 1 || (TS == 0 && (EPI == EPI_RELU || EPI == EPI_RELU_POOL)), "direct stores: ReLU epilogues only");
     static constexpr int NOB = 1;  // staging buffers per group (the other group's buffer gives the overlap)
     static constexpr int O_SLAB = 128 * 128;
     static constexpr int O2_SLAB = 32 * 128;
     static constexpr int OT_SLAB = 256 * 128;  // transposed convs: [16 rows][16 px][64 ch] of the 2x-upsampled output
     static constexpr int O_GROUP = NOB * (O_SLAB + (EPI == EPI_RELU_POOL ? O2_SLAB : 0));
-    static constexpr int O_BYTES = (EPI == EPI_CONVT || EPI == EPI_T4) ? 2 * OT_SLAB : 2 * O_GROUP;
+    static constexpr int O_BYTES = !TS ? 0 : (EPI == EPI_CONVT || EPI == EPI_T4) ? 2 * OT_SLAB : 2 * O_GROUP;
     // dynamic shared memory needed (bytes), including 1 KB of alignment slack
     static int smem_bytes(int kb_count, int a_stages, int w_stages) {
         int w_items = WRES ? kb_count * TAPS : w_stages;
-        return 1024 + w_items * W_BYTES + a_stages * A_BYTES + O_BYTES + 512;
+        return 1024 + w_items * W_BYTES + a_stages * A_BYTES + O_BYTES + 1024;
     }
 };
 
@@ -271,8 +276,8 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint64_t* a_full = bars;
     uint64_t* a_empty = bars + kMaxStages;
     uint64_t* w_full = bars + 2 * kMaxStages;
-    uint64_t* w_empty = bars + 3 * kMaxStages;
-    uint64_t* acc_full = bars + 4 * kMaxStages;
+    uint64_t* w_empty = w_full + kMaxWStages;
+    uint64_t* acc_full = w_empty + kMaxWStages;
     uint64_t* acc_empty = acc_full + 2;
     uint64_t* res_full = acc_empty + 2;  // EPI_ADD: residual tile of each epilogue group has landed in its slab
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_full + 2);
@@ -297,6 +302,8 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int i = 0; i < kMaxStages; ++i) {
             mbar_init(&a_full[i], CG);
             mbar_init(&a_empty[i], 1);
+        }
+        for (int i = 0; i < kMaxWStages; ++i) {
             mbar_init(&w_full[i], CG);
             mbar_init(&w_empty[i], 1);
         }
@@ -347,7 +354,24 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
             uint32_t a_stage = 0, a_phase = 0, w_stage = 0, w_phase = 0;
             const int kb_total = p.kb_count * KSUB;
-            pdl_wait();  // activations are the previous layer's output (the resident weights above are constants)
+            // Streamed weights are constants too: the first ring-full of weight tiles of this CTA's first work item is
+            // requested BEFORE waiting for the previous layer, so on a launch-bound (small-batch) pass they are in flight
+            // while that layer finishes. The main loop below skips exactly these tiles.
+            int w_pre = 0;
+            if (!WRES && unit < p.num_work) {
+                const int n_tile0 = unit % p.n_tiles;
+                for (int kb = 0; kb < kb_total && w_pre < WST; ++kb) {
+                    const int cb = kb / KSUB, sub = kb % KSUB;
+                    for (int step = 0; step < STEPS && w_pre < WST; ++step) {
+                        const Step sm(step, sub, n_tile0);
+                        expect(&w_full[w_pre], W_BYTES);   // first use of every stage: its "empty" phase is trivially free
+                        load_w(w_smem + w_pre * W_BYTES, &w_full[w_pre], cb * 64,
+                               sm.w_tap * p.w_rows_per_tap + (Cfg::T4 ? 0 : n_tile0 * N));
+                        ++w_pre;
+                    }
+                }
+            }
+            pdl_wait();  // activations are the previous layer's output (the weights above are constants)
             for (int work = unit; work < p.num_work; work += units) {
                 const int n_tile = work % p.n_tiles;
                 const int st = work / p.n_tiles;
@@ -382,10 +406,14 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     if (!WRES) {
                         for (int step = 0; step < STEPS; ++step) {
                             const Step sm(step, sub, n_tile);
-                            mbar_wait(&w_empty[w_stage], w_phase ^ 1);
-                            expect(&w_full[w_stage], W_BYTES);
-                            load_w(w_smem + w_stage * W_BYTES, &w_full[w_stage], cb * 64,
-                                   sm.w_tap * p.w_rows_per_tap + (Cfg::T4 ? 0 : n_tile * N));
+                            if (w_pre > 0) {
+                                --w_pre;  // already requested above
+                            } else {
+                                mbar_wait(&w_empty[w_stage], w_phase ^ 1);
+                                expect(&w_full[w_stage], W_BYTES);
+                                load_w(w_smem + w_stage * W_BYTES, &w_full[w_stage], cb * 64,
+                                       sm.w_tap * p.w_rows_per_tap + (Cfg::T4 ? 0 : n_tile * N));
+                            }
                             if (++w_stage == static_cast<uint32_t>(WST)) {
                                 w_stage = 0;
                                 w_phase ^= 1;
@@ -555,8 +583,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         uint8_t* slab = og + ob * Cfg::O_SLAB;
                         uint8_t* slab2 = og + Cfg::NOB * Cfg::O_SLAB + ob * Cfg::O2_SLAB;
                         // the store that used this buffer NOB slabs ago must have finished READING it
-                        if (issuer) bulk_wait_read<Cfg::NOB - 1>();
-                        named_bar_sync(bar_id, 128);
+                        if constexpr (TS) {
+                            if (issuer) bulk_wait_read<Cfg::NOB - 1>();
+                            named_bar_sync(bar_id, 128);
+                        }
                         // EPI_ADD: the optional SECOND residual (ESRGAN's long skip, last block only) comes straight from
                         // global memory, this thread's pixel = one 128-byte line
                         uint4 rv2[(EPI == EPI_ADD || EPI == EPI_DGRAD) ? 8 : 1];
@@ -661,12 +691,23 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                     st_sq[cs * 2 + ch] += warp_transpose_sum(sq, lane);
                                 }
                             }
-                            uint8_t* rowp = slab + row * 128;
+                            if constexpr (TS) {
+                                uint8_t* rowp = slab + row * 128;
 #pragma unroll
-                            for (int jj = 0; jj < 4; ++jj) {
-                                const int cj = ch * 4 + jj;  // 16-byte chunk inside the 128-byte row
-                                st_shared_v4(rowp + ((cj ^ (row & 7)) << 4), pk[4 * jj], pk[4 * jj + 1], pk[4 * jj + 2],
-                                             pk[4 * jj + 3]);
+                                for (int jj = 0; jj < 4; ++jj) {
+                                    const int cj = ch * 4 + jj;  // 16-byte chunk inside the 128-byte row
+                                    st_shared_v4(rowp + ((cj ^ (row & 7)) << 4), pk[4 * jj], pk[4 * jj + 1], pk[4 * jj + 2],
+                                                 pk[4 * jj + 3]);
+                                }
+                            } else {
+                                const int yy = tc.y0 + yl, xx = tc.x0 + xl;
+                                if (tc.b < p.B && yy < p.H && xx < p.W) {
+                                    const size_t pix = (static_cast<size_t>(tc.b) * p.H + yy) * p.W + xx;
+                                    uint16_t* dst = static_cast<uint16_t*>(p.out) + pix * p.out_cs + p.out_c0 + n_tile * N + cs * 64 + ch * 32;
+#pragma unroll
+                                    for (int jj = 0; jj < 4; ++jj)
+                                        st_global_v4(dst + jj * 8, pk[4 * jj], pk[4 * jj + 1], pk[4 * jj + 2], pk[4 * jj + 3]);
+                                }
                             }
                             if constexpr (EPI == EPI_RELU_POOL) {
                                 // 2x2 max: x partner is lane^1, y partner is lane^8 (row = y*8 + x).
@@ -680,13 +721,26 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                 const uint32_t o1 = sub == 0 ? pk[1] : sub == 1 ? pk[5] : sub == 2 ? pk[9] : pk[13];
                                 const uint32_t o2 = sub == 0 ? pk[2] : sub == 1 ? pk[6] : sub == 2 ? pk[10] : pk[14];
                                 const uint32_t o3 = sub == 0 ? pk[3] : sub == 1 ? pk[7] : sub == 2 ? pk[11] : pk[15];
-                                const int cj = ch * 4 + sub;
-                                st_shared_v4(slab2 + prow_i * 128 + ((cj ^ (prow_i & 7)) << 4), o0, o1, o2, o3);
+                                if constexpr (TS) {
+                                    const int cj = ch * 4 + sub;
+                                    st_shared_v4(slab2 + prow_i * 128 + ((cj ^ (prow_i & 7)) << 4), o0, o1, o2, o3);
+                                } else {
+                                    // this lane's quarter (8 channels) of the pooled pixel (H, W are even)
+                                    const int py = (tc.y0 + yl) >> 1, pxx = (tc.x0 + xl) >> 1;
+                                    if (tc.b < p.B && tc.y0 + yl < p.H && tc.x0 + xl < p.W) {
+                                        const size_t ppix = (static_cast<size_t>(tc.b) * (p.H >> 1) + py) * (p.W >> 1) + pxx;
+                                        uint16_t* d2 = static_cast<uint16_t*>(p.out2) + ppix * p.out2_cs + p.out2_c0 + n_tile * N + cs * 64 +
+                                                       ch * 32 + sub * 8;
+                                        st_global_v4(d2, o0, o1, o2, o3);
+                                    }
+                                }
                             }
                         });
-                        fence_proxy_async();
-                        named_bar_sync(bar_id, 128);
-                        if (issuer && !(EPI == EPI_LRELU && p.out_f32 != nullptr)) {
+                        if constexpr (TS) {
+                            fence_proxy_async();
+                            named_bar_sync(bar_id, 128);
+                        }
+                        if (TS && issuer && !(EPI == EPI_LRELU && p.out_f32 != nullptr)) {
                             const int c64 = n_tile * N + cs * 64;
                             tma_store_4d(&tmO, slab, p.out_c0 + c64, tc.x0, tc.y0, tc.b);
                             if constexpr (EPI == EPI_RELU_POOL)

@@ -13,6 +13,8 @@
 // so the result is bit-identical to Pillow.
 #include <math.h>
 
+#include <algorithm>
+
 #include "cid_internal.h"
 #include "ptx.cuh"
 
@@ -22,8 +24,19 @@ constexpr int kPrecisionBits = 32 - 8 - 2;
 
 struct ResizeCoeffs {
     int ksize = 0;
+    int out_size = 0;
     int* bounds = nullptr;  // device [out][2] = (xmin, count)
     int* kk = nullptr;      // device [out][ksize] fixed-point weights
+    std::vector<int> host_bounds;
+    // largest input span (last start + count - first start) over aligned groups of `tile` consecutive outputs
+    int max_span(int tile) const {
+        int best = 0;
+        for (int o0 = 0; o0 < out_size; o0 += tile) {
+            const int o1 = std::min(out_size, o0 + tile) - 1;
+            best = std::max(best, host_bounds[2 * o1] + host_bounds[2 * o1 + 1] - host_bounds[2 * o0]);
+        }
+        return best;
+    }
 };
 
 static double bicubic_filter(double x) {
@@ -87,6 +100,8 @@ static int get_coeffs(cid_ctx* c, int in_size, int out_size, ResizeCoeffs** out)
     CID_CHECK_CUDA(cudaMalloc(reinterpret_cast<void**>(&rc->kk), kk.size() * 4));
     CID_CHECK_CUDA(cudaMemcpy(rc->bounds, bounds.data(), bounds.size() * 4, cudaMemcpyHostToDevice));
     CID_CHECK_CUDA(cudaMemcpy(rc->kk, kk.data(), kk.size() * 4, cudaMemcpyHostToDevice));
+    rc->out_size = out_size;
+    rc->host_bounds = bounds;
     c->resize_coeffs[key] = rc;
     *out = rc;
     return 0;
@@ -128,7 +143,149 @@ __global__ void __launch_bounds__(256) resample_u8_kernel(const uint8_t* __restr
     out[t] = clip8(ss);
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Both passes in ONE kernel for 3-channel images: a block owns a TX x TY tile of the output, stages the input window it
+// needs in shared memory with 16-byte loads, runs the horizontal pass into a second shared buffer (rounded and clipped to
+// u8 exactly as Pillow's intermediate image is) and the vertical pass from there to global memory with 4-byte stores.
+// The intermediate image never touches HBM and no thread does a 64-bit division. Same integer arithmetic as the
+// two-pass kernels above (which stay as the fallback for other channel counts / extreme scale factors): bit-identical.
+// Shared memory: [row offsets R ints][kH TX*ksH ints][kV TY*ksV ints][bH TX*2][bV TY*2][s_in R x pitch][s_mid R x TX*3]
+// ---------------------------------------------------------------------------------------------------------------------
+struct ResizeFusedParams {
+    const uint8_t* in;
+    uint8_t* out;
+    int B, in_h, in_w, out_h, out_w;
+    const int *boundsH, *kkH, *boundsV, *kkV;
+    int ksH, ksV;
+    int tiles_x, tiles_y;
+    int max_rows;   // input rows a tile can need
+    int pitch;      // bytes per staged input row (multiple of 16, includes the alignment slack)
+};
+
+template <int TX, int TY>
+__global__ void __launch_bounds__(256) resize_fused_kernel(const ResizeFusedParams p) {
+    constexpr int C = 3, ROWB = TX * C;  // bytes of one tile row of the output / intermediate
+    static_assert(ROWB % 4 == 0, "4-byte stores");
+    extern __shared__ __align__(16) uint8_t rs_smem[];
+    int* row_off = reinterpret_cast<int*>(rs_smem);
+    int* kH = row_off + p.max_rows;
+    int* kV = kH + TX * p.ksH;
+    int* bH = kV + TY * p.ksV;
+    int* bV = bH + TX * 2;
+    uint8_t* s_in = reinterpret_cast<uint8_t*>(bV + TY * 2);
+    s_in += (16 - (reinterpret_cast<uintptr_t>(s_in) & 15)) & 15;
+    uint8_t* s_mid = s_in + static_cast<size_t>(p.max_rows) * p.pitch;
+
+    const int tile = blockIdx.x;
+    const int tx = tile % p.tiles_x;
+    const int ty = (tile / p.tiles_x) % p.tiles_y;
+    const int b = tile / (p.tiles_x * p.tiles_y);
+    const int x0 = tx * TX, y0 = ty * TY;
+    const int nx = min(TX, p.out_w - x0), ny = min(TY, p.out_h - y0);
+    const int tid = threadIdx.x;
+
+    // coefficient tables and bounds of this tile's output columns / rows
+    for (int i = tid; i < TX * p.ksH; i += 256) kH[i] = (i / p.ksH) < nx ? __ldg(p.kkH + static_cast<size_t>(x0) * p.ksH + i) : 0;
+    for (int i = tid; i < TY * p.ksV; i += 256) kV[i] = (i / p.ksV) < ny ? __ldg(p.kkV + static_cast<size_t>(y0) * p.ksV + i) : 0;
+    for (int i = tid; i < TX * 2; i += 256) bH[i] = (i >> 1) < nx ? __ldg(p.boundsH + 2 * x0 + i) : 0;
+    for (int i = tid; i < TY * 2; i += 256) bV[i] = (i >> 1) < ny ? __ldg(p.boundsV + 2 * y0 + i) : 0;
+    // input window: the bounds are monotone, so the first / last output column (row) of the tile give the range
+    const int xlo = __ldg(p.boundsH + 2 * x0);
+    const int xhi = __ldg(p.boundsH + 2 * (x0 + nx - 1)) + __ldg(p.boundsH + 2 * (x0 + nx - 1) + 1);
+    const int ylo = __ldg(p.boundsV + 2 * y0);
+    const int yhi = __ldg(p.boundsV + 2 * (y0 + ny - 1)) + __ldg(p.boundsV + 2 * (y0 + ny - 1) + 1);
+    const int rows = yhi - ylo, row_bytes = (xhi - xlo) * C;
+    // stage the window: per row, the 16-byte chunks that cover [start, start + row_bytes); the row keeps its misalignment
+    const size_t img_end = static_cast<size_t>(p.B) * p.in_h * p.in_w * C;
+    const int chunks = (row_bytes + 15 + 15) / 16;  // upper bound incl. the misalignment
+    for (int i = tid; i < rows * chunks; i += 256) {
+        const int r = i / chunks, ck = i - r * chunks;
+        const size_t start = ((static_cast<size_t>(b) * p.in_h + ylo + r) * p.in_w + xlo) * C;
+        const size_t a0 = start & ~static_cast<size_t>(15);
+        const size_t a = a0 + static_cast<size_t>(ck) * 16;
+        if (ck == 0) row_off[r] = static_cast<int>(start - a0);
+        if (a < start + row_bytes) {
+            uint4 v;
+            if (a + 16 <= img_end && (reinterpret_cast<uintptr_t>(p.in) & 15) == 0) {
+                v = __ldg(reinterpret_cast<const uint4*>(p.in + a));
+            } else {  // the tensor's tail (or an unaligned base pointer): byte loads
+                uint8_t t[16];
+                for (int e = 0; e < 16; ++e) t[e] = a + e < img_end ? p.in[a + e] : 0;
+                v = *reinterpret_cast<const uint4*>(t);
+            }
+            *reinterpret_cast<uint4*>(s_in + static_cast<size_t>(r) * p.pitch + ck * 16) = v;
+        }
+    }
+    __syncthreads();
+    // horizontal pass: 4 consecutive bytes (x, c) of one staged row per thread-iteration
+    for (int i = tid; i < rows * (ROWB / 4); i += 256) {
+        const int r = i / (ROWB / 4), j4 = (i - r * (ROWB / 4)) * 4;
+        const uint8_t* row = s_in + static_cast<size_t>(r) * p.pitch + row_off[r];
+        uint32_t packed = 0;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const int j = j4 + e, xx = j / C, c = j - xx * C;
+            const int lo = bH[2 * xx] - xlo, cnt = bH[2 * xx + 1];
+            const int* k = kH + xx * p.ksH;
+            const uint8_t* src = row + lo * C + c;
+            int ss = 1 << (kPrecisionBits - 1);
+            for (int t = 0; t < cnt; ++t) ss += static_cast<int>(src[t * C]) * k[t];
+            packed |= static_cast<uint32_t>(clip8(ss)) << (8 * e);
+        }
+        *reinterpret_cast<uint32_t*>(s_mid + r * ROWB + j4) = packed;
+    }
+    __syncthreads();
+    // vertical pass
+    const bool wide = (p.out_w * C) % 4 == 0 && (reinterpret_cast<uintptr_t>(p.out) & 3) == 0;
+    for (int i = tid; i < ny * (ROWB / 4); i += 256) {
+        const int yy = i / (ROWB / 4), j4 = (i - yy * (ROWB / 4)) * 4;
+        if (j4 >= nx * C) continue;
+        const int lo = bV[2 * yy] - ylo, cnt = bV[2 * yy + 1];
+        const int* k = kV + yy * p.ksV;
+        int s0 = 1 << (kPrecisionBits - 1), s1 = s0, s2 = s0, s3 = s0;
+        for (int t = 0; t < cnt; ++t) {
+            const uint32_t v = *reinterpret_cast<const uint32_t*>(s_mid + (lo + t) * ROWB + j4);
+            const int kt = k[t];
+            s0 += static_cast<int>(v & 0xffu) * kt;
+            s1 += static_cast<int>((v >> 8) & 0xffu) * kt;
+            s2 += static_cast<int>((v >> 16) & 0xffu) * kt;
+            s3 += static_cast<int>(v >> 24) * kt;
+        }
+        uint8_t* dst = p.out + ((static_cast<size_t>(b) * p.out_h + y0 + yy) * p.out_w + x0) * C + j4;
+        const uint32_t o = static_cast<uint32_t>(clip8(s0)) | (static_cast<uint32_t>(clip8(s1)) << 8) |
+                           (static_cast<uint32_t>(clip8(s2)) << 16) | (static_cast<uint32_t>(clip8(s3)) << 24);
+        if (wide && j4 + 4 <= nx * C) {
+            *reinterpret_cast<uint32_t*>(dst) = o;
+        } else {
+            for (int e = 0; e < 4; ++e)
+                if (j4 + e < nx * C) dst[e] = static_cast<uint8_t>(o >> (8 * e));
+        }
+    }
+}
+
 // ToTensor + Normalize: u8 NHWC -> fp32 NCHW, (v/255 - mean)/std with each op rounded in fp32.
+// Vector form (H*W a multiple of 4): a thread converts 4 consecutive pixels - three 4-byte loads, a 256-entry table in
+// shared memory built with the exact fp32 operation sequence, three 16-byte stores (one per channel plane).
+__global__ void __launch_bounds__(256) normalize4_kernel(const uint8_t* __restrict__ in, float* __restrict__ out, size_t quads,
+                                                         size_t plane, float mean, float stdv) {
+    __shared__ float lut[256];
+    lut[threadIdx.x] = __fdiv_rn(__fsub_rn(__fdiv_rn(static_cast<float>(threadIdx.x), 255.f), mean), stdv);
+    __syncthreads();
+    const size_t q = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (q >= quads) return;
+    const size_t pix = q * 4;
+    const size_t b = pix / plane, r = pix - b * plane;
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(in + pix * 3);
+    const uint32_t w0 = __ldg(src), w1 = __ldg(src + 1), w2 = __ldg(src + 2);  // r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3
+    float* o = out + b * 3 * plane + r;
+    const float4 cr = make_float4(lut[w0 & 0xff], lut[w0 >> 24], lut[(w1 >> 16) & 0xff], lut[(w2 >> 8) & 0xff]);
+    const float4 cg = make_float4(lut[(w0 >> 8) & 0xff], lut[w1 & 0xff], lut[w1 >> 24], lut[(w2 >> 16) & 0xff]);
+    const float4 cb = make_float4(lut[(w0 >> 16) & 0xff], lut[(w1 >> 8) & 0xff], lut[w2 & 0xff], lut[w2 >> 24]);
+    *reinterpret_cast<float4*>(o) = cr;
+    *reinterpret_cast<float4*>(o + plane) = cg;
+    *reinterpret_cast<float4*>(o + 2 * plane) = cb;
+}
+
 __global__ void __launch_bounds__(256) normalize_kernel(const uint8_t* __restrict__ in, float* __restrict__ out, int B,
                                                         int H, int W, float mean, float stdv) {
     const size_t total = static_cast<size_t>(B) * H * W;
@@ -159,6 +316,36 @@ int cid_resize_bicubic_u8(cid_handle h, const uint8_t* in, uint8_t* out, uint8_t
     ResizeCoeffs *ch = nullptr, *cv = nullptr;
     if (get_coeffs(h, in_w, out_w, &ch)) return 1;
     if (get_coeffs(h, in_h, out_h, &cv)) return 1;
+    if (C == 3) {
+        // fused two-pass kernel: the largest tile whose input window fits in shared memory
+        const int tiles[3][2] = {{64, 16}, {32, 8}, {16, 4}};
+        for (int ti = 0; ti < 3; ++ti) {
+            const int TX = tiles[ti][0], TY = tiles[ti][1];
+            const int max_cols = std::min(in_w, ch->max_span(TX)), max_rows = std::min(in_h, cv->max_span(TY));
+            ResizeFusedParams p;
+            p.in = in; p.out = out; p.B = B; p.in_h = in_h; p.in_w = in_w; p.out_h = out_h; p.out_w = out_w;
+            p.boundsH = ch->bounds; p.kkH = ch->kk; p.boundsV = cv->bounds; p.kkV = cv->kk;
+            p.ksH = ch->ksize; p.ksV = cv->ksize;
+            p.tiles_x = (out_w + TX - 1) / TX; p.tiles_y = (out_h + TY - 1) / TY;
+            p.max_rows = max_rows;
+            p.pitch = (max_cols * 3 + 15 + 15) / 16 * 16 + 16;
+            const size_t smem = static_cast<size_t>(max_rows) * 4 + static_cast<size_t>(TX) * p.ksH * 4 + static_cast<size_t>(TY) * p.ksV * 4 +
+                                (TX + TY) * 8 + 16 + static_cast<size_t>(max_rows) * p.pitch + static_cast<size_t>(max_rows) * TX * 3;
+            if (smem > 100 * 1024) continue;  // two blocks per SM at least
+            const long long nblocks = static_cast<long long>(B) * p.tiles_x * p.tiles_y;
+            CID_REQUIRE(nblocks < (1ll << 31), "resize: too many tiles");
+            auto launch = [&](auto kern) -> int {
+                CID_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+                kern<<<static_cast<unsigned>(nblocks), 256, smem, st>>>(p);
+                CID_CHECK_CUDA(cudaGetLastError());
+                return 0;
+            };
+            const int rc = ti == 0 ? launch(resize_fused_kernel<64, 16>) : ti == 1 ? launch(resize_fused_kernel<32, 8>) : launch(resize_fused_kernel<16, 4>);
+            if (rc) return 1;
+            h->launches++;
+            return 0;
+        }
+    }
     {
         const size_t total = static_cast<size_t>(B) * in_h * out_w * C;
         resample_u8_kernel<true><<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(
@@ -183,8 +370,13 @@ int cid_normalize_u8_to_f32_nchw(cid_handle h, const uint8_t* in, float* out, in
     DeviceGuard g(h->device);
     CID_REQUIRE(g.ok, "cannot select CUDA device %d", h->device);
     const size_t total = static_cast<size_t>(B) * H * W;
-    normalize_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        in, out, B, H, W, mean, stdv);
+    const size_t plane = static_cast<size_t>(H) * W;
+    if (plane % 4 == 0 && ((reinterpret_cast<uintptr_t>(in) & 3) | (reinterpret_cast<uintptr_t>(out) & 15)) == 0)
+        normalize4_kernel<<<static_cast<unsigned>((total / 4 + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+            in, out, total / 4, plane, mean, stdv);
+    else
+        normalize_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+            in, out, B, H, W, mean, stdv);
     CID_CHECK_CUDA(cudaGetLastError());
     h->launches++;
     return 0;

@@ -213,7 +213,7 @@ static int launch_conv_t(cid_train* t, const CUtensorMap& tmA, const CUtensorMap
                          cudaStream_t st) {
     using Cfg = ConvCfg<N, TAPS, S, WRES, EPI, PW, TS, CG>;
     cid_ctx* c = t->g;
-    const int budget = c->max_smem - 1024 - 512 - Cfg::O_BYTES;
+    const int budget = c->max_smem - 1024 - 1024 - Cfg::O_BYTES;
     int w_stages = WRES ? 1 : (N == 256 && TS ? 3 : 4);
     const int w_bytes = (WRES ? p.kb_count * TAPS : w_stages) * Cfg::W_BYTES;
     int a_stages = std::min(kMaxStages, (budget - w_bytes) / Cfg::A_BYTES);
