@@ -396,6 +396,27 @@ def test_patch_app_on_a_stand_in_module(dev, tmp_path):
         check_float(net(x.to(dev)).cpu(), orc.forward(sd2, x), x)
 
 
+def test_micro_batcher_concurrent_uploads(dev):
+    """concurrent upload-route requests (backend/app.py:401-406, one batch of one each) share batched
+    forwards through MicroBatcher; every caller gets exactly what a single-image call returns, within +-1 LSB of the
+    reference route, and fewer forwards run than requests arrived."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    from cid_b200 import MicroBatcher
+    net, sd = make_net(dev, 4, 2.0)
+    imgs = [synthetic_noisy_u8(100 + i, 1, 30, 27)[0].numpy() for i in range(12)] + \
+           [synthetic_noisy_u8(200 + i, 1, 64, 48)[0].numpy() for i in range(8)]
+    singles = [enhance_batch_u8(net, torch.from_numpy(im)[None].to(dev))[0].cpu().numpy() for im in imgs]
+    with MicroBatcher(net, device=dev, max_batch=8, max_wait_ms=50.0) as mb:
+        with ThreadPoolExecutor(20) as ex:
+            outs = list(ex.map(mb.enhance, imgs))
+    for im, o, s1 in zip(imgs, outs, singles):
+        assert np.array_equal(o, s1)                                   # batching is invisible: bit-identical
+        ref = orc.enhance_u8(sd, im[None])[0]
+        assert np.abs(o.astype(np.int32) - ref.astype(np.int32)).max() <= LSB
+    assert sum(mb.batches) == 20 and len(mb.batches) < 20 and max(mb.batches) <= 8
+
+
 @pytest.mark.parametrize("H,W", [(256, 256), (512, 512)])
 def test_high_resolution_single_image(dev, H, W):
     """BASELINE.json configs[3]: the upload-route shape, batch 1."""

@@ -156,3 +156,44 @@ def test_public_surface():
                  "enhance_batch_u8", "enhance_batch_host", "patch_app"):
         assert hasattr(cid_b200, name)
     assert cid_b200.MODEL_CFG["denoise"]["pad_divisor"] == 4 and cid_b200.MODEL_CFG["denoise"]["scale"] == 1
+
+
+def test_micro_batcher_groups_concurrent_requests_by_shape():
+    """Route-level micro-batching (backend/app.py:401-406 builds a batch of one per request): requests
+    queued together run as one forward per image size, every caller gets its own image's result, errors propagate."""
+    import threading
+
+    from cid_b200 import MicroBatcher
+    from cid_b200.batcher import _Request, group_by_shape
+
+    reqs = [_Request(np.zeros((h, w, 3), np.uint8)) for h, w in [(8, 8), (8, 12), (8, 8), (8, 8), (8, 12), (8, 8)]]
+    groups = group_by_shape(reqs, max_batch=3)
+    assert [[r.image.shape[:2] for r in g] for g in groups] == [[(8, 8)] * 3, [(8, 12)] * 2, [(8, 8)]]
+
+    gate = threading.Event()
+    seen = []
+
+    def run_batch(host_in):                      # stands in for H2D -> cid_forward_u8_nhwc -> D2H
+        gate.wait(5)
+        seen.append(tuple(host_in.shape))
+        if host_in.shape[1] == 5:
+            raise RuntimeError("cid_forward_u8_nhwc: boom")
+        return 255 - host_in
+
+    rng = np.random.default_rng(0)
+    with MicroBatcher(run_batch=run_batch, device="cpu", max_batch=4, max_wait_ms=200.0) as mb:
+        imgs = [rng.integers(0, 256, (6, 7, 3), dtype=np.uint8) for _ in range(6)] + \
+               [rng.integers(0, 256, (9, 4, 3), dtype=np.uint8) for _ in range(2)]
+        futs = [mb.submit(im) for im in imgs]
+        bad = mb.submit(np.zeros((5, 5, 3), np.uint8))
+        gate.set()
+        for im, f in zip(imgs, futs):
+            assert np.array_equal(f.result(10), 255 - im)
+        with pytest.raises(RuntimeError, match="boom"):
+            bad.result(10)
+        with pytest.raises(ValueError):
+            mb.submit(np.zeros((4, 4), np.uint8))
+    assert sum(mb.batches) == 8 and len(mb.batches) < 8 and max(mb.batches) <= 4     # batched, bounded by max_batch
+    assert all(s[1:] in ((6, 7, 3), (9, 4, 3), (5, 5, 3)) for s in seen)
+    with pytest.raises(RuntimeError):
+        mb.submit(imgs[0])                         # closed
