@@ -548,8 +548,6 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         p.out2 = buf(B_P1); p.out2_cs = 64; p.out2_c0 = 0;
         if (pick_split(c, tiles(0), 64, 2, 2)) {  // one tile per CTA, weights resident
             if (launch_conv<64, 9, 1, true, EPI_RELU_POOL, 10, 1>(c, 24, pl->tmA[1], c->tmW[1], pl->tmO[1], pl->tmO2[1], p, st)) return 1;
-        } else if (c->direct_store & 1) {
-            if (launch_conv<64, 9, 2, true, EPI_RELU_POOL, 10, 0, 2>(c, 10, pl->tmA[1], c->tmWh[1], pl->tmO[1], pl->tmO2[1], p, st)) return 1;
         } else {
             if (launch_conv<64, 9, 2, true, EPI_RELU_POOL, 10, 1, 2>(c, 10, pl->tmA[1], c->tmWh[1], pl->tmO[1], pl->tmO2[1], p, st)) return 1;
         }
@@ -586,11 +584,17 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         }
         if (prof_mark(c, st)) return 1;
     }
-    {  // L6 up2 (convT) -> cat2[:,0:128]; CTA pair: each CTA streams half of the 256 KB weight matrix per tile pair
+    {  // L6 up2 (convT) -> cat2[:,0:128]; 4*128 columns in two blocks of 256. CTA pair; by default a pair keeps ITS column
+       // block's half of the weight matrix (2 x 64 KB) resident and walks every pixel tile (the A tiles are read twice, from
+       // L2); "up2_stream" = each CTA streams half of the 256 KB weight matrix per tile pair instead
         ConvParams p = base(6, 2);
-        p.n_tiles = 2;  // 4*128 columns in tiles of 256
+        p.n_tiles = 2;
         p.out = buf(B_CAT2); p.out_cs = 256; p.out_c0 = 0;
-        if (launch_conv<256, 1, 1, false, EPI_CONVT, 0, 1, 2>(c, 20, pl->tmA[6], c->tmWh[6], pl->tmO[6], pl->tmO[6], p, st)) return 1;
+        if (c->up2_stream) {
+            if (launch_conv<256, 1, 1, false, EPI_CONVT, 0, 1, 2>(c, 20, pl->tmA[6], c->tmWh[6], pl->tmO[6], pl->tmO[6], p, st)) return 1;
+        } else {
+            if (launch_conv<256, 1, 1, true, EPI_CONVT, 0, 1, 2>(c, 20, pl->tmA[6], c->tmWh[6], pl->tmO[6], pl->tmO[6], p, st)) return 1;
+        }
     }
     if (prof_mark(c, st)) return 1;
     for (int l = 7; l <= 8; ++l) {  // L7 upconv2.0 (reads cat2) -> u2a, L8 upconv2.2 -> u2b
@@ -613,11 +617,7 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
     {  // L10 upconv1.0 (reads cat1) -> u1a; CTA pair (resident weights halved: 74 KB per CTA)
         ConvParams p = base(10, 0);
         p.out = buf(B_U1A); p.out_cs = 64; p.out_c0 = 0;
-        if (c->direct_store & 2) {
-            if (launch_conv<64, 9, 1, true, EPI_RELU, 10, 0, 2>(c, 15, pl->tmA[10], c->tmWh[10], pl->tmO[10], pl->tmO[10], p, st)) return 1;
-        } else {
-            if (launch_conv<64, 9, 1, true, EPI_RELU, 10, 1, 2>(c, 15, pl->tmA[10], c->tmWh[10], pl->tmO[10], pl->tmO[10], p, st)) return 1;
-        }
+        if (launch_conv<64, 9, 1, true, EPI_RELU, 10, 1, 2>(c, 15, pl->tmA[10], c->tmWh[10], pl->tmO[10], pl->tmO[10], p, st)) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L11 upconv1.2 + tanh -> y   (transposed GEMM: weights on M, the halo patch on N)
@@ -952,10 +952,12 @@ int cid_set_option(cid_handle h, const char* name, int64_t value) {
         for (auto& pl : h->plans) { graph_release(pl.graph[0]); graph_release(pl.graph[1]); }
         return 0;
     }
-    // N = 64 layers: epilogue writes global memory straight from registers instead of staging + TMA store
-    // (bit 0 = down1.2, bit 1 = upconv1.0; identical results)
-    if (!strcmp(name, "direct_store")) {
-        h->direct_store = static_cast<int>(value);
+    if (!strcmp(name, "sp_scatter")) {  // salt & pepper noiser: 1 = copy + scatter launches instead of the one-pass slab kernel
+        h->sp_scatter = value != 0;
+        return 0;
+    }
+    if (!strcmp(name, "up2_stream")) {  // A/B switch for up2's weight handling (run_layers, L6)
+        h->up2_stream = value != 0;
         return 0;
     }
     if (!strcmp(name, "graph")) {  // CUDA-graph replay of launch-bound passes (default on)

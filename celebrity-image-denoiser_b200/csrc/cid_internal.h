@@ -102,7 +102,8 @@ struct cid_ctx {
     uint32_t attr_done = 0;           // bit per kernel instantiation: max-dynamic-smem attribute set
     std::map<uint64_t, void*> resize_coeffs;  // (in_size,out_size) -> device coefficient block
     int regime = 0;                   // "regime" option: 0 per-layer choice, 1 batch-256 configuration, 2 N-split form
-    int direct_store = 0;             // "direct_store" option (N = 64 layers' epilogue without shared-memory staging)
+    bool sp_scatter = false;          // "sp_scatter" option: salt & pepper as copy + two scatter launches (the fallback form)
+    bool up2_stream = false;          // "up2_stream" option: stream up2's weights instead of keeping a column block resident
     bool use_graph = true;            // "graph" option: CUDA-graph replay of launch-bound passes
     bool graph_broken = false;        // capture / node update failed once: eager launches from then on
     void* capture_stream = nullptr;   // cudaStream_t the graphs are captured on (nothing ever executes on it)

@@ -32,6 +32,9 @@ enum : int {  // TANH_*: last_conv_umma.cuh; LRELU/T4: the Keras cGAN layers (le
     EPI_RELU = 0, EPI_RELU_POOL = 1, EPI_CONVT = 2, EPI_TANH_F32 = 3, EPI_TANH_U8 = 4, EPI_LRELU = 5, EPI_T4 = 6, EPI_TANH_F32_NHWC = 7,
     EPI_ADD = 8,  // bias + residual add(s), no activation (ESRGAN / SRGAN skip connections)
     EPI_LINEAR_F32_NHWC = 10,  // last_conv_umma.cuh without tanh: the discriminator's 64 -> 3 input gradient
+    EPI_LRELU_BN = 11,  // training: EPI_LRELU whose result goes out as fp32 NHWC (ConvParams::out_f32) with the BatchNorm batch
+                        // statistics reduced in the epilogue (ConvParams::stats). A separate instantiation: the extra live
+                        // registers and branches cost the inference LeakyReLU layers 40 % (ESRGAN block.0 0.25 -> 0.41 ms)
     EPI_DGRAD = 9  // training: data gradient = bias-free linear output, optionally masked by the ReLU of the layer's
                    // own input activation (ConvParams::res2 = that activation, > 0 keeps the gradient)
 };
@@ -63,11 +66,11 @@ struct ConvParams {
     int bias_per_column; // EPI_CONVT as pixel shuffle: bias indexed by GEMM column instead of by channel
     float mask_slope;    // EPI_T4 with res2 set (training): the output gradient is multiplied by the LeakyReLU derivative of
                          // the activation res2 at the OUTPUT pixel (1 where it is positive, mask_slope elsewhere)
-    double* stats;       // EPI_LRELU with out_f32 (training): per-channel sum (stats[c]) and sum of squares (stats[128 + c])
+    double* stats;       // EPI_LRELU_BN (training): per-channel sum (stats[c]) and sum of squares (stats[128 + c])
                          // of the fp32 outputs over all real pixels = the batch statistics of the BatchNorm that follows,
                          // reduced in the epilogue (warp transpose-sum, per-CTA register accumulators, one double atomic
                          // per channel per warp at the end); may be null
-    float* out_f32;      // EPI_LRELU only: if set, the result is written as fp32 NHWC straight from registers (no bf16
+    float* out_f32;      // EPI_LRELU_BN only: the result is written as fp32 NHWC straight from registers (no bf16
                          // staging / TMA store): the discriminator's pre-BatchNorm outputs, whose mean >> std
 };
 
@@ -117,17 +120,19 @@ struct ConvCfg {
                                                              : 512;
     // The epilogue stages each 64-channel slab of a tile in shared memory (SW128 rows, same geometry as
     // the A boxes) and writes it with one TMA store. Each of the 2 epilogue groups has NOB buffers.
-    // TS = 1: the epilogue stages each output slab in shared memory and writes it with one TMA store. TS = 0 (EPI_RELU /
-    // EPI_RELU_POOL only): every thread writes its pixel's channels straight from registers with 16-byte global stores -
-    // the N = 64 layers sit on the shared-memory roofline, and staging costs 32-40 KB of shared-memory
-    // traffic per tile (write + TMA read) on top of the ~200 KB the MMAs need.
-    static_assert(TS == 1 || (TS == 0 && (EPI == EPI_RELU || EPI == EPI_RELU_POOL)), "direct stores: ReLU epilogues only");
+    // TS = 1: the epilogue stages each output slab in shared memory and writes it with one TMA store (the only form; a
+    // register-direct 16-byte-store epilogue for the N = 64 layers measured 60 % SLOWER on down1.2 - every warp store
+    // touches 32 lines with 16 bytes each - profiles/r02b_direct_store_*.json - and was removed).
+    static_assert(TS == 1, "staged epilogue");
     static constexpr int NOB = 1;  // staging buffers per group (the other group's buffer gives the overlap)
     static constexpr int O_SLAB = 128 * 128;
     static constexpr int O2_SLAB = 32 * 128;
     static constexpr int OT_SLAB = 256 * 128;  // transposed convs: [16 rows][16 px][64 ch] of the 2x-upsampled output
     static constexpr int O_GROUP = NOB * (O_SLAB + (EPI == EPI_RELU_POOL ? O2_SLAB : 0));
-    static constexpr int O_BYTES = !TS ? 0 : (EPI == EPI_CONVT || EPI == EPI_T4) ? 2 * OT_SLAB : 2 * O_GROUP;
+    // EPI_ADD: each group also owns a residual buffer (one slab) that the block-skip tile is TMA-loaded into one work item
+    // ahead, so the load overlaps the previous slab's TMA store and the wait for the next accumulator
+    static constexpr int R_BYTES = EPI == EPI_ADD ? 2 * O_SLAB : 0;
+    static constexpr int O_BYTES = !TS ? 0 : (EPI == EPI_CONVT || EPI == EPI_T4) ? 2 * OT_SLAB : 2 * O_GROUP + R_BYTES;
     // dynamic shared memory needed (bytes), including 1 KB of alignment slack
     static int smem_bytes(int kb_count, int a_stages, int w_stages) {
         int w_items = WRES ? kb_count * TAPS : w_stages;
@@ -347,10 +352,12 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     tma_load_2d(dst, &tmW, bar, c0, row, kEvictLast);
             };
             if (WRES) {
+                // n_tiles > 1 (host guarantees units % n_tiles == 0): this CTA only ever sees column block unit % n_tiles
+                const int wrow0 = (unit % p.n_tiles) * N;
                 expect(&w_full[0], static_cast<uint32_t>(w_items) * W_BYTES);
                 for (int kb = 0; kb < p.kb_count; ++kb)
                     for (int tap = 0; tap < TAPS; ++tap)
-                        load_w(w_smem + (kb * TAPS + tap) * W_BYTES, &w_full[0], kb * 64, tap * p.w_rows_per_tap);
+                        load_w(w_smem + (kb * TAPS + tap) * W_BYTES, &w_full[0], kb * 64, tap * p.w_rows_per_tap + wrow0);
             }
             uint32_t a_stage = 0, a_phase = 0, w_stage = 0, w_phase = 0;
             const int kb_total = p.kb_count * KSUB;
@@ -529,14 +536,16 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const bool issuer = (threadIdx.x == 64 + 128 * g);  // lane 0 of the group's first warp
         const int bar_id = 1 + g;
         uint8_t* og = o_smem + g * Cfg::O_GROUP;
+        uint8_t* rg = o_smem + 2 * Cfg::O_GROUP + g * Cfg::O_SLAB;  // EPI_ADD: this group's residual buffer
+        (void)rg;
         uint32_t acc_it = 0;
         uint32_t o_count = 0;  // slabs this group has staged so far
-        // BatchNorm statistics (EPI_LRELU + stats): lane = channel inside a 32-channel chunk
-        float st_sum[EPI == EPI_LRELU ? N / 32 : 1], st_sq[EPI == EPI_LRELU ? N / 32 : 1];
+        // BatchNorm statistics (EPI_LRELU_BN): lane = channel inside a 32-channel chunk
+        float st_sum[EPI == EPI_LRELU_BN ? N / 32 : 1], st_sq[EPI == EPI_LRELU_BN ? N / 32 : 1];
 #pragma unroll
-        for (int i = 0; i < (EPI == EPI_LRELU ? N / 32 : 1); ++i) st_sum[i] = st_sq[i] = 0.f;
+        for (int i = 0; i < (EPI == EPI_LRELU_BN ? N / 32 : 1); ++i) st_sum[i] = st_sq[i] = 0.f;
         // EPI_ADD: the first residual tensor (tmO2 = its tile map, same geometry as the output's) is TMA-loaded into
-        // the group's staging slab one work item ahead: right after the slab's previous TMA store has been read out.
+        // the group's residual buffer one work item ahead: as soon as the previous item's add has read the buffer.
         // Group g owns exactly slab j = g of every work item (S * N/64 == 2). Out-of-image pixels load as zeros.
         const bool res_tma = EPI == EPI_ADD && p.res != nullptr;
         auto issue_residual = [&](int w) {
@@ -546,7 +555,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 const int sj = g / (N / 64), csj = g % (N / 64);
                 const TileCoord tcr = decode_tile(p, (stw * CG + static_cast<int>(rank)) * S + sj);
                 mbar_arrive_expect_tx(&res_full[g], Cfg::O_SLAB);
-                tma_load_4d(og, &tmO2, &res_full[g], nt * N + csj * 64, tcr.x0, tcr.y0, tcr.b, kEvictFirst);
+                tma_load_4d(rg, &tmO2, &res_full[g], nt * N + csj * 64, tcr.x0, tcr.y0, tcr.b, kEvictFirst);
             }
         };
         if (res_tma && issuer && unit < p.num_work) {
@@ -563,13 +572,13 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             tc_fence_after();
             const uint32_t tbase = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * Cfg::ACC_COLS;
             {
-                if constexpr (EPI == EPI_RELU || EPI == EPI_RELU_POOL || EPI == EPI_LRELU || EPI == EPI_ADD || EPI == EPI_DGRAD) {
+                if constexpr (EPI == EPI_RELU || EPI == EPI_RELU_POOL || EPI == EPI_LRELU || EPI == EPI_LRELU_BN || EPI == EPI_ADD || EPI == EPI_DGRAD) {
                     constexpr int SL = N / 64;  // 64-channel slabs per pixel tile
                     const int sub = (xl & 1) | ((yl & 1) << 1);
                     const int prow_i = (yl >> 1) * 4 + (xl >> 1);
                     const float slope = p.slope;
                     auto act = [&](float x) {  // ReLU, or LeakyReLU(slope) for the Keras layers
-                        if constexpr (EPI == EPI_LRELU) return x > 0.f ? x : x * slope;
+                        if constexpr (EPI == EPI_LRELU || EPI == EPI_LRELU_BN) return x > 0.f ? x : x * slope;
                         if constexpr (EPI == EPI_ADD || EPI == EPI_DGRAD) return x;
                         return fmaxf(x, 0.f);
                     };
@@ -616,18 +625,18 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
                                 for (int i = 0; i < 8; ++i) rv2[i] = __ldg(r2 + i);
                             }
-                            if (res_tma) mbar_wait(&res_full[g], acc_it & 1);  // the residual tile is in `slab`
+                            if (res_tma) mbar_wait(&res_full[g], acc_it & 1);  // the residual tile is in `rg`
                         }
                         for_each_chunk<2>(tbase + s * Cfg::NACC + cs * 64, [&](int ch, uint32_t (&v)[32]) {
                             const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_tile * N + cs * 64 + ch * 32);
                             uint32_t pk[16];
-                            float fv[EPI == EPI_LRELU ? 32 : 1];
+                            float fv[EPI == EPI_LRELU_BN ? 32 : 1];
                             if constexpr (EPI == EPI_ADD) {
                                 // v[2i], v[2i+1] += the bf16 pair i of this 32-channel half
 #pragma unroll
                                 for (int i = 0; i < 4; ++i) {
                                     const int cjr = ch * 4 + i;
-                                    const uint4 a = res_tma ? ld_shared_v4(slab + row * 128 + ((cjr ^ (row & 7)) << 4))
+                                    const uint4 a = res_tma ? ld_shared_v4(rg + row * 128 + ((cjr ^ (row & 7)) << 4))
                                                             : make_uint4(0u, 0u, 0u, 0u);
                                     const uint4 b = rv2[ch * 4 + i];
                                     const uint32_t w[4] = {a.x, a.y, a.z, a.w}, w2[4] = {b.x, b.y, b.z, b.w};
@@ -666,7 +675,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                 const float f3 = act(__uint_as_float(v[4 * jj + 3]) + bb.w);
                                 pk[2 * jj + 0] = pack_bf16x2(f0, f1);
                                 pk[2 * jj + 1] = pack_bf16x2(f2, f3);
-                                if constexpr (EPI == EPI_LRELU) {
+                                if constexpr (EPI == EPI_LRELU_BN) {
                                     fv[4 * jj + 0] = f0; fv[4 * jj + 1] = f1; fv[4 * jj + 2] = f2; fv[4 * jj + 3] = f3;
                                     if (p.out_f32 != nullptr) {
                                         const int yy = tc.y0 + yl, xx = tc.x0 + xl;
@@ -678,7 +687,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                     }
                                 }
                             }
-                            if constexpr (EPI == EPI_LRELU) {
+                            if constexpr (EPI == EPI_LRELU_BN) {
                                 if (p.stats != nullptr) {
                                     const bool live = tc.b < p.B && tc.y0 + yl < p.H && tc.x0 + xl < p.W;
                                     float sq[32];
@@ -699,15 +708,6 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                     st_shared_v4(rowp + ((cj ^ (row & 7)) << 4), pk[4 * jj], pk[4 * jj + 1], pk[4 * jj + 2],
                                                  pk[4 * jj + 3]);
                                 }
-                            } else {
-                                const int yy = tc.y0 + yl, xx = tc.x0 + xl;
-                                if (tc.b < p.B && yy < p.H && xx < p.W) {
-                                    const size_t pix = (static_cast<size_t>(tc.b) * p.H + yy) * p.W + xx;
-                                    uint16_t* dst = static_cast<uint16_t*>(p.out) + pix * p.out_cs + p.out_c0 + n_tile * N + cs * 64 + ch * 32;
-#pragma unroll
-                                    for (int jj = 0; jj < 4; ++jj)
-                                        st_global_v4(dst + jj * 8, pk[4 * jj], pk[4 * jj + 1], pk[4 * jj + 2], pk[4 * jj + 3]);
-                                }
                             }
                             if constexpr (EPI == EPI_RELU_POOL) {
                                 // 2x2 max: x partner is lane^1, y partner is lane^8 (row = y*8 + x).
@@ -724,15 +724,6 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                 if constexpr (TS) {
                                     const int cj = ch * 4 + sub;
                                     st_shared_v4(slab2 + prow_i * 128 + ((cj ^ (prow_i & 7)) << 4), o0, o1, o2, o3);
-                                } else {
-                                    // this lane's quarter (8 channels) of the pooled pixel (H, W are even)
-                                    const int py = (tc.y0 + yl) >> 1, pxx = (tc.x0 + xl) >> 1;
-                                    if (tc.b < p.B && tc.y0 + yl < p.H && tc.x0 + xl < p.W) {
-                                        const size_t ppix = (static_cast<size_t>(tc.b) * (p.H >> 1) + py) * (p.W >> 1) + pxx;
-                                        uint16_t* d2 = static_cast<uint16_t*>(p.out2) + ppix * p.out2_cs + p.out2_c0 + n_tile * N + cs * 64 +
-                                                       ch * 32 + sub * 8;
-                                        st_global_v4(d2, o0, o1, o2, o3);
-                                    }
                                 }
                             }
                         });
@@ -740,17 +731,15 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             fence_proxy_async();
                             named_bar_sync(bar_id, 128);
                         }
-                        if (TS && issuer && !(EPI == EPI_LRELU && p.out_f32 != nullptr)) {
+                        if (TS && issuer && !(EPI == EPI_LRELU_BN && p.out_f32 != nullptr)) {
                             const int c64 = n_tile * N + cs * 64;
                             tma_store_4d(&tmO, slab, p.out_c0 + c64, tc.x0, tc.y0, tc.b);
                             if constexpr (EPI == EPI_RELU_POOL)
                                 tma_store_4d(&tmO2, slab2, p.out2_c0 + c64, tc.x0 >> 1, tc.y0 >> 1, tc.b);
                             bulk_commit();
                         }
-                        if (res_tma && issuer && work + units < p.num_work) {
-                            bulk_wait_read<0>();  // the store above has read the slab: it can take the next residual tile
-                            issue_residual(work + units);
-                        }
+                        // (every thread of the group passed the barrier above after its last read of `rg`)
+                        if (res_tma && issuer && work + units < p.num_work) issue_residual(work + units);
                         ++o_count;
                     }
                 } else if constexpr (EPI == EPI_T4) {
@@ -895,7 +884,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
             ++acc_it;
         }
-        if constexpr (EPI == EPI_LRELU) {
+        if constexpr (EPI == EPI_LRELU_BN) {
             if (p.stats != nullptr) {
 #pragma unroll
                 for (int i = 0; i < N / 32; ++i) {

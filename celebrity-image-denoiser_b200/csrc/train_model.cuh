@@ -668,7 +668,7 @@ static int d_forward(const TrainRun& r, const float* img) {
         p.out_f32 = static_cast<float*>(r.tbuf(TB_DZ1D));
         p.stats = t->dsc + DS_BN + 0 * 256;  // batch statistics reduced in the epilogue
         CID_CHECK_CUDA(cudaMemsetAsync(p.stats, 0, 256 * 8, r.st));
-        if (launch_conv_t<64, 16, 2, false, EPI_LRELU, 9, 1>(t, *tmA, t->df_tm[1], *tmO, p, r.st)) return 1;
+        if (launch_conv_t<64, 16, 2, false, EPI_LRELU_BN, 9, 1>(t, *tmA, t->df_tm[1], *tmO, p, r.st)) return 1;
     }
     if (bn_forward(r, 1, r.tbuf(TB_DZ1D), r.tbuf(TB_DA1), 1)) return 1;
     {  // model.5: 3x3 64 -> 128 -> z2
@@ -681,7 +681,7 @@ static int d_forward(const TrainRun& r, const float* img) {
         p.out_f32 = static_cast<float*>(r.tbuf(TB_DZ2D));
         p.stats = t->dsc + DS_BN + 1 * 256;  // batch statistics reduced in the epilogue
         CID_CHECK_CUDA(cudaMemsetAsync(p.stats, 0, 256 * 8, r.st));
-        if (launch_conv_t<128, 9, 2, false, EPI_LRELU, 10, 1>(t, *tmA, t->df_tm[2], *tmO, p, r.st)) return 1;
+        if (launch_conv_t<128, 9, 2, false, EPI_LRELU_BN, 10, 1>(t, *tmA, t->df_tm[2], *tmO, p, r.st)) return 1;
     }
     if (bn_forward(r, 2, r.tbuf(TB_DZ2D), r.tbuf(TB_DA2), 1)) return 1;
     {  // model.8: 3x3 stride 2 128 -> 128 -> z3
@@ -694,7 +694,7 @@ static int d_forward(const TrainRun& r, const float* img) {
         p.out_f32 = static_cast<float*>(r.tbuf(TB_DZ3D));
         p.stats = t->dsc + DS_BN + 2 * 256;  // batch statistics reduced in the epilogue
         CID_CHECK_CUDA(cudaMemsetAsync(p.stats, 0, 256 * 8, r.st));
-        if (launch_conv_t<128, 16, 2, false, EPI_LRELU, 9, 1>(t, *tmA, t->df_tm[3], *tmO, p, r.st)) return 1;
+        if (launch_conv_t<128, 16, 2, false, EPI_LRELU_BN, 9, 1>(t, *tmA, t->df_tm[3], *tmO, p, r.st)) return 1;
     }
     if (bn_forward(r, 3, r.tbuf(TB_DZ3D), r.tbuf(TB_DA3), 2)) return 1;
     CID_CHECK_CUDA(cudaMemsetAsync(t->fsc + FS_POOLED, 0, static_cast<size_t>(B) * 128 * 4, r.st));

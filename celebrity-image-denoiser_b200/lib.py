@@ -9,7 +9,10 @@ from __future__ import annotations
 import ctypes as C
 from pathlib import Path
 
-_LIB_PATH = Path(__file__).resolve().parent / "csrc" / "libcid_b200.so"
+import os
+
+# CID_B200_LIB: another build of the same library (same-box A/B runs of two kernel versions, tools/gpu_session.sh)
+_LIB_PATH = Path(os.environ.get("CID_B200_LIB") or Path(__file__).resolve().parent / "csrc" / "libcid_b200.so")
 _lib = None
 
 ABI_VERSION = 7

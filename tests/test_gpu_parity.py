@@ -529,6 +529,29 @@ def test_salt_pepper_integer_product_edge_and_coords_validation(dev, golden_dir)
         cu_noiser.add_salt_pepper_noise(img, 0.02, 0.02, coords=coords[:, :-2])
 
 
+@pytest.mark.parametrize("B,H,W", [(3, 17, 23), (2, 100, 100), (1, 512, 512), (5, 301, 77), (2, 1024, 640)])
+def test_salt_pepper_one_pass_equals_scatter_form(dev, B, H, W):
+    """The one-pass slab kernel (image rows in shared memory, every CTA regenerating the image's Philox draw list) against
+    the copy + two-scatter-launch form: same counters, same order (salt, then pepper) -> identical bytes, both domains,
+    also for slabs that start at addresses that are not 16-byte aligned and for images that need several slabs."""
+    eng = cu_noiser._engine(dev)
+    g = torch.Generator(device=dev).manual_seed(B * 1000 + H)
+    img = torch.randint(0, 256, (B, H, W, 3), dtype=torch.uint8, device=dev, generator=g)
+    odd = torch.randint(0, 256, (B * H * W * 3 + 5,), dtype=torch.uint8, device=dev, generator=g)[5:].view(B, H, W, 3)
+    outs = {}
+    for scatter in (0, 1):
+        eng.set_option("sp_scatter", scatter)
+        try:
+            outs[scatter] = [cu_noiser.add_salt_pepper_noise(img, 0.02, 0.03, seed=11, offset=7).cpu(),
+                             cu_noiser.add_salt_pepper(img, amount=0.05, seed=12).cpu(),
+                             cu_noiser.add_salt_pepper_noise(odd, 0.02, 0.02, seed=13).cpu()]
+        finally:
+            eng.set_option("sp_scatter", 0)
+    for a, b in zip(outs[0], outs[1]):
+        assert torch.equal(a, b)
+    assert not torch.equal(outs[0][0], img.cpu())
+
+
 @pytest.mark.parametrize("name", ["unit_noise_24x40", "unit_noise_33x17"])
 def test_unit_domain_noiser_supplied_draws_bit_exact(dev, golden_dir, name):
     """The [0,1]-domain noiser (esrgan_addNoise.py:7-41) on the device with the reference's own draws: bit-exact."""

@@ -11,9 +11,18 @@ B = int(sys.argv[2]) if len(sys.argv) > 2 else 256
 S = int(sys.argv[3]) if len(sys.argv) > 3 else 128
 net = (ESRGANGenerator if model == "esrgan" else SRGANGenerator)()
 net.load_state_dict(so.init_state_dict(model, 0), strict=True)
-net = net.cuda().eval().set_option("profile", 1)
+net = net.cuda().eval()
 x = synthetic_noisy_u8(3, B, S, S).cuda()
 y = net.forward_u8(x)
+for _ in range(3):
+    net.forward_u8(x, out=y)
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+for _ in range(10):
+    net.forward_u8(x, out=y)
+e1.record(); torch.cuda.synchronize()
+print(model, B, S, "UNPROFILED ms/forward", e0.elapsed_time(e1) / 10, "img/s", B / (e0.elapsed_time(e1) / 10) * 1e3)
+net.set_option("profile", 1)
 for _ in range(3):
     net.forward_u8(x, out=y)
 net.profile_read()
