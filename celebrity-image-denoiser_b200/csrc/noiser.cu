@@ -11,6 +11,8 @@
 // numpy's MT19937 stream cannot be reproduced on the device, so each kernel has two modes:
 // "supplied" (the caller passes the reference's own noise / coordinates -> bit-exact parity) and
 // "philox" (Philox4x32-10 counter RNG, Box-Muller for normals -> statistical parity).
+#include <string.h>
+
 #include "cid_internal.h"
 #include "ptx.cuh"
 
@@ -377,11 +379,13 @@ __global__ void __launch_bounds__(256) impulse_kernel(uint8_t* __restrict__ out,
         col = cc[1];
     } else {
         const uint2 key = make_uint2(static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
-        const uint64_t ctr = offset + static_cast<uint64_t>(b) * stride + first + i;
+        // draw j = b * stride + first + i of the batch: Philox counter offset + j / 2, words (x, y) or (z, w)
+        const uint64_t j = static_cast<uint64_t>(b) * stride + first + i;
+        const uint64_t ctr = offset + (j >> 1);
         const uint4 r = philox4x32_10(make_uint4(static_cast<uint32_t>(ctr), static_cast<uint32_t>(ctr >> 32), 1u, 0u), key);
         // randint(0, dim-1): high is exclusive, so the last row / column is never hit
-        row = static_cast<int>(__umulhi(r.x, static_cast<uint32_t>(H - 1)));
-        col = static_cast<int>(__umulhi(r.y, static_cast<uint32_t>(W - 1)));
+        row = static_cast<int>(__umulhi((j & 1) ? r.z : r.x, static_cast<uint32_t>(H - 1)));
+        col = static_cast<int>(__umulhi((j & 1) ? r.w : r.y, static_cast<uint32_t>(W - 1)));
     }
     if (row < 0 || row >= H || col < 0 || col >= W) return;
     uint8_t* px = out + ((static_cast<size_t>(b) * H + row) * W + col) * C;
@@ -392,21 +396,27 @@ __global__ void __launch_bounds__(256) impulse_kernel(uint8_t* __restrict__ out,
 // Salt & pepper in ONE pass. The three-launch form above (copy, salt scatter, pepper scatter) moves the batch through HBM
 // once for the copy and then pays a read-modify-write of a 32-byte sector for every one of the millions of scattered
 // byte stores (ncu, 256 x 512^2: copy 59 us at 6.8 TB/s, each scatter 130 us with 92 MB read + 100 MB written).
-// Here a CTA owns a slab of `rows` image rows in shared memory: load (16-byte, coalesced) -> every thread walks the
-// image's draw list and applies the draws that land in the slab (salt first, barrier, then pepper: the reference's order,
-// noise_generation.py:17-21) -> store. Every CTA of an image regenerates the image's whole draw list (Philox is a pure
-// function of the counter), so the draws - and therefore the output - are bit-identical to the scatter kernels; the
-// price is `slabs` times the RNG work, which stays below the copy time for slabs of >= 64 KB.
+// Here a CTA owns a slab of `rows` image rows in shared memory: bulk load (cp.async.bulk, no thread touches the bytes)
+// -> every thread walks the image's draw list and applies the draws that land in the slab (salt first, barrier, then
+// pepper: the reference's order, noise_generation.py:17-21) -> bulk store. Every CTA of an image regenerates the image's
+// whole draw list (Philox is a pure function of the counter), so the output is bit-identical to the scatter kernels; the
+// price is `slabs` times the RNG work - with 31 k draws per 512^2 image that work, not the copy, sets the time, so the
+// slab is as large as shared memory allows (one 1024-thread CTA per SM) and one Philox call serves two draws.
+// Tried and dropped: the image in the distributed shared memory of an 8-CTA cluster with every draw computed once and
+// stored into its owner's slab (st.shared::cluster.u8): 94 k remote byte stores per image made it slower (1.11 vs
+// 0.94 ms for 1024 images).
 // UNIT = the [0,1]-domain variant (esrgan_addNoise.py:15-25): element coordinates (row, col, channel), full randint range.
 // ---------------------------------------------------------------------------------------------------------------------
 constexpr int kSpThreads = 1024;
+constexpr uint32_t kSpChunk = 32768;  // bytes per bulk copy
 
 template <bool UNIT>
 __global__ void __launch_bounds__(kSpThreads, 1) salt_pepper_slab_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out,
                                                                          int H, int W, int C, int rows, int slabs, int n_salt,
                                                                          int n_pepper, const int32_t* __restrict__ coords,
                                                                          uint64_t seed, uint64_t offset) {
-    extern __shared__ __align__(16) uint8_t sp_smem[];
+    extern __shared__ __align__(128) uint8_t sp_smem[];
+    __shared__ __align__(8) uint64_t sp_bar;
     const int b = blockIdx.x / slabs, sl = blockIdx.x - b * slabs;
     const int r0 = sl * rows, nr = min(rows, H - r0);
     const size_t row_bytes = static_cast<size_t>(W) * C;
@@ -415,58 +425,82 @@ __global__ void __launch_bounds__(kSpThreads, 1) salt_pepper_slab_kernel(const u
     const uint8_t* src = in + g0;
     uint8_t* dst = out + g0;
     const int tid = threadIdx.x;
-    // load: the slab keeps its misalignment (smem offset = global address mod 16) so that 16-byte chunks line up
+    // The slab keeps its misalignment (shared-memory offset = global address mod 16), so its 16-byte-aligned body moves
+    // with bulk async copies and only the <= 15-byte head / tail with ordinary loads and stores.
     const int mis = static_cast<int>(reinterpret_cast<uintptr_t>(src) & 15);
     const bool same_mis = (reinterpret_cast<uintptr_t>(dst) & 15) == static_cast<uintptr_t>(mis);
     uint8_t* slab = sp_smem + mis;
     const int head = mis ? min(16 - mis, nbytes) : 0;
-    const int body = (nbytes - head) / 16;
-    const int tail0 = head + body * 16;
+    const int body = (nbytes - head) & ~15;
+    const int tail0 = head + body;
+    if (tid == 0) {
+        mbar_init(&sp_bar, 1);
+        fence_mbar_init();
+        if (body > 0) {
+            mbar_arrive_expect_tx(&sp_bar, static_cast<uint32_t>(body));
+            for (int o = 0; o < body; o += kSpChunk)
+                bulk_load_1d(slab + head + o, src + head + o, min(static_cast<uint32_t>(body - o), kSpChunk), &sp_bar);
+        }
+    }
     for (int i = tid; i < head; i += kSpThreads) slab[i] = src[i];
-    for (int i = tid; i < body; i += kSpThreads)
-        *reinterpret_cast<uint4*>(slab + head + i * 16) = __ldg(reinterpret_cast<const uint4*>(src + head) + i);
     for (int i = tail0 + tid; i < nbytes; i += kSpThreads) slab[i] = src[i];
-    __syncthreads();
+    __syncthreads();  // barrier initialised, head / tail in place
+    if (body > 0) mbar_wait(&sp_bar, 0);
     const int stride = n_salt + n_pepper;
     const uint2 key = make_uint2(static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+    auto apply = [&](int row, int col, int ch, uint8_t value) {
+        if (row < r0 || row >= r0 + nr || col < 0 || col >= W) return;
+        uint8_t* px = slab + (static_cast<size_t>(row - r0) * W + col) * C;
+        if (UNIT) {
+            if (ch >= 0 && ch < C) px[ch] = value;
+        } else {
+            for (int c = 0; c < C; ++c) px[c] = value;
+        }
+    };
 #pragma unroll 1
     for (int pass = 0; pass < 2; ++pass) {
         const int first = pass ? n_salt : 0, count = pass ? n_pepper : n_salt;
         const uint8_t value = pass ? 0 : 255;
-        for (int i = tid; i < count; i += kSpThreads) {
-            int row, col, ch = 0;
-            if (coords) {
+        if (coords) {
+            for (int i = tid; i < count; i += kSpThreads) {
                 const int32_t* cc = coords + (static_cast<size_t>(b) * stride + first + i) * (UNIT ? 3 : 2);
-                row = __ldg(cc);
-                col = __ldg(cc + 1);
-                if (UNIT) ch = __ldg(cc + 2);
-            } else {
-                const uint64_t ctr = offset + static_cast<uint64_t>(b) * stride + first + i;
+                apply(__ldg(cc), __ldg(cc + 1), UNIT ? __ldg(cc + 2) : 0, value);
+            }
+        } else {
+            // draw j of the image (j = first + i) comes from Philox counter offset + (b * stride + j) / DPC, lane j % DPC
+            constexpr int DPC = UNIT ? 1 : 2;  // draws per Philox call
+            const uint64_t d0 = static_cast<uint64_t>(b) * stride + first;  // global index of the pass's first draw
+            const uint64_t c0 = d0 / DPC, c1 = (d0 + count + DPC - 1) / DPC;
+            for (uint64_t cidx = c0 + tid; cidx < c1; cidx += kSpThreads) {
+                const uint64_t ctr = offset + cidx;
                 const uint4 r = philox4x32_10(make_uint4(static_cast<uint32_t>(ctr), static_cast<uint32_t>(ctr >> 32), UNIT ? 7u : 1u, 0u), key);
                 if (UNIT) {
-                    row = static_cast<int>(__umulhi(r.x, static_cast<uint32_t>(H)));
-                    col = static_cast<int>(__umulhi(r.y, static_cast<uint32_t>(W)));
-                    ch = static_cast<int>(__umulhi(r.z, static_cast<uint32_t>(C)));
+                    apply(static_cast<int>(__umulhi(r.x, static_cast<uint32_t>(H))), static_cast<int>(__umulhi(r.y, static_cast<uint32_t>(W))),
+                          static_cast<int>(__umulhi(r.z, static_cast<uint32_t>(C))), value);
                 } else {  // randint(0, dim-1): high is exclusive, the last row / column is never hit
-                    row = static_cast<int>(__umulhi(r.x, static_cast<uint32_t>(H - 1)));
-                    col = static_cast<int>(__umulhi(r.y, static_cast<uint32_t>(W - 1)));
+                    const uint64_t j0 = cidx * 2;
+                    if (j0 >= d0 && j0 < d0 + count)
+                        apply(static_cast<int>(__umulhi(r.x, static_cast<uint32_t>(H - 1))),
+                              static_cast<int>(__umulhi(r.y, static_cast<uint32_t>(W - 1))), 0, value);
+                    if (j0 + 1 >= d0 && j0 + 1 < d0 + count)
+                        apply(static_cast<int>(__umulhi(r.z, static_cast<uint32_t>(H - 1))),
+                              static_cast<int>(__umulhi(r.w, static_cast<uint32_t>(W - 1))), 0, value);
                 }
-            }
-            if (row < r0 || row >= r0 + nr || col < 0 || col >= W) continue;
-            uint8_t* px = slab + (static_cast<size_t>(row - r0) * W + col) * C;
-            if (UNIT) {
-                if (ch >= 0 && ch < C) px[ch] = value;
-            } else {
-                for (int c = 0; c < C; ++c) px[c] = value;
             }
         }
         __syncthreads();
     }
     if (same_mis) {
+        fence_proxy_async();  // the byte stores above must be visible to the bulk-copy engine
+        __syncthreads();
+        if (tid == 0 && body > 0) {
+            for (int o = 0; o < body; o += kSpChunk)
+                bulk_store_1d(dst + head + o, slab + head + o, min(static_cast<uint32_t>(body - o), kSpChunk));
+            bulk_commit();
+        }
         for (int i = tid; i < head; i += kSpThreads) dst[i] = slab[i];
-        for (int i = tid; i < body; i += kSpThreads)
-            *(reinterpret_cast<uint4*>(dst + head) + i) = *reinterpret_cast<const uint4*>(slab + head + i * 16);
         for (int i = tail0 + tid; i < nbytes; i += kSpThreads) dst[i] = slab[i];
+        if (tid == 0 && body > 0) bulk_wait_read<0>();  // shared memory stays allocated until the engine has read it
     } else {
         for (int i = tid; i < nbytes; i += kSpThreads) dst[i] = slab[i];
     }
@@ -478,7 +512,7 @@ template <bool UNIT>
 static int launch_salt_pepper_slab(cid_ctx* h, const uint8_t* in, uint8_t* out, int B, int H, int W, int C, int n_salt,
                                    int n_pepper, const int32_t* coords, uint64_t seed, uint64_t offset, cudaStream_t st) {
     const size_t row_bytes = static_cast<size_t>(W) * C;
-    const size_t cap = static_cast<size_t>(h->max_smem) - 1024 - 16;
+    const size_t cap = static_cast<size_t>(h->max_smem) - 2048;
     if (row_bytes == 0 || row_bytes * 8 > cap) return -1;
     int slabs = static_cast<int>((static_cast<size_t>(H) * row_bytes + cap - 1) / cap);
     // small batches: more, smaller slabs so that the grid covers the SMs (the RNG work per image grows with `slabs`)
@@ -487,11 +521,11 @@ static int launch_salt_pepper_slab(cid_ctx* h, const uint8_t* in, uint8_t* out, 
         ++slabs;
     const int rows = (H + slabs - 1) / slabs;
     slabs = (H + rows - 1) / rows;
-    const size_t smem = static_cast<size_t>(rows) * row_bytes + 16;
+    const size_t smem = static_cast<size_t>(rows) * row_bytes + 32;
     const long long grid = static_cast<long long>(B) * slabs;
     if (grid >= (1ll << 31)) return -1;
     auto kern = salt_pepper_slab_kernel<UNIT>;
-    CID_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
+    CID_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem - 1024));  // (+ the static mbarrier)
     kern<<<static_cast<unsigned>(grid), kSpThreads, smem, st>>>(in, out, H, W, C, rows, slabs, n_salt, n_pepper, coords, seed, offset);
     CID_CHECK_CUDA(cudaGetLastError());
     h->launches++;

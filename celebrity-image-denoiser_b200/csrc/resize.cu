@@ -149,7 +149,17 @@ __global__ void __launch_bounds__(256) resample_u8_kernel(const uint8_t* __restr
 // u8 exactly as Pillow's intermediate image is) and the vertical pass from there to global memory with 4-byte stores.
 // The intermediate image never touches HBM and no thread does a 64-bit division. Same integer arithmetic as the
 // two-pass kernels above (which stay as the fallback for other channel counts / extreme scale factors): bit-identical.
-// Shared memory: [row offsets R ints][kH TX*ksH ints][kV TY*ksV ints][bH TX*2][bV TY*2][s_in R x pitch][s_mid R x TX*3]
+//
+// The kernel is bound by instruction issue, not by HBM: a 2x down-scale needs 9 + 9 taps per output byte and the input
+// is 4x the output, i.e. ~31 integer MACs per output byte = 6 MACs per byte of HBM traffic - at 6.5 TB/s that would be
+// 39 T MAC/s, more than the 36 T lane-instructions/s the whole GPU issues. So the work per MAC is what counts:
+//   * KS (compile-time tap count >= the table's ksize; taps past an output's own count have zero coefficients, so every
+//     output runs the same fully unrolled KS taps - reads past its window hit padding bytes times zero);
+//   * horizontal pass: one thread = one output pixel (3 channels). Its 3*KS input bytes are contiguous: KS*3/4+1 aligned
+//     32-bit shared loads, funnel-shifted to byte 0, then one PRMT + one IMAD per MAC; the coefficients come as 16-byte
+//     loads shared by the 3 channels;
+//   * vertical pass: one thread = 4 consecutive bytes of an output row: one 32-bit shared load per tap, PRMT + IMAD per MAC.
+// Shared memory: [row offsets R ints][kH TX*KS ints][kV TY*KS ints][bH TX][bV TY][s_in R x pitch][s_mid R x TX*3][slack]
 // ---------------------------------------------------------------------------------------------------------------------
 struct ResizeFusedParams {
     const uint8_t* in;
@@ -159,20 +169,26 @@ struct ResizeFusedParams {
     int ksH, ksV;
     int tiles_x, tiles_y;
     int max_rows;   // input rows a tile can need
-    int pitch;      // bytes per staged input row (multiple of 16, includes the alignment slack)
+    int pitch;      // bytes per staged input row (multiple of 16, includes the alignment slack and 3*KS bytes of padding)
 };
 
-template <int TX, int TY>
+__device__ __forceinline__ int byte_of(uint32_t w, int k) {  // byte k of w, zero-extended: one PRMT
+    return static_cast<int>(__byte_perm(w, 0u, 0x4440u + static_cast<uint32_t>(k)));
+}
+
+template <int TX, int TY, int KS>
 __global__ void __launch_bounds__(256) resize_fused_kernel(const ResizeFusedParams p) {
     constexpr int C = 3, ROWB = TX * C;  // bytes of one tile row of the output / intermediate
+    constexpr int KP = (KS + 3) & ~3;     // coefficient row pitch (ints): 16-byte loads
+    constexpr int NW = (C * KS + 3) / 4;  // normalised words that hold one output pixel's 3*KS input bytes
     static_assert(ROWB % 4 == 0, "4-byte stores");
     extern __shared__ __align__(16) uint8_t rs_smem[];
-    int* row_off = reinterpret_cast<int*>(rs_smem);
-    int* kH = row_off + p.max_rows;
-    int* kV = kH + TX * p.ksH;
-    int* bH = kV + TY * p.ksV;
-    int* bV = bH + TX * 2;
-    uint8_t* s_in = reinterpret_cast<uint8_t*>(bV + TY * 2);
+    int* kH = reinterpret_cast<int*>(rs_smem);
+    int* kV = kH + TX * KP;
+    int* row_off = kV + TY * KP;
+    int* bH = row_off + ((p.max_rows + 3) & ~3);
+    int* bV = bH + TX;
+    uint8_t* s_in = reinterpret_cast<uint8_t*>(bV + TY);
     s_in += (16 - (reinterpret_cast<uintptr_t>(s_in) & 15)) & 15;
     uint8_t* s_mid = s_in + static_cast<size_t>(p.max_rows) * p.pitch;
 
@@ -184,20 +200,27 @@ __global__ void __launch_bounds__(256) resize_fused_kernel(const ResizeFusedPara
     const int nx = min(TX, p.out_w - x0), ny = min(TY, p.out_h - y0);
     const int tid = threadIdx.x;
 
-    // coefficient tables and bounds of this tile's output columns / rows
-    for (int i = tid; i < TX * p.ksH; i += 256) kH[i] = (i / p.ksH) < nx ? __ldg(p.kkH + static_cast<size_t>(x0) * p.ksH + i) : 0;
-    for (int i = tid; i < TY * p.ksV; i += 256) kV[i] = (i / p.ksV) < ny ? __ldg(p.kkV + static_cast<size_t>(y0) * p.ksV + i) : 0;
-    for (int i = tid; i < TX * 2; i += 256) bH[i] = (i >> 1) < nx ? __ldg(p.boundsH + 2 * x0 + i) : 0;
-    for (int i = tid; i < TY * 2; i += 256) bV[i] = (i >> 1) < ny ? __ldg(p.boundsV + 2 * y0 + i) : 0;
     // input window: the bounds are monotone, so the first / last output column (row) of the tile give the range
     const int xlo = __ldg(p.boundsH + 2 * x0);
     const int xhi = __ldg(p.boundsH + 2 * (x0 + nx - 1)) + __ldg(p.boundsH + 2 * (x0 + nx - 1) + 1);
     const int ylo = __ldg(p.boundsV + 2 * y0);
     const int yhi = __ldg(p.boundsV + 2 * (y0 + ny - 1)) + __ldg(p.boundsV + 2 * (y0 + ny - 1) + 1);
     const int rows = yhi - ylo, row_bytes = (xhi - xlo) * C;
+    // coefficient tables (zero beyond the table's own ksize and beyond the tile) and window-relative first taps
+    for (int i = tid; i < TX * KP; i += 256) {
+        const int xx = i / KP, t = i - xx * KP;
+        kH[i] = (xx < nx && t < p.ksH) ? __ldg(p.kkH + static_cast<size_t>(x0 + xx) * p.ksH + t) : 0;
+    }
+    for (int i = tid; i < TY * KP; i += 256) {
+        const int yy = i / KP, t = i - yy * KP;
+        kV[i] = (yy < ny && t < p.ksV) ? __ldg(p.kkV + static_cast<size_t>(y0 + yy) * p.ksV + t) : 0;
+    }
+    for (int i = tid; i < TX; i += 256) bH[i] = i < nx ? __ldg(p.boundsH + 2 * (x0 + i)) - xlo : 0;
+    for (int i = tid; i < TY; i += 256) bV[i] = i < ny ? __ldg(p.boundsV + 2 * (y0 + i)) - ylo : 0;
     // stage the window: per row, the 16-byte chunks that cover [start, start + row_bytes); the row keeps its misalignment
     const size_t img_end = static_cast<size_t>(p.B) * p.in_h * p.in_w * C;
     const int chunks = (row_bytes + 15 + 15) / 16;  // upper bound incl. the misalignment
+    const bool aligned_base = (reinterpret_cast<uintptr_t>(p.in) & 15) == 0;
     for (int i = tid; i < rows * chunks; i += 256) {
         const int r = i / chunks, ck = i - r * chunks;
         const size_t start = ((static_cast<size_t>(b) * p.in_h + ylo + r) * p.in_w + xlo) * C;
@@ -206,7 +229,7 @@ __global__ void __launch_bounds__(256) resize_fused_kernel(const ResizeFusedPara
         if (ck == 0) row_off[r] = static_cast<int>(start - a0);
         if (a < start + row_bytes) {
             uint4 v;
-            if (a + 16 <= img_end && (reinterpret_cast<uintptr_t>(p.in) & 15) == 0) {
+            if (a + 16 <= img_end && aligned_base) {
                 v = __ldg(reinterpret_cast<const uint4*>(p.in + a));
             } else {  // the tensor's tail (or an unaligned base pointer): byte loads
                 uint8_t t[16];
@@ -217,39 +240,62 @@ __global__ void __launch_bounds__(256) resize_fused_kernel(const ResizeFusedPara
         }
     }
     __syncthreads();
-    // horizontal pass: 4 consecutive bytes (x, c) of one staged row per thread-iteration
-    for (int i = tid; i < rows * (ROWB / 4); i += 256) {
-        const int r = i / (ROWB / 4), j4 = (i - r * (ROWB / 4)) * 4;
-        const uint8_t* row = s_in + static_cast<size_t>(r) * p.pitch + row_off[r];
-        uint32_t packed = 0;
+    // horizontal pass: one output pixel (3 channels) of one staged row per thread-iteration
+    for (int i = tid; i < rows * TX; i += 256) {
+        const int r = i / TX, xx = i - r * TX;
+        const uint32_t addr = static_cast<uint32_t>(r) * p.pitch + row_off[r] + bH[xx] * C;  // byte offset into s_in
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(s_in + (addr & ~3u));
+        const uint32_t sh = (addr & 3u) * 8u;
+        uint32_t w[NW + 1];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            const int j = j4 + e, xx = j / C, c = j - xx * C;
-            const int lo = bH[2 * xx] - xlo, cnt = bH[2 * xx + 1];
-            const int* k = kH + xx * p.ksH;
-            const uint8_t* src = row + lo * C + c;
-            int ss = 1 << (kPrecisionBits - 1);
-            for (int t = 0; t < cnt; ++t) ss += static_cast<int>(src[t * C]) * k[t];
-            packed |= static_cast<uint32_t>(clip8(ss)) << (8 * e);
+        for (int j = 0; j <= NW; ++j) w[j] = wp[j];
+#pragma unroll
+        for (int j = 0; j < NW; ++j) w[j] = __funnelshift_r(w[j], w[j + 1], sh);
+        const int4* k4 = reinterpret_cast<const int4*>(kH + xx * KP);
+        int s0 = 1 << (kPrecisionBits - 1), s1 = s0, s2 = s0;
+#pragma unroll
+        for (int q = 0; q < KP / 4; ++q) {
+            const int4 kk = k4[q];
+            const int kq[4] = {kk.x, kk.y, kk.z, kk.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int t = q * 4 + e;
+                if (t < KS) {
+                    s0 += byte_of(w[(3 * t) >> 2], (3 * t) & 3) * kq[e];
+                    s1 += byte_of(w[(3 * t + 1) >> 2], (3 * t + 1) & 3) * kq[e];
+                    s2 += byte_of(w[(3 * t + 2) >> 2], (3 * t + 2) & 3) * kq[e];
+                }
+            }
         }
-        *reinterpret_cast<uint32_t*>(s_mid + r * ROWB + j4) = packed;
+        uint8_t* m = s_mid + r * ROWB + xx * C;
+        m[0] = clip8(s0);
+        m[1] = clip8(s1);
+        m[2] = clip8(s2);
     }
     __syncthreads();
-    // vertical pass
+    // vertical pass: 4 consecutive bytes of one output row per thread-iteration
     const bool wide = (p.out_w * C) % 4 == 0 && (reinterpret_cast<uintptr_t>(p.out) & 3) == 0;
     for (int i = tid; i < ny * (ROWB / 4); i += 256) {
         const int yy = i / (ROWB / 4), j4 = (i - yy * (ROWB / 4)) * 4;
         if (j4 >= nx * C) continue;
-        const int lo = bV[2 * yy] - ylo, cnt = bV[2 * yy + 1];
-        const int* k = kV + yy * p.ksV;
+        const uint8_t* col = s_mid + bV[yy] * ROWB + j4;
+        const int4* k4 = reinterpret_cast<const int4*>(kV + yy * KP);
         int s0 = 1 << (kPrecisionBits - 1), s1 = s0, s2 = s0, s3 = s0;
-        for (int t = 0; t < cnt; ++t) {
-            const uint32_t v = *reinterpret_cast<const uint32_t*>(s_mid + (lo + t) * ROWB + j4);
-            const int kt = k[t];
-            s0 += static_cast<int>(v & 0xffu) * kt;
-            s1 += static_cast<int>((v >> 8) & 0xffu) * kt;
-            s2 += static_cast<int>((v >> 16) & 0xffu) * kt;
-            s3 += static_cast<int>(v >> 24) * kt;
+#pragma unroll
+        for (int q = 0; q < KP / 4; ++q) {
+            const int4 kk = k4[q];
+            const int kq[4] = {kk.x, kk.y, kk.z, kk.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int t = q * 4 + e;
+                if (t < KS) {
+                    const uint32_t v = *reinterpret_cast<const uint32_t*>(col + t * ROWB);
+                    s0 += byte_of(v, 0) * kq[e];
+                    s1 += byte_of(v, 1) * kq[e];
+                    s2 += byte_of(v, 2) * kq[e];
+                    s3 += byte_of(v, 3) * kq[e];
+                }
+            }
         }
         uint8_t* dst = p.out + ((static_cast<size_t>(b) * p.out_h + y0 + yy) * p.out_w + x0) * C + j4;
         const uint32_t o = static_cast<uint32_t>(clip8(s0)) | (static_cast<uint32_t>(clip8(s1)) << 8) |
@@ -316,22 +362,27 @@ int cid_resize_bicubic_u8(cid_handle h, const uint8_t* in, uint8_t* out, uint8_t
     ResizeCoeffs *ch = nullptr, *cv = nullptr;
     if (get_coeffs(h, in_w, out_w, &ch)) return 1;
     if (get_coeffs(h, in_h, out_h, &cv)) return 1;
-    if (C == 3) {
-        // fused two-pass kernel: the largest tile whose input window fits in shared memory
-        const int tiles[3][2] = {{64, 16}, {32, 8}, {16, 4}};
+    if (C == 3 && std::max(ch->ksize, cv->ksize) <= 17) {
+        // fused two-pass kernel: the largest tile whose input window fits in shared memory (two blocks per SM at least);
+        // KS = the compile-time tap count that covers both tables
+        const int ks = std::max(ch->ksize, cv->ksize);
+        const int KS = ks <= 5 ? 5 : ks <= 9 ? 9 : 17;
+        const int tiles[3][2] = {{64, 32}, {64, 16}, {32, 8}};
         for (int ti = 0; ti < 3; ++ti) {
             const int TX = tiles[ti][0], TY = tiles[ti][1];
-            const int max_cols = std::min(in_w, ch->max_span(TX)), max_rows = std::min(in_h, cv->max_span(TY));
+            const int KP = (KS + 3) & ~3;
+            const int max_cols = std::min(in_w, ch->max_span(TX)), max_rows = std::min(in_h, cv->max_span(TY)) ;
             ResizeFusedParams p;
             p.in = in; p.out = out; p.B = B; p.in_h = in_h; p.in_w = in_w; p.out_h = out_h; p.out_w = out_w;
             p.boundsH = ch->bounds; p.kkH = ch->kk; p.boundsV = cv->bounds; p.kkV = cv->kk;
             p.ksH = ch->ksize; p.ksV = cv->ksize;
             p.tiles_x = (out_w + TX - 1) / TX; p.tiles_y = (out_h + TY - 1) / TY;
-            p.max_rows = max_rows;
-            p.pitch = (max_cols * 3 + 15 + 15) / 16 * 16 + 16;
-            const size_t smem = static_cast<size_t>(max_rows) * 4 + static_cast<size_t>(TX) * p.ksH * 4 + static_cast<size_t>(TY) * p.ksV * 4 +
-                                (TX + TY) * 8 + 16 + static_cast<size_t>(max_rows) * p.pitch + static_cast<size_t>(max_rows) * TX * 3;
-            if (smem > 100 * 1024) continue;  // two blocks per SM at least
+            // the vertical pass reads KS rows from an output's first row: rows past the window are padding (zero taps)
+            p.max_rows = max_rows + KS;
+            p.pitch = (max_cols * 3 + 15 + 15 + 3 * KS + 8) / 16 * 16 + 16;
+            const size_t smem = static_cast<size_t>(TX + TY) * KP * 4 + static_cast<size_t>((p.max_rows + 3) & ~3) * 4 + (TX + TY) * 4 + 16 +
+                                static_cast<size_t>(p.max_rows) * p.pitch + static_cast<size_t>(p.max_rows) * TX * 3 + 64;
+            if (smem > 100 * 1024) continue;
             const long long nblocks = static_cast<long long>(B) * p.tiles_x * p.tiles_y;
             CID_REQUIRE(nblocks < (1ll << 31), "resize: too many tiles");
             auto launch = [&](auto kern) -> int {
@@ -340,7 +391,10 @@ int cid_resize_bicubic_u8(cid_handle h, const uint8_t* in, uint8_t* out, uint8_t
                 CID_CHECK_CUDA(cudaGetLastError());
                 return 0;
             };
-            const int rc = ti == 0 ? launch(resize_fused_kernel<64, 16>) : ti == 1 ? launch(resize_fused_kernel<32, 8>) : launch(resize_fused_kernel<16, 4>);
+            int rc;
+            if (ti == 0) rc = KS == 5 ? launch(resize_fused_kernel<64, 32, 5>) : KS == 9 ? launch(resize_fused_kernel<64, 32, 9>) : launch(resize_fused_kernel<64, 32, 17>);
+            else if (ti == 1) rc = KS == 5 ? launch(resize_fused_kernel<64, 16, 5>) : KS == 9 ? launch(resize_fused_kernel<64, 16, 9>) : launch(resize_fused_kernel<64, 16, 17>);
+            else rc = KS == 5 ? launch(resize_fused_kernel<32, 8, 5>) : KS == 9 ? launch(resize_fused_kernel<32, 8, 9>) : launch(resize_fused_kernel<32, 8, 17>);
             if (rc) return 1;
             h->launches++;
             return 0;

@@ -671,6 +671,19 @@ def test_resize_vs_oracle_256(dev):
         assert np.array_equal(out[b], orc.resize_bicubic_u8(img[b].numpy(), (256, 256)))
 
 
+@pytest.mark.parametrize("ih,iw,oh,ow", [(512, 512, 256, 256), (128, 160, 256, 320), (97, 131, 97, 131), (301, 257, 90, 77),
+                                         (640, 480, 128, 96), (70, 900, 64, 64), (33, 47, 129, 64), (5, 7, 3, 2)])
+def test_resize_tap_classes_vs_oracle(dev, ih, iw, oh, ow):
+    """Every tap-count class of the fused resampler (5 taps: up-scale / identity; 9: <= 2x down; 17: <= 4x down; wider
+    kernels and mixed up/down scaling fall to the two-launch form), tiles that overhang the image, misaligned rows:
+    bit-identical to the Pillow restatement, which the Pillow goldens pin (test_oracle_golden.py)."""
+    img = synthetic_noisy_u8(ih * 7 + ow, 2, ih, iw)
+    out = cu_noiser.resize_bicubic(img.to(dev), (ow, oh)).cpu().numpy()
+    assert out.shape == (2, oh, ow, 3)
+    for b in range(2):
+        assert np.array_equal(out[b], orc.resize_bicubic_u8(img[b].numpy(), (ow, oh)))
+
+
 def test_normalize_bit_exact(dev):
     img = synthetic_noisy_u8(2, 3, 20, 28)
     out = cu_noiser.normalize_to_tensor(img.to(dev)).cpu()
