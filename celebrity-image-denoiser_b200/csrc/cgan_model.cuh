@@ -155,6 +155,8 @@ static int cgan_pack(cid_ctx* c) {
         CID_CHECK_CUDA(cudaMalloc(reinterpret_cast<void**>(&c->bias_dev[l]), bias.size() * 4));
         CID_CHECK_CUDA(cudaMemcpy(c->bias_dev[l], bias.data(), bias.size() * 4, cudaMemcpyHostToDevice));
         if (l > 0 && make_weight_map(&c->tmW[l], c->w_dev[l], rows, row_len, box_rows)) return 1;
+        // CTA-pair form (each CTA of a pair loads half of every weight tile)
+        if (l > 0 && box_rows % 2 == 0 && make_weight_map(&c->tmWh[l], c->w_dev[l], rows, row_len, box_rows / 2)) return 1;
     }
     return 0;
 }
@@ -244,14 +246,22 @@ static int cgan_run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, c
         ConvParams p = base(2, 2);
         p.n_tiles = 2;
         p.out = buf(CB_C2); p.out_cs = 128; p.out_c0 = 0;
-        if (launch_conv<128, 8, 1, false, EPI_T4, 10, 1>(c, 21, pl->tmA[2], c->tmW[2], pl->tmO[2], pl->tmO[2], p, st)) return 1;
+        if (c->cgan_pair & 1) {
+            if (launch_conv<128, 8, 1, false, EPI_T4, 10, 1, 2>(c, 21, pl->tmA[2], c->tmWh[2], pl->tmO[2], pl->tmO[2], p, st)) return 1;
+        } else {
+            if (launch_conv<128, 8, 1, false, EPI_T4, 10, 1>(c, 21, pl->tmA[2], c->tmW[2], pl->tmO[2], pl->tmO[2], p, st)) return 1;
+        }
     }
     if (prof_mark(c, st)) return 1;
     {  // G3: transposed 4x4 s2 128 -> 64
         ConvParams p = base(3, 1);
         p.n_tiles = 2;
         p.out = buf(CB_C3); p.out_cs = 64; p.out_c0 = 0;
-        if (launch_conv<64, 8, 2, false, EPI_T4, 10, 1>(c, 22, pl->tmA[3], c->tmW[3], pl->tmO[3], pl->tmO[3], p, st)) return 1;
+        if (c->cgan_pair & 2) {
+            if (launch_conv<64, 8, 2, false, EPI_T4, 10, 1, 2>(c, 22, pl->tmA[3], c->tmWh[3], pl->tmO[3], pl->tmO[3], p, st)) return 1;
+        } else {
+            if (launch_conv<64, 8, 2, false, EPI_T4, 10, 1>(c, 22, pl->tmA[3], c->tmW[3], pl->tmO[3], pl->tmO[3], p, st)) return 1;
+        }
     }
     if (prof_mark(c, st)) return 1;
     {  // G4: 3x3 conv 64 -> 3 + tanh

@@ -952,6 +952,10 @@ int cid_set_option(cid_handle h, const char* name, int64_t value) {
         for (auto& pl : h->plans) { graph_release(pl.graph[0]); graph_release(pl.graph[1]); }
         return 0;
     }
+    if (!strcmp(name, "cgan_pair")) {
+        h->cgan_pair = static_cast<int>(value);
+        return 0;
+    }
     if (!strcmp(name, "sp_scatter")) {  // salt & pepper noiser: 1 = copy + scatter launches instead of the one-pass slab kernel
         h->sp_scatter = value != 0;
         return 0;

@@ -102,6 +102,8 @@ struct cid_ctx {
     uint32_t attr_done = 0;           // bit per kernel instantiation: max-dynamic-smem attribute set
     std::map<uint64_t, void*> resize_coeffs;  // (in_size,out_size) -> device coefficient block
     int regime = 0;                   // "regime" option: 0 per-layer choice, 1 batch-256 configuration, 2 N-split form
+    int cgan_pair = 2;                // "cgan_pair" option: bit 0 = conv2d_transpose, bit 1 = conv2d_transpose_1 as CTA pairs (bit-identical;
+                                      // measured at batch 256 @256^2: transpose_1 1.48 -> 1.28 ms as a pair, transpose unchanged)
     bool sp_scatter = false;          // "sp_scatter" option: salt & pepper as copy + two scatter launches (the fallback form)
     bool up2_stream = false;          // "up2_stream" option: stream up2's weights instead of keeping a column block resident
     bool use_graph = true;            // "graph" option: CUDA-graph replay of launch-bound passes
