@@ -386,21 +386,46 @@ static void launch_k(bool pdl, void (*kern)(KArgs...), dim3 grid, dim3 block, si
     (void)cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
 }
 
+// Shared-memory split of a streamed-weight kernel between the A ring (halo patches) and the weight ring: the A ring covers
+// ~4500 tensor cycles of K blocks (at least two), the weight ring gets the rest (at most kMaxWStages, at least 4 if the
+// A ring can give way).
+template <class Cfg, int N, int S>
+static void stage_split(int budget, int* a_stages, int* w_stages) {
+    const int kb_cycles = Cfg::STEPS * S * 4 * (N / 2);  // tensor cycles one K block's patches last
+    const int kb_in_flight = std::max(2, (4500 + kb_cycles - 1) / kb_cycles + 1);
+    int a = std::min(kMaxStages, std::max(S + 1, S * kb_in_flight));
+    auto w_for = [&](int aa) { return std::min(kMaxWStages, (budget - aa * Cfg::A_BYTES) / Cfg::W_BYTES); };
+    while (a > S + 1 && w_for(a) < 4) --a;
+    *a_stages = a;
+    *w_stages = std::max(2, w_for(a));
+}
+
 // deep_w: small-batch form - a CTA runs one or two work items, so a few A stages suffice and the rest of the shared
 // memory becomes weight stages: the kernel is then bound by weight-tile latency x tiles in flight (ncu, batch 1: a K = 2304
 // item took 13.8 us for 2.3 us of MMAs with 4 stages of 8 KB in flight).
 template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0, int TS = 0, int CG = 1>
 static int launch_conv(cid_ctx* c, int slot, const CUtensorMap& tmA, const CUtensorMap& tmW, const CUtensorMap& tmO,
-                       const CUtensorMap& tmO2, ConvParams p, cudaStream_t st, bool deep_w = false) {
+                       const CUtensorMap& tmO2, ConvParams p, cudaStream_t st, bool deep_w = false, int w_req = 0) {
     using Cfg = ConvCfg<N, TAPS, S, WRES, EPI, PW, TS, CG>;
     const int budget = c->max_smem - 1024 - 1024 - Cfg::O_BYTES;
-    // (transposed conv as a CTA pair: half-size weight stages, so twice as many fit - the layer is bound by weight-tile
-    // latency x stages in flight, not by bytes)
-    int w_stages = WRES ? 1 : (N == 256 && TS ? (CG == 2 && TAPS == 1 ? 6 : 3) : 4);
+    // Streamed weights: a weight tile lasts S * 4 MMAs (256-1024 tensor cycles) while a halo patch lasts STEPS times as
+    // long, and the MMA warp was found waiting on WEIGHT tiles (L2 latency x tiles in flight: every CTA streams the same
+    // tiles at the same time). So the A ring gets two K blocks' worth of patches (2 * S) and the weight ring the rest of
+    // the shared memory. Sweep at batch 256 (tools/wst_sweep.sh, profiles/r02j_wst_sweep.txt): upconv2.2 0.239 ms at 4
+    // weight stages, 0.216 at 8, 0.205 at 12; bottleneck.2 0.222 / 0.213 at 4 / 8; down2.2 0.261 / 0.230 at 4 / 10 -
+    // and a cliff as soon as the A ring drops to S + 1.
     int a_cap = kMaxStages;
-    if (deep_w && !WRES) {
-        a_cap = std::min(kMaxStages, std::max(S + 1, std::min(p.kb_count + 1, 5)));
-        w_stages = std::max(w_stages, std::min(kMaxWStages, (budget - a_cap * Cfg::A_BYTES) / Cfg::W_BYTES));
+    int w_stages = 1;
+    if (!WRES) {
+        stage_split<Cfg, N, S>(budget, &a_cap, &w_stages);
+        if (deep_w) {
+            a_cap = std::min(kMaxStages, std::max(S + 1, std::min(p.kb_count + 1, 5)));
+            w_stages = std::max(2, std::min(kMaxWStages, (budget - a_cap * Cfg::A_BYTES) / Cfg::W_BYTES));
+        }
+        if (w_req > 0) {
+            w_stages = w_req;
+            a_cap = kMaxStages;
+        }
     }
     const int w_bytes = (WRES ? p.kb_count * TAPS : w_stages) * Cfg::W_BYTES;
     int a_stages = std::min(a_cap, (budget - w_bytes) / Cfg::A_BYTES);
@@ -570,7 +595,7 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         if (pick_split(c, tiles(1), 128, 2, 2)) {
             if (split_pool(3, p)) return 1;
         } else {
-            if (launch_conv<128, 9, 2, false, EPI_RELU_POOL, 10, 1, 2>(c, 12, pl->tmA[3], c->tmWh[3], pl->tmO[3], pl->tmO2[3], p, st)) return 1;
+            if (launch_conv<128, 9, 2, false, EPI_RELU_POOL, 10, 1, 2>(c, 12, pl->tmA[3], c->tmWh[3], pl->tmO[3], pl->tmO2[3], p, st, false, c->wst[3])) return 1;
         }
     }
     if (prof_mark(c, st)) return 1;
@@ -579,6 +604,8 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         p.out = buf(l == 4 ? B_B0 : B_B1); p.out_cs = 256; p.out_c0 = 0;
         if (pick_split(c, tiles(2), 256, 1, 1)) {
             if (split_relu(l, p)) return 1;
+        } else if (c->bott_pair) {  // CTA pair: each CTA streams half of every 32 KB weight tile
+            if (launch_conv<256, 9, 1, false, EPI_RELU, 10, 1, 2>(c, 3, pl->tmA[l], c->tmWh[l], pl->tmO[l], pl->tmO[l], p, st, false, c->wst[l])) return 1;
         } else {
             if (launch_conv<256, 9, 1, false, EPI_RELU, 10, 1>(c, 3, pl->tmA[l], c->tmW[l], pl->tmO[l], pl->tmO[l], p, st)) return 1;
         }
@@ -603,7 +630,7 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         if (pick_split(c, tiles(1), 128, 2, 2)) {
             if (split_relu(l, p)) return 1;
         } else {
-            if (launch_conv<128, 9, 2, false, EPI_RELU, 10, 1, 2>(c, 14, pl->tmA[l], c->tmWh[l], pl->tmO[l], pl->tmO[l], p, st)) return 1;
+            if (launch_conv<128, 9, 2, false, EPI_RELU, 10, 1, 2>(c, 14, pl->tmA[l], c->tmWh[l], pl->tmO[l], pl->tmO[l], p, st, false, c->wst[l])) return 1;
         }
         if (prof_mark(c, st)) return 1;
     }
@@ -950,6 +977,16 @@ int cid_set_option(cid_handle h, const char* name, int64_t value) {
         CID_REQUIRE(value >= 0 && value <= 2, "regime must be 0 (auto), 1 (large) or 2 (split)");
         h->regime = static_cast<int>(value);
         for (auto& pl : h->plans) { graph_release(pl.graph[0]); graph_release(pl.graph[1]); }
+        return 0;
+    }
+    if (!strncmp(name, "wst", 3) && name[3] >= '0' && name[3] <= '9') {  // "wst7" = weight-ring depth of layer 7 (tuning)
+        const int l = atoi(name + 3);
+        CID_REQUIRE(l >= 0 && l < 16 && value >= 0 && value <= kMaxWStages, "wst<layer>: layer 0..15, depth 0..%d", kMaxWStages);
+        h->wst[l] = static_cast<int>(value);
+        return 0;
+    }
+    if (!strcmp(name, "bott_pair")) {
+        h->bott_pair = value != 0;
         return 0;
     }
     if (!strcmp(name, "cgan_pair")) {

@@ -104,6 +104,10 @@ struct cid_ctx {
     int regime = 0;                   // "regime" option: 0 per-layer choice, 1 batch-256 configuration, 2 N-split form
     int cgan_pair = 2;                // "cgan_pair" option: bit 0 = conv2d_transpose, bit 1 = conv2d_transpose_1 as CTA pairs (bit-identical;
                                       // measured at batch 256 @256^2: transpose_1 1.48 -> 1.28 ms as a pair, transpose unchanged)
+    bool bott_pair = true;            // "bott_pair" option: the two bottleneck layers as CTA pairs (each CTA streams half of every 32 KB
+                                      // weight tile: bottleneck.2 0.239 -> 0.210 ms = 1475 TFLOP/s, bit-identical)
+    int wst[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // "wst<l>" options: weight-ring depth of the streamed-weight
+                                      // layers in their batch-256 form (0 = launch_conv's default), see run_layers
     bool sp_scatter = false;          // "sp_scatter" option: salt & pepper as copy + two scatter launches (the fallback form)
     bool up2_stream = false;          // "up2_stream" option: stream up2's weights instead of keeping a column block resident
     bool use_graph = true;            // "graph" option: CUDA-graph replay of launch-bound passes

@@ -214,9 +214,10 @@ static int launch_conv_t(cid_train* t, const CUtensorMap& tmA, const CUtensorMap
     using Cfg = ConvCfg<N, TAPS, S, WRES, EPI, PW, TS, CG>;
     cid_ctx* c = t->g;
     const int budget = c->max_smem - 1024 - 1024 - Cfg::O_BYTES;
-    int w_stages = WRES ? 1 : (N == 256 && TS ? 3 : 4);
+    int w_stages = 1, a_cap = kMaxStages;
+    if (!WRES) stage_split<Cfg, N, S>(budget, &a_cap, &w_stages);  // (cid_api.cu: deep weight ring, A ring of ~2 K blocks)
     const int w_bytes = (WRES ? p.kb_count * TAPS : w_stages) * Cfg::W_BYTES;
-    int a_stages = std::min(kMaxStages, (budget - w_bytes) / Cfg::A_BYTES);
+    int a_stages = std::min(a_cap, (budget - w_bytes) / Cfg::A_BYTES);
     CID_REQUIRE(a_stages >= S + 1, "train conv<%d,%d,%d>: shared memory too small (%d stages)", N, TAPS, S, a_stages);
     p.a_stages = a_stages;
     p.w_stages = w_stages;
