@@ -405,7 +405,7 @@ static void stage_split(int budget, int* a_stages, int* w_stages) {
 // item took 13.8 us for 2.3 us of MMAs with 4 stages of 8 KB in flight).
 template <int N, int TAPS, int S, bool WRES, int EPI, int PW = 0, int TS = 0, int CG = 1>
 static int launch_conv(cid_ctx* c, int slot, const CUtensorMap& tmA, const CUtensorMap& tmW, const CUtensorMap& tmO,
-                       const CUtensorMap& tmO2, ConvParams p, cudaStream_t st, bool deep_w = false, int w_req = 0) {
+                       const CUtensorMap& tmO2, ConvParams p, cudaStream_t st, bool deep_w = false, int w_req = 0, int a_req = 0) {
     using Cfg = ConvCfg<N, TAPS, S, WRES, EPI, PW, TS, CG>;
     const int budget = c->max_smem - 1024 - 1024 - Cfg::O_BYTES;
     // Streamed weights: a weight tile lasts S * 4 MMAs (256-1024 tensor cycles) while a halo patch lasts STEPS times as
@@ -429,6 +429,7 @@ static int launch_conv(cid_ctx* c, int slot, const CUtensorMap& tmA, const CUten
     }
     const int w_bytes = (WRES ? p.kb_count * TAPS : w_stages) * Cfg::W_BYTES;
     int a_stages = std::min(a_cap, (budget - w_bytes) / Cfg::A_BYTES);
+    if (a_req > 0) a_stages = std::min(a_stages, std::max(a_req, S + 1));
     CID_REQUIRE(a_stages >= S + 1, "conv<%d,%d,%d>: shared memory too small (%d stages)", N, TAPS, S, a_stages);
     p.a_stages = a_stages;
     p.w_stages = w_stages;
@@ -574,7 +575,7 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         if (pick_split(c, tiles(0), 64, 2, 2)) {  // one tile per CTA, weights resident
             if (launch_conv<64, 9, 1, true, EPI_RELU_POOL, 10, 1>(c, 24, pl->tmA[1], c->tmW[1], pl->tmO[1], pl->tmO2[1], p, st)) return 1;
         } else {
-            if (launch_conv<64, 9, 2, true, EPI_RELU_POOL, 10, 1, 2>(c, 10, pl->tmA[1], c->tmWh[1], pl->tmO[1], pl->tmO2[1], p, st)) return 1;
+            if (launch_conv<64, 9, 2, true, EPI_RELU_POOL, 10, 1, 2>(c, 10, pl->tmA[1], c->tmWh[1], pl->tmO[1], pl->tmO2[1], p, st, false, 0, c->ast[1])) return 1;
         }
     }
     if (prof_mark(c, st)) return 1;
@@ -584,7 +585,7 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         if (pick_split(c, tiles(1), 128, 1, 2)) {
             if (split_relu(2, p)) return 1;
         } else {  // CTA pair: the resident weights (147 KB) only fit next to the staging buffers when halved
-            if (launch_conv<128, 9, 1, true, EPI_RELU, 10, 1, 2>(c, 11, pl->tmA[2], c->tmWh[2], pl->tmO[2], pl->tmO[2], p, st)) return 1;
+            if (launch_conv<128, 9, 1, true, EPI_RELU, 10, 1, 2>(c, 11, pl->tmA[2], c->tmWh[2], pl->tmO[2], pl->tmO[2], p, st, false, 0, c->ast[2])) return 1;
         }
     }
     if (prof_mark(c, st)) return 1;
@@ -620,7 +621,7 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         if (c->up2_stream) {
             if (launch_conv<256, 1, 1, false, EPI_CONVT, 0, 1, 2>(c, 20, pl->tmA[6], c->tmWh[6], pl->tmO[6], pl->tmO[6], p, st)) return 1;
         } else {
-            if (launch_conv<256, 1, 1, true, EPI_CONVT, 0, 1, 2>(c, 20, pl->tmA[6], c->tmWh[6], pl->tmO[6], pl->tmO[6], p, st)) return 1;
+            if (launch_conv<256, 1, 1, true, EPI_CONVT, 0, 1, 2>(c, 20, pl->tmA[6], c->tmWh[6], pl->tmO[6], pl->tmO[6], p, st, false, 0, c->ast[6])) return 1;
         }
     }
     if (prof_mark(c, st)) return 1;
@@ -638,13 +639,17 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         ConvParams p = base(9, 1);
         p.n_tiles = 1;  // 4*64 columns in one tile of 256
         p.out = buf(B_CAT1); p.out_cs = 128; p.out_c0 = 0;
-        if (launch_conv<256, 1, 1, true, EPI_CONVT, 0, 1>(c, 21, pl->tmA[9], c->tmW[9], pl->tmO[9], pl->tmO[9], p, st)) return 1;
+        if (c->up1_pair) {
+            if (launch_conv<256, 1, 1, true, EPI_CONVT, 0, 1, 2>(c, 21, pl->tmA[9], c->tmWh[9], pl->tmO[9], pl->tmO[9], p, st, false, 0, c->ast[9])) return 1;
+        } else {
+            if (launch_conv<256, 1, 1, true, EPI_CONVT, 0, 1>(c, 21, pl->tmA[9], c->tmW[9], pl->tmO[9], pl->tmO[9], p, st, false, 0, c->ast[9])) return 1;
+        }
     }
     if (prof_mark(c, st)) return 1;
     {  // L10 upconv1.0 (reads cat1) -> u1a; CTA pair (resident weights halved: 74 KB per CTA)
         ConvParams p = base(10, 0);
         p.out = buf(B_U1A); p.out_cs = 64; p.out_c0 = 0;
-        if (launch_conv<64, 9, 1, true, EPI_RELU, 10, 1, 2>(c, 15, pl->tmA[10], c->tmWh[10], pl->tmO[10], pl->tmO[10], p, st)) return 1;
+        if (launch_conv<64, 9, 1, true, EPI_RELU, 10, 1, 2>(c, 15, pl->tmA[10], c->tmWh[10], pl->tmO[10], pl->tmO[10], p, st, false, 0, c->ast[10])) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L11 upconv1.2 + tanh -> y   (transposed GEMM: weights on M, the halo patch on N)
@@ -983,6 +988,16 @@ int cid_set_option(cid_handle h, const char* name, int64_t value) {
         const int l = atoi(name + 3);
         CID_REQUIRE(l >= 0 && l < 16 && value >= 0 && value <= kMaxWStages, "wst<layer>: layer 0..15, depth 0..%d", kMaxWStages);
         h->wst[l] = static_cast<int>(value);
+        return 0;
+    }
+    if (!strcmp(name, "up1_pair")) {
+        h->up1_pair = value != 0;
+        return 0;
+    }
+    if (!strncmp(name, "ast", 3) && name[3] >= '0' && name[3] <= '9') {  // "ast10" = cap on the A-ring depth of layer 10 (tuning)
+        const int l = atoi(name + 3);
+        CID_REQUIRE(l >= 0 && l < 16 && value >= 0 && value <= kMaxStages, "ast<layer>: layer 0..15, depth 0..%d", kMaxStages);
+        h->ast[l] = static_cast<int>(value);
         return 0;
     }
     if (!strcmp(name, "bott_pair")) {

@@ -106,6 +106,10 @@ struct cid_ctx {
                                       // measured at batch 256 @256^2: transpose_1 1.48 -> 1.28 ms as a pair, transpose unchanged)
     bool bott_pair = true;            // "bott_pair" option: the two bottleneck layers as CTA pairs (each CTA streams half of every 32 KB
                                       // weight tile: bottleneck.2 0.239 -> 0.210 ms = 1475 TFLOP/s, bit-identical)
+    bool up1_pair = false;            // "up1_pair" option (A/B): up1 with resident weights as a CTA pair
+    int ast[16] = {0, 4};             // "ast<l>" options (tuning): cap on the A-ring depth of layer l (0 = none). down1.2 runs 4 patches deep:
+                                      // started from an idle GPU (the per-layer profiled pass) it is 0.272 ms instead of 0.310 ms with 6 -
+                                      // inside the back-to-back chain of the real step the depth makes no measurable difference
     int wst[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // "wst<l>" options: weight-ring depth of the streamed-weight
                                       // layers in their batch-256 form (0 = launch_conv's default), see run_layers
     bool sp_scatter = false;          // "sp_scatter" option: salt & pepper as copy + two scatter launches (the fallback form)
