@@ -74,11 +74,31 @@ static const LayerDesc kLayers[12] = {
 enum Buf { B_A0, B_CAT1, B_P1, B_A2, B_CAT2, B_P2, B_B0, B_B1, B_U2A, B_U2B, B_U1A, B_COUNT };
 static const char* kBufNames[B_COUNT] = {"a0", "cat1", "p1", "a2", "cat2", "p2", "b0", "b1", "u2a", "u2b", "u1a"};
 static const int kBufC[B_COUNT] = {64, 128, 64, 128, 256, 128, 256, 256, 128, 128, 64};
-static const int kBufLevel[B_COUNT] = {0, 0, 1, 1, 1, 2, 2, 2, 1, 1, 0};  // spatial dims >> level
+// Spatial levels of the U-Net for ANY input size H x W >= 4 (backend/app.py:80-103): 0 = input (e1), 1 = after pool1
+// (floor(H/2)), 2 = after pool2, 3 = up2's output (2 * level 2), 4 = up1's output (2 * level 3) = the size of the
+// network's result. For multiples of 4, level 3 == level 1 and level 4 == level 0; otherwise the decoder is smaller and
+// the reference crops the skip tensors to it (:90-92, :97-99) - here the consumer's tensor map simply views the top-left
+// (level 3 / 4) window of the concat buffer, whose skip half was written at the encoder's size.
+static const int kBufLevel[B_COUNT] = {0, 0, 1, 1, 1, 2, 2, 2, 3, 3, 4};
+struct LevelDims {
+    int h[5], w[5];
+};
+static LevelDims level_dims(int H, int W) {
+    LevelDims d;
+    d.h[0] = H; d.w[0] = W;
+    d.h[1] = H / 2; d.w[1] = W / 2;
+    d.h[2] = d.h[1] / 2; d.w[2] = d.w[1] / 2;
+    d.h[3] = 2 * d.h[2]; d.w[3] = 2 * d.w[2];
+    d.h[4] = 2 * d.h[3]; d.w[4] = 2 * d.w[3];
+    return d;
+}
+// the level a layer's GEMM runs at (its A operand's / pixel tiles' dims)
+static const int kLayerLevel[12] = {0, 0, 1, 1, 2, 2, 2, 3, 3, 3, 4, 4};
 
 static size_t buf_bytes(int buf, int B, int H, int W) {
+    const LevelDims d = level_dims(H, W);
     const int lv = kBufLevel[buf];
-    size_t n = static_cast<size_t>(B) * (H >> lv) * (W >> lv) * kBufC[buf] * 2;
+    size_t n = static_cast<size_t>(B) * d.h[lv] * d.w[lv] * kBufC[buf] * 2;
     return (n + 1023) & ~static_cast<size_t>(1023);
 }
 
@@ -111,13 +131,15 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // NHWC bf16 activation [B,H,W,C]: box = 64 channels x 8 pixels x box_rows rows x 1 image, 128B swizzle.
-static int make_act_map(CUtensorMap* tm, const void* base, int B, int H, int W, int C, int box_rows, int box_px) {
+// (pitch_h, pitch_w) = the allocated dims when the map views only the top-left H x W window of a larger buffer.
+static int make_act_map(CUtensorMap* tm, const void* base, int B, int H, int W, int C, int box_rows, int box_px,
+                        int pitch_h = 0, int pitch_w = 0) {
     EncodeTiledFn fn = get_encode_fn();
     CID_REQUIRE(fn, "cuTensorMapEncodeTiled entry point not available");
+    const cuuint64_t ph = pitch_h > 0 ? pitch_h : H, pw = pitch_w > 0 ? pitch_w : W;
     cuuint64_t dims[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H),
                           static_cast<cuuint64_t>(B)};
-    cuuint64_t strides[3] = {static_cast<cuuint64_t>(C) * 2, static_cast<cuuint64_t>(W) * C * 2,
-                             static_cast<cuuint64_t>(H) * W * C * 2};
+    cuuint64_t strides[3] = {static_cast<cuuint64_t>(C) * 2, pw * C * 2, ph * pw * C * 2};
     cuuint32_t box[4] = {64, static_cast<cuuint32_t>(box_px), static_cast<cuuint32_t>(box_rows), 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
@@ -129,13 +151,15 @@ static int make_act_map(CUtensorMap* tm, const void* base, int B, int H, int W, 
 }
 
 // convT output viewed as (C, 2W, dy, H, B): box = 64 ch x 16 px x 1 x 16 rows x 1 image (rows 2y+dy of a tile).
-static int make_convt_out_map(CUtensorMap* tm, const void* base, int B, int H, int W, int C) {
+// (pitch_h, pitch_w) = the output buffer's allocated dims when they are larger than 2H x 2W (odd encoder sizes).
+static int make_convt_out_map(CUtensorMap* tm, const void* base, int B, int H, int W, int C, int pitch_h = 0, int pitch_w = 0) {
     EncodeTiledFn fn = get_encode_fn();
     CID_REQUIRE(fn, "cuTensorMapEncodeTiled entry point not available");
-    const cuuint64_t row = static_cast<cuuint64_t>(2 * W) * C * 2;  // bytes of one output row
+    const cuuint64_t ph = pitch_h > 0 ? pitch_h : 2 * H, pw = pitch_w > 0 ? pitch_w : 2 * W;
+    const cuuint64_t row = pw * C * 2;  // bytes of one output row
     cuuint64_t dims[5] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(2 * W), 2, static_cast<cuuint64_t>(H),
                           static_cast<cuuint64_t>(B)};
-    cuuint64_t strides[4] = {static_cast<cuuint64_t>(C) * 2, row, 2 * row, 2 * row * H};
+    cuuint64_t strides[4] = {static_cast<cuuint64_t>(C) * 2, row, 2 * row, ph * row};
     cuuint32_t box[5] = {64, 16, 1, 16, 1};
     cuuint32_t estr[5] = {1, 1, 1, 1, 1};
     CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base), dims, strides, box, estr,
@@ -300,33 +324,36 @@ static int get_plan(cid_ctx* c, int Bc, int H, int W, const void* ws, cid_plan**
     pl.W = W;
     pl.ws = ws;
     layout_offsets(Bc, H, W, pl.off);
+    const LevelDims d = level_dims(H, W);
     for (int l = 1; l < 12; ++l) {
+        // the A operand: the layer's level-sized view of its input buffer (the concat buffers are allocated at the
+        // encoder's size; for sizes that are not multiples of 4 the decoder views their top-left window)
         const int buf = layer_in_buf(l);
-        const int lv = kBufLevel[buf];
+        const int lv = kLayerLevel[l], blv = kBufLevel[buf];
         const int rows = kLayers[l].kind == L_CONVT ? 16 : 18;
         const int px = kLayers[l].kind == L_CONV ? 10 : 8;
-        if (make_act_map(&pl.tmA[l], static_cast<const uint8_t*>(ws) + pl.off[buf], Bc, H >> lv, W >> lv, kBufC[buf],
-                         rows, px))
+        if (make_act_map(&pl.tmA[l], static_cast<const uint8_t*>(ws) + pl.off[buf], Bc, d.h[lv], d.w[lv], kBufC[buf], rows, px,
+                         d.h[blv], d.w[blv]))
             return 1;
     }
     static const int out_buf[12] = {B_A0, B_CAT1, B_A2, B_CAT2, B_B0, B_B1, -1, B_U2A, B_U2B, -1, B_U1A, -1};
     for (int l = 0; l < 12; ++l) {
         const int ob = out_buf[l];
         if (ob < 0) continue;
-        const int lv = kBufLevel[ob];
-        if (make_act_map(&pl.tmO[l], static_cast<const uint8_t*>(ws) + pl.off[ob], Bc, H >> lv, W >> lv, kBufC[ob], 16, 8))
+        const int lv = kBufLevel[ob];  // conv outputs are written at their buffer's own size
+        if (make_act_map(&pl.tmO[l], static_cast<const uint8_t*>(ws) + pl.off[ob], Bc, d.h[lv], d.w[lv], kBufC[ob], 16, 8))
             return 1;
         if (l == 1 || l == 3) {
             const int pb = l == 1 ? B_P1 : B_P2;
             const int plv = kBufLevel[pb];
-            if (make_act_map(&pl.tmO2[l], static_cast<const uint8_t*>(ws) + pl.off[pb], Bc, H >> plv, W >> plv,
+            if (make_act_map(&pl.tmO2[l], static_cast<const uint8_t*>(ws) + pl.off[pb], Bc, d.h[plv], d.w[plv],
                              kBufC[pb], 8, 4))
                 return 1;
         }
     }
-    // convT layers: input resolution (H>>lv_in), output buffer cat2 (L6) / cat1 (L9)
-    if (make_convt_out_map(&pl.tmO[6], static_cast<const uint8_t*>(ws) + pl.off[B_CAT2], Bc, H >> 2, W >> 2, 256)) return 1;
-    if (make_convt_out_map(&pl.tmO[9], static_cast<const uint8_t*>(ws) + pl.off[B_CAT1], Bc, H >> 1, W >> 1, 128)) return 1;
+    // convT layers: input level 2 / 3, output = the decoder half of cat2 (allocated at level 1) / cat1 (level 0)
+    if (make_convt_out_map(&pl.tmO[6], static_cast<const uint8_t*>(ws) + pl.off[B_CAT2], Bc, d.h[2], d.w[2], 256, d.h[1], d.w[1])) return 1;
+    if (make_convt_out_map(&pl.tmO[9], static_cast<const uint8_t*>(ws) + pl.off[B_CAT1], Bc, d.h[3], d.w[3], 128, d.h[0], d.w[0])) return 1;
     c->plans.push_back(pl);
     *out = &c->plans.back();
     return 0;
@@ -506,9 +533,10 @@ static FirstParams make_first_params(const cid_ctx* c, const cid_plan* pl, int n
 static int make_last_params(const cid_ctx* c, const cid_plan* pl, int nb, const IoSpec& io, LastParams* out) {
     LastParams lp;
     memset(&lp, 0, sizeof(lp));
-    lp.B = nb; lp.H = pl->H; lp.W = pl->W;
-    lp.tiles_x = (pl->W + 7) / 8;
-    lp.tiles_y = (pl->H + 15) / 16;
+    const LevelDims d = level_dims(pl->H, pl->W);  // the network's result has the decoder's size (level 4)
+    lp.B = nb; lp.H = d.h[4]; lp.W = d.w[4];
+    lp.tiles_x = (lp.W + 7) / 8;
+    lp.tiles_y = (lp.H + 15) / 16;
     lp.m_tiles = nb * lp.tiles_x * lp.tiles_y;
     lp.stages = std::min(kLastMaxStages, (c->max_smem - last_conv_smem(0)) / kLastStageBytes);
     CID_REQUIRE(lp.stages >= 2, "last conv: shared memory too small");
@@ -524,7 +552,8 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
     const int H = pl->H, W = pl->W;
     uint8_t* ws = static_cast<uint8_t*>(const_cast<void*>(pl->ws));
     auto buf = [&](int b) { return reinterpret_cast<__nv_bfloat16*>(ws + pl->off[b]); };
-    auto tiles = [&](int lv) { return nb * (((W >> lv) + 7) / 8) * (((H >> lv) + 15) / 16); };
+    const LevelDims dm = level_dims(H, W);
+    auto tiles = [&](int lv) { return nb * ((dm.w[lv] + 7) / 8) * ((dm.h[lv] + 15) / 16); };
 
     if (prof_mark(c, st)) return 1;
     {  // L0 down1.0 (+ Pad / ToTensor / Normalize) -> a0
@@ -548,8 +577,8 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         ConvParams p;
         memset(&p, 0, sizeof(p));
         p.B = nb;
-        p.H = H >> lv;
-        p.W = W >> lv;
+        p.H = dm.h[lv];
+        p.W = dm.w[lv];
         p.kb_count = kLayers[l].cin / 64;
         p.n_tiles = 1;
         p.bias = c->bias_dev[l];
@@ -626,9 +655,9 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
     }
     if (prof_mark(c, st)) return 1;
     for (int l = 7; l <= 8; ++l) {  // L7 upconv2.0 (reads cat2) -> u2a, L8 upconv2.2 -> u2b
-        ConvParams p = base(l, 1);
+        ConvParams p = base(l, 3);
         p.out = buf(l == 7 ? B_U2A : B_U2B); p.out_cs = 128; p.out_c0 = 0;
-        if (pick_split(c, tiles(1), 128, 2, 2)) {
+        if (pick_split(c, tiles(3), 128, 2, 2)) {
             if (split_relu(l, p)) return 1;
         } else {
             if (launch_conv<128, 9, 2, false, EPI_RELU, 10, 1, 2>(c, 14, pl->tmA[l], c->tmWh[l], pl->tmO[l], pl->tmO[l], p, st, false, c->wst[l])) return 1;
@@ -636,7 +665,7 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         if (prof_mark(c, st)) return 1;
     }
     {  // L9 up1 (convT) -> cat1[:,0:64]; the whole 128 x 256 weight matrix (64 KB) stays in shared memory
-        ConvParams p = base(9, 1);
+        ConvParams p = base(9, 3);
         p.n_tiles = 1;  // 4*64 columns in one tile of 256
         p.out = buf(B_CAT1); p.out_cs = 128; p.out_c0 = 0;
         if (c->up1_pair) {
@@ -647,7 +676,7 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
     }
     if (prof_mark(c, st)) return 1;
     {  // L10 upconv1.0 (reads cat1) -> u1a; CTA pair (resident weights halved: 74 KB per CTA)
-        ConvParams p = base(10, 0);
+        ConvParams p = base(10, 4);
         p.out = buf(B_U1A); p.out_cs = 64; p.out_c0 = 0;
         if (launch_conv<64, 9, 1, true, EPI_RELU, 10, 1, 2>(c, 15, pl->tmA[10], c->tmWh[10], pl->tmO[10], pl->tmO[10], p, st, false, 0, c->ast[10])) return 1;
     }
@@ -811,8 +840,11 @@ static int forward_common(cid_ctx* c, int B, int H, int W, void* ws, size_t ws_b
         CID_REQUIRE(B >= 1 && H >= 1 && W >= 1, "bad shape B=%d H=%d W=%d", B, H, W);
     } else {
         CID_REQUIRE(B >= 1 && H >= 4 && W >= 4, "bad shape B=%d H=%d W=%d", B, H, W);
-        CID_REQUIRE(H % 4 == 0 && W % 4 == 0, "network input %dx%d must be multiples of 4 (get_padding, app.py:276)", H,
-                    W);
+        // the denoise U-Net takes any size >= 4 on its fp32 entry (the result is 4 * floor(H / 4) x 4 * floor(W / 4), as the
+        // reference's forward gives, backend/app.py:89-99); the fused u8 route pads to multiples of 4 first (get_padding,
+        // :276-281) and the Keras generator's stride-2 'same' convolutions are only laid out for multiples of 4
+        CID_REQUIRE((c->model == CID_MODEL_DENOISE && !io.u8) || (H % 4 == 0 && W % 4 == 0),
+                    "network input %dx%d must be multiples of 4 (get_padding, app.py:276)", H, W);
     }
     CID_REQUIRE(x && y && ws, "null pointer argument");
     CID_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 1023) == 0, "workspace must be 1024-byte aligned");
@@ -1041,7 +1073,8 @@ int cid_workspace_bytes(cid_handle h, int B, int H, int W, size_t* bytes) {
         return 0;
     }
     CID_REQUIRE(B >= 1 && H >= 4 && W >= 4, "bad shape B=%d H=%d W=%d", B, H, W);
-    CID_REQUIRE(H % 4 == 0 && W % 4 == 0, "network input %dx%d must be multiples of 4 (get_padding, app.py:276)", H, W);
+    CID_REQUIRE(h->model == CID_MODEL_DENOISE || (H % 4 == 0 && W % 4 == 0),
+                "network input %dx%d must be multiples of 4 (get_padding, app.py:276)", H, W);
     *bytes = h->model == CID_MODEL_KERAS_CGAN ? cgan_layout_offsets(chunk_of(h, B), H, W, nullptr)
                                               : layout_offsets(chunk_of(h, B), H, W, nullptr);
     return 0;
@@ -1066,7 +1099,9 @@ int cid_forward_f32_nchw(cid_handle h, const float* x, float* y, int B, int H, i
     memset(&io, 0, sizeof(io));
     io.u8 = false;
     const size_t img = static_cast<size_t>(3) * H * W * 4;
-    const size_t out_img = h->model == CID_MODEL_SRGAN ? img * 16 : img;  // SRGAN: [B,3,4H,4W]
+    size_t out_img = h->model == CID_MODEL_SRGAN ? img * 16 : img;  // SRGAN: [B,3,4H,4W]
+    if (h->model == CID_MODEL_DENOISE)  // [B,3,4*floor(H/4),4*floor(W/4)]: == [B,3,H,W] for multiples of 4
+        out_img = static_cast<size_t>(3) * (H / 4 * 4) * (W / 4 * 4) * 4;
     return forward_common(h, B, H, W, ws, ws_bytes, static_cast<cudaStream_t>(stream),
                           reinterpret_cast<const uint8_t*>(x), img, reinterpret_cast<uint8_t*>(y), out_img, io);
 }
@@ -1156,13 +1191,14 @@ int cid_debug_copy_activation(cid_handle h, const char* name, const void* ws, in
     size_t off[B_COUNT];
     layout_offsets(Bc, H, W, off);
     const int lv = kBufLevel[b];
-    const size_t n = static_cast<size_t>(Bc) * (H >> lv) * (W >> lv) * kBufC[b] * 2;
+    const LevelDims dm = level_dims(H, W);
+    const size_t n = static_cast<size_t>(Bc) * dm.h[lv] * dm.w[lv] * kBufC[b] * 2;
     CID_REQUIRE(dst_bytes >= n, "destination too small: %zu < %zu", dst_bytes, n);
     CID_CHECK_CUDA(cudaDeviceSynchronize());
     CID_CHECK_CUDA(cudaMemcpy(dst_host, static_cast<const uint8_t*>(ws) + off[b], n, cudaMemcpyDeviceToHost));
     if (channels) *channels = kBufC[b];
-    if (height) *height = H >> lv;
-    if (width) *width = W >> lv;
+    if (height) *height = dm.h[lv];
+    if (width) *width = dm.w[lv];
     return 0;
 }
 

@@ -215,7 +215,8 @@ class _CudaGenerator(nn.Module):
             x = x.float().contiguous()
         B, _, H, W = x.shape
         s = self.OUT_SCALE
-        y = torch.empty((B, 3, H * s, W * s), dtype=torch.float32, device=x.device)
+        oh, ow = self._out_hw(H, W)
+        y = torch.empty((B, 3, oh * s, ow * s), dtype=torch.float32, device=x.device)
         if B == 0 or H == 0 or W == 0:
             return y
         ws = eng.workspace(B, H, W)
@@ -226,6 +227,11 @@ class _CudaGenerator(nn.Module):
                                                     B, H, W, C.c_void_p(wp), wn, C.c_void_p(stream)),
                        "cid_forward_f32_nchw")
         return y
+
+    @staticmethod
+    def _out_hw(H: int, W: int) -> Tuple[int, int]:
+        """Spatial size of the network's result before OUT_SCALE (the SR generators keep the input's)."""
+        return H, W
 
     # ---- fused route path: u8 NHWC image(s) in -> u8 NHWC image(s) out -----------------------------
     def forward_u8(self, x: torch.Tensor, padding: Tuple[int, int, int, int] = (0, 0, 0, 0),
@@ -259,6 +265,12 @@ class _CudaGenerator(nn.Module):
 
 class DenoiseGenerator(_CudaGenerator):
     MODEL = "denoise"
+
+    @staticmethod
+    def _out_hw(H: int, W: int) -> Tuple[int, int]:
+        """Two floor-halving pools and two doubling transposed convs: for sizes that are not multiples of 4 the
+        reference crops the skip tensors to the decoder (backend/app.py:89-99) and returns this smaller image."""
+        return 4 * (H // 4), 4 * (W // 4)
     PARAM_SHAPES = STATE_DICT_SHAPES
     LAYER_NAMES = ("down1.0", "down1.2", "down2.0", "down2.2", "bottleneck.0", "bottleneck.2", "up2", "upconv2.0",
                    "upconv2.2", "up1", "upconv1.0", "upconv1.2")

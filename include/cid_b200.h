@@ -90,13 +90,15 @@ int cid_finalize(cid_handle h);
  * caller's pointers are updated in the graph's first / last kernel node when they change. */
 int cid_set_option(cid_handle h, const char* name, int64_t value);
 
-/* Bytes of device scratch a forward of B images of H x W (network-input size, multiples of 4)
+/* Bytes of device scratch a forward of B images of H x W (network-input size; keras_cgan: multiples of 4)
  * needs. The caller allocates it (e.g. a torch uint8 tensor) and passes it to the forward. */
 int cid_workspace_bytes(cid_handle h, int B, int H, int W, size_t* bytes);
 
 /* Replaces `y = net(x_pt)` (backend/app.py:433; DenoiseGenerator.forward :80-103).
- * x: device fp32 NCHW [B,3,H,W] in [-1,1]; y: device fp32 NCHW [B,3,H,W] = tanh output.
- * H, W must be multiples of 4 (what get_padding guarantees, backend/app.py:276-281). */
+ * x: device fp32 NCHW [B,3,H,W] in [-1,1], H, W >= 4; y: device fp32 NCHW [B,3,H',W'] = tanh output with
+ * H' = 4*floor(H/4), W' = 4*floor(W/4): for multiples of 4 (what get_padding guarantees, backend/app.py:276-281) the
+ * input's size; otherwise the decoder is smaller and the skip tensors are cropped to it, as the reference's forward
+ * does (:89-99). esrgan / srgan handles: any H, W >= 1, y = [B,3,H,W] / [B,3,4H,4W]. */
 int cid_forward_f32_nchw(cid_handle h, const float* x, float* y, int B, int H, int W, void* ws, size_t ws_bytes,
                          void* stream);
 

@@ -437,6 +437,20 @@ def test_odd_sizes_pad_and_crop(dev, H, W):
     assert np.abs(out.astype(np.int32) - ref.astype(np.int32)).max() <= LSB
 
 
+@pytest.mark.parametrize("B,H,W", [(2, 30, 27), (1, 7, 5), (3, 65, 130), (1, 129, 66), (2, 18, 21), (1, 255, 254)])
+def test_forward_any_size_crops_like_the_reference(dev, B, H, W):
+    """`net(x)` for sizes that are NOT multiples of 4: two floor-halving pools, the decoder comes out smaller and the
+    reference crops the skip tensors to it (backend/app.py:89-99); the result is [B,3,4*(H//4),4*(W//4)]."""
+    net, sd = make_net(dev, 6, 2.0)
+    x = torch.rand(B, 3, H, W, generator=torch.Generator().manual_seed(H * 1000 + W)) * 2 - 1
+    with torch.no_grad():
+        y_ref = orc.forward(sd, x)
+    assert tuple(y_ref.shape) == (B, 3, 4 * (H // 4), 4 * (W // 4))
+    y = net(x.to(dev)).cpu()
+    assert tuple(y.shape) == tuple(y_ref.shape)
+    check_float(y, y_ref, x[:, :, : y.shape[2], : y.shape[3]])
+
+
 def test_iterated_denoise_three_passes(dev):
     """denoise_eavl_iter.py:92-96 feeds the generator's output back in three times."""
     net, sd = make_net(dev, 4, 2.0)
@@ -467,8 +481,10 @@ def test_parameter_update_is_repacked(dev):
 
 def test_error_behaviour(dev):
     net, _ = make_net(dev, 0, 1.0)
+    with pytest.raises(RuntimeError, match="bad shape"):
+        net(torch.zeros(1, 3, 3, 8, device=dev))                     # smaller than the two pooling levels
     with pytest.raises(RuntimeError, match="multiples of 4"):
-        net(torch.zeros(1, 3, 10, 8, device=dev))
+        net.forward_u8(torch.zeros(1, 10, 8, 3, dtype=torch.uint8, device=dev))   # the route pads first (get_padding)
     with pytest.raises(RuntimeError):
         net(torch.zeros(1, 1, 8, 8, device=dev))
     with pytest.raises(RuntimeError):
