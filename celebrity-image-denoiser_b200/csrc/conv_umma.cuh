@@ -70,8 +70,8 @@ struct ConvParams {
                          // of the fp32 outputs over all real pixels = the batch statistics of the BatchNorm that follows,
                          // reduced in the epilogue (warp transpose-sum, per-CTA register accumulators, one double atomic
                          // per channel per warp at the end); may be null
-    float* out_f32;      // EPI_LRELU_BN only: the result is written as fp32 NHWC straight from registers (no bf16
-                         // staging / TMA store): the discriminator's pre-BatchNorm outputs, whose mean >> std
+    float* out_f32;      // EPI_LRELU_BN: the fp32 NHWC result (= what tmO maps; staged in shared memory and written by TMA):
+                         // the discriminator's pre-BatchNorm outputs, whose mean >> std
 };
 
 // Tap geometry (TAPS):
@@ -128,7 +128,8 @@ struct ConvCfg {
     static constexpr int O_SLAB = 128 * 128;
     static constexpr int O2_SLAB = 32 * 128;
     static constexpr int OT_SLAB = 256 * 128;  // transposed convs: [16 rows][16 px][64 ch] of the 2x-upsampled output
-    static constexpr int O_GROUP = NOB * (O_SLAB + (EPI == EPI_RELU_POOL ? O2_SLAB : 0));
+    // (EPI_LRELU_BN stages fp32: a 64-channel slab = two 32-channel half-slabs of [128 px][128 B], stored by two TMA stores)
+    static constexpr int O_GROUP = EPI == EPI_LRELU_BN ? 2 * O_SLAB : NOB * (O_SLAB + (EPI == EPI_RELU_POOL ? O2_SLAB : 0));
     // EPI_ADD: each group also owns a residual buffer (one slab) that the block-skip tile is TMA-loaded into one work item
     // ahead, so the load overlaps the previous slab's TMA store and the wait for the next accumulator
     static constexpr int R_BYTES = EPI == EPI_ADD ? 2 * O_SLAB : 0;
@@ -224,21 +225,6 @@ __device__ __forceinline__ void for_each_chunk(uint32_t taddr, F&& f) {
             f(ch + 1, vb);
         }
     }
-}
-
-// x[c] per lane (32 values) -> the sum over the warp's 32 lanes of x[lane]: recursive halving, 31 shuffles.
-__device__ __forceinline__ float warp_transpose_sum(float (&x)[32], int lane) {
-#pragma unroll
-    for (int off = 16; off >= 1; off >>= 1) {
-        const bool up = (lane & off) != 0;
-#pragma unroll
-        for (int i = 0; i < off; ++i) {
-            const float send = up ? x[i] : x[i + off];
-            const float keep = up ? x[i + off] : x[i];
-            x[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
-        }
-    }
-    return x[0];
 }
 
 // Same, over NCH chunks whose 32-column chunk index is given by map(i), i = 0..NCH-1.
@@ -630,7 +616,6 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         for_each_chunk<2>(tbase + s * Cfg::NACC + cs * 64, [&](int ch, uint32_t (&v)[32]) {
                             const float4* b4 = reinterpret_cast<const float4*>(p.bias + n_tile * N + cs * 64 + ch * 32);
                             uint32_t pk[16];
-                            float fv[EPI == EPI_LRELU_BN ? 32 : 1];
                             if constexpr (EPI == EPI_ADD) {
                                 // v[2i], v[2i+1] += the bf16 pair i of this 32-channel half
 #pragma unroll
@@ -676,31 +661,18 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                 pk[2 * jj + 0] = pack_bf16x2(f0, f1);
                                 pk[2 * jj + 1] = pack_bf16x2(f2, f3);
                                 if constexpr (EPI == EPI_LRELU_BN) {
-                                    fv[4 * jj + 0] = f0; fv[4 * jj + 1] = f1; fv[4 * jj + 2] = f2; fv[4 * jj + 3] = f3;
-                                    if (p.out_f32 != nullptr) {
-                                        const int yy = tc.y0 + yl, xx = tc.x0 + xl;
-                                        if (tc.b < p.B && yy < p.H && xx < p.W) {
-                                            const size_t pix = (static_cast<size_t>(tc.b) * p.H + yy) * p.W + xx;
-                                            float* dst = p.out_f32 + pix * p.out_cs + p.out_c0 + n_tile * N + cs * 64 + ch * 32 + 4 * jj;
-                                            *reinterpret_cast<float4*>(dst) = make_float4(f0, f1, f2, f3);
-                                        }
-                                    }
-                                }
-                            }
-                            if constexpr (EPI == EPI_LRELU_BN) {
-                                if (p.stats != nullptr) {
+                                    // fp32 result: this pixel's 32 channels = one 128-byte row of half-slab `ch` (SW128),
+                                    // written out by a TMA store below (per-thread 16-byte global stores touch 32 lines
+                                    // with 16 bytes each per warp instruction: the layer ran at 21 % of the tensor peak).
+                                    // Pixels outside the image are staged as zeros (the store clips them; the batch
+                                    // statistics below then need no mask).
                                     const bool live = tc.b < p.B && tc.y0 + yl < p.H && tc.x0 + xl < p.W;
-                                    float sq[32];
-#pragma unroll
-                                    for (int i = 0; i < 32; ++i) {
-                                        fv[i] = live ? fv[i] : 0.f;
-                                        sq[i] = fv[i] * fv[i];
-                                    }
-                                    st_sum[cs * 2 + ch] += warp_transpose_sum(fv, lane);
-                                    st_sq[cs * 2 + ch] += warp_transpose_sum(sq, lane);
+                                    st_shared_v4(slab + ch * Cfg::O_SLAB + row * 128 + ((jj ^ (row & 7)) << 4),
+                                                 live ? __float_as_uint(f0) : 0u, live ? __float_as_uint(f1) : 0u,
+                                                 live ? __float_as_uint(f2) : 0u, live ? __float_as_uint(f3) : 0u);
                                 }
                             }
-                            if constexpr (TS) {
+                            if constexpr (TS && EPI != EPI_LRELU_BN) {
                                 uint8_t* rowp = slab + row * 128;
 #pragma unroll
                                 for (int jj = 0; jj < 4; ++jj) {
@@ -731,7 +703,32 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             fence_proxy_async();
                             named_bar_sync(bar_id, 128);
                         }
-                        if (TS && issuer && !(EPI == EPI_LRELU_BN && p.out_f32 != nullptr)) {
+                        if constexpr (EPI == EPI_LRELU_BN) {
+                            if (issuer) {  // tmO = the fp32 map of the output (box 32 ch x 8 px x 16 rows)
+                                const int c64 = n_tile * N + cs * 64;
+                                tma_store_4d(&tmO, slab, p.out_c0 + c64, tc.x0, tc.y0, tc.b);
+                                tma_store_4d(&tmO, slab + Cfg::O_SLAB, p.out_c0 + c64 + 32, tc.x0, tc.y0, tc.b);
+                                bulk_commit();
+                            }
+                            // BatchNorm batch statistics from the staged tile: lane = channel, this warp's 32 pixel rows
+                            // (one row = 32 banks, the swizzle keeps the lanes on distinct banks: conflict-free), summed
+                            // into per-CTA register accumulators - no shuffles
+                            if (p.stats != nullptr) {
+#pragma unroll
+                                for (int hh = 0; hh < 2; ++hh) {
+                                    const uint8_t* hs = slab + hh * Cfg::O_SLAB + ((lane & 3) << 2);
+                                    float a1 = 0.f, a2 = 0.f;
+#pragma unroll 8
+                                    for (int r = q * 32; r < q * 32 + 32; ++r) {
+                                        const float v = *reinterpret_cast<const float*>(hs + r * 128 + (((lane >> 2) ^ (r & 7)) << 4));
+                                        a1 += v;
+                                        a2 = fmaf(v, v, a2);
+                                    }
+                                    st_sum[cs * 2 + hh] += a1;
+                                    st_sq[cs * 2 + hh] += a2;
+                                }
+                            }
+                        } else if (TS && issuer) {
                             const int c64 = n_tile * N + cs * 64;
                             tma_store_4d(&tmO, slab, p.out_c0 + c64, tc.x0, tc.y0, tc.b);
                             if constexpr (EPI == EPI_RELU_POOL)

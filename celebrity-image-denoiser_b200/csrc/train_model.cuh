@@ -191,7 +191,25 @@ static int make_act_map_s2(CUtensorMap* tm, const void* base, int B, int H, int 
     return 0;
 }
 
-// kind: 0 plain box, 1 stride-2 box, 2 the 5-D 2x-upsampling scatter map (H, W = INPUT resolution)
+// fp32 NHWC [B,H,W,C]: box = 32 channels (one 128-byte swizzle row) x 8 pixels x 16 rows - the staged output tile of
+// the discriminator's pre-BatchNorm convolutions (EPI_LRELU_BN)
+static int make_act_map_f32(CUtensorMap* tm, const void* base, int B, int H, int W, int C) {
+    EncodeTiledFn fn = get_encode_fn();
+    CID_REQUIRE(fn, "cuTensorMapEncodeTiled entry point not available");
+    cuuint64_t dims[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H),
+                          static_cast<cuuint64_t>(B)};
+    cuuint64_t strides[3] = {static_cast<cuuint64_t>(C) * 4, static_cast<cuuint64_t>(W) * C * 4,
+                             static_cast<cuuint64_t>(H) * W * C * 4};
+    cuuint32_t box[4] = {32, 8, 16, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CID_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(fp32 activation %dx%dx%dx%d) failed: %d", B, H, W, C, static_cast<int>(r));
+    return 0;
+}
+
+// kind: 0 plain box, 1 stride-2 box, 2 the 5-D 2x-upsampling scatter map (H, W = INPUT resolution), 3 fp32 output tile
 static const CUtensorMap* tmap(cid_train* t, const void* base, int B, int H, int W, int C, int rows, int px, int kind) {
     char key[160];
     snprintf(key, sizeof(key), "%p/%d/%d/%d/%d/%d/%d/%d", base, B, H, W, C, rows, px, kind);
@@ -200,6 +218,7 @@ static const CUtensorMap* tmap(cid_train* t, const void* base, int B, int H, int
     CUtensorMap tm;  // (the cache is trimmed only between steps, train_make_run: pointers handed out stay valid)
     int rc = kind == 0   ? make_act_map(&tm, base, B, H, W, C, rows, px)
              : kind == 1 ? make_act_map_s2(&tm, base, B, H, W, C, rows, px)
+             : kind == 3 ? make_act_map_f32(&tm, base, B, H, W, C)
                          : make_convt_out_map(&tm, base, B, H, W, C);
     if (rc) return nullptr;
     return &(t->maps[key] = tm);
@@ -661,7 +680,7 @@ static int d_forward(const TrainRun& r, const float* img) {
     }
     {  // model.2: 3x3 stride 2 (as 4x4 stride 2 with a zero 4th tap row / column) -> z1
         const CUtensorMap* tmA = tmap(t, r.tbuf(TB_DA0), B, H, W, 64, 17, 9, 1);
-        const CUtensorMap* tmO = tmap(t, r.tbuf(TB_DZ1D), B, H >> 1, W >> 1, 64, 16, 8, 0);
+        const CUtensorMap* tmO = tmap(t, r.tbuf(TB_DZ1D), B, H >> 1, W >> 1, 64, 16, 8, 3);  // fp32 output tile
         if (!tmA || !tmO) return 1;
         ConvParams p = conv_base(r, 1, 64, 64);
         p.bias = t->d_bias_pad[1];
@@ -674,7 +693,7 @@ static int d_forward(const TrainRun& r, const float* img) {
     if (bn_forward(r, 1, r.tbuf(TB_DZ1D), r.tbuf(TB_DA1), 1)) return 1;
     {  // model.5: 3x3 64 -> 128 -> z2
         const CUtensorMap* tmA = tmap(t, r.tbuf(TB_DA1), B, H >> 1, W >> 1, 64, 18, 10, 0);
-        const CUtensorMap* tmO = tmap(t, r.tbuf(TB_DZ2D), B, H >> 1, W >> 1, 128, 16, 8, 0);
+        const CUtensorMap* tmO = tmap(t, r.tbuf(TB_DZ2D), B, H >> 1, W >> 1, 128, 16, 8, 3);  // fp32 output tile
         if (!tmA || !tmO) return 1;
         ConvParams p = conv_base(r, 1, 64, 128);
         p.bias = t->d_bias_pad[2];
@@ -687,7 +706,7 @@ static int d_forward(const TrainRun& r, const float* img) {
     if (bn_forward(r, 2, r.tbuf(TB_DZ2D), r.tbuf(TB_DA2), 1)) return 1;
     {  // model.8: 3x3 stride 2 128 -> 128 -> z3
         const CUtensorMap* tmA = tmap(t, r.tbuf(TB_DA2), B, H >> 1, W >> 1, 128, 17, 9, 1);
-        const CUtensorMap* tmO = tmap(t, r.tbuf(TB_DZ3D), B, H >> 2, W >> 2, 128, 16, 8, 0);
+        const CUtensorMap* tmO = tmap(t, r.tbuf(TB_DZ3D), B, H >> 2, W >> 2, 128, 16, 8, 3);  // fp32 output tile
         if (!tmA || !tmO) return 1;
         ConvParams p = conv_base(r, 2, 128, 128);
         p.bias = t->d_bias_pad[3];
