@@ -611,7 +611,10 @@ static int dgrad3x3(const TrainRun& r, int lv, const void* dz, int k_ch, const C
         if (tmWh) return launch_conv_t<128, 9, 2, false, EPI_DGRAD, 10, 1, 2>(t, *tmA, *tmWh, *tmO, p, r.st);
         return launch_conv_t<128, 9, 2, false, EPI_DGRAD, 10, 1>(t, *tmA, tmW, *tmO, p, r.st);
     }
-    if (n_ch == 256) return launch_conv_t<256, 9, 1, false, EPI_DGRAD, 10, 1>(t, *tmA, tmW, *tmO, p, r.st);
+    if (n_ch == 256) {  // CTA pair: each CTA streams half of every 32 KB weight tile (as the forward's bottleneck layers)
+        if (tmWh) return launch_conv_t<256, 9, 1, false, EPI_DGRAD, 10, 1, 2>(t, *tmA, *tmWh, *tmO, p, r.st);
+        return launch_conv_t<256, 9, 1, false, EPI_DGRAD, 10, 1>(t, *tmA, tmW, *tmO, p, r.st);
+    }
     set_error("dgrad3x3: unsupported width %d", n_ch);
     return 1;
 }
