@@ -277,7 +277,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--layers", action="store_true", help="also print the per-layer table to stderr")
     ap.add_argument("--opt", action="append", default=[], metavar="NAME=VALUE",
-                    help="cid_set_option on the generator (A/B experiments, e.g. --opt up2_stream=1)")
+                    help="cid_set_option on the generator (A/B experiments, e.g. --opt wst7=8)")
     ap.add_argument("--only", default="", help="comma list of extra sections to run (default: all): "
                                                "sustained,latency,strong,train,membound")
     ap.add_argument("--sustained-seconds", type=float, default=3.0)

@@ -634,24 +634,18 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         p.out = buf(l == 4 ? B_B0 : B_B1); p.out_cs = 256; p.out_c0 = 0;
         if (pick_split(c, tiles(2), 256, 1, 1)) {
             if (split_relu(l, p)) return 1;
-        } else if (c->bott_pair) {  // CTA pair: each CTA streams half of every 32 KB weight tile
+        } else {  // CTA pair: each CTA streams half of every 32 KB weight tile (single CTAs: bottleneck.2 0.239 ms, pair 0.210)
             if (launch_conv<256, 9, 1, false, EPI_RELU, 10, 1, 2>(c, 3, pl->tmA[l], c->tmWh[l], pl->tmO[l], pl->tmO[l], p, st, false, c->wst[l])) return 1;
-        } else {
-            if (launch_conv<256, 9, 1, false, EPI_RELU, 10, 1>(c, 3, pl->tmA[l], c->tmW[l], pl->tmO[l], pl->tmO[l], p, st)) return 1;
         }
         if (prof_mark(c, st)) return 1;
     }
-    {  // L6 up2 (convT) -> cat2[:,0:128]; 4*128 columns in two blocks of 256. CTA pair; by default a pair keeps ITS column
-       // block's half of the weight matrix (2 x 64 KB) resident and walks every pixel tile (the A tiles are read twice, from
-       // L2); "up2_stream" = each CTA streams half of the 256 KB weight matrix per tile pair instead
+    {  // L6 up2 (convT) -> cat2[:,0:128]; 4*128 columns in two blocks of 256. CTA pair; a pair keeps ITS column block's half of
+       // the weight matrix (2 x 64 KB) resident and walks every pixel tile (the A tiles are read twice, the second time from
+       // L2): 0.105 -> 0.093 ms against streaming half of the 256 KB matrix per tile pair
         ConvParams p = base(6, 2);
         p.n_tiles = 2;
         p.out = buf(B_CAT2); p.out_cs = 256; p.out_c0 = 0;
-        if (c->up2_stream) {
-            if (launch_conv<256, 1, 1, false, EPI_CONVT, 0, 1, 2>(c, 20, pl->tmA[6], c->tmWh[6], pl->tmO[6], pl->tmO[6], p, st)) return 1;
-        } else {
-            if (launch_conv<256, 1, 1, true, EPI_CONVT, 0, 1, 2>(c, 20, pl->tmA[6], c->tmWh[6], pl->tmO[6], pl->tmO[6], p, st, false, 0, c->ast[6])) return 1;
-        }
+        if (launch_conv<256, 1, 1, true, EPI_CONVT, 0, 1, 2>(c, 20, pl->tmA[6], c->tmWh[6], pl->tmO[6], pl->tmO[6], p, st, false, 0, c->ast[6])) return 1;
     }
     if (prof_mark(c, st)) return 1;
     for (int l = 7; l <= 8; ++l) {  // L7 upconv2.0 (reads cat2) -> u2a, L8 upconv2.2 -> u2b
@@ -668,11 +662,7 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
         ConvParams p = base(9, 3);
         p.n_tiles = 1;  // 4*64 columns in one tile of 256
         p.out = buf(B_CAT1); p.out_cs = 128; p.out_c0 = 0;
-        if (c->up1_pair) {
-            if (launch_conv<256, 1, 1, true, EPI_CONVT, 0, 1, 2>(c, 21, pl->tmA[9], c->tmWh[9], pl->tmO[9], pl->tmO[9], p, st, false, 0, c->ast[9])) return 1;
-        } else {
-            if (launch_conv<256, 1, 1, true, EPI_CONVT, 0, 1>(c, 21, pl->tmA[9], c->tmW[9], pl->tmO[9], pl->tmO[9], p, st, false, 0, c->ast[9])) return 1;
-        }
+        if (launch_conv<256, 1, 1, true, EPI_CONVT, 0, 1>(c, 21, pl->tmA[9], c->tmW[9], pl->tmO[9], pl->tmO[9], p, st, false, 0, c->ast[9])) return 1;
     }
     if (prof_mark(c, st)) return 1;
     {  // L10 upconv1.0 (reads cat1) -> u1a; CTA pair (resident weights halved: 74 KB per CTA)
@@ -1022,30 +1012,14 @@ int cid_set_option(cid_handle h, const char* name, int64_t value) {
         h->wst[l] = static_cast<int>(value);
         return 0;
     }
-    if (!strcmp(name, "up1_pair")) {
-        h->up1_pair = value != 0;
-        return 0;
-    }
     if (!strncmp(name, "ast", 3) && name[3] >= '0' && name[3] <= '9') {  // "ast10" = cap on the A-ring depth of layer 10 (tuning)
         const int l = atoi(name + 3);
         CID_REQUIRE(l >= 0 && l < 16 && value >= 0 && value <= kMaxStages, "ast<layer>: layer 0..15, depth 0..%d", kMaxStages);
         h->ast[l] = static_cast<int>(value);
         return 0;
     }
-    if (!strcmp(name, "bott_pair")) {
-        h->bott_pair = value != 0;
-        return 0;
-    }
-    if (!strcmp(name, "cgan_pair")) {
-        h->cgan_pair = static_cast<int>(value);
-        return 0;
-    }
     if (!strcmp(name, "sp_scatter")) {  // salt & pepper noiser: 1 = copy + scatter launches instead of the one-pass slab kernel
         h->sp_scatter = value != 0;
-        return 0;
-    }
-    if (!strcmp(name, "up2_stream")) {  // A/B switch for up2's weight handling (run_layers, L6)
-        h->up2_stream = value != 0;
         return 0;
     }
     if (!strcmp(name, "graph")) {  // CUDA-graph replay of launch-bound passes (default on)

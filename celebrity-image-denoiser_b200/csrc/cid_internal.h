@@ -102,18 +102,12 @@ struct cid_ctx {
     uint32_t attr_done = 0;           // bit per kernel instantiation: max-dynamic-smem attribute set
     std::map<uint64_t, void*> resize_coeffs;  // (in_size,out_size) -> device coefficient block
     int regime = 0;                   // "regime" option: 0 per-layer choice, 1 batch-256 configuration, 2 N-split form
-    int cgan_pair = 2;                // "cgan_pair" option: bit 0 = conv2d_transpose, bit 1 = conv2d_transpose_1 as CTA pairs (bit-identical;
-                                      // measured at batch 256 @256^2: transpose_1 1.48 -> 1.28 ms as a pair, transpose unchanged)
-    bool bott_pair = true;            // "bott_pair" option: the two bottleneck layers as CTA pairs (each CTA streams half of every 32 KB
-                                      // weight tile: bottleneck.2 0.239 -> 0.210 ms = 1475 TFLOP/s, bit-identical)
-    bool up1_pair = false;            // "up1_pair" option (A/B): up1 with resident weights as a CTA pair
     int ast[16] = {0, 4};             // "ast<l>" options (tuning): cap on the A-ring depth of layer l (0 = none). down1.2 runs 4 patches deep:
                                       // started from an idle GPU (the per-layer profiled pass) it is 0.272 ms instead of 0.310 ms with 6 -
                                       // inside the back-to-back chain of the real step the depth makes no measurable difference
     int wst[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // "wst<l>" options: weight-ring depth of the streamed-weight
                                       // layers in their batch-256 form (0 = launch_conv's default), see run_layers
     bool sp_scatter = false;          // "sp_scatter" option: salt & pepper as copy + two scatter launches (the fallback form)
-    bool up2_stream = false;          // "up2_stream" option: stream up2's weights instead of keeping a column block resident
     bool use_graph = true;            // "graph" option: CUDA-graph replay of launch-bound passes
     bool graph_broken = false;        // capture / node update failed once: eager launches from then on
     void* capture_stream = nullptr;   // cudaStream_t the graphs are captured on (nothing ever executes on it)

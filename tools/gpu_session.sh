@@ -7,5 +7,5 @@ python -c "
 import json;d=json.loads(open('gpurun_out/${tag}_bench_short.json').read().strip().splitlines()[-1]);print('value',round(d['value']),d['ms_per_step'],'e2e',round(d['e2e']['value']),'train ms',d['train']['ms_per_step'])"
 timeout 200 python tools/sr_perf.py esrgan 256 128 2>&1 | grep UNPROFILED
 timeout 200 python tools/sr_perf.py srgan 64 128 2>&1 | tail -3
-timeout 200 python tools/cgan_perf.py 256 2>&1 | head -1
+timeout 200 python tools/cgan_perf.py 256 2>&1 | tail -1
 timeout 200 python tools/lat_debug.py 2>&1 | head -1
