@@ -356,7 +356,11 @@ def main():
     pipe = HostPipeline(net, dev, min(args.sub_batch, B), H, W, depth=args.depth)
     io_bytes = [0, 0]
     for stage, key in (("all", "e2e"), ("copy", "e2e_copy"), ("compute", "e2e_compute")):
-        for _ in range(3):
+        # every timed region starts from the same board state as `value` did (idle, then W warm-up passes): straight after
+        # a full-power region the board is power-capped and the same loop runs 5-10 % slower (power-limited)
+        torch.cuda.synchronize(dev)
+        time.sleep(0.5)
+        for _ in range(max(Wm, 3)):
             pipe.run(host_in, host_out, stage=stage)
         torch.cuda.synchronize(dev)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

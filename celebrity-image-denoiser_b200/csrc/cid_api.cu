@@ -707,7 +707,7 @@ static bool same_io(const IoSpec& a, const IoSpec& b) {
 
 static bool graph_wanted(const cid_ctx* c, const cid_plan* pl, int nb) {
     if (!c->use_graph || c->profile || c->graph_broken || nb != pl->Bc) return false;
-    return static_cast<size_t>(nb) * pl->H * pl->W <= (1u << 20);  // longer passes are not launch-bound
+    return static_cast<int64_t>(nb) * pl->H * pl->W <= c->graph_max_px;  // longer passes are not launch-bound
 }
 
 static int graph_capture(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cid_graph* g) {
@@ -1020,6 +1020,11 @@ int cid_set_option(cid_handle h, const char* name, int64_t value) {
     }
     if (!strcmp(name, "sp_scatter")) {  // salt & pepper noiser: 1 = copy + scatter launches instead of the one-pass slab kernel
         h->sp_scatter = value != 0;
+        return 0;
+    }
+    if (!strcmp(name, "graph_max_px")) {
+        CID_REQUIRE(value >= 0, "graph_max_px must be >= 0");
+        h->graph_max_px = value;
         return 0;
     }
     if (!strcmp(name, "graph")) {  // CUDA-graph replay of launch-bound passes (default on)

@@ -102,6 +102,7 @@ struct cid_ctx {
     uint32_t attr_done = 0;           // bit per kernel instantiation: max-dynamic-smem attribute set
     std::map<uint64_t, void*> resize_coeffs;  // (in_size,out_size) -> device coefficient block
     int regime = 0;                   // "regime" option: 0 per-layer choice, 1 batch-256 configuration, 2 N-split form
+    int64_t graph_max_px = 1 << 20;   // "graph_max_px" option: passes of at most this many pixels replay as a CUDA graph
     int ast[16] = {0, 4};             // "ast<l>" options (tuning): cap on the A-ring depth of layer l (0 = none). down1.2 runs 4 patches deep:
                                       // started from an idle GPU (the per-layer profiled pass) it is 0.272 ms instead of 0.310 ms with 6 -
                                       // inside the back-to-back chain of the real step the depth makes no measurable difference
