@@ -463,6 +463,12 @@ static int launch_conv(cid_ctx* c, int slot, const CUtensorMap& tmA, const CUten
     p.tiles_x = (p.W + 7) / 8;
     p.tiles_y = (p.H + 15) / 16;
     p.m_tiles = p.B * p.tiles_x * p.tiles_y;
+    {
+        auto lg = [](int v) { int k = 0; while ((1 << k) < v) ++k; return (1 << k) == v ? k : -1; };
+        p.tx_sh = lg(p.tiles_x);
+        p.ty_sh = lg(p.tiles_y);
+        if (p.tx_sh < 0 || p.ty_sh < 0) p.tx_sh = p.ty_sh = -1;
+    }
     p.num_work = ((p.m_tiles + S * CG - 1) / (S * CG)) * p.n_tiles;  // work items of one CTA (or CTA pair)
     const int smem = Cfg::smem_bytes(p.kb_count, a_stages, w_stages);
     auto kern = conv_umma_kernel<N, TAPS, S, WRES, EPI, PW, TS, CG>;

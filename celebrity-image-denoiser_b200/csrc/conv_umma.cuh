@@ -49,6 +49,7 @@ struct ConvParams {
     int n_tiles;         // tiles of width N across the GEMM N extent
     int tiles_x, tiles_y;
     int m_tiles;         // B * tiles_x * tiles_y
+    int tx_sh, ty_sh;    // log2(tiles_x), log2(tiles_y) when both are powers of two, else -1 (decode_tile)
     int num_work;        // ceil(m_tiles / S) * n_tiles
     int a_stages, w_stages;
     int w_rows_per_tap;  // rows of the packed weight matrix per tap (= padded Cout)
@@ -184,6 +185,14 @@ __device__ __forceinline__ TileCoord decode_tile(int tiles_x, int tiles_y, int m
     return t;
 }
 __device__ __forceinline__ TileCoord decode_tile(const ConvParams& p, int mt) {
+    if (p.tx_sh >= 0) {  // tiles_x and tiles_y are powers of two (128 x 128 images: 16 x 8): shifts instead of two divisions
+        TileCoord t;
+        const int r = mt >> p.tx_sh;
+        t.x0 = (mt & (p.tiles_x - 1)) * 8;
+        t.y0 = (r & (p.tiles_y - 1)) * 16;
+        t.b = r >> p.ty_sh;
+        return t;
+    }
     return decode_tile(p.tiles_x, p.tiles_y, mt);
 }
 
@@ -833,7 +842,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     auto chunk_of = [&](int i) { return c64mode ? slab_i * 4 + i : (i >> 1) * 4 + slab_i * 2 + (i & 1); };
                     for_each_chunk_mapped<4>(tbase, chunk_of, [&](int ch, uint32_t (&v)[32]) {
                         const int n = n_tile * N + ch * 32;
-                        const int quad = n / p.cout;
+                        const int quad = c64mode ? (n >> 6) : (n >> 7);  // p.cout is 64 or 128
                         const int c = n - quad * p.cout;
                         // transposed conv: one bias per output channel; pixel shuffle: one per GEMM column
                         const float4* b4 = reinterpret_cast<const float4*>(p.bias + (p.bias_per_column ? n : c));
