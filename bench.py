@@ -89,7 +89,7 @@ def library_sha():
 class ClockSampler:
     """Samples SM clock / throttle reasons through NVML while the timed region runs."""
 
-    def __init__(self, index: int, period_s: float = 0.004):
+    def __init__(self, index: int, period_s: float = 0.002):
         self.samples, self.reasons, self.max_mhz = [], set(), None
         self.period = period_s
         self._stop = threading.Event()
@@ -128,6 +128,11 @@ class ClockSampler:
 
     def start(self):
         if self.nv is not None:
+            try:  # first NVML queries of a process can take tens of ms: pay for them before the timed region
+                self.nv.nvmlDeviceGetClockInfo(self.dev, self.nv.NVML_CLOCK_SM)
+                self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.dev)
+            except Exception:
+                pass
             self._thread = threading.Thread(target=self._loop, daemon=True)
             self._thread.start()
         return self
