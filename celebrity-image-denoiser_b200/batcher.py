@@ -133,8 +133,9 @@ class MicroBatcher:
                     H, W = group[0].image.shape[:2]
                     host_in, _ = self._buffers(H, W)
                     nb = len(group)
+                    staged = host_in.numpy()          # a view of the (pinned) staging tensor
                     for i, r in enumerate(group):
-                        host_in[i].copy_(torch.from_numpy(r.image))
+                        np.copyto(staged[i], r.image)  # (np.asarray(PIL image) is read-only: no torch.from_numpy on it)
                     out = self._run_batch(host_in[:nb])
                     self.batches.append(nb)
                     res = out.numpy()
