@@ -14,6 +14,7 @@
 #include <math.h>
 
 #include <algorithm>
+#include <mutex>
 
 #include "cid_internal.h"
 #include "ptx.cuh"
@@ -346,11 +347,158 @@ __global__ void __launch_bounds__(256) normalize_kernel(const uint8_t* __restric
             __fdiv_rn(__fsub_rn(__fdiv_rn(static_cast<float>(px[c]), 255.f), mean), stdv);
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of the two-pass resize (cid_resize_bicubic_u8_static, below). Everything the two passes need
+// besides the caller's input and output lives in ONE file-scope device array: the four coefficient tables (computed on
+// the device, so there is no host vector and no copy either) and the intermediate image of the horizontal pass.
+// Every GPU that loads the library holds the array (kStaticScratchBytes) until the process exits.
+//   [0, kStaticTableBytes)                    boundsH | kkH | boundsV | kkV   (ints)
+//   [kStaticTableBytes, kStaticScratchBytes)  intermediate image, B x in_h x out_w x C bytes
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr size_t kStaticTableBytes = CID_RESIZE_STATIC_TABLE_BYTES;
+constexpr size_t kStaticTmpBytes = CID_RESIZE_STATIC_TMP_BYTES;
+constexpr size_t kStaticScratchBytes = kStaticTableBytes + kStaticTmpBytes;
+static __device__ __align__(256) uint8_t g_resize_static_scratch[kStaticScratchBytes];
+
+// host_coeffs()'s arithmetic on the device: the same double operations in the same order, each one rounded on its own
+// (no fused multiply-add), so the fixed-point tables - and with them the image - are the ones the host builds.
+__device__ __forceinline__ double bicubic_filter_dev(double x) {
+    const double a = -0.5;
+    if (x < 0.0) x = -x;
+    if (x < 1.0) {
+        const double t = __dsub_rn(__dmul_rn(a + 2.0, x), a + 3.0);
+        return __dadd_rn(__dmul_rn(__dmul_rn(t, x), x), 1.0);
+    }
+    if (x < 2.0) {
+        const double t = __dadd_rn(__dmul_rn(__dsub_rn(x, 5.0), x), 8.0);
+        return __dmul_rn(__dsub_rn(__dmul_rn(t, x), 4.0), a);
+    }
+    return 0.0;
+}
+
+__device__ __forceinline__ int static_ksize(int in_size, int out_size) {
+    double fs = __ddiv_rn(static_cast<double>(static_cast<float>(in_size)), static_cast<double>(out_size));
+    if (fs < 1.0) fs = 1.0;
+    return static_cast<int>(ceil(__dmul_rn(2.0, fs))) * 2 + 1;
+}
+
+// One thread per output column (first out_w threads) or output row (the next out_h): its (first tap, count) pair and
+// its ksize fixed-point weights, written into the table region of the static array (named directly: device code).
+__global__ void __launch_bounds__(128) static_coeffs_kernel(int in_w, int out_w, int in_h, int out_h) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= out_w + out_h) return;
+    int* tab = reinterpret_cast<int*>(g_resize_static_scratch);
+    const int ksH = static_ksize(in_w, out_w);
+    int in_size = in_w, out_size = out_w;
+    int* bounds = tab;
+    int* kk = tab + 2 * out_w;
+    if (t >= out_w) {
+        t -= out_w;
+        in_size = in_h;
+        out_size = out_h;
+        bounds = tab + out_w * (2 + ksH);
+        kk = bounds + 2 * out_h;
+    }
+    const double scale = __ddiv_rn(static_cast<double>(static_cast<float>(in_size)), static_cast<double>(out_size));
+    const double filterscale = scale < 1.0 ? 1.0 : scale;
+    const double support = __dmul_rn(2.0, filterscale);
+    const int ksize = static_cast<int>(ceil(support)) * 2 + 1;
+    const double center = __dmul_rn(__dadd_rn(static_cast<double>(t), 0.5), scale);
+    const double ss = __ddiv_rn(1.0, filterscale);
+    int xmin = static_cast<int>(__dadd_rn(__dsub_rn(center, support), 0.5));
+    if (xmin < 0) xmin = 0;
+    int xmax = static_cast<int>(__dadd_rn(__dadd_rn(center, support), 0.5));
+    if (xmax > in_size) xmax = in_size;
+    xmax -= xmin;
+    double ww = 0.0;
+    for (int x = 0; x < xmax; ++x)
+        ww = __dadd_rn(ww, bicubic_filter_dev(__dmul_rn(__dadd_rn(__dsub_rn(static_cast<double>(x + xmin), center), 0.5), ss)));
+    int* k = kk + static_cast<size_t>(t) * ksize;
+    for (int x = 0; x < ksize; ++x) {
+        double w = 0.0;
+        if (x < xmax) {
+            w = bicubic_filter_dev(__dmul_rn(__dadd_rn(__dsub_rn(static_cast<double>(x + xmin), center), 0.5), ss));
+            if (ww != 0.0) w = __ddiv_rn(w, ww);
+        }
+        const double v = __dmul_rn(w, static_cast<double>(1 << kPrecisionBits));
+        k[x] = w < 0 ? static_cast<int>(__dadd_rn(-0.5, v)) : static_cast<int>(__dadd_rn(0.5, v));
+    }
+    bounds[2 * t] = xmin;
+    bounds[2 * t + 1] = xmax;
+}
+
+// The array's device address, looked up once per device with that device current (in host code the array's name is only
+// a host-side stand-in for the symbol, not an address a kernel can use).
+static int static_scratch_ptr(int device, uint8_t** out) {
+    constexpr int kMaxDevices = 64;
+    static std::mutex mu;
+    static uint8_t* ptrs[kMaxDevices] = {};
+    CID_REQUIRE(device >= 0 && device < kMaxDevices, "cid_resize_bicubic_u8_static: device %d out of range", device);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[device]) {
+        void* p = nullptr;
+        CID_CHECK_CUDA(cudaGetSymbolAddress(&p, g_resize_static_scratch));
+        CID_REQUIRE(p != nullptr, "cid_resize_bicubic_u8_static: no device address for the scratch array");
+        ptrs[device] = static_cast<uint8_t*>(p);
+    }
+    *out = ptrs[device];
+    return 0;
+}
+
 }  // namespace cid
 
 using namespace cid;
 
 extern "C" {
+
+int cid_resize_bicubic_u8_static(int device, const uint8_t* in, uint8_t* out, int B, int in_h, int in_w, int out_h,
+                                 int out_w, int C, void* stream) {
+    CID_REQUIRE(in && out, "cid_resize_bicubic_u8_static: null argument");
+    CID_REQUIRE(B >= 1 && in_h >= 1 && in_w >= 1 && out_h >= 1 && out_w >= 1 && C >= 1, "bad shape");
+    // the same ksize host_coeffs() derives (float box, double scale)
+    auto ksize_of = [](int in_size, int out_size) {
+        double fs = static_cast<double>(static_cast<float>(in_size)) / out_size;
+        if (fs < 1.0) fs = 1.0;
+        return static_cast<int>(ceil(2.0 * fs)) * 2 + 1;
+    };
+    const int ksH = ksize_of(in_w, out_w), ksV = ksize_of(in_h, out_h);
+    const size_t table_bytes = (static_cast<size_t>(out_w) * (2 + ksH) + static_cast<size_t>(out_h) * (2 + ksV)) * 4;
+    const size_t tmp_bytes = static_cast<size_t>(B) * in_h * out_w * C;
+    CID_REQUIRE(table_bytes <= kStaticTableBytes,
+                "cid_resize_bicubic_u8_static: coefficient tables of %zu bytes exceed the static limit of %zu "
+                "(use cid_resize_bicubic_u8)", table_bytes, kStaticTableBytes);
+    CID_REQUIRE(tmp_bytes <= kStaticTmpBytes,
+                "cid_resize_bicubic_u8_static: B*in_h*out_w*C = %zu bytes exceeds the static limit of %zu "
+                "(use cid_resize_bicubic_u8)", tmp_bytes, kStaticTmpBytes);
+    DeviceGuard g(device);
+    CID_REQUIRE(g.ok, "cannot select CUDA device %d", device);
+    uint8_t* scratch = nullptr;
+    if (static_scratch_ptr(device, &scratch)) return 1;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int* boundsH = reinterpret_cast<const int*>(scratch);
+    const int* kkH = boundsH + 2 * out_w;
+    const int* boundsV = boundsH + static_cast<size_t>(out_w) * (2 + ksH);
+    const int* kkV = boundsV + 2 * out_h;
+    uint8_t* tmp = scratch + kStaticTableBytes;
+    // nothing in the array has to start at zero: the first kernel rewrites every table entry the passes read, the
+    // horizontal pass every intermediate byte the vertical pass reads
+    static_coeffs_kernel<<<(out_w + out_h + 127) / 128, 128, 0, st>>>(in_w, out_w, in_h, out_h);
+    CID_CHECK_CUDA(cudaGetLastError());
+    {
+        const size_t total = tmp_bytes;
+        resample_u8_kernel<true><<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(
+            in, tmp, B, in_h, in_w, in_h, out_w, C, boundsH, kkH, ksH);
+        CID_CHECK_CUDA(cudaGetLastError());
+    }
+    {
+        const size_t total = static_cast<size_t>(B) * out_h * out_w * C;
+        CID_REQUIRE(total + 255 < (1ull << 39), "resize: output too large");
+        resample_u8_kernel<false><<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(
+            tmp, out, B, in_h, out_w, out_h, out_w, C, boundsV, kkV, ksV);
+        CID_CHECK_CUDA(cudaGetLastError());
+    }
+    return 0;
+}
 
 int cid_resize_bicubic_u8(cid_handle h, const uint8_t* in, uint8_t* out, uint8_t* tmp, int B, int in_h, int in_w,
                           int out_h, int out_w, int C, void* stream) {

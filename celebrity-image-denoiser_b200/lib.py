@@ -47,6 +47,8 @@ _SIGNATURES = {
                                                 C.c_double, C.c_void_p, C.c_int64, C.c_uint64, C.c_uint64, C.c_void_p]),
     "cid_resize_bicubic_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                         C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "cid_resize_bicubic_u8_static": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                                               C.c_int, C.c_int, C.c_void_p]),
     "cid_normalize_u8_to_f32_nchw": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                                C.c_float, C.c_float, C.c_void_p]),
     "cid_kernel_launches": (C.c_int64, [C.c_void_p]),

@@ -174,6 +174,24 @@ int cid_noise_salt_pepper_unit_u8(cid_handle h, const uint8_t* in, uint8_t* out,
 int cid_resize_bicubic_u8(cid_handle h, const uint8_t* in, uint8_t* out, uint8_t* tmp, int B, int in_h, int in_w,
                           int out_h, int out_w, int C, void* stream);
 
+/* No counterpart in the reference: added for callers that cannot allocate
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc). The same two-pass resize as
+ * cid_resize_bicubic_u8 (bit-identical output), without a handle and without any allocation, host or device: the
+ * coefficient tables are computed on the device, and they and the intermediate image of the horizontal pass live in one
+ * static device array inside the library (CID_RESIZE_STATIC_TABLE_BYTES + CID_RESIZE_STATIC_TMP_BYTES, held by every
+ * GPU that loads the library until the process exits). Runs on CUDA device `device`, on `stream`. Limits, checked
+ * before anything is launched (non-zero return, reason in cid_last_error):
+ *   B*in_h*out_w*C                                      <= CID_RESIZE_STATIC_TMP_BYTES
+ *   4*(out_w*(2 + ksize_w) + out_h*(2 + ksize_h))       <= CID_RESIZE_STATIC_TABLE_BYTES,
+ *                                                          ksize = 2*ceil(2*max(in/out, 1)) + 1 per axis
+ * Every call shares the array and nothing in it needs clearing (each call rewrites all it reads), but two calls that
+ * overlap on the GPU (different streams, or host threads, of one process on one device) race: keep
+ * calls to this entry point on one stream, or order them with events. */
+#define CID_RESIZE_STATIC_TABLE_BYTES (256u << 10)
+#define CID_RESIZE_STATIC_TMP_BYTES (8u << 20)
+int cid_resize_bicubic_u8_static(int device, const uint8_t* in, uint8_t* out, int B, int in_h, int in_w, int out_h,
+                                 int out_w, int C, void* stream);
+
 /* Replaces ToTensor + Normalize(mean, std) (backend/app.py:401-406, denoisegan_eval.py:76-79):
  * u8 NHWC [B,H,W,3] -> fp32 NCHW [B,3,H,W], (v/255 - mean)/std, each step rounded in fp32 as
  * torch does. (The u8 forward above fuses this into its first layer; this entry point exists for
