@@ -61,39 +61,56 @@ __device__ __forceinline__ float block_sum(float v, float* red /* >= 32 floats *
 // wgrad_umma.cuh (T = 1, no halo); wg27_scatter_kernel then adds the 64 x 27 result into the gradient tensor.
 // ---------------------------------------------------------------------------------------------------------------------
 // zero_upper: also write the 32 always-zero upper channels (needed once per workspace use, see wgrad_edge).
+// A block owns a 32 x 4 pixel tile: it stages the tile's 34 x 6 x 3 source window (zero outside the image) in shared
+// memory with coalesced loads, then every thread gathers its pixel's 27 values from there - no per-tap bounds checks or
+// 64-bit address arithmetic (the one-thread-one-pixel form with 27 guarded global loads was instruction-issue bound:
+// 69 % issue-active at 0.18 of HBM peak, `profiles/r02t_train_mem`).
+constexpr int kI2cTx = 32, kI2cTy = 4;
 __global__ void __launch_bounds__(128) im2col3_kernel(const float* v3, int v3_nchw, int sign, __nv_bfloat16* u, int B, int H,
                                                       int W, int zero_upper) {
     // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
     pdl_launch_dependents();
     pdl_wait();
-    const size_t total = static_cast<size_t>(B) * H * W;
-    const size_t pix = static_cast<size_t>(blockIdx.x) * 128 + threadIdx.x;
-    if (pix >= total) return;
-    const int x = static_cast<int>(pix % W);
-    const int y = static_cast<int>((pix / W) % H);
-    const int b = static_cast<int>(pix / (static_cast<size_t>(W) * H));
-    float f[32];
+    constexpr int SW = kI2cTx + 2, SH = kI2cTy + 2;
+    __shared__ float s[3][SH][SW];
+    const uint32_t tiles_x = (W + kI2cTx - 1) / kI2cTx, tiles_y = (H + kI2cTy - 1) / kI2cTy;
+    const uint32_t tx = blockIdx.x % tiles_x, tt = blockIdx.x / tiles_x;
+    const uint32_t ty = tt % tiles_y, b = tt / tiles_y;
+    const int x0 = static_cast<int>(tx) * kI2cTx, y0 = static_cast<int>(ty) * kI2cTy;
+    for (int i = threadIdx.x; i < 3 * SH * SW; i += 128) {
+        const int r = i / (3 * SW), j = i - r * (3 * SW);
+        const int ci = v3_nchw ? j / SW : j % 3, px = v3_nchw ? j % SW : j / 3;
+        const int yy = y0 - 1 + r, xx = x0 - 1 + px;
+        float v = 0.f;
+        if (yy >= 0 && yy < H && xx >= 0 && xx < W)
+            v = v3_nchw ? __ldg(v3 + ((static_cast<size_t>(b) * 3 + ci) * H + yy) * W + xx)
+                        : __ldg(v3 + ((static_cast<size_t>(b) * H + yy) * W + xx) * 3 + ci);
+        s[ci][r][px] = v;
+    }
+    __syncthreads();
+    // a thread owns ONE 16-byte chunk (8 of the 27 (ci, tap) channels) of the pixels of one tile column: four consecutive
+    // lanes write the 64 contiguous bytes of a pixel, so every 32-byte sector leaves the SM fully written
+    const int chunk = threadIdx.x & 3, lx = threadIdx.x >> 2;
+    int off[8];  // offset of channel 8 * chunk + e in the staged window, relative to the pixel's own slot; -1 = zero
 #pragma unroll
-    for (int i = 0; i < 32; ++i) f[i] = 0.f;
+    for (int e = 0; e < 8; ++e) {
+        const int idx = 8 * chunk + e, ci = idx / 9, tap = idx - 9 * ci, ky = tap / 3, kx = tap - 3 * ky;
+        off[e] = idx < 27 ? (ci * SH + 1 + sign * (ky - 1)) * SW + 1 + sign * (kx - 1) : -1;
+    }
+    const float* sf = &s[0][0][0];
+    const int x = x0 + lx;
+    if (x >= W) return;
 #pragma unroll
-    for (int ky = 0; ky < 3; ++ky)
+    for (int ly = 0; ly < kI2cTy; ++ly) {
+        const int y = y0 + ly;
+        if (y >= H) break;
+        const int base = ly * SW + lx;
+        float f[8];
 #pragma unroll
-        for (int kx = 0; kx < 3; ++kx) {
-            const int yy = y + sign * (ky - 1), xx = x + sign * (kx - 1);
-            if (yy < 0 || yy >= H || xx < 0 || xx >= W) continue;
-#pragma unroll
-            for (int ci = 0; ci < 3; ++ci)
-                f[ci * 9 + ky * 3 + kx] = v3_nchw ? __ldg(v3 + ((static_cast<size_t>(b) * 3 + ci) * H + yy) * W + xx)
-                                                  : __ldg(v3 + ((static_cast<size_t>(b) * H + yy) * W + xx) * 3 + ci);
-        }
-    __nv_bfloat16* dst = u + pix * 64;
-#pragma unroll
-    for (int j = 0; j < 4; ++j)
-        st_global_v4(dst + j * 8, pack_bf16x2(f[8 * j], f[8 * j + 1]), pack_bf16x2(f[8 * j + 2], f[8 * j + 3]),
-                     pack_bf16x2(f[8 * j + 4], f[8 * j + 5]), pack_bf16x2(f[8 * j + 6], f[8 * j + 7]));
-    if (zero_upper) {
-#pragma unroll
-        for (int j = 4; j < 8; ++j) st_global_v4(dst + j * 8, 0u, 0u, 0u, 0u);
+        for (int e = 0; e < 8; ++e) f[e] = off[e] >= 0 ? sf[base + off[e]] : 0.f;
+        __nv_bfloat16* dst = u + ((static_cast<size_t>(b) * H + y) * W + x) * 64 + chunk * 8;
+        st_global_v4(dst, pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+        if (zero_upper) st_global_v4(dst + 32, 0u, 0u, 0u, 0u);
     }
 }
 
@@ -215,43 +232,44 @@ __global__ void __launch_bounds__(256) colsum_kernel(const ZT* v, size_t P, int 
 //   dz[p][c] = (e[p][c] > 0) ? gskip[p][c] + (p is the first arg-max of its 2x2 window ? gpool[p/2][c] : 0) : 0
 // e and gskip live in channel slices of the concat buffers (stride cs, first channel c0).
 // ---------------------------------------------------------------------------------------------------------------------
-// One thread = one 2x2 window x 8 channels: 4 e + 4 gskip + 1 gpool loads, 4 stores (H, W even).
+// One thread = one 2x2 window x 4 channels: 4 e + 4 gskip + 1 gpool 8-byte loads, 4 stores (H, W even). Four channels
+// (not eight) per thread keep the kernel at ~40 registers, i.e. 5+ blocks per SM instead of 2: the kernel is a pure
+// stream and was waiting on its own loads with a quarter of the warps resident. 32-bit index arithmetic (the host checks
+// that the item count fits).
 __global__ void __launch_bounds__(256) poolbwd_kernel(const __nv_bfloat16* e, const __nv_bfloat16* gskip, int cs, int c0,
                                                       const __nv_bfloat16* gpool, __nv_bfloat16* dz, int B, int H, int W, int C) {
     // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
     pdl_launch_dependents();
     pdl_wait();
-    const int chunks = C >> 3;
-    const int Hp = H >> 1, Wp = W >> 1;
-    const size_t total = static_cast<size_t>(B) * Hp * Wp * chunks;
-    const size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
+    const uint32_t chunks = static_cast<uint32_t>(C) >> 2;
+    const uint32_t Hp = static_cast<uint32_t>(H) >> 1, Wp = static_cast<uint32_t>(W) >> 1;
+    const uint32_t total = static_cast<uint32_t>(B) * Hp * Wp * chunks;
+    const uint32_t i = blockIdx.x * 256u + threadIdx.x;
     if (i >= total) return;
-    const int ck = static_cast<int>(i % chunks);
-    const size_t pp = i / chunks;  // pooled pixel
-    const int xp = static_cast<int>(pp % Wp);
-    const int yp = static_cast<int>((pp / Wp) % Hp);
-    const size_t b = pp / (static_cast<size_t>(Wp) * Hp);
-    size_t q[4];
-    uint4 ev[4], gv[4];
+    const uint32_t ck = i % chunks, pp = i / chunks;  // pooled pixel
+    const uint32_t xp = pp % Wp, t = pp / Wp;
+    const uint32_t yp = t % Hp, b = t / Hp;
+    const size_t q0 = (static_cast<size_t>(b) * H + 2 * yp) * W + 2 * xp;
+    size_t q[4] = {q0, q0 + 1, q0 + W, q0 + W + 1};
+    uint2 ev[4], gv[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-        q[j] = (b * H + 2 * yp + (j >> 1)) * W + 2 * xp + (j & 1);
-        ev[j] = __ldg(reinterpret_cast<const uint4*>(e + q[j] * cs + c0 + ck * 8));
-        gv[j] = __ldg(reinterpret_cast<const uint4*>(gskip + q[j] * cs + c0 + ck * 8));
+        ev[j] = __ldg(reinterpret_cast<const uint2*>(e + q[j] * cs + c0 + ck * 4));
+        gv[j] = __ldg(reinterpret_cast<const uint2*>(gskip + q[j] * cs + c0 + ck * 4));
     }
-    const uint4 gp = __ldg(reinterpret_cast<const uint4*>(gpool + pp * C + ck * 8));
-    const uint32_t gpw[4] = {gp.x, gp.y, gp.z, gp.w};
-    uint32_t o[4][4];
+    const uint2 gp = __ldg(reinterpret_cast<const uint2*>(gpool + static_cast<size_t>(pp) * C + ck * 4));
+    uint32_t o[4][2];
 #pragma unroll
-    for (int wi = 0; wi < 4; ++wi) {
+    for (int wi = 0; wi < 2; ++wi) {
         float r[4][2];
+        const uint32_t gpw = wi ? gp.y : gp.x;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             float ej[4], gj[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                const uint32_t w = wi == 0 ? ev[j].x : wi == 1 ? ev[j].y : wi == 2 ? ev[j].z : ev[j].w;
-                const uint32_t g = wi == 0 ? gv[j].x : wi == 1 ? gv[j].y : wi == 2 ? gv[j].z : gv[j].w;
+                const uint32_t w = wi ? ev[j].y : ev[j].x;
+                const uint32_t g = wi ? gv[j].y : gv[j].x;
                 ej[j] = h ? bf16_hi(w) : bf16_lo(w);
                 gj[j] = h ? bf16_hi(g) : bf16_lo(g);
             }
@@ -260,7 +278,7 @@ __global__ void __launch_bounds__(256) poolbwd_kernel(const __nv_bfloat16* e, co
 #pragma unroll
             for (int j = 3; j >= 0; --j)
                 if (ej[j] == mx) first = j;
-            const float gpv = h ? bf16_hi(gpw[wi]) : bf16_lo(gpw[wi]);
+            const float gpv = h ? bf16_hi(gpw) : bf16_lo(gpw);
 #pragma unroll
             for (int j = 0; j < 4; ++j) r[j][h] = ej[j] > 0.f ? gj[j] + (first == j ? gpv : 0.f) : 0.f;
         }
@@ -268,7 +286,8 @@ __global__ void __launch_bounds__(256) poolbwd_kernel(const __nv_bfloat16* e, co
         for (int j = 0; j < 4; ++j) o[j][wi] = pack_bf16x2(r[j][0], r[j][1]);
     }
 #pragma unroll
-    for (int j = 0; j < 4; ++j) st_global_v4(dz + q[j] * C + ck * 8, o[j][0], o[j][1], o[j][2], o[j][3]);
+    for (int j = 0; j < 4; ++j)
+        *reinterpret_cast<uint2*>(dz + q[j] * C + ck * 4) = make_uint2(o[j][0], o[j][1]);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -327,8 +346,20 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const ZT* z, __nv_bfloat1
     }
 }
 
+// four consecutive channels of a bf16 or fp32 NHWC tensor as floats
+__device__ __forceinline__ void load4(const __nv_bfloat16* p, float (&f)[4]) {
+    const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
+    f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+}
+__device__ __forceinline__ void load4(const float* p, float (&f)[4]) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(p));
+    f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w;
+}
+
 // dY = dA * lrelu'(y); sums[c] += {sum dY, sum dY * xhat}. dA comes from a tensor (da) or, for the layer under the
-// average pool, is broadcast from dpool[b][c] (already divided by H*W). 8 channels per thread.
+// average pool, is broadcast from dpool[b][c] (already divided by H*W). 4 channels per thread and four pixels in flight:
+// with 8 channels the per-channel constants alone took 48 registers and two blocks per SM could not cover the load
+// latency of this pure stream (0.43 of HBM peak, `profiles/r02t_train_mem`).
 template <typename ZT>
 __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const ZT* z, const __nv_bfloat16* da,
                                                             const float* dpool, size_t P, size_t hw, int C,
@@ -337,43 +368,44 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const ZT* z, const _
     // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
     pdl_launch_dependents();
     pdl_wait();
-    __shared__ float red[256 * 8];
-    __shared__ float red2[256 * 8];
-    const int chunks = C >> 3, rpi = 256 / chunks;
+    __shared__ float red[256 * 4];
+    __shared__ float red2[256 * 4];
+    const int chunks = C >> 2, rpi = 256 / chunks;
     const int ck = threadIdx.x % chunks, rg = threadIdx.x / chunks;
     const size_t p0 = static_cast<size_t>(blockIdx.x) * ppb, p1 = min(P, p0 + ppb);
-    const int c8 = ck * 8;
-    float mean[8], istd[8], ga[8], be[8], s[8], q[8];
+    const int c4 = ck * 4;
+    float mean[4], istd[4], ga[4], be[4], s[4], q[4];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        mean[j] = stats[2 * (c8 + j)]; istd[j] = stats[2 * (c8 + j) + 1];
-        ga[j] = gamma[c8 + j]; be[j] = beta[c8 + j];
+    for (int j = 0; j < 4; ++j) {
+        mean[j] = stats[2 * (c4 + j)]; istd[j] = stats[2 * (c4 + j) + 1];
+        ga[j] = gamma[c4 + j]; be[j] = beta[c4 + j];
         s[j] = 0.f; q[j] = 0.f;
     }
-#pragma unroll 2
-    for (size_t pix = p0 + rg; pix < p1; pix += rpi) {
-        float zz[8], dd[8];
-        load8(z + pix * C + c8, zz);
-        if (da) {
-            load8(da + pix * C + c8, dd);
-        } else {
-            const size_t b = pix / hw;
+    if (rg < rpi) {  // C / 4 divides 256 for the discriminator's 64 / 128 channels: every thread has a row group
+#pragma unroll 4
+        for (size_t pix = p0 + rg; pix < p1; pix += rpi) {
+            float zz[4], dd[4];
+            load4(z + pix * C + c4, zz);
+            if (da) {
+                load4(da + pix * C + c4, dd);
+            } else {
+                const size_t b = pix / hw;
+                load4(dpool + b * C + c4, dd);
+            }
 #pragma unroll
-            for (int j = 0; j < 8; ++j) dd[j] = dpool[b * C + c8 + j];
+            for (int j = 0; j < 4; ++j) {
+                const float xh = (zz[j] - mean[j]) * istd[j];
+                const float yv = ga[j] * xh + be[j];
+                const float dy = yv > 0.f ? dd[j] : dd[j] * slope;
+                s[j] += dy;
+                q[j] = fmaf(dy, xh, q[j]);
+            }
         }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const float xh = (zz[j] - mean[j]) * istd[j];
-            const float yv = ga[j] * xh + be[j];
-            const float dy = yv > 0.f ? dd[j] : dd[j] * slope;
-            s[j] += dy;
-            q[j] = fmaf(dy, xh, q[j]);
+        for (int j = 0; j < 4; ++j) {
+            red[(rg * chunks + ck) * 4 + j] = s[j];
+            red2[(rg * chunks + ck) * 4 + j] = q[j];
         }
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        red[(rg * chunks + ck) * 8 + j] = s[j];
-        red2[(rg * chunks + ck) * 8 + j] = q[j];
     }
     __syncthreads();
     if (threadIdx.x < C) {

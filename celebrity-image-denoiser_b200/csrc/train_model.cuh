@@ -389,9 +389,10 @@ static int wgrad(cid_train* t, int geom, const void* A, int a_C, int m_ch, const
     return 1;
 }
 
-// pixels per block of the column reductions: ~8 blocks per SM (small tensors were latency-bound with few blocks)
-static int reduce_ppb(const cid_train* t, size_t P) {
-    const size_t target = static_cast<size_t>(t->num_sms) * 8;
+// pixels per block of the column reductions: ONE wave of `per_sm` resident blocks per SM (per_sm = what the kernel's
+// registers allow: a second, partly filled wave costs a whole block time; small tensors were latency-bound with few blocks)
+static int reduce_ppb(const cid_train* t, size_t P, int per_sm = 8) {
+    const size_t target = static_cast<size_t>(t->num_sms) * per_sm;
     size_t ppb = (P + target - 1) / target;
     ppb = (ppb + 31) / 32 * 32;
     return static_cast<int>(std::min<size_t>(std::max<size_t>(ppb, 64), 4096));
@@ -410,7 +411,9 @@ static int colsum(cid_train* t, const void* v, size_t P, int cs, int c0, int C, 
 static int wgrad_edge(cid_train* t, const void* v64, const float* v3, int v3_nchw, int sign, float* out, int out_mode,
                       void* ubuf, int B, int H, int W, cudaStream_t st, float* bias_out = nullptr) {
     const size_t P = static_cast<size_t>(B) * H * W;
-    launch_k(t->g->pdl, im2col3_kernel, static_cast<unsigned>((P + 127) / 128), 128, 0, st, v3, v3_nchw, sign, static_cast<__nv_bfloat16*>(ubuf), B, H, W, t->u_upper_zeroed ? 0 : 1);
+    const size_t i2c_tiles = static_cast<size_t>(B) * ((H + kI2cTy - 1) / kI2cTy) * ((W + kI2cTx - 1) / kI2cTx);
+    CID_REQUIRE(i2c_tiles < (1ull << 31), "im2col3: too many tiles");
+    launch_k(t->g->pdl, im2col3_kernel, static_cast<unsigned>(i2c_tiles), 128, 0, st, v3, v3_nchw, sign, static_cast<__nv_bfloat16*>(ubuf), B, H, W, t->u_upper_zeroed ? 0 : 1);
     t->u_upper_zeroed = true;  // channels 32..63 of U stay zero for the rest of this iteration (4 launches share the buffer)
     CID_CHECK_CUDA(cudaGetLastError());
     float* scratch = t->fsc + FS_WG27;
@@ -746,7 +749,7 @@ static int bn_backward(const TrainRun& r, int l, const void* z, const void* da, 
     const float* gamma = train_ptr(t, bn + ".weight", 0);
     const float* beta = train_ptr(t, bn + ".bias", 0);
     CID_CHECK_CUDA(cudaMemsetAsync(sums, 0, 256 * 8, r.st));
-    const int ppb = reduce_ppb(t, P);
+    const int ppb = reduce_ppb(t, P, 5);  // 48 registers x 256 threads: 5 blocks per SM
     launch_k(t->g->pdl, bn_bwd_reduce_kernel<float>, static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, r.st, 
         static_cast<const float*>(z), static_cast<const __nv_bfloat16*>(da), t->fsc + FS_DPOOL, P, hw, C, stats, gamma,
         beta, 0.2f, sums, ppb);
@@ -852,7 +855,7 @@ static int g_backward_layers(const TrainRun& r, const float* noisy) {
     auto gw = [&](int l) { return train_ptr(t, std::string("generator.") + kLayers[l].name + ".weight", 1); };
     auto gb = [&](int l) { return train_ptr(t, std::string("generator.") + kLayers[l].name + ".bias", 1); };
     auto pool_bwd = [&](int cat, int C, int lv, int gcat, int gpool, int dz) {
-        const size_t total = r.pixels(lv) / 4 * (C / 8);  // one thread per 2x2 window x 8 channels
+        const size_t total = r.pixels(lv) / 4 * (C / 4);  // one thread per 2x2 window x 4 channels (< 2^32: workspace-bound)
         launch_k(t->g->pdl, poolbwd_kernel, static_cast<unsigned>((total + 255) / 256), 256, 0, r.st, 
             static_cast<const __nv_bfloat16*>(r.gbuf(cat)), static_cast<const __nv_bfloat16*>(r.tbuf(gcat)), 2 * C, C,
             static_cast<const __nv_bfloat16*>(r.tbuf(gpool)), static_cast<__nv_bfloat16*>(r.tbuf(dz)), B, H >> lv, W >> lv, C);
