@@ -361,10 +361,10 @@ __device__ __forceinline__ void load4(const float* p, float (&f)[4]) {
 // with 8 channels the per-channel constants alone took 48 registers and two blocks per SM could not cover the load
 // latency of this pure stream (0.43 of HBM peak, `profiles/r02t_train_mem`).
 template <typename ZT>
-__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const ZT* z, const __nv_bfloat16* da,
+__global__ void __launch_bounds__(256, 5) bn_bwd_reduce_kernel(const ZT* z, const __nv_bfloat16* da,
                                                             const float* dpool, size_t P, size_t hw, int C,
                                                             const float* stats, const float* gamma, const float* beta,
-                                                            float slope, double* sums, int ppb) {
+                                                            float slope, double* sums, int ppb, int reps) {
     // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
     pdl_launch_dependents();
     pdl_wait();
@@ -415,23 +415,31 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const ZT* z, const _
             a += red[r * C + cc];
             b2 += red2[r * C + cc];
         }
-        atomicAdd(sums + cc, static_cast<double>(a));
-        atomicAdd(sums + C + cc, static_cast<double>(b2));
+        // the blocks of the one wave finish together: `reps` replicas of the 2 C sums (summed by the finalize kernel) keep
+        // the same-address depth of the double atomics at blocks / reps
+        double* dst = sums + static_cast<size_t>(blockIdx.x % reps) * (2 * C);
+        atomicAdd(dst + cc, static_cast<double>(a));
+        atomicAdd(dst + C + cc, static_cast<double>(b2));
     }
 }
 
 // per-channel table of the backward apply: with xh = (z - mean) * istd, y = z * a2 + b2, dy = dA * lrelu'(y):
 //   dz = gamma * istd * (dy - sum_dy / n - xh * sum_dyxh / n) = k0 * dy - c1 - z * c2
 // btab[c] = {a2, b2, k0, c1, c2}; optionally the gradients of gamma / beta: += {sum dY xhat, sum dY}
-__global__ void bn_bwd_finalize_kernel(const double* sums, int C, double n, const float* stats, const float* gamma,
+__global__ void bn_bwd_finalize_kernel(const double* sums_rep, int reps, int C, double n, const float* stats, const float* gamma,
                                        const float* beta, float* btab, float* ggamma, float* gbeta) {
     // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
     pdl_launch_dependents();
     pdl_wait();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
+    double sums[2] = {0.0, 0.0};  // {sum dY, sum dY xhat} of channel c over the replicas
+    for (int r = 0; r < reps; ++r) {
+        sums[0] += sums_rep[r * 2 * C + c];
+        sums[1] += sums_rep[r * 2 * C + C + c];
+    }
     const float mean = stats[2 * c], istd = stats[2 * c + 1], ga = gamma[c];
-    const float m_dy = static_cast<float>(sums[c] / n), m_dyx = static_cast<float>(sums[C + c] / n);
+    const float m_dy = static_cast<float>(sums[0] / n), m_dyx = static_cast<float>(sums[1] / n);
     const float k0 = ga * istd;
     btab[5 * c + 0] = ga * istd;
     btab[5 * c + 1] = beta[c] - ga * istd * mean;
@@ -439,8 +447,8 @@ __global__ void bn_bwd_finalize_kernel(const double* sums, int C, double n, cons
     btab[5 * c + 3] = k0 * (m_dy - m_dyx * mean * istd);
     btab[5 * c + 4] = k0 * m_dyx * istd;
     if (ggamma) {
-        gbeta[c] += static_cast<float>(sums[c]);
-        ggamma[c] += static_cast<float>(sums[C + c]);
+        gbeta[c] += static_cast<float>(sums[0]);
+        ggamma[c] += static_cast<float>(sums[1]);
     }
 }
 

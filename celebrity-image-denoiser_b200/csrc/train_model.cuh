@@ -89,7 +89,8 @@ struct cid_train {
 namespace cid {
 
 // double scratch layout
-enum { DS_BN = 0 /* 3 layers x 2 x 128 */, DS_BWD = 768 /* 3 x 2 x 128 */, DS_LOSS = 1536 /* 8 */, DS_COUNT = 1544 };
+constexpr int kBwdReps = 8;  // replicas of the BatchNorm-backward sums (see bn_bwd_reduce_kernel)
+enum { DS_BN = 0 /* 3 layers x 2 x 128 */, DS_BWD = 768 /* 3 x kBwdReps x 2 x 128 */, DS_LOSS = 768 + 3 * kBwdReps * 256 /* 8 */, DS_COUNT = DS_LOSS + 8 };
 // float scratch layout
 enum { FS_STATS = 0 /* 3 x 256 */, FS_POOLED = 768 /* B*128 */, FS_DPOOL = 768 + 128 * 1024, FS_PROBS = 768 + 2 * 128 * 1024,
        FS_TAB = FS_PROBS + 1024 /* 3 x 256: forward affine table */, FS_BTAB = FS_TAB + 768 /* 3 x 5 x 128 */,
@@ -743,18 +744,24 @@ static int bn_backward(const TrainRun& r, int l, const void* z, const void* da, 
     const int C = kDCout[l];
     const size_t P = r.pixels(lv);
     const size_t hw = static_cast<size_t>(r.H >> lv) * (r.W >> lv);
-    double* sums = t->dsc + DS_BWD + (l - 1) * 256;
+    double* sums = t->dsc + DS_BWD + (l - 1) * (kBwdReps * 256);
     const float* stats = t->fsc + FS_STATS + (l - 1) * 256;
     const std::string bn = "discriminator.model." + std::to_string(kDBnIdx[l]);
     const float* gamma = train_ptr(t, bn + ".weight", 0);
     const float* beta = train_ptr(t, bn + ".bias", 0);
-    CID_CHECK_CUDA(cudaMemsetAsync(sums, 0, 256 * 8, r.st));
-    const int ppb = reduce_ppb(t, P, 5);  // 48 registers x 256 threads: 5 blocks per SM
+    CID_CHECK_CUDA(cudaMemsetAsync(sums, 0, kBwdReps * 256 * 8, r.st));
+    static int per_sm = 0;  // resident blocks per SM of the reduce kernel (one wave: see reduce_ppb)
+    if (per_sm == 0) {
+        int nb = 0;
+        CID_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, bn_bwd_reduce_kernel<float>, 256, 0));
+        per_sm = std::max(nb, 1);
+    }
+    const int ppb = reduce_ppb(t, P, per_sm);
     launch_k(t->g->pdl, bn_bwd_reduce_kernel<float>, static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, r.st, 
         static_cast<const float*>(z), static_cast<const __nv_bfloat16*>(da), t->fsc + FS_DPOOL, P, hw, C, stats, gamma,
-        beta, 0.2f, sums, ppb);
+        beta, 0.2f, sums, ppb, kBwdReps);
     float* btab = t->fsc + FS_BTAB + (l - 1) * 640;
-    launch_k(t->g->pdl, bn_bwd_finalize_kernel, 1, 128, 0, r.st, sums, C, static_cast<double>(P), stats, gamma, beta, btab,
+    launch_k(t->g->pdl, bn_bwd_finalize_kernel, 1, 128, 0, r.st, sums, kBwdReps, C, static_cast<double>(P), stats, gamma, beta, btab,
                                                 param_grads ? train_ptr(t, bn + ".weight", 1) : nullptr,
                                                 param_grads ? train_ptr(t, bn + ".bias", 1) : nullptr);
     const size_t n8 = P * C / 8;
