@@ -565,8 +565,8 @@ static int run_layers(cid_ctx* c, cid_plan* pl, int nb, const IoSpec& io, cudaSt
     {  // L0 down1.0 (+ Pad / ToTensor / Normalize) -> a0
         const FirstParams fp = make_first_params(c, pl, nb, io);
         if (!(c->attr_done & (1u << 30))) {
-            CID_CHECK_CUDA(cudaFuncSetAttribute(first_conv_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFirstSmem));
-            CID_CHECK_CUDA(cudaFuncSetAttribute(first_conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFirstSmem));
+            CID_CHECK_CUDA(cudaFuncSetAttribute(first_conv_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFirstSmemMask));
+            CID_CHECK_CUDA(cudaFuncSetAttribute(first_conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFirstSmemMask));
             c->attr_done |= (1u << 30);
         }
         const int grid = std::min(fp.m_tiles, c->num_sms * kFirstCtasPerSm);

@@ -42,6 +42,10 @@ constexpr int kFirstStageBytes = kFirstPlane;
 constexpr int kFirstWBytes = 9 * 2 * 64 * 16;  // [tap][k chunk][cout][8 bf16]
 constexpr int kFirstOutBufs = 2;               // staged output slabs ([128 px][64 ch] bf16, SW128) in flight
 constexpr int kFirstSmem = 1024 + kFirstOutBufs * 16384 + kFirstWBytes + kFirstStages * kFirstStageBytes + 1024 + 32 + 256;
+// training (FirstParams::mask): the ReLU mask tiles ([128 px][64 ch] bf16, two in flight) sit behind everything else
+constexpr int kFirstMaskOff = (kFirstOutBufs * 16384 + kFirstWBytes + kFirstStages * kFirstStageBytes + 264 * 4 + 256 + 1023) / 1024 * 1024;
+constexpr int kFirstSmemMask = 1024 + kFirstMaskOff + 2 * 16384;
+static_assert(kFirstMaskOff + 1024 >= kFirstSmem - 1024 && kFirstCtasPerSm * (kFirstSmemMask + 1024) <= 227 * 1024, "first conv smem");
 
 struct FirstParams {
     int B, H, W;          // network-input dims (after padding to a multiple of 4)
@@ -254,12 +258,55 @@ first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParam
         const bool issuer = (warp == 5 && lane == 0);
         (void)yl; (void)xl;
         TileWalk tw(p.tiles_x, p.tiles_y, mt_begin);
+        // ReLU mask (training): every thread copies its own pixel's 128 bytes of the NEXT tile into shared memory with
+        // cp.async while it works on the current one (a synchronous load per tile cost ~1 us of exposed latency each)
+        uint8_t* m_smem = smem + kFirstMaskOff;
+        auto mask_fetch = [&](int tx, int ty, int b, uint32_t slot) {
+            // coalesced: 8 lanes copy the 8 chunks of one pixel row, a warp instruction covers 4 whole 128-byte lines
+            const int c = lane & 7;
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                const int r = q * 32 + it * 4 + (lane >> 3);
+                const int yy = ty * 16 + (r >> 3), xx = tx * 8 + (r & 7);
+                if (b < p.B && yy < p.H && xx < p.W)
+                    cp_async_16(smem_u32(m_smem + slot * 16384 + r * 128 + ((c ^ (r & 7)) << 4)),
+                                p.mask + ((static_cast<size_t>(b) * p.H + yy) * p.W + xx) * 64 + c * 8);
+            }
+            cp_async_commit();
+        };
+        // ... and pulls its line of the tile kMaskAhead tiles ahead into L2 (one tile of cp.async distance does not
+        // cover the DRAM latency; a third 16 KB buffer does not fit beside two resident CTAs)
+        constexpr int kMaskAhead = 4;
+        TileWalk twp(p.tiles_x, p.tiles_y, mt_begin);
+        int pf = mt_begin;
+        auto mask_prefetch_l2 = [&]() {
+            if (pf < mt_end) {
+                const int yy = twp.ty * 16 + yl, xx = twp.tx * 8 + xl;
+                if (twp.b < p.B && yy < p.H && xx < p.W)
+                    prefetch_l2(p.mask + ((static_cast<size_t>(twp.b) * p.H + yy) * p.W + xx) * 64);
+                twp.next(p.tiles_x, p.tiles_y);
+                ++pf;
+            }
+        };
+        if (p.mask != nullptr) {
+            for (int k = 0; k < kMaskAhead; ++k) mask_prefetch_l2();
+            if (mt_begin < mt_end) mask_fetch(tw.tx, tw.ty, tw.b, 0);
+        }
         for (int mt = mt_begin; mt < mt_end; ++mt) {
             const int tx = tw.tx, ty = tw.ty, b = tw.b;
             tw.next(p.tiles_x, p.tiles_y);
+            if (p.mask != nullptr) {
+                mask_prefetch_l2();
+                if (mt + 1 < mt_end) mask_fetch(tw.tx, tw.ty, tw.b, (acc_it + 1) & 1);
+                else cp_async_commit();
+            }
             const uint32_t buf = acc_it & 1;
             mbar_wait(&acc_full[buf], (acc_it >> 1) & 1);
             tc_fence_after();
+            if (p.mask != nullptr) {  // this tile's mask has landed (copied by the lanes of this warp)
+                cp_async_wait<1>();
+                __syncwarp();
+            }
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * N;
             const uint32_t ob = acc_it % kFirstOutBufs;
             // the TMA store that used this slab kFirstOutBufs tiles ago must have finished reading it
@@ -291,11 +338,10 @@ first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParam
                 if (p.mask != nullptr) {
                     const int yy = ty * 16 + yl, xx = tx * 8 + xl;
                     if (b < p.B && yy < p.H && xx < p.W) {
-                        const uint4* m4 = reinterpret_cast<const uint4*>(
-                            p.mask + ((static_cast<size_t>(b) * p.H + yy) * p.W + xx) * 64 + ch * 32);
+                        const uint8_t* mrow = m_smem + (acc_it & 1) * 16384 + row * 128;
 #pragma unroll
                         for (int i = 0; i < 4; ++i) {
-                            const uint4 m = __ldg(m4 + i);
+                            const uint4 m = *reinterpret_cast<const uint4*>(mrow + (((ch * 4 + i) ^ (row & 7)) << 4));
                             const uint32_t w[4] = {m.x, m.y, m.z, m.w};
 #pragma unroll
                             for (int e = 0; e < 4; ++e) {

@@ -685,7 +685,7 @@ static int d_forward(const TrainRun& r, const float* img) {
         fp.m_tiles = B * fp.tiles_x * fp.tiles_y;
         fp.w_packed = static_cast<const uint4*>(t->df_w[0]);
         fp.slope = 0.2f;
-        CID_CHECK_CUDA(cudaFuncSetAttribute(first_conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFirstSmem));
+        CID_CHECK_CUDA(cudaFuncSetAttribute(first_conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFirstSmemMask));
         const int grid = std::min(fp.m_tiles, t->num_sms * kFirstCtasPerSm);
         CID_CHECK_CUDA(launch_ex(t->g, first_conv_umma_kernel<false>, grid, kFirstThreads, kFirstSmem, r.st, 1, *tmO, fp));
         CID_CHECK_CUDA(cudaGetLastError());
@@ -887,7 +887,8 @@ static int g_backward_layers(const TrainRun& r, const float* noisy) {
         fp.slope = 1.f;
         fp.mask = static_cast<const __nv_bfloat16*>(r.gbuf(B_U1A));
         const int grid = std::min(fp.m_tiles, t->num_sms * kFirstCtasPerSm);
-        CID_CHECK_CUDA(launch_ex(t->g, first_conv_umma_kernel<false>, grid, kFirstThreads, kFirstSmem, r.st, 1, *tmO, fp));
+        CID_CHECK_CUDA(cudaFuncSetAttribute(first_conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFirstSmemMask));
+        CID_CHECK_CUDA(launch_ex(t->g, first_conv_umma_kernel<false>, grid, kFirstThreads, kFirstSmemMask, r.st, 1, *tmO, fp));
         CID_CHECK_CUDA(cudaGetLastError());
         t->launches++;
     }
