@@ -293,37 +293,45 @@ __global__ void __launch_bounds__(256) poolbwd_kernel(const __nv_bfloat16* e, co
 // ---------------------------------------------------------------------------------------------------------------------
 // Train-mode BatchNorm2d (eps 1e-5, momentum 0.1) + LeakyReLU(0.2)
 // ---------------------------------------------------------------------------------------------------------------------
-// stats[c] = {mean, invstd}; running statistics updated as torch does (unbiased variance)
-__global__ void bn_finalize_kernel(const double* dsum, const double* dsq, double n, int C, float eps, float momentum,
-                                   float* stats, float* running_mean, float* running_var, float* nbt, const float* gamma,
-                                   const float* beta, float* tab) {
-    // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
-    pdl_launch_dependents();
-    pdl_wait();
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
-    const double mean = dsum[c] / n;
-    double var = dsq[c] / n - mean * mean;
-    if (var < 0) var = 0;
-    stats[2 * c] = static_cast<float>(mean);
-    const float istd = static_cast<float>(1.0 / sqrt(var + static_cast<double>(eps)));
-    stats[2 * c + 1] = istd;
-    tab[2 * c] = gamma[c] * istd;
-    tab[2 * c + 1] = beta[c] - gamma[c] * istd * static_cast<float>(mean);
-    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * static_cast<float>(mean);
-    running_var[c] = (1.f - momentum) * running_var[c] + momentum * static_cast<float>(var * n / (n - 1.0));
-    if (c == 0) nbt[0] += 1.f;
-}
+// Batch statistics -> the affine table of the apply kernel. Every block of bn_apply_kernel derives the table for itself
+// from the double sums the producing conv's epilogue left (C <= 128 channels: one thread each, ~200 cycles - cheaper
+// than a one-block kernel and its launch boundary in the dependency chain); block 0 also publishes stats[c] =
+// {mean, invstd} for the backward kernels and updates the running statistics as torch does (unbiased variance).
+struct BnFwd {
+    const double *dsum, *dsq;  // per-channel sum and sum of squares over the n = B*H*W pixels
+    double n;
+    float eps, momentum;
+    float *stats, *running_mean, *running_var, *nbt;
+    const float *gamma, *beta;
+};
 
-// a = lrelu(z * a2 + b2) with tab[c] = {a2 = gamma * invstd, b2 = beta - gamma * mean * invstd}; 8 channels per thread
+// a = lrelu(z * a2 + b2) with {a2 = gamma * invstd, b2 = beta - gamma * mean * invstd}; 8 channels per thread
 constexpr int kBnIter = 8;  // items (8 channels of one pixel) per thread of the BatchNorm apply kernels
 
 template <typename ZT>
-__global__ void __launch_bounds__(256) bn_apply_kernel(const ZT* z, __nv_bfloat16* a, size_t P, int C, const float* tab,
+__global__ void __launch_bounds__(256) bn_apply_kernel(const ZT* z, __nv_bfloat16* a, size_t P, int C, const BnFwd f,
                                                        float slope) {
     // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
     pdl_launch_dependents();
     pdl_wait();
+    __shared__ float tab[2 * 128];
+    if (static_cast<int>(threadIdx.x) < C) {
+        const int c = threadIdx.x;
+        const double mean = f.dsum[c] / f.n;
+        double var = f.dsq[c] / f.n - mean * mean;
+        if (var < 0) var = 0;
+        const float istd = static_cast<float>(1.0 / sqrt(var + static_cast<double>(f.eps)));
+        tab[2 * c] = f.gamma[c] * istd;
+        tab[2 * c + 1] = f.beta[c] - f.gamma[c] * istd * static_cast<float>(mean);
+        if (blockIdx.x == 0) {
+            f.stats[2 * c] = static_cast<float>(mean);
+            f.stats[2 * c + 1] = istd;
+            f.running_mean[c] = (1.f - f.momentum) * f.running_mean[c] + f.momentum * static_cast<float>(mean);
+            f.running_var[c] = (1.f - f.momentum) * f.running_var[c] + f.momentum * static_cast<float>(var * f.n / (f.n - 1.0));
+            if (c == 0) f.nbt[0] += 1.f;
+        }
+    }
+    __syncthreads();
     // 256 is a multiple of C/8: a thread keeps the same 8 channels over its items, their table entries in registers
     const int chunks = C >> 3;
     const int c8 = static_cast<int>(threadIdx.x % chunks) * 8;
@@ -424,41 +432,46 @@ __global__ void __launch_bounds__(256, 5) bn_bwd_reduce_kernel(const ZT* z, cons
 }
 
 // per-channel table of the backward apply: with xh = (z - mean) * istd, y = z * a2 + b2, dy = dA * lrelu'(y):
-//   dz = gamma * istd * (dy - sum_dy / n - xh * sum_dyxh / n) = k0 * dy - c1 - z * c2
-// btab[c] = {a2, b2, k0, c1, c2}; optionally the gradients of gamma / beta: += {sum dY xhat, sum dY}
-__global__ void bn_bwd_finalize_kernel(const double* sums_rep, int reps, int C, double n, const float* stats, const float* gamma,
-                                       const float* beta, float* btab, float* ggamma, float* gbeta) {
-    // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
-    pdl_launch_dependents();
-    pdl_wait();
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
-    double sums[2] = {0.0, 0.0};  // {sum dY, sum dY xhat} of channel c over the replicas
-    for (int r = 0; r < reps; ++r) {
-        sums[0] += sums_rep[r * 2 * C + c];
-        sums[1] += sums_rep[r * 2 * C + C + c];
-    }
-    const float mean = stats[2 * c], istd = stats[2 * c + 1], ga = gamma[c];
-    const float m_dy = static_cast<float>(sums[0] / n), m_dyx = static_cast<float>(sums[1] / n);
-    const float k0 = ga * istd;
-    btab[5 * c + 0] = ga * istd;
-    btab[5 * c + 1] = beta[c] - ga * istd * mean;
-    btab[5 * c + 2] = k0;
-    btab[5 * c + 3] = k0 * (m_dy - m_dyx * mean * istd);
-    btab[5 * c + 4] = k0 * m_dyx * istd;
-    if (ggamma) {
-        gbeta[c] += static_cast<float>(sums[0]);
-        ggamma[c] += static_cast<float>(sums[1]);
-    }
-}
+//   dz = gamma * istd * (dy - sum_dy / n - xh * sum_dyxh / n) = k0 * dy - c1 - z * c2,  table = {a2, b2, k0, c1, c2}
+// Every block derives the table for itself from the replicated sums of bn_bwd_reduce_kernel (as the forward apply does);
+// block 0 optionally adds the gradients of gamma / beta: += {sum dY xhat, sum dY}.
+struct BnBwd {
+    const double* sums_rep;  // [reps][2][C]
+    int reps;
+    double n;
+    const float *stats, *gamma, *beta;
+    float *ggamma, *gbeta;  // may be null
+};
 
 template <typename ZT>
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const ZT* z, const __nv_bfloat16* da,
                                                            const float* dpool, __nv_bfloat16* dz, size_t P, size_t hw,
-                                                           int C, float slope, const float* btab) {
+                                                           int C, float slope, const BnBwd f) {
     // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
     pdl_launch_dependents();
     pdl_wait();
+    __shared__ float btab[5 * 128];
+    if (static_cast<int>(threadIdx.x) < C) {
+        const int c = threadIdx.x;
+        double sums[2] = {0.0, 0.0};  // {sum dY, sum dY xhat} of channel c over the replicas
+        for (int r = 0; r < f.reps; ++r) {
+            sums[0] += f.sums_rep[r * 2 * C + c];
+            sums[1] += f.sums_rep[r * 2 * C + C + c];
+        }
+        const float mean = f.stats[2 * c], istd = f.stats[2 * c + 1], ga = f.gamma[c];
+        const float m_dy = static_cast<float>(sums[0] / f.n), m_dyx = static_cast<float>(sums[1] / f.n);
+        const float k0 = ga * istd;
+        btab[5 * c + 0] = ga * istd;
+        btab[5 * c + 1] = f.beta[c] - ga * istd * mean;
+        btab[5 * c + 2] = k0;
+        btab[5 * c + 3] = k0 * (m_dy - m_dyx * mean * istd);
+        btab[5 * c + 4] = k0 * m_dyx * istd;
+        if (blockIdx.x == 0 && f.ggamma) {
+            f.gbeta[c] += static_cast<float>(sums[0]);
+            f.ggamma[c] += static_cast<float>(sums[1]);
+        }
+    }
+    __syncthreads();
     const int chunks = C >> 3;
     const int c8 = static_cast<int>(threadIdx.x % chunks) * 8;
     float t0[8], t1[8], t2[8], t3[8], t4[8];

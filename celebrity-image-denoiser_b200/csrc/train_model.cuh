@@ -93,8 +93,7 @@ constexpr int kBwdReps = 8;  // replicas of the BatchNorm-backward sums (see bn_
 enum { DS_BN = 0 /* 3 layers x 2 x 128 */, DS_BWD = 768 /* 3 x kBwdReps x 2 x 128 */, DS_LOSS = 768 + 3 * kBwdReps * 256 /* 8 */, DS_COUNT = DS_LOSS + 8 };
 // float scratch layout
 enum { FS_STATS = 0 /* 3 x 256 */, FS_POOLED = 768 /* B*128 */, FS_DPOOL = 768 + 128 * 1024, FS_PROBS = 768 + 2 * 128 * 1024,
-       FS_TAB = FS_PROBS + 1024 /* 3 x 256: forward affine table */, FS_BTAB = FS_TAB + 768 /* 3 x 5 x 128 */,
-       FS_WG27 = FS_BTAB + 1920 /* 64 x 64 */, FS_COUNT = FS_WG27 + 4096 };
+       FS_WG27 = FS_PROBS + 1024 /* 64 x 64 */, FS_COUNT = FS_WG27 + 4096 };
 constexpr int kTrainMaxBatch = 1024;
 
 static void train_build_table(cid_train* t) {
@@ -656,16 +655,16 @@ static int bn_forward(const TrainRun& r, int l, const void* z, void* a, int lv) 
     double* sums = t->dsc + DS_BN + (l - 1) * 256;
     float* stats = t->fsc + FS_STATS + (l - 1) * 256;
     const std::string bn = "discriminator.model." + std::to_string(kDBnIdx[l]);
-    float* tab = t->fsc + FS_TAB + (l - 1) * 256;
-    launch_k(t->g->pdl, bn_finalize_kernel, 1, 128, 0, r.st, sums, sums + 128, static_cast<double>(P), C, 1e-5f, 0.1f, stats,
-                                            train_ptr(t, bn + ".running_mean", 0), train_ptr(t, bn + ".running_var", 0),
-                                            train_ptr(t, bn + ".num_batches_tracked", 0), train_ptr(t, bn + ".weight", 0),
-                                            train_ptr(t, bn + ".bias", 0), tab);
+    BnFwd f;
+    f.dsum = sums; f.dsq = sums + 128; f.n = static_cast<double>(P); f.eps = 1e-5f; f.momentum = 0.1f; f.stats = stats;
+    f.running_mean = train_ptr(t, bn + ".running_mean", 0); f.running_var = train_ptr(t, bn + ".running_var", 0);
+    f.nbt = train_ptr(t, bn + ".num_batches_tracked", 0);
+    f.gamma = train_ptr(t, bn + ".weight", 0); f.beta = train_ptr(t, bn + ".bias", 0);
     const size_t n8 = P * C / 8;
     launch_k(t->g->pdl, bn_apply_kernel<float>, static_cast<unsigned>((n8 + 256 * kBnIter - 1) / (256 * kBnIter)), 256, 0, r.st, 
-        static_cast<const float*>(z), static_cast<__nv_bfloat16*>(a), P, C, tab, 0.2f);
+        static_cast<const float*>(z), static_cast<__nv_bfloat16*>(a), P, C, f, 0.2f);
     CID_CHECK_CUDA(cudaGetLastError());
-    t->launches += 2;
+    t->launches += 1;
     return 0;
 }
 
@@ -760,15 +759,15 @@ static int bn_backward(const TrainRun& r, int l, const void* z, const void* da, 
     launch_k(t->g->pdl, bn_bwd_reduce_kernel<float>, static_cast<unsigned>((P + ppb - 1) / ppb), 256, 0, r.st, 
         static_cast<const float*>(z), static_cast<const __nv_bfloat16*>(da), t->fsc + FS_DPOOL, P, hw, C, stats, gamma,
         beta, 0.2f, sums, ppb, kBwdReps);
-    float* btab = t->fsc + FS_BTAB + (l - 1) * 640;
-    launch_k(t->g->pdl, bn_bwd_finalize_kernel, 1, 128, 0, r.st, sums, kBwdReps, C, static_cast<double>(P), stats, gamma, beta, btab,
-                                                param_grads ? train_ptr(t, bn + ".weight", 1) : nullptr,
-                                                param_grads ? train_ptr(t, bn + ".bias", 1) : nullptr);
+    BnBwd f;
+    f.sums_rep = sums; f.reps = kBwdReps; f.n = static_cast<double>(P); f.stats = stats; f.gamma = gamma; f.beta = beta;
+    f.ggamma = param_grads ? train_ptr(t, bn + ".weight", 1) : nullptr;
+    f.gbeta = param_grads ? train_ptr(t, bn + ".bias", 1) : nullptr;
     const size_t n8 = P * C / 8;
     launch_k(t->g->pdl, bn_bwd_apply_kernel<float>, static_cast<unsigned>((n8 + 256 * kBnIter - 1) / (256 * kBnIter)), 256, 0, r.st, 
         static_cast<const float*>(z), static_cast<const __nv_bfloat16*>(da), t->fsc + FS_DPOOL,
-        static_cast<__nv_bfloat16*>(dz), P, hw, C, 0.2f, btab);
-    t->launches += 3;
+        static_cast<__nv_bfloat16*>(dz), P, hw, C, 0.2f, f);
+    t->launches += 2;
     CID_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
