@@ -82,8 +82,9 @@ def load_ncu_traffic():
 
 
 def library_sha():
-    p = ROOT / "celebrity-image-denoiser_b200" / "csrc" / "libcid_b200.so"
-    return hashlib.sha256(p.read_bytes()).hexdigest()[:16] if p.exists() else None
+    """Hash of the library's SOURCES (nvcc output is not byte-reproducible): names the build a profile belongs to."""
+    from cid_b200.build import source_sha
+    return source_sha()
 
 
 class ClockSampler:
@@ -489,9 +490,9 @@ def main():
             lay = ncu["layers"][dom]
             scale = (imgs_per_pass * H * W) / (ncu["batch"] * ncu["height"] * ncu["width"])
             traffic = (lay["dram_read_bytes"] + lay["dram_write_bytes"]) * scale
-            same = ncu.get("library_sha") == library_sha()
+            same = ncu.get("source_sha") == library_sha()
             traffic_src = (f"dram__bytes_read+write per launch, ncu --set full, {ncu['file']} "
-                           f"({'captured with this build of libcid_b200.so' if same else 'captured with an OLDER build of the library'})"
+                           f"({'captured with a build of these csrc/ sources' if same else 'captured with a build of OLDER csrc/ sources'})"
                            ", scaled to this launch's pixel count")
         roofline = {"bound": "tensor", "kernel": f"conv_umma_kernel[{dom}]", "achieved": achieved,
                     "peak": peaks["bf16"], "unit": "TFLOP/s", "frac": achieved / peaks["bf16"],

@@ -36,6 +36,19 @@ def needs_build() -> bool:
     return any(d.stat().st_mtime > t for d in deps)
 
 
+def source_sha() -> str:
+    """Hash of the sources libcid_b200.so is built from (nvcc's output is not byte-reproducible, so profiles name the
+    build they were captured with by its sources, not by the binary)."""
+    import hashlib
+    h = hashlib.sha256()
+    deps = sorted(list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.h")))
+    deps.append(CSRC.parent.parent / "include" / "cid_b200.h")
+    for d in deps:
+        h.update(d.name.encode())
+        h.update(d.read_bytes())
+    return h.hexdigest()[:16]
+
+
 def build_library(force: bool = False, verbose: bool = False) -> Path:
     """Compile csrc/*.cu into csrc/libcid_b200.so (no-op if up to date)."""
     if not force and not needs_build():

@@ -33,7 +33,9 @@ def traffic_json(hdr, units, data, path, batch, size):
     def val(r, m):
         v, u = float(r[hdr.index(m)]), units[hdr.index(m)]
         return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-3, "us": 1, "ms": 1e3}.get(u, 1)
-    out = {"batch": batch, "height": size, "width": size, "library_sha": hashlib.sha256(so.read_bytes()).hexdigest()[:16],
+    sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+    from cid_b200.build import source_sha
+    out = {"batch": batch, "height": size, "width": size, "source_sha": source_sha(),
            "how": "ncu --set full --clock-control none, one forward; dram__bytes_read.sum / dram__bytes_write.sum per launch",
            "layers": {}}
     assert len(data) >= 12, "expected the 12 layer kernels of one forward"
