@@ -423,9 +423,10 @@ def main():
         xs = x.repeat((b - a + B - 1) // B, 1, 1, 1)[: b - a].contiguous()
         ys = torch.empty_like(xs)
         net.set_option("chunk", 256)
-        tm.region("strong", lambda: net.forward_u8(xs, pad, out=ys), 5, warm=2)
+        n_strong = 20  # (5 passes were a 15 ms window at 8 GPUs: one slow rank's clock ramp decided the max over ranks)
+        tm.region("strong", lambda: net.forward_u8(xs, pad, out=ys), n_strong, warm=3)
         net.set_option("chunk", max(args.chunk, 0))
-        strong = {"images": 2048, "images_this_rank": b - a, "iters": 5}
+        strong = {"images": 2048, "images_this_rank": b - a, "iters": n_strong}
         del xs, ys
         torch.cuda.empty_cache()
 
