@@ -29,6 +29,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--phases", action="store_true", help="also time the four phases separately")
+    ap.add_argument("--opt", action="append", default=[], help="name=value for cid_train_set_option (A/B switches)")
     ap.add_argument("--nccl", action="store_true", help="N > 1: NCCL all-reduce + Adam instead of the fused peer-memory kernel")
     ap.add_argument("--check", action="store_true", help="N > 1: run 3 steps on both all-reduce paths and compare the weights")
     a = ap.parse_args()
@@ -47,6 +48,8 @@ def main():
     torch.manual_seed(0)
     g, d = DenoiseGenerator(), DenoiseDiscriminator()
     tr = DenoiseGANTrainStep(g, d, device=dev, peer_allreduce=not a.nccl)
+    for kv in a.opt:
+        tr.set_option(kv.split("=")[0], int(kv.split("=")[1]))
     gen = torch.Generator(device="cpu").manual_seed(1234 + rank)
     clean = (torch.rand(a.B, 3, a.H // 8, a.W // 8, generator=gen))
     clean = torch.nn.functional.interpolate(clean, size=(a.H, a.W), mode="bicubic", align_corners=False).clamp(0, 1)
