@@ -536,9 +536,9 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint32_t acc_it = 0;
         uint32_t o_count = 0;  // slabs this group has staged so far
         // BatchNorm statistics (EPI_LRELU_BN): lane = channel inside a 32-channel chunk
-        float st_sum[EPI == EPI_LRELU_BN ? N / 32 : 1], st_sq[EPI == EPI_LRELU_BN ? N / 32 : 1];
-#pragma unroll
-        for (int i = 0; i < (EPI == EPI_LRELU_BN ? N / 32 : 1); ++i) st_sum[i] = st_sq[i] = 0.f;
+        // (group g stages the slabs j = g, g + 2: always the SAME 64-channel column block cs = j % SL - two accumulators)
+        static_assert(EPI != EPI_LRELU_BN || N <= 128, "EPI_LRELU_BN: one column block per epilogue group");
+        float st_sum[2] = {0.f, 0.f}, st_sq[2] = {0.f, 0.f};
         // EPI_ADD: the first residual tensor (tmO2 = its tile map, same geometry as the output's) is TMA-loaded into
         // the group's residual buffer one work item ahead: as soon as the previous item's add has read the buffer.
         // Group g owns exactly slab j = g of every work item (S * N/64 == 2). Out-of-image pixels load as zeros.
@@ -558,11 +558,43 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                          // may run before those layers have finished (the TMA producer's wait does not cover it)
             issue_residual(unit);
         }
+        // Training (EPI_DGRAD / EPI_T4 with res2): the derivative mask is one 128-byte line of the layer's input activation
+        // per output pixel, read by the thread that owns the pixel. The epilogue is the critical path of these kernels and
+        // never waits for an accumulator, so each of those reads used to cost a full DRAM latency: every thread now pulls
+        // the lines of its NEXT work item into L2 while it works on the current one.
+        auto prefetch_mask = [&](int w) {
+            if constexpr (EPI == EPI_DGRAD || EPI == EPI_T4) {
+                if (p.res2 == nullptr || w >= p.num_work) return;
+                constexpr int SLp = N / 64;
+                const int nt = w % p.n_tiles, stw = w / p.n_tiles;
+#pragma unroll
+                for (int j = 0; j < S * SLp; ++j) {
+                    if ((j & 1) != g) continue;
+                    const TileCoord tcw = decode_tile(p, (stw * CG + static_cast<int>(rank)) * S + j / SLp);
+                    const uint16_t* base = static_cast<const uint16_t*>(p.res2);
+                    if constexpr (EPI == EPI_DGRAD) {
+                        const int yy = tcw.y0 + yl, xx = tcw.x0 + xl;
+                        if (tcw.b < p.B && yy < p.H && xx < p.W)
+                            prefetch_l2(base + ((static_cast<size_t>(tcw.b) * p.H + yy) * p.W + xx) * p.res2_cs + nt * N + (j % SLp) * 64);
+                    } else {
+                        const int oy = 2 * (tcw.y0 + yl) + nt;
+#pragma unroll
+                        for (int px = 0; px < 2; ++px) {
+                            const int ox = 2 * (tcw.x0 + xl) + px;
+                            if (tcw.b < p.B && oy < 2 * p.H && ox < 2 * p.W)
+                                prefetch_l2(base + ((static_cast<size_t>(tcw.b) * (2 * p.H) + oy) * (2 * p.W) + ox) * p.res2_cs + (j % SLp) * 64);
+                        }
+                    }
+                }
+            }
+        };
+        prefetch_mask(unit);
         for (int work = unit; work < p.num_work; work += units) {
             const int n_tile = work % p.n_tiles;
             const int st = work / p.n_tiles;
             const uint32_t buf = acc_it & 1;
             const uint32_t aph = (acc_it >> 1) & 1;
+            prefetch_mask(work + units);
             mbar_wait(&acc_full[buf], aph);
             tc_fence_after();
             const uint32_t tbase = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * Cfg::ACC_COLS;
@@ -573,12 +605,12 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     const int prow_i = (yl >> 1) * 4 + (xl >> 1);
                     const float slope = p.slope;
                     auto act = [&](float x) {  // ReLU, or LeakyReLU(slope) for the Keras layers
-                        if constexpr (EPI == EPI_LRELU || EPI == EPI_LRELU_BN) return x > 0.f ? x : x * slope;
-                        if constexpr (EPI == EPI_ADD || EPI == EPI_DGRAD) return x;
+                        if constexpr (EPI == EPI_LRELU) return x > 0.f ? x : x * slope;
+                        if constexpr (EPI == EPI_ADD || EPI == EPI_DGRAD || EPI == EPI_LRELU_BN) return x;  // (BN: z = conv + bias)
                         return fmaxf(x, 0.f);
                     };
                     (void)slope;
-#pragma unroll
+#pragma unroll((EPI == EPI_LRELU_BN || EPI == EPI_DGRAD) ? 1 : S * SL)  // training-only epilogues: rolled (they stalled on instruction fetch)
                     for (int j = 0; j < S * SL; ++j) {
                         if ((j & 1) != g) continue;
                         const int s = j / SL, cs = j % SL;
@@ -674,11 +706,13 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                     // written out by a TMA store below (per-thread 16-byte global stores touch 32 lines
                                     // with 16 bytes each per warp instruction: the layer ran at 21 % of the tensor peak).
                                     // Pixels outside the image are staged as zeros (the store clips them; the batch
-                                    // statistics below then need no mask).
+                                    // statistics below then need no mask): a branch, uniform for every full tile.
                                     const bool live = tc.b < p.B && tc.y0 + yl < p.H && tc.x0 + xl < p.W;
-                                    st_shared_v4(slab + ch * Cfg::O_SLAB + row * 128 + ((jj ^ (row & 7)) << 4),
-                                                 live ? __float_as_uint(f0) : 0u, live ? __float_as_uint(f1) : 0u,
-                                                 live ? __float_as_uint(f2) : 0u, live ? __float_as_uint(f3) : 0u);
+                                    uint8_t* dst = slab + ch * Cfg::O_SLAB + row * 128 + ((jj ^ (row & 7)) << 4);
+                                    if (live)
+                                        st_shared_v4(dst, __float_as_uint(f0), __float_as_uint(f1), __float_as_uint(f2), __float_as_uint(f3));
+                                    else
+                                        st_shared_v4(dst, 0u, 0u, 0u, 0u);
                                 }
                             }
                             if constexpr (TS && EPI != EPI_LRELU_BN) {
@@ -733,8 +767,8 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                         a1 += v;
                                         a2 = fmaf(v, v, a2);
                                     }
-                                    st_sum[cs * 2 + hh] += a1;
-                                    st_sq[cs * 2 + hh] += a2;
+                                    st_sum[hh] += a1;
+                                    st_sq[hh] += a2;
                                 }
                             }
                         } else if (TS && issuer) {
@@ -760,6 +794,26 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         const int s = j / SL, cs = j % SL;
                         const TileCoord tc = decode_tile(p, (st * CG + static_cast<int>(rank)) * S + s);
                         uint8_t* slab = o_smem + g * Cfg::OT_SLAB;
+                        // Training (res2): the LeakyReLU mask of chunk i = 64 bytes of the activation at this thread's output
+                        // pixel (2y+py, 2x+px). Its loads run TWO chunks ahead of their use (mk[i & 1]; chunks 0 and 1 are
+                        // requested before the slab's barrier and TMEM loads): waiting for them in place, four times per
+                        // slab, was a quarter of this kernel's stall samples.
+                        uint4 mk[2][4];
+                        bool mlive[2];
+#pragma unroll
+                        for (int px = 0; px < 2; ++px)
+                            mlive[px] = p.res2 != nullptr && tc.b < p.B && 2 * (tc.y0 + yl) + n_tile < 2 * p.H && 2 * (tc.x0 + xl) + px < 2 * p.W;
+                        auto mask_load = [&](int i) {  // i = 2 px + half
+                            const int px = i >> 1;
+                            if (mlive[px]) {
+                                const size_t pix = (static_cast<size_t>(tc.b) * (2 * p.H) + 2 * (tc.y0 + yl) + n_tile) * (2 * p.W) + 2 * (tc.x0 + xl) + px;
+                                const uint4* m4 = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.res2) + pix * p.res2_cs + cs * 64 + (i & 1) * 32);
+#pragma unroll
+                                for (int k = 0; k < 4; ++k) mk[i & 1][k] = __ldg(m4 + k);
+                            }
+                        };
+                        mask_load(0);
+                        mask_load(1);
                         if (issuer) bulk_wait_read<0>();
                         named_bar_sync(bar_id, 128);
                         // chunk i: px = i >> 1, 32-channel half = i & 1
@@ -771,16 +825,12 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             const float4* b4 = reinterpret_cast<const float4*>(p.bias + c);
                             uint32_t pk[16];
                             if (p.res2 != nullptr) {
-                                // LeakyReLU backward of the layer below, fused: 32 channels of the activation at this
-                                // thread's output pixel (2y+py, 2x+px)
-                                const int oy = 2 * (tc.y0 + yl) + n_tile, ox = 2 * (tc.x0 + xl) + px;
-                                if (tc.b < p.B && oy < 2 * p.H && ox < 2 * p.W) {
-                                    const size_t pix = (static_cast<size_t>(tc.b) * (2 * p.H) + oy) * (2 * p.W) + ox;
-                                    const uint4* m4 = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.res2) +
-                                                                                      pix * p.res2_cs + c);
+                                // LeakyReLU backward of the layer below, fused (mask loaded two chunks ahead, see above)
+                                const int ci = px * 2 + (((c - cs * 64) >> 5) & 1);  // this chunk's index in the slab
+                                if (mlive[px]) {
 #pragma unroll
                                     for (int i = 0; i < 4; ++i) {
-                                        const uint4 m = __ldg(m4 + i);
+                                        const uint4 m = mk[ci & 1][i];
                                         const uint32_t w[4] = {m.x, m.y, m.z, m.w};
 #pragma unroll
                                         for (int e = 0; e < 4; ++e) {
@@ -791,6 +841,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                         }
                                     }
                                 }
+                                if (ci + 2 < 4) mask_load(ci + 2);
                             }
 #pragma unroll
                             for (int jj = 0; jj < 8; ++jj) {
@@ -892,12 +943,13 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
         if constexpr (EPI == EPI_LRELU_BN) {
             if (p.stats != nullptr) {
+                // (n_tiles == 1 on this path) this group's column block: channels 64 cs + 32 hh + lane
+                const int c0 = (N / 64 == 1 ? 0 : g) * 64 + lane;
 #pragma unroll
-                for (int i = 0; i < N / 32; ++i) {
-                    // (n_tiles == 1 on this path: chunk i = channels 32 i .. 32 i + 31)
-                    if (st_sum[i] != 0.f || st_sq[i] != 0.f) {
-                        atomicAdd(p.stats + i * 32 + lane, static_cast<double>(st_sum[i]));
-                        atomicAdd(p.stats + 128 + i * 32 + lane, static_cast<double>(st_sq[i]));
+                for (int hh = 0; hh < 2; ++hh) {
+                    if (st_sum[hh] != 0.f || st_sq[hh] != 0.f) {
+                        atomicAdd(p.stats + c0 + hh * 32, static_cast<double>(st_sum[hh]));
+                        atomicAdd(p.stats + 128 + c0 + hh * 32, static_cast<double>(st_sq[hh]));
                     }
                 }
             }
