@@ -1245,6 +1245,10 @@ int cid_train_set_option(cid_train_handle t, const char* name, int64_t value) {
         t->peer_spin_ns = static_cast<unsigned long long>(value) * 1000000ull;
         return 0;
     }
+    if (!strcmp(name, "edge_fused")) {  // A/B switch: 3-channel weight gradients in one kernel (default) or via the im2col tensor
+        t->edge_fused = value != 0;
+        return 0;
+    }
     return cid_set_option(t->g, name, value);  // "pdl", ...
 }
 

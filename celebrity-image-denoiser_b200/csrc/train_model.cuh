@@ -72,6 +72,7 @@ struct cid_train {
     float* fsc = nullptr;             // float scratch: BN stats, pooled, dpool, probs
     std::map<std::string, CUtensorMap> maps;
     int64_t step_g = 0, step_d = 0;
+    int edge_fused = 1;               // option "edge_fused": 3-channel weight gradients in one kernel (0 = im2col3 + wgrad + scatter)
     bool u_upper_zeroed = false;      // the im2col buffer's zero half has been written in this iteration (reset by d_backward)
     // data-parallel peers (cid_train_set_peers): symmetric state / flag buffers of every rank, mapped into this process
     int peer_world = 0, peer_rank = 0, peer_epoch = 0;
@@ -407,9 +408,40 @@ static int colsum(cid_train* t, const void* v, size_t P, int cs, int c0, int C, 
     return 0;
 }
 
+// the same in ONE kernel (wgrad_edge_umma_kernel: the im2col operand is built in shared memory, the result goes straight
+// into the gradient tensor)
+static int wgrad_edge_fused(cid_train* t, const void* v64, const float* v3, int v3_nchw, int sign, float* out, int out_mode,
+                            int B, int H, int W, cudaStream_t st, float* bias_out) {
+    WgEdgeParams p;
+    memset(&p, 0, sizeof(p));
+    p.B = B; p.H = H; p.W = W;
+    p.tiles_x = (W + 7) / 8;
+    p.tiles_y = (H + 15) / 16;
+    p.m_tiles = B * p.tiles_x * p.tiles_y;
+    p.v3 = v3; p.v3_nchw = v3_nchw; p.sign = sign;
+    p.out = out; p.out_mode = out_mode; p.bias_out = bias_out;
+    const int extra = kWgEdgeBuilders * 2 * kWgEdgeWinW * 4 + 32 + 256;
+    p.stages = std::min(kWgMaxStages, (t->max_smem - 2048 - extra) / kWgEdgeStage);
+    CID_REQUIRE(p.stages >= kWgEdgeBuilders, "wgrad_edge: shared memory too small (%d stages for %d builder warps)", p.stages, kWgEdgeBuilders);
+    const CUtensorMap* tmA = tmap(t, v64, B, H, W, 64, 16, 8, 0);
+    if (!tmA) return 1;
+    const int smem = std::max(p.stages * kWgEdgeStage + extra + 1024, 120 * 1024);  // one CTA per SM
+    static uint64_t attr_set = 0;  // bit per device
+    if (!(attr_set >> (t->device & 63) & 1)) {
+        CID_CHECK_CUDA(cudaFuncSetAttribute(wgrad_edge_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, t->max_smem));
+        attr_set |= 1ull << (t->device & 63);
+    }
+    const int grid = std::max(1, std::min(t->num_sms, p.m_tiles));
+    launch_k(t->g->pdl, wgrad_edge_umma_kernel, grid, kWgEdgeThreads, smem, st, *tmA, p);
+    CID_CHECK_CUDA(cudaGetLastError());
+    t->launches++;
+    return 0;
+}
+
 // weight gradient of a 3-channel layer: R[c64][ci*9+tap] = sum_p v64[p][c64] * v3[p + sign*(tap - centre)][ci]
 static int wgrad_edge(cid_train* t, const void* v64, const float* v3, int v3_nchw, int sign, float* out, int out_mode,
                       void* ubuf, int B, int H, int W, cudaStream_t st, float* bias_out = nullptr) {
+    if (t->edge_fused) return wgrad_edge_fused(t, v64, v3, v3_nchw, sign, out, out_mode, B, H, W, st, bias_out);
     const size_t P = static_cast<size_t>(B) * H * W;
     const size_t i2c_tiles = static_cast<size_t>(B) * ((H + kI2cTy - 1) / kI2cTy) * ((W + kI2cTx - 1) / kI2cTx);
     CID_REQUIRE(i2c_tiles < (1ull << 31), "im2col3: too many tiles");

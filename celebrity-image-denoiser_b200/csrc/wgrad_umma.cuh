@@ -318,4 +318,223 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Weight gradients of the two 3-channel layers (Conv2d(3,64): V64 = dZ, V3 = the layer input, sign +1; Conv2d(64,3):
+// V64 = the layer input, V3 = dZ, sign -1) with the im2col operand built IN the kernel:
+//   R[c64][ci*9 + tap] = sum_p V64[p][c64] * V3[p + sign*(tap - centre)][ci]
+// Operand A = the 8 x 16 pixel tile of V64 (TMA, as above). Operand B = U[p][ci*9 + tap] (27 of 64 channels, the rest
+// zero): the four epilogue warps - idle during the main loop otherwise - gather it, one tile per warp, from a shared-memory
+// window of the fp32 3-channel source (10 x 18 pixels, loaded one tile ahead) and write it straight into the stage's
+// SW128 tile, the layout TMA would have produced. Saves the im2col kernel and its 64-channel bf16 tensor (a write and a read of 128 B per pixel
+// for 54 B of information) and the scatter kernel: the epilogue adds into the gradient tensor directly.
+// Channel 27 of U is all ones: column 27 of the result is the layer's bias gradient (Conv2d(3,64): sum of dZ), no reduction
+// pass. full[stage] = the TMA transaction + the builder warp's arrival; empty[stage] = the MMA commit.
+// ---------------------------------------------------------------------------------------------------------------------
+// one pixel's 27 im2col values from a source window [18 rows][32 slots] (slot = x*3 + ci for an NHWC source, ci*10 + x for
+// NCHW); wp points at the pixel's own slot (ci = 0). Compile-time sign / layout: every read is one LDS with an immediate.
+template <int SIGN, bool NCHW>
+__device__ __forceinline__ void wg_edge_gather(const float* wp, float (&f)[32]) {
+    constexpr int SX = NCHW ? 1 : 3, SC = NCHW ? 10 : 1;
+#pragma unroll
+    for (int ci = 0; ci < 3; ++ci)
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) f[ci * 9 + ky * 3 + kx] = wp[ci * SC + SIGN * ((ky - 1) * 32 + (kx - 1) * SX)];
+}
+
+struct WgEdgeParams {
+    int B, H, W;
+    int tiles_x, tiles_y, m_tiles, stages;
+    const float* v3;  // fp32 NHWC-3 or NCHW-3
+    int v3_nchw, sign;
+    float* out;       // mode 0: out[(c64*3 + ci)*9 + tap], mode 1: out[(ci*64 + c64)*9 + tap]
+    int out_mode;
+    float* bias_out;  // += column sums of V64 (may be null)
+};
+
+constexpr int kWgEdgeStage = 2 * 128 * 128;  // A tile + U tile
+// builder warps (warps 2..): each owns every 6th tile of the CTA. Must not exceed the number of stages: a warp that has
+// finished tile k (so tile k - stages has been consumed) goes on to tile k + builders, whose parity wait on the stage's
+// "empty" barrier is only unambiguous if tile k + builders - 2*stages has been consumed as well.
+constexpr int kWgEdgeBuilders = 6;
+constexpr int kWgEdgeThreads = 64 + 32 * kWgEdgeBuilders;
+constexpr int kWgEdgeWinW = 18 * 32;         // floats of one builder warp's source window: [18 rows][32 slots, 30 used]
+
+__global__ void __launch_bounds__(kWgEdgeThreads, 1)
+wgrad_edge_umma_kernel(const __grid_constant__ CUtensorMap tmA, const WgEdgeParams p) {
+    constexpr int A_ATOM = 128 * 128;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    float* win = reinterpret_cast<float*>(smem + p.stages * kWgEdgeStage);  // [builder warp][2][18][32]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(win + kWgEdgeBuilders * 2 * kWgEdgeWinW + 8);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + kWgMaxStages;
+    uint64_t* acc_full = bars + 2 * kWgMaxStages;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int per = (p.m_tiles + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+    const int t_begin = blockIdx.x * per;
+    const int t_end = min(p.m_tiles, t_begin + per);
+    const bool has_work = t_begin < t_end;
+    const bool do_bias = p.bias_out != nullptr;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        for (int i = 0; i < kWgMaxStages; ++i) {
+            mbar_init(&full[i], 1 + 1);                   // the TMA transaction + the tile's builder warp
+            mbar_init(&empty[i], 1);                      // the MMA commit
+        }
+        mbar_init(acc_full, 1);
+        fence_mbar_init();
+    }
+    // channels 32..63 of every U tile stay zero for the whole kernel (chunks 4..7 of each 128-byte row, in any swizzle)
+    for (int i = threadIdx.x; i < p.stages * 128 * 4; i += kWgEdgeThreads) {
+        const int st = i / 512, r = (i >> 2) & 127, c = 4 + (i & 3);
+        st_shared_v4(smem + st * kWgEdgeStage + A_ATOM + r * 128 + ((c ^ (r & 7)) << 4), 0u, 0u, 0u, 0u);
+    }
+    fence_proxy_async();
+    if (warp == 1) tmem_alloc(tmem_slot, 64);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_launch_dependents();
+
+    if (warp == 0) {
+        if (lane == 0 && has_work) {
+            pdl_wait();
+            uint32_t stage = 0, phase = 0;
+            for (int mt = t_begin; mt < t_end; ++mt) {
+                const int tx = mt % p.tiles_x;
+                const int r = mt / p.tiles_x;
+                const int ty = r % p.tiles_y;
+                const int b = r / p.tiles_y;
+                mbar_wait(&empty[stage], phase ^ 1);
+                mbar_arrive_expect_tx(&full[stage], A_ATOM);
+                tma_load_4d(smem + stage * kWgEdgeStage, &tmA, &full[stage], 0, tx * 8, ty * 16, b, kEvictNormal);
+                if (++stage == static_cast<uint32_t>(p.stages)) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (has_work) {
+            constexpr uint32_t idesc = umma_idesc_bf16_mn(128, 64);
+            uint32_t stage = 0, phase = 0;
+            for (int mt = t_begin; mt < t_end; ++mt) {
+                mbar_wait(&full[stage], phase);
+                tc_fence_after();
+                const uint32_t sa = smem_u32(smem + stage * kWgEdgeStage);
+                if (elect_one()) {
+#pragma unroll
+                    for (int k8 = 0; k8 < 8; ++k8)  // K = 16 pixels = tile rows 2*k8, 2*k8+1
+                        umma_bf16_ss(tmem_base, umma_desc_mn_sw128(sa + k8 * 2048, 0, 1024),
+                                     umma_desc_mn_sw128(sa + A_ATOM + k8 * 2048, 0, 1024), idesc, (mt == t_begin && k8 == 0) ? 0u : 1u);
+                    umma_commit(&empty[stage]);
+                }
+                __syncwarp();
+                if (++stage == static_cast<uint32_t>(p.stages)) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+            if (elect_one()) umma_commit(acc_full);
+            __syncwarp();
+        }
+    } else if (has_work) {
+        // ======================= U-tile builders (then bias reducers, then the epilogue) =======================
+        // Every builder warp owns every 6th tile of the CTA and its own pair of source windows, so six tiles are being
+        // built at any time (one warp's chain window -> gather -> fence -> arrive is ~1.5 us of latencies; 128 threads on
+        // one tile at a time made the kernel builder-bound at 1.9 us per tile).
+        const int bw = warp - 2;
+        const int q = warp & 3;
+        float* wwin = win + bw * (2 * kWgEdgeWinW);  // two windows [18 rows][32 slots]
+        // window slot of this lane: NHWC source: slot = wx*3 + ci (30 contiguous floats per row); NCHW: slot = ci*10 + wx
+        const int wx_l = p.v3_nchw ? lane % 10 : lane / 3, ci_l = p.v3_nchw ? lane / 10 : lane % 3;
+        const int sx = p.v3_nchw ? 1 : 3;
+        auto load_window = [&](int mt, float (&w)[18]) {
+            const int tx = mt % p.tiles_x;
+            const int r0 = mt / p.tiles_x;
+            const int ty = r0 % p.tiles_y;
+            const int b = r0 / p.tiles_y;
+            const int xx = tx * 8 - 1 + wx_l;
+            const bool col_ok = lane < 30 && mt < t_end && b < p.B && xx >= 0 && xx < p.W;
+#pragma unroll
+            for (int k = 0; k < 18; ++k) {
+                const int yy = ty * 16 - 1 + k;
+                float v = 0.f;
+                if (col_ok && yy >= 0 && yy < p.H)
+                    v = p.v3_nchw ? __ldg(p.v3 + ((static_cast<size_t>(b) * 3 + ci_l) * p.H + yy) * p.W + xx)
+                                  : __ldg(p.v3 + ((static_cast<size_t>(b) * p.H + yy) * p.W + xx) * 3 + ci_l);
+                w[k] = v;
+            }
+        };
+        pdl_wait();  // the 3-channel source is an earlier kernel's output
+        float wn[18];
+        load_window(t_begin + bw, wn);
+        int buf = 0;
+        for (int kt = bw; t_begin + kt < t_end; kt += kWgEdgeBuilders, buf ^= 1) {
+            const int mt = t_begin + kt;
+            const uint32_t stage = static_cast<uint32_t>(kt % p.stages), phase = static_cast<uint32_t>(kt / p.stages) & 1u;
+            float* wb = wwin + buf * kWgEdgeWinW;
+#pragma unroll
+            for (int k = 0; k < 18; ++k) wb[k * 32 + lane] = wn[k];
+            load_window(mt + kWgEdgeBuilders, wn);  // in flight while this tile is gathered
+            __syncwarp();
+            mbar_wait(&empty[stage], phase ^ 1);
+            uint8_t* ut = smem + stage * kWgEdgeStage + A_ATOM;
+#pragma unroll 1
+            for (int pass = 0; pass < 4; ++pass) {
+                const int et = pass * 32 + lane, yl = et >> 3, xl = et & 7;
+                // channel ci*9 + ky*3 + kx = source pixel + sign*(ky-1, kx-1)
+                const float* wp = wb + (yl + 1) * 32 + (xl + 1) * sx;
+                float f[32];
+                f[27] = 1.f;  // a channel of ones: column 27 of the result = sum_p V64[p][c64] = the bias gradient, for free
+#pragma unroll
+                for (int i = 28; i < 32; ++i) f[i] = 0.f;
+                if (p.v3_nchw) {
+                    if (p.sign > 0) wg_edge_gather<1, true>(wp, f); else wg_edge_gather<-1, true>(wp, f);
+                } else {
+                    if (p.sign > 0) wg_edge_gather<1, false>(wp, f); else wg_edge_gather<-1, false>(wp, f);
+                }
+                uint8_t* ub = ut + et * 128;
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    st_shared_v4(ub + ((c ^ (et & 7)) << 4), pack_bf16x2(f[8 * c], f[8 * c + 1]), pack_bf16x2(f[8 * c + 2], f[8 * c + 3]),
+                                 pack_bf16x2(f[8 * c + 4], f[8 * c + 5]), pack_bf16x2(f[8 * c + 6], f[8 * c + 7]));
+            }
+            fence_proxy_async();  // generic-proxy writes -> visible to the tensor core
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&full[stage]);
+        }
+        mbar_wait(acc_full, 0);
+        tc_fence_after();
+        if (q < 2 && bw < 4) {  // (warps 4, 5) accumulator rows 0..63 = the 64 channels of V64; rows 64..127 repeat them
+            const int c64 = q * 32 + lane;
+            uint32_t v[32];
+            tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16), v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 27; ++j) {
+                const int ci = j / 9, tap = j - ci * 9;
+                float* dst = p.out_mode ? p.out + (ci * 64 + c64) * 9 + tap : p.out + (c64 * 3 + ci) * 9 + tap;
+                red_add_f32(dst, __uint_as_float(v[j]));
+            }
+            if (do_bias) red_add_f32(p.bias_out + c64, __uint_as_float(v[27]));
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 64);
+    }
+}
+
+
 }  // namespace cid
