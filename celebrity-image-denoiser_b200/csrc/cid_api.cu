@@ -1245,10 +1245,6 @@ int cid_train_set_option(cid_train_handle t, const char* name, int64_t value) {
         t->peer_spin_ns = static_cast<unsigned long long>(value) * 1000000ull;
         return 0;
     }
-    if (!strcmp(name, "edge_fused")) {  // A/B switch: 3-channel weight gradients in one kernel (default) or via the im2col tensor
-        t->edge_fused = value != 0;
-        return 0;
-    }
     return cid_set_option(t->g, name, value);  // "pdl", ...
 }
 
@@ -1318,7 +1314,6 @@ int cid_train_d_backward(cid_train_handle t, const float* noisy, const float* cl
     TrainRun r;
     if (train_make_run(t, B, H, W, ws, ws_bytes, st, &r)) return 1;
     t->B = B; t->H = H; t->W = W; t->ws = ws;
-    t->u_upper_zeroed = false;
     CID_CHECK_CUDA(cudaMemsetAsync(t->state + train_P(t) + t->n_g, 0, t->n_d * 4, st));
     CID_CHECK_CUDA(cudaMemsetAsync(t->dsc + DS_LOSS, 0, 2 * 8, st));
     // denoised = G(noisy)  (training.py:411)
@@ -1472,7 +1467,7 @@ int cid_train_debug_buffer(cid_train_handle t, const char* name, const void* ws,
     CID_REQUIRE(t && name && ws && dst_host, "cid_train_debug_buffer: null argument");
     static const char* names[TB_COUNT] = {"y", "gz", "gx", "dz10", "gcat1", "dz8", "dz7", "gcat2", "dz5", "dz4", "gp2", "dz3", "dz2",
                                           "gp1", "dz1", "dz0", "d_a0", "d_z1", "d_a1", "d_z2", "d_a2", "d_z3", "d_a3", "d_g3", "d_g2",
-                                          "d_g1", "d_g0", "gz_nchw", "u"};
+                                          "d_g1", "d_g0", "gz_nchw"};
     int b = -1;
     for (int i = 0; i < TB_COUNT; ++i)
         if (!strcmp(name, names[i])) b = i;

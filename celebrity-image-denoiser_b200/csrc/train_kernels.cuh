@@ -1,5 +1,4 @@
-// Memory-bound and small kernels of the training step: im2col of the 3-channel tensors (operand of the
-// edge layers' tensor-core weight gradients), MaxPool / ReLU / tanh backward, train-mode BatchNorm apply and backward,
+// Memory-bound and small kernels of the training step: MaxPool / ReLU / tanh backward, train-mode BatchNorm apply and backward,
 // the discriminator head with BCELoss, column sums, Adam and the fp32 -> bf16 weight re-pack.
 //
 // Reference ops (file:line in /root/reference/backend/trainingcode/denoise_gan_code/training.py):
@@ -51,79 +50,6 @@ __device__ __forceinline__ float block_sum(float v, float* red /* >= 32 floats *
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
     }
     return s;  // valid in thread 0
-}
-
-// ---------------------------------------------------------------------------------------------------------------------
-// Weight gradients of the 3-channel layers on tensor cores: R[c64][ci*9 + tap] = sum_p V64[p][c64] * V3[p + sign*(tap - centre)][ci]
-// (sign +1: Conv2d(3,64), V64 = dZ, V3 = the layer input; sign -1: Conv2d(64,3), V64 = the layer input, V3 = dZ).
-// U[p][ci*9 + tap] = V3[p + sign*(tap - centre)][ci] as a
-// 64-channel bf16 NHWC tensor (27 real channels, the rest zero), so that R = V64^T U is ONE plain weight-gradient GEMM of
-// wgrad_umma.cuh (T = 1, no halo); wg27_scatter_kernel then adds the 64 x 27 result into the gradient tensor.
-// ---------------------------------------------------------------------------------------------------------------------
-// zero_upper: also write the 32 always-zero upper channels (needed once per workspace use, see wgrad_edge).
-// A block owns a 32 x 4 pixel tile: it stages the tile's 34 x 6 x 3 source window (zero outside the image) in shared
-// memory with coalesced loads, then every thread gathers its pixel's 27 values from there - no per-tap bounds checks or
-// 64-bit address arithmetic (the one-thread-one-pixel form with 27 guarded global loads was instruction-issue bound:
-// 69 % issue-active at 0.18 of HBM peak, `profiles/r02t_train_mem`).
-constexpr int kI2cTx = 32, kI2cTy = 4;
-__global__ void __launch_bounds__(128) im2col3_kernel(const float* v3, int v3_nchw, int sign, __nv_bfloat16* u, int B, int H,
-                                                      int W, int zero_upper) {
-    // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
-    pdl_launch_dependents();
-    pdl_wait();
-    constexpr int SW = kI2cTx + 2, SH = kI2cTy + 2;
-    __shared__ float s[3][SH][SW];
-    const uint32_t tiles_x = (W + kI2cTx - 1) / kI2cTx, tiles_y = (H + kI2cTy - 1) / kI2cTy;
-    const uint32_t tx = blockIdx.x % tiles_x, tt = blockIdx.x / tiles_x;
-    const uint32_t ty = tt % tiles_y, b = tt / tiles_y;
-    const int x0 = static_cast<int>(tx) * kI2cTx, y0 = static_cast<int>(ty) * kI2cTy;
-    for (int i = threadIdx.x; i < 3 * SH * SW; i += 128) {
-        const int r = i / (3 * SW), j = i - r * (3 * SW);
-        const int ci = v3_nchw ? j / SW : j % 3, px = v3_nchw ? j % SW : j / 3;
-        const int yy = y0 - 1 + r, xx = x0 - 1 + px;
-        float v = 0.f;
-        if (yy >= 0 && yy < H && xx >= 0 && xx < W)
-            v = v3_nchw ? __ldg(v3 + ((static_cast<size_t>(b) * 3 + ci) * H + yy) * W + xx)
-                        : __ldg(v3 + ((static_cast<size_t>(b) * H + yy) * W + xx) * 3 + ci);
-        s[ci][r][px] = v;
-    }
-    __syncthreads();
-    // a thread owns ONE 16-byte chunk (8 of the 27 (ci, tap) channels) of the pixels of one tile column: four consecutive
-    // lanes write the 64 contiguous bytes of a pixel, so every 32-byte sector leaves the SM fully written
-    const int chunk = threadIdx.x & 3, lx = threadIdx.x >> 2;
-    int off[8];  // offset of channel 8 * chunk + e in the staged window, relative to the pixel's own slot; -1 = zero
-#pragma unroll
-    for (int e = 0; e < 8; ++e) {
-        const int idx = 8 * chunk + e, ci = idx / 9, tap = idx - 9 * ci, ky = tap / 3, kx = tap - 3 * ky;
-        off[e] = idx < 27 ? (ci * SH + 1 + sign * (ky - 1)) * SW + 1 + sign * (kx - 1) : -1;
-    }
-    const float* sf = &s[0][0][0];
-    const int x = x0 + lx;
-    if (x >= W) return;
-#pragma unroll
-    for (int ly = 0; ly < kI2cTy; ++ly) {
-        const int y = y0 + ly;
-        if (y >= H) break;
-        const int base = ly * SW + lx;
-        float f[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) f[e] = off[e] >= 0 ? sf[base + off[e]] : 0.f;
-        __nv_bfloat16* dst = u + ((static_cast<size_t>(b) * H + y) * W + x) * 64 + chunk * 8;
-        st_global_v4(dst, pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
-        if (zero_upper) st_global_v4(dst + 32, 0u, 0u, 0u, 0u);
-    }
-}
-
-// scratch[c64][j] (64 x 64 fp32, j = ci*9 + tap < 27) -> out[(c64*3 + ci)*9 + tap] (mode 0) / out[(ci*64 + c64)*9 + tap]
-__global__ void wg27_scatter_kernel(const float* scratch, float* out, int out_mode) {
-    // programmatic dependent launch: the next kernel may start its set-up now; this one orders itself after its predecessor
-    pdl_launch_dependents();
-    pdl_wait();
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= 64 * 27) return;
-    const int c = i / 27, j = i % 27, ci = j / 9, tap = j % 9;
-    float* dst = out_mode ? out + (ci * 64 + c) * 9 + tap : out + (c * 3 + ci) * 9 + tap;
-    *dst += scratch[c * 64 + j];
 }
 
 // ---------------------------------------------------------------------------------------------------------------------

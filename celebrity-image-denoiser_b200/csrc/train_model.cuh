@@ -40,13 +40,12 @@ enum TBuf {
     TB_DZ10, TB_GCAT1, TB_DZ8, TB_DZ7, TB_GCAT2, TB_DZ5, TB_DZ4, TB_GP2, TB_DZ3, TB_DZ2, TB_GP1, TB_DZ1, TB_DZ0,
     TB_DA0, TB_DZ1D, TB_DA1, TB_DZ2D, TB_DA2, TB_DZ3D, TB_DA3, TB_DG3, TB_DG2, TB_DG1, TB_DG0,
     TB_GZC,  // gz as fp32 NCHW
-    TB_U,  // im2col of a 3-channel tensor (27 of 64 channels used): operand of the edge layers' weight gradients
     TB_COUNT
 };
 static const int kTBufC[TB_COUNT] = {3, 3, 3, 64, 128, 128, 128, 256, 256, 256, 128, 128, 128, 64, 64, 64,
-                                     64, 64, 64, 128, 128, 128, 128, 128, 128, 64, 64, 3, 64};
+                                     64, 64, 64, 128, 128, 128, 128, 128, 128, 64, 64, 3};
 static const int kTBufLevel[TB_COUNT] = {0, 0, 0, 0, 0, 1, 1, 1, 2, 2, 2, 1, 1, 1, 0, 0,
-                                         0, 1, 1, 1, 1, 2, 2, 2, 1, 1, 0, 0, 0};
+                                         0, 1, 1, 1, 1, 2, 2, 2, 1, 1, 0, 0};
 
 }  // namespace cid
 
@@ -72,8 +71,6 @@ struct cid_train {
     float* fsc = nullptr;             // float scratch: BN stats, pooled, dpool, probs
     std::map<std::string, CUtensorMap> maps;
     int64_t step_g = 0, step_d = 0;
-    int edge_fused = 1;               // option "edge_fused": 3-channel weight gradients in one kernel (0 = im2col3 + wgrad + scatter)
-    bool u_upper_zeroed = false;      // the im2col buffer's zero half has been written in this iteration (reset by d_backward)
     // data-parallel peers (cid_train_set_peers): symmetric state / flag buffers of every rank, mapped into this process
     int peer_world = 0, peer_rank = 0, peer_epoch = 0;
     const float* peer_state[8] = {nullptr};
@@ -94,7 +91,7 @@ constexpr int kBwdReps = 8;  // replicas of the BatchNorm-backward sums (see bn_
 enum { DS_BN = 0 /* 3 layers x 2 x 128 */, DS_BWD = 768 /* 3 x kBwdReps x 2 x 128 */, DS_LOSS = 768 + 3 * kBwdReps * 256 /* 8 */, DS_COUNT = DS_LOSS + 8 };
 // float scratch layout
 enum { FS_STATS = 0 /* 3 x 256 */, FS_POOLED = 768 /* B*128 */, FS_DPOOL = 768 + 128 * 1024, FS_PROBS = 768 + 2 * 128 * 1024,
-       FS_WG27 = FS_PROBS + 1024 /* 64 x 64 */, FS_COUNT = FS_WG27 + 4096 };
+       FS_COUNT = FS_PROBS + 1024 };
 constexpr int kTrainMaxBatch = 1024;
 
 static void train_build_table(cid_train* t) {
@@ -327,8 +324,7 @@ static int launch_wgrad(cid_train* t, const CUtensorMap& tmA, const CUtensorMap&
 }
 
 // geometry of a weight gradient: 0 = 3x3 stride 1, 1 = 3x3 stride 2 (operand B = the 2x larger layer input),
-// 2 = ConvTranspose k2 s2 (operand A = the layer input, operand B = the 2x larger output gradient),
-// 3 = plain product A^T B of two tensors of the same resolution (the im2col route of the 3-channel layers)
+// 2 = ConvTranspose k2 s2 (operand A = the layer input, operand B = the 2x larger output gradient)
 static void wgrad_roles(WgParams& p, int geom, int m_ch, int n_ch, int NA, int NB) {
     p.n_roles = 0;
     for (int mb = 0; mb < m_ch / (64 * NA); ++mb)
@@ -350,15 +346,13 @@ static void wgrad_roles(WgParams& p, int geom, int m_ch, int n_ch, int NA, int N
                     push(ky - 1, -1, ky * 3 + 0, ky * 3 + 2, -1);  // even columns of the 2x input: kx = 0 (px 0), kx = 2 (px 1)
                     push(ky - 1, 0, ky * 3 + 1, -1, -1);           // odd columns: kx = 1
                 }
-            } else if (geom == 2) {
-                for (int q = 0; q < 4; ++q) push(q >> 1, q & 1, q, -1, -1);
             } else {
-                push(0, 0, 0, -1, -1);
+                for (int q = 0; q < 4; ++q) push(q >> 1, q & 1, q, -1, -1);
             }
         }
-    p.scale = (geom == 0 || geom == 3) ? 1 : 2;
+    p.scale = geom == 0 ? 1 : 2;
     p.pw = geom == 0 ? 10 : geom == 1 ? 9 : 8;
-    p.kk = geom == 2 ? 4 : geom == 3 ? 1 : 9;
+    p.kk = geom == 2 ? 4 : 9;
     p.s_m = n_ch;
 }
 
@@ -375,16 +369,14 @@ static int wgrad(cid_train* t, int geom, const void* A, int a_C, int m_ch, const
     const int NA = m_ch >= 128 ? 2 : 1, NB = n_ch >= 128 ? 2 : 1;
     wgrad_roles(p, geom, m_ch, n_ch, NA, NB);
     const CUtensorMap* tmA = tmap(t, A, B, H, W, a_C, 16, 8, 0);
-    const CUtensorMap* tmB = geom == 0   ? tmap(t, Bt, B, H, W, b_C, 16, 10, 0)
-                             : geom == 3 ? tmap(t, Bt, B, H, W, b_C, 16, 8, 0)
-                                         : tmap(t, Bt, B, 2 * H, 2 * W, b_C, 16, p.pw, 1);
+    const CUtensorMap* tmB = geom == 0 ? tmap(t, Bt, B, H, W, b_C, 16, 10, 0) : tmap(t, Bt, B, 2 * H, 2 * W, b_C, 16, p.pw, 1);
     if (!tmA || !tmB) return 1;
     const int T = geom == 0 ? 3 : geom == 1 ? 2 : 1;
 #define CID_WG(na, nb, tt) \
     if (NA == na && NB == nb && T == tt) return launch_wgrad<na, nb, tt>(t, *tmA, *tmB, p, st);
     CID_WG(1, 1, 3) CID_WG(1, 2, 3) CID_WG(2, 1, 3) CID_WG(2, 2, 3)
     CID_WG(1, 1, 2) CID_WG(2, 2, 2)
-    CID_WG(2, 1, 1) CID_WG(2, 2, 1) CID_WG(1, 1, 1)
+    CID_WG(2, 1, 1) CID_WG(2, 2, 1)
 #undef CID_WG
     set_error("wgrad: no kernel for NA=%d NB=%d T=%d", NA, NB, T);
     return 1;
@@ -408,10 +400,11 @@ static int colsum(cid_train* t, const void* v, size_t P, int cs, int c0, int C, 
     return 0;
 }
 
-// the same in ONE kernel (wgrad_edge_umma_kernel: the im2col operand is built in shared memory, the result goes straight
-// into the gradient tensor)
-static int wgrad_edge_fused(cid_train* t, const void* v64, const float* v3, int v3_nchw, int sign, float* out, int out_mode,
-                            int B, int H, int W, cudaStream_t st, float* bias_out) {
+// weight gradient of a 3-channel layer: out += R[c64][ci*9+tap] = sum_p v64[p][c64] * v3[p + sign*(tap - centre)][ci]
+// (wgrad_edge_umma_kernel: the im2col operand is built in shared memory, the result goes straight into the gradient
+// tensor; bias_out += column sums of v64)
+static int wgrad_edge(cid_train* t, const void* v64, const float* v3, int v3_nchw, int sign, float* out, int out_mode,
+                      int B, int H, int W, cudaStream_t st, float* bias_out = nullptr) {
     WgEdgeParams p;
     memset(&p, 0, sizeof(p));
     p.B = B; p.H = H; p.W = W;
@@ -435,25 +428,6 @@ static int wgrad_edge_fused(cid_train* t, const void* v64, const float* v3, int 
     launch_k(t->g->pdl, wgrad_edge_umma_kernel, grid, kWgEdgeThreads, smem, st, *tmA, p);
     CID_CHECK_CUDA(cudaGetLastError());
     t->launches++;
-    return 0;
-}
-
-// weight gradient of a 3-channel layer: R[c64][ci*9+tap] = sum_p v64[p][c64] * v3[p + sign*(tap - centre)][ci]
-static int wgrad_edge(cid_train* t, const void* v64, const float* v3, int v3_nchw, int sign, float* out, int out_mode,
-                      void* ubuf, int B, int H, int W, cudaStream_t st, float* bias_out = nullptr) {
-    if (t->edge_fused) return wgrad_edge_fused(t, v64, v3, v3_nchw, sign, out, out_mode, B, H, W, st, bias_out);
-    const size_t P = static_cast<size_t>(B) * H * W;
-    const size_t i2c_tiles = static_cast<size_t>(B) * ((H + kI2cTy - 1) / kI2cTy) * ((W + kI2cTx - 1) / kI2cTx);
-    CID_REQUIRE(i2c_tiles < (1ull << 31), "im2col3: too many tiles");
-    launch_k(t->g->pdl, im2col3_kernel, static_cast<unsigned>(i2c_tiles), 128, 0, st, v3, v3_nchw, sign, static_cast<__nv_bfloat16*>(ubuf), B, H, W, t->u_upper_zeroed ? 0 : 1);
-    t->u_upper_zeroed = true;  // channels 32..63 of U stay zero for the rest of this iteration (4 launches share the buffer)
-    CID_CHECK_CUDA(cudaGetLastError());
-    float* scratch = t->fsc + FS_WG27;
-    CID_CHECK_CUDA(cudaMemsetAsync(scratch, 0, 4096 * 4, st));
-    if (wgrad(t, 3, v64, 64, 64, ubuf, 64, 64, B, H, W, scratch, st, bias_out)) return 1;
-    launch_k(t->g->pdl, wg27_scatter_kernel, (64 * 27 + 255) / 256, 256, 0, st, scratch, out, out_mode);
-    CID_CHECK_CUDA(cudaGetLastError());
-    t->launches += 2;
     return 0;
 }
 
@@ -858,7 +832,7 @@ static int d_backward(const TrainRun& r, const float* img, float target, float s
         if (launch_conv_t<64, 8, 2, false, EPI_T4, 10, 1, 2>(t, *tmA, t->dd_tmh[1], *tmO, p, r.st)) return 1;
     }
     if (param_grads) {
-                if (wgrad_edge(t, r.tbuf(TB_DG0), img, 1, 1, gradp(0, ".weight"), 0, r.tbuf(TB_U), B, H, W, r.st, gradp(0, ".bias"))) return 1;
+                if (wgrad_edge(t, r.tbuf(TB_DG0), img, 1, 1, gradp(0, ".weight"), 0, B, H, W, r.st, gradp(0, ".bias"))) return 1;
     }
     if (want_gx) {
         // 64 -> 3 data gradient on the last-conv kernel (transposed GEMM) with a linear fp32 NHWC epilogue
@@ -901,7 +875,7 @@ static int g_backward_layers(const TrainRun& r, const float* noisy) {
     };
     // L11 upconv1.2 (64 -> 3): bias gradient came with gz
     {
-        if (wgrad_edge(t, r.gbuf(B_U1A), static_cast<const float*>(r.tbuf(TB_GZ)), 0, -1, gw(11), 1, r.tbuf(TB_U), B, H, W, r.st))
+        if (wgrad_edge(t, r.gbuf(B_U1A), static_cast<const float*>(r.tbuf(TB_GZ)), 0, -1, gw(11), 1, B, H, W, r.st))
             return 1;
         // data gradient (3 -> 64 conv of gz with flipped weights, masked by u1a > 0) on the tensor-core first-conv kernel
         const CUtensorMap* tmO = tmap(t, r.tbuf(TB_DZ10), B, H, W, 64, 16, 8, 0);
@@ -961,7 +935,7 @@ static int g_backward_layers(const TrainRun& r, const float* noisy) {
     if (dgrad3x3(r, 0, r.tbuf(TB_DZ1), 64, t->gd_tm[1], r.tbuf(TB_DZ0), 64, r.gbuf(B_A0), 64, &t->gd_tmh[1])) return 1;
     // L0 down1.0 (3 -> 64)
         {
-        if (wgrad_edge(t, r.tbuf(TB_DZ0), noisy, 1, 1, gw(0), 0, r.tbuf(TB_U), B, H, W, r.st, gb(0))) return 1;
+        if (wgrad_edge(t, r.tbuf(TB_DZ0), noisy, 1, 1, gw(0), 0, B, H, W, r.st, gb(0))) return 1;
     }
     return 0;
 }
