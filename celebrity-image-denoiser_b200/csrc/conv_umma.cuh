@@ -65,6 +65,8 @@ struct ConvParams {
     const void* res2;    //          (second one optional)
     int res_cs, res2_cs;
     int bias_per_column; // EPI_CONVT as pixel shuffle: bias indexed by GEMM column instead of by channel
+    int linear;          // EPI_T4: bias is all zeros and slope is 1 (the training data-gradient launches): the epilogue packs the
+                         // accumulator as it is
     float mask_slope;    // EPI_T4 with res2 set (training): the output gradient is multiplied by the LeakyReLU derivative of
                          // the activation res2 at the OUTPUT pixel (1 where it is positive, mask_slope elsewhere)
     double* stats;       // EPI_LRELU_BN (training): per-channel sum (stats[c]) and sum of squares (stats[128 + c])
@@ -589,6 +591,39 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
         };
         prefetch_mask(unit);
+        // EPI_T4 with res2 (training): the LeakyReLU mask of chunk i = 2 px + half of a slab = 64 bytes of the activation
+        // at this thread's output pixel (2y+py, 2x+px), held in t4_mk[i & 1]. Chunks 0 and 1 of the group's NEXT slab are
+        // requested as soon as the current slab has consumed its last chunk (across work items when a group has one slab
+        // per work item), chunks 2 and 3 when 0 and 1 have been used: waiting for the loads in place, four times per slab,
+        // was a quarter of this kernel's stall samples.
+        uint4 t4_mk[2][4];
+        bool t4_live[2] = {false, false};
+        (void)t4_mk;
+        auto t4_mask_load = [&](int i, const TileCoord& tcw, int nt, int csw) {  // i = 2 px + half
+            if constexpr (EPI == EPI_T4) {
+                const int px = i >> 1;
+                if (t4_live[px]) {
+                    const size_t pix = (static_cast<size_t>(tcw.b) * (2 * p.H) + 2 * (tcw.y0 + yl) + nt) * (2 * p.W) + 2 * (tcw.x0 + xl) + px;
+                    const uint4* m4 = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.res2) + pix * p.res2_cs + csw * 64 + (i & 1) * 32);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) t4_mk[i & 1][k] = __ldg(m4 + k);
+                }
+            }
+        };
+        auto t4_mask_begin = [&](const TileCoord& tcw, int nt, int csw) {  // first two chunks of a slab
+            if constexpr (EPI == EPI_T4) {
+#pragma unroll
+                for (int px = 0; px < 2; ++px)
+                    t4_live[px] = p.res2 != nullptr && tcw.b < p.B && 2 * (tcw.y0 + yl) + nt < 2 * p.H && 2 * (tcw.x0 + xl) + px < 2 * p.W;
+                t4_mask_load(0, tcw, nt, csw);
+                t4_mask_load(1, tcw, nt, csw);
+            }
+        };
+        constexpr bool T4_ONE_SLAB = EPI == EPI_T4 && S * (N / 64) == 2;  // one slab per group per work item: j = g
+        if constexpr (T4_ONE_SLAB) {
+            if (unit < p.num_work)
+                t4_mask_begin(decode_tile(p, ((unit / p.n_tiles) * CG + static_cast<int>(rank)) * S + g / (N / 64)), unit % p.n_tiles, g % (N / 64));
+        }
         for (int work = unit; work < p.num_work; work += units) {
             const int n_tile = work % p.n_tiles;
             const int st = work / p.n_tiles;
@@ -794,26 +829,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         const int s = j / SL, cs = j % SL;
                         const TileCoord tc = decode_tile(p, (st * CG + static_cast<int>(rank)) * S + s);
                         uint8_t* slab = o_smem + g * Cfg::OT_SLAB;
-                        // Training (res2): the LeakyReLU mask of chunk i = 64 bytes of the activation at this thread's output
-                        // pixel (2y+py, 2x+px). Its loads run TWO chunks ahead of their use (mk[i & 1]; chunks 0 and 1 are
-                        // requested before the slab's barrier and TMEM loads): waiting for them in place, four times per
-                        // slab, was a quarter of this kernel's stall samples.
-                        uint4 mk[2][4];
-                        bool mlive[2];
-#pragma unroll
-                        for (int px = 0; px < 2; ++px)
-                            mlive[px] = p.res2 != nullptr && tc.b < p.B && 2 * (tc.y0 + yl) + n_tile < 2 * p.H && 2 * (tc.x0 + xl) + px < 2 * p.W;
-                        auto mask_load = [&](int i) {  // i = 2 px + half
-                            const int px = i >> 1;
-                            if (mlive[px]) {
-                                const size_t pix = (static_cast<size_t>(tc.b) * (2 * p.H) + 2 * (tc.y0 + yl) + n_tile) * (2 * p.W) + 2 * (tc.x0 + xl) + px;
-                                const uint4* m4 = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.res2) + pix * p.res2_cs + cs * 64 + (i & 1) * 32);
-#pragma unroll
-                                for (int k = 0; k < 4; ++k) mk[i & 1][k] = __ldg(m4 + k);
-                            }
-                        };
-                        mask_load(0);
-                        mask_load(1);
+                        if constexpr (!T4_ONE_SLAB) t4_mask_begin(tc, n_tile, cs);  // (else requested one slab ago)
                         if (issuer) bulk_wait_read<0>();
                         named_bar_sync(bar_id, 128);
                         // chunk i: px = i >> 1, 32-channel half = i & 1
@@ -827,10 +843,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             if (p.res2 != nullptr) {
                                 // LeakyReLU backward of the layer below, fused (mask loaded two chunks ahead, see above)
                                 const int ci = px * 2 + (((c - cs * 64) >> 5) & 1);  // this chunk's index in the slab
-                                if (mlive[px]) {
+                                if (t4_live[px]) {
 #pragma unroll
                                     for (int i = 0; i < 4; ++i) {
-                                        const uint4 m = mk[ci & 1][i];
+                                        const uint4 m = t4_mk[ci & 1][i];
                                         const uint32_t w[4] = {m.x, m.y, m.z, m.w};
 #pragma unroll
                                         for (int e = 0; e < 4; ++e) {
@@ -841,21 +857,27 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                         }
                                     }
                                 }
-                                if (ci + 2 < 4) mask_load(ci + 2);
+                                if (ci + 2 < 4) t4_mask_load(ci + 2, tc, n_tile, cs);
                             }
+                            if (p.linear) {  // zero bias, slope 1 (training data gradients): nothing to add or select
 #pragma unroll
-                            for (int jj = 0; jj < 8; ++jj) {
-                                const float4 bb = __ldg(b4 + jj);
-                                float f0 = __uint_as_float(v[4 * jj + 0]) + bb.x;
-                                float f1 = __uint_as_float(v[4 * jj + 1]) + bb.y;
-                                float f2 = __uint_as_float(v[4 * jj + 2]) + bb.z;
-                                float f3 = __uint_as_float(v[4 * jj + 3]) + bb.w;
-                                f0 = f0 > 0.f ? f0 : f0 * slope;
-                                f1 = f1 > 0.f ? f1 : f1 * slope;
-                                f2 = f2 > 0.f ? f2 : f2 * slope;
-                                f3 = f3 > 0.f ? f3 : f3 * slope;
-                                pk[2 * jj + 0] = pack_bf16x2(f0, f1);
-                                pk[2 * jj + 1] = pack_bf16x2(f2, f3);
+                                for (int jj = 0; jj < 16; ++jj)
+                                    pk[jj] = pack_bf16x2(__uint_as_float(v[2 * jj]), __uint_as_float(v[2 * jj + 1]));
+                            } else {
+#pragma unroll
+                                for (int jj = 0; jj < 8; ++jj) {
+                                    const float4 bb = __ldg(b4 + jj);
+                                    float f0 = __uint_as_float(v[4 * jj + 0]) + bb.x;
+                                    float f1 = __uint_as_float(v[4 * jj + 1]) + bb.y;
+                                    float f2 = __uint_as_float(v[4 * jj + 2]) + bb.z;
+                                    float f3 = __uint_as_float(v[4 * jj + 3]) + bb.w;
+                                    f0 = f0 > 0.f ? f0 : f0 * slope;
+                                    f1 = f1 > 0.f ? f1 : f1 * slope;
+                                    f2 = f2 > 0.f ? f2 : f2 * slope;
+                                    f3 = f3 > 0.f ? f3 : f3 * slope;
+                                    pk[2 * jj + 0] = pack_bf16x2(f0, f1);
+                                    pk[2 * jj + 1] = pack_bf16x2(f2, f3);
+                                }
                             }
                             const int orow_i = yl * 16 + 2 * xl + px;
                             uint8_t* rowp = slab + orow_i * 128;
@@ -867,6 +889,11 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                              pk[4 * jj + 3]);
                             }
                         });
+                        if constexpr (T4_ONE_SLAB) {  // the mask registers are free: request the next work item's first chunks
+                            const int wn = work + units;
+                            if (wn < p.num_work)
+                                t4_mask_begin(decode_tile(p, ((wn / p.n_tiles) * CG + static_cast<int>(rank)) * S + s), wn % p.n_tiles, cs);
+                        }
                         fence_proxy_async();
                         named_bar_sync(bar_id, 128);
                         if (issuer) {

@@ -601,6 +601,7 @@ static ConvParams conv_base(const TrainRun& r, int lv, int k_ch, int n_ch) {
     p.cout = n_ch;
     p.w_rows_per_tap = n_ch;
     p.slope = 1.f;
+    p.linear = 1;  // (zero bias, slope 1: what the data-gradient launches keep; the forward convs set their own bias and do not read it)
     return p;
 }
 
