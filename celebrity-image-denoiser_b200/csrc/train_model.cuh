@@ -64,7 +64,7 @@ struct cid_train {
     int gd_n[12] = {0};               // tile width N of the pack's tensor map
     void* df_w[4] = {nullptr};        // discriminator forward packs (conv1..3)
     void* dd_w[4] = {nullptr};        // discriminator data-gradient packs (conv1..3)
-    CUtensorMap df_tm[4], dd_tm[4], dd_tmh[4];
+    CUtensorMap df_tm[4], df_tmh[4], dd_tm[4], dd_tmh[4];  // (tmh: half-height weight boxes of the CTA-pair launches)
     float* zero_bias = nullptr;       // 512 zeros
     float* d_bias_pad[4] = {nullptr}; // fp32 conv biases padded for float4 epilogue loads
     double* dsc = nullptr;            // double scratch: BN sums, backward sums, losses
@@ -474,6 +474,7 @@ static int train_alloc_packs(cid_train* t) {
         CID_CHECK_CUDA(cudaMalloc(&t->df_w[l], n * 2));
         CID_CHECK_CUDA(cudaMalloc(&t->dd_w[l], n * 2));
         if (make_weight_map(&t->df_tm[l], t->df_w[l], (s2 ? 16 : 9) * cout, cin, cout)) return 1;
+        if (make_weight_map(&t->df_tmh[l], t->df_w[l], (s2 ? 16 : 9) * cout, cin, cout / 2)) return 1;
         if (make_weight_map(&t->dd_tm[l], t->dd_w[l], (s2 ? 16 : 9) * cin, cout, cin)) return 1;
         if (make_weight_map(&t->dd_tmh[l], t->dd_w[l], (s2 ? 16 : 9) * cin, cout, cin / 2)) return 1;
     }
@@ -707,7 +708,7 @@ static int d_forward(const TrainRun& r, const float* img) {
         p.out_f32 = static_cast<float*>(r.tbuf(TB_DZ1D));
         p.stats = t->dsc + DS_BN + 0 * 256;  // batch statistics reduced in the epilogue
         CID_CHECK_CUDA(cudaMemsetAsync(p.stats, 0, 256 * 8, r.st));
-        if (launch_conv_t<64, 16, 2, false, EPI_LRELU_BN, 9, 1>(t, *tmA, t->df_tm[1], *tmO, p, r.st)) return 1;
+        if (launch_conv_t<64, 16, 2, false, EPI_LRELU_BN, 9, 1, 2>(t, *tmA, t->df_tmh[1], *tmO, p, r.st)) return 1;  // CTA pair
     }
     if (bn_forward(r, 1, r.tbuf(TB_DZ1D), r.tbuf(TB_DA1), 1)) return 1;
     {  // model.5: 3x3 64 -> 128 -> z2
@@ -720,7 +721,9 @@ static int d_forward(const TrainRun& r, const float* img) {
         p.out_f32 = static_cast<float*>(r.tbuf(TB_DZ2D));
         p.stats = t->dsc + DS_BN + 1 * 256;  // batch statistics reduced in the epilogue
         CID_CHECK_CUDA(cudaMemsetAsync(p.stats, 0, 256 * 8, r.st));
-        if (launch_conv_t<128, 9, 2, false, EPI_LRELU_BN, 10, 1>(t, *tmA, t->df_tm[2], *tmO, p, r.st)) return 1;
+        // CTA pair (as the generator's same-shaped down2.0): with K = 64 a weight tile feeds only 8 MMAs - the single-CTA form
+        // waited on weight tiles (tensor pipe 46 % busy)
+        if (launch_conv_t<128, 9, 2, false, EPI_LRELU_BN, 10, 1, 2>(t, *tmA, t->df_tmh[2], *tmO, p, r.st)) return 1;
     }
     if (bn_forward(r, 2, r.tbuf(TB_DZ2D), r.tbuf(TB_DA2), 1)) return 1;
     {  // model.8: 3x3 stride 2 128 -> 128 -> z3
@@ -733,7 +736,7 @@ static int d_forward(const TrainRun& r, const float* img) {
         p.out_f32 = static_cast<float*>(r.tbuf(TB_DZ3D));
         p.stats = t->dsc + DS_BN + 2 * 256;  // batch statistics reduced in the epilogue
         CID_CHECK_CUDA(cudaMemsetAsync(p.stats, 0, 256 * 8, r.st));
-        if (launch_conv_t<128, 16, 2, false, EPI_LRELU_BN, 9, 1>(t, *tmA, t->df_tm[3], *tmO, p, r.st)) return 1;
+        if (launch_conv_t<128, 16, 2, false, EPI_LRELU_BN, 9, 1, 2>(t, *tmA, t->df_tmh[3], *tmO, p, r.st)) return 1;  // CTA pair
     }
     if (bn_forward(r, 3, r.tbuf(TB_DZ3D), r.tbuf(TB_DA3), 2)) return 1;
     CID_CHECK_CUDA(cudaMemsetAsync(t->fsc + FS_POOLED, 0, static_cast<size_t>(B) * 128 * 4, r.st));
