@@ -810,7 +810,7 @@ static int d_backward(const TrainRun& r, const float* img, float target, float s
         ConvParams p = conv_base(r, 2, 128, 128);
         p.n_tiles = 2;
         p.out = r.tbuf(TB_DG2); p.out_cs = 128;
-        if (launch_conv_t<128, 8, 1, false, EPI_T4, 10, 1>(t, *tmA, t->dd_tm[3], *tmO, p, r.st)) return 1;
+        if (launch_conv_t<128, 8, 1, false, EPI_T4, 10, 1, 2>(t, *tmA, t->dd_tmh[3], *tmO, p, r.st)) return 1;  // CTA pair
     }
     // layer 2 (model.5 / model.6)
     if (bn_backward(r, 2, r.tbuf(TB_DZ2D), r.tbuf(TB_DG2), r.tbuf(TB_DG2), 1, param_grads)) return 1;
