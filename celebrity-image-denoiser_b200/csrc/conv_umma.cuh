@@ -713,20 +713,6 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                     }
                                 }
                             }
-                            if constexpr (EPI == EPI_DGRAD) {
-                                // zero the gradient where the activation (bf16, post-ReLU: >= 0) is not positive
-#pragma unroll
-                                for (int i = 0; i < 4; ++i) {
-                                    const uint4 m = rv2[ch * 4 + i];
-                                    const uint32_t w[4] = {m.x, m.y, m.z, m.w};
-#pragma unroll
-                                    for (int e = 0; e < 4; ++e) {
-                                        const int col = (i * 4 + e) * 2;
-                                        if (!(__uint_as_float(w[e] << 16) > 0.f)) v[col] = 0u;
-                                        if (!(__uint_as_float(w[e] & 0xffff0000u) > 0.f)) v[col + 1] = 0u;
-                                    }
-                                }
-                            }
 #pragma unroll
                             for (int jj = 0; jj < 8; ++jj) {
                                 const float4 bb = EPI == EPI_DGRAD ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldg(b4 + jj);
@@ -748,6 +734,19 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                         st_shared_v4(dst, __float_as_uint(f0), __float_as_uint(f1), __float_as_uint(f2), __float_as_uint(f3));
                                     else
                                         st_shared_v4(dst, 0u, 0u, 0u, 0u);
+                                }
+                            }
+                            if constexpr (EPI == EPI_DGRAD) {
+                                // zero the gradient where the activation (bf16, post-ReLU: >= 0) is not positive: on the
+                                // packed pairs, one packed compare (0xffff per true half) and one AND per two values
+                                const __nv_bfloat162 zero2 = __float2bfloat162_rn(0.f);
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) {
+                                    const uint4 m = rv2[ch * 4 + i];
+                                    const uint32_t w[4] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+                                    for (int e = 0; e < 4; ++e)
+                                        pk[i * 4 + e] &= __hgt2_mask(*reinterpret_cast<const __nv_bfloat162*>(&w[e]), zero2);
                                 }
                             }
                             if constexpr (TS && EPI != EPI_LRELU_BN) {

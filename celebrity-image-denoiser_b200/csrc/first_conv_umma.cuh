@@ -344,12 +344,8 @@ first_conv_umma_kernel(const __grid_constant__ CUtensorMap tmO, const FirstParam
                             const uint4 m = *reinterpret_cast<const uint4*>(mrow + (((ch * 4 + i) ^ (row & 7)) << 4));
                             const uint32_t w[4] = {m.x, m.y, m.z, m.w};
 #pragma unroll
-                            for (int e = 0; e < 4; ++e) {
-                                uint32_t keep = 0u;
-                                if (__uint_as_float(w[e] << 16) > 0.f) keep |= 0x0000ffffu;
-                                if (__uint_as_float(w[e] & 0xffff0000u) > 0.f) keep |= 0xffff0000u;
-                                pk[i * 4 + e] &= keep;
-                            }
+                            for (int e = 0; e < 4; ++e)  // one packed compare (0xffff per positive half) + one AND per pair
+                                pk[i * 4 + e] &= __hgt2_mask(*reinterpret_cast<const __nv_bfloat162*>(&w[e]), __float2bfloat162_rn(0.f));
                         }
                     }
                 }
