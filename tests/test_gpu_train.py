@@ -75,6 +75,27 @@ def test_gradients_match_oracle(B, H, W):
     tr.close()
 
 
+@pytest.mark.parametrize("B,H,W", [(2, 24, 20), (4, 36, 44)])
+def test_generator_gradients_with_partial_tiles_in_both_dimensions(B, H, W):
+    """W % 8 = 4 and H % 16 = 8 / 4: every kernel of the step (tile 8 x 16 pixels) clips a tile in x AND in y at every level,
+    including the fused 3-channel weight-gradient kernel's source windows. Generator side only: the discriminator's
+    end-to-end tolerance is precision-limited at such small batches (its kernels are checked at these shapes by
+    test_discriminator_backward_kernels_given_their_own_forward)."""
+    og, od, tr, noisy, clean = _make(9, B, H, W)
+    ref = to.instrumented_gradients(og, od, noisy, clean)
+    nz, cl = noisy.cuda().contiguous(), clean.cuda().contiguous()
+    tr.d_backward(nz, cl)
+    tr.g_backward(nz, cl)
+    g_grads = tr.grads("generator")
+    L = tr.losses()
+    for k in ("d_loss", "g_loss", "content", "adv"):
+        assert abs(L[k] - ref[k]) <= 2e-3 * abs(ref[k]) + 1e-5, (k, L[k], ref[k])
+    for k, want in ref["g_grads"].items():
+        rel, cos = _rel_cos(g_grads[k].cpu().reshape(want.shape), want)
+        assert cos >= 0.997 and rel <= 8e-2, ("generator", k, rel, cos)
+    tr.close()
+
+
 def test_activation_gradients_match_oracle():
     B, H, W = 4, 32, 32
     og, od, tr, noisy, clean = _make(3, B, H, W)
@@ -91,14 +112,15 @@ def test_activation_gradients_match_oracle():
     tr.close()
 
 
-def test_discriminator_backward_kernels_given_their_own_forward():
-    """Separates precision from kernels for the discriminator (whose end-to-end gradient tolerance is loose because bf16
+@pytest.mark.parametrize("B,H,W", [(4, 32, 32), (2, 24, 20), (4, 36, 44)])
+def test_discriminator_backward_kernels_given_their_own_forward(B, H, W):
+    """(The second and third shapes leave partial tiles in BOTH dimensions at every level: W % 8 = 4, H % 16 = 8 / 4.)
+    Separates precision from kernels for the discriminator (whose end-to-end gradient tolerance is loose because bf16
     forward differences flip LeakyReLU signs): every backward stage is recomputed in fp32 torch FROM THE TENSORS THE GPU
     PASS ITSELF STORED (its fp32 pre-BatchNorm z, its bf16 activations, its own upstream gradient) and compared with
     what the next kernel produced. With the forward held fixed only the backward kernels' own round-off is left
     (bf16 weights in the data-gradient convs, bf16 storage of each result): tight."""
     F = torch.nn.functional
-    B, H, W = 4, 32, 32
     og, od, tr, noisy, clean = _make(5, B, H, W)
     tr.d_backward(noisy.cuda().contiguous(), clean.cuda().contiguous())  # buffers now hold the pass on G(noisy), target 0
     m = od.model
